@@ -1,0 +1,148 @@
+/* mibmi.h -- C-ABI of the B200-native int8 edgeEEGNet / MI-BMInet inference path.
+ *
+ * Plain C, no torch types.  This is the boundary a maintainer of the reference binds against; it
+ * replaces, for the integer-inference hot path only, the reference's
+ *
+ *   void net_model_compute(const int8_t* p_data, int8_t* p_output);
+ *        edge-eegnet_wolf/src/cl/net/model.h:40, implemented in src/cl/net/model.c:42-106
+ *
+ * whose network is baked in at link time from the generated arrays of
+ *   edge-eegnet_wolf/data/gen_net_header.py:109-224  (net.h / net.c).
+ * Here the same arrays are handed over at run time (mibmi_params_t), one handle per network, and a
+ * call processes a whole batch of independent trials on the GPU.
+ *
+ * Integer semantics are the reference's: int8 operands, int32 accumulation,
+ * requantisation (acc + offset) / factor with C truncating division (divisor of either sign),
+ * clip = __CLIP_R(x, 127) = [-128, 127], '>>' arithmetic.
+ *
+ * All functions return MIBMI_OK (0) or a negative mibmi_status; nothing prints or aborts.  There is
+ * no CPU fallback: without a CUDA device every compute entry point returns MIBMI_ERR_CUDA.
+ * Distinct handles may be used concurrently from different threads; one handle may be used from
+ * several threads as long as each call is given its own stream (the handle is read-only after
+ * creation, except for mibmi_set_option and the *_host entry points, which own staging buffers).
+ */
+#ifndef MIBMI_H
+#define MIBMI_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MIBMI_VERSION 100 /* 0.1.0 */
+
+#if defined(__GNUC__)
+#define MIBMI_API __attribute__((visibility("default")))
+#else
+#define MIBMI_API
+#endif
+
+typedef enum {
+    MIBMI_OK = 0,
+    MIBMI_ERR_NULL = -1,        /* null pointer argument */
+    MIBMI_ERR_SHAPE = -2,       /* unsupported or inconsistent network dimensions */
+    MIBMI_ERR_PARAM = -3,       /* invalid parameter value (zero divisor, bad layout / option ...) */
+    MIBMI_ERR_ALIGN = -4,       /* device pointer not sufficiently aligned for the selected layout */
+    MIBMI_ERR_CUDA = -5,        /* CUDA runtime error (see mibmi_last_cuda_error) or no device */
+    MIBMI_ERR_UNSUPPORTED = -6  /* request valid but not available on the forced kernel path */
+} mibmi_status;
+
+/* Input layouts of one batch of trials (int8, values in [-127, 127] as produced by
+ * gen_input_header.py:73; -128 is accepted and handled exactly). */
+#define MIBMI_LAYOUT_BCT 0  /* [B][C][T]        -- module order, edgeEEGNet.forward x[B,1,C,T]         */
+#define MIBMI_LAYOUT_BTC 1  /* [B][T][C_ALIGN]  -- Wolf order of net_model_compute (gen_input_header.py:75-76) */
+
+/* Network description: the exported arrays of gen_net_header.py (names without the "net_" prefix).
+ * All pointers are HOST pointers; mibmi_create copies what it needs. */
+typedef struct {
+    int32_t C, T;          /* EEG channels, samples per trial                     (NET_C, NET_T)          */
+    int32_t F1, D, F2, N;  /* F2 must equal F1*D and D == 1 (golden_model.py:169); N classes               */
+    int32_t Nf;            /* temporal filter length, must be 64 (golden_model.py:216-219)                */
+    int32_t reorder_bn;    /* 1: REORDER_BN build (Makefile:34, canonical); 0: plain variant (follows the C) */
+
+    const int32_t* l1_factor;          /* [F2]            gen_net_header.py:109 */
+    const int32_t* l1_offset;          /* [F2]            :110                  */
+    const int8_t*  l1_weight_align;    /* [F2][C_ALIGN]   :114 (dot-product order, rows padded to 4)     */
+    const int32_t* l2_factor;          /* [F2]            :149 (already x8 for the pooling)              */
+    const int32_t* l2_offset;          /* [F2]            :150                  */
+    const int8_t*  l2_weight_reverse;  /* [F2][64]        :154 (torch / cross-correlation order)         */
+    int32_t        l3_factor;          /* NET_L3_FACTOR   :175                  */
+    const int8_t*  l3_weight;          /* [F2][16]        :177 (flipped: true-convolution order)         */
+    const int32_t* l4_factor;          /* [F2]            :194                  */
+    const int32_t* l4_offset;          /* [F2]            :195                  */
+    const int8_t*  l4_weight;          /* [F2 out][F2 in] :197                  */
+    int32_t        l5_factor;          /* NET_L5_FACTOR   :221                  */
+    const int8_t*  l5_bias;            /* [N]             :222                  */
+    const int8_t*  l5_weight;          /* [N][F2*T64_ALIGN] :224 (each row of T64 padded to 4)           */
+} mibmi_params_t;
+
+typedef struct mibmi_net mibmi_net_t; /* opaque */
+
+/* Kernel paths (mibmi_set_option(MIBMI_OPT_FORCE_PATH, ...), mibmi_last_path). */
+#define MIBMI_PATH_AUTO 0     /* fused tensor-core kernel when the network qualifies, else generic    */
+#define MIBMI_PATH_GENERIC 1  /* exact reference-order kernel: any shape, both reorder_bn modes, taps */
+#define MIBMI_PATH_FUSED 2    /* fused sm_100a kernel (int8 MMA + magic-number requantisation)        */
+
+#define MIBMI_OPT_FORCE_PATH 1
+#define MIBMI_OPT_CTAS_PER_SM 2   /* 0 = default */
+#define MIBMI_OPT_HOST_CHUNK 3    /* trials per H2D/compute/D2H chunk of the *_host entry point; 0 = default */
+
+MIBMI_API int mibmi_version(void);
+MIBMI_API const char* mibmi_strerror(int status);
+/* cudaError_t of the most recent failing CUDA call on this handle (0 if none). */
+MIBMI_API int mibmi_last_cuda_error(const mibmi_net_t* net);
+
+/* Validate and upload a network to `device` (CUDA ordinal). */
+MIBMI_API int mibmi_create(const mibmi_params_t* params, int device, mibmi_net_t** out);
+MIBMI_API int mibmi_destroy(mibmi_net_t* net);
+
+MIBMI_API int mibmi_set_option(mibmi_net_t* net, int option, int64_t value);
+/* Which path the most recent forward on this handle ran (MIBMI_PATH_GENERIC / MIBMI_PATH_FUSED). */
+MIBMI_API int mibmi_last_path(const mibmi_net_t* net);
+/* 1 if the fused path can run this network (shape supported, requant parameters within the proven
+ * range of the magic-number division), else 0 with the reason in *why (static string, may be NULL). */
+MIBMI_API int mibmi_fused_supported(const mibmi_net_t* net, const char** why);
+/* Kernel launches issued on behalf of this handle since creation (evidence counter). */
+MIBMI_API int64_t mibmi_launch_count(const mibmi_net_t* net);
+
+/* Batched forward, device buffers, asynchronous on `stream` (a cudaStream_t, may be NULL).
+ *   x_dev      int8, B trials in `layout`; 16-byte aligned
+ *   logits_dev int8 [B][N], caller-allocated; 4-byte aligned
+ * Replaces B calls of net_model_compute (model.c:42). */
+MIBMI_API int mibmi_forward_int8(mibmi_net_t* net, const int8_t* x_dev, int64_t B, int layout,
+                       int8_t* logits_dev, void* stream);
+
+/* Same, plus the inter-layer activations (the taps of QuantLab/export_net_data.py:112-167 in integer
+ * form).  Any of the tap pointers may be NULL.  Runs the generic path.
+ *   y1 [B][F2][T], y2 [B][F2][T/8], y3 [B][F2][T/8], y4 [B][F2][T/64]  (int8, device) */
+MIBMI_API int mibmi_forward_int8_taps(mibmi_net_t* net, const int8_t* x_dev, int64_t B, int layout,
+                            int8_t* logits_dev, int8_t* y1, int8_t* y2, int8_t* y3, int8_t* y4,
+                            void* stream);
+
+/* End-to-end convenience for callers that hold HOST buffers (what a cgo / ctypes caller of the
+ * reference has): chunked H2D copy -> forward -> D2H copy, double-buffered on two internal streams
+ * through pinned staging memory.  Synchronous: returns when logits_host is complete. */
+MIBMI_API int mibmi_forward_int8_host(mibmi_net_t* net, const int8_t* x_host, int64_t B, int layout,
+                            int8_t* logits_host);
+
+/* Input quantisation pre-op (gen_input_header.py:73, STEActivation with floorToZero,
+ * QuantLab/quantlab/indiv/ste_ops.py:88-102):  q = trunc(clip(x / abs_max, -1, 1) * 127).
+ * x_dev float32 [n] -> q_dev int8 [n] (same element order). */
+MIBMI_API int mibmi_quantize_input_f32(const float* x_dev, int64_t n, float abs_max, int8_t* q_dev, void* stream);
+/* Output de-quantisation post-op (functional.py:338-353): y = q / 127 * abs_max. */
+MIBMI_API int mibmi_dequantize_logits_f32(const int8_t* q_dev, int64_t n, float abs_max, float* y_dev, void* stream);
+
+/* Diagnostics: the (magic, shift) pair the fused path uses for a positive divisor d >= 4, such that
+ * trunc(x / d) == (mulhi32(x, magic) >> shift) + (x < 0) for |x| < 2^29.  MIBMI_ERR_PARAM if d < 4. */
+MIBMI_API int mibmi_debug_magic(int32_t d, int32_t* magic, int32_t* shift);
+/* Diagnostics (no GPU needed): writes the packed network the fused kernel reads into out[cap] and
+ * returns its size; out == NULL only queries the size.  MIBMI_ERR_UNSUPPORTED (+ *why) if the fused
+ * path cannot run this network. */
+MIBMI_API int64_t mibmi_debug_pack_fused(const mibmi_params_t* params, void* out, int64_t cap, const char** why);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MIBMI_H */

@@ -1,0 +1,474 @@
+// C-ABI of libmibmi.so (include/mibmi.h): validation, parameter packing, dispatch, host staging.
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <atomic>
+#include <mutex>
+#include <new>
+#include <vector>
+
+#include "../../include/mibmi.h"
+#include "mibmi_common.cuh"
+#include "mibmi_kernels.h"
+
+using namespace mibmi;
+
+struct mibmi_net {
+    int device = 0, num_sms = 0;
+    int C = 0, T = 0, F2 = 0, N = 0, reorder = 1;
+    GenericNet* gen_dev = nullptr;
+    int8_t* w5_dev = nullptr;
+    FusedNet* fused_dev = nullptr;
+    bool fused_ok = false;
+    const char* fused_why = "";
+    int force_path = MIBMI_PATH_AUTO, ctas_per_sm = 0;
+    int64_t host_chunk = 0;
+    std::atomic<int> last_path{0};
+    std::atomic<int> last_cuda{0};
+    std::atomic<int64_t> launches{0};
+    // host entry point staging (guarded by host_mu)
+    std::mutex host_mu;
+    cudaStream_t hs[2] = {nullptr, nullptr};
+    int8_t* hx_dev[2] = {nullptr, nullptr};
+    int8_t* hy_dev[2] = {nullptr, nullptr};
+    int8_t* hx_pin[2] = {nullptr, nullptr};
+    int8_t* hy_pin[2] = {nullptr, nullptr};
+    int64_t h_cap = 0;
+};
+
+namespace {
+
+struct DeviceGuard {
+    int prev = -1;
+    cudaError_t err;
+    explicit DeviceGuard(int dev) {
+        err = cudaGetDevice(&prev);
+        if (err == cudaSuccess && prev != dev) err = cudaSetDevice(dev);
+    }
+    ~DeviceGuard() {
+        int cur = -1;
+        if (prev >= 0 && cudaGetDevice(&cur) == cudaSuccess && cur != prev) cudaSetDevice(prev);
+    }
+};
+
+inline int fail_cuda(mibmi_net* n, cudaError_t e) {
+    if (n) n->last_cuda.store((int)e);
+    return MIBMI_ERR_CUDA;
+}
+inline int align4(int d) { return (d + 3) / 4 * 4; }
+inline int64_t iabs64(int64_t v) { return v < 0 ? -v : v; }
+
+// tdiv(x, d) == (mulhi(x, m) >> s) + (x < 0)  for d >= 4 and |x| < 2^29  (proved in DESIGN.md,
+// brute-forced in tests/test_host_logic.py through mibmi_debug_magic).
+bool magic_for(int64_t d, int* m, int* s) {
+    if (d < 4 || d > 0x7fffffff) return false;
+    int lg = 0;
+    while ((int64_t(1) << (lg + 1)) <= d) lg++;   // floor(log2 d) >= 2
+    const int p = 30 + lg;
+    const int64_t mm = (int64_t)(((__int128)1 << p) / d) + 1;
+    if (mm >= (int64_t(1) << 31)) return false;
+    *m = (int)mm;
+    *s = p - 32;
+    return true;
+}
+
+constexpr int64_t kMagicRange = int64_t(1) << 29;
+
+struct Pooled { int thr, sig, soff, m, sh; };
+
+// requant of a pooled layer (L2 / L4, REORDER_BN): x = sum_8 max(v, thr) + off, y = clip(x / fac)
+bool pack_pooled(int64_t vmax, int off, int fac, Pooled* o, const char** why) {
+    const int thr = -(off >> 3);
+    const int64_t smax = 8 * (vmax > iabs64(thr) ? vmax : iabs64(thr));
+    if (smax + iabs64(off) >= kMagicRange) { *why = "pooled accumulator outside the magic-division range"; return false; }
+    if (!magic_for(iabs64(fac), &o->m, &o->sh)) { *why = "|factor| < 4 in a pooled layer"; return false; }
+    o->thr = thr;
+    o->sig = fac < 0 ? -1 : 1;
+    o->soff = fac < 0 ? -off : off;
+    return true;
+}
+
+bool pack_fused(const mibmi_params_t* p, FusedNet* f, const char** why) {
+    const int C = p->C, T = p->T, F2 = p->F2, CA = align4(C);
+    const int T64 = (T / 8) / 8, T64A = align4(T64), T64P = align4(T64);
+    memset(f, 0, sizeof(*f));
+    if (F2 != 16 || p->N != 4) { *why = "fused kernel needs F2 == 16 and N == 4"; return false; }
+    if (!p->reorder_bn) { *why = "fused kernel implements the REORDER_BN variant only"; return false; }
+    if (!fused_has_instance(C, T)) { *why = "no fused instantiation for this (C, T)"; return false; }
+    // ---- layer 1: sign of the factor folded into weights and offset
+    for (int k = 0; k < 16; k++) {
+        const int fac = p->l1_factor[k], sg = fac < 0 ? -1 : 1;
+        int64_t sum = 0;
+        for (int c = 0; c < C; c++) {
+            const int w = p->l1_weight_align[k * CA + c];
+            if (sg < 0 && w == -128) { *why = "weight -128 cannot be negated (negative layer-1 factor)"; return false; }
+            sum += iabs64(w);
+        }
+        if (128 * sum + iabs64(p->l1_offset[k]) >= kMagicRange) { *why = "layer-1 accumulator outside the magic-division range"; return false; }
+        if (!magic_for(iabs64(fac), &f->m1[k], &f->sh1[k])) { *why = "|l1_factor| < 4"; return false; }
+        f->off1[k] = sg * p->l1_offset[k];
+    }
+    const int ksteps = (C + 31) / 32;
+    for (int s = 0; s < ksteps; s++)
+        for (int h = 0; h < 2; h++)
+            for (int row = 0; row < 16; row++)
+                for (int q = 0; q < 4; q++) {
+                    uint32_t word = 0;
+                    const int sg = p->l1_factor[row] < 0 ? -1 : 1;
+                    for (int i = 0; i < 4; i++) {
+                        const int c = 32 * s + 16 * h + 4 * i + q;   // K position 16h + 4q + i <-> channel c
+                        const int w = c < C ? sg * p->l1_weight_align[row * CA + c] : 0;
+                        word |= (uint32_t)(uint8_t)(int8_t)w << (8 * i);
+                    }
+                    f->w1frag[((s * 2 + h) * 16 + row) * 4 + q] = word;
+                }
+    // ---- layer 2
+    for (int k = 0; k < 16; k++) {
+        const int8_t* w = p->l2_weight_reverse + k * 64;
+        int64_t sum = 0;
+        for (int j = 0; j < 64; j++) sum += iabs64(w[j]);
+        Pooled po;
+        if (!pack_pooled(128 * sum, p->l2_offset[k], p->l2_factor[k], &po, why)) return false;
+        f->thr2[k] = po.thr; f->sig2[k] = po.sig; f->soff2[k] = po.soff; f->m2[k] = po.m; f->sh2[k] = po.sh;
+        for (int r = 0; r < 4; r++)
+            for (int j = 0; j < 128; j++) {
+                const int tap = j + r - 32;
+                f->w2sh[k * kToepChanBytes + r * kToepCopyStride + j] = (tap >= 0 && tap < 64) ? (uint8_t)w[tap] : 0;
+            }
+    }
+    // ---- layer 3 (exported array is flipped: torch-order tap j = l3_weight[15 - j])
+    {
+        const int sg = p->l3_factor < 0 ? -1 : 1;
+        if (!magic_for(iabs64(p->l3_factor), &f->m3, &f->sh3)) { *why = "|l3_factor| < 4"; return false; }
+        for (int k = 0; k < 16; k++)
+            for (int r = 0; r < 4; r++)
+                for (int i = 0; i < 5; i++) {
+                    uint32_t word = 0;
+                    for (int b = 0; b < 4; b++) {
+                        const int tap = 4 * i + b - r;
+                        int w = (tap >= 0 && tap < 16) ? p->l3_weight[k * 16 + 15 - tap] : 0;
+                        if (sg < 0 && w == -128) { *why = "weight -128 cannot be negated (negative layer-3 factor)"; return false; }
+                        word |= (uint32_t)(uint8_t)(int8_t)(sg * w) << (8 * b);
+                    }
+                    f->w3sh[(k * 4 + r) * 5 + i] = word;
+                }
+    }
+    // ---- layer 4
+    for (int k = 0; k < 16; k++) {
+        const int8_t* w = p->l4_weight + k * 16;
+        int64_t sum = 0;
+        for (int i = 0; i < 16; i++) sum += iabs64(w[i]);
+        Pooled po;
+        if (!pack_pooled(128 * sum, p->l4_offset[k], p->l4_factor[k], &po, why)) return false;
+        f->thr4[k] = po.thr; f->sig4[k] = po.sig; f->soff4[k] = po.soff; f->m4[k] = po.m; f->sh4[k] = po.sh;
+        for (int q = 0; q < 4; q++) {
+            uint32_t word = 0;
+            for (int i = 0; i < 4; i++) word |= (uint32_t)(uint8_t)w[4 * q + i] << (8 * i);
+            f->w4frag[k * 4 + q] = word;
+        }
+    }
+    // ---- layer 5
+    {
+        const int sg = p->l5_factor < 0 ? -1 : 1;
+        if (!magic_for(iabs64(p->l5_factor), &f->m5, &f->sh5)) { *why = "|l5_factor| < 4"; return false; }
+        for (int n = 0; n < 4; n++) {
+            int64_t sum = 0;
+            for (int k = 0; k < 16; k++)
+                for (int t = 0; t < T64; t++) {
+                    const int w = p->l5_weight[(n * 16 + k) * T64A + t];
+                    if (sg < 0 && w == -128) { *why = "weight -128 cannot be negated (negative layer-5 factor)"; return false; }
+                    f->w5p[(n * 16 + k) * T64P + t] = (int8_t)(sg * w);
+                    sum += iabs64(w);
+                }
+            if (128 * sum + 128 >= kMagicRange) { *why = "layer-5 accumulator outside the magic-division range"; return false; }
+            f->b5[n] = sg * p->l5_bias[n];
+        }
+    }
+    return true;
+}
+
+int validate(const mibmi_params_t* p) {
+    if (!p->l1_factor || !p->l1_offset || !p->l1_weight_align || !p->l2_factor || !p->l2_offset ||
+        !p->l2_weight_reverse || !p->l3_weight || !p->l4_factor || !p->l4_offset || !p->l4_weight ||
+        !p->l5_bias || !p->l5_weight)
+        return MIBMI_ERR_NULL;
+    if (p->C < 1 || p->C > kMaxC || p->T < 64 || p->T > (1 << 16)) return MIBMI_ERR_SHAPE;
+    if (p->F2 < 4 || p->F2 > kMaxF2 || p->F2 % 4 != 0) return MIBMI_ERR_SHAPE;       // gen_net_header.py:63
+    if (p->D != 1 || p->F2 != p->F1 * p->D) return MIBMI_ERR_SHAPE;                   // golden_model.py:83,169
+    if (p->Nf != kNf) return MIBMI_ERR_SHAPE;                                         // golden_model.py:216-219
+    if (p->N < 1 || p->N > kMaxN) return MIBMI_ERR_SHAPE;
+    if (generic_smem_bytes(p->T, p->F2) > 220 * 1024) return MIBMI_ERR_SHAPE;
+    if (p->l3_factor == 0 || p->l5_factor == 0) return MIBMI_ERR_PARAM;
+    for (int k = 0; k < p->F2; k++) {
+        if (p->l1_factor[k] == 0 || p->l2_factor[k] == 0 || p->l4_factor[k] == 0) return MIBMI_ERR_PARAM;
+        if (!p->reorder_bn && ((p->l2_factor[k] >> 3) == 0 || (p->l4_factor[k] >> 3) == 0)) return MIBMI_ERR_PARAM;
+    }
+    return MIBMI_OK;
+}
+
+void free_host_staging(mibmi_net* n) {
+    for (int i = 0; i < 2; i++) {
+        if (n->hx_dev[i]) cudaFree(n->hx_dev[i]);
+        if (n->hy_dev[i]) cudaFree(n->hy_dev[i]);
+        if (n->hx_pin[i]) cudaFreeHost(n->hx_pin[i]);
+        if (n->hy_pin[i]) cudaFreeHost(n->hy_pin[i]);
+        n->hx_dev[i] = n->hy_dev[i] = n->hx_pin[i] = n->hy_pin[i] = nullptr;
+    }
+    n->h_cap = 0;
+}
+
+size_t trial_bytes(const mibmi_net* n, int layout) {
+    return layout == MIBMI_LAYOUT_BCT ? (size_t)n->C * n->T : (size_t)n->T * align4(n->C);
+}
+
+int forward_impl(mibmi_net* net, const int8_t* x, int64_t B, int layout, int8_t* logits, int8_t* t1, int8_t* t2,
+                 int8_t* t3, int8_t* t4, bool taps, cudaStream_t stream) {
+    if (!net || !x || !logits) return MIBMI_ERR_NULL;
+    if (B < 0 || (layout != MIBMI_LAYOUT_BCT && layout != MIBMI_LAYOUT_BTC)) return MIBMI_ERR_PARAM;
+    if (B == 0) return MIBMI_OK;
+    if (((uintptr_t)x & 15) != 0 || (net->N == 4 && ((uintptr_t)logits & 3) != 0)) return MIBMI_ERR_ALIGN;
+    int path = net->force_path;
+    const bool fused_possible = net->fused_ok && layout == MIBMI_LAYOUT_BCT && !taps;
+    if (path == MIBMI_PATH_AUTO) path = fused_possible ? MIBMI_PATH_FUSED : MIBMI_PATH_GENERIC;
+    if (path == MIBMI_PATH_FUSED && !fused_possible) return MIBMI_ERR_UNSUPPORTED;
+    DeviceGuard dg(net->device);
+    if (dg.err != cudaSuccess) return fail_cuda(net, dg.err);
+    cudaError_t e;
+    if (path == MIBMI_PATH_FUSED)
+        e = launch_fused(net->fused_dev, net->C, net->T, x, B, logits, net->num_sms, net->ctas_per_sm, stream);
+    else
+        e = launch_generic(net->gen_dev, net->T, net->F2, x, B, layout, logits, t1, t2, t3, t4, net->num_sms, stream);
+    if (e != cudaSuccess) return fail_cuda(net, e);
+    net->last_path.store(path);
+    net->launches.fetch_add(1);
+    return MIBMI_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int mibmi_version(void) { return MIBMI_VERSION; }
+
+const char* mibmi_strerror(int status) {
+    switch (status) {
+        case MIBMI_OK: return "ok";
+        case MIBMI_ERR_NULL: return "null pointer argument";
+        case MIBMI_ERR_SHAPE: return "unsupported or inconsistent network dimensions";
+        case MIBMI_ERR_PARAM: return "invalid parameter value";
+        case MIBMI_ERR_ALIGN: return "device pointer not sufficiently aligned";
+        case MIBMI_ERR_CUDA: return "CUDA error or no CUDA device";
+        case MIBMI_ERR_UNSUPPORTED: return "not available on the forced kernel path";
+        default: return "unknown status";
+    }
+}
+
+int mibmi_last_cuda_error(const mibmi_net_t* net) { return net ? net->last_cuda.load() : 0; }
+int mibmi_last_path(const mibmi_net_t* net) { return net ? net->last_path.load() : 0; }
+int64_t mibmi_launch_count(const mibmi_net_t* net) { return net ? net->launches.load() : 0; }
+
+int mibmi_fused_supported(const mibmi_net_t* net, const char** why) {
+    if (!net) return 0;
+    if (why) *why = net->fused_ok ? "" : net->fused_why;
+    return net->fused_ok ? 1 : 0;
+}
+
+int mibmi_debug_magic(int32_t d, int32_t* m, int32_t* s) {
+    if (!m || !s) return MIBMI_ERR_NULL;
+    return magic_for(d, m, s) ? MIBMI_OK : MIBMI_ERR_PARAM;
+}
+
+// Diagnostics (no GPU needed): the packed network exactly as the fused kernel reads it.
+int64_t mibmi_debug_pack_fused(const mibmi_params_t* p, void* out, int64_t cap, const char** why) {
+    if (!p) return MIBMI_ERR_NULL;
+    int st = validate(p);
+    if (st != MIBMI_OK) return st;
+    if (!out) return (int64_t)sizeof(FusedNet);
+    if (cap < (int64_t)sizeof(FusedNet)) return MIBMI_ERR_PARAM;
+    const char* w = "";
+    const bool ok = pack_fused(p, reinterpret_cast<FusedNet*>(out), &w);
+    if (why) *why = w;
+    return ok ? (int64_t)sizeof(FusedNet) : MIBMI_ERR_UNSUPPORTED;
+}
+
+int mibmi_create(const mibmi_params_t* p, int device, mibmi_net_t** out) {
+    if (!p || !out) return MIBMI_ERR_NULL;
+    *out = nullptr;
+    int st = validate(p);
+    if (st != MIBMI_OK) return st;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) return MIBMI_ERR_CUDA;
+    mibmi_net* n = new (std::nothrow) mibmi_net();
+    if (!n) return MIBMI_ERR_CUDA;
+    n->device = device;
+    n->C = p->C; n->T = p->T; n->F2 = p->F2; n->N = p->N; n->reorder = p->reorder_bn ? 1 : 0;
+    DeviceGuard dg(device);
+    cudaError_t e = dg.err;
+    const int C = p->C, T = p->T, F2 = p->F2, N = p->N, CA = align4(C), T64 = (T / 8) / 8, T64A = align4(T64);
+    std::vector<int8_t> w5((size_t)N * F2 * T64);
+    GenericNet* g = new (std::nothrow) GenericNet();
+    FusedNet* f = new (std::nothrow) FusedNet();
+    if (!g || !f) { delete g; delete f; delete n; return MIBMI_ERR_CUDA; }
+    memset(g, 0, sizeof(*g));
+    g->C = C; g->T = T; g->F2 = F2; g->N = N; g->T8 = T / 8; g->T64 = T64; g->reorder = n->reorder;
+    for (int k = 0; k < F2; k++) {
+        g->fac1[k] = p->l1_factor[k]; g->off1[k] = p->l1_offset[k];
+        g->fac2[k] = p->l2_factor[k]; g->off2[k] = p->l2_offset[k];
+        g->fac4[k] = p->l4_factor[k]; g->off4[k] = p->l4_offset[k];
+        for (int c = 0; c < C; c++) g->w1[k * C + c] = p->l1_weight_align[k * CA + c];
+        for (int j = 0; j < kNf; j++) g->w2[k * kNf + j] = p->l2_weight_reverse[k * kNf + j];
+        for (int j = 0; j < kL3Taps; j++) g->w3[k * kL3Taps + j] = p->l3_weight[k * kL3Taps + (kL3Taps - 1 - j)];
+        for (int i = 0; i < F2; i++) g->w4[k * F2 + i] = p->l4_weight[k * F2 + i];
+    }
+    g->fac3 = p->l3_factor; g->fac5 = p->l5_factor;
+    for (int c = 0; c < N; c++) {
+        g->b5[c] = p->l5_bias[c];
+        for (int k = 0; k < F2; k++)
+            for (int t = 0; t < T64; t++) w5[((size_t)c * F2 + k) * T64 + t] = p->l5_weight[((size_t)c * F2 + k) * T64A + t];
+    }
+    n->fused_ok = pack_fused(p, f, &n->fused_why);
+
+    cudaDeviceProp prop;
+    if (e == cudaSuccess) e = cudaGetDeviceProperties(&prop, device);
+    if (e == cudaSuccess) n->num_sms = prop.multiProcessorCount;
+    if (e == cudaSuccess) e = cudaMalloc(&n->w5_dev, w5.size() ? w5.size() : 1);
+    if (e == cudaSuccess) e = cudaMemcpy(n->w5_dev, w5.data(), w5.size(), cudaMemcpyHostToDevice);
+    g->w5 = n->w5_dev;
+    if (e == cudaSuccess) e = cudaMalloc(&n->gen_dev, sizeof(GenericNet));
+    if (e == cudaSuccess) e = cudaMemcpy(n->gen_dev, g, sizeof(GenericNet), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess && n->fused_ok) {
+        e = cudaMalloc(&n->fused_dev, sizeof(FusedNet));
+        if (e == cudaSuccess) e = cudaMemcpy(n->fused_dev, f, sizeof(FusedNet), cudaMemcpyHostToDevice);
+    }
+    delete g;
+    delete f;
+    if (e != cudaSuccess) {
+        mibmi_destroy(n);
+        return MIBMI_ERR_CUDA;
+    }
+    *out = n;
+    return MIBMI_OK;
+}
+
+int mibmi_destroy(mibmi_net_t* net) {
+    if (!net) return MIBMI_ERR_NULL;
+    {
+        DeviceGuard dg(net->device);
+        if (net->gen_dev) cudaFree(net->gen_dev);
+        if (net->w5_dev) cudaFree(net->w5_dev);
+        if (net->fused_dev) cudaFree(net->fused_dev);
+        free_host_staging(net);
+        for (int i = 0; i < 2; i++)
+            if (net->hs[i]) cudaStreamDestroy(net->hs[i]);
+    }
+    delete net;
+    return MIBMI_OK;
+}
+
+int mibmi_set_option(mibmi_net_t* net, int option, int64_t value) {
+    if (!net) return MIBMI_ERR_NULL;
+    switch (option) {
+        case MIBMI_OPT_FORCE_PATH:
+            if (value < MIBMI_PATH_AUTO || value > MIBMI_PATH_FUSED) return MIBMI_ERR_PARAM;
+            if (value == MIBMI_PATH_FUSED && !net->fused_ok) return MIBMI_ERR_UNSUPPORTED;
+            net->force_path = (int)value;
+            return MIBMI_OK;
+        case MIBMI_OPT_CTAS_PER_SM:
+            if (value < 0 || value > 8) return MIBMI_ERR_PARAM;
+            net->ctas_per_sm = (int)value;
+            return MIBMI_OK;
+        case MIBMI_OPT_HOST_CHUNK:
+            if (value < 0) return MIBMI_ERR_PARAM;
+            net->host_chunk = value;
+            return MIBMI_OK;
+        default:
+            return MIBMI_ERR_PARAM;
+    }
+}
+
+int mibmi_forward_int8(mibmi_net_t* net, const int8_t* x_dev, int64_t B, int layout, int8_t* logits_dev, void* stream) {
+    return forward_impl(net, x_dev, B, layout, logits_dev, nullptr, nullptr, nullptr, nullptr, false, (cudaStream_t)stream);
+}
+
+int mibmi_forward_int8_taps(mibmi_net_t* net, const int8_t* x_dev, int64_t B, int layout, int8_t* logits_dev,
+                            int8_t* y1, int8_t* y2, int8_t* y3, int8_t* y4, void* stream) {
+    if (net && net->force_path == MIBMI_PATH_FUSED) return MIBMI_ERR_UNSUPPORTED;
+    return forward_impl(net, x_dev, B, layout, logits_dev, y1, y2, y3, y4, true, (cudaStream_t)stream);
+}
+
+int mibmi_forward_int8_host(mibmi_net_t* net, const int8_t* x_host, int64_t B, int layout, int8_t* logits_host) {
+    if (!net || !x_host || !logits_host) return MIBMI_ERR_NULL;
+    if (B < 0 || (layout != MIBMI_LAYOUT_BCT && layout != MIBMI_LAYOUT_BTC)) return MIBMI_ERR_PARAM;
+    if (B == 0) return MIBMI_OK;
+    std::lock_guard<std::mutex> lock(net->host_mu);
+    DeviceGuard dg(net->device);
+    if (dg.err != cudaSuccess) return fail_cuda(net, dg.err);
+    const size_t tb = trial_bytes(net, layout);
+    int64_t chunk = net->host_chunk > 0 ? net->host_chunk : 8192;
+    if (chunk > B) chunk = B;
+    cudaError_t e = cudaSuccess;
+    // is the caller's memory page-locked?  then copy straight from / to it
+    cudaPointerAttributes pa;
+    bool x_pinned = cudaPointerGetAttributes(&pa, x_host) == cudaSuccess && pa.type == cudaMemoryTypeHost;
+    bool y_pinned = cudaPointerGetAttributes(&pa, logits_host) == cudaSuccess && pa.type == cudaMemoryTypeHost;
+    cudaGetLastError();
+    if (net->h_cap < chunk) {
+        free_host_staging(net);
+        for (int i = 0; i < 2 && e == cudaSuccess; i++) {
+            if (!net->hs[i]) e = cudaStreamCreateWithFlags(&net->hs[i], cudaStreamNonBlocking);
+            if (e == cudaSuccess) e = cudaMalloc(&net->hx_dev[i], tb * chunk);
+            if (e == cudaSuccess) e = cudaMalloc(&net->hy_dev[i], (size_t)net->N * chunk);
+            if (e == cudaSuccess) e = cudaMallocHost(&net->hx_pin[i], tb * chunk);
+            if (e == cudaSuccess) e = cudaMallocHost(&net->hy_pin[i], (size_t)net->N * chunk);
+        }
+        if (e != cudaSuccess) { free_host_staging(net); return fail_cuda(net, e); }
+        net->h_cap = chunk;
+    }
+    int status = MIBMI_OK;
+    int64_t pending_lo[2] = {-1, -1}, pending_n[2] = {0, 0};
+    int64_t done = 0;
+    for (int i = 0; done < B || pending_lo[0] >= 0 || pending_lo[1] >= 0; i++) {
+        const int s = i & 1;
+        if (pending_lo[s] >= 0) {   // retire the chunk that used this slot two steps ago
+            e = cudaStreamSynchronize(net->hs[s]);
+            if (e != cudaSuccess) { status = fail_cuda(net, e); break; }
+            if (!y_pinned) memcpy(logits_host + pending_lo[s] * net->N, net->hy_pin[s], (size_t)pending_n[s] * net->N);
+            pending_lo[s] = -1;
+        }
+        if (done >= B) continue;
+        const int64_t nb = B - done < chunk ? B - done : chunk;
+        const int8_t* src = x_host + (size_t)done * tb;
+        if (!x_pinned) { memcpy(net->hx_pin[s], src, tb * nb); src = net->hx_pin[s]; }
+        e = cudaMemcpyAsync(net->hx_dev[s], src, tb * nb, cudaMemcpyHostToDevice, net->hs[s]);
+        if (e != cudaSuccess) { status = fail_cuda(net, e); break; }
+        status = forward_impl(net, net->hx_dev[s], nb, layout, net->hy_dev[s], nullptr, nullptr, nullptr, nullptr, false, net->hs[s]);
+        if (status != MIBMI_OK) break;
+        int8_t* dst = y_pinned ? logits_host + (size_t)done * net->N : net->hy_pin[s];
+        e = cudaMemcpyAsync(dst, net->hy_dev[s], (size_t)nb * net->N, cudaMemcpyDeviceToHost, net->hs[s]);
+        if (e != cudaSuccess) { status = fail_cuda(net, e); break; }
+        pending_lo[s] = done;
+        pending_n[s] = nb;
+        done += nb;
+    }
+    if (status != MIBMI_OK) {
+        cudaStreamSynchronize(net->hs[0]);
+        cudaStreamSynchronize(net->hs[1]);
+    }
+    return status;
+}
+
+int mibmi_quantize_input_f32(const float* x_dev, int64_t n, float abs_max, int8_t* q_dev, void* stream) {
+    if (!x_dev || !q_dev) return MIBMI_ERR_NULL;
+    if (n < 0 || !(abs_max > 0.0f)) return MIBMI_ERR_PARAM;
+    return launch_quantize(x_dev, n, abs_max, q_dev, (cudaStream_t)stream) == cudaSuccess ? MIBMI_OK : MIBMI_ERR_CUDA;
+}
+
+int mibmi_dequantize_logits_f32(const int8_t* q_dev, int64_t n, float abs_max, float* y_dev, void* stream) {
+    if (!q_dev || !y_dev) return MIBMI_ERR_NULL;
+    if (n < 0) return MIBMI_ERR_PARAM;
+    return launch_dequantize(q_dev, n, abs_max, y_dev, (cudaStream_t)stream) == cudaSuccess ? MIBMI_OK : MIBMI_ERR_CUDA;
+}
+
+}  // extern "C"

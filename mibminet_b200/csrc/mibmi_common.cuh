@@ -1,0 +1,71 @@
+// Shared device-side definitions of the int8 edgeEEGNet / MI-BMInet path (sm_100a).
+//
+// Reference semantics (edge-eegnet_wolf/src/cl/net/layer1..5.c,
+// python_utils/golden_model.py:153-379): int8 x int8 -> int32 accumulate, requantisation
+// (acc + offset) / factor with C truncating division, clip to [-128, 127].
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace mibmi {
+
+constexpr int kNf = 64;       // temporal filter taps (golden_model.py:216-219)
+constexpr int kL3Taps = 16;   // layer-3 taps
+constexpr int kMaxF2 = 32;
+constexpr int kMaxC = 256;
+constexpr int kMaxN = 8;
+
+// ---------------------------------------------------------------------------------------------
+// Network as the generic (reference-order) kernel reads it.  Lives in global memory.
+struct GenericNet {
+    int C, T, F2, N, T8, T64, reorder;
+    int fac1[kMaxF2], off1[kMaxF2];
+    int fac2[kMaxF2], off2[kMaxF2];
+    int fac4[kMaxF2], off4[kMaxF2];
+    int fac3, fac5;
+    int b5[kMaxN];
+    int8_t w1[kMaxF2 * kMaxC];        // [F2][C]
+    int8_t w2[kMaxF2 * kNf];          // [F2][64]  torch (cross-correlation) order
+    int8_t w3[kMaxF2 * kL3Taps];      // [F2][16]  torch order (exported array un-flipped)
+    int8_t w4[kMaxF2 * kMaxF2];       // [F2 out][F2 in]
+    const int8_t* w5;                 // [N][F2][T64]  device pointer (size depends on T)
+};
+
+// ---------------------------------------------------------------------------------------------
+// Network as the fused kernel reads it (F2 == 16, N == 4, reorder_bn == 1).  Copied to shared
+// memory by every CTA.  Divisors are made positive on the host (the sign is folded into the L1 /
+// L3 / L5 weights and into `sig` for the pooled layers) and replaced by (magic, shift) pairs:
+//   tdiv(x, d) == (mulhi(x, magic) >> shift) + (x < 0)      for |x| < 2^29, d >= 4
+constexpr int kToepCopyStride = 192;                 // bytes between the 4 byte-shifted copies
+constexpr int kToepChanBytes = 4 * kToepCopyStride;  // 768 B per channel
+constexpr int kMaxT64P = 32;                         // padded T/64 (fused path: T <= 2048)
+
+struct FusedNet {
+    // layer 1: A fragments of mma.m16n8k32 [kstep][half][row 16][q 4]
+    uint32_t w1frag[2 * 2 * 16 * 4];
+    int off1[16], m1[16], sh1[16];
+    // layer 2: per channel 4 byte-shifted zero-padded copies of the 64 taps
+    alignas(16) uint8_t w2sh[16 * kToepChanBytes];
+    int thr2[16], sig2[16], soff2[16], m2[16], sh2[16];
+    // layer 3: per channel, per byte phase r, 5 words of shifted taps
+    uint32_t w3sh[16 * 4 * 5];
+    int m3, sh3;
+    // layer 4: A fragments of mma.m16n8k16 [row 16][q 4]
+    uint32_t w4frag[16 * 4];
+    int thr4[16], sig4[16], soff4[16], m4[16], sh4[16];
+    // layer 5: [n 4][k 16][T64P] zero padded, sign folded
+    alignas(16) int8_t w5p[4 * 16 * kMaxT64P];
+    int b5[4];
+    int m5, sh5;
+    int pad_[2];
+};
+static_assert(sizeof(FusedNet) % 16 == 0, "FusedNet is copied with 128-bit accesses");
+
+// C '/' : truncate toward zero.  (The generic kernel uses the hardware sequence as is.)
+__device__ __forceinline__ int clip8(int x) { return min(max(x, -128), 127); }
+
+__device__ __forceinline__ int tdiv_magic(int x, int m, int s) {
+    return (__mulhi(x, m) >> s) + (int)((unsigned)x >> 31);
+}
+
+}  // namespace mibmi

@@ -1,0 +1,192 @@
+"""Host side of the int8 edgeEEGNet / MI-BMInet path: one `Int8Net` = one mibmi handle.
+
+PyTorch is used for device memory and streams only; all compute goes through the C-ABI
+(include/mibmi.h) into the hand-written sm_100a kernels.  No CPU fallback exists.
+
+The Python-level counterpart in the reference is `GoldenModel.__call__`
+(edge-eegnet_wolf/python_utils/golden_model.py:104-107: one int [C, T] trial -> int [N] logits); the
+C-level one is `net_model_compute` (src/cl/net/model.c:42).  `Int8Net.forward` is the batched form.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Dict, Mapping, Optional, Union
+
+import numpy as np
+import torch
+
+from . import _lib
+from .convert import WolfParams, align4, params_from_export, params_from_state_dict
+
+_LAYOUTS = {"bct": _lib.LAYOUT_BCT, "btc": _lib.LAYOUT_BTC}
+_PATHS = {"auto": _lib.PATH_AUTO, "generic": _lib.PATH_GENERIC, "fused": _lib.PATH_FUSED}
+_PATH_NAMES = {v: k for k, v in _PATHS.items()}
+
+
+def _device_index(device) -> int:
+    d = torch.device(device if device is not None else "cuda")
+    if d.type != "cuda":
+        raise ValueError("mibminet_b200 runs on CUDA devices only (there is no CPU path)")
+    return d.index if d.index is not None else torch.cuda.current_device()
+
+
+class Int8Net:
+    """Integer network resident on one GPU."""
+
+    def __init__(self, params: Union[WolfParams, Mapping[str, np.ndarray]], C: Optional[int] = None,
+                 T: Optional[int] = None, device=None, reorder_bn: bool = True, F1: int = 16, D: int = 1, N: int = 4):
+        if isinstance(params, WolfParams):
+            self.params: Optional[WolfParams] = params
+            arrays = params.to_wolf_arrays()
+            C, T, F1, D, N = params.C, params.T, params.F1, params.D, params.N
+        else:
+            self.params = None
+            arrays = dict(params)
+            if C is None or T is None:
+                raise ValueError("C and T are required with raw exported arrays")
+        self.arrays: Dict[str, np.ndarray] = arrays
+        self.C, self.T, self.F1, self.D, self.F2, self.N = int(C), int(T), int(F1), int(D), int(F1 * D), int(N)
+        self.T8, self.T64 = self.T // 8, (self.T // 8) // 8
+        self.reorder_bn = bool(reorder_bn)
+        self.device_index = _device_index(device)
+        self.device = torch.device("cuda", self.device_index)
+        self._L = _lib.lib()
+        p, keep = _lib.make_params(arrays, self.C, self.T, F1=self.F1, D=self.D, N=self.N, reorder_bn=self.reorder_bn)
+        h = ctypes.c_void_p()
+        _lib.check(self._L.mibmi_create(ctypes.byref(p), self.device_index, ctypes.byref(h)), "mibmi_create")
+        del keep
+        self._h = h
+
+    # ---- constructors --------------------------------------------------------------------------
+    @classmethod
+    def from_state_dict(cls, sd: Mapping, C: int, T: int, F1: int = 16, D: int = 1, N: int = 4, **kw) -> "Int8Net":
+        """QuantLab edgeEEGNet state_dict / net.npz mapping (convert_torch_format.py maths)."""
+        return cls(params_from_state_dict(sd, C=C, T=T, F1=F1, D=D, N=N), **kw)
+
+    @classmethod
+    def from_export(cls, net_npz: str, config_json: str, **kw) -> "Int8Net":
+        """QuantLab/export_net_data.py output: net.npz + config.json."""
+        return cls(params_from_export(net_npz, config_json), **kw)
+
+    # ---- lifetime --------------------------------------------------------------------------------
+    def close(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            self._L.mibmi_destroy(h)
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- options / introspection ---------------------------------------------------------------
+    def set_path(self, path: str):
+        _lib.check(self._L.mibmi_set_option(self._h, _lib.OPT_FORCE_PATH, _PATHS[path]), "set_path")
+
+    def set_ctas_per_sm(self, n: int):
+        _lib.check(self._L.mibmi_set_option(self._h, _lib.OPT_CTAS_PER_SM, int(n)), "set_ctas_per_sm")
+
+    def set_host_chunk(self, n: int):
+        _lib.check(self._L.mibmi_set_option(self._h, _lib.OPT_HOST_CHUNK, int(n)), "set_host_chunk")
+
+    @property
+    def last_path(self) -> str:
+        return _PATH_NAMES.get(self._L.mibmi_last_path(self._h), "none")
+
+    @property
+    def launch_count(self) -> int:
+        return int(self._L.mibmi_launch_count(self._h))
+
+    def fused_supported(self):
+        why = ctypes.c_char_p()
+        ok = self._L.mibmi_fused_supported(self._h, ctypes.byref(why))
+        return bool(ok), (why.value or b"").decode()
+
+    def trial_bytes(self, layout: str = "bct") -> int:
+        return self.C * self.T if layout == "bct" else self.T * align4(self.C)
+
+    # ---- compute -----------------------------------------------------------------------------------
+    def _check_x(self, x: torch.Tensor, layout: str):
+        if x.dtype != torch.int8:
+            raise TypeError("x must be int8 (use quantize_input for float trials)")
+        if not x.is_cuda or x.device.index != self.device_index:
+            raise ValueError(f"x must live on {self.device}")
+        want = (self.C, self.T) if layout == "bct" else (self.T, align4(self.C))
+        if x.dim() == 4 and x.shape[1] == 1:      # module order [B, 1, C, T]
+            x = x[:, 0]
+        if x.dim() != 3 or tuple(x.shape[1:]) != want:
+            raise ValueError(f"x must be [B, {want[0]}, {want[1]}] for layout '{layout}', got {tuple(x.shape)}")
+        return x.contiguous()
+
+    def forward(self, x: torch.Tensor, layout: str = "bct", out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """int8 trials [B, C, T] ('bct') or [B, T, C_ALIGN] ('btc', Wolf order) -> int8 logits [B, N].
+        Asynchronous on the current torch CUDA stream."""
+        x = self._check_x(x, layout)
+        B = x.shape[0]
+        if out is None:
+            out = torch.empty((B, self.N), dtype=torch.int8, device=self.device)
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        _lib.check(self._L.mibmi_forward_int8(self._h, x.data_ptr(), B, _LAYOUTS[layout], out.data_ptr(), stream),
+                   "mibmi_forward_int8")
+        return out
+
+    __call__ = forward
+
+    def forward_taps(self, x: torch.Tensor, layout: str = "bct"):
+        """-> (logits, {'y1','y2','y3','y4'}) : inter-layer int8 activations (generic path)."""
+        x = self._check_x(x, layout)
+        B = x.shape[0]
+        mk = lambda n: torch.empty((B, self.F2, n), dtype=torch.int8, device=self.device)
+        out = torch.empty((B, self.N), dtype=torch.int8, device=self.device)
+        taps = {"y1": mk(self.T), "y2": mk(self.T8), "y3": mk(self.T8), "y4": mk(self.T64)}
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        _lib.check(self._L.mibmi_forward_int8_taps(self._h, x.data_ptr(), B, _LAYOUTS[layout], out.data_ptr(),
+                                                   taps["y1"].data_ptr(), taps["y2"].data_ptr(),
+                                                   taps["y3"].data_ptr(), taps["y4"].data_ptr(), stream),
+                   "mibmi_forward_int8_taps")
+        return out, taps
+
+    def forward_host(self, x: Union[torch.Tensor, np.ndarray], layout: str = "bct",
+                     out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """HOST int8 trials -> HOST int8 logits through mibmi_forward_int8_host (chunked, pipelined
+        H2D / compute / D2H; pinned host tensors are copied from directly).  Synchronous."""
+        if isinstance(x, np.ndarray):
+            x = torch.from_numpy(np.ascontiguousarray(x))
+        if x.is_cuda or x.dtype != torch.int8:
+            raise TypeError("forward_host takes a CPU int8 tensor")
+        x = x.contiguous()
+        B = x.shape[0]
+        if x.numel() != B * self.trial_bytes(layout):
+            raise ValueError("bad trial shape")
+        if out is None:
+            out = torch.empty((B, self.N), dtype=torch.int8, pin_memory=True)
+        _lib.check(self._L.mibmi_forward_int8_host(self._h, x.data_ptr(), B, _LAYOUTS[layout], out.data_ptr()),
+                   "mibmi_forward_int8_host")
+        return out
+
+    def quantize_input(self, x: torch.Tensor, abs_max: Optional[float] = None) -> torch.Tensor:
+        """float32 trials -> int8 (gen_input_header.py:73; STEActivation floorToZero)."""
+        if abs_max is None:
+            if self.params is None:
+                raise ValueError("abs_max required")
+            abs_max = self.params.input_scale
+        x = x.to(self.device, torch.float32).contiguous()
+        q = torch.empty(x.shape, dtype=torch.int8, device=self.device)
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        _lib.check(self._L.mibmi_quantize_input_f32(x.data_ptr(), x.numel(), float(abs_max), q.data_ptr(), stream),
+                   "mibmi_quantize_input_f32")
+        return q
+
+    def dequantize_logits(self, q: torch.Tensor, abs_max: Optional[float] = None) -> torch.Tensor:
+        """int8 logits -> float32 (functional.py:338-353)."""
+        if abs_max is None:
+            if self.params is None:
+                raise ValueError("abs_max required")
+            abs_max = self.params.output_scale
+        q = q.contiguous()
+        y = torch.empty(q.shape, dtype=torch.float32, device=self.device)
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        _lib.check(self._L.mibmi_dequantize_logits_f32(q.data_ptr(), q.numel(), float(abs_max), y.data_ptr(), stream),
+                   "mibmi_dequantize_logits_f32")
+        return y

@@ -77,7 +77,7 @@ def main():
 
         fx = {"C": C, "T": T, "seed": seed, "x": x}
         fx.update({"arr." + k: v for k, v in arrays.items()})
-        fx.update({"sd." + k: v for k, v in sd.items() if not k.endswith(".weight")})
+        fx.update({"sd." + k: v for k, v in sd.items() if k.startswith("batch_norm") or not k.endswith(".weight")})
         for rb in (True, False):
             g = GoldenModel(os.path.join(d, "config.json"), os.path.join(d, "net.npz"),
                             clip_balanced=False, reorder_bn=rb)

@@ -1,0 +1,168 @@
+"""GPU parity tests (run on the B200 box: pytest -m gpu).  Every call goes through the C-ABI
+(libmibmi.so); the oracle (oracle/golden_np.py, oracle/wolf_port.c) and the committed reference
+outputs (tests/golden/) are the checkers.  Bar: bit-exact, every logit."""
+import numpy as np
+import pytest
+import torch
+
+import golden_np
+import wolf_port
+from conftest import golden_files, load_golden
+from mibminet_b200 import convert, synth
+from mibminet_b200.engine import Int8Net
+
+pytestmark = pytest.mark.gpu
+
+FUSED_SHAPES = [(64, 480), (38, 480), (24, 480), (19, 480), (16, 480), (8, 480)]
+
+
+def _cuda(x):
+    return torch.from_numpy(np.ascontiguousarray(x)).cuda()
+
+
+def _net(C, T, seed, **kw):
+    sd = synth.make_state_dict(C=C, T=T, seed=seed)
+    p = convert.params_from_state_dict(sd, C=C, T=T)
+    return Int8Net(p, device="cuda:0", **kw), p.to_wolf_arrays()
+
+
+# ---- against the reference's own outputs ---------------------------------------------------------------
+@pytest.mark.parametrize("path", ["generic", "fused"])
+def test_reference_fixtures(golden, path):
+    fx = golden
+    net = Int8Net(fx["arrays"], C=fx["C"], T=fx["T"], device="cuda:0")
+    ok, why = net.fused_supported()
+    if path == "fused" and not ok:
+        assert (fx["C"], fx["T"]) not in FUSED_SHAPES, why
+        pytest.skip(why)
+    net.set_path(path)
+    y = net.forward(_cuda(fx["x"])).cpu().numpy()
+    assert net.last_path == path
+    assert np.array_equal(y, fx["golden_reorder"])      # Python golden model (golden_model.py:104)
+    assert np.array_equal(y, fx["c_default"])           # C model, Makefile-default flags (model.c:42)
+
+
+def test_reference_fixtures_taps_and_plain_variant(golden):
+    fx = golden
+    x = _cuda(fx["x"])
+    net = Int8Net(fx["arrays"], C=fx["C"], T=fx["T"], device="cuda:0")
+    y, taps = net.forward_taps(x)
+    assert np.array_equal(y.cpu().numpy(), fx["golden_reorder"])
+    for name in ("y1", "y2", "y3", "y4"):
+        assert np.array_equal(taps[name].cpu().numpy(), fx[f"golden_reorder_{name}"]), name
+    plain = Int8Net(fx["arrays"], C=fx["C"], T=fx["T"], device="cuda:0", reorder_bn=False)
+    assert not plain.fused_supported()[0]
+    yp, tp = plain.forward_taps(x)
+    assert np.array_equal(yp.cpu().numpy(), fx["c_plain"])   # follows the C (layer4.c:115-117)
+    for name in ("y1", "y2", "y3"):
+        assert np.array_equal(tp[name].cpu().numpy(), fx[f"golden_plain_{name}"]), name
+
+
+def test_wolf_input_layout(golden):
+    fx = golden
+    net = Int8Net(fx["arrays"], C=fx["C"], T=fx["T"], device="cuda:0")
+    xw = convert.to_wolf_input(fx["x"])   # [B][T][C_ALIGN]  (gen_input_header.py:75-76)
+    y = net.forward(_cuda(xw), layout="btc").cpu().numpy()
+    assert np.array_equal(y, fx["golden_reorder"])
+
+
+# ---- against the oracle on seeded random nets / trials ------------------------------------------------
+@pytest.mark.parametrize("C,T", FUSED_SHAPES)
+@pytest.mark.parametrize("seed", [21, 22, 23])
+def test_fused_vs_oracle_random(C, T, seed):
+    net, arrays = _net(C, T, seed)
+    ok, why = net.fused_supported()
+    assert ok, why
+    B = 777   # not a multiple of anything: ragged tail over the persistent grid
+    x = synth.make_trials(B, C, T, seed=seed, dist="gauss" if seed % 2 else "uniform")
+    y = net.forward(_cuda(x)).cpu().numpy()
+    assert net.last_path == "fused"
+    ref = wolf_port.forward(arrays, C, T, x)
+    bad = np.nonzero((y != ref).any(axis=1))[0]
+    assert bad.size == 0, f"{bad.size} trials differ, first {bad[:5]}: {y[bad[:2]]} vs {ref[bad[:2]]}"
+    net.set_path("generic")
+    assert np.array_equal(net.forward(_cuda(x)).cpu().numpy(), ref)
+
+
+@pytest.mark.parametrize("C,T", [(22, 1125), (64, 480), (5, 64), (64, 1024), (3, 200)])
+def test_generic_vs_oracle_random(C, T):
+    net, arrays = _net(C, T, seed=31)
+    net.set_path("generic")
+    x = synth.make_trials(65, C, T, seed=5)
+    for rb in (True, False):
+        n = Int8Net(arrays, C=C, T=T, device="cuda:0", reorder_bn=rb)
+        n.set_path("generic")
+        y = n.forward(_cuda(x)).cpu().numpy()
+        assert np.array_equal(y, golden_np.forward(arrays, C, T, x, reorder_bn=rb)), rb
+        assert np.array_equal(y, wolf_port.forward(arrays, C, T, x, reorder_bn=rb)), rb
+
+
+def test_edge_batches_and_extreme_inputs():
+    C, T = 64, 480
+    net, arrays = _net(C, T, seed=41)
+    for B in (1, 2, 3, 295, 296, 297, 593):    # around 1x / 2x the persistent grid (148 SMs x 2 CTAs)
+        x = synth.make_trials(B, C, T, seed=B)
+        assert np.array_equal(net.forward(_cuda(x)).cpu().numpy(), wolf_port.forward(arrays, C, T, x)), B
+    # saturating inputs: all +127, all -127, all -128 (outside quantize_to_int's range but valid int8), zeros
+    x = np.stack([np.full((C, T), v, np.int8) for v in (127, -127, -128, 0)])
+    x = np.concatenate([x, np.where(np.arange(T)[None, :] % 2 == 0, 127, -128).astype(np.int8)[None].repeat(C, 1)
+                        .reshape(1, C, T)])
+    assert np.array_equal(net.forward(_cuda(x)).cpu().numpy(), wolf_port.forward(arrays, C, T, x))
+    # empty batch
+    y = net.forward(torch.empty((0, C, T), dtype=torch.int8, device="cuda:0"))
+    assert y.shape == (0, 4)
+
+
+def test_full_size_batch_65536_every_logit():
+    """BASELINE config 2: 64 x 480, B = 65536, every logit compared with the CPU integer path."""
+    C, T, B = 64, 480, 65536
+    net, arrays = _net(C, T, seed=0)
+    x = synth.make_trials(B, C, T, seed=99)
+    y = net.forward(_cuda(x)).cpu().numpy()
+    assert net.last_path == "fused"
+    ref = wolf_port.forward(arrays, C, T, x)      # all host cores
+    assert np.array_equal(y, ref)
+    # size-independent properties: per-trial independence (any permutation of the batch permutes
+    # the logits), determinism, and a checksum of the logits against the oracle's
+    perm = np.random.default_rng(1).permutation(B)
+    y2 = net.forward(_cuda(x[perm])).cpu().numpy()
+    assert np.array_equal(y2, y[perm])
+    assert int(y.astype(np.int64).sum()) == int(ref.astype(np.int64).sum())
+
+
+def test_host_entry_point_matches_device_path():
+    C, T, B = 64, 480, 5000
+    net, arrays = _net(C, T, seed=3)
+    net.set_host_chunk(1024)
+    x = synth.make_trials(B, C, T, seed=8)
+    ref = wolf_port.forward(arrays, C, T, x)
+    xp = torch.from_numpy(x).pin_memory()
+    assert np.array_equal(net.forward_host(xp).numpy(), ref)          # pinned: direct copies
+    assert np.array_equal(net.forward_host(torch.from_numpy(x)).numpy(), ref)   # pageable: staged
+
+
+def test_float_pre_and_post_ops():
+    C, T = 64, 480
+    net, arrays = _net(C, T, seed=5)
+    rng = np.random.default_rng(0)
+    xf = rng.normal(0, 0.5, size=(33, C, T)).astype(np.float32)
+    q = net.quantize_input(torch.from_numpy(xf).cuda())
+    assert np.array_equal(q.cpu().numpy(), convert.quantize_input(xf, net.params.input_scale))   # functional.py:308-335
+    y = net.forward(q)
+    yf = net.dequantize_logits(y).cpu().numpy()
+    ref = convert.dequantize(y.cpu().numpy(), net.params.output_scale)
+    assert np.allclose(yf, ref, rtol=1e-6, atol=0)   # float32 vs the reference's float64: 1e-6 relative
+
+
+def test_errors_are_reported_not_printed():
+    C, T = 64, 480
+    net, _ = _net(C, T, seed=1)
+    with pytest.raises(ValueError):
+        net.forward(torch.zeros((2, C, T + 1), dtype=torch.int8, device="cuda:0"))
+    with pytest.raises(TypeError):
+        net.forward(torch.zeros((2, C, T), dtype=torch.float32, device="cuda:0"))
+    x = torch.zeros((2 * C * T + 1,), dtype=torch.int8, device="cuda:0")[1:].view(2, C, T)   # misaligned
+    from mibminet_b200._lib import MibmiError, ERR_ALIGN
+    with pytest.raises(MibmiError) as ei:
+        net.forward(x)
+    assert ei.value.status == ERR_ALIGN
