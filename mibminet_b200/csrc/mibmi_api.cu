@@ -225,9 +225,10 @@ size_t trial_bytes(const mibmi_net* n, int layout) {
 
 int forward_impl(mibmi_net* net, const int8_t* x, int64_t B, int layout, int8_t* logits, int8_t* t1, int8_t* t2,
                  int8_t* t3, int8_t* t4, bool taps, cudaStream_t stream) {
-    if (!net || !x || !logits) return MIBMI_ERR_NULL;
+    if (!net) return MIBMI_ERR_NULL;
     if (B < 0 || (layout != MIBMI_LAYOUT_BCT && layout != MIBMI_LAYOUT_BTC)) return MIBMI_ERR_PARAM;
-    if (B == 0) return MIBMI_OK;
+    if (B == 0) return MIBMI_OK;   // empty batch: nothing to read or write, pointers may be null
+    if (!x || !logits) return MIBMI_ERR_NULL;
     if (((uintptr_t)x & 15) != 0 || (net->N == 4 && ((uintptr_t)logits & 3) != 0)) return MIBMI_ERR_ALIGN;
     int path = net->force_path;
     const bool fused_possible = net->fused_ok && layout == MIBMI_LAYOUT_BCT && !taps;
@@ -399,9 +400,10 @@ int mibmi_forward_int8_taps(mibmi_net_t* net, const int8_t* x_dev, int64_t B, in
 }
 
 int mibmi_forward_int8_host(mibmi_net_t* net, const int8_t* x_host, int64_t B, int layout, int8_t* logits_host) {
-    if (!net || !x_host || !logits_host) return MIBMI_ERR_NULL;
+    if (!net) return MIBMI_ERR_NULL;
     if (B < 0 || (layout != MIBMI_LAYOUT_BCT && layout != MIBMI_LAYOUT_BTC)) return MIBMI_ERR_PARAM;
     if (B == 0) return MIBMI_OK;
+    if (!x_host || !logits_host) return MIBMI_ERR_NULL;
     std::lock_guard<std::mutex> lock(net->host_mu);
     DeviceGuard dg(net->device);
     if (dg.err != cudaSuccess) return fail_cuda(net, dg.err);

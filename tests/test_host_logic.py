@@ -42,6 +42,7 @@ def test_validation_errors_need_no_gpu():
     p2, keep2 = _lib.make_params(bad, fx["C"], fx["T"])
     assert L.mibmi_create(ctypes.byref(p2), 0, ctypes.byref(h)) == _lib.ERR_PARAM
     assert L.mibmi_forward_int8(None, None, 1, 0, None, None) == _lib.ERR_NULL
+    assert L.mibmi_forward_int8_host(None, None, 0, 0, None) == _lib.ERR_NULL
 
 
 @pytest.mark.parametrize("d", [4, 5, 7, 8, 9, 63, 64, 65, 277, 852, 1145, 4096, 5771, 65535, 65536, 1 << 20, 16777259,
