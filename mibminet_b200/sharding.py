@@ -1,0 +1,66 @@
+"""Trial-batch sharding across GPUs.
+
+Trials are independent and the network is ~18 kB, so multi-GPU inference is: replicate the network,
+give every rank a contiguous slice of the trials (streaming: a slice of the subjects), run the same
+kernel, and gather the `int8 [B, N]` logits once at the end -- one NCCL all_gather over NVLink, or a
+host-side concatenation.  There is no collective inside the network.
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Tuple
+
+import torch
+import torch.distributed as dist
+
+
+def shard_bounds(n_items: int, world: int, rank: int) -> Tuple[int, int]:
+    """Contiguous, balanced partition: the first `n_items % world` ranks hold one item more."""
+    if not (0 <= rank < world) or n_items < 0:
+        raise ValueError("bad shard request")
+    base, rem = divmod(n_items, world)
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+def shard_sizes(n_items: int, world: int) -> List[int]:
+    return [shard_bounds(n_items, world, r)[1] - shard_bounds(n_items, world, r)[0] for r in range(world)]
+
+
+def gather_logits(local: torch.Tensor, n_total: int, group: Optional[dist.ProcessGroup] = None) -> torch.Tensor:
+    """All ranks get the logits of all `n_total` trials, in trial order.
+
+    `local` is this rank's `[n_local, N]` int8 block as produced by `shard_bounds`.  Equal shards use a
+    single all_gather_into_tensor; ragged shards are padded to the largest shard (4 B per trial, so the
+    padding is noise)."""
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    sizes = shard_sizes(n_total, world)
+    if local.shape[0] != sizes[rank]:
+        raise ValueError(f"rank {rank}: expected {sizes[rank]} local trials, got {local.shape[0]}")
+    n_cls = local.shape[1]
+    mx = max(sizes)
+    if mx == 0:
+        return local.new_empty((0, n_cls))
+    send = local
+    if local.shape[0] != mx:
+        send = local.new_zeros((mx, n_cls))
+        send[:local.shape[0]] = local
+    out = local.new_empty((world * mx, n_cls))
+    dist.all_gather_into_tensor(out, send.contiguous(), group=group)
+    if all(s == mx for s in sizes):
+        return out
+    return torch.cat([out[r * mx:r * mx + sizes[r]] for r in range(world)], dim=0)
+
+
+class ShardedInt8Net:
+    """One `Int8Net` per rank; `forward(x_all_or_local)` returns the gathered logits on every rank."""
+
+    def __init__(self, net, group: Optional[dist.ProcessGroup] = None):
+        self.net = net
+        self.group = group
+
+    def forward_local(self, x_local: torch.Tensor, **kw) -> torch.Tensor:
+        return self.net.forward(x_local, **kw)
+
+    def forward(self, x_local: torch.Tensor, n_total: int, **kw) -> torch.Tensor:
+        return gather_logits(self.forward_local(x_local, **kw), n_total, self.group)
