@@ -84,6 +84,7 @@ typedef struct mibmi_net mibmi_net_t; /* opaque */
 #define MIBMI_PATH_AUTO 0     /* fused tensor-core kernel when the network qualifies, else generic    */
 #define MIBMI_PATH_GENERIC 1  /* exact reference-order kernel: any shape, both reorder_bn modes, taps */
 #define MIBMI_PATH_FUSED 2    /* fused sm_100a kernel (int8 MMA + magic-number requantisation)        */
+#define MIBMI_PATH_FUSED_V1 3 /* round-1 homogeneous fused kernel, kept for A/B measurements          */
 
 #define MIBMI_OPT_FORCE_PATH 1
 #define MIBMI_OPT_CTAS_PER_SM 2   /* 0 = default */
@@ -115,7 +116,8 @@ MIBMI_API int mibmi_forward_int8(mibmi_net_t* net, const int8_t* x_dev, int64_t 
                        int8_t* logits_dev, void* stream);
 
 /* Same, plus the inter-layer activations (the taps of QuantLab/export_net_data.py:112-167 in integer
- * form).  Any of the tap pointers may be NULL.  Runs the generic path.
+ * form).  Any of the tap pointers may be NULL.  Runs the generic path unless MIBMI_PATH_FUSED is forced
+ * (the fused kernel then stores the taps from its registers: a diagnostic instantiation).
  *   y1 [B][F2][T], y2 [B][F2][T/8], y3 [B][F2][T/8], y4 [B][F2][T/64]  (int8, device) */
 MIBMI_API int mibmi_forward_int8_taps(mibmi_net_t* net, const int8_t* x_dev, int64_t B, int layout,
                             int8_t* logits_dev, int8_t* y1, int8_t* y2, int8_t* y3, int8_t* y4,
@@ -141,6 +143,8 @@ MIBMI_API int mibmi_debug_magic(int32_t d, int32_t* magic, int32_t* shift);
  * returns its size; out == NULL only queries the size.  MIBMI_ERR_UNSUPPORTED (+ *why) if the fused
  * path cannot run this network. */
 MIBMI_API int64_t mibmi_debug_pack_fused(const mibmi_params_t* params, void* out, int64_t cap, const char** why);
+/* Same for the warp-specialised pipeline kernel (MIBMI_PATH_FUSED). */
+MIBMI_API int64_t mibmi_debug_pack_pipe(const mibmi_params_t* params, void* out, int64_t cap, const char** why);
 
 #ifdef __cplusplus
 }

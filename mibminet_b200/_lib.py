@@ -16,7 +16,7 @@ from . import _build
 OK = 0
 ERR_NULL, ERR_SHAPE, ERR_PARAM, ERR_ALIGN, ERR_CUDA, ERR_UNSUPPORTED = -1, -2, -3, -4, -5, -6
 LAYOUT_BCT, LAYOUT_BTC = 0, 1
-PATH_AUTO, PATH_GENERIC, PATH_FUSED = 0, 1, 2
+PATH_AUTO, PATH_GENERIC, PATH_FUSED, PATH_FUSED_V1 = 0, 1, 2, 3
 OPT_FORCE_PATH, OPT_CTAS_PER_SM, OPT_HOST_CHUNK = 1, 2, 3
 
 # every symbol include/mibmi.h declares (tests/test_abi.py checks the header against this list)
@@ -25,6 +25,7 @@ SYMBOLS = [
     "mibmi_set_option", "mibmi_last_path", "mibmi_fused_supported", "mibmi_launch_count",
     "mibmi_forward_int8", "mibmi_forward_int8_taps", "mibmi_forward_int8_host",
     "mibmi_quantize_input_f32", "mibmi_dequantize_logits_f32", "mibmi_debug_magic", "mibmi_debug_pack_fused",
+    "mibmi_debug_pack_pipe",
 ]
 
 
@@ -83,6 +84,8 @@ def lib() -> ctypes.CDLL:
     L.mibmi_debug_magic.argtypes = [ctypes.c_int32, ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_int32)]
     L.mibmi_debug_pack_fused.argtypes = [ctypes.POINTER(Params), vp, i64, ctypes.POINTER(ctypes.c_char_p)]
     L.mibmi_debug_pack_fused.restype = i64
+    L.mibmi_debug_pack_pipe.argtypes = [ctypes.POINTER(Params), vp, i64, ctypes.POINTER(ctypes.c_char_p)]
+    L.mibmi_debug_pack_pipe.restype = i64
     _lib = L
     return L
 
@@ -117,16 +120,25 @@ def debug_magic(d: int):
     return st, m.value, s.value
 
 
-def debug_pack_fused(arrays, C, T, reorder_bn=True):
-    """-> (bytes of the packed FusedNet | None, reason)."""
+def _debug_pack(fn, arrays, C, T, reorder_bn):
     p, keep = make_params(arrays, C, T, reorder_bn=reorder_bn)
     L = lib()
-    size = L.mibmi_debug_pack_fused(ctypes.byref(p), None, 0, None)
+    size = fn(ctypes.byref(p), None, 0, None)
     if size < 0:
         return None, L.mibmi_strerror(int(size)).decode()
     buf = (ctypes.c_uint8 * size)()
     why = ctypes.c_char_p()
-    r = L.mibmi_debug_pack_fused(ctypes.byref(p), buf, size, ctypes.byref(why))
+    r = fn(ctypes.byref(p), buf, size, ctypes.byref(why))
     if r < 0:
         return None, (why.value or b"").decode()
     return bytes(buf), ""
+
+
+def debug_pack_fused(arrays, C, T, reorder_bn=True):
+    """-> (bytes of the packed FusedNet of the round-1 kernel | None, reason)."""
+    return _debug_pack(lib().mibmi_debug_pack_fused, arrays, C, T, reorder_bn)
+
+
+def debug_pack_pipe(arrays, C, T, reorder_bn=True):
+    """-> (bytes of the packed PipeNet of the pipeline kernel | None, reason)."""
+    return _debug_pack(lib().mibmi_debug_pack_pipe, arrays, C, T, reorder_bn)

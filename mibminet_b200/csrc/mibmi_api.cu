@@ -20,9 +20,12 @@ struct mibmi_net {
     int C = 0, T = 0, F2 = 0, N = 0, reorder = 1;
     GenericNet* gen_dev = nullptr;
     int8_t* w5_dev = nullptr;
-    FusedNet* fused_dev = nullptr;
+    FusedNet* fused_dev = nullptr;     // legacy homogeneous kernel (MIBMI_PATH_FUSED_V1)
     bool fused_ok = false;
     const char* fused_why = "";
+    PipeNet* pipe_dev = nullptr;       // warp-specialised pipeline kernel (MIBMI_PATH_FUSED)
+    bool pipe_ok = false, pipe_fast1 = false;
+    const char* pipe_why = "";
     int force_path = MIBMI_PATH_AUTO, ctas_per_sm = 0;
     int64_t host_chunk = 0;
     std::atomic<int> last_path{0};
@@ -189,6 +192,164 @@ bool pack_fused(const mibmi_params_t* p, FusedNet* f, const char** why) {
     return true;
 }
 
+// magic for the "no shift" form q = mulhi(x, m) + (x < 0), m = floor(2^32 / d) + 1.  With e = m d - 2^32
+// in (0, d] the form is exact while |x| e <= 2^32; outside [-129 d, 129 d] the true quotient saturates
+// under clip8 and the approximation errs only away from zero, so exactness is needed on that range only.
+bool magic32_for(int64_t d, int64_t xmax, int* m) {
+    if (d < 4 || d > 0x7fffffff) return false;
+    const int64_t mm = (int64_t(1) << 32) / d + 1;
+    const int64_t e = mm * d - (int64_t(1) << 32);
+    const int64_t lim = xmax < 130 * d ? xmax : 130 * d;
+    if ((__int128)lim * e > ((__int128)1 << 32)) return false;
+    *m = (int)mm;
+    return true;
+}
+
+// position p (0..15) inside a 16-byte chunk of a layer-1 output row holds sample sigma(p) of the chunk
+// (the order stmatrix leaves the MMA accumulator fragments in, mibmi_pipe.cu)
+inline int y1_sigma(int p) { return (p & 1) + 2 * (p >> 2) + 8 * ((p >> 1) & 1); }
+
+bool pack_pipe(const mibmi_params_t* p, PipeNet* f, const char** why) {
+    const int C = p->C, T = p->T, F2 = p->F2, CA4 = align4(C);
+    const int T64 = (T / 8) / 8, T64A = align4(T64), T64P = (T64 + 1) / 2 * 2;
+    memset(f, 0, sizeof(*f));
+    if (F2 != 16 || p->N != 4) { *why = "fused kernel needs F2 == 16 and N == 4"; return false; }
+    if (!p->reorder_bn) { *why = "fused kernel implements the REORDER_BN variant only"; return false; }
+    if (!pipe_has_instance(C, T)) { *why = "no fused instantiation for this (C, T)"; return false; }
+    // ---- layer 1: sign of the factor folded into weights and offset
+    const int half0 = (C + 1) / 2, half1 = C - half0;      // PCfg::CA / CB
+    bool fast1 = true;
+    int64_t xmax1[16];
+    for (int k = 0; k < 16; k++) {
+        const int fac = p->l1_factor[k], sg = fac < 0 ? -1 : 1;
+        int64_t sum = 0;
+        for (int c = 0; c < C; c++) {
+            const int w = p->l1_weight_align[k * CA4 + c];
+            if (sg < 0 && w == -128) { *why = "weight -128 cannot be negated (negative layer-1 factor)"; return false; }
+            sum += iabs64(w);
+        }
+        xmax1[k] = 128 * sum + iabs64(p->l1_offset[k]);
+        if (xmax1[k] >= kMagicRange) { *why = "layer-1 accumulator outside the magic-division range"; return false; }
+        int m;
+        if (!magic32_for(iabs64(fac), xmax1[k], &m)) fast1 = false;
+        f->off1[k] = sg * p->l1_offset[k];
+    }
+    for (int k = 0; k < 16; k++) {
+        const int64_t d = iabs64(p->l1_factor[k]);
+        if (fast1) { magic32_for(d, xmax1[k], &f->m1[k]); f->sh1[k] = 0; }
+        else if (!magic_for(d, &f->m1[k], &f->sh1[k])) { *why = "|l1_factor| < 4"; return false; }
+    }
+    f->fast1 = fast1 ? 1 : 0;
+    for (int kb = 0; kb < (C + 15) / 16; kb++)
+        for (int hf = 0; hf < 2; hf++)
+            for (int lane = 0; lane < 32; lane++) {
+                const int g = lane >> 2, q = lane & 3, row = g + 8 * hf;
+                const int sg = p->l1_factor[row] < 0 ? -1 : 1;
+                uint32_t word = 0;
+                for (int i = 0; i < 4; i++) {
+                    const int r = 4 * q + i;                       // K position in the block = ldmatrix row
+                    const int region = (r >> 2) & 1, idx = 8 * kb + 4 * (r >> 3) + (r & 3);
+                    const bool valid = idx < (region ? half1 : half0);
+                    const int c = region ? half0 + idx : idx;
+                    const int w = valid ? sg * p->l1_weight_align[row * CA4 + c] : 0;
+                    word |= (uint32_t)(uint8_t)(int8_t)w << (8 * i);
+                }
+                f->w1blk[kb][hf][lane] = word;
+            }
+    // ---- layer 2: Toeplitz B fragments.  Window-relative sample j = o + 1 + tap (o = output offset in
+    // the 32-sample window), K position kk of k-step s <-> j = 32 s + 16 (kk / 16) + sigma(kk % 16)
+    for (int k = 0; k < 16; k++) {
+        const int8_t* w = p->l2_weight_reverse + k * 64;
+        int64_t sum = 0;
+        for (int j = 0; j < 64; j++) sum += iabs64(w[j]);
+        Pooled po;
+        if (!pack_pooled(128 * sum, p->l2_offset[k], p->l2_factor[k], &po, why)) return false;
+        f->thr2[k] = po.thr; f->sig2[k] = po.sig; f->soff2[k] = po.soff; f->m2[k] = po.m; f->sh2[k] = po.sh;
+        for (int v = 0; v < 4; v++)
+            for (int s = 0; s < 3; s++)
+                for (int h = 0; h < 2; h++)
+                    for (int lane = 0; lane < 32; lane++) {
+                        const int g = lane >> 2, q = lane & 3;
+                        const int o = 8 * (g >> 1) + 2 * v + (g & 1);
+                        uint32_t word = 0;
+                        for (int i = 0; i < 4; i++) {
+                            const int j = 32 * s + 16 * h + y1_sigma(4 * q + i);
+                            const int tap = j - o - 1;
+                            const int val = (tap >= 0 && tap < 64) ? w[tap] : 0;
+                            word |= (uint32_t)(uint8_t)(int8_t)val << (8 * i);
+                        }
+                        f->w2frag[k][v * 6 + s * 2 + h][lane] = word;
+                    }
+    }
+    // ---- layer 3 (exported array is flipped: torch-order tap j = l3_weight[15 - j]); kk = o + tap + 1
+    {
+        const int sg = p->l3_factor < 0 ? -1 : 1;
+        if (!magic_for(iabs64(p->l3_factor), &f->m3, &f->sh3)) { *why = "|l3_factor| < 4"; return false; }
+        for (int k = 0; k < 16; k++)
+            for (int v = 0; v < 2; v++)
+                for (int h = 0; h < 2; h++)
+                    for (int lane = 0; lane < 32; lane++) {
+                        const int g = lane >> 2, q = lane & 3;
+                        const int o = 8 * v + g;
+                        uint32_t word = 0;
+                        for (int i = 0; i < 4; i++) {
+                            const int tap = 16 * h + 4 * q + i - o - 1;
+                            int val = (tap >= 0 && tap < 16) ? p->l3_weight[k * 16 + 15 - tap] : 0;
+                            if (sg < 0 && val == -128) { *why = "weight -128 cannot be negated (negative layer-3 factor)"; return false; }
+                            word |= (uint32_t)(uint8_t)(int8_t)(sg * val) << (8 * i);
+                        }
+                        f->w3frag[k][v * 2 + h][lane] = word;
+                    }
+    }
+    // ---- layer 4
+    for (int k = 0; k < 16; k++) {
+        const int8_t* w = p->l4_weight + k * 16;
+        int64_t sum = 0;
+        for (int i = 0; i < 16; i++) sum += iabs64(w[i]);
+        Pooled po;
+        if (!pack_pooled(128 * sum, p->l4_offset[k], p->l4_factor[k], &po, why)) return false;
+        f->thr4[k] = po.thr; f->sig4[k] = po.sig; f->soff4[k] = po.soff; f->m4[k] = po.m; f->sh4[k] = po.sh;
+    }
+    for (int hf = 0; hf < 2; hf++)
+        for (int lane = 0; lane < 32; lane++) {
+            const int g = lane >> 2, q = lane & 3;
+            uint32_t word = 0;
+            for (int i = 0; i < 4; i++) word |= (uint32_t)(uint8_t)p->l4_weight[(g + 8 * hf) * 16 + 4 * q + i] << (8 * i);
+            f->w4frag[hf][lane] = word;
+        }
+    // ---- layer 5: A fragments, K index kk = ch * T64P + t
+    {
+        const int sg = p->l5_factor < 0 ? -1 : 1;
+        if (!magic_for(iabs64(p->l5_factor), &f->m5, &f->sh5)) { *why = "|l5_factor| < 4"; return false; }
+        if (T64P / 2 > kPipeMaxKst5) { *why = "T too large for the fused classifier"; return false; }
+        for (int n = 0; n < 4; n++) {
+            int64_t sum = 0;
+            for (int k = 0; k < 16; k++)
+                for (int t = 0; t < T64; t++) {
+                    const int w = p->l5_weight[(n * 16 + k) * T64A + t];
+                    if (sg < 0 && w == -128) { *why = "weight -128 cannot be negated (negative layer-5 factor)"; return false; }
+                    sum += iabs64(w);
+                }
+            if (128 * sum + 128 >= kMagicRange) { *why = "layer-5 accumulator outside the magic-division range"; return false; }
+            f->b5[n] = sg * p->l5_bias[n];
+        }
+        for (int ks = 0; ks < T64P / 2; ks++)
+            for (int h = 0; h < 2; h++)
+                for (int lane = 0; lane < 32; lane++) {
+                    const int g = lane >> 2, q = lane & 3;
+                    uint32_t word = 0;
+                    if (g < 4)
+                        for (int i = 0; i < 4; i++) {
+                            const int kk = 32 * ks + 16 * h + 4 * q + i, ch = kk / T64P, t = kk % T64P;
+                            const int w = (t < T64) ? sg * p->l5_weight[(g * 16 + ch) * T64A + t] : 0;
+                            word |= (uint32_t)(uint8_t)(int8_t)w << (8 * i);
+                        }
+                    f->w5frag[ks][h][lane] = word;
+                }
+    }
+    return true;
+}
+
 int validate(const mibmi_params_t* p) {
     if (!p->l1_factor || !p->l1_offset || !p->l1_weight_align || !p->l2_factor || !p->l2_offset ||
         !p->l2_weight_reverse || !p->l3_weight || !p->l4_factor || !p->l4_offset || !p->l4_weight ||
@@ -231,13 +392,17 @@ int forward_impl(mibmi_net* net, const int8_t* x, int64_t B, int layout, int8_t*
     if (!x || !logits) return MIBMI_ERR_NULL;
     if (((uintptr_t)x & 15) != 0 || (net->N == 4 && ((uintptr_t)logits & 3) != 0)) return MIBMI_ERR_ALIGN;
     int path = net->force_path;
-    const bool fused_possible = net->fused_ok && layout == MIBMI_LAYOUT_BCT && !taps;
-    if (path == MIBMI_PATH_AUTO) path = fused_possible ? MIBMI_PATH_FUSED : MIBMI_PATH_GENERIC;
-    if (path == MIBMI_PATH_FUSED && !fused_possible) return MIBMI_ERR_UNSUPPORTED;
+    const bool pipe_possible = net->pipe_ok && layout == MIBMI_LAYOUT_BCT;
+    const bool v1_possible = net->fused_ok && layout == MIBMI_LAYOUT_BCT && !taps;
+    if (path == MIBMI_PATH_AUTO) path = (pipe_possible && !taps) ? MIBMI_PATH_FUSED : MIBMI_PATH_GENERIC;
+    if (path == MIBMI_PATH_FUSED && !pipe_possible) return MIBMI_ERR_UNSUPPORTED;
+    if (path == MIBMI_PATH_FUSED_V1 && !v1_possible) return MIBMI_ERR_UNSUPPORTED;
     DeviceGuard dg(net->device);
     if (dg.err != cudaSuccess) return fail_cuda(net, dg.err);
     cudaError_t e;
     if (path == MIBMI_PATH_FUSED)
+        e = launch_pipe(net->pipe_dev, net->pipe_fast1, net->C, net->T, x, B, logits, t1, t2, t3, t4, net->num_sms, stream);
+    else if (path == MIBMI_PATH_FUSED_V1)
         e = launch_fused(net->fused_dev, net->C, net->T, x, B, logits, net->num_sms, net->ctas_per_sm, stream);
     else
         e = launch_generic(net->gen_dev, net->T, net->F2, x, B, layout, logits, t1, t2, t3, t4, net->num_sms, stream);
@@ -272,8 +437,8 @@ int64_t mibmi_launch_count(const mibmi_net_t* net) { return net ? net->launches.
 
 int mibmi_fused_supported(const mibmi_net_t* net, const char** why) {
     if (!net) return 0;
-    if (why) *why = net->fused_ok ? "" : net->fused_why;
-    return net->fused_ok ? 1 : 0;
+    if (why) *why = net->pipe_ok ? "" : net->pipe_why;
+    return net->pipe_ok ? 1 : 0;
 }
 
 int mibmi_debug_magic(int32_t d, int32_t* m, int32_t* s) {
@@ -294,6 +459,18 @@ int64_t mibmi_debug_pack_fused(const mibmi_params_t* p, void* out, int64_t cap, 
     return ok ? (int64_t)sizeof(FusedNet) : MIBMI_ERR_UNSUPPORTED;
 }
 
+int64_t mibmi_debug_pack_pipe(const mibmi_params_t* p, void* out, int64_t cap, const char** why) {
+    if (!p) return MIBMI_ERR_NULL;
+    int st = validate(p);
+    if (st != MIBMI_OK) return st;
+    if (!out) return (int64_t)sizeof(PipeNet);
+    if (cap < (int64_t)sizeof(PipeNet)) return MIBMI_ERR_PARAM;
+    const char* w = "";
+    const bool ok = pack_pipe(p, reinterpret_cast<PipeNet*>(out), &w);
+    if (why) *why = w;
+    return ok ? (int64_t)sizeof(PipeNet) : MIBMI_ERR_UNSUPPORTED;
+}
+
 int mibmi_create(const mibmi_params_t* p, int device, mibmi_net_t** out) {
     if (!p || !out) return MIBMI_ERR_NULL;
     *out = nullptr;
@@ -311,7 +488,8 @@ int mibmi_create(const mibmi_params_t* p, int device, mibmi_net_t** out) {
     std::vector<int8_t> w5((size_t)N * F2 * T64);
     GenericNet* g = new (std::nothrow) GenericNet();
     FusedNet* f = new (std::nothrow) FusedNet();
-    if (!g || !f) { delete g; delete f; delete n; return MIBMI_ERR_CUDA; }
+    PipeNet* pn = new (std::nothrow) PipeNet();
+    if (!g || !f || !pn) { delete g; delete f; delete pn; delete n; return MIBMI_ERR_CUDA; }
     memset(g, 0, sizeof(*g));
     g->C = C; g->T = T; g->F2 = F2; g->N = N; g->T8 = T / 8; g->T64 = T64; g->reorder = n->reorder;
     for (int k = 0; k < F2; k++) {
@@ -330,6 +508,8 @@ int mibmi_create(const mibmi_params_t* p, int device, mibmi_net_t** out) {
             for (int t = 0; t < T64; t++) w5[((size_t)c * F2 + k) * T64 + t] = p->l5_weight[((size_t)c * F2 + k) * T64A + t];
     }
     n->fused_ok = pack_fused(p, f, &n->fused_why);
+    n->pipe_ok = pack_pipe(p, pn, &n->pipe_why);
+    n->pipe_fast1 = pn->fast1 != 0;
 
     cudaDeviceProp prop;
     if (e == cudaSuccess) e = cudaGetDeviceProperties(&prop, device);
@@ -343,8 +523,13 @@ int mibmi_create(const mibmi_params_t* p, int device, mibmi_net_t** out) {
         e = cudaMalloc(&n->fused_dev, sizeof(FusedNet));
         if (e == cudaSuccess) e = cudaMemcpy(n->fused_dev, f, sizeof(FusedNet), cudaMemcpyHostToDevice);
     }
+    if (e == cudaSuccess && n->pipe_ok) {
+        e = cudaMalloc(&n->pipe_dev, sizeof(PipeNet));
+        if (e == cudaSuccess) e = cudaMemcpy(n->pipe_dev, pn, sizeof(PipeNet), cudaMemcpyHostToDevice);
+    }
     delete g;
     delete f;
+    delete pn;
     if (e != cudaSuccess) {
         mibmi_destroy(n);
         return MIBMI_ERR_CUDA;
@@ -360,6 +545,7 @@ int mibmi_destroy(mibmi_net_t* net) {
         if (net->gen_dev) cudaFree(net->gen_dev);
         if (net->w5_dev) cudaFree(net->w5_dev);
         if (net->fused_dev) cudaFree(net->fused_dev);
+        if (net->pipe_dev) cudaFree(net->pipe_dev);
         free_host_staging(net);
         for (int i = 0; i < 2; i++)
             if (net->hs[i]) cudaStreamDestroy(net->hs[i]);
@@ -372,8 +558,9 @@ int mibmi_set_option(mibmi_net_t* net, int option, int64_t value) {
     if (!net) return MIBMI_ERR_NULL;
     switch (option) {
         case MIBMI_OPT_FORCE_PATH:
-            if (value < MIBMI_PATH_AUTO || value > MIBMI_PATH_FUSED) return MIBMI_ERR_PARAM;
-            if (value == MIBMI_PATH_FUSED && !net->fused_ok) return MIBMI_ERR_UNSUPPORTED;
+            if (value < MIBMI_PATH_AUTO || value > MIBMI_PATH_FUSED_V1) return MIBMI_ERR_PARAM;
+            if (value == MIBMI_PATH_FUSED && !net->pipe_ok) return MIBMI_ERR_UNSUPPORTED;
+            if (value == MIBMI_PATH_FUSED_V1 && !net->fused_ok) return MIBMI_ERR_UNSUPPORTED;
             net->force_path = (int)value;
             return MIBMI_OK;
         case MIBMI_OPT_CTAS_PER_SM:
@@ -395,7 +582,7 @@ int mibmi_forward_int8(mibmi_net_t* net, const int8_t* x_dev, int64_t B, int lay
 
 int mibmi_forward_int8_taps(mibmi_net_t* net, const int8_t* x_dev, int64_t B, int layout, int8_t* logits_dev,
                             int8_t* y1, int8_t* y2, int8_t* y3, int8_t* y4, void* stream) {
-    if (net && net->force_path == MIBMI_PATH_FUSED) return MIBMI_ERR_UNSUPPORTED;
+    if (net && net->force_path == MIBMI_PATH_FUSED_V1) return MIBMI_ERR_UNSUPPORTED;
     return forward_impl(net, x_dev, B, layout, logits_dev, y1, y2, y3, y4, true, (cudaStream_t)stream);
 }
 

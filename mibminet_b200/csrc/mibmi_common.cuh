@@ -61,6 +61,36 @@ struct FusedNet {
 };
 static_assert(sizeof(FusedNet) % 16 == 0, "FusedNet is copied with 128-bit accesses");
 
+// ---------------------------------------------------------------------------------------------
+// Network as the warp-specialised pipeline kernel (mibmi_pipe.cu) reads it: every array is already
+// in MMA-fragment order, one 32-bit word per lane, so each warp loads its constants once with
+// coalesced global loads and keeps them in registers for the whole launch (nothing of the network
+// lives in shared memory).  Same host-side sign folding as FusedNet.
+constexpr int kPipeMaxKB16 = 4;     // layer-1 blocks of 16 channels (C <= 64)
+constexpr int kPipeMaxKst5 = 16;    // layer-5 k-steps of 32 (T/64 padded to even <= 32)
+
+struct PipeNet {
+    // layer 1: A fragments per 16-channel block: [block][row half (g, g+8)][lane]
+    uint32_t w1blk[kPipeMaxKB16][2][32];
+    int off1[16], m1[16], sh1[16];
+    int fast1;                      // 1: sh1 == 0 everywhere (magic = floor(2^32/d)+1, exact after clip8)
+    int pad0_[3];
+    // layer 2: Toeplitz B fragments [channel][variant*6 + kstep*2 + half][lane]
+    uint32_t w2frag[16][24][32];
+    int thr2[16], sig2[16], soff2[16], m2[16], sh2[16];
+    // layer 3: Toeplitz B fragments [channel][variant*2 + half][lane]
+    uint32_t w3frag[16][4][32];
+    int m3, sh3, pad1_[2];
+    // layer 4: A fragments [row half][lane]
+    uint32_t w4frag[2][32];
+    int thr4[16], sig4[16], soff4[16], m4[16], sh4[16];
+    // layer 5: A fragments [kstep][k half][lane] (rows >= 4 are zero)
+    uint32_t w5frag[kPipeMaxKst5][2][32];
+    int b5[4];
+    int m5, sh5, pad2_[2];
+};
+static_assert(sizeof(PipeNet) % 16 == 0, "PipeNet alignment");
+
 // C '/' : truncate toward zero.  (The generic kernel uses the hardware sequence as is.)
 __device__ __forceinline__ int clip8(int x) { return min(max(x, -128), 127); }
 

@@ -1,0 +1,411 @@
+// Warp-specialised int8 edgeEEGNet / MI-BMInet forward for sm_100a (the hot kernel of libmibmi.so).
+//
+// One persistent CTA per SM (25 warps) streams trials b = blockIdx.x + n * gridDim.x through all five
+// layers; inter-layer activations never leave shared memory, the network never enters it (every warp
+// keeps its MMA fragments of the weights in registers for the whole launch).
+//
+//   warp 24 "C"   TMA producer: two cp.async.bulk copies per trial into an S-stage ring (mbarrier
+//                 complete_tx), then layers 4 + 5 of the trial whose layer 3 has finished
+//   warps 0-7 "A"   layer 1, spatial conv: D[16 filters x 8 samples] += W1[16 x 32 ch] * X[32 ch x 8]
+//                 with mma.sync m16n8k32.s8; the [C][T] -> channel-contiguous B operand comes out of
+//                 ldmatrix.m16n16.trans.b8 (the two channel halves of a trial sit 16 B apart modulo
+//                 128, so every 8-row phase is bank-conflict free); requant = one IMAD.HI (+ shift) +
+//                 sign fix-up, saturating pack, one stmatrix per 32 samples
+//                 -- edge-eegnet_wolf/src/cl/net/layer1.c:87-96
+//   warps 8-23 "B"  one temporal channel each.  Layer 2, depthwise 64-tap conv as a Hankel x Toeplitz
+//                 product: A[16 windows x 32] straight from the layer-1 row by ldmatrix (windows 32
+//                 samples apart; even / odd 16-byte chunks live in two planes so that a phase reads 128
+//                 contiguous bytes), B = 4 Toeplitz variants of the taps held in 24 registers; every
+//                 thread ends up with complete pooling groups of 8, so ReLU-threshold + sum-pool +
+//                 requant need no shuffles -- layer2.c:87-118 (REORDER_BN).
+//                 Layer 3, depthwise 16-tap conv, the same trick with one k-step -- layer3.c:70
+//   warp 24       layer 4, pointwise conv: mma.sync m16n8k16 over a sample order that layer 3 wrote so
+//                 that a thread again owns whole pooling groups -- layer4.c:99-140; layer 5, classifier,
+//                 4 MMAs against the [16][T64] activations -- layer5.c:81-89
+//
+// Hand-off between the roles is mbarrier-only (no __syncthreads after the prologue):
+//   full_x / empty_x [S]   producer <-> A      full_y1 / empty_y1 [2]   A <-> B
+//   full_y3 / empty_y3 [2] B <-> C
+// Integer results are bit-identical to the reference (tests/test_parity_gpu.py).
+#include "mibmi_common.cuh"
+#include "mibmi_kernels.h"
+#include "mibmi_ptx.cuh"
+
+namespace mibmi {
+
+constexpr int kAW = 8;                        // layer-1 warps
+constexpr int kBW = 16;                       // layer-2/3 warps (one channel each)
+constexpr int kPipeThreads = (kAW + kBW + 1) * 32;
+
+template <int C_, int T_, int S_>
+struct PCfg {
+    static constexpr int C = C_, T = T_, S = S_;
+    static constexpr int KB16 = (C + 15) / 16, KP = KB16 / 2, KR = KB16 % 2;
+    static constexpr int CA = (C + 1) / 2, CB = C - CA;          // channel halves (two bulk copies)
+    static constexpr int ROFF = CA * T + 16;                     // second half: +16 B modulo 128
+    static constexpr int T8 = T / 8, T64 = T8 / 8;
+    static constexpr int UNITS = T / 32;                         // layer-1 units of 32 samples
+    static constexpr int MROWS = (T8 * 8 + 31) / 32, MT = (MROWS + 15) / 16;
+    static constexpr int NCH = 16 * MT + 2;                      // 16-byte chunks per plane
+    static constexpr int PLANE = 16 * NCH, Y1S = 2 * PLANE + 16; // Y1S / 16 odd: conflict-free stmatrix
+    static constexpr int NW3 = (T8 + 15) / 16, Y2S = 16 * (NW3 + 1);
+    static constexpr int Y3CH = 2 * ((NW3 + 1) / 2), Y3S = 16 * (Y3CH + 1);
+    static constexpr int NST = (T64 + 3) / 4;                    // layer-4 super-tiles of 4 pooling groups
+    static constexpr int T64P = (T64 + 1) / 2 * 2, KST5 = T64P / 2;
+    static constexpr int TRIAL_BYTES = C * T;
+    static constexpr int XS_BYTES = ((C * T + 16 + 127) / 128) * 128;
+    static constexpr int Y1_BYTES = 16 * Y1S, Y3_BYTES = 16 * Y3S;
+    // barriers (8 B each)
+    static constexpr int BAR_FULL_X = 0, BAR_EMPTY_X = 8 * S, BAR_FULL_Y1 = 16 * S, BAR_EMPTY_Y1 = 16 * S + 16,
+                         BAR_FULL_Y3 = 16 * S + 32, BAR_EMPTY_Y3 = 16 * S + 48;
+    // shared memory map
+    static constexpr int OFF_XS = 256;
+    static constexpr int OFF_Y1 = OFF_XS + S * XS_BYTES;
+    static constexpr int OFF_Y2 = OFF_Y1 + 2 * Y1_BYTES;
+    static constexpr int OFF_Y3 = OFF_Y2 + 16 * Y2S;
+    static constexpr int OFF_Y4 = OFF_Y3 + 2 * Y3_BYTES;
+    static constexpr int SMEM = ((OFF_Y4 + 16 * T64P + 127) / 128) * 128;
+    static_assert(T % 32 == 0, "bulk-copy loader: whole 32-sample units and 16-byte rows");
+    static_assert(T8 % 2 == 0, "layer 3 stores sample pairs");
+    static_assert(KB16 >= 1 && KB16 <= kPipeMaxKB16, "C <= 64");
+    static_assert(UNITS + 1 <= NCH - 1, "layer-1 chunks fit the planes with one zero chunk on each side");
+    static_assert(16 * S + 64 <= 256, "barrier area");
+    static_assert(KST5 <= kPipeMaxKst5, "T too large for PipeNet::w5frag");
+    static_assert(SMEM <= 227 * 1024, "shared memory");
+};
+
+// smem byte offset (within a stage) of row r of 16-channel block kb of the layer-1 B operand.
+// Rows alternate between the two channel halves in groups of 4 so that any 8 consecutive rows hit 8
+// different 16-byte bank groups (T / 16 = 2 mod 4 for T = 480); rows past C point at row 0 (zero weights).
+template <class K>
+__device__ __forceinline__ uint32_t l1_row_offset(int kb, int r) {
+    const int region = (r >> 2) & 1;
+    const int idx = 8 * kb + 4 * (r >> 3) + (r & 3);
+    const bool valid = idx < (region ? K::CB : K::CA);
+    return valid ? (uint32_t)(region ? K::ROFF + idx * K::T : idx * K::T) : 0u;
+}
+
+template <bool FAST>
+__device__ __forceinline__ int tdiv1(int x, int m, int s) {
+    if (FAST) return __mulhi(x, m) + (int)((unsigned)x >> 31);
+    return (__mulhi(x, m) >> s) + (int)((unsigned)x >> 31);
+}
+
+template <class K, bool FAST1, bool TAPS>
+__global__ void __launch_bounds__(kPipeThreads, 1)
+pipe_forward_kernel(const PipeNet* __restrict__ net, const int8_t* __restrict__ x, long long B,
+                    int8_t* __restrict__ logits, int8_t* __restrict__ tap1, int8_t* __restrict__ tap2,
+                    int8_t* __restrict__ tap3, int8_t* __restrict__ tap4) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int g = lane >> 2, q = lane & 3;
+    const uint32_t sbase = smem_u32(smem);
+    const long long first = blockIdx.x, stride = gridDim.x;
+    const int nloc = first < B ? (int)((B - first + stride - 1) / stride) : 0;
+
+    // ---- prologue: barriers, zero the activation buffers (their padding stays zero for the whole launch)
+    if (tid == 0) {
+        for (int s = 0; s < K::S; s++) {
+            mbar_init(sbase + K::BAR_FULL_X + 8 * s, 1);
+            mbar_init(sbase + K::BAR_EMPTY_X + 8 * s, kAW);
+        }
+        for (int i = 0; i < 2; i++) {
+            mbar_init(sbase + K::BAR_FULL_Y1 + 8 * i, kAW);
+            mbar_init(sbase + K::BAR_EMPTY_Y1 + 8 * i, kBW);
+            mbar_init(sbase + K::BAR_FULL_Y3 + 8 * i, kBW);
+            mbar_init(sbase + K::BAR_EMPTY_Y3 + 8 * i, 1);
+        }
+        mbar_fence_init();
+    }
+    {
+        uint4* z = reinterpret_cast<uint4*>(smem + K::OFF_Y1);
+        for (int i = tid; i < (K::SMEM - K::OFF_Y1) / 16; i += kPipeThreads) z[i] = make_uint4(0, 0, 0, 0);
+    }
+    __syncthreads();
+
+    if (warp < kAW) {
+        // =====================================================================================
+        // A: layer 1
+        // =====================================================================================
+        uint32_t afr[K::KB16][2];
+#pragma unroll
+        for (int kb = 0; kb < K::KB16; kb++) {
+            afr[kb][0] = net->w1blk[kb][0][lane];
+            afr[kb][1] = net->w1blk[kb][1][lane];
+        }
+        const int off_lo = net->off1[g], off_hi = net->off1[g + 8];
+        const int m_lo = net->m1[g], m_hi = net->m1[g + 8], sh_lo = net->sh1[g], sh_hi = net->sh1[g + 8];
+        uint32_t xoff[K::KP + 1];
+#pragma unroll
+        for (int s = 0; s < K::KP; s++) xoff[s] = l1_row_offset<K>(2 * s + (lane >> 4), lane & 15);
+        if (K::KR) xoff[K::KP] = l1_row_offset<K>(K::KB16 - 1, lane & 15);
+        // stmatrix: matrix j = lane >> 3 holds filters 8 (j >> 1) .. +7 of plane (j & 1); chunk u + 1
+        const uint32_t st_off = ((lane & 7) + 8 * (lane >> 4)) * K::Y1S + ((lane >> 3) & 1) * K::PLANE + 16;
+
+        for (int n = 0; n < nloc; n++) {
+            const int st = n % K::S, buf = n & 1;
+            mbar_wait(sbase + K::BAR_FULL_X + 8 * st, (n / K::S) & 1);
+            mbar_wait(sbase + K::BAR_EMPTY_Y1 + 8 * buf, ((n >> 1) & 1) ^ 1);
+            const uint32_t xb = sbase + K::OFF_XS + st * K::XS_BYTES;
+            const uint32_t yb = sbase + K::OFF_Y1 + buf * K::Y1_BYTES + st_off;
+#pragma unroll 1
+            for (int u = warp; u < K::UNITS; u += kAW) {
+                int acc[4][4];
+#pragma unroll
+                for (int j = 0; j < 4; j++) { acc[j][0] = acc[j][1] = off_lo; acc[j][2] = acc[j][3] = off_hi; }
+#pragma unroll
+                for (int th = 0; th < 2; th++) {
+#pragma unroll
+                    for (int s = 0; s < K::KP; s++) {
+                        uint32_t d[4];
+                        ldsm_t_x2(d, xb + xoff[s] + 32 * u + 16 * th);
+                        const uint32_t a[4] = {afr[2 * s][0], afr[2 * s][1], afr[2 * s + 1][0], afr[2 * s + 1][1]};
+                        mma_k32(acc[2 * th], a, d[0], d[2]);
+                        mma_k32(acc[2 * th + 1], a, d[1], d[3]);
+                    }
+                    if (K::KR) {
+                        uint32_t d[2];
+                        ldsm_t_x1(d, xb + xoff[K::KP] + 32 * u + 16 * th);
+                        mma_k16(acc[2 * th], afr[K::KB16 - 1][0], afr[K::KB16 - 1][1], d[0]);
+                        mma_k16(acc[2 * th + 1], afr[K::KB16 - 1][0], afr[K::KB16 - 1][1], d[1]);
+                    }
+                }
+                // requant; thread (g, q) owns samples 32u + 8nt + 2q, +1 (nt = 0..3) of filters g and g + 8
+                int v[4][4];
+#pragma unroll
+                for (int nt = 0; nt < 4; nt++) {
+                    v[nt][0] = tdiv1<FAST1>(acc[nt][0], m_lo, sh_lo);
+                    v[nt][1] = tdiv1<FAST1>(acc[nt][1], m_lo, sh_lo);
+                    v[nt][2] = tdiv1<FAST1>(acc[nt][2], m_hi, sh_hi);
+                    v[nt][3] = tdiv1<FAST1>(acc[nt][3], m_hi, sh_hi);
+                }
+                const uint32_t w00 = pack4_sat(v[0][0], v[0][1], v[1][0], v[1][1]);   // filter g,     chunk 2u
+                const uint32_t w01 = pack4_sat(v[2][0], v[2][1], v[3][0], v[3][1]);   // filter g,     chunk 2u + 1
+                const uint32_t w10 = pack4_sat(v[0][2], v[0][3], v[1][2], v[1][3]);   // filter g + 8, chunk 2u
+                const uint32_t w11 = pack4_sat(v[2][2], v[2][3], v[3][2], v[3][3]);   // filter g + 8, chunk 2u + 1
+                stsm_x4(yb + 16 * u, w00, w01, w10, w11);
+                if (TAPS && tap1) {
+                    const long long b = first + (long long)n * stride;
+#pragma unroll
+                    for (int nt = 0; nt < 4; nt++)
+#pragma unroll
+                        for (int e = 0; e < 4; e++) {
+                            const int f = g + 8 * (e >> 1), t = 32 * u + 8 * nt + 2 * q + (e & 1);
+                            tap1[((size_t)b * 16 + f) * K::T + t] = (int8_t)clip8(v[nt][e]);
+                        }
+                }
+            }
+            __syncwarp();
+            if (lane == 0) {
+                mbar_arrive(sbase + K::BAR_EMPTY_X + 8 * st);
+                mbar_arrive(sbase + K::BAR_FULL_Y1 + 8 * buf);
+            }
+        }
+    } else if (warp < kAW + kBW) {
+        // =====================================================================================
+        // B: layers 2 + 3 of channel k
+        // =====================================================================================
+        const int k = warp - kAW;
+        uint32_t bt[4][3][2];
+#pragma unroll
+        for (int v = 0; v < 4; v++)
+#pragma unroll
+            for (int s = 0; s < 3; s++)
+#pragma unroll
+                for (int h = 0; h < 2; h++) bt[v][s][h] = net->w2frag[k][v * 6 + s * 2 + h][lane];
+        const int thr = net->thr2[k], sig = net->sig2[k], soff = net->soff2[k], m2 = net->m2[k], sh2 = net->sh2[k];
+        uint32_t b3[2][2];
+#pragma unroll
+        for (int v = 0; v < 2; v++)
+#pragma unroll
+            for (int h = 0; h < 2; h++) b3[v][h] = net->w3frag[k][v * 2 + h][lane];
+        const int m3 = net->m3, sh3 = net->sh3;
+        // ldmatrix.x4 lane addressing: matrix j = lane >> 3, row (lane & 7) + 8 (j & 1), k-half j >> 1
+        const int lrow = (lane & 7) + 8 * ((lane >> 3) & 1);
+        const uint32_t l2_off = k * K::Y1S + (lane >> 4) * K::PLANE + 16 * lrow;
+        const int l3_row = lrow < K::NW3 ? lrow : K::NW3 - 1;
+        const uint32_t l3_addr = sbase + K::OFF_Y2 + k * K::Y2S + 16 * (l3_row + (lane >> 4));
+        uint8_t* y2row = smem + K::OFF_Y2 + k * K::Y2S;
+        // layer-3 stores: sample t = 16 i + 8 v + 2 q (+1) goes to chunk 2 (i >> 1) + (q >> 1), position
+        // 8 (q & 1) + 4 (i & 1) + 2 v: the order layer 4 wants (pooling group = MMA column pair)
+        const uint32_t y3_off = k * K::Y3S + 16 * (q >> 1) + 8 * (q & 1);
+
+        for (int n = 0; n < nloc; n++) {
+            const int buf = n & 1, par = (n >> 1) & 1;
+            const long long b = first + (long long)n * stride;
+            mbar_wait(sbase + K::BAR_FULL_Y1 + 8 * buf, par);
+            const uint32_t ya = sbase + K::OFF_Y1 + buf * K::Y1_BYTES + l2_off;
+#pragma unroll 1
+            for (int mt = 0; mt < K::MT; mt++) {
+                int acc[4][4];
+#pragma unroll
+                for (int v = 0; v < 4; v++) acc[v][0] = acc[v][1] = acc[v][2] = acc[v][3] = 0;
+#pragma unroll
+                for (int s = 0; s < 3; s++) {
+                    uint32_t a[4];
+                    ldsm_x4(a, ya + 16 * (16 * mt + s));
+#pragma unroll
+                    for (int v = 0; v < 4; v++) mma_k32(acc[v], a, bt[v][s][0], bt[v][s][1]);
+                }
+#pragma unroll
+                for (int hf = 0; hf < 2; hf++) {
+                    int s = 0;
+#pragma unroll
+                    for (int v = 0; v < 4; v++) s += max(acc[v][2 * hf], thr) + max(acc[v][2 * hf + 1], thr);
+                    const int p = 4 * (16 * mt + g + 8 * hf) + q;     // pooled sample index
+                    const int o = clip8(tdiv_magic(s * sig + soff, m2, sh2));
+                    if (p < K::T8) {
+                        y2row[8 + p] = (uint8_t)o;
+                        if (TAPS && tap2) tap2[((size_t)b * 16 + k) * K::T8 + p] = (int8_t)o;
+                    }
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(sbase + K::BAR_EMPTY_Y1 + 8 * buf);
+            mbar_wait(sbase + K::BAR_EMPTY_Y3 + 8 * buf, par ^ 1);
+            // ---- layer 3
+            {
+                uint32_t a[4];
+                ldsm_x4(a, l3_addr);
+                int c3[2][4];
+#pragma unroll
+                for (int v = 0; v < 2; v++) {
+                    c3[v][0] = c3[v][1] = c3[v][2] = c3[v][3] = 0;
+                    mma_k32(c3[v], a, b3[v][0], b3[v][1]);
+                }
+                uint8_t* y3b = smem + K::OFF_Y3 + buf * K::Y3_BYTES + y3_off;
+#pragma unroll
+                for (int half = 0; half < (K::NW3 > 8 ? 2 : 1); half++) {
+                    const int i = g + 8 * half;
+#pragma unroll
+                    for (int v = 0; v < 2; v++) {
+                        const int t = 16 * i + 8 * v + 2 * q;
+                        const int lo = tdiv_magic(c3[v][2 * half], m3, sh3), hi = tdiv_magic(c3[v][2 * half + 1], m3, sh3);
+                        const uint32_t w = pack2_sat(lo, hi);
+                        if (t < K::T8) {
+                            *reinterpret_cast<uint16_t*>(y3b + 32 * (i >> 1) + 4 * (i & 1) + 2 * v) = (uint16_t)w;
+                            if (TAPS && tap3) {
+                                tap3[((size_t)b * 16 + k) * K::T8 + t] = (int8_t)(w & 0xff);
+                                tap3[((size_t)b * 16 + k) * K::T8 + t + 1] = (int8_t)((w >> 8) & 0xff);
+                            }
+                        }
+                    }
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(sbase + K::BAR_FULL_Y3 + 8 * buf);
+        }
+    } else {
+        // =====================================================================================
+        // C: TMA producer, layers 4 + 5
+        // =====================================================================================
+        auto issue = [&](int st, int n) {
+            const int8_t* src = x + (size_t)(first + (long long)n * stride) * K::TRIAL_BYTES;
+            const uint32_t dst = sbase + K::OFF_XS + st * K::XS_BYTES;
+            const uint32_t bar = sbase + K::BAR_FULL_X + 8 * st;
+            mbar_expect_tx(bar, K::TRIAL_BYTES);
+            bulk_g2s(dst, src, K::CA * K::T, bar);
+            if (K::CB > 0) bulk_g2s(dst + K::ROFF, src + K::CA * K::T, K::CB * K::T, bar);
+        };
+        if (lane == 0)
+            for (int s = 0; s < K::S && s < nloc; s++) issue(s, s);
+
+        const uint32_t w4a0 = net->w4frag[0][lane], w4a1 = net->w4frag[1][lane];
+        const int thr_lo = net->thr4[g], thr_hi = net->thr4[g + 8];
+        const int sig_lo = net->sig4[g], sig_hi = net->sig4[g + 8];
+        const int soff_lo = net->soff4[g], soff_hi = net->soff4[g + 8];
+        const int m4_lo = net->m4[g], m4_hi = net->m4[g + 8], sh4_lo = net->sh4[g], sh4_hi = net->sh4[g + 8];
+        const int b5 = net->b5[g & 3], m5 = net->m5, sh5 = net->sh5;
+        const uint32_t l4_off = (lane & 15) * K::Y3S + 16 * (lane >> 4);
+        uint8_t* y4 = smem + K::OFF_Y4;
+        const uint32_t* y4w = reinterpret_cast<const uint32_t*>(y4);
+
+        for (int n = 0; n < nloc; n++) {
+            const int st = n % K::S, buf = n & 1, par = (n >> 1) & 1;
+            const long long b = first + (long long)n * stride;
+            if (n + K::S < nloc) {      // refill the stage trial n used with trial n + S
+                mbar_wait(sbase + K::BAR_EMPTY_X + 8 * st, (n / K::S) & 1);
+                if (lane == 0) issue(st, n + K::S);
+            }
+            mbar_wait(sbase + K::BAR_FULL_Y3 + 8 * buf, par);
+            const uint32_t y3a = sbase + K::OFF_Y3 + buf * K::Y3_BYTES + l4_off;
+#pragma unroll
+            for (int s4 = 0; s4 < K::NST; s4++) {
+                uint32_t d[4];
+                ldsm_t_x2(d, y3a + 32 * s4);
+                int c[4][4];
+#pragma unroll
+                for (int v = 0; v < 4; v++) {
+                    c[v][0] = c[v][1] = c[v][2] = c[v][3] = 0;
+                    mma_k16(c[v], w4a0, w4a1, d[v]);
+                }
+                int s_lo = 0, s_hi = 0;
+#pragma unroll
+                for (int v = 0; v < 4; v++) {
+                    s_lo += max(c[v][0], thr_lo) + max(c[v][1], thr_lo);
+                    s_hi += max(c[v][2], thr_hi) + max(c[v][3], thr_hi);
+                }
+                const int grp = 4 * s4 + q;
+                const int o_lo = clip8(tdiv_magic(s_lo * sig_lo + soff_lo, m4_lo, sh4_lo));
+                const int o_hi = clip8(tdiv_magic(s_hi * sig_hi + soff_hi, m4_hi, sh4_hi));
+                if (grp < K::T64) {
+                    y4[g * K::T64P + grp] = (uint8_t)o_lo;
+                    y4[(g + 8) * K::T64P + grp] = (uint8_t)o_hi;
+                    if (TAPS && tap4) {
+                        tap4[((size_t)b * 16 + g) * K::T64 + grp] = (int8_t)o_lo;
+                        tap4[((size_t)b * 16 + g + 8) * K::T64 + grp] = (int8_t)o_hi;
+                    }
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(sbase + K::BAR_EMPTY_Y3 + 8 * buf);
+            // ---- layer 5: D[class][0] = W5[class][k, t] . y4[k, t]; only MMA column 0 carries data
+            int z[4] = {0, 0, 0, 0};
+#pragma unroll
+            for (int ks = 0; ks < K::KST5; ks++) {
+                const uint32_t a[4] = {__ldg(&net->w5frag[ks][0][lane]), 0u, __ldg(&net->w5frag[ks][1][lane]), 0u};
+                const uint32_t b0 = g == 0 ? y4w[8 * ks + q] : 0u, b1 = g == 0 ? y4w[8 * ks + 4 + q] : 0u;
+                mma_k32(z, a, b0, b1);
+            }
+            if (q == 0 && g < 4) logits[(size_t)b * 4 + g] = (int8_t)clip8(tdiv_magic(z[0] + b5, m5, sh5));
+            __syncwarp();   // y4 is rewritten by the next trial
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+template <int C, int T>
+static cudaError_t launch_pipe_instance(const PipeNet* net_dev, bool fast1, const int8_t* x, long long B,
+                                        int8_t* logits, int8_t* t1, int8_t* t2, int8_t* t3, int8_t* t4,
+                                        int num_sms, cudaStream_t stream) {
+    using K = PCfg<C, T, 4>;
+    const bool taps = t1 || t2 || t3 || t4;
+    auto kern = taps ? pipe_forward_kernel<K, false, true>
+                     : (fast1 ? pipe_forward_kernel<K, true, false> : pipe_forward_kernel<K, false, false>);
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, K::SMEM);
+    if (e != cudaSuccess) return e;
+    long long grid = num_sms;
+    if (grid > B) grid = B;
+    kern<<<(unsigned)grid, kPipeThreads, K::SMEM, stream>>>(net_dev, x, B, logits, t1, t2, t3, t4);
+    return cudaGetLastError();
+}
+
+#define MIBMI_PIPE_SHAPES(X) X(64, 480) X(38, 480) X(24, 480) X(19, 480) X(16, 480) X(8, 480)
+
+bool pipe_has_instance(int C, int T) {
+#define X(c, t) if (C == c && T == t) return true;
+    MIBMI_PIPE_SHAPES(X)
+#undef X
+    return false;
+}
+
+cudaError_t launch_pipe(const PipeNet* net_dev, bool fast1, int C, int T, const int8_t* x, long long B,
+                        int8_t* logits, int8_t* t1, int8_t* t2, int8_t* t3, int8_t* t4, int num_sms,
+                        cudaStream_t stream) {
+#define X(c, t) if (C == c && T == t) return launch_pipe_instance<c, t>(net_dev, fast1, x, B, logits, t1, t2, t3, t4, num_sms, stream);
+    MIBMI_PIPE_SHAPES(X)
+#undef X
+    return cudaErrorInvalidValue;
+}
+
+}  // namespace mibmi

@@ -1,0 +1,94 @@
+// Inline-PTX helpers shared by the sm_100a kernels: mbarrier, bulk async copy (TMA), warp-level
+// int8 MMA, ldmatrix / stmatrix, saturating packs.  Fragment layouts were checked on the box with
+// tools/probe_ldsm.cu.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace mibmi {
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+// ---- mbarrier -------------------------------------------------------------------------------
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_fence_init() {
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t done = 0;
+    for (uint32_t spins = 0; !done; ++spins) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+        if (spins > (1u << 22)) __trap();   // never hang the box: a lost arrival becomes a launch failure
+    }
+}
+// TMA bulk copy global -> shared, completion counted in bytes on an mbarrier (SASS: UBLKCP)
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+
+// ---- warp-level int8 MMA (SASS: IMMA.16832.S8.S8 / IMMA.16816.S8.S8) --------------------------
+//   A (row)  a0: (row g, k 4q..4q+3)  a1: (row g+8, k 4q..)  a2: (row g, k 16+4q..)  a3: (row g+8, k 16+4q..)
+//   B (col)  b0: (k 4q..4q+3, col g)  b1: (k 16+4q.., col g)
+//   C        c0, c1: (row g, cols 2q, 2q+1)   c2, c3: (row g+8, cols 2q, 2q+1)        g = lane>>2, q = lane&3
+__device__ __forceinline__ void mma_k32(int (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.s8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+r"(d[0]), "+r"(d[1]), "+r"(d[2]), "+r"(d[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ void mma_k16(int (&d)[4], uint32_t a0, uint32_t a1, uint32_t b0) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.s32.s8.s8.s32 {%0,%1,%2,%3}, {%4,%5}, {%6}, {%0,%1,%2,%3};"
+                 : "+r"(d[0]), "+r"(d[1]), "+r"(d[2]), "+r"(d[3]) : "r"(a0), "r"(a1), "r"(b0));
+}
+
+// ---- ldmatrix / stmatrix ----------------------------------------------------------------------
+// four 8x16-byte matrices; lane l supplies the address of row (l & 7) of matrix (l >> 3); register j of
+// thread (g, q) = bytes 4q..4q+3 of row g of matrix j
+__device__ __forceinline__ void ldsm_x4(uint32_t (&r)[4], uint32_t addr) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr) : "memory");
+}
+__device__ __forceinline__ void stsm_x4(uint32_t addr, uint32_t r0, uint32_t r1, uint32_t r2, uint32_t r3) {
+    asm volatile("stmatrix.sync.aligned.m8n8.x4.shared.b16 [%0], {%1,%2,%3,%4};"
+                 ::"r"(addr), "r"(r0), "r"(r1), "r"(r2), "r"(r3) : "memory");
+}
+// transposing byte load: 16 rows x 16 bytes per matrix, lane l (l < 16 per matrix; lanes 16..31 address the
+// second matrix of .x2) supplies row l & 15.  Thread (g, q) receives per matrix M
+//   r0 = { M[4q][g], M[4q+1][g], M[4q+2][g], M[4q+3][g] }      r1 = the same rows at column g + 8
+__device__ __forceinline__ void ldsm_t_x1(uint32_t (&r)[2], uint32_t addr) {
+    asm volatile("ldmatrix.sync.aligned.m16n16.x1.trans.shared.b8 {%0,%1}, [%2];"
+                 : "=r"(r[0]), "=r"(r[1]) : "r"(addr) : "memory");
+}
+__device__ __forceinline__ void ldsm_t_x2(uint32_t (&r)[4], uint32_t addr) {
+    asm volatile("ldmatrix.sync.aligned.m16n16.x2.trans.shared.b8 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr) : "memory");
+}
+
+// ---- saturating packs (SASS: I2IP.S8.S32.SAT) --------------------------------------------------
+// bytes (v0, v1, v2, v3) -> one word, each saturated to [-128, 127]
+__device__ __forceinline__ uint32_t pack4_sat(int v0, int v1, int v2, int v3) {
+    uint32_t t, d;
+    asm("cvt.pack.sat.s8.s32.b32 %0, %1, %2, 0;" : "=r"(t) : "r"(v3), "r"(v2));
+    asm("cvt.pack.sat.s8.s32.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(v1), "r"(v0), "r"(t));
+    return d;
+}
+// bytes (v0, v1) in the low half-word
+__device__ __forceinline__ uint32_t pack2_sat(int v0, int v1) {
+    uint32_t d;
+    asm("cvt.pack.sat.s8.s32.b32 %0, %1, %2, 0;" : "=r"(d) : "r"(v1), "r"(v0));
+    return d;
+}
+
+}  // namespace mibmi

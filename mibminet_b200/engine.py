@@ -19,7 +19,8 @@ from . import _lib
 from .convert import WolfParams, align4, params_from_export, params_from_state_dict
 
 _LAYOUTS = {"bct": _lib.LAYOUT_BCT, "btc": _lib.LAYOUT_BTC}
-_PATHS = {"auto": _lib.PATH_AUTO, "generic": _lib.PATH_GENERIC, "fused": _lib.PATH_FUSED}
+_PATHS = {"auto": _lib.PATH_AUTO, "generic": _lib.PATH_GENERIC, "fused": _lib.PATH_FUSED,
+          "fused_v1": _lib.PATH_FUSED_V1}
 _PATH_NAMES = {v: k for k, v in _PATHS.items()}
 
 
