@@ -40,7 +40,7 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=65536, help="trials per GPU per step")
-    ap.add_argument("--path", default="auto", choices=["auto", "fused", "generic"])
+    ap.add_argument("--path", default="auto", choices=["auto", "fused", "fused_v1", "generic"])
     ap.add_argument("--ctas-per-sm", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")

@@ -35,7 +35,8 @@ namespace mibmi {
 
 constexpr int kAW = 8;                        // layer-1 warps
 constexpr int kBW = 16;                       // layer-2/3 warps (one channel each)
-constexpr int kPipeThreads = (kAW + kBW + 1) * 32;
+constexpr int kCW = 2;                         // layer-4/5 warps (alternate trials)
+constexpr int kPipeThreads = (kAW + kBW + kCW + 1) * 32;   // + 1 TMA producer warp
 
 template <int C_, int T_, int S_>
 struct PCfg {
@@ -64,13 +65,15 @@ struct PCfg {
     static constexpr int OFF_Y2 = OFF_Y1 + 2 * Y1_BYTES;
     static constexpr int OFF_Y3 = OFF_Y2 + 16 * Y2S;
     static constexpr int OFF_Y4 = OFF_Y3 + 2 * Y3_BYTES;
-    static constexpr int SMEM = ((OFF_Y4 + 16 * T64P + 127) / 128) * 128;
+    static constexpr int Y4_BYTES = ((16 * T64P + 15) / 16) * 16;
+    static constexpr int SMEM = ((OFF_Y4 + kCW * Y4_BYTES + 127) / 128) * 128;
     static_assert(T % 32 == 0, "bulk-copy loader: whole 32-sample units and 16-byte rows");
     static_assert(T8 % 2 == 0, "layer 3 stores sample pairs");
     static_assert(KB16 >= 1 && KB16 <= kPipeMaxKB16, "C <= 64");
     static_assert(UNITS + 1 <= NCH - 1, "layer-1 chunks fit the planes with one zero chunk on each side");
     static_assert(16 * S + 64 <= 256, "barrier area");
     static_assert(KST5 <= kPipeMaxKst5, "T too large for PipeNet::w5frag");
+    static_assert(kCW == 2, "y3 is double buffered: one layer-4/5 warp per buffer");
     static_assert(SMEM <= 227 * 1024, "shared memory");
 };
 
@@ -155,13 +158,16 @@ pipe_forward_kernel(const PipeNet* __restrict__ net, const int8_t* __restrict__ 
                 for (int j = 0; j < 4; j++) { acc[j][0] = acc[j][1] = off_lo; acc[j][2] = acc[j][3] = off_hi; }
 #pragma unroll
                 for (int th = 0; th < 2; th++) {
+                    // one m16n8k16 per (16-channel block, n-tile): ldmatrix registers feed the MMAs as they
+                    // are (an m16n8k32 would want the two k-halves of one n-tile in adjacent registers)
 #pragma unroll
                     for (int s = 0; s < K::KP; s++) {
                         uint32_t d[4];
                         ldsm_t_x2(d, xb + xoff[s] + 32 * u + 16 * th);
-                        const uint32_t a[4] = {afr[2 * s][0], afr[2 * s][1], afr[2 * s + 1][0], afr[2 * s + 1][1]};
-                        mma_k32(acc[2 * th], a, d[0], d[2]);
-                        mma_k32(acc[2 * th + 1], a, d[1], d[3]);
+                        mma_k16(acc[2 * th], afr[2 * s][0], afr[2 * s][1], d[0]);
+                        mma_k16(acc[2 * th + 1], afr[2 * s][0], afr[2 * s][1], d[1]);
+                        mma_k16(acc[2 * th], afr[2 * s + 1][0], afr[2 * s + 1][1], d[2]);
+                        mma_k16(acc[2 * th + 1], afr[2 * s + 1][0], afr[2 * s + 1][1], d[3]);
                     }
                     if (K::KR) {
                         uint32_t d[2];
@@ -295,9 +301,9 @@ pipe_forward_kernel(const PipeNet* __restrict__ net, const int8_t* __restrict__ 
             __syncwarp();
             if (lane == 0) mbar_arrive(sbase + K::BAR_FULL_Y3 + 8 * buf);
         }
-    } else {
+    } else if (warp == kAW + kBW + kCW) {
         // =====================================================================================
-        // C: TMA producer, layers 4 + 5
+        // P: TMA producer -- refill the stage of trial n with trial n + S as soon as layer 1 released it
         // =====================================================================================
         auto issue = [&](int st, int n) {
             const int8_t* src = x + (size_t)(first + (long long)n * stride) * K::TRIAL_BYTES;
@@ -307,9 +313,19 @@ pipe_forward_kernel(const PipeNet* __restrict__ net, const int8_t* __restrict__ 
             bulk_g2s(dst, src, K::CA * K::T, bar);
             if (K::CB > 0) bulk_g2s(dst + K::ROFF, src + K::CA * K::T, K::CB * K::T, bar);
         };
-        if (lane == 0)
+        if (lane == 0) {
             for (int s = 0; s < K::S && s < nloc; s++) issue(s, s);
-
+            for (int n = 0; n + K::S < nloc; n++) {
+                const int st = n % K::S;
+                mbar_wait(sbase + K::BAR_EMPTY_X + 8 * st, (n / K::S) & 1);
+                issue(st, n + K::S);
+            }
+        }
+    } else {
+        // =====================================================================================
+        // C: layers 4 + 5; warp j handles the trials with n = j (mod 2), i.e. y3 buffer j
+        // =====================================================================================
+        const int cj = warp - (kAW + kBW);
         const uint32_t w4a0 = net->w4frag[0][lane], w4a1 = net->w4frag[1][lane];
         const int thr_lo = net->thr4[g], thr_hi = net->thr4[g + 8];
         const int sig_lo = net->sig4[g], sig_hi = net->sig4[g + 8];
@@ -317,16 +333,17 @@ pipe_forward_kernel(const PipeNet* __restrict__ net, const int8_t* __restrict__ 
         const int m4_lo = net->m4[g], m4_hi = net->m4[g + 8], sh4_lo = net->sh4[g], sh4_hi = net->sh4[g + 8];
         const int b5 = net->b5[g & 3], m5 = net->m5, sh5 = net->sh5;
         const uint32_t l4_off = (lane & 15) * K::Y3S + 16 * (lane >> 4);
-        uint8_t* y4 = smem + K::OFF_Y4;
+        uint8_t* y4 = smem + K::OFF_Y4 + cj * K::Y4_BYTES;
+        uint32_t w5a[K::KST5 <= 4 ? K::KST5 : 1][2];
+        if (K::KST5 <= 4) {
+#pragma unroll
+            for (int ks = 0; ks < K::KST5; ks++) { w5a[ks][0] = net->w5frag[ks][0][lane]; w5a[ks][1] = net->w5frag[ks][1][lane]; }
+        }
         const uint32_t* y4w = reinterpret_cast<const uint32_t*>(y4);
 
-        for (int n = 0; n < nloc; n++) {
-            const int st = n % K::S, buf = n & 1, par = (n >> 1) & 1;
+        for (int n = cj; n < nloc; n += kCW) {
+            const int buf = cj, par = (n >> 1) & 1;
             const long long b = first + (long long)n * stride;
-            if (n + K::S < nloc) {      // refill the stage trial n used with trial n + S
-                mbar_wait(sbase + K::BAR_EMPTY_X + 8 * st, (n / K::S) & 1);
-                if (lane == 0) issue(st, n + K::S);
-            }
             mbar_wait(sbase + K::BAR_FULL_Y3 + 8 * buf, par);
             const uint32_t y3a = sbase + K::OFF_Y3 + buf * K::Y3_BYTES + l4_off;
 #pragma unroll
@@ -363,7 +380,8 @@ pipe_forward_kernel(const PipeNet* __restrict__ net, const int8_t* __restrict__ 
             int z[4] = {0, 0, 0, 0};
 #pragma unroll
             for (int ks = 0; ks < K::KST5; ks++) {
-                const uint32_t a[4] = {__ldg(&net->w5frag[ks][0][lane]), 0u, __ldg(&net->w5frag[ks][1][lane]), 0u};
+                const uint32_t a[4] = {K::KST5 <= 4 ? w5a[K::KST5 <= 4 ? ks : 0][0] : __ldg(&net->w5frag[ks][0][lane]), 0u,
+                                       K::KST5 <= 4 ? w5a[K::KST5 <= 4 ? ks : 0][1] : __ldg(&net->w5frag[ks][1][lane]), 0u};
                 const uint32_t b0 = g == 0 ? y4w[8 * ks + q] : 0u, b1 = g == 0 ? y4w[8 * ks + 4 + q] : 0u;
                 mma_k32(z, a, b0, b1);
             }
