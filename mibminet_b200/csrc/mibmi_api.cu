@@ -205,9 +205,6 @@ bool magic32_for(int64_t d, int64_t xmax, int* m) {
     return true;
 }
 
-// position p (0..15) inside a 16-byte chunk of a layer-1 output row holds sample sigma(p) of the chunk
-// (the order stmatrix leaves the MMA accumulator fragments in, mibmi_pipe.cu)
-inline int y1_sigma(int p) { return (p & 1) + 2 * (p >> 2) + 8 * ((p >> 1) & 1); }
 
 bool pack_pipe(const mibmi_params_t* p, PipeNet* f, const char** why) {
     const int C = p->C, T = p->T, F2 = p->F2, CA4 = align4(C);
@@ -240,10 +237,12 @@ bool pack_pipe(const mibmi_params_t* p, PipeNet* f, const char** why) {
         else if (!magic_for(d, &f->m1[k], &f->sh1[k])) { *why = "|l1_factor| < 4"; return false; }
     }
     f->fast1 = fast1 ? 1 : 0;
+    // W1 is the B operand of layer 1: [block][n-tile][lane] = channels (ldmatrix rows) 4q..4q+3 of the
+    // block, filter 8 nt + g
     for (int kb = 0; kb < (C + 15) / 16; kb++)
-        for (int hf = 0; hf < 2; hf++)
+        for (int nt = 0; nt < 2; nt++)
             for (int lane = 0; lane < 32; lane++) {
-                const int g = lane >> 2, q = lane & 3, row = g + 8 * hf;
+                const int g = lane >> 2, q = lane & 3, row = 8 * nt + g;
                 const int sg = p->l1_factor[row] < 0 ? -1 : 1;
                 uint32_t word = 0;
                 for (int i = 0; i < 4; i++) {
@@ -254,10 +253,10 @@ bool pack_pipe(const mibmi_params_t* p, PipeNet* f, const char** why) {
                     const int w = valid ? sg * p->l1_weight_align[row * CA4 + c] : 0;
                     word |= (uint32_t)(uint8_t)(int8_t)w << (8 * i);
                 }
-                f->w1blk[kb][hf][lane] = word;
+                f->w1blk[kb][nt][lane] = word;
             }
     // ---- layer 2: Toeplitz B fragments.  Window-relative sample j = o + 1 + tap (o = output offset in
-    // the 32-sample window), K position kk of k-step s <-> j = 32 s + 16 (kk / 16) + sigma(kk % 16)
+    // the 32-sample window), K position kk of k-step s <-> j = 32 s + kk
     for (int k = 0; k < 16; k++) {
         const int8_t* w = p->l2_weight_reverse + k * 64;
         int64_t sum = 0;
@@ -273,7 +272,7 @@ bool pack_pipe(const mibmi_params_t* p, PipeNet* f, const char** why) {
                         const int o = 8 * (g >> 1) + 2 * v + (g & 1);
                         uint32_t word = 0;
                         for (int i = 0; i < 4; i++) {
-                            const int j = 32 * s + 16 * h + y1_sigma(4 * q + i);
+                            const int j = 32 * s + 16 * h + 4 * q + i;
                             const int tap = j - o - 1;
                             const int val = (tap >= 0 && tap < 64) ? w[tap] : 0;
                             word |= (uint32_t)(uint8_t)(int8_t)val << (8 * i);

@@ -70,7 +70,7 @@ constexpr int kPipeMaxKB16 = 4;     // layer-1 blocks of 16 channels (C <= 64)
 constexpr int kPipeMaxKst5 = 16;    // layer-5 k-steps of 32 (T/64 padded to even <= 32)
 
 struct PipeNet {
-    // layer 1: A fragments per 16-channel block: [block][row half (g, g+8)][lane]
+    // layer 1: W1 as MMA B fragments per 16-channel block: [block][filter n-tile (0-7, 8-15)][lane]
     uint32_t w1blk[kPipeMaxKB16][2][32];
     int off1[16], m1[16], sh1[16];
     int fast1;                      // 1: sh1 == 0 everywhere (magic = floor(2^32/d)+1, exact after clip8)

@@ -130,20 +130,30 @@ pipe_forward_kernel(const PipeNet* __restrict__ net, const int8_t* __restrict__ 
         // =====================================================================================
         // A: layer 1
         // =====================================================================================
-        uint32_t afr[K::KB16][2];
+        // W1 as the B operand: [block][filter n-tile][lane] = (channels 4q..4q+3 of the block, filter 8 nt + g)
+        uint32_t wfr[K::KB16][2];
 #pragma unroll
         for (int kb = 0; kb < K::KB16; kb++) {
-            afr[kb][0] = net->w1blk[kb][0][lane];
-            afr[kb][1] = net->w1blk[kb][1][lane];
+            wfr[kb][0] = net->w1blk[kb][0][lane];
+            wfr[kb][1] = net->w1blk[kb][1][lane];
         }
-        const int off_lo = net->off1[g], off_hi = net->off1[g + 8];
-        const int m_lo = net->m1[g], m_hi = net->m1[g + 8], sh_lo = net->sh1[g], sh_hi = net->sh1[g + 8];
+        // accumulator columns 2q, 2q+1 of n-tile nt <-> filters 8 nt + 2q, + 1
+        int off1[2][2], mg1[2][2], sh1[2][2];
+#pragma unroll
+        for (int nt = 0; nt < 2; nt++)
+#pragma unroll
+            for (int e = 0; e < 2; e++) {
+                off1[nt][e] = net->off1[8 * nt + 2 * q + e];
+                mg1[nt][e] = net->m1[8 * nt + 2 * q + e];
+                sh1[nt][e] = net->sh1[8 * nt + 2 * q + e];
+            }
         uint32_t xoff[K::KP + 1];
 #pragma unroll
         for (int s = 0; s < K::KP; s++) xoff[s] = l1_row_offset<K>(2 * s + (lane >> 4), lane & 15);
         if (K::KR) xoff[K::KP] = l1_row_offset<K>(K::KB16 - 1, lane & 15);
-        // stmatrix: matrix j = lane >> 3 holds filters 8 (j >> 1) .. +7 of plane (j & 1); chunk u + 1
-        const uint32_t st_off = ((lane & 7) + 8 * (lane >> 4)) * K::Y1S + ((lane >> 3) & 1) * K::PLANE + 16;
+        // stmatrix.trans: matrix j = lane >> 3 = 2 mt + nt holds filters 8 nt .. + 7, samples 16 mt .. + 15 of the
+        // unit, i.e. chunk 2 (u + 1) + mt = plane mt, index u + 1
+        const uint32_t st_off = ((lane & 7) + 8 * ((lane >> 3) & 1)) * K::Y1S + (lane >> 4) * K::PLANE + 16;
 
         for (int n = 0; n < nloc; n++) {
             const int st = n % K::S, buf = n & 1;
@@ -153,53 +163,52 @@ pipe_forward_kernel(const PipeNet* __restrict__ net, const int8_t* __restrict__ 
             const uint32_t yb = sbase + K::OFF_Y1 + buf * K::Y1_BYTES + st_off;
 #pragma unroll 1
             for (int u = warp; u < K::UNITS; u += kAW) {
-                int acc[4][4];
+                // D[16 samples x 8 filters] += X^T[16 samples x 32 ch] * W1^T[32 ch x 8 filters]: the four
+                // registers of one transposing ldmatrix.x2 are exactly one A fragment
+                int acc[2][2][4];
 #pragma unroll
-                for (int j = 0; j < 4; j++) { acc[j][0] = acc[j][1] = off_lo; acc[j][2] = acc[j][3] = off_hi; }
+                for (int mt = 0; mt < 2; mt++)
 #pragma unroll
-                for (int th = 0; th < 2; th++) {
-                    // one m16n8k16 per (16-channel block, n-tile): ldmatrix registers feed the MMAs as they
-                    // are (an m16n8k32 would want the two k-halves of one n-tile in adjacent registers)
+                    for (int nt = 0; nt < 2; nt++) {
+                        acc[mt][nt][0] = acc[mt][nt][2] = off1[nt][0];
+                        acc[mt][nt][1] = acc[mt][nt][3] = off1[nt][1];
+                    }
+#pragma unroll
+                for (int mt = 0; mt < 2; mt++) {
 #pragma unroll
                     for (int s = 0; s < K::KP; s++) {
                         uint32_t d[4];
-                        ldsm_t_x2(d, xb + xoff[s] + 32 * u + 16 * th);
-                        mma_k16(acc[2 * th], afr[2 * s][0], afr[2 * s][1], d[0]);
-                        mma_k16(acc[2 * th + 1], afr[2 * s][0], afr[2 * s][1], d[1]);
-                        mma_k16(acc[2 * th], afr[2 * s + 1][0], afr[2 * s + 1][1], d[2]);
-                        mma_k16(acc[2 * th + 1], afr[2 * s + 1][0], afr[2 * s + 1][1], d[3]);
+                        ldsm_t_x2(d, xb + xoff[s] + 32 * u + 16 * mt);
+                        mma_k32(acc[mt][0], d, wfr[2 * s][0], wfr[2 * s + 1][0]);
+                        mma_k32(acc[mt][1], d, wfr[2 * s][1], wfr[2 * s + 1][1]);
                     }
                     if (K::KR) {
                         uint32_t d[2];
-                        ldsm_t_x1(d, xb + xoff[K::KP] + 32 * u + 16 * th);
-                        mma_k16(acc[2 * th], afr[K::KB16 - 1][0], afr[K::KB16 - 1][1], d[0]);
-                        mma_k16(acc[2 * th + 1], afr[K::KB16 - 1][0], afr[K::KB16 - 1][1], d[1]);
+                        ldsm_t_x1(d, xb + xoff[K::KP] + 32 * u + 16 * mt);
+                        mma_k16(acc[mt][0], d[0], d[1], wfr[K::KB16 - 1][0]);
+                        mma_k16(acc[mt][1], d[0], d[1], wfr[K::KB16 - 1][1]);
                     }
                 }
-                // requant; thread (g, q) owns samples 32u + 8nt + 2q, +1 (nt = 0..3) of filters g and g + 8
-                int v[4][4];
+                // requant; thread (g, q) owns samples 32u + 16mt + g, + 8 of filters 8nt + 2q, + 1
+                uint32_t w[2][2];
 #pragma unroll
-                for (int nt = 0; nt < 4; nt++) {
-                    v[nt][0] = tdiv1<FAST1>(acc[nt][0], m_lo, sh_lo);
-                    v[nt][1] = tdiv1<FAST1>(acc[nt][1], m_lo, sh_lo);
-                    v[nt][2] = tdiv1<FAST1>(acc[nt][2], m_hi, sh_hi);
-                    v[nt][3] = tdiv1<FAST1>(acc[nt][3], m_hi, sh_hi);
-                }
-                const uint32_t w00 = pack4_sat(v[0][0], v[0][1], v[1][0], v[1][1]);   // filter g,     chunk 2u
-                const uint32_t w01 = pack4_sat(v[2][0], v[2][1], v[3][0], v[3][1]);   // filter g,     chunk 2u + 1
-                const uint32_t w10 = pack4_sat(v[0][2], v[0][3], v[1][2], v[1][3]);   // filter g + 8, chunk 2u
-                const uint32_t w11 = pack4_sat(v[2][2], v[2][3], v[3][2], v[3][3]);   // filter g + 8, chunk 2u + 1
-                stsm_x4(yb + 16 * u, w00, w01, w10, w11);
-                if (TAPS && tap1) {
-                    const long long b = first + (long long)n * stride;
+                for (int mt = 0; mt < 2; mt++)
 #pragma unroll
-                    for (int nt = 0; nt < 4; nt++)
+                    for (int nt = 0; nt < 2; nt++) {
+                        int v[4];
 #pragma unroll
-                        for (int e = 0; e < 4; e++) {
-                            const int f = g + 8 * (e >> 1), t = 32 * u + 8 * nt + 2 * q + (e & 1);
-                            tap1[((size_t)b * 16 + f) * K::T + t] = (int8_t)clip8(v[nt][e]);
+                        for (int c = 0; c < 4; c++) v[c] = tdiv1<FAST1>(acc[mt][nt][c], mg1[nt][c & 1], sh1[nt][c & 1]);
+                        w[mt][nt] = pack4_sat(v[0], v[1], v[2], v[3]);
+                        if (TAPS && tap1) {
+                            const long long b = first + (long long)n * stride;
+#pragma unroll
+                            for (int c = 0; c < 4; c++) {
+                                const int f = 8 * nt + 2 * q + (c & 1), t = 32 * u + 16 * mt + g + 8 * (c >> 1);
+                                tap1[((size_t)b * 16 + f) * K::T + t] = (int8_t)clip8(v[c]);
+                            }
                         }
-                }
+                    }
+                stsm_t8_x4(yb + 16 * u, w[0][0], w[0][1], w[1][0], w[1][1]);
             }
             __syncwarp();
             if (lane == 0) {

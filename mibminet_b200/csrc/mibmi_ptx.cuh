@@ -64,6 +64,13 @@ __device__ __forceinline__ void stsm_x4(uint32_t addr, uint32_t r0, uint32_t r1,
     asm volatile("stmatrix.sync.aligned.m8n8.x4.shared.b16 [%0], {%1,%2,%3,%4};"
                  ::"r"(addr), "r"(r0), "r"(r1), "r"(r2), "r"(r3) : "memory");
 }
+// transposing byte store of MMA accumulator fragments: four 16x8 byte matrices V; register j of thread (g, q)
+// holds { V[g][2q], V[g][2q+1], V[g+8][2q], V[g+8][2q+1] } of matrix j (the m16n8 C-fragment order, saturated
+// to bytes); memory receives V^T: row c (8 rows of 16 bytes, address from lane 8 j + c) = column c of V
+__device__ __forceinline__ void stsm_t8_x4(uint32_t addr, uint32_t r0, uint32_t r1, uint32_t r2, uint32_t r3) {
+    asm volatile("stmatrix.sync.aligned.m16n8.x4.trans.shared.b8 [%0], {%1,%2,%3,%4};"
+                 ::"r"(addr), "r"(r0), "r"(r1), "r"(r2), "r"(r3) : "memory");
+}
 // transposing byte load: 16 rows x 16 bytes per matrix, lane l (l < 16 per matrix; lanes 16..31 address the
 // second matrix of .x2) supplies row l & 15.  Thread (g, q) receives per matrix M
 //   r0 = { M[4q][g], M[4q+1][g], M[4q+2][g], M[4q+3][g] }      r1 = the same rows at column g + 8
