@@ -30,6 +30,10 @@ sys.path.insert(0, ROOT)
 C, T, N_CLASSES, NET_SEED = 64, 480, 4, 0
 ALG_BYTES_PER_TRIAL = C * T + N_CLASSES          # int8 input + 4 B logits
 METRIC = "int8 edgeEEGNet trials/sec"
+# ncu (profiles/r1b_ncu_full_metrics.csv): 2.013346 GB read + 3.9255 MB written per launch of 65536 trials
+NCU_TRAFFIC_BYTES_PER_TRIAL = (2.013346e9 + 3.925504e6) / 65536
+KERNEL_NAMES = {"fused": "pipe_forward_kernel<PCfg<64,480,4>>", "fused_v1": "fused_forward_kernel<Cfg<64,480>>",
+                "generic": "generic_forward_kernel"}
 WORKLOAD = "edgeEEGNet int8 forward, PhysionetMMMI shape 64ch x 480 samples, 4 classes (BASELINE config 2)"
 
 
@@ -265,9 +269,12 @@ def main():
                        "collective": "one NCCL all_gather of int8 logits per step" if world > 1 else "none",
                        "kernel_path": net.last_path, "bit_exact_checked": None},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "peak_source": peak_src, "kernel": "fused_forward_kernel<Cfg<64,480>>",
+                         "traffic": NCU_TRAFFIC_BYTES_PER_TRIAL * B if net.last_path == "fused" else None,
+                         "traffic_source": "ncu --set full dram__bytes_read.sum + dram__bytes_write.sum per launch of 65536 "
+                                           "trials (profiles/r1b_ncu_full_metrics.csv), scaled to this batch",
+                         "peak_source": peak_src, "kernel": KERNEL_NAMES.get(net.last_path, net.last_path),
                          "kernel_ms": ms_kernel, "alg_bytes_per_trial": ALG_BYTES_PER_TRIAL,
-                         "note": "ALU-pipe bound (requantisation), see DESIGN.md"},
+                         "note": "latency/issue bound (27 warps per SM, 47 % issue slots, IMMA pipe 38 %), see DESIGN.md"},
             "gpu_launches": int(launches), "clocks": clocks, "e2e": e2e,
         }
         if not args.no_cpu_baseline:
