@@ -46,6 +46,7 @@ def parse_args():
     ap.add_argument("--batch", type=int, default=65536, help="trials per GPU per step")
     ap.add_argument("--path", default="auto", choices=["auto", "fused", "fused_v1", "generic"])
     ap.add_argument("--ctas-per-sm", type=int, default=0)
+    ap.add_argument("--shape", default="64x480", help="CxT of the trials (default: BASELINE config 2; 22x1125 = config 3)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
@@ -154,7 +155,12 @@ def main_reference(args, rank):
 
 
 def main():
+    global C, T, ALG_BYTES_PER_TRIAL, WORKLOAD
     args = parse_args()
+    if args.shape != "64x480":
+        C, T = (int(v) for v in args.shape.split("x"))
+        ALG_BYTES_PER_TRIAL = C * T + N_CLASSES
+        WORKLOAD = f"edgeEEGNet int8 forward, {C}ch x {T} samples, 4 classes (--shape {args.shape})"
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -265,14 +271,14 @@ def main():
             "vs_baseline": None, "dtype": "int8", "data": "synthetic",
             "config": {"workload": WORKLOAD, "trials_per_gpu_per_step": B, "global_batch": world * B,
                        "layout": "[B][C][T] int8 (module order)", "parallelism": f"trial-batch sharding x{world}",
-                       "l2_policy": "input per step 2.01 GB > 126 MB L2, no flush needed",
+                       "l2_policy": f"input per step {B * C * T / 1e9:.2f} GB > 126 MB L2, no flush needed",
                        "collective": "one NCCL all_gather of int8 logits per step" if world > 1 else "none",
                        "kernel_path": net.last_path, "bit_exact_checked": None},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": NCU_TRAFFIC_BYTES_PER_TRIAL * B if net.last_path == "fused" else None,
+                         "traffic": NCU_TRAFFIC_BYTES_PER_TRIAL * B if (net.last_path == "fused" and args.shape == "64x480") else None,
                          "traffic_source": "ncu --set full dram__bytes_read.sum + dram__bytes_write.sum per launch of 65536 "
                                            "trials (profiles/r1b_ncu_full_metrics.csv), scaled to this batch",
-                         "peak_source": peak_src, "kernel": KERNEL_NAMES.get(net.last_path, net.last_path),
+                         "peak_source": peak_src, "kernel": KERNEL_NAMES.get(net.last_path, net.last_path).replace("64,480", f"{C},{T}"),
                          "kernel_ms": ms_kernel, "alg_bytes_per_trial": ALG_BYTES_PER_TRIAL,
                          "note": "latency/issue bound (27 warps per SM, 47 % issue slots, IMMA pipe 38 %), see DESIGN.md"},
             "gpu_launches": int(launches), "clocks": clocks, "e2e": e2e,

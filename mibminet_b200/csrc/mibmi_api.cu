@@ -248,8 +248,11 @@ bool pack_pipe(const mibmi_params_t* p, PipeNet* f, const char** why) {
                 for (int i = 0; i < 4; i++) {
                     const int r = 4 * q + i;                       // K position in the block = ldmatrix row
                     const int region = (r >> 2) & 1, idx = 8 * kb + 4 * (r >> 3) + (r & 3);
-                    const bool valid = idx < (region ? half1 : half0);
-                    const int c = region ? half0 + idx : idx;
+                    // rows that are not 16-byte aligned (T % 16 != 0) go through the realigning loader, whose
+                    // scratch keeps the natural channel order; otherwise the two channel halves interleave
+                    const bool natural = (T % 16) != 0;
+                    const bool valid = natural ? (16 * kb + r < C) : (idx < (region ? half1 : half0));
+                    const int c = natural ? 16 * kb + r : (region ? half0 + idx : idx);
                     const int w = valid ? sg * p->l1_weight_align[row * CA4 + c] : 0;
                     word |= (uint32_t)(uint8_t)(int8_t)w << (8 * i);
                 }

@@ -43,9 +43,14 @@ struct PCfg {
     static constexpr int C = C_, T = T_, S = S_;
     static constexpr int KB16 = (C + 15) / 16, KP = KB16 / 2, KR = KB16 % 2;
     static constexpr int CA = (C + 1) / 2, CB = C - CA;          // channel halves (two bulk copies)
-    static constexpr int ROFF = CA * T + 16;                     // second half: +16 B modulo 128
+    // REAL: rows of T bytes are not 16-byte aligned in global memory (T % 16 != 0, e.g. 22 x 1125): every row
+    // is bulk-copied from the 16-byte boundary below it and the layer-1 warps shift it into place (see A)
+    static constexpr bool REAL = (T % 16) != 0;
     static constexpr int T8 = T / 8, T64 = T8 / 8;
-    static constexpr int UNITS = T / 32;                         // layer-1 units of 32 samples
+    static constexpr int UNITS = (T + 31) / 32;                  // layer-1 units of 32 samples
+    static constexpr int XP = REAL ? 32 * UNITS + 48 : T;        // row pitch inside a stage
+    static constexpr int ROFF = REAL ? 0 : CA * T + 16;          // second half: +16 B modulo 128
+    static constexpr int SCR_ROW = 48, SCR_WARP = 32 * SCR_ROW;  // REAL: per-warp [32 ch][32 samples (+16 pad)]
     static constexpr int MROWS = (T8 * 8 + 31) / 32, MT = (MROWS + 15) / 16;
     static constexpr int NCH = 16 * MT + 2;                      // 16-byte chunks per plane
     static constexpr int PLANE = 16 * NCH, Y1S = 2 * PLANE + 16; // Y1S / 16 odd: conflict-free stmatrix
@@ -54,7 +59,7 @@ struct PCfg {
     static constexpr int NST = (T64 + 3) / 4;                    // layer-4 super-tiles of 4 pooling groups
     static constexpr int T64P = (T64 + 1) / 2 * 2, KST5 = T64P / 2;
     static constexpr int TRIAL_BYTES = C * T;
-    static constexpr int XS_BYTES = ((C * T + 16 + 127) / 128) * 128;
+    static constexpr int XS_BYTES = (((REAL ? C * XP : C * T + 16) + 127) / 128) * 128;
     static constexpr int Y1_BYTES = 16 * Y1S, Y3_BYTES = 16 * Y3S;
     // barriers (8 B each)
     static constexpr int BAR_FULL_X = 0, BAR_EMPTY_X = 8 * S, BAR_FULL_Y1 = 16 * S, BAR_EMPTY_Y1 = 16 * S + 16,
@@ -66,8 +71,10 @@ struct PCfg {
     static constexpr int OFF_Y3 = OFF_Y2 + 16 * Y2S;
     static constexpr int OFF_Y4 = OFF_Y3 + 2 * Y3_BYTES;
     static constexpr int Y4_BYTES = ((16 * T64P + 15) / 16) * 16;
-    static constexpr int SMEM = ((OFF_Y4 + kCW * Y4_BYTES + 127) / 128) * 128;
-    static_assert(T % 32 == 0, "bulk-copy loader: whole 32-sample units and 16-byte rows");
+    static constexpr int OFF_SCR = ((OFF_Y4 + kCW * Y4_BYTES + 15) / 16) * 16;
+    static constexpr int SMEM = ((OFF_SCR + (REAL ? kAW * SCR_WARP : 0) + 127) / 128) * 128;
+    static_assert(REAL || T % 32 == 0, "aligned loader: whole 32-sample units");
+    static_assert(!REAL || C <= 32, "realigning loader: one lane per channel");
     static_assert(T8 % 2 == 0, "layer 3 stores sample pairs");
     static_assert(KB16 >= 1 && KB16 <= kPipeMaxKB16, "C <= 64");
     static_assert(UNITS + 1 <= NCH - 1, "layer-1 chunks fit the planes with one zero chunk on each side");
@@ -147,10 +154,15 @@ pipe_forward_kernel(const PipeNet* __restrict__ net, const int8_t* __restrict__ 
                 mg1[nt][e] = net->m1[8 * nt + 2 * q + e];
                 sh1[nt][e] = net->sh1[8 * nt + 2 * q + e];
             }
+        // REAL: the operand rows come from this warp's scratch ([channel][48 B], natural channel order)
         uint32_t xoff[K::KP + 1];
 #pragma unroll
-        for (int s = 0; s < K::KP; s++) xoff[s] = l1_row_offset<K>(2 * s + (lane >> 4), lane & 15);
-        if (K::KR) xoff[K::KP] = l1_row_offset<K>(K::KB16 - 1, lane & 15);
+        for (int s = 0; s < K::KP; s++)
+            xoff[s] = K::REAL ? (uint32_t)(K::OFF_SCR + warp * K::SCR_WARP + (16 * (lane >> 4) + (lane & 15)) * K::SCR_ROW)
+                              : l1_row_offset<K>(2 * s + (lane >> 4), lane & 15);
+        if (K::KR) xoff[K::KP] = K::REAL ? (uint32_t)(K::OFF_SCR + warp * K::SCR_WARP + (lane & 15) * K::SCR_ROW)
+                                         : l1_row_offset<K>(K::KB16 - 1, lane & 15);
+        static_assert(!K::REAL || K::KB16 <= 2, "scratch holds 32 channels");
         // stmatrix.trans: matrix j = lane >> 3 = 2 mt + nt holds filters 8 nt .. + 7, samples 16 mt .. + 15 of the
         // unit, i.e. chunk 2 (u + 1) + mt = plane mt, index u + 1
         const uint32_t st_off = ((lane & 7) + 8 * ((lane >> 3) & 1)) * K::Y1S + (lane >> 4) * K::PLANE + 16;
@@ -159,10 +171,32 @@ pipe_forward_kernel(const PipeNet* __restrict__ net, const int8_t* __restrict__ 
             const int st = n % K::S, buf = n & 1;
             mbar_wait(sbase + K::BAR_FULL_X + 8 * st, (n / K::S) & 1);
             mbar_wait(sbase + K::BAR_EMPTY_Y1 + 8 * buf, ((n >> 1) & 1) ^ 1);
-            const uint32_t xb = sbase + K::OFF_XS + st * K::XS_BYTES;
+            const uint32_t xb = K::REAL ? sbase : sbase + K::OFF_XS + st * K::XS_BYTES;
             const uint32_t yb = sbase + K::OFF_Y1 + buf * K::Y1_BYTES + st_off;
+            // REAL: byte misalignment of row `lane` of this trial (x itself is 16-byte aligned)
+            const long long bq = first + (long long)n * stride;
+            const int rsh = K::REAL ? (int)((bq * (long long)(K::TRIAL_BYTES & 15) + (long long)lane * (K::T & 15)) & 15) : 0;
 #pragma unroll 1
             for (int u = warp; u < K::UNITS; u += kAW) {
+                if (K::REAL) {
+                    // shift 32 samples of every channel into place: 9 aligned words -> 8 funnel shifts -> scratch
+                    __syncwarp();
+                    if (lane < K::C) {
+                        const uint32_t* src = reinterpret_cast<const uint32_t*>(
+                            smem + K::OFF_XS + st * K::XS_BYTES + lane * K::XP + 32 * u + (rsh & ~3));
+                        uint32_t w[9], o[8];
+#pragma unroll
+                        for (int i = 0; i < 9; i++) w[i] = src[i];
+                        const int bs = 8 * (rsh & 3);
+#pragma unroll
+                        for (int i = 0; i < 8; i++) o[i] = __funnelshift_r(w[i], w[i + 1], bs);
+                        uint4* dst = reinterpret_cast<uint4*>(smem + K::OFF_SCR + warp * K::SCR_WARP + lane * K::SCR_ROW);
+                        dst[0] = make_uint4(o[0], o[1], o[2], o[3]);
+                        dst[1] = make_uint4(o[4], o[5], o[6], o[7]);
+                    }
+                    __syncwarp();
+                }
+                const uint32_t xu = K::REAL ? 0u : 32u * u;
                 // D[16 samples x 8 filters] += X^T[16 samples x 32 ch] * W1^T[32 ch x 8 filters]: the four
                 // registers of one transposing ldmatrix.x2 are exactly one A fragment
                 int acc[2][2][4];
@@ -178,13 +212,13 @@ pipe_forward_kernel(const PipeNet* __restrict__ net, const int8_t* __restrict__ 
 #pragma unroll
                     for (int s = 0; s < K::KP; s++) {
                         uint32_t d[4];
-                        ldsm_t_x2(d, xb + xoff[s] + 32 * u + 16 * mt);
+                        ldsm_t_x2(d, xb + xoff[s] + xu + 16 * mt);
                         mma_k32(acc[mt][0], d, wfr[2 * s][0], wfr[2 * s + 1][0]);
                         mma_k32(acc[mt][1], d, wfr[2 * s][1], wfr[2 * s + 1][1]);
                     }
                     if (K::KR) {
                         uint32_t d[2];
-                        ldsm_t_x1(d, xb + xoff[K::KP] + 32 * u + 16 * mt);
+                        ldsm_t_x1(d, xb + xoff[K::KP] + xu + 16 * mt);
                         mma_k16(acc[mt][0], d[0], d[1], wfr[K::KB16 - 1][0]);
                         mma_k16(acc[mt][1], d[0], d[1], wfr[K::KB16 - 1][1]);
                     }
@@ -197,14 +231,18 @@ pipe_forward_kernel(const PipeNet* __restrict__ net, const int8_t* __restrict__ 
                     for (int nt = 0; nt < 2; nt++) {
                         int v[4];
 #pragma unroll
-                        for (int c = 0; c < 4; c++) v[c] = tdiv1<FAST1>(acc[mt][nt][c], mg1[nt][c & 1], sh1[nt][c & 1]);
+                        for (int c = 0; c < 4; c++) {
+                            v[c] = tdiv1<FAST1>(acc[mt][nt][c], mg1[nt][c & 1], sh1[nt][c & 1]);
+                            // samples past T (only in the last unit) are layer 2's zero padding
+                            if (K::T % 32 != 0 && 32 * u + 16 * mt + g + 8 * (c >> 1) >= K::T) v[c] = 0;
+                        }
                         w[mt][nt] = pack4_sat(v[0], v[1], v[2], v[3]);
                         if (TAPS && tap1) {
                             const long long b = first + (long long)n * stride;
 #pragma unroll
                             for (int c = 0; c < 4; c++) {
                                 const int f = 8 * nt + 2 * q + (c & 1), t = 32 * u + 16 * mt + g + 8 * (c >> 1);
-                                tap1[((size_t)b * 16 + f) * K::T + t] = (int8_t)clip8(v[c]);
+                                if (t < K::T) tap1[((size_t)b * 16 + f) * K::T + t] = (int8_t)clip8(v[c]);
                             }
                         }
                     }
@@ -315,14 +353,25 @@ pipe_forward_kernel(const PipeNet* __restrict__ net, const int8_t* __restrict__ 
         // P: TMA producer -- refill the stage of trial n with trial n + S as soon as layer 1 released it
         // =====================================================================================
         auto issue = [&](int st, int n) {
-            const int8_t* src = x + (size_t)(first + (long long)n * stride) * K::TRIAL_BYTES;
+            const size_t toff = (size_t)(first + (long long)n * stride) * K::TRIAL_BYTES;
             const uint32_t dst = sbase + K::OFF_XS + st * K::XS_BYTES;
             const uint32_t bar = sbase + K::BAR_FULL_X + 8 * st;
-            mbar_expect_tx(bar, K::TRIAL_BYTES);
-            bulk_g2s(dst, src, K::CA * K::T, bar);
-            if (K::CB > 0) bulk_g2s(dst + K::ROFF, src + K::CA * K::T, K::CB * K::T, bar);
+            if (K::REAL) {
+                // lane c copies row c from the 16-byte boundary below it (x is 16-byte aligned); the last row of
+                // the last trial may read up to 15 bytes past the batch, inside its final 16-byte granule
+                const size_t off = toff + (size_t)lane * K::T;
+                const uint32_t bytes = lane < K::C ? (uint32_t)(((off & 15) + K::T + 15) & ~(size_t)15) : 0u;
+                const uint32_t total = __reduce_add_sync(0xffffffffu, bytes);
+                if (lane == 0) mbar_expect_tx(bar, total);
+                __syncwarp();
+                if (lane < K::C) bulk_g2s(dst + lane * K::XP, x + (off & ~(size_t)15), bytes, bar);
+            } else if (lane == 0) {
+                mbar_expect_tx(bar, K::TRIAL_BYTES);
+                bulk_g2s(dst, x + toff, K::CA * K::T, bar);
+                if (K::CB > 0) bulk_g2s(dst + K::ROFF, x + toff + K::CA * K::T, K::CB * K::T, bar);
+            }
         };
-        if (lane == 0) {
+        if (K::REAL || lane == 0) {
             for (int s = 0; s < K::S && s < nloc; s++) issue(s, s);
             for (int n = 0; n + K::S < nloc; n++) {
                 const int st = n % K::S;
@@ -417,7 +466,7 @@ static cudaError_t launch_pipe_instance(const PipeNet* net_dev, bool fast1, cons
     return cudaGetLastError();
 }
 
-#define MIBMI_PIPE_SHAPES(X) X(64, 480) X(38, 480) X(24, 480) X(19, 480) X(16, 480) X(8, 480)
+#define MIBMI_PIPE_SHAPES(X) X(64, 480) X(38, 480) X(24, 480) X(19, 480) X(16, 480) X(8, 480) X(22, 1125)
 
 bool pipe_has_instance(int C, int T) {
 #define X(c, t) if (C == c && T == t) return true;

@@ -13,7 +13,7 @@ from mibminet_b200.engine import Int8Net
 
 pytestmark = pytest.mark.gpu
 
-FUSED_SHAPES = [(64, 480), (38, 480), (24, 480), (19, 480), (16, 480), (8, 480)]
+FUSED_SHAPES = [(64, 480), (38, 480), (24, 480), (19, 480), (16, 480), (8, 480), (22, 1125)]
 
 
 def _cuda(x):
@@ -56,6 +56,21 @@ def test_reference_fixtures_taps_and_plain_variant(golden):
     assert np.array_equal(yp.cpu().numpy(), fx["c_plain"])   # follows the C (layer4.c:115-117)
     for name in ("y1", "y2", "y3"):
         assert np.array_equal(tp[name].cpu().numpy(), fx[f"golden_plain_{name}"]), name
+
+
+def test_reference_fixtures_taps_from_the_fused_kernel(golden):
+    """The pipeline kernel's diagnostic instantiation stores y1..y4 from its registers: every layer
+    of the fused path is pinned to the reference's per-layer outputs, not only the logits."""
+    fx = golden
+    net = Int8Net(fx["arrays"], C=fx["C"], T=fx["T"], device="cuda:0")
+    if not net.fused_supported()[0]:
+        pytest.skip(net.fused_supported()[1])
+    net.set_path("fused")
+    y, taps = net.forward_taps(_cuda(fx["x"]))
+    assert net.last_path == "fused"
+    for name in ("y1", "y2", "y3", "y4"):
+        assert np.array_equal(taps[name].cpu().numpy(), fx[f"golden_reorder_{name}"]), name
+    assert np.array_equal(y.cpu().numpy(), fx["golden_reorder"])
 
 
 def test_wolf_input_layout(golden):
@@ -111,6 +126,41 @@ def test_edge_batches_and_extreme_inputs():
     # empty batch
     y = net.forward(torch.empty((0, C, T), dtype=torch.int8, device="cuda:0"))
     assert y.shape == (0, 4)
+
+
+def test_unaligned_rows_22x1125_every_misalignment():
+    """BASELINE config 3 (BCI-IV-2a): rows of 1125 bytes are never 16-byte aligned; the byte shift of a
+    row depends on (trial, channel).  A 16-byte-aligned sub-batch view may start at any multiple of 8 trials."""
+    C, T = 22, 1125
+    net, arrays = _net(C, T, seed=51)
+    assert net.fused_supported()[0], net.fused_supported()[1]
+    B = 1237
+    x = synth.make_trials(B, C, T, seed=52)
+    ref = wolf_port.forward(arrays, C, T, x)
+    xd = _cuda(x)
+    y = net.forward(xd).cpu().numpy()
+    assert net.last_path == "fused"
+    assert np.array_equal(y, ref)
+    for lo in (8, 16, 1000):                      # views: lo * 24750 is a multiple of 16
+        assert np.array_equal(net.forward(xd[lo:]).cpu().numpy(), ref[lo:]), lo
+    for Bs in (1, 2, 7, 149):
+        assert np.array_equal(net.forward(xd[:Bs].clone()).cpu().numpy(), ref[:Bs]), Bs
+    # saturating inputs
+    xs = np.stack([np.full((C, T), v, np.int8) for v in (127, -127, -128, 0)])
+    assert np.array_equal(net.forward(_cuda(xs)).cpu().numpy(), wolf_port.forward(arrays, C, T, xs))
+
+
+def test_full_size_batch_22x1125_every_logit():
+    """BASELINE config 3 at 65536 trials: every logit against the CPU integer path + permutation property."""
+    C, T, B = 22, 1125, 65536
+    net, arrays = _net(C, T, seed=2)
+    x = synth.make_trials(B, C, T, seed=77)
+    y = net.forward(_cuda(x)).cpu().numpy()
+    assert net.last_path == "fused"
+    ref = wolf_port.forward(arrays, C, T, x)
+    assert np.array_equal(y, ref)
+    perm = np.random.default_rng(2).permutation(B)
+    assert np.array_equal(net.forward(_cuda(x[perm])).cpu().numpy(), y[perm])
 
 
 def test_full_size_batch_65536_every_logit():
