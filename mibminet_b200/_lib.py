@@ -58,7 +58,9 @@ def lib() -> ctypes.CDLL:
     if _lib is not None:
         return _lib
     path = _build.LIB
-    if _build.is_stale():
+    if os.environ.get("MIBMI_LIB_PATH"):          # experiment builds (tools/build_variant.py)
+        path = os.environ["MIBMI_LIB_PATH"]
+    elif _build.is_stale():
         if os.environ.get("MIBMI_NO_BUILD") and os.path.exists(path):
             pass
         else:

@@ -33,10 +33,37 @@
 
 namespace mibmi {
 
+#ifdef MIBMI_PROF
+// experiment build only (nvcc -DMIBMI_PROF): per-warp cycles spent in each mbarrier wait, read by tools/prof_pipe.py
+__device__ long long g_prof[148 * 32 * 4];
+#define PWAIT(slot, ...) do { if (!mbar_test(__VA_ARGS__)) { const long long t0_ = clock64(); mbar_wait(__VA_ARGS__); pw_[slot] += clock64() - t0_; } } while (0)
+#define PROF_BEGIN long long pw_[3] = {0, 0, 0}; const long long pt0_ = clock64();
+#define PROF_END if ((threadIdx.x & 31) == 0) { long long* o_ = g_prof + (blockIdx.x * 32 + (threadIdx.x >> 5)) * 4; \
+    o_[0] = clock64() - pt0_; o_[1] = pw_[0]; o_[2] = pw_[1]; o_[3] = pw_[2]; }
+#else
+#define PWAIT(slot, ...) mbar_wait(__VA_ARGS__)
+#define PROF_BEGIN
+#define PROF_END
+#endif
+
 constexpr int kAW = 8;                        // layer-1 warps
 constexpr int kBW = 16;                       // layer-2/3 warps (one channel each)
 constexpr int kCW = 2;                         // layer-4/5 warps (alternate trials)
 constexpr int kPipeThreads = (kAW + kBW + kCW + 1) * 32;   // + 1 TMA producer warp
+#ifndef MIBMI_ROTATE
+#define MIBMI_ROTATE 1
+#endif
+#ifndef MIBMI_STAGES
+#define MIBMI_STAGES 4
+#endif
+#ifndef MIBMI_NY1
+#define MIBMI_NY1 3
+#endif
+#ifndef MIBMI_NY3
+#define MIBMI_NY3 4
+#endif
+constexpr int kNY1 = MIBMI_NY1;                // layer-1 output ring (A -> B)
+constexpr int kNY3 = MIBMI_NY3;                // layer-3 output ring (B -> C)
 
 template <int C_, int T_, int S_>
 struct PCfg {
@@ -62,26 +89,26 @@ struct PCfg {
     static constexpr int XS_BYTES = (((REAL ? C * XP : C * T + 16) + 127) / 128) * 128;
     static constexpr int Y1_BYTES = 16 * Y1S, Y3_BYTES = 16 * Y3S;
     // barriers (8 B each)
-    static constexpr int BAR_FULL_X = 0, BAR_EMPTY_X = 8 * S, BAR_FULL_Y1 = 16 * S, BAR_EMPTY_Y1 = 16 * S + 16,
-                         BAR_FULL_Y3 = 16 * S + 32, BAR_EMPTY_Y3 = 16 * S + 48;
+    static constexpr int BAR_FULL_X = 0, BAR_EMPTY_X = 8 * S, BAR_FULL_Y1 = 16 * S, BAR_EMPTY_Y1 = BAR_FULL_Y1 + 8 * kNY1,
+                         BAR_FULL_Y3 = BAR_EMPTY_Y1 + 8 * kNY1, BAR_EMPTY_Y3 = BAR_FULL_Y3 + 8 * kNY3,
+                         BAR_END = BAR_EMPTY_Y3 + 8 * kNY3;
     // shared memory map
     static constexpr int OFF_XS = 256;
     static constexpr int OFF_Y1 = OFF_XS + S * XS_BYTES;
-    static constexpr int OFF_Y2 = OFF_Y1 + 2 * Y1_BYTES;
+    static constexpr int OFF_Y2 = OFF_Y1 + kNY1 * Y1_BYTES;
     static constexpr int OFF_Y3 = OFF_Y2 + 16 * Y2S;
-    static constexpr int OFF_Y4 = OFF_Y3 + 2 * Y3_BYTES;
+    static constexpr int OFF_Y4 = OFF_Y3 + kNY3 * Y3_BYTES;
     static constexpr int Y4_BYTES = ((16 * T64P + 15) / 16) * 16;
     static constexpr int OFF_SCR = ((OFF_Y4 + kCW * Y4_BYTES + 15) / 16) * 16;
-    static constexpr int SMEM = ((OFF_SCR + (REAL ? kAW * SCR_WARP : 0) + 127) / 128) * 128;
+    static constexpr int SMEM_RAW = ((OFF_SCR + (REAL ? kAW * SCR_WARP : 0) + 127) / 128) * 128;
+    static constexpr int SMEM = SMEM_RAW <= 227 * 1024 ? SMEM_RAW : 0;   // 0: this depth is never instantiated
     static_assert(REAL || T % 32 == 0, "aligned loader: whole 32-sample units");
     static_assert(!REAL || C <= 32, "realigning loader: one lane per channel");
     static_assert(T8 % 2 == 0, "layer 3 stores sample pairs");
     static_assert(KB16 >= 1 && KB16 <= kPipeMaxKB16, "C <= 64");
     static_assert(UNITS + 1 <= NCH - 1, "layer-1 chunks fit the planes with one zero chunk on each side");
-    static_assert(16 * S + 64 <= 256, "barrier area");
+    static_assert(BAR_END <= 256, "barrier area");
     static_assert(KST5 <= kPipeMaxKst5, "T too large for PipeNet::w5frag");
-    static_assert(kCW == 2, "y3 is double buffered: one layer-4/5 warp per buffer");
-    static_assert(SMEM <= 227 * 1024, "shared memory");
 };
 
 // smem byte offset (within a stage) of row r of 16-channel block kb of the layer-1 B operand.
@@ -119,9 +146,11 @@ pipe_forward_kernel(const PipeNet* __restrict__ net, const int8_t* __restrict__ 
             mbar_init(sbase + K::BAR_FULL_X + 8 * s, 1);
             mbar_init(sbase + K::BAR_EMPTY_X + 8 * s, kAW);
         }
-        for (int i = 0; i < 2; i++) {
+        for (int i = 0; i < kNY1; i++) {
             mbar_init(sbase + K::BAR_FULL_Y1 + 8 * i, kAW);
             mbar_init(sbase + K::BAR_EMPTY_Y1 + 8 * i, kBW);
+        }
+        for (int i = 0; i < kNY3; i++) {
             mbar_init(sbase + K::BAR_FULL_Y3 + 8 * i, kBW);
             mbar_init(sbase + K::BAR_EMPTY_Y3 + 8 * i, 1);
         }
@@ -132,6 +161,7 @@ pipe_forward_kernel(const PipeNet* __restrict__ net, const int8_t* __restrict__ 
         for (int i = tid; i < (K::SMEM - K::OFF_Y1) / 16; i += kPipeThreads) z[i] = make_uint4(0, 0, 0, 0);
     }
     __syncthreads();
+    PROF_BEGIN
 
     if (warp < kAW) {
         // =====================================================================================
@@ -168,16 +198,17 @@ pipe_forward_kernel(const PipeNet* __restrict__ net, const int8_t* __restrict__ 
         const uint32_t st_off = ((lane & 7) + 8 * ((lane >> 3) & 1)) * K::Y1S + (lane >> 4) * K::PLANE + 16;
 
         for (int n = 0; n < nloc; n++) {
-            const int st = n % K::S, buf = n & 1;
-            mbar_wait(sbase + K::BAR_FULL_X + 8 * st, (n / K::S) & 1);
-            mbar_wait(sbase + K::BAR_EMPTY_Y1 + 8 * buf, ((n >> 1) & 1) ^ 1);
+            const int st = n % K::S, buf = n % kNY1;
+            PWAIT(0, sbase + K::BAR_FULL_X + 8 * st, (n / K::S) & 1);
+            PWAIT(1, sbase + K::BAR_EMPTY_Y1 + 8 * buf, ((n / kNY1) & 1) ^ 1);
             const uint32_t xb = K::REAL ? sbase : sbase + K::OFF_XS + st * K::XS_BYTES;
             const uint32_t yb = sbase + K::OFF_Y1 + buf * K::Y1_BYTES + st_off;
             // REAL: byte misalignment of row `lane` of this trial (x itself is 16-byte aligned)
             const long long bq = first + (long long)n * stride;
             const int rsh = K::REAL ? (int)((bq * (long long)(K::TRIAL_BYTES & 15) + (long long)lane * (K::T & 15)) & 15) : 0;
 #pragma unroll 1
-            for (int u = warp; u < K::UNITS; u += kAW) {
+            // the warp that gets one unit fewer rotates with the trial: A warps only meet at the y1 barriers
+            for (int u = MIBMI_ROTATE ? (warp + n) % kAW : warp; u < K::UNITS; u += kAW) {
                 if (K::REAL) {
                     // shift 32 samples of every channel into place: 9 aligned words -> 8 funnel shifts -> scratch
                     __syncwarp();
@@ -284,9 +315,10 @@ pipe_forward_kernel(const PipeNet* __restrict__ net, const int8_t* __restrict__ 
         const uint32_t y3_off = k * K::Y3S + 16 * (q >> 1) + 8 * (q & 1);
 
         for (int n = 0; n < nloc; n++) {
-            const int buf = n & 1, par = (n >> 1) & 1;
+            const int buf = n % kNY1, par = (n / kNY1) & 1;
+            const int buf3 = n % kNY3, par3 = (n / kNY3) & 1;
             const long long b = first + (long long)n * stride;
-            mbar_wait(sbase + K::BAR_FULL_Y1 + 8 * buf, par);
+            PWAIT(0, sbase + K::BAR_FULL_Y1 + 8 * buf, par);
             const uint32_t ya = sbase + K::OFF_Y1 + buf * K::Y1_BYTES + l2_off;
 #pragma unroll 1
             for (int mt = 0; mt < K::MT; mt++) {
@@ -315,7 +347,7 @@ pipe_forward_kernel(const PipeNet* __restrict__ net, const int8_t* __restrict__ 
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(sbase + K::BAR_EMPTY_Y1 + 8 * buf);
-            mbar_wait(sbase + K::BAR_EMPTY_Y3 + 8 * buf, par ^ 1);
+            PWAIT(1, sbase + K::BAR_EMPTY_Y3 + 8 * buf3, par3 ^ 1);
             // ---- layer 3
             {
                 uint32_t a[4];
@@ -326,7 +358,7 @@ pipe_forward_kernel(const PipeNet* __restrict__ net, const int8_t* __restrict__ 
                     c3[v][0] = c3[v][1] = c3[v][2] = c3[v][3] = 0;
                     mma_k32(c3[v], a, b3[v][0], b3[v][1]);
                 }
-                uint8_t* y3b = smem + K::OFF_Y3 + buf * K::Y3_BYTES + y3_off;
+                uint8_t* y3b = smem + K::OFF_Y3 + buf3 * K::Y3_BYTES + y3_off;
 #pragma unroll
                 for (int half = 0; half < (K::NW3 > 8 ? 2 : 1); half++) {
                     const int i = g + 8 * half;
@@ -346,7 +378,7 @@ pipe_forward_kernel(const PipeNet* __restrict__ net, const int8_t* __restrict__ 
                 }
             }
             __syncwarp();
-            if (lane == 0) mbar_arrive(sbase + K::BAR_FULL_Y3 + 8 * buf);
+            if (lane == 0) mbar_arrive(sbase + K::BAR_FULL_Y3 + 8 * buf3);
         }
     } else if (warp == kAW + kBW + kCW) {
         // =====================================================================================
@@ -375,7 +407,7 @@ pipe_forward_kernel(const PipeNet* __restrict__ net, const int8_t* __restrict__ 
             for (int s = 0; s < K::S && s < nloc; s++) issue(s, s);
             for (int n = 0; n + K::S < nloc; n++) {
                 const int st = n % K::S;
-                mbar_wait(sbase + K::BAR_EMPTY_X + 8 * st, (n / K::S) & 1);
+                PWAIT(0, sbase + K::BAR_EMPTY_X + 8 * st, (n / K::S) & 1);
                 issue(st, n + K::S);
             }
         }
@@ -400,9 +432,9 @@ pipe_forward_kernel(const PipeNet* __restrict__ net, const int8_t* __restrict__ 
         const uint32_t* y4w = reinterpret_cast<const uint32_t*>(y4);
 
         for (int n = cj; n < nloc; n += kCW) {
-            const int buf = cj, par = (n >> 1) & 1;
+            const int buf = n % kNY3, par = (n / kNY3) & 1;
             const long long b = first + (long long)n * stride;
-            mbar_wait(sbase + K::BAR_FULL_Y3 + 8 * buf, par);
+            PWAIT(0, sbase + K::BAR_FULL_Y3 + 8 * buf, par);
             const uint32_t y3a = sbase + K::OFF_Y3 + buf * K::Y3_BYTES + l4_off;
 #pragma unroll
             for (int s4 = 0; s4 < K::NST; s4++) {
@@ -447,6 +479,7 @@ pipe_forward_kernel(const PipeNet* __restrict__ net, const int8_t* __restrict__ 
             __syncwarp();   // y4 is rewritten by the next trial
         }
     }
+    PROF_END
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -454,7 +487,11 @@ template <int C, int T>
 static cudaError_t launch_pipe_instance(const PipeNet* net_dev, bool fast1, const int8_t* x, long long B,
                                         int8_t* logits, int8_t* t1, int8_t* t2, int8_t* t3, int8_t* t4,
                                         int num_sms, cudaStream_t stream) {
-    using K = PCfg<C, T, 4>;
+    // deepest input ring (<= MIBMI_STAGES) that fits the 227 KB of shared memory
+    constexpr int S = PCfg<C, T, MIBMI_STAGES>::SMEM_RAW <= 227 * 1024 ? MIBMI_STAGES
+                    : PCfg<C, T, MIBMI_STAGES - 1>::SMEM_RAW <= 227 * 1024 ? MIBMI_STAGES - 1
+                    : PCfg<C, T, MIBMI_STAGES - 2>::SMEM_RAW <= 227 * 1024 ? MIBMI_STAGES - 2 : 3;
+    using K = PCfg<C, T, S>;
     const bool taps = t1 || t2 || t3 || t4;
     auto kern = taps ? pipe_forward_kernel<K, false, true>
                      : (fast1 ? pipe_forward_kernel<K, true, false> : pipe_forward_kernel<K, false, false>);
@@ -485,3 +522,9 @@ cudaError_t launch_pipe(const PipeNet* net_dev, bool fast1, int C, int T, const 
 }
 
 }  // namespace mibmi
+
+#ifdef MIBMI_PROF
+extern "C" __attribute__((visibility("default"))) int mibmi_debug_prof(long long* out_host) {
+    return (int)cudaMemcpyFromSymbol(out_host, mibmi::g_prof, sizeof(mibmi::g_prof));
+}
+#endif
