@@ -47,6 +47,12 @@ def parse_args():
     ap.add_argument("--path", default="auto", choices=["auto", "fused", "fused_v1", "generic"])
     ap.add_argument("--ctas-per-sm", type=int, default=0)
     ap.add_argument("--shape", default="64x480", help="CxT of the trials (default: BASELINE config 2; 22x1125 = config 3)")
+    ap.add_argument("--workload", default="trials", choices=["trials", "stream"],
+                    help="trials: BASELINE config 2 (default, the headline line); stream: config 5, sliding windows "
+                         "(480 samples, stride 16) over continuous 64-ch recordings")
+    ap.add_argument("--subjects", type=int, default=4096, help="stream workload: subjects per GPU")
+    ap.add_argument("--stream-len", type=int, default=9600, help="stream workload: samples per subject (60 s at 160 Hz)")
+    ap.add_argument("--stream-mode", default="auto", choices=["auto", "fused", "gather"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
@@ -154,6 +160,77 @@ def main_reference(args, rank):
         "gpu_launches": 0}))
 
 
+def main_stream(args, rank, local_rank, world):
+    """BASELINE config 5: every rank scores its own subjects (weak scaling, no collective); a step = all windows of
+    all subjects once.  Metric: windows/s (a window = one trial of the headline metric)."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from mibminet_b200 import convert, synth
+    from mibminet_b200.engine import Int8Net
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    S, L, hop = args.subjects, args.stream_len, 16
+    params = convert.params_from_state_dict(synth.make_state_dict(C=C, T=T, seed=NET_SEED), C=C, T=T)
+    net = Int8Net(params, device=dev)
+    net.set_stream_mode(args.stream_mode)
+    g = torch.Generator(device=dev)
+    g.manual_seed(2000 + rank)
+    x = torch.randint(-127, 128, (S, C, L), dtype=torch.int8, device=dev, generator=g)
+    W = net.stream_windows(L, hop)
+    out = torch.empty((S, W, N_CLASSES), dtype=torch.int8, device=dev)
+    for _ in range(max(args.warmup, 3)):
+        net.forward_stream(x, hop, out=out)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    l0 = net.launch_count
+    t0 = time.perf_counter()
+    ev0.record()
+    for _ in range(args.steps):
+        net.forward_stream(x, hop, out=out)
+    ev1.record()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    t1 = time.perf_counter()
+    clocks = sampler.stop(t0, t1) if sampler else None
+    t = torch.tensor([ev0.elapsed_time(ev1)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t[0]) / args.steps
+    if rank == 0:
+        peak, peak_src = measured_peaks()
+        nwin = S * W
+        alg = S * C * L + nwin * N_CLASSES            # the stream is read once, 4 B of logits per window
+        res = {"metric": "int8 edgeEEGNet windows/sec (sliding windows, stride 16)", "value": world * nwin / (ms * 1e-3),
+               "unit": "windows/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms,
+               "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int8", "data": "synthetic",
+               "config": {"workload": f"BASELINE config 5: {S} subjects/GPU x {C} ch x {L} samples, windows of {T} stride {hop}",
+                          "windows_per_gpu_per_step": nwin, "kernel_path": net.last_path, "stream_mode": args.stream_mode,
+                          "l2_policy": f"input per step {S * C * L / 1e9:.2f} GB > 126 MB L2"},
+               "roofline": {"bound": "hbm", "achieved": alg / (ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                            "frac": alg / (ms * 1e-3) / 1e9 / peak, "traffic": None, "peak_source": peak_src,
+                            "alg_bytes_per_window": alg / nwin,
+                            "note": "issue-bound, not HBM-bound: the stream is read once (about 1 kB per window)"},
+               "gpu_launches": int(net.launch_count - l0), "clocks": clocks}
+        if not args.no_cpu_baseline:
+            sys.path.insert(0, os.path.join(ROOT, "oracle"))
+            import wolf_port
+            ns = min(S, 4)
+            ref = wolf_port.forward_stream(params.to_wolf_arrays(), C, T, x[:ns].cpu().numpy(), hop)
+            res["config"]["bit_exact_checked"] = bool(np.array_equal(ref, out[:ns].cpu().numpy()))
+        print(json.dumps(res))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
 def main():
     global C, T, ALG_BYTES_PER_TRIAL, WORKLOAD
     args = parse_args()
@@ -166,6 +243,8 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     if args.impl == "reference":
         return main_reference(args, rank)
+    if args.workload == "stream":
+        return main_stream(args, rank, local_rank, world)
 
     import numpy as np
     import torch

@@ -86,9 +86,16 @@ typedef struct mibmi_net mibmi_net_t; /* opaque */
 #define MIBMI_PATH_FUSED 2    /* fused sm_100a kernel (int8 MMA + magic-number requantisation)        */
 #define MIBMI_PATH_FUSED_V1 3 /* round-1 homogeneous fused kernel, kept for A/B measurements          */
 
+#define MIBMI_PATH_STREAM 4   /* sliding-window streaming kernel (mibmi_forward_stream_int8)             */
+
+#define MIBMI_STREAM_AUTO 0    /* fused streaming kernel when it applies (hop 16, L % 16 == 0), else gather */
+#define MIBMI_STREAM_FUSED 1   /* fused streaming kernel or MIBMI_ERR_UNSUPPORTED                          */
+#define MIBMI_STREAM_GATHER 2  /* materialise the windows, then the per-trial path (any hop)               */
+
 #define MIBMI_OPT_FORCE_PATH 1
 #define MIBMI_OPT_CTAS_PER_SM 2   /* 0 = default */
 #define MIBMI_OPT_HOST_CHUNK 3    /* trials per H2D/compute/D2H chunk of the *_host entry point; 0 = default */
+#define MIBMI_OPT_STREAM_MODE 4   /* MIBMI_STREAM_* */
 
 MIBMI_API int mibmi_version(void);
 MIBMI_API const char* mibmi_strerror(int status);
@@ -128,6 +135,26 @@ MIBMI_API int mibmi_forward_int8_taps(mibmi_net_t* net, const int8_t* x_dev, int
  * through pinned staging memory.  Synchronous: returns when logits_host is complete. */
 MIBMI_API int mibmi_forward_int8_host(mibmi_net_t* net, const int8_t* x_host, int64_t B, int layout,
                             int8_t* logits_host);
+
+/* Sliding-window scoring of continuous recordings (BASELINE config 5).  x_dev int8 [S][C][L]: S independent
+ * streams (subjects) of L samples, 16-byte aligned; window w of stream s is x[s][:, w*hop : w*hop + T] and is
+ * scored exactly as one call of net_model_compute (model.c:42) on it -- per-window zero padding included.
+ *   logits_dev int8 [S][W][N],  W = mibmi_stream_windows(net, L, hop) = (L - T) / hop + 1
+ * With hop == 16 and L % 16 == 0 the fused streaming kernel computes layer 1 once per sample and the interior
+ * of layer 2 once per 8 samples instead of once per window; any other hop materialises the windows in a
+ * stream-ordered scratch buffer and runs the per-trial path.  Asynchronous on `stream`. */
+MIBMI_API int64_t mibmi_stream_windows(const mibmi_net_t* net, int64_t L, int32_t hop);
+MIBMI_API int mibmi_stream_supported(const mibmi_net_t* net, const char** why);
+MIBMI_API int mibmi_forward_stream_int8(mibmi_net_t* net, const int8_t* x_dev, int64_t S, int64_t L, int32_t hop,
+                                        int8_t* logits_dev, void* stream);
+/* Same on the fused streaming kernel, plus its intermediate results (any pointer may be NULL):
+ *   y2_stream [S][16][2 (W-1) + T/8]  pooled layer-2 samples of the stream (position j is written where it is
+ *                                     interior to some window: y2 of window w, sample p in [4, T/8-5], is [2 w + p])
+ *   y2_edges  [S][W][16][8]           y2 samples 0..3 and T/8-4 .. T/8-1 of every window
+ *   y3 [S][W][16][T/8], y4 [S][W][16][T/64] */
+MIBMI_API int mibmi_forward_stream_int8_taps(mibmi_net_t* net, const int8_t* x_dev, int64_t S, int64_t L, int32_t hop,
+                                             int8_t* logits_dev, int8_t* y2_stream, int8_t* y2_edges, int8_t* y3,
+                                             int8_t* y4, void* stream);
 
 /* Input quantisation pre-op (gen_input_header.py:73, STEActivation with floorToZero,
  * QuantLab/quantlab/indiv/ste_ops.py:88-102):  q = trunc(clip(x / abs_max, -1, 1) * 127).

@@ -16,8 +16,9 @@ from . import _build
 OK = 0
 ERR_NULL, ERR_SHAPE, ERR_PARAM, ERR_ALIGN, ERR_CUDA, ERR_UNSUPPORTED = -1, -2, -3, -4, -5, -6
 LAYOUT_BCT, LAYOUT_BTC = 0, 1
-PATH_AUTO, PATH_GENERIC, PATH_FUSED, PATH_FUSED_V1 = 0, 1, 2, 3
-OPT_FORCE_PATH, OPT_CTAS_PER_SM, OPT_HOST_CHUNK = 1, 2, 3
+PATH_AUTO, PATH_GENERIC, PATH_FUSED, PATH_FUSED_V1, PATH_STREAM = 0, 1, 2, 3, 4
+STREAM_AUTO, STREAM_FUSED, STREAM_GATHER = 0, 1, 2
+OPT_FORCE_PATH, OPT_CTAS_PER_SM, OPT_HOST_CHUNK, OPT_STREAM_MODE = 1, 2, 3, 4
 
 # every symbol include/mibmi.h declares (tests/test_abi.py checks the header against this list)
 SYMBOLS = [
@@ -25,7 +26,8 @@ SYMBOLS = [
     "mibmi_set_option", "mibmi_last_path", "mibmi_fused_supported", "mibmi_launch_count",
     "mibmi_forward_int8", "mibmi_forward_int8_taps", "mibmi_forward_int8_host",
     "mibmi_quantize_input_f32", "mibmi_dequantize_logits_f32", "mibmi_debug_magic", "mibmi_debug_pack_fused",
-    "mibmi_debug_pack_pipe",
+    "mibmi_debug_pack_pipe", "mibmi_stream_windows", "mibmi_stream_supported", "mibmi_forward_stream_int8",
+    "mibmi_forward_stream_int8_taps",
 ]
 
 
@@ -81,6 +83,11 @@ def lib() -> ctypes.CDLL:
     L.mibmi_forward_int8.argtypes = [vp, vp, i64, i32, vp, vp]
     L.mibmi_forward_int8_taps.argtypes = [vp, vp, i64, i32, vp, vp, vp, vp, vp, vp]
     L.mibmi_forward_int8_host.argtypes = [vp, vp, i64, i32, vp]
+    L.mibmi_stream_windows.argtypes = [vp, i64, ctypes.c_int32]
+    L.mibmi_stream_windows.restype = i64
+    L.mibmi_stream_supported.argtypes = [vp, ctypes.POINTER(ctypes.c_char_p)]
+    L.mibmi_forward_stream_int8.argtypes = [vp, vp, i64, i64, ctypes.c_int32, vp, vp]
+    L.mibmi_forward_stream_int8_taps.argtypes = [vp, vp, i64, i64, ctypes.c_int32, vp, vp, vp, vp, vp, vp]
     L.mibmi_quantize_input_f32.argtypes = [vp, i64, ctypes.c_float, vp, vp]
     L.mibmi_dequantize_logits_f32.argtypes = [vp, i64, ctypes.c_float, vp, vp]
     L.mibmi_debug_magic.argtypes = [ctypes.c_int32, ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_int32)]

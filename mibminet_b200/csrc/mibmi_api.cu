@@ -26,6 +26,10 @@ struct mibmi_net {
     PipeNet* pipe_dev = nullptr;       // warp-specialised pipeline kernel (MIBMI_PATH_FUSED)
     bool pipe_ok = false, pipe_fast1 = false;
     const char* pipe_why = "";
+    StreamNet* stream_dev = nullptr;   // sliding-window streaming kernel (mibmi_forward_stream_int8)
+    bool stream_ok = false;
+    const char* stream_why = "";
+    int stream_mode = MIBMI_STREAM_AUTO;
     int force_path = MIBMI_PATH_AUTO, ctas_per_sm = 0;
     int64_t host_chunk = 0;
     std::atomic<int> last_path{0};
@@ -352,6 +356,100 @@ bool pack_pipe(const mibmi_params_t* p, PipeNet* f, const char** why) {
     return true;
 }
 
+// Streaming kernel: shared parts come from the pipeline packing; window-specific zero padding becomes masked
+// Toeplitz fragments (see StreamNet in mibmi_common.cuh).
+bool pack_stream(const mibmi_params_t* p, const PipeNet* pn, StreamNet* f, const char** why) {
+    const int C = p->C, T = p->T, CA4 = align4(C), T8 = T / 8;
+    memset(f, 0, sizeof(*f));
+    if (!stream_has_instance(C, T)) { *why = "no streaming instantiation for this (C, T)"; return false; }
+    memcpy(f->off1, pn->off1, sizeof(f->off1)); memcpy(f->m1, pn->m1, sizeof(f->m1)); memcpy(f->sh1, pn->sh1, sizeof(f->sh1));
+    f->fast1 = pn->fast1;
+    memcpy(f->w2frag, pn->w2frag, sizeof(f->w2frag));
+    memcpy(f->thr2, pn->thr2, sizeof(f->thr2)); memcpy(f->sig2, pn->sig2, sizeof(f->sig2)); memcpy(f->soff2, pn->soff2, sizeof(f->soff2));
+    memcpy(f->m2, pn->m2, sizeof(f->m2)); memcpy(f->sh2, pn->sh2, sizeof(f->sh2));
+    f->m3 = pn->m3; f->sh3 = pn->sh3;
+    memcpy(f->w4frag, pn->w4frag, sizeof(f->w4frag));
+    memcpy(f->thr4, pn->thr4, sizeof(f->thr4)); memcpy(f->sig4, pn->sig4, sizeof(f->sig4)); memcpy(f->soff4, pn->soff4, sizeof(f->soff4));
+    memcpy(f->m4, pn->m4, sizeof(f->m4)); memcpy(f->sh4, pn->sh4, sizeof(f->sh4));
+    memcpy(f->w5frag, pn->w5frag, sizeof(f->w5frag));
+    memcpy(f->b5, pn->b5, sizeof(f->b5)); f->m5 = pn->m5; f->sh5 = pn->sh5;
+    // layer 1, natural channel order: K position r of block kb <-> channel 16 kb + r
+    for (int kb = 0; kb < (C + 15) / 16; kb++)
+        for (int nt = 0; nt < 2; nt++)
+            for (int lane = 0; lane < 32; lane++) {
+                const int g = lane >> 2, q = lane & 3, row = 8 * nt + g;
+                const int sg = p->l1_factor[row] < 0 ? -1 : 1;
+                uint32_t word = 0;
+                for (int i = 0; i < 4; i++) {
+                    const int c = 16 * kb + 4 * q + i;
+                    const int w = c < C ? sg * p->l1_weight_align[row * CA4 + c] : 0;
+                    word |= (uint32_t)(uint8_t)(int8_t)w << (8 * i);
+                }
+                f->w1nat[kb][nt][lane] = word;
+            }
+    // layer 2 edges.  Left: output o of the window from its samples ii = 0..63, tap = ii - o + 31 (31 zeros of
+    // left padding, gen_net_header.py:145).  Right: output T - 32 + o from samples T - 64 + ii, tap = ii - o - 1.
+    for (int k = 0; k < 16; k++) {
+        const int8_t* w = p->l2_weight_reverse + k * 64;
+        for (int v = 0; v < 4; v++)
+            for (int s = 0; s < 2; s++)
+                for (int h = 0; h < 2; h++)
+                    for (int lane = 0; lane < 32; lane++) {
+                        const int g = lane >> 2, q = lane & 3;
+                        const int o = 8 * (g >> 1) + 2 * v + (g & 1);
+                        uint32_t wl = 0, wr = 0;
+                        for (int i = 0; i < 4; i++) {
+                            const int ii = 32 * s + 16 * h + 4 * q + i;
+                            const int tl = ii - o + 31, tr = ii - o - 1;
+                            wl |= (uint32_t)(uint8_t)((tl >= 0 && tl < 64) ? w[tl] : 0) << (8 * i);
+                            wr |= (uint32_t)(uint8_t)((tr >= 0 && tr < 64) ? w[tr] : 0) << (8 * i);
+                        }
+                        f->w2L[k][v * 4 + s * 2 + h][lane] = wl;
+                        f->w2R[k][v * 4 + s * 2 + h][lane] = wr;
+                    }
+    }
+    // layer 3, window = MMA row.  Block b covers outputs 16 b .. 16 b + 15 from pooled samples p = 16 b - 8 + kk;
+    // torch-order tap jt = p - t + 7 (7 zeros of left padding, gen_net_header.py:171), exported array flipped.
+    // Samples p < 4 and p > T8 - 5 are window specific: masked here, supplied through w3e.
+    {
+        const int sg = p->l3_factor < 0 ? -1 : 1;
+        const int nb3 = (T8 + 15) / 16;
+        for (int k = 0; k < 16; k++) {
+            for (int cls = 0; cls < 3; cls++)
+                for (int e = 0; e < 2; e++)
+                    for (int h = 0; h < 2; h++)
+                        for (int lane = 0; lane < 32; lane++) {
+                            const int c = lane >> 2, q = lane & 3;
+                            const int b = cls == 0 ? 0 : (cls == 2 ? nb3 - 1 : 1);
+                            uint32_t word = 0;
+                            for (int i = 0; i < 4; i++) {
+                                const int kk = 16 * h + 4 * q + i, pp = 16 * b - 8 + kk;
+                                const int jt = kk - 8 * e - c - 1;
+                                const bool interior = cls == 1 || (pp >= 4 && pp <= T8 - 5);
+                                const int val = (jt >= 0 && jt < 16 && interior) ? sg * p->l3_weight[k * 16 + 15 - jt] : 0;
+                                word |= (uint32_t)(uint8_t)(int8_t)val << (8 * i);
+                            }
+                            f->w3s[k][cls * 4 + e * 2 + h][lane] = word;
+                        }
+            for (int idx = 0; idx < 4; idx++)
+                for (int lane = 0; lane < 32; lane++) {
+                    const int c = lane >> 2, q = lane & 3;
+                    const int n = idx < 2 ? idx : 2 * (nb3 - 1) + (idx - 2);
+                    uint32_t word = 0;
+                    for (int i = 0; i < 4; i++) {
+                        const int kk = 4 * q + i;
+                        const int pe = kk < 4 ? kk : (kk < 8 ? T8 - 8 + kk : -1000);
+                        const int jt = pe - (8 * n + c) + 7;
+                        const int val = (jt >= 0 && jt < 16) ? sg * p->l3_weight[k * 16 + 15 - jt] : 0;
+                        word |= (uint32_t)(uint8_t)(int8_t)val << (8 * i);
+                    }
+                    f->w3e[k][idx][lane] = word;
+                }
+        }
+    }
+    return true;
+}
+
 int validate(const mibmi_params_t* p) {
     if (!p->l1_factor || !p->l1_offset || !p->l1_weight_align || !p->l2_factor || !p->l2_offset ||
         !p->l2_weight_reverse || !p->l3_weight || !p->l4_factor || !p->l4_offset || !p->l4_weight ||
@@ -491,7 +589,8 @@ int mibmi_create(const mibmi_params_t* p, int device, mibmi_net_t** out) {
     GenericNet* g = new (std::nothrow) GenericNet();
     FusedNet* f = new (std::nothrow) FusedNet();
     PipeNet* pn = new (std::nothrow) PipeNet();
-    if (!g || !f || !pn) { delete g; delete f; delete pn; delete n; return MIBMI_ERR_CUDA; }
+    StreamNet* sn = new (std::nothrow) StreamNet();
+    if (!g || !f || !pn || !sn) { delete g; delete f; delete pn; delete sn; delete n; return MIBMI_ERR_CUDA; }
     memset(g, 0, sizeof(*g));
     g->C = C; g->T = T; g->F2 = F2; g->N = N; g->T8 = T / 8; g->T64 = T64; g->reorder = n->reorder;
     for (int k = 0; k < F2; k++) {
@@ -512,6 +611,8 @@ int mibmi_create(const mibmi_params_t* p, int device, mibmi_net_t** out) {
     n->fused_ok = pack_fused(p, f, &n->fused_why);
     n->pipe_ok = pack_pipe(p, pn, &n->pipe_why);
     n->pipe_fast1 = pn->fast1 != 0;
+    if (n->pipe_ok) n->stream_ok = pack_stream(p, pn, sn, &n->stream_why);
+    else n->stream_why = n->pipe_why;
 
     cudaDeviceProp prop;
     if (e == cudaSuccess) e = cudaGetDeviceProperties(&prop, device);
@@ -529,9 +630,14 @@ int mibmi_create(const mibmi_params_t* p, int device, mibmi_net_t** out) {
         e = cudaMalloc(&n->pipe_dev, sizeof(PipeNet));
         if (e == cudaSuccess) e = cudaMemcpy(n->pipe_dev, pn, sizeof(PipeNet), cudaMemcpyHostToDevice);
     }
+    if (e == cudaSuccess && n->stream_ok) {
+        e = cudaMalloc(&n->stream_dev, sizeof(StreamNet));
+        if (e == cudaSuccess) e = cudaMemcpy(n->stream_dev, sn, sizeof(StreamNet), cudaMemcpyHostToDevice);
+    }
     delete g;
     delete f;
     delete pn;
+    delete sn;
     if (e != cudaSuccess) {
         mibmi_destroy(n);
         return MIBMI_ERR_CUDA;
@@ -548,6 +654,7 @@ int mibmi_destroy(mibmi_net_t* net) {
         if (net->w5_dev) cudaFree(net->w5_dev);
         if (net->fused_dev) cudaFree(net->fused_dev);
         if (net->pipe_dev) cudaFree(net->pipe_dev);
+        if (net->stream_dev) cudaFree(net->stream_dev);
         free_host_staging(net);
         for (int i = 0; i < 2; i++)
             if (net->hs[i]) cudaStreamDestroy(net->hs[i]);
@@ -568,6 +675,11 @@ int mibmi_set_option(mibmi_net_t* net, int option, int64_t value) {
         case MIBMI_OPT_CTAS_PER_SM:
             if (value < 0 || value > 8) return MIBMI_ERR_PARAM;
             net->ctas_per_sm = (int)value;
+            return MIBMI_OK;
+        case MIBMI_OPT_STREAM_MODE:
+            if (value < MIBMI_STREAM_AUTO || value > MIBMI_STREAM_GATHER) return MIBMI_ERR_PARAM;
+            if (value == MIBMI_STREAM_FUSED && !net->stream_ok) return MIBMI_ERR_UNSUPPORTED;
+            net->stream_mode = (int)value;
             return MIBMI_OK;
         case MIBMI_OPT_HOST_CHUNK:
             if (value < 0) return MIBMI_ERR_PARAM;
@@ -648,6 +760,73 @@ int mibmi_forward_int8_host(mibmi_net_t* net, const int8_t* x_host, int64_t B, i
         cudaStreamSynchronize(net->hs[1]);
     }
     return status;
+}
+
+int64_t mibmi_stream_windows(const mibmi_net_t* net, int64_t L, int32_t hop) {
+    if (!net) return MIBMI_ERR_NULL;
+    if (hop < 1 || L < net->T) return MIBMI_ERR_PARAM;
+    return (L - net->T) / hop + 1;
+}
+
+int mibmi_stream_supported(const mibmi_net_t* net, const char** why) {
+    if (!net) return 0;
+    if (why) *why = net->stream_ok ? "" : net->stream_why;
+    return net->stream_ok ? 1 : 0;
+}
+
+static int stream_impl(mibmi_net* net, const int8_t* x, int64_t S, int64_t L, int32_t hop, int8_t* logits, int8_t* t2i,
+                       int8_t* t2e, int8_t* t3, int8_t* t4, bool taps, cudaStream_t stream) {
+    if (!net) return MIBMI_ERR_NULL;
+    if (S < 0 || hop < 1 || L < net->T) return MIBMI_ERR_PARAM;
+    if (S == 0) return MIBMI_OK;
+    if (!x || !logits) return MIBMI_ERR_NULL;
+    if (((uintptr_t)x & 15) != 0 || (net->N == 4 && ((uintptr_t)logits & 3) != 0)) return MIBMI_ERR_ALIGN;
+    const int64_t W = (L - net->T) / hop + 1;
+    const bool fused_possible = net->stream_ok && hop == 16 && L % 16 == 0 && S * net->C < (int64_t(1) << 31) &&
+                                L < (int64_t(1) << 31);
+    int mode = net->stream_mode;
+    if (mode == MIBMI_STREAM_AUTO) mode = fused_possible ? MIBMI_STREAM_FUSED : MIBMI_STREAM_GATHER;
+    if (mode == MIBMI_STREAM_FUSED && !fused_possible) return MIBMI_ERR_UNSUPPORTED;
+    if (taps && mode != MIBMI_STREAM_FUSED) return MIBMI_ERR_UNSUPPORTED;
+    DeviceGuard dg(net->device);
+    if (dg.err != cudaSuccess) return fail_cuda(net, dg.err);
+    if (mode == MIBMI_STREAM_FUSED) {
+        cudaError_t e = launch_stream(net->stream_dev, net->pipe_fast1, net->C, net->T, x, S, L, logits, t2i, t2e, t3, t4,
+                                      net->num_sms, stream);
+        if (e != cudaSuccess) return fail_cuda(net, e);
+        net->last_path.store(MIBMI_PATH_STREAM);
+        net->launches.fetch_add(1);
+        return MIBMI_OK;
+    }
+    // any hop / shape: materialise bounded batches of windows (stream-ordered scratch), then the per-trial path
+    const int64_t total = S * W, tb = (int64_t)net->C * net->T;
+    int64_t chunk = (int64_t(256) << 20) / tb;
+    if (chunk > total) chunk = total;
+    int8_t* scratch = nullptr;
+    cudaError_t e = cudaMallocAsync(&scratch, (size_t)(chunk * tb), stream);
+    if (e != cudaSuccess) return fail_cuda(net, e);
+    int status = MIBMI_OK;
+    for (int64_t lo = 0; lo < total && status == MIBMI_OK; lo += chunk) {
+        const int64_t nw = total - lo < chunk ? total - lo : chunk;
+        e = launch_gather_windows(x, L, net->C, net->T, hop, W, lo, nw, scratch, stream);
+        if (e != cudaSuccess) { status = fail_cuda(net, e); break; }
+        net->launches.fetch_add(1);
+        status = forward_impl(net, scratch, nw, MIBMI_LAYOUT_BCT, logits + lo * net->N, nullptr, nullptr, nullptr, nullptr,
+                              false, stream);
+    }
+    cudaFreeAsync(scratch, stream);
+    return status;
+}
+
+int mibmi_forward_stream_int8(mibmi_net_t* net, const int8_t* x_dev, int64_t S, int64_t L, int32_t hop, int8_t* logits_dev,
+                              void* stream) {
+    return stream_impl(net, x_dev, S, L, hop, logits_dev, nullptr, nullptr, nullptr, nullptr, false, (cudaStream_t)stream);
+}
+
+int mibmi_forward_stream_int8_taps(mibmi_net_t* net, const int8_t* x_dev, int64_t S, int64_t L, int32_t hop,
+                                   int8_t* logits_dev, int8_t* y2_stream, int8_t* y2_edges, int8_t* y3, int8_t* y4,
+                                   void* stream) {
+    return stream_impl(net, x_dev, S, L, hop, logits_dev, y2_stream, y2_edges, y3, y4, true, (cudaStream_t)stream);
 }
 
 int mibmi_quantize_input_f32(const float* x_dev, int64_t n, float abs_max, int8_t* q_dev, void* stream) {

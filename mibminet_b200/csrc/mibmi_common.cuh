@@ -91,6 +91,33 @@ struct PipeNet {
 };
 static_assert(sizeof(PipeNet) % 16 == 0, "PipeNet alignment");
 
+// ---------------------------------------------------------------------------------------------
+// Network as the sliding-window streaming kernel (mibmi_stream.cu) reads it.  Windows of T samples every
+// 16 samples of a continuous stream share layer 1 and the interior of layer 2; what is window specific
+// (the zero padding at the window edges) is folded into masked Toeplitz fragments:
+//   w2L / w2R   layer-2 outputs 0..31 / T-32..T-1 of a window from its first / last 64 samples only
+//   w3s         layer 3 with the window as the MMA row: class 0 / 1 / 2 = first / middle / last 16-output
+//               block (inputs p < 4 and p > T/8 - 5 masked: they come from w3e instead)
+//   w3e         layer-3 contribution of the 8 window-specific pooled samples (p = 0..3, T/8-4..T/8-1)
+struct StreamNet {
+    uint32_t w1nat[kPipeMaxKB16][2][32];   // W1 B fragments, natural channel order (channel = 16 block + row)
+    int off1[16], m1[16], sh1[16];
+    int fast1, pad0_[3];
+    uint32_t w2frag[16][24][32];           // interior Toeplitz (same as PipeNet)
+    uint32_t w2L[16][16][32];              // [channel][variant*4 + kstep*2 + half][lane]
+    uint32_t w2R[16][16][32];
+    int thr2[16], sig2[16], soff2[16], m2[16], sh2[16];
+    uint32_t w3s[16][12][32];              // [channel][class*4 + e*2 + half][lane]
+    uint32_t w3e[16][4][32];               // [channel][n-tile 0, 1, last-1, last][lane]  (k16 B fragments)
+    int m3, sh3, pad1_[2];
+    uint32_t w4frag[2][32];
+    int thr4[16], sig4[16], soff4[16], m4[16], sh4[16];
+    uint32_t w5frag[kPipeMaxKst5][2][32];
+    int b5[4];
+    int m5, sh5, pad2_[2];
+};
+static_assert(sizeof(StreamNet) % 16 == 0, "StreamNet alignment");
+
 // C '/' : truncate toward zero.  (The generic kernel uses the hardware sequence as is.)
 __device__ __forceinline__ int clip8(int x) { return min(max(x, -128), 127); }
 

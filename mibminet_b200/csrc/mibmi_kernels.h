@@ -8,6 +8,7 @@ namespace mibmi {
 struct GenericNet;
 struct FusedNet;
 struct PipeNet;
+struct StreamNet;
 
 size_t generic_smem_bytes(int T, int F2);
 cudaError_t launch_generic(const GenericNet* net_dev, int T, int F2, const int8_t* x, long long B, int layout,
@@ -29,5 +30,15 @@ bool pipe_has_instance(int C, int T);
 cudaError_t launch_pipe(const PipeNet* net_dev, bool fast1, int C, int T, const int8_t* x, long long B,
                         int8_t* logits, int8_t* t1, int8_t* t2, int8_t* t3, int8_t* t4, int num_sms,
                         cudaStream_t stream);
+
+// Sliding-window streaming kernel (mibmi_stream.cu): x [S][C][L] -> logits [S][W][4], W = (L - T) / 16 + 1.
+// Optional taps: t2i [S][16][2 (W-1) + T/8] stream-level pooled layer-2 samples (interior positions only),
+// t2e [S][W][16][8] the 4 + 4 edge samples of every window, t3 [S][W][16][T/8], t4 [S][W][16][T/64].
+bool stream_has_instance(int C, int T);
+cudaError_t launch_stream(const StreamNet* net_dev, bool fast1, int C, int T, const int8_t* x, long long S, long long L,
+                          int8_t* logits, int8_t* t2i, int8_t* t2e, int8_t* t3, int8_t* t4, int num_sms, cudaStream_t stream);
+// Fallback: windows first .. first + nw - 1 (global index subject * W + w) of the streams -> out [nw][C][T]
+cudaError_t launch_gather_windows(const int8_t* x, long long L, int C, int T, int hop, long long W, long long first,
+                                  long long nw, int8_t* out, cudaStream_t stream);
 
 }  // namespace mibmi

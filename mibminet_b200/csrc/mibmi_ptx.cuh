@@ -51,6 +51,13 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t
                  ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
 }
 
+// TMA 2-D tile load through a tensor map (SASS: UTMALDG), completion on an mbarrier
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const void* tmap, int c0, int c1, uint32_t bar) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                 ::"r"(dst), "l"(tmap), "r"(c0), "r"(c1), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
 // ---- warp-level int8 MMA (SASS: IMMA.16832.S8.S8 / IMMA.16816.S8.S8) --------------------------
 //   A (row)  a0: (row g, k 4q..4q+3)  a1: (row g+8, k 4q..)  a2: (row g, k 16+4q..)  a3: (row g+8, k 16+4q..)
 //   B (col)  b0: (k 4q..4q+3, col g)  b1: (k 16+4q.., col g)
@@ -71,6 +78,11 @@ __device__ __forceinline__ void mma_k16(int (&d)[4], uint32_t a0, uint32_t a1, u
 __device__ __forceinline__ void ldsm_x4(uint32_t (&r)[4], uint32_t addr) {
     asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
                  : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr) : "memory");
+}
+// two 8x16-byte matrices (lanes 0-7 / 8-15 supply the row addresses; the others must still be valid)
+__device__ __forceinline__ void ldsm_x2(uint32_t (&r)[2], uint32_t addr) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x2.shared.b16 {%0,%1}, [%2];"
+                 : "=r"(r[0]), "=r"(r[1]) : "r"(addr) : "memory");
 }
 __device__ __forceinline__ void stsm_x4(uint32_t addr, uint32_t r0, uint32_t r1, uint32_t r2, uint32_t r3) {
     asm volatile("stmatrix.sync.aligned.m8n8.x4.shared.b16 [%0], {%1,%2,%3,%4};"

@@ -22,6 +22,8 @@ _LAYOUTS = {"bct": _lib.LAYOUT_BCT, "btc": _lib.LAYOUT_BTC}
 _PATHS = {"auto": _lib.PATH_AUTO, "generic": _lib.PATH_GENERIC, "fused": _lib.PATH_FUSED,
           "fused_v1": _lib.PATH_FUSED_V1}
 _PATH_NAMES = {v: k for k, v in _PATHS.items()}
+_PATH_NAMES[_lib.PATH_STREAM] = "stream"
+_STREAM_MODES = {"auto": _lib.STREAM_AUTO, "fused": _lib.STREAM_FUSED, "gather": _lib.STREAM_GATHER}
 
 
 def _device_index(device) -> int:
@@ -146,6 +148,56 @@ class Int8Net:
                                                    taps["y1"].data_ptr(), taps["y2"].data_ptr(),
                                                    taps["y3"].data_ptr(), taps["y4"].data_ptr(), stream),
                    "mibmi_forward_int8_taps")
+        return out, taps
+
+    # ---- sliding-window scoring of continuous recordings (BASELINE config 5) -----------------------
+    def stream_supported(self):
+        why = ctypes.c_char_p()
+        ok = self._L.mibmi_stream_supported(self._h, ctypes.byref(why))
+        return bool(ok), (why.value or b"").decode()
+
+    def set_stream_mode(self, mode: str):
+        _lib.check(self._L.mibmi_set_option(self._h, _lib.OPT_STREAM_MODE, _STREAM_MODES[mode]), "set_stream_mode")
+
+    def stream_windows(self, L: int, hop: int = 16) -> int:
+        return (int(L) - self.T) // int(hop) + 1
+
+    def _check_stream(self, x: torch.Tensor):
+        if x.dtype != torch.int8:
+            raise TypeError("x must be int8")
+        if not x.is_cuda or x.device.index != self.device_index:
+            raise ValueError(f"x must live on {self.device}")
+        if x.dim() != 3 or x.shape[1] != self.C or x.shape[2] < self.T:
+            raise ValueError(f"x must be [S, {self.C}, L >= {self.T}], got {tuple(x.shape)}")
+        return x.contiguous()
+
+    def forward_stream(self, x: torch.Tensor, hop: int = 16, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """int8 streams [S, C, L] -> int8 logits [S, W, N] of every window x[s, :, w*hop : w*hop + T].
+        Asynchronous on the current torch CUDA stream."""
+        x = self._check_stream(x)
+        S, L = x.shape[0], x.shape[2]
+        W = self.stream_windows(L, hop)
+        if out is None:
+            out = torch.empty((S, W, self.N), dtype=torch.int8, device=self.device)
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        _lib.check(self._L.mibmi_forward_stream_int8(self._h, x.data_ptr(), S, L, int(hop), out.data_ptr(), stream),
+                   "mibmi_forward_stream_int8")
+        return out
+
+    def forward_stream_taps(self, x: torch.Tensor, hop: int = 16):
+        """-> (logits, {'y2_stream','y2_edges','y3','y4'}) from the fused streaming kernel (see mibmi.h)."""
+        x = self._check_stream(x)
+        S, L = x.shape[0], x.shape[2]
+        W = self.stream_windows(L, hop)
+        z = lambda *shape: torch.zeros(shape, dtype=torch.int8, device=self.device)
+        out = z(S, W, self.N)
+        taps = {"y2_stream": z(S, self.F2, 2 * (W - 1) + self.T8), "y2_edges": z(S, W, self.F2, 8),
+                "y3": z(S, W, self.F2, self.T8), "y4": z(S, W, self.F2, self.T64)}
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        _lib.check(self._L.mibmi_forward_stream_int8_taps(
+            self._h, x.data_ptr(), S, L, int(hop), out.data_ptr(), taps["y2_stream"].data_ptr(),
+            taps["y2_edges"].data_ptr(), taps["y3"].data_ptr(), taps["y4"].data_ptr(), stream),
+            "mibmi_forward_stream_int8_taps")
         return out, taps
 
     def forward_host(self, x: Union[torch.Tensor, np.ndarray], layout: str = "bct",

@@ -77,3 +77,25 @@ def forward(arrays, C, T, x, F2=16, N=4, reorder_bn=True, threads=0, return_laye
         layers[name] = taps[:, o:o + F2 * n].reshape(B, F2, n)
         o += F2 * n
     return out, layers
+
+
+def stream_windows(x, T, hop=16):
+    """x int8 [S][C][L] -> every window materialised, [S * W][C][T] with W = (L - T) // hop + 1
+    (what a caller of net_model_compute would have to build: one trial per window)."""
+    x = np.ascontiguousarray(x, dtype=np.int8)
+    S, C, L = x.shape
+    W = (L - T) // hop + 1
+    v = np.lib.stride_tricks.sliding_window_view(x, T, axis=2)[:, :, ::hop][:, :, :W]   # [S][C][W][T]
+    return np.ascontiguousarray(v.transpose(0, 2, 1, 3)).reshape(S * W, C, T), W
+
+
+def forward_stream(arrays, C, T, x, hop=16, return_layers=False, threads=0):
+    """Sliding-window oracle: the integer network on every materialised window.
+    -> logits [S][W][N]  (and the per-window layer outputs [S][W][...] if return_layers)."""
+    xs, W = stream_windows(x, T, hop)
+    S = x.shape[0]
+    r = forward(arrays, C, T, xs, threads=threads, return_layers=return_layers)
+    if not return_layers:
+        return r.reshape(S, W, -1)
+    y, layers = r
+    return y.reshape(S, W, -1), {k: v.reshape((S, W) + v.shape[1:]) for k, v in layers.items()}

@@ -216,3 +216,63 @@ def test_errors_are_reported_not_printed():
     with pytest.raises(MibmiError) as ei:
         net.forward(x)
     assert ei.value.status == ERR_ALIGN
+
+
+# ---- sliding-window streaming (BASELINE config 5) -------------------------------------------------------
+def _stream_case(C, T, S, L, seed):
+    net, arrays = _net(C, T, seed)
+    x = synth.make_trials(S, C, L, seed=seed + 100, dist="gauss" if seed % 2 else "uniform")
+    return net, arrays, x
+
+
+@pytest.mark.parametrize("C,S,L,seed", [(64, 3, 480 + 16 * 70, 61), (64, 2, 480, 62), (64, 5, 480 + 16 * 31, 63),
+                                         (64, 1, 480 + 16 * 32, 64), (38, 2, 480 + 16 * 40, 65), (8, 3, 480 + 16 * 45, 66),
+                                         (16, 2, 480 + 16 * 33, 67), (24, 2, 480 + 16 * 64, 68)])
+def test_stream_fused_vs_materialised_windows(C, S, L, seed):
+    """Every window of the fused streaming kernel == the oracle on the materialised window, per layer."""
+    T = 480
+    net, arrays, x = _stream_case(C, T, S, L, seed)
+    assert net.stream_supported()[0], net.stream_supported()[1]
+    net.set_stream_mode("fused")
+    ref, lay = wolf_port.forward_stream(arrays, C, T, x, return_layers=True)
+    W = ref.shape[1]
+    y, taps = net.forward_stream_taps(_cuda(x))
+    assert net.last_path == "stream"
+    y2 = lay["y2"]                                      # [S][W][16][60]
+    e = taps["y2_edges"].cpu().numpy()
+    assert np.array_equal(e[..., :4], y2[..., :4]), "left edge samples of layer 2"
+    assert np.array_equal(e[..., 4:], y2[..., 56:]), "right edge samples of layer 2"
+    s2 = taps["y2_stream"].cpu().numpy()               # [S][16][2 (W-1) + 60]
+    for w in range(W):
+        assert np.array_equal(s2[:, :, 2 * w + 4: 2 * w + 56], y2[:, w, :, 4:56]), f"interior of layer 2, window {w}"
+    assert np.array_equal(taps["y3"].cpu().numpy(), lay["y3"]), "layer 3"
+    assert np.array_equal(taps["y4"].cpu().numpy(), lay["y4"]), "layer 4"
+    assert np.array_equal(y.cpu().numpy(), ref)
+    assert np.array_equal(net.forward_stream(_cuda(x)).cpu().numpy(), ref)     # production instantiation
+
+
+def test_stream_gather_fallback_any_hop():
+    C, T = 64, 480
+    net, arrays, x = _stream_case(C, T, 2, 480 + 700, 71)
+    for hop in (16, 8, 5, 160):
+        net.set_stream_mode("gather" if hop == 16 else "auto")
+        y = net.forward_stream(_cuda(x), hop=hop).cpu().numpy()
+        assert net.last_path == "fused"
+        assert np.array_equal(y, wolf_port.forward_stream(arrays, C, T, x, hop=hop)), hop
+    # 22 x 1125 has no fused streaming instantiation: auto falls back to materialised windows
+    net2, arrays2, x2 = _stream_case(22, 1125, 2, 1125 + 16 * 9, 72)
+    assert not net2.stream_supported()[0]
+    assert np.array_equal(net2.forward_stream(_cuda(x2)).cpu().numpy(), wolf_port.forward_stream(arrays2, 22, 1125, x2))
+
+
+def test_stream_config5_slice_every_logit():
+    """BASELINE config 5 shape (64 ch, windows of 480, stride 16) on 64 subjects x 60 s at 160 Hz."""
+    C, T, S, L = 64, 480, 64, 9600
+    net, arrays, x = _stream_case(C, T, S, L, 73)
+    y = net.forward_stream(_cuda(x)).cpu().numpy()
+    assert net.last_path == "stream"
+    assert y.shape == (S, (L - T) // 16 + 1, 4)
+    assert np.array_equal(y, wolf_port.forward_stream(arrays, C, T, x))
+    # shift property: dropping the first 16 samples of every stream drops the first window, nothing else
+    y2 = net.forward_stream(_cuda(x[:, :, 16:])).cpu().numpy()
+    assert np.array_equal(y2, y[:, 1:])
