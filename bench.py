@@ -53,6 +53,8 @@ def parse_args():
     ap.add_argument("--subjects", type=int, default=4096, help="stream workload: subjects per GPU")
     ap.add_argument("--stream-len", type=int, default=9600, help="stream workload: samples per subject (60 s at 160 Hz)")
     ap.add_argument("--stream-mode", default="auto", choices=["auto", "fused", "gather"])
+    ap.add_argument("--gather", default="auto", choices=["auto", "peer", "nccl"],
+                    help="multi-GPU logits gather: fused peer stores (symmetric memory) or NCCL all_gather per step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
@@ -273,11 +275,35 @@ def main():
     x = torch.randint(-127, 128, (B, C, T), dtype=torch.int8, device=dev, generator=g)
     logits = torch.empty((B, N_CLASSES), dtype=torch.int8, device=dev)
     gathered = torch.empty((world * B, N_CLASSES), dtype=torch.int8, device=dev) if world > 1 else None
+    # multi-GPU: the all-gather of the logits is fused into the kernel (P2P stores into every rank's symmetric
+    # buffer over NVLink, mibmi_forward_int8_gather); NCCL all_gather per step is the fallback
+    peer = None
+    if world > 1 and args.gather in ("auto", "peer"):
+        from mibminet_b200.sharding import PeerGather
+        try:
+            peer = PeerGather(net, world * B)
+        except RuntimeError as e:
+            if args.gather == "peer":
+                raise
+            if rank == 0:
+                print(f"[bench] peer gather unavailable ({e}); using NCCL all_gather", file=sys.stderr)
+        ok = torch.tensor([1 if peer is not None else 0], device=dev)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if int(ok[0]) == 0:
+            peer = None
+
+    def run_step():
+        if peer is not None:
+            peer.forward(x)
+        else:
+            net.forward(x, out=logits)
+            if world > 1:
+                dist.all_gather_into_tensor(gathered, logits)
 
     def step():
-        net.forward(x, out=logits)
-        if world > 1:
-            dist.all_gather_into_tensor(gathered, logits)
+        run_step()
+        if peer is not None:
+            peer.wait()                  # warm-up only: the timed loop synchronises the ranks once, at its end
 
     for _ in range(max(args.warmup, 3)):
         step()
@@ -294,10 +320,16 @@ def main():
     ev0.record()
     for i in range(args.steps):
         k_ev[i][0].record()
-        net.forward(x, out=logits)
+        if peer is not None:
+            peer.forward(x)
+        else:
+            net.forward(x, out=logits)
         k_ev[i][1].record()
-        if world > 1:
+        if world > 1 and peer is None:
             dist.all_gather_into_tensor(gathered, logits)
+    if peer is not None:
+        gathered = peer.wait()           # one barrier: every rank's rows of the last step are in place
+        logits = gathered[rank * B:(rank + 1) * B]
     ev1.record()
     torch.cuda.synchronize()
     if world > 1:
@@ -307,6 +339,12 @@ def main():
     launches = net.launch_count - launches0
     clocks = sampler.stop(t_wall0, t_wall1) if sampler else None
 
+    gather_checked = None
+    if world > 1:
+        # outside the timed region: the gathered logits against an independent NCCL all_gather of the local ones
+        chk = torch.empty((world * B, N_CLASSES), dtype=torch.int8, device=dev)
+        dist.all_gather_into_tensor(chk, logits.contiguous())
+        gather_checked = bool(torch.equal(chk, gathered))
     ms_total = ev0.elapsed_time(ev1)
     ms_kernel = float(np.mean([a.elapsed_time(b) for a, b in k_ev]))
     t = torch.tensor([ms_total, ms_kernel], dtype=torch.float64, device=dev)
@@ -351,8 +389,10 @@ def main():
             "config": {"workload": WORKLOAD, "trials_per_gpu_per_step": B, "global_batch": world * B,
                        "layout": "[B][C][T] int8 (module order)", "parallelism": f"trial-batch sharding x{world}",
                        "l2_policy": f"input per step {B * C * T / 1e9:.2f} GB > 126 MB L2, no flush needed",
-                       "collective": "one NCCL all_gather of int8 logits per step" if world > 1 else "none",
-                       "kernel_path": net.last_path, "bit_exact_checked": None},
+                       "collective": ("none" if world == 1 else
+                                      "fused: kernel epilogue stores the logits into every rank's symmetric buffer over NVLink, "
+                                      "one barrier at the end" if peer is not None else "one NCCL all_gather of int8 logits per step"),
+                       "kernel_path": net.last_path, "bit_exact_checked": None, "gather_checked": gather_checked},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": NCU_TRAFFIC_BYTES_PER_TRIAL * B if (net.last_path == "fused" and args.shape == "64x480") else None,
                          "traffic_source": "ncu --set full dram__bytes_read.sum + dram__bytes_write.sum per launch of 65536 "

@@ -122,6 +122,15 @@ MIBMI_API int64_t mibmi_launch_count(const mibmi_net_t* net);
 MIBMI_API int mibmi_forward_int8(mibmi_net_t* net, const int8_t* x_dev, int64_t B, int layout,
                        int8_t* logits_dev, void* stream);
 
+/* Forward fused with the all-gather of a batch that is sharded over several GPUs: the logits of
+ * the B local trials are written to rows [row0, row0 + B) of EVERY buffer out_dev[0 .. n_out-1] (int8 [rows][N];
+ * out_dev is a HOST array of device pointers: this rank's buffer and the peer-mapped buffers of the other ranks,
+ * e.g. CUDA IPC / symmetric memory over NVLink).  The fused kernel stores the 4 bytes of a trial to every
+ * destination from its epilogue -- no collective is launched; other paths copy peer to peer on `stream`.
+ * The caller synchronises the ranks (one barrier) before anyone reads a gathered buffer.  n_out <= 16. */
+MIBMI_API int mibmi_forward_int8_gather(mibmi_net_t* net, const int8_t* x_dev, int64_t B, int layout,
+                                        int8_t* const* out_dev, int32_t n_out, int64_t row0, void* stream);
+
 /* Same, plus the inter-layer activations (the taps of QuantLab/export_net_data.py:112-167 in integer
  * form).  Any of the tap pointers may be NULL.  Runs the generic path unless MIBMI_PATH_FUSED is forced
  * (the fused kernel then stores the taps from its registers: a diagnostic instantiation).

@@ -27,7 +27,7 @@ SYMBOLS = [
     "mibmi_forward_int8", "mibmi_forward_int8_taps", "mibmi_forward_int8_host",
     "mibmi_quantize_input_f32", "mibmi_dequantize_logits_f32", "mibmi_debug_magic", "mibmi_debug_pack_fused",
     "mibmi_debug_pack_pipe", "mibmi_stream_windows", "mibmi_stream_supported", "mibmi_forward_stream_int8",
-    "mibmi_forward_stream_int8_taps",
+    "mibmi_forward_stream_int8_taps", "mibmi_forward_int8_gather",
 ]
 
 
@@ -83,6 +83,7 @@ def lib() -> ctypes.CDLL:
     L.mibmi_forward_int8.argtypes = [vp, vp, i64, i32, vp, vp]
     L.mibmi_forward_int8_taps.argtypes = [vp, vp, i64, i32, vp, vp, vp, vp, vp, vp]
     L.mibmi_forward_int8_host.argtypes = [vp, vp, i64, i32, vp]
+    L.mibmi_forward_int8_gather.argtypes = [vp, vp, i64, i32, ctypes.POINTER(vp), ctypes.c_int32, i64, vp]
     L.mibmi_stream_windows.argtypes = [vp, i64, ctypes.c_int32]
     L.mibmi_stream_windows.restype = i64
     L.mibmi_stream_supported.argtypes = [vp, ctypes.POINTER(ctypes.c_char_p)]

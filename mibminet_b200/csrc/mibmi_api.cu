@@ -485,7 +485,7 @@ size_t trial_bytes(const mibmi_net* n, int layout) {
 }
 
 int forward_impl(mibmi_net* net, const int8_t* x, int64_t B, int layout, int8_t* logits, int8_t* t1, int8_t* t2,
-                 int8_t* t3, int8_t* t4, bool taps, cudaStream_t stream) {
+                 int8_t* t3, int8_t* t4, bool taps, cudaStream_t stream, const PeerOut* peers = nullptr) {
     if (!net) return MIBMI_ERR_NULL;
     if (B < 0 || (layout != MIBMI_LAYOUT_BCT && layout != MIBMI_LAYOUT_BTC)) return MIBMI_ERR_PARAM;
     if (B == 0) return MIBMI_OK;   // empty batch: nothing to read or write, pointers may be null
@@ -500,13 +500,21 @@ int forward_impl(mibmi_net* net, const int8_t* x, int64_t B, int layout, int8_t*
     DeviceGuard dg(net->device);
     if (dg.err != cudaSuccess) return fail_cuda(net, dg.err);
     cudaError_t e;
+    PeerOut none;
+    none.n = 0;
     if (path == MIBMI_PATH_FUSED)
-        e = launch_pipe(net->pipe_dev, net->pipe_fast1, net->C, net->T, x, B, logits, t1, t2, t3, t4, net->num_sms, stream);
+        e = launch_pipe(net->pipe_dev, net->pipe_fast1, net->C, net->T, x, B, logits, peers ? *peers : none, t1, t2, t3, t4,
+                        net->num_sms, stream);
     else if (path == MIBMI_PATH_FUSED_V1)
         e = launch_fused(net->fused_dev, net->C, net->T, x, B, logits, net->num_sms, net->ctas_per_sm, stream);
     else
         e = launch_generic(net->gen_dev, net->T, net->F2, x, B, layout, logits, t1, t2, t3, t4, net->num_sms, stream);
     if (e != cudaSuccess) return fail_cuda(net, e);
+    if (peers && path != MIBMI_PATH_FUSED)      // kernels without the fused gather: peer copies on the same stream
+        for (int i = 0; i < peers->n; i++) {
+            e = cudaMemcpyAsync(peers->p[i], logits, (size_t)B * net->N, cudaMemcpyDefault, stream);
+            if (e != cudaSuccess) return fail_cuda(net, e);
+        }
     net->last_path.store(path);
     net->launches.fetch_add(1);
     return MIBMI_OK;
@@ -692,6 +700,20 @@ int mibmi_set_option(mibmi_net_t* net, int option, int64_t value) {
 
 int mibmi_forward_int8(mibmi_net_t* net, const int8_t* x_dev, int64_t B, int layout, int8_t* logits_dev, void* stream) {
     return forward_impl(net, x_dev, B, layout, logits_dev, nullptr, nullptr, nullptr, nullptr, false, (cudaStream_t)stream);
+}
+
+int mibmi_forward_int8_gather(mibmi_net_t* net, const int8_t* x_dev, int64_t B, int layout, int8_t* const* out_dev,
+                              int32_t n_out, int64_t row0, void* stream) {
+    if (!net || !out_dev) return MIBMI_ERR_NULL;
+    if (n_out < 1 || n_out > kMaxPeers + 1 || row0 < 0) return MIBMI_ERR_PARAM;
+    PeerOut po;
+    po.n = n_out - 1;
+    for (int i = 0; i < n_out; i++) {
+        if (!out_dev[i]) return MIBMI_ERR_NULL;
+        if (i > 0) po.p[i - 1] = out_dev[i] + row0 * net->N;
+    }
+    return forward_impl(net, x_dev, B, layout, out_dev[0] + row0 * net->N, nullptr, nullptr, nullptr, nullptr, false,
+                        (cudaStream_t)stream, &po);
 }
 
 int mibmi_forward_int8_taps(mibmi_net_t* net, const int8_t* x_dev, int64_t B, int layout, int8_t* logits_dev,

@@ -26,9 +26,16 @@ cudaError_t launch_fused(const FusedNet* net_dev, int C, int T, const int8_t* x,
 
 // Warp-specialised pipeline kernel (mibmi_pipe.cu): the default fused path.  Optional taps
 // (y1 [B][16][T], y2/y3 [B][16][T/8], y4 [B][16][T/64]) select a diagnostic instantiation.
+// Extra destinations of the logits (peer-mapped buffers of the other ranks): the all-gather of a sharded batch
+// is done by the kernel's own stores over NVLink.
+constexpr int kMaxPeers = 15;
+struct PeerOut {
+    int8_t* p[kMaxPeers];
+    int n;
+};
 bool pipe_has_instance(int C, int T);
 cudaError_t launch_pipe(const PipeNet* net_dev, bool fast1, int C, int T, const int8_t* x, long long B,
-                        int8_t* logits, int8_t* t1, int8_t* t2, int8_t* t3, int8_t* t4, int num_sms,
+                        int8_t* logits, const PeerOut& peers, int8_t* t1, int8_t* t2, int8_t* t3, int8_t* t4, int num_sms,
                         cudaStream_t stream);
 
 // Sliding-window streaming kernel (mibmi_stream.cu): x [S][C][L] -> logits [S][W][4], W = (L - T) / 16 + 1.

@@ -131,7 +131,7 @@ __device__ __forceinline__ int tdiv1(int x, int m, int s) {
 template <class K, bool FAST1, bool TAPS>
 __global__ void __launch_bounds__(kPipeThreads, 1)
 pipe_forward_kernel(const PipeNet* __restrict__ net, const int8_t* __restrict__ x, long long B,
-                    int8_t* __restrict__ logits, int8_t* __restrict__ tap1, int8_t* __restrict__ tap2,
+                    int8_t* __restrict__ logits, const PeerOut peers, int8_t* __restrict__ tap1, int8_t* __restrict__ tap2,
                     int8_t* __restrict__ tap3, int8_t* __restrict__ tap4) {
     extern __shared__ __align__(128) uint8_t smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -475,7 +475,12 @@ pipe_forward_kernel(const PipeNet* __restrict__ net, const int8_t* __restrict__ 
                 const uint32_t b0 = g == 0 ? y4w[8 * ks + q] : 0u, b1 = g == 0 ? y4w[8 * ks + 4 + q] : 0u;
                 mma_k32(z, a, b0, b1);
             }
-            if (q == 0 && g < 4) logits[(size_t)b * 4 + g] = (int8_t)clip8(tdiv_magic(z[0] + b5, m5, sh5));
+            if (q == 0 && g < 4) {
+                const int8_t o = (int8_t)clip8(tdiv_magic(z[0] + b5, m5, sh5));
+                logits[(size_t)b * 4 + g] = o;
+                // fused all-gather: the same 4 bytes go to every peer's buffer (NVLink P2P stores)
+                for (int i = 0; i < peers.n; i++) peers.p[i][(size_t)b * 4 + g] = o;
+            }
             __syncwarp();   // y4 is rewritten by the next trial
         }
     }
@@ -485,7 +490,7 @@ pipe_forward_kernel(const PipeNet* __restrict__ net, const int8_t* __restrict__ 
 // ---------------------------------------------------------------------------------------------
 template <int C, int T>
 static cudaError_t launch_pipe_instance(const PipeNet* net_dev, bool fast1, const int8_t* x, long long B,
-                                        int8_t* logits, int8_t* t1, int8_t* t2, int8_t* t3, int8_t* t4,
+                                        int8_t* logits, const PeerOut& peers, int8_t* t1, int8_t* t2, int8_t* t3, int8_t* t4,
                                         int num_sms, cudaStream_t stream) {
     // deepest input ring (<= MIBMI_STAGES) that fits the 227 KB of shared memory
     constexpr int S = PCfg<C, T, MIBMI_STAGES>::SMEM_RAW <= 227 * 1024 ? MIBMI_STAGES
@@ -499,7 +504,7 @@ static cudaError_t launch_pipe_instance(const PipeNet* net_dev, bool fast1, cons
     if (e != cudaSuccess) return e;
     long long grid = num_sms;
     if (grid > B) grid = B;
-    kern<<<(unsigned)grid, kPipeThreads, K::SMEM, stream>>>(net_dev, x, B, logits, t1, t2, t3, t4);
+    kern<<<(unsigned)grid, kPipeThreads, K::SMEM, stream>>>(net_dev, x, B, logits, peers, t1, t2, t3, t4);
     return cudaGetLastError();
 }
 
@@ -513,9 +518,9 @@ bool pipe_has_instance(int C, int T) {
 }
 
 cudaError_t launch_pipe(const PipeNet* net_dev, bool fast1, int C, int T, const int8_t* x, long long B,
-                        int8_t* logits, int8_t* t1, int8_t* t2, int8_t* t3, int8_t* t4, int num_sms,
+                        int8_t* logits, const PeerOut& peers, int8_t* t1, int8_t* t2, int8_t* t3, int8_t* t4, int num_sms,
                         cudaStream_t stream) {
-#define X(c, t) if (C == c && T == t) return launch_pipe_instance<c, t>(net_dev, fast1, x, B, logits, t1, t2, t3, t4, num_sms, stream);
+#define X(c, t) if (C == c && T == t) return launch_pipe_instance<c, t>(net_dev, fast1, x, B, logits, peers, t1, t2, t3, t4, num_sms, stream);
     MIBMI_PIPE_SHAPES(X)
 #undef X
     return cudaErrorInvalidValue;

@@ -136,6 +136,16 @@ class Int8Net:
 
     __call__ = forward
 
+    def forward_gather(self, x: torch.Tensor, out_ptrs, row0: int, layout: str = "bct"):
+        """Forward fused with the all-gather of a sharded batch: the logits of the local trials go to rows
+        [row0, row0 + B) of every buffer in `out_ptrs` (device pointers; own buffer first, then the peer-mapped
+        buffers of the other ranks).  See mibmi_forward_int8_gather."""
+        x = self._check_x(x, layout)
+        arr = (ctypes.c_void_p * len(out_ptrs))(*[int(p) for p in out_ptrs])
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        _lib.check(self._L.mibmi_forward_int8_gather(self._h, x.data_ptr(), x.shape[0], _LAYOUTS[layout], arr,
+                                                     len(out_ptrs), int(row0), stream), "mibmi_forward_int8_gather")
+
     def forward_taps(self, x: torch.Tensor, layout: str = "bct"):
         """-> (logits, {'y1','y2','y3','y4'}) : inter-layer int8 activations (generic path)."""
         x = self._check_x(x, layout)

@@ -64,3 +64,44 @@ class ShardedInt8Net:
 
     def forward(self, x_local: torch.Tensor, n_total: int, **kw) -> torch.Tensor:
         return gather_logits(self.forward_local(x_local, **kw), n_total, self.group)
+
+
+class PeerGather:
+    """All-gather fused into the kernel (mibmi_forward_int8_gather): every rank owns a `[n_total, N]` int8 buffer
+    in CUDA symmetric memory; a rank's kernel stores the logits of its own trials into the same rows of ALL
+    buffers over NVLink (P2P stores from the epilogue), so no collective is launched per forward.
+
+        pg = PeerGather(net, n_total)            # collective: allocation + rendezvous
+        pg.forward(x_local)                      # asynchronous, no communication call
+        ...
+        full = pg.wait()                         # one barrier; `full` holds every rank's logits
+
+    Raises RuntimeError when symmetric memory cannot be set up (the caller then uses `gather_logits`)."""
+
+    def __init__(self, net, n_total: int, group: Optional[dist.ProcessGroup] = None):
+        import torch.distributed._symmetric_memory as symm_mem
+        self.net = net
+        self.group = group if group is not None else dist.group.WORLD
+        self.world, self.rank = dist.get_world_size(self.group), dist.get_rank(self.group)
+        self.n_total = int(n_total)
+        self.lo, self.hi = shard_bounds(self.n_total, self.world, self.rank)
+        try:
+            self.buf = symm_mem.empty((max(self.n_total, 1), net.N), dtype=torch.int8, device=net.device)
+            self.handle = symm_mem.rendezvous(self.buf, self.group.group_name)
+            ptrs = [int(p) for p in self.handle.buffer_ptrs]
+        except Exception as e:   # noqa: BLE001 -- any failure means "not available here"
+            raise RuntimeError(f"symmetric memory unavailable: {e}") from e
+        if len(ptrs) != self.world:
+            raise RuntimeError("symmetric memory rendezvous returned an unexpected number of peers")
+        # own buffer first: the kernel's primary destination
+        self.ptrs = [ptrs[self.rank]] + [p for r, p in enumerate(ptrs) if r != self.rank]
+
+    def forward(self, x_local: torch.Tensor, **kw) -> None:
+        if x_local.shape[0] != self.hi - self.lo:
+            raise ValueError(f"rank {self.rank}: expected {self.hi - self.lo} local trials, got {x_local.shape[0]}")
+        self.net.forward_gather(x_local, self.ptrs, self.lo, **kw)
+
+    def wait(self) -> torch.Tensor:
+        """Barrier across the ranks (on the current stream): afterwards every row of the buffer is final."""
+        self.handle.barrier()
+        return self.buf[:self.n_total]

@@ -276,3 +276,20 @@ def test_stream_config5_slice_every_logit():
     # shift property: dropping the first 16 samples of every stream drops the first window, nothing else
     y2 = net.forward_stream(_cuda(x[:, :, 16:])).cpu().numpy()
     assert np.array_equal(y2, y[:, 1:])
+
+
+# ---- forward fused with the gather (multi-destination epilogue) -----------------------------------------
+@pytest.mark.parametrize("C,T", [(64, 480), (22, 1125), (5, 64)])
+def test_forward_gather_writes_every_destination(C, T):
+    """mibmi_forward_int8_gather on one GPU: three destination buffers stand in for three ranks' symmetric
+    buffers; rows outside [row0, row0 + B) stay untouched.  (5, 64) has no fused kernel: peer copies."""
+    net, arrays = _net(C, T, seed=81)
+    B, row0, rows = 333, 100, 600
+    x = synth.make_trials(B, C, T, seed=82)
+    ref = wolf_port.forward(arrays, C, T, x)
+    bufs = [torch.full((rows, 4), 77, dtype=torch.int8, device="cuda:0") for _ in range(3)]
+    net.forward_gather(_cuda(x), [b.data_ptr() for b in bufs], row0)
+    for b in bufs:
+        h = b.cpu().numpy()
+        assert np.array_equal(h[row0:row0 + B], ref)
+        assert (h[:row0] == 77).all() and (h[row0 + B:] == 77).all()
