@@ -262,6 +262,15 @@ bool pack_pipe(const mibmi_params_t* p, PipeNet* f, const char** why) {
                 }
                 f->w1blk[kb][nt][lane] = word;
             }
+    {
+        const int kpad = (C + 31) / 32 * 32;
+        for (int n = 0; n < 16; n++) {
+            const int sg = p->l1_factor[n] < 0 ? -1 : 1;
+            for (int c = 0; c < C && c < 64; c++)
+                f->w1umma[(n >> 3) * (kpad / 16) * 128 + (c >> 4) * 128 + (n & 7) * 16 + (c & 15)] =
+                    (uint8_t)(int8_t)(sg * p->l1_weight_align[n * CA4 + c]);
+        }
+    }
     // ---- layer 2: Toeplitz B fragments.  Window-relative sample j = o + 1 + tap (o = output offset in
     // the 32-sample window), K position kk of k-step s <-> j = 32 s + kk
     for (int k = 0; k < 16; k++) {

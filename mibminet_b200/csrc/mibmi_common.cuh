@@ -75,6 +75,9 @@ struct PipeNet {
     int off1[16], m1[16], sh1[16];
     int fast1;                      // 1: sh1 == 0 everywhere (magic = floor(2^32/d)+1, exact after clip8)
     int pad0_[3];
+    // layer 1 for tcgen05.mma: W1 [16 filters][KPAD channels] as K-major 8 x 16-byte core matrices,
+    // byte (n >> 3) * (KPAD / 16) * 128 + (c >> 4) * 128 + (n & 7) * 16 + (c & 15), natural channel order
+    alignas(16) uint8_t w1umma[16 * 64];
     // layer 2: Toeplitz B fragments [channel][variant*6 + kstep*2 + half][lane]
     uint32_t w2frag[16][24][32];
     int thr2[16], sig2[16], soff2[16], m2[16], sh2[16];

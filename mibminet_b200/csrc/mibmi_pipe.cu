@@ -27,9 +27,13 @@
 //   full_x / empty_x [S]   producer <-> A      full_y1 / empty_y1 [2]   A <-> B
 //   full_y3 / empty_y3 [2] B <-> C
 // Integer results are bit-identical to the reference (tests/test_parity_gpu.py).
+#include <cuda.h>
+#include <string.h>
+
 #include "mibmi_common.cuh"
 #include "mibmi_kernels.h"
 #include "mibmi_ptx.cuh"
+#include "mibmi_tmap.h"
 
 namespace mibmi {
 
@@ -49,7 +53,10 @@ __device__ long long g_prof[148 * 32 * 4];
 constexpr int kAW = 8;                        // layer-1 warps
 constexpr int kBW = 16;                       // layer-2/3 warps (one channel each)
 constexpr int kCW = 2;                         // layer-4/5 warps (alternate trials)
-constexpr int kPipeThreads = (kAW + kBW + kCW + 1) * 32;   // + 1 TMA producer warp
+constexpr int kPipeThreads = (kAW + kBW + kCW + 2) * 32;   // + TMA producer warp + tcgen05.mma issuer warp
+#ifndef MIBMI_UMMA
+#define MIBMI_UMMA 1
+#endif
 #ifndef MIBMI_ROTATE
 #define MIBMI_ROTATE 1
 #endif
@@ -73,6 +80,17 @@ struct PCfg {
     // REAL: rows of T bytes are not 16-byte aligned in global memory (T % 16 != 0, e.g. 22 x 1125): every row
     // is bulk-copied from the 16-byte boundary below it and the layer-1 warps shift it into place (see A)
     static constexpr bool REAL = (T % 16) != 0;
+    // UMMA: layer 1 on the 5th-generation tensor core.  The trial arrives as 2-D TMA tiles [KPAD ch][128 samples]
+    // with the 128-byte swizzle = the canonical MN-major operand of tcgen05.mma (kind::i8, M = 128 samples, N = 16
+    // filters, K = 32 channels per instruction); the int32 accumulators of a trial live in TMEM (16 columns per
+    // tile, two trials in flight) and the layer-1 warps read them back with tcgen05.ld.16x256b, whose register
+    // layout is the m16n8 fragment the requantisation epilogue was written for.
+    static constexpr bool UMMA = MIBMI_UMMA && !REAL;
+    static constexpr int TILES = (T + 127) / 128, KPAD = (C + 31) / 32 * 32, KSTEPS = KPAD / 32;
+    static constexpr int TILE_BYTES = KPAD * 128;
+    static constexpr int TMEM_COLS_TRIAL = 16 * TILES;            // accumulator columns of one trial
+    static constexpr int TMEM_COLS = 2 * TMEM_COLS_TRIAL <= 32 ? 32 : 2 * TMEM_COLS_TRIAL <= 64 ? 64 :
+                                     2 * TMEM_COLS_TRIAL <= 128 ? 128 : 2 * TMEM_COLS_TRIAL <= 256 ? 256 : 512;
     static constexpr int T8 = T / 8, T64 = T8 / 8;
     static constexpr int UNITS = (T + 31) / 32;                  // layer-1 units of 32 samples
     static constexpr int XP = REAL ? 32 * UNITS + 48 : T;        // row pitch inside a stage
@@ -86,14 +104,17 @@ struct PCfg {
     static constexpr int NST = (T64 + 3) / 4;                    // layer-4 super-tiles of 4 pooling groups
     static constexpr int T64P = (T64 + 1) / 2 * 2, KST5 = T64P / 2;
     static constexpr int TRIAL_BYTES = C * T;
-    static constexpr int XS_BYTES = (((REAL ? C * XP : C * T + 16) + 127) / 128) * 128;
+    static constexpr int XS_BYTES = UMMA ? TILES * TILE_BYTES : (((REAL ? C * XP : C * T + 16) + 127) / 128) * 128;
     static constexpr int Y1_BYTES = 16 * Y1S, Y3_BYTES = 16 * Y3S;
     // barriers (8 B each)
     static constexpr int BAR_FULL_X = 0, BAR_EMPTY_X = 8 * S, BAR_FULL_Y1 = 16 * S, BAR_EMPTY_Y1 = BAR_FULL_Y1 + 8 * kNY1,
                          BAR_FULL_Y3 = BAR_EMPTY_Y1 + 8 * kNY1, BAR_EMPTY_Y3 = BAR_FULL_Y3 + 8 * kNY3,
-                         BAR_END = BAR_EMPTY_Y3 + 8 * kNY3;
+                         BAR_TFULL = BAR_EMPTY_Y3 + 8 * kNY3, BAR_TEMPTY = BAR_TFULL + 16, BAR_END = BAR_TEMPTY + 16;
     // shared memory map
-    static constexpr int OFF_XS = 256;
+    static constexpr int OFF_TMEM = 248;                         // TMEM base address written by tcgen05.alloc
+    static constexpr int OFF_W1 = 1024;                          // UMMA: W1 as 8 x 16-byte core matrices (K-major)
+    static constexpr int W1_SBO = KSTEPS * 256;                  // bytes between the two groups of 8 filters
+    static constexpr int OFF_XS = UMMA ? 3072 : 256;             // UMMA tiles: 1024-byte aligned swizzle atoms
     static constexpr int OFF_Y1 = OFF_XS + S * XS_BYTES;
     static constexpr int OFF_Y2 = OFF_Y1 + kNY1 * Y1_BYTES;
     static constexpr int OFF_Y3 = OFF_Y2 + 16 * Y2S;
@@ -107,7 +128,8 @@ struct PCfg {
     static_assert(T8 % 2 == 0, "layer 3 stores sample pairs");
     static_assert(KB16 >= 1 && KB16 <= kPipeMaxKB16, "C <= 64");
     static_assert(UNITS + 1 <= NCH - 1, "layer-1 chunks fit the planes with one zero chunk on each side");
-    static_assert(BAR_END <= 256, "barrier area");
+    static_assert(BAR_END <= OFF_TMEM, "barrier area");
+    static_assert(!UMMA || (2 * TMEM_COLS_TRIAL <= 512 && 16 * KPAD <= 2048), "TMEM / W1 staging");
     static_assert(KST5 <= kPipeMaxKst5, "T too large for PipeNet::w5frag");
 };
 
@@ -130,7 +152,7 @@ __device__ __forceinline__ int tdiv1(int x, int m, int s) {
 
 template <class K, bool FAST1, bool TAPS>
 __global__ void __launch_bounds__(kPipeThreads, 1)
-pipe_forward_kernel(const PipeNet* __restrict__ net, const int8_t* __restrict__ x, long long B,
+pipe_forward_kernel(const __grid_constant__ CUtensorMap tmx, const PipeNet* __restrict__ net, const int8_t* __restrict__ x, long long B,
                     int8_t* __restrict__ logits, const PeerOut peers, int8_t* __restrict__ tap1, int8_t* __restrict__ tap2,
                     int8_t* __restrict__ tap3, int8_t* __restrict__ tap4) {
     extern __shared__ __align__(128) uint8_t smem[];
@@ -144,7 +166,7 @@ pipe_forward_kernel(const PipeNet* __restrict__ net, const int8_t* __restrict__ 
     if (tid == 0) {
         for (int s = 0; s < K::S; s++) {
             mbar_init(sbase + K::BAR_FULL_X + 8 * s, 1);
-            mbar_init(sbase + K::BAR_EMPTY_X + 8 * s, kAW);
+            mbar_init(sbase + K::BAR_EMPTY_X + 8 * s, K::UMMA ? 1 : kAW);   // UMMA: one tcgen05.commit frees a stage
         }
         for (int i = 0; i < kNY1; i++) {
             mbar_init(sbase + K::BAR_FULL_Y1 + 8 * i, kAW);
@@ -154,19 +176,93 @@ pipe_forward_kernel(const PipeNet* __restrict__ net, const int8_t* __restrict__ 
             mbar_init(sbase + K::BAR_FULL_Y3 + 8 * i, kBW);
             mbar_init(sbase + K::BAR_EMPTY_Y3 + 8 * i, 1);
         }
+        for (int i = 0; i < 2; i++) {
+            mbar_init(sbase + K::BAR_TFULL + 8 * i, 1);
+            mbar_init(sbase + K::BAR_TEMPTY + 8 * i, kAW);
+        }
         mbar_fence_init();
+    }
+    if (K::UMMA) {
+        // W1 as the K-major B operand; TMEM for two trials' accumulators (allocated by the issuer warp)
+        for (int i = tid; i < 16 * K::KPAD / 4; i += kPipeThreads)
+            reinterpret_cast<uint32_t*>(smem + K::OFF_W1)[i] = reinterpret_cast<const uint32_t*>(net->w1umma)[i];
+        if (warp == kAW + kBW + kCW + 1) tmem_alloc(sbase + K::OFF_TMEM, K::TMEM_COLS);
+        fence_proxy_async();
+        tc_fence_before();
     }
     {
         uint4* z = reinterpret_cast<uint4*>(smem + K::OFF_Y1);
         for (int i = tid; i < (K::SMEM - K::OFF_Y1) / 16; i += kPipeThreads) z[i] = make_uint4(0, 0, 0, 0);
     }
     __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = K::UMMA ? *reinterpret_cast<const uint32_t*>(smem + K::OFF_TMEM) : 0u;
     PROF_BEGIN
 
     if (warp < kAW) {
         // =====================================================================================
         // A: layer 1
         // =====================================================================================
+      if constexpr (K::UMMA) {
+        // the contraction ran on the tensor core (issuer warp below); this warp owns TMEM lanes 32 (warp & 3) ..
+        // + 31 = samples 32 (warp & 3) .. of every 128-sample tile, and tiles jb, jb + 2 (jb alternates per trial)
+        int off1[2][2], mg1[2][2], sh1[2][2];
+#pragma unroll
+        for (int nt = 0; nt < 2; nt++)
+#pragma unroll
+            for (int e = 0; e < 2; e++) {
+                off1[nt][e] = net->off1[8 * nt + 2 * q + e];
+                mg1[nt][e] = net->m1[8 * nt + 2 * q + e];
+                sh1[nt][e] = net->sh1[8 * nt + 2 * q + e];
+            }
+        const uint32_t st_off = ((lane & 7) + 8 * ((lane >> 3) & 1)) * K::Y1S + (lane >> 4) * K::PLANE + 16;
+        const int qi = warp & 3;
+        for (int n = 0; n < nloc; n++) {
+            const int buf = n % kNY1, ab = n & 1;
+            PWAIT(0, sbase + K::BAR_TFULL + 8 * ab, (n >> 1) & 1);
+            tc_fence_after();
+            PWAIT(1, sbase + K::BAR_EMPTY_Y1 + 8 * buf, ((n / kNY1) & 1) ^ 1);
+            const uint32_t yb = sbase + K::OFF_Y1 + buf * K::Y1_BYTES + st_off;
+#pragma unroll 1
+            for (int j = ((warp >> 2) + (MIBMI_ROTATE ? n : 0)) & 1; j < K::TILES; j += 2) {
+                const int u = 4 * j + qi;                        // unit of 32 samples
+                if (32 * u >= K::T) break;
+                uint32_t r[2][8];
+                const uint32_t ta = tmem_base + ((uint32_t)(32 * qi) << 16) + ab * K::TMEM_COLS_TRIAL + 16 * j;
+                tmem_ld_16x256b_x2(r[0], ta);
+                tmem_ld_16x256b_x2(r[1], ta + (16u << 16));
+                tmem_ld_wait();
+                uint32_t w[2][2];
+#pragma unroll
+                for (int mt = 0; mt < 2; mt++)
+#pragma unroll
+                    for (int nt = 0; nt < 2; nt++) {
+                        int v[4];
+#pragma unroll
+                        for (int c = 0; c < 4; c++) {
+                            v[c] = tdiv1<FAST1>((int)r[mt][4 * nt + c] + off1[nt][c & 1], mg1[nt][c & 1], sh1[nt][c & 1]);
+                            if (K::T % 32 != 0 && 32 * u + 16 * mt + g + 8 * (c >> 1) >= K::T) v[c] = 0;
+                        }
+                        w[mt][nt] = pack4_sat(v[0], v[1], v[2], v[3]);
+                        if (TAPS && tap1) {
+                            const long long b = first + (long long)n * stride;
+#pragma unroll
+                            for (int c = 0; c < 4; c++) {
+                                const int f = 8 * nt + 2 * q + (c & 1), t = 32 * u + 16 * mt + g + 8 * (c >> 1);
+                                if (t < K::T) tap1[((size_t)b * 16 + f) * K::T + t] = (int8_t)clip8(v[c]);
+                            }
+                        }
+                    }
+                stsm_t8_x4(yb + 16 * u, w[0][0], w[0][1], w[1][0], w[1][1]);
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) {
+                mbar_arrive(sbase + K::BAR_TEMPTY + 8 * ab);
+                mbar_arrive(sbase + K::BAR_FULL_Y1 + 8 * buf);
+            }
+        }
+      } else {
         // W1 as the B operand: [block][filter n-tile][lane] = (channels 4q..4q+3 of the block, filter 8 nt + g)
         uint32_t wfr[K::KB16][2];
 #pragma unroll
@@ -285,6 +381,7 @@ pipe_forward_kernel(const PipeNet* __restrict__ net, const int8_t* __restrict__ 
                 mbar_arrive(sbase + K::BAR_FULL_Y1 + 8 * buf);
             }
         }
+      }
     } else if (warp < kAW + kBW) {
         // =====================================================================================
         // B: layers 2 + 3 of channel k
@@ -397,6 +494,14 @@ pipe_forward_kernel(const PipeNet* __restrict__ net, const int8_t* __restrict__ 
                 if (lane == 0) mbar_expect_tx(bar, total);
                 __syncwarp();
                 if (lane < K::C) bulk_g2s(dst + lane * K::XP, x + (off & ~(size_t)15), bytes, bar);
+            } else if (K::UMMA) {
+                if (lane == 0) {
+                    // 128-sample tiles [C][128] of the [B * C][T] tensor; columns past T are zero-filled
+                    mbar_expect_tx(bar, K::TILES * K::C * 128);
+#pragma unroll
+                    for (int j = 0; j < K::TILES; j++)
+                        tma_load_2d(dst + j * K::TILE_BYTES, &tmx, 128 * j, (int)((first + (long long)n * stride) * K::C), bar);
+                }
             } else if (lane == 0) {
                 mbar_expect_tx(bar, K::TRIAL_BYTES);
                 bulk_g2s(dst, x + toff, K::CA * K::T, bar);
@@ -409,6 +514,32 @@ pipe_forward_kernel(const PipeNet* __restrict__ net, const int8_t* __restrict__ 
                 const int st = n % K::S;
                 PWAIT(0, sbase + K::BAR_EMPTY_X + 8 * st, (n / K::S) & 1);
                 issue(st, n + K::S);
+            }
+        }
+    } else if (warp == kAW + kBW + kCW + 1) {
+        // =====================================================================================
+        // M: tcgen05.mma issuer (one thread).  Per trial: TILES x KSTEPS instructions
+        //    D[128 samples x 16 filters] (+)= Xt[128 x 32 ch] * W1t[32 x 16], then two commits: the input stage
+        //    is free (no A-warp touches it any more) and the accumulators are complete
+        // =====================================================================================
+        if (K::UMMA && lane == 0) {
+            constexpr uint32_t idesc = umma_idesc_i8(128, 16);
+            for (int n = 0; n < nloc; n++) {
+                const int st = n % K::S, ab = n & 1;
+                PWAIT(0, sbase + K::BAR_FULL_X + 8 * st, (n / K::S) & 1);
+                PWAIT(1, sbase + K::BAR_TEMPTY + 8 * ab, ((n >> 1) & 1) ^ 1);
+                tc_fence_after();
+                const uint32_t xs = sbase + K::OFF_XS + st * K::XS_BYTES;
+#pragma unroll
+                for (int j = 0; j < K::TILES; j++)
+#pragma unroll
+                    for (int ks = 0; ks < K::KSTEPS; ks++)
+                        umma_i8(tmem_base + ab * K::TMEM_COLS_TRIAL + 16 * j,
+                                umma_desc(xs + j * K::TILE_BYTES + ks * 4096, 16, 1024, 2),      // MN-major, 128B swizzle
+                                umma_desc(sbase + K::OFF_W1 + ks * 256, 128, K::W1_SBO, 0),      // K-major core matrices
+                                idesc, ks > 0);
+                umma_commit(sbase + K::BAR_EMPTY_X + 8 * st);
+                umma_commit(sbase + K::BAR_TFULL + 8 * ab);
             }
         }
     } else {
@@ -485,9 +616,26 @@ pipe_forward_kernel(const PipeNet* __restrict__ net, const int8_t* __restrict__ 
         }
     }
     PROF_END
+    if (K::UMMA) {
+        tc_fence_before();
+        __syncthreads();
+        if (warp == kAW + kBW + kCW + 1) tmem_dealloc(tmem_base, K::TMEM_COLS);
+    }
 }
 
 // ---------------------------------------------------------------------------------------------
+tmap_encode_t tmap_encoder() {
+    static tmap_encode_t fn = [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult qr;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qr) != cudaSuccess ||
+            qr != cudaDriverEntryPointSuccess)
+            p = nullptr;
+        return (tmap_encode_t)p;
+    }();
+    return fn;
+}
+
 template <int C, int T>
 static cudaError_t launch_pipe_instance(const PipeNet* net_dev, bool fast1, const int8_t* x, long long B,
                                         int8_t* logits, const PeerOut& peers, int8_t* t1, int8_t* t2, int8_t* t3, int8_t* t4,
@@ -497,6 +645,20 @@ static cudaError_t launch_pipe_instance(const PipeNet* net_dev, bool fast1, cons
                     : PCfg<C, T, MIBMI_STAGES - 1>::SMEM_RAW <= 227 * 1024 ? MIBMI_STAGES - 1
                     : PCfg<C, T, MIBMI_STAGES - 2>::SMEM_RAW <= 227 * 1024 ? MIBMI_STAGES - 2 : 3;
     using K = PCfg<C, T, S>;
+    CUtensorMap tm;
+    memset(&tm, 0, sizeof(tm));
+    if (K::UMMA) {
+        tmap_encode_t enc = tmap_encoder();
+        if (!enc) return cudaErrorNotSupported;
+        cuuint64_t dims[2] = {(cuuint64_t)T, (cuuint64_t)(B * C)};
+        cuuint64_t strides[1] = {(cuuint64_t)T};
+        cuuint32_t box[2] = {128, (cuuint32_t)C};
+        cuuint32_t estr[2] = {1, 1};
+        if (enc(&tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<int8_t*>(x), dims, strides, box, estr,
+                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+            return cudaErrorInvalidValue;
+    }
     const bool taps = t1 || t2 || t3 || t4;
     auto kern = taps ? pipe_forward_kernel<K, false, true>
                      : (fast1 ? pipe_forward_kernel<K, true, false> : pipe_forward_kernel<K, false, false>);
@@ -504,7 +666,7 @@ static cudaError_t launch_pipe_instance(const PipeNet* net_dev, bool fast1, cons
     if (e != cudaSuccess) return e;
     long long grid = num_sms;
     if (grid > B) grid = B;
-    kern<<<(unsigned)grid, kPipeThreads, K::SMEM, stream>>>(net_dev, x, B, logits, peers, t1, t2, t3, t4);
+    kern<<<(unsigned)grid, kPipeThreads, K::SMEM, stream>>>(tm, net_dev, x, B, logits, peers, t1, t2, t3, t4);
     return cudaGetLastError();
 }
 

@@ -58,6 +58,46 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const void* tmap, int 
 }
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
+// ---- tcgen05 (5th-generation tensor core, accumulators in TMEM) ----------------------------------
+// descriptor / layout facts were verified on the box with tools/probe_umma.cu
+__device__ __forceinline__ void tmem_alloc(uint32_t smem_result, uint32_t cols) {      // one full warp
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_result), "r"(cols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t cols) {          // the same warp
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+// shared-memory matrix descriptor (cute::UMMA::SmemDescriptor): start address, leading / stride byte offsets
+// (all >> 4), version 1 (Blackwell), layout type (0 = no swizzle, 2 = 128-byte swizzle)
+__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes, uint32_t layout_type) {
+    return (uint64_t)((saddr >> 4) & 0x3fff) | ((uint64_t)((lbo_bytes >> 4) & 0x3fff) << 16) |
+           ((uint64_t)((sbo_bytes >> 4) & 0x3fff) << 32) | ((uint64_t)1 << 46) | ((uint64_t)layout_type << 61);
+}
+// instruction descriptor (cute::UMMA::InstrDescriptor) of kind::i8: S32 accumulator, signed int8 A and B,
+// A MN-major (the [channel][sample] tile), B K-major, N >> 3 at bit 17, M >> 4 at bit 24
+__device__ __forceinline__ constexpr uint32_t umma_idesc_i8(int M, int N) {
+    return (2u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+// D[tmem] (+)= A[smem] * B[smem], issued by ONE thread (SASS: UTCIMMA)
+__device__ __forceinline__ void umma_i8(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%5, %5, %5, %5}, p;\n\t}"
+                 ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate), "r"(0u) : "memory");
+}
+// arrive on an mbarrier when every tcgen05.mma issued so far by this thread has completed (SASS: UTCBAR)
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.b64 [%0];" ::"r"(bar) : "memory");
+}
+// 16 TMEM lanes x 16 columns -> 8 registers in the m16n8 accumulator-fragment order (SASS: LDTM.16dp256bit.x2):
+// r[4 nt + c] = (lane g + 8 (c >> 1), column 8 nt + 2 q + (c & 1))
+__device__ __forceinline__ void tmem_ld_16x256b_x2(uint32_t (&r)[8], uint32_t taddr) {
+    asm volatile("tcgen05.ld.sync.aligned.16x256b.x2.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]) : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
 // ---- warp-level int8 MMA (SASS: IMMA.16832.S8.S8 / IMMA.16816.S8.S8) --------------------------
 //   A (row)  a0: (row g, k 4q..4q+3)  a1: (row g+8, k 4q..)  a2: (row g, k 16+4q..)  a3: (row g+8, k 16+4q..)
 //   B (col)  b0: (k 4q..4q+3, col g)  b1: (k 16+4q.., col g)

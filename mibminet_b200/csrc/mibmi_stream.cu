@@ -23,6 +23,7 @@
 #include "mibmi_common.cuh"
 #include "mibmi_kernels.h"
 #include "mibmi_ptx.cuh"
+#include "mibmi_tmap.h"
 
 namespace mibmi {
 
@@ -385,22 +386,6 @@ stream_forward_kernel(const __grid_constant__ CUtensorMap tmx, const StreamNet* 
 }
 
 // ---------------------------------------------------------------------------------------------
-typedef CUresult (*tmap_encode_t)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
-                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
-                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-static tmap_encode_t tmap_encoder() {
-    static tmap_encode_t fn = [] {
-        void* p = nullptr;
-        cudaDriverEntryPointQueryResult qr;
-        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qr) != cudaSuccess ||
-            qr != cudaDriverEntryPointSuccess)
-            p = nullptr;
-        return (tmap_encode_t)p;
-    }();
-    return fn;
-}
-
 template <int C, int T>
 static cudaError_t launch_stream_instance(const StreamNet* net_dev, bool fast1, const int8_t* x, long long S, long long L,
                                           int8_t* logits, int8_t* t2i, int8_t* t2e, int8_t* t3, int8_t* t4, int num_sms,
