@@ -32,7 +32,7 @@ ALG_BYTES_PER_TRIAL = C * T + N_CLASSES          # int8 input + 
 METRIC = "int8 edgeEEGNet trials/sec"
 # ncu (profiles/r1b_ncu_full_metrics.csv): 2.013346 GB read + 3.9255 MB written per launch of 65536 trials
 NCU_TRAFFIC_BYTES_PER_TRIAL = (2.013346e9 + 3.925504e6) / 65536
-KERNEL_NAMES = {"fused": "pipe_forward_kernel<PCfg<64,480,4>>", "fused_v1": "fused_forward_kernel<Cfg<64,480>>",
+KERNEL_NAMES = {"fused": "tc_forward_kernel<TCfg<64,480>>", "fused_pipe": "pipe_forward_kernel<PCfg<64,480,4>>", "fused_v1": "fused_forward_kernel<Cfg<64,480>>",
                 "generic": "generic_forward_kernel"}
 WORKLOAD = "edgeEEGNet int8 forward, PhysionetMMMI shape 64ch x 480 samples, 4 classes (BASELINE config 2)"
 
@@ -44,7 +44,7 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=65536, help="trials per GPU per step")
-    ap.add_argument("--path", default="auto", choices=["auto", "fused", "fused_v1", "generic"])
+    ap.add_argument("--path", default="auto", choices=["auto", "fused", "fused_pipe", "fused_v1", "generic"])
     ap.add_argument("--ctas-per-sm", type=int, default=0)
     ap.add_argument("--shape", default="64x480", help="CxT of the trials (default: BASELINE config 2; 22x1125 = config 3)")
     ap.add_argument("--workload", default="trials", choices=["trials", "stream"],

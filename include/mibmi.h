@@ -83,9 +83,11 @@ typedef struct mibmi_net mibmi_net_t; /* opaque */
 /* Kernel paths (mibmi_set_option(MIBMI_OPT_FORCE_PATH, ...), mibmi_last_path). */
 #define MIBMI_PATH_AUTO 0     /* fused tensor-core kernel when the network qualifies, else generic    */
 #define MIBMI_PATH_GENERIC 1  /* exact reference-order kernel: any shape, both reorder_bn modes, taps */
-#define MIBMI_PATH_FUSED 2    /* fused sm_100a kernel (int8 MMA + magic-number requantisation)        */
+#define MIBMI_PATH_FUSED 2    /* fused sm_100a kernel: tcgen05 / TMEM kernel where the shape has one, else  *
+                               * the mma.sync pipeline kernel (magic-number requantisation in both)          */
 #define MIBMI_PATH_FUSED_V1 3 /* round-1 homogeneous fused kernel, kept for A/B measurements          */
 
+#define MIBMI_PATH_FUSED_PIPE 5 /* force the warp-specialised mma.sync pipeline kernel (A/B measurements)   */
 #define MIBMI_PATH_STREAM 4   /* sliding-window streaming kernel (mibmi_forward_stream_int8)             */
 
 #define MIBMI_STREAM_AUTO 0    /* fused streaming kernel when it applies (hop 16, L % 16 == 0), else gather */

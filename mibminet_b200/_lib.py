@@ -16,7 +16,7 @@ from . import _build
 OK = 0
 ERR_NULL, ERR_SHAPE, ERR_PARAM, ERR_ALIGN, ERR_CUDA, ERR_UNSUPPORTED = -1, -2, -3, -4, -5, -6
 LAYOUT_BCT, LAYOUT_BTC = 0, 1
-PATH_AUTO, PATH_GENERIC, PATH_FUSED, PATH_FUSED_V1, PATH_STREAM = 0, 1, 2, 3, 4
+PATH_AUTO, PATH_GENERIC, PATH_FUSED, PATH_FUSED_V1, PATH_STREAM, PATH_FUSED_PIPE = 0, 1, 2, 3, 4, 5
 STREAM_AUTO, STREAM_FUSED, STREAM_GATHER = 0, 1, 2
 OPT_FORCE_PATH, OPT_CTAS_PER_SM, OPT_HOST_CHUNK, OPT_STREAM_MODE = 1, 2, 3, 4
 

@@ -24,7 +24,7 @@ struct mibmi_net {
     bool fused_ok = false;
     const char* fused_why = "";
     PipeNet* pipe_dev = nullptr;       // warp-specialised pipeline kernel (MIBMI_PATH_FUSED)
-    bool pipe_ok = false, pipe_fast1 = false;
+    bool pipe_ok = false, pipe_fast1 = false, tc_ok = false;
     const char* pipe_why = "";
     StreamNet* stream_dev = nullptr;   // sliding-window streaming kernel (mibmi_forward_stream_int8)
     bool stream_ok = false;
@@ -280,6 +280,12 @@ bool pack_pipe(const mibmi_params_t* p, PipeNet* f, const char** why) {
         Pooled po;
         if (!pack_pooled(128 * sum, p->l2_offset[k], p->l2_factor[k], &po, why)) return false;
         f->thr2[k] = po.thr; f->sig2[k] = po.sig; f->soff2[k] = po.soff; f->m2[k] = po.m; f->sh2[k] = po.sh;
+        for (int n = 0; n < 16; n++)
+            for (int kk = 0; kk < 96; kk++) {
+                const int tap = kk - n - 1;
+                f->w2umma[k * 1536 + (n >> 3) * 768 + (kk >> 4) * 128 + (n & 7) * 16 + (kk & 15)] =
+                    (tap >= 0 && tap < 64) ? (uint8_t)w[tap] : 0;
+            }
         for (int v = 0; v < 4; v++)
             for (int s = 0; s < 3; s++)
                 for (int h = 0; h < 2; h++)
@@ -504,14 +510,17 @@ int forward_impl(mibmi_net* net, const int8_t* x, int64_t B, int layout, int8_t*
     const bool pipe_possible = net->pipe_ok && layout == MIBMI_LAYOUT_BCT;
     const bool v1_possible = net->fused_ok && layout == MIBMI_LAYOUT_BCT && !taps;
     if (path == MIBMI_PATH_AUTO) path = (pipe_possible && !taps) ? MIBMI_PATH_FUSED : MIBMI_PATH_GENERIC;
-    if (path == MIBMI_PATH_FUSED && !pipe_possible) return MIBMI_ERR_UNSUPPORTED;
+    if ((path == MIBMI_PATH_FUSED || path == MIBMI_PATH_FUSED_PIPE) && !pipe_possible) return MIBMI_ERR_UNSUPPORTED;
     if (path == MIBMI_PATH_FUSED_V1 && !v1_possible) return MIBMI_ERR_UNSUPPORTED;
     DeviceGuard dg(net->device);
     if (dg.err != cudaSuccess) return fail_cuda(net, dg.err);
     cudaError_t e;
     PeerOut none;
     none.n = 0;
-    if (path == MIBMI_PATH_FUSED)
+    if (path == MIBMI_PATH_FUSED && net->tc_ok)
+        e = launch_tc(net->pipe_dev, net->pipe_fast1, net->C, net->T, x, B, logits, peers ? *peers : none, t1, t2, t3, t4,
+                      net->num_sms, stream);
+    else if (path == MIBMI_PATH_FUSED || path == MIBMI_PATH_FUSED_PIPE)
         e = launch_pipe(net->pipe_dev, net->pipe_fast1, net->C, net->T, x, B, logits, peers ? *peers : none, t1, t2, t3, t4,
                         net->num_sms, stream);
     else if (path == MIBMI_PATH_FUSED_V1)
@@ -519,7 +528,7 @@ int forward_impl(mibmi_net* net, const int8_t* x, int64_t B, int layout, int8_t*
     else
         e = launch_generic(net->gen_dev, net->T, net->F2, x, B, layout, logits, t1, t2, t3, t4, net->num_sms, stream);
     if (e != cudaSuccess) return fail_cuda(net, e);
-    if (peers && path != MIBMI_PATH_FUSED)      // kernels without the fused gather: peer copies on the same stream
+    if (peers && path != MIBMI_PATH_FUSED && path != MIBMI_PATH_FUSED_PIPE)      // kernels without the fused gather: peer copies on the same stream
         for (int i = 0; i < peers->n; i++) {
             e = cudaMemcpyAsync(peers->p[i], logits, (size_t)B * net->N, cudaMemcpyDefault, stream);
             if (e != cudaSuccess) return fail_cuda(net, e);
@@ -628,6 +637,7 @@ int mibmi_create(const mibmi_params_t* p, int device, mibmi_net_t** out) {
     n->fused_ok = pack_fused(p, f, &n->fused_why);
     n->pipe_ok = pack_pipe(p, pn, &n->pipe_why);
     n->pipe_fast1 = pn->fast1 != 0;
+    n->tc_ok = n->pipe_ok && tc_has_instance(p->C, p->T);
     if (n->pipe_ok) n->stream_ok = pack_stream(p, pn, sn, &n->stream_why);
     else n->stream_why = n->pipe_why;
 
@@ -684,8 +694,8 @@ int mibmi_set_option(mibmi_net_t* net, int option, int64_t value) {
     if (!net) return MIBMI_ERR_NULL;
     switch (option) {
         case MIBMI_OPT_FORCE_PATH:
-            if (value < MIBMI_PATH_AUTO || value > MIBMI_PATH_FUSED_V1) return MIBMI_ERR_PARAM;
-            if (value == MIBMI_PATH_FUSED && !net->pipe_ok) return MIBMI_ERR_UNSUPPORTED;
+            if (value < MIBMI_PATH_AUTO || value > MIBMI_PATH_FUSED_PIPE || value == MIBMI_PATH_STREAM) return MIBMI_ERR_PARAM;
+            if ((value == MIBMI_PATH_FUSED || value == MIBMI_PATH_FUSED_PIPE) && !net->pipe_ok) return MIBMI_ERR_UNSUPPORTED;
             if (value == MIBMI_PATH_FUSED_V1 && !net->fused_ok) return MIBMI_ERR_UNSUPPORTED;
             net->force_path = (int)value;
             return MIBMI_OK;

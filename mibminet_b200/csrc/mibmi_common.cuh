@@ -78,6 +78,9 @@ struct PipeNet {
     // layer 1 for tcgen05.mma: W1 [16 filters][KPAD channels] as K-major 8 x 16-byte core matrices,
     // byte (n >> 3) * (KPAD / 16) * 128 + (c >> 4) * 128 + (n & 7) * 16 + (c & 15), natural channel order
     alignas(16) uint8_t w1umma[16 * 64];
+    // layer 2 for tcgen05.mma (mibmi_tc.cu): per channel the Toeplitz operand B[n][kk] = tap (kk - n - 1) of the
+    // 64 taps, [16 outputs][96 samples] as K-major core matrices: byte (n >> 3) * 768 + (kk >> 4) * 128 + (n & 7) * 16 + (kk & 15)
+    alignas(16) uint8_t w2umma[16 * 1536];
     // layer 2: Toeplitz B fragments [channel][variant*6 + kstep*2 + half][lane]
     uint32_t w2frag[16][24][32];
     int thr2[16], sig2[16], soff2[16], m2[16], sh2[16];

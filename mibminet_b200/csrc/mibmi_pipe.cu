@@ -60,6 +60,22 @@ constexpr int kPipeThreads = (kAW + kBW + kCW + 2) * 32;   // + TMA producer war
 #ifndef MIBMI_ROTATE
 #define MIBMI_ROTATE 1
 #endif
+// experiment switches (tools/build_variant.py): role timings in isolation; results are wrong when set
+#ifdef MIBMI_EXP_SKIP_A
+#define EXP_SKIP_A && false
+#else
+#define EXP_SKIP_A
+#endif
+#ifdef MIBMI_EXP_SKIP_L2
+#define EXP_SKIP_L2 && false
+#else
+#define EXP_SKIP_L2
+#endif
+#ifdef MIBMI_EXP_SKIP_L3
+#define EXP_DO_L3 false
+#else
+#define EXP_DO_L3 true
+#endif
 #ifndef MIBMI_STAGES
 #define MIBMI_STAGES 4
 #endif
@@ -224,7 +240,7 @@ pipe_forward_kernel(const __grid_constant__ CUtensorMap tmx, const PipeNet* __re
             PWAIT(1, sbase + K::BAR_EMPTY_Y1 + 8 * buf, ((n / kNY1) & 1) ^ 1);
             const uint32_t yb = sbase + K::OFF_Y1 + buf * K::Y1_BYTES + st_off;
 #pragma unroll 1
-            for (int j = ((warp >> 2) + (MIBMI_ROTATE ? n : 0)) & 1; j < K::TILES; j += 2) {
+            for (int j = ((warp >> 2) + (MIBMI_ROTATE ? n : 0)) & 1; j < K::TILES EXP_SKIP_A; j += 2) {
                 const int u = 4 * j + qi;                        // unit of 32 samples
                 if (32 * u >= K::T) break;
                 uint32_t r[2][8];
@@ -418,7 +434,7 @@ pipe_forward_kernel(const __grid_constant__ CUtensorMap tmx, const PipeNet* __re
             PWAIT(0, sbase + K::BAR_FULL_Y1 + 8 * buf, par);
             const uint32_t ya = sbase + K::OFF_Y1 + buf * K::Y1_BYTES + l2_off;
 #pragma unroll 1
-            for (int mt = 0; mt < K::MT; mt++) {
+            for (int mt = 0; mt < K::MT EXP_SKIP_L2; mt++) {
                 int acc[4][4];
 #pragma unroll
                 for (int v = 0; v < 4; v++) acc[v][0] = acc[v][1] = acc[v][2] = acc[v][3] = 0;
@@ -446,7 +462,7 @@ pipe_forward_kernel(const __grid_constant__ CUtensorMap tmx, const PipeNet* __re
             if (lane == 0) mbar_arrive(sbase + K::BAR_EMPTY_Y1 + 8 * buf);
             PWAIT(1, sbase + K::BAR_EMPTY_Y3 + 8 * buf3, par3 ^ 1);
             // ---- layer 3
-            {
+            if (EXP_DO_L3) {
                 uint32_t a[4];
                 ldsm_x4(a, l3_addr);
                 int c3[2][4];

@@ -1,0 +1,485 @@
+// Tensor-core-resident int8 edgeEEGNet forward for sm_100a: layers 1 AND 2 run on tcgen05.mma (kind::i8) with
+// their int32 accumulators in TMEM; the warps only requantise.  (Successor of mibmi_pipe.cu for shapes whose
+// rows are 16-byte aligned; measured motivation in DESIGN.md 4.1: the mma.sync kernel is bound by the dependent
+// latency of its layer-2 warps, not by any pipe.)
+//
+// One persistent CTA per SM (23 warps) works on QUADS of 4 trials:
+//   P   warp 20   2-D TMA tiles [C][128 samples], 128-byte swizzle, 4 per trial, 3-stage ring
+//   M1  warp 21   layer 1: per tile D[128 samples x 16 filters] = Xt[128 x C] * W1t (A = the swizzled TMA tile read
+//                 MN-major, B = W1 K-major core matrices); accumulators of two trials in TMEM columns 0..127
+//                 -- edge-eegnet_wolf/src/cl/net/layer1.c:87-96
+//   A   warps 0-7 layer-1 epilogue: tcgen05.ld.16x256b (= the m16n8 fragment), + BN offset, magic division,
+//                 saturating pack, stmatrix.trans into y1[filter][32 zeros | trial | 32 zeros | trial ...]
+//   M2  warp 22   layer 2 (depthwise 64-tap conv) of a whole quad per temporal channel as 3 instructions:
+//                 D[128 rows x 16 outputs] = Hankel(y1 row)[128 x 96] * Toeplitz(taps)[96 x 16], where the Hankel
+//                 operand is the y1 byte array itself described with overlapping strides (row m = bytes 16 m ..,
+//                 LBO = 16 B, SBO = 128 B): no im2col.  Rows 32 s + i of the tile = outputs 16 i .. 16 i + 15 of the
+//                 trial in slot s; the 32 zero bytes between trials are both trials' padding
+//                 (gen_net_header.py:145-146).  TMEM columns 128 + 16 k -- layer2.c:87-118 (REORDER_BN)
+//   B   warps 8-15 layer-2 epilogue (thread = TMEM lane = 16 consecutive conv outputs = two pooling groups:
+//                 threshold, sum, requant, no shuffles), then layer 3 with mma.sync where the 16 MMA rows are the
+//                 4 trials x 4 blocks of 16 samples -- layer3.c:70
+//   C   warps 16-19 layers 4 + 5 of one trial each, as in mibmi_pipe.cu -- layer4.c:99-140, layer5.c:81-89
+// Hand-off is mbarrier-only; tcgen05.commit frees input stages / y1 buffers and publishes accumulators.
+// Bit-identical to the reference (tests/test_parity_gpu.py).
+#include <cuda.h>
+#include <string.h>
+
+#include "mibmi_common.cuh"
+#include "mibmi_kernels.h"
+#include "mibmi_ptx.cuh"
+#include "mibmi_tmap.h"
+
+namespace mibmi {
+
+constexpr int kTcAW = 8, kTcBW = 8, kTcCW = 4;
+constexpr int kTcWarpP = kTcAW + kTcBW + kTcCW, kTcWarpM1 = kTcWarpP + 1, kTcWarpM2 = kTcWarpP + 2;
+constexpr int kTcThreads = (kTcWarpM2 + 1) * 32;
+
+template <int C_, int T_>
+struct TCfg {
+    static constexpr int C = C_, T = T_, SX = 3;
+    static constexpr int TILES = (T + 127) / 128, KPAD = (C + 31) / 32 * 32, KSTEPS = KPAD / 32;
+    static constexpr int TILE_BYTES = KPAD * 128, XS_BYTES = TILES * TILE_BYTES;
+    static constexpr int T8 = T / 8, T64 = T8 / 8, ROWS = T / 16;          // layer-2 rows (16 outputs) per trial
+    static constexpr int SLOT = 512;                                        // trial pitch in a y1 row: 32 MMA rows
+    static constexpr int CHS = 32 + 8 * SLOT + 16;                          // y1 row of one filter: 2 quads; / 16 odd
+    static constexpr int NW3 = (T8 + 15) / 16;                              // layer-3 blocks of 16 samples
+    static constexpr int Y2S = 80, Y2_BUF = 4 * 16 * Y2S;
+    static constexpr int Y3S = 80, Y3_TRIAL = 16 * Y3S;
+    static constexpr int NST = (T64 + 3) / 4, T64P = (T64 + 1) / 2 * 2, KST5 = T64P / 2;
+    static constexpr int Y4_BYTES = ((16 * T64P + 15) / 16) * 16;
+    static constexpr int W2_CH = 16 * 96;                                   // Toeplitz B operand of one channel
+    // TMEM columns
+    static constexpr int TM_L1 = 0, TM_L1_TRIAL = 16 * TILES, TM_L2 = 128;
+    // barriers
+    static constexpr int BAR_FULL_X = 0, BAR_EMPTY_X = 8 * SX, BAR_T1_FULL = 16 * SX, BAR_T1_EMPTY = BAR_T1_FULL + 16,
+                         BAR_Y1_FULL = BAR_T1_EMPTY + 16, BAR_Y1_EMPTY = BAR_Y1_FULL + 16, BAR_T2_FULL = BAR_Y1_EMPTY + 16,
+                         BAR_T2_EMPTY = BAR_T2_FULL + 16, BAR_Y2_FULL = BAR_T2_EMPTY + 16, BAR_Y3_FULL = BAR_Y2_FULL + 16,
+                         BAR_Y3_EMPTY = BAR_Y3_FULL + 16, BAR_END = BAR_Y3_EMPTY + 16;
+    // shared memory map
+    static constexpr int OFF_TMEM = 248;
+    static constexpr int OFF_C2 = 256;                                      // int [16][8]: thr, sig, soff, m, sh
+    static constexpr int OFF_W1 = 1024;
+    static constexpr int OFF_W2 = 2048;
+    static constexpr int OFF_XS = ((OFF_W2 + 16 * W2_CH + 1023) / 1024) * 1024;
+    static constexpr int OFF_Y1 = OFF_XS + SX * XS_BYTES;
+    static constexpr int OFF_Y2 = OFF_Y1 + 16 * CHS;
+    static constexpr int OFF_Y3 = OFF_Y2 + 2 * Y2_BUF;
+    static constexpr int OFF_Y4 = OFF_Y3 + 8 * Y3_TRIAL;
+    static constexpr int SMEM = ((OFF_Y4 + kTcCW * Y4_BYTES + 127) / 128) * 128;
+    static_assert(T % 32 == 0 && T <= SLOT - 32, "trial fits a 512-byte slot with 32 zero bytes");
+    static_assert(TM_L1 + 2 * TM_L1_TRIAL <= TM_L2, "TMEM map");
+    static_assert(NW3 <= 4, "layer 3: 4 trials x 4 blocks fill the 16 MMA rows");
+    static_assert(KST5 <= 4, "classifier fragments live in registers");
+    static_assert(BAR_END <= OFF_TMEM && 16 * KPAD <= 1024, "barrier / W1 area");
+    static_assert(SMEM <= 227 * 1024, "shared memory");
+};
+
+template <bool FAST>
+__device__ __forceinline__ int tc_div1(int x, int m, int s) {
+    if (FAST) return __mulhi(x, m) + (int)((unsigned)x >> 31);
+    return (__mulhi(x, m) >> s) + (int)((unsigned)x >> 31);
+}
+
+__device__ __forceinline__ void tmem_ld_32x32b_x16(uint32_t (&r)[16], uint32_t taddr) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+                   "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]) : "r"(taddr));
+}
+// instruction descriptor with both operands K-major (layer 2)
+__device__ __forceinline__ constexpr uint32_t umma_idesc_i8_kk(int M, int N) {
+    return (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+template <class K, bool FAST1, bool TAPS>
+__global__ void __launch_bounds__(kTcThreads, 1)
+tc_forward_kernel(const __grid_constant__ CUtensorMap tmx, const PipeNet* __restrict__ net, long long B,
+                  int8_t* __restrict__ logits, const PeerOut peers, int8_t* __restrict__ tap1, int8_t* __restrict__ tap2,
+                  int8_t* __restrict__ tap3, int8_t* __restrict__ tap4) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int g = lane >> 2, q = lane & 3;
+    const uint32_t sbase = smem_u32(smem);
+    const long long nquads_total = (B + 3) / 4;
+    const long long firstq = blockIdx.x, strideq = gridDim.x;
+    const int nq = firstq < nquads_total ? (int)((nquads_total - firstq + strideq - 1) / strideq) : 0;   // quads of this CTA
+    const int ntr = 4 * nq;                                                                               // trial slots
+
+    // ---- prologue ------------------------------------------------------------------------------------
+    if (tid == 0) {
+        for (int s = 0; s < K::SX; s++) {
+            mbar_init(sbase + K::BAR_FULL_X + 8 * s, 1);
+            mbar_init(sbase + K::BAR_EMPTY_X + 8 * s, 1);            // tcgen05.commit of M1
+        }
+        for (int i = 0; i < 2; i++) {
+            mbar_init(sbase + K::BAR_T1_FULL + 8 * i, 1);            // commit of M1
+            mbar_init(sbase + K::BAR_T1_EMPTY + 8 * i, kTcAW);
+            mbar_init(sbase + K::BAR_Y1_FULL + 8 * i, 4 * kTcAW);    // 4 trials x 8 layer-1 warps
+            mbar_init(sbase + K::BAR_Y1_EMPTY + 8 * i, 1);           // commit of M2
+            mbar_init(sbase + K::BAR_T2_FULL + 8 * i, 1);            // commit of M2 (per half of the channels)
+            mbar_init(sbase + K::BAR_T2_EMPTY + 8 * i, kTcBW / 2);
+            mbar_init(sbase + K::BAR_Y2_FULL + 8 * i, kTcBW);
+            mbar_init(sbase + K::BAR_Y3_FULL + 8 * i, kTcBW);
+            mbar_init(sbase + K::BAR_Y3_EMPTY + 8 * i, kTcCW);
+        }
+        mbar_fence_init();
+    }
+    for (int i = tid; i < 16 * K::KPAD / 4; i += kTcThreads)
+        reinterpret_cast<uint32_t*>(smem + K::OFF_W1)[i] = reinterpret_cast<const uint32_t*>(net->w1umma)[i];
+    for (int i = tid; i < 16 * K::W2_CH / 16; i += kTcThreads)
+        reinterpret_cast<uint4*>(smem + K::OFF_W2)[i] = reinterpret_cast<const uint4*>(net->w2umma)[i];
+    for (int i = tid; i < 16 * 8; i += kTcThreads) {
+        const int k = i >> 3, f = i & 7;
+        reinterpret_cast<int*>(smem + K::OFF_C2)[i] = f == 0 ? net->thr2[k] : f == 1 ? net->sig2[k] : f == 2 ? net->soff2[k]
+                                                      : f == 3 ? net->m2[k] : f == 4 ? net->sh2[k] : 0;
+    }
+    {
+        uint4* z = reinterpret_cast<uint4*>(smem + K::OFF_Y1);     // zero gaps of y1, y2 / y3 padding
+        for (int i = tid; i < (K::SMEM - K::OFF_Y1) / 16; i += kTcThreads) z[i] = make_uint4(0, 0, 0, 0);
+    }
+    if (warp == kTcWarpM1) tmem_alloc(sbase + K::OFF_TMEM, 512);
+    fence_proxy_async();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *reinterpret_cast<const uint32_t*>(smem + K::OFF_TMEM);
+
+    if (warp < kTcAW) {
+        // =====================================================================================
+        // A: layer-1 epilogue.  TMEM lanes 32 (warp & 3) .. + 31 of tiles jb, jb + 2
+        // =====================================================================================
+        int off1[2][2], mg1[2][2], sh1[2][2];
+#pragma unroll
+        for (int nt = 0; nt < 2; nt++)
+#pragma unroll
+            for (int e = 0; e < 2; e++) {
+                off1[nt][e] = net->off1[8 * nt + 2 * q + e];
+                mg1[nt][e] = net->m1[8 * nt + 2 * q + e];
+                sh1[nt][e] = net->sh1[8 * nt + 2 * q + e];
+            }
+        // stmatrix.trans: matrix j = lane >> 3 = 2 mt + nt: filters 8 nt .. + 7 (rows), samples 16 mt .. + 15
+        const uint32_t st_off = sbase + K::OFF_Y1 + ((lane & 7) + 8 * ((lane >> 3) & 1)) * K::CHS + 16 * (lane >> 4) + 32;
+        const int qi = warp & 3;
+        for (int n = 0; n < ntr; n++) {
+            const int gq = n >> 2, s = n & 3, buf = gq & 1, ab = n & 1;
+            mbar_wait(sbase + K::BAR_T1_FULL + 8 * ab, (n >> 1) & 1);
+            tc_fence_after();
+            if (s == 0) mbar_wait(sbase + K::BAR_Y1_EMPTY + 8 * buf, ((gq >> 1) & 1) ^ 1);
+            const uint32_t yb = st_off + K::SLOT * (4 * buf + s);
+#pragma unroll 1
+            for (int j = ((warp >> 2) + n) & 1; j < K::TILES; j += 2) {
+                const int u = 4 * j + qi;
+                if (32 * u >= K::T) break;
+                uint32_t r[2][8];
+                const uint32_t ta = tmem_base + ((uint32_t)(32 * qi) << 16) + K::TM_L1 + ab * K::TM_L1_TRIAL + 16 * j;
+                tmem_ld_16x256b_x2(r[0], ta);
+                tmem_ld_16x256b_x2(r[1], ta + (16u << 16));
+                tmem_ld_wait();
+                uint32_t w[2][2];
+#pragma unroll
+                for (int mt = 0; mt < 2; mt++)
+#pragma unroll
+                    for (int nt = 0; nt < 2; nt++) {
+                        int v[4];
+#pragma unroll
+                        for (int c = 0; c < 4; c++)
+                            v[c] = tc_div1<FAST1>((int)r[mt][4 * nt + c] + off1[nt][c & 1], mg1[nt][c & 1], sh1[nt][c & 1]);
+                        w[mt][nt] = pack4_sat(v[0], v[1], v[2], v[3]);
+                        if (TAPS && tap1) {
+                            const long long b = 4 * (firstq + (long long)gq * strideq) + s;
+                            if (b < B)
+#pragma unroll
+                                for (int c = 0; c < 4; c++) {
+                                    const int f = 8 * nt + 2 * q + (c & 1), t = 32 * u + 16 * mt + g + 8 * (c >> 1);
+                                    tap1[((size_t)b * 16 + f) * K::T + t] = (int8_t)clip8(v[c]);
+                                }
+                        }
+                    }
+                stsm_t8_x4(yb + 32 * u, w[0][0], w[0][1], w[1][0], w[1][1]);
+            }
+            tc_fence_before();
+            fence_proxy_async();          // y1 is read by the tensor core (async proxy)
+            __syncwarp();
+            if (lane == 0) {
+                mbar_arrive(sbase + K::BAR_T1_EMPTY + 8 * ab);
+                mbar_arrive(sbase + K::BAR_Y1_FULL + 8 * buf);
+            }
+        }
+    } else if (warp == kTcWarpP) {
+        // =====================================================================================
+        // P: TMA producer
+        // =====================================================================================
+        if (lane == 0) {
+            auto issue = [&](int st, int n) {
+                const long long b = 4 * (firstq + (long long)(n >> 2) * strideq) + (n & 3);   // b >= B: zero filled
+                const uint32_t dst = sbase + K::OFF_XS + st * K::XS_BYTES;
+                const uint32_t bar = sbase + K::BAR_FULL_X + 8 * st;
+                mbar_expect_tx(bar, K::TILES * K::C * 128);
+#pragma unroll
+                for (int j = 0; j < K::TILES; j++) tma_load_2d(dst + j * K::TILE_BYTES, &tmx, 128 * j, (int)(b * K::C), bar);
+            };
+            for (int s = 0; s < K::SX && s < ntr; s++) issue(s, s);
+            for (int n = 0; n + K::SX < ntr; n++) {
+                const int st = n % K::SX;
+                mbar_wait(sbase + K::BAR_EMPTY_X + 8 * st, (n / K::SX) & 1);
+                issue(st, n + K::SX);
+            }
+        }
+    } else if (warp == kTcWarpM1) {
+        // =====================================================================================
+        // M1: layer-1 MMAs, TILES x KSTEPS per trial
+        // =====================================================================================
+        if (lane == 0) {
+            constexpr uint32_t idesc = umma_idesc_i8(128, 16);
+            for (int n = 0; n < ntr; n++) {
+                const int st = n % K::SX, ab = n & 1;
+                mbar_wait(sbase + K::BAR_FULL_X + 8 * st, (n / K::SX) & 1);
+                mbar_wait(sbase + K::BAR_T1_EMPTY + 8 * ab, ((n >> 1) & 1) ^ 1);
+                tc_fence_after();
+                const uint32_t xs = sbase + K::OFF_XS + st * K::XS_BYTES;
+#pragma unroll
+                for (int j = 0; j < K::TILES; j++)
+#pragma unroll
+                    for (int ks = 0; ks < K::KSTEPS; ks++)
+                        umma_i8(tmem_base + K::TM_L1 + ab * K::TM_L1_TRIAL + 16 * j,
+                                umma_desc(xs + j * K::TILE_BYTES + ks * 4096, 16, 1024, 2),
+                                umma_desc(sbase + K::OFF_W1 + ks * 256, 128, K::KSTEPS * 256, 0), idesc, ks > 0);
+                umma_commit(sbase + K::BAR_EMPTY_X + 8 * st);
+                umma_commit(sbase + K::BAR_T1_FULL + 8 * ab);
+            }
+        }
+    } else if (warp == kTcWarpM2) {
+        // =====================================================================================
+        // M2: layer-2 MMAs of a quad: per channel 3 x (M = 128 rows, N = 16 outputs, K = 32 samples)
+        // =====================================================================================
+        if (lane == 0) {
+            constexpr uint32_t idesc = umma_idesc_i8_kk(128, 16);
+            for (int gq = 0; gq < nq; gq++) {
+                const int buf = gq & 1;
+                mbar_wait(sbase + K::BAR_Y1_FULL + 8 * buf, (gq >> 1) & 1);
+                tc_fence_after();
+#pragma unroll 1
+                for (int h = 0; h < 2; h++) {
+                    mbar_wait(sbase + K::BAR_T2_EMPTY + 8 * h, (gq & 1) ^ 1);
+                    tc_fence_after();
+#pragma unroll 1
+                    for (int k = 8 * h; k < 8 * h + 8; k++)
+#pragma unroll
+                        for (int ks = 0; ks < 3; ks++)
+                            umma_i8(tmem_base + K::TM_L2 + 16 * k,
+                                    umma_desc(sbase + K::OFF_Y1 + k * K::CHS + 4 * K::SLOT * buf + 32 * ks, 16, 128, 0),
+                                    umma_desc(sbase + K::OFF_W2 + k * K::W2_CH + 256 * ks, 128, 768, 0), idesc, ks > 0);
+                    umma_commit(sbase + K::BAR_T2_FULL + 8 * h);
+                }
+                umma_commit(sbase + K::BAR_Y1_EMPTY + 8 * buf);
+            }
+        }
+    } else if (warp < kTcAW + kTcBW) {
+        // =====================================================================================
+        // B: layer-2 epilogue of (trial slot = warp & 3, channels 8 h .. 8 h + 7), then layer 3 of two channels
+        // =====================================================================================
+        const int wb = warp - kTcAW, s = warp & 3, h = wb >> 2;
+        const int lrow = (lane & 7) + 8 * ((lane >> 3) & 1);
+        uint32_t b3[2][2][2];
+#pragma unroll
+        for (int c = 0; c < 2; c++)
+#pragma unroll
+            for (int v = 0; v < 2; v++)
+#pragma unroll
+                for (int hh = 0; hh < 2; hh++) b3[c][v][hh] = net->w3frag[2 * wb + c][v * 2 + hh][lane];
+        const int m3 = net->m3, sh3 = net->sh3;
+        const int4* c2 = reinterpret_cast<const int4*>(smem + K::OFF_C2);
+        for (int gq = 0; gq < nq; gq++) {
+            const int buf = gq & 1, par = (gq >> 1) & 1;
+            const long long b0 = 4 * (firstq + (long long)gq * strideq);
+            // ---- layer 2: thread = row `lane` of slot s: conv outputs 16 lane .. 16 lane + 15 of 8 channels
+            mbar_wait(sbase + K::BAR_T2_FULL + 8 * h, gq & 1);
+            tc_fence_after();
+            uint8_t* y2s = smem + K::OFF_Y2 + buf * K::Y2_BUF + s * (16 * K::Y2S) + 8 + 2 * lane;
+#pragma unroll 2
+            for (int kk = 0; kk < 8; kk++) {
+                const int k = 8 * h + kk;
+                uint32_t r[16];
+                tmem_ld_32x32b_x16(r, tmem_base + ((uint32_t)(32 * s) << 16) + K::TM_L2 + 16 * k);
+                const int4 ca = c2[2 * k];                       // thr, sig, soff, m
+                const int shk = reinterpret_cast<const int*>(smem + K::OFF_C2)[8 * k + 4];
+                tmem_ld_wait();
+                int s0 = 0, s1 = 0;
+#pragma unroll
+                for (int i = 0; i < 8; i++) {
+                    s0 += max((int)r[i], ca.x);
+                    s1 += max((int)r[8 + i], ca.x);
+                }
+                const int o0 = clip8(tdiv_magic(s0 * ca.y + ca.z, ca.w, shk));
+                const int o1 = clip8(tdiv_magic(s1 * ca.y + ca.z, ca.w, shk));
+                if (lane < K::ROWS) {
+                    *reinterpret_cast<uint16_t*>(y2s + k * K::Y2S) = (uint16_t)((o0 & 0xff) | ((o1 & 0xff) << 8));
+                    if (TAPS && tap2 && b0 + s < B) {
+                        int8_t* o = tap2 + ((size_t)(b0 + s) * 16 + k) * K::T8 + 2 * lane;
+                        o[0] = (int8_t)o0;
+                        o[1] = (int8_t)o1;
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) {
+                mbar_arrive(sbase + K::BAR_T2_EMPTY + 8 * h);
+                mbar_arrive(sbase + K::BAR_Y2_FULL + 8 * buf);
+            }
+            // ---- layer 3 of channels 2 wb, 2 wb + 1: MMA row r = 4 slot + block of 16 samples
+            mbar_wait(sbase + K::BAR_Y2_FULL + 8 * buf, par);
+            mbar_wait(sbase + K::BAR_Y3_EMPTY + 8 * buf, par ^ 1);
+#pragma unroll
+            for (int c = 0; c < 2; c++) {
+                const int k = 2 * wb + c;
+                uint32_t a[4];
+                ldsm_x4(a, sbase + K::OFF_Y2 + buf * K::Y2_BUF + ((lrow >> 2) * 16 + k) * K::Y2S + 16 * (lrow & 3) + 16 * (lane >> 4));
+                int c3[2][4];
+#pragma unroll
+                for (int v = 0; v < 2; v++) {
+                    c3[v][0] = c3[v][1] = c3[v][2] = c3[v][3] = 0;
+                    mma_k32(c3[v], a, b3[c][v][0], b3[c][v][1]);
+                }
+#pragma unroll
+                for (int hf = 0; hf < 2; hf++) {
+                    const int row = g + 8 * hf, sl = row >> 2, i = row & 3;          // trial slot, block of 16 samples
+                    uint8_t* y3b = smem + K::OFF_Y3 + (4 * buf + sl) * K::Y3_TRIAL + k * K::Y3S + 16 * (q >> 1) + 8 * (q & 1) +
+                                   32 * (i >> 1) + 4 * (i & 1);
+#pragma unroll
+                    for (int v = 0; v < 2; v++) {
+                        const int t = 16 * i + 8 * v + 2 * q;
+                        const uint32_t w = pack2_sat(tdiv_magic(c3[v][2 * hf], m3, sh3), tdiv_magic(c3[v][2 * hf + 1], m3, sh3));
+                        if (t < K::T8) {
+                            *reinterpret_cast<uint16_t*>(y3b + 2 * v) = (uint16_t)w;
+                            if (TAPS && tap3 && b0 + sl < B) {
+                                int8_t* o = tap3 + ((size_t)(b0 + sl) * 16 + k) * K::T8 + t;
+                                o[0] = (int8_t)(w & 0xff);
+                                o[1] = (int8_t)((w >> 8) & 0xff);
+                            }
+                        }
+                    }
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(sbase + K::BAR_Y3_FULL + 8 * buf);
+        }
+    } else if (warp < kTcAW + kTcBW + kTcCW) {
+        // =====================================================================================
+        // C: layers 4 + 5 of the trial in slot (warp & 3) of every quad
+        // =====================================================================================
+        const int sl = warp & 3, cj = warp - (kTcAW + kTcBW);
+        const uint32_t w4a0 = net->w4frag[0][lane], w4a1 = net->w4frag[1][lane];
+        const int thr_lo = net->thr4[g], thr_hi = net->thr4[g + 8];
+        const int sig_lo = net->sig4[g], sig_hi = net->sig4[g + 8];
+        const int soff_lo = net->soff4[g], soff_hi = net->soff4[g + 8];
+        const int m4_lo = net->m4[g], m4_hi = net->m4[g + 8], sh4_lo = net->sh4[g], sh4_hi = net->sh4[g + 8];
+        const int b5 = net->b5[g & 3], m5 = net->m5, sh5 = net->sh5;
+        const uint32_t l4_off = (lane & 15) * K::Y3S + 16 * (lane >> 4);
+        uint8_t* y4 = smem + K::OFF_Y4 + cj * K::Y4_BYTES;
+        uint32_t w5a[K::KST5][2];
+#pragma unroll
+        for (int ks = 0; ks < K::KST5; ks++) { w5a[ks][0] = net->w5frag[ks][0][lane]; w5a[ks][1] = net->w5frag[ks][1][lane]; }
+        const uint32_t* y4w = reinterpret_cast<const uint32_t*>(y4);
+        for (int gq = 0; gq < nq; gq++) {
+            const int buf = gq & 1, par = (gq >> 1) & 1;
+            const long long b = 4 * (firstq + (long long)gq * strideq) + sl;
+            mbar_wait(sbase + K::BAR_Y3_FULL + 8 * buf, par);
+            const uint32_t y3a = sbase + K::OFF_Y3 + (4 * buf + sl) * K::Y3_TRIAL + l4_off;
+#pragma unroll
+            for (int s4 = 0; s4 < K::NST; s4++) {
+                uint32_t d[4];
+                ldsm_t_x2(d, y3a + 32 * s4);
+                int c[4][4];
+#pragma unroll
+                for (int v = 0; v < 4; v++) {
+                    c[v][0] = c[v][1] = c[v][2] = c[v][3] = 0;
+                    mma_k16(c[v], w4a0, w4a1, d[v]);
+                }
+                int s_lo = 0, s_hi = 0;
+#pragma unroll
+                for (int v = 0; v < 4; v++) {
+                    s_lo += max(c[v][0], thr_lo) + max(c[v][1], thr_lo);
+                    s_hi += max(c[v][2], thr_hi) + max(c[v][3], thr_hi);
+                }
+                const int grp = 4 * s4 + q;
+                const int o_lo = clip8(tdiv_magic(s_lo * sig_lo + soff_lo, m4_lo, sh4_lo));
+                const int o_hi = clip8(tdiv_magic(s_hi * sig_hi + soff_hi, m4_hi, sh4_hi));
+                if (grp < K::T64) {
+                    y4[g * K::T64P + grp] = (uint8_t)o_lo;
+                    y4[(g + 8) * K::T64P + grp] = (uint8_t)o_hi;
+                    if (TAPS && tap4 && b < B) {
+                        tap4[((size_t)b * 16 + g) * K::T64 + grp] = (int8_t)o_lo;
+                        tap4[((size_t)b * 16 + g + 8) * K::T64 + grp] = (int8_t)o_hi;
+                    }
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(sbase + K::BAR_Y3_EMPTY + 8 * buf);
+            int z[4] = {0, 0, 0, 0};
+#pragma unroll
+            for (int ks = 0; ks < K::KST5; ks++) {
+                const uint32_t a[4] = {w5a[ks][0], 0u, w5a[ks][1], 0u};
+                const uint32_t bb0 = g == 0 ? y4w[8 * ks + q] : 0u, bb1 = g == 0 ? y4w[8 * ks + 4 + q] : 0u;
+                mma_k32(z, a, bb0, bb1);
+            }
+            if (q == 0 && g < 4 && b < B) {
+                const int8_t o = (int8_t)clip8(tdiv_magic(z[0] + b5, m5, sh5));
+                logits[(size_t)b * 4 + g] = o;
+                for (int i = 0; i < peers.n; i++) peers.p[i][(size_t)b * 4 + g] = o;    // fused all-gather (NVLink P2P)
+            }
+            __syncwarp();
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == kTcWarpM1) tmem_dealloc(tmem_base, 512);
+}
+
+// ---------------------------------------------------------------------------------------------
+template <int C, int T>
+static cudaError_t launch_tc_instance(const PipeNet* net_dev, bool fast1, const int8_t* x, long long B, int8_t* logits,
+                                      const PeerOut& peers, int8_t* t1, int8_t* t2, int8_t* t3, int8_t* t4, int num_sms,
+                                      cudaStream_t stream) {
+    using K = TCfg<C, T>;
+    tmap_encode_t enc = tmap_encoder();
+    if (!enc) return cudaErrorNotSupported;
+    CUtensorMap tm;
+    cuuint64_t dims[2] = {(cuuint64_t)T, (cuuint64_t)(B * C)};
+    cuuint64_t strides[1] = {(cuuint64_t)T};
+    cuuint32_t box[2] = {128, (cuuint32_t)C};
+    cuuint32_t estr[2] = {1, 1};
+    if (enc(&tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<int8_t*>(x), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+            CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+        return cudaErrorInvalidValue;
+    const bool taps = t1 || t2 || t3 || t4;
+    auto kern = taps ? tc_forward_kernel<K, false, true>
+                     : (fast1 ? tc_forward_kernel<K, true, false> : tc_forward_kernel<K, false, false>);
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, K::SMEM);
+    if (e != cudaSuccess) return e;
+    long long grid = num_sms;
+    const long long quads = (B + 3) / 4;
+    if (grid > quads) grid = quads;
+    kern<<<(unsigned)grid, kTcThreads, K::SMEM, stream>>>(tm, net_dev, B, logits, peers, t1, t2, t3, t4);
+    return cudaGetLastError();
+}
+
+#define MIBMI_TC_SHAPES(X) X(64, 480) X(38, 480) X(24, 480) X(19, 480) X(16, 480) X(8, 480)
+
+bool tc_has_instance(int C, int T) {
+#define X(c, t) if (C == c && T == t) return true;
+    MIBMI_TC_SHAPES(X)
+#undef X
+    return false;
+}
+
+cudaError_t launch_tc(const PipeNet* net_dev, bool fast1, int C, int T, const int8_t* x, long long B, int8_t* logits,
+                      const PeerOut& peers, int8_t* t1, int8_t* t2, int8_t* t3, int8_t* t4, int num_sms, cudaStream_t stream) {
+#define X(c, t) if (C == c && T == t) return launch_tc_instance<c, t>(net_dev, fast1, x, B, logits, peers, t1, t2, t3, t4, num_sms, stream);
+    MIBMI_TC_SHAPES(X)
+#undef X
+    return cudaErrorInvalidValue;
+}
+
+}  // namespace mibmi

@@ -20,7 +20,7 @@ from .convert import WolfParams, align4, params_from_export, params_from_state_d
 
 _LAYOUTS = {"bct": _lib.LAYOUT_BCT, "btc": _lib.LAYOUT_BTC}
 _PATHS = {"auto": _lib.PATH_AUTO, "generic": _lib.PATH_GENERIC, "fused": _lib.PATH_FUSED,
-          "fused_v1": _lib.PATH_FUSED_V1}
+          "fused_v1": _lib.PATH_FUSED_V1, "fused_pipe": _lib.PATH_FUSED_PIPE}
 _PATH_NAMES = {v: k for k, v in _PATHS.items()}
 _PATH_NAMES[_lib.PATH_STREAM] = "stream"
 _STREAM_MODES = {"auto": _lib.STREAM_AUTO, "fused": _lib.STREAM_FUSED, "gather": _lib.STREAM_GATHER}

@@ -97,6 +97,50 @@ probe(const __grid_constant__ CUtensorMap tm, const int8_t* __restrict__ w1, int
     if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 32;" ::"r"(tmem));
 }
 
+// throughput: `reps` back-to-back tcgen05.mma (M = 128, N = n, K = 32, i8) from one thread, then one commit
+__global__ void __launch_bounds__(128, 1) timing(int reps, int n, long long* cyc) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    __shared__ __align__(8) unsigned long long bar;
+    __shared__ uint32_t tmem_base_s;
+    const int tid = threadIdx.x, warp = tid >> 5;
+    for (int i = tid; i < 16384 / 4; i += 128) reinterpret_cast<uint32_t*>(smem)[i] = 0x01010101u * (i & 3);
+    if (tid == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(s32(&bar)));
+        asm volatile("fence.mbarrier_init.release.cluster;");
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(s32(&tmem_base_s)));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    asm volatile("tcgen05.fence::before_thread_sync;");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;");
+    const uint32_t tmem = tmem_base_s;
+    if (tid == 0) {
+        const uint32_t idesc = (2u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | ((uint32_t)(n >> 3) << 17) | ((128u >> 4) << 24);
+        const uint64_t da = (uint64_t)((s32(smem) >> 4) & 0x3fff) | ((uint64_t)1 << 16) | ((uint64_t)(1024 >> 4) << 32) | ((uint64_t)1 << 46) | ((uint64_t)2 << 61);
+        const uint64_t db = (uint64_t)(((s32(smem) + 8192) >> 4) & 0x3fff) | ((uint64_t)(128 >> 4) << 16) | ((uint64_t)(256 >> 4) << 32) | ((uint64_t)1 << 46);
+        const long long t0 = clock64();
+        for (int i = 0; i < reps; i++) {
+            const uint32_t d = tmem + (uint32_t)((i & 3) * 64);          // 4 independent accumulators
+            asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                         "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%5, %5, %5, %5}, p;\n\t}"
+                         ::"r"(d), "l"(da), "l"(db), "r"(idesc), "r"(1u), "r"(0u) : "memory");
+        }
+        const long long t1 = clock64();
+        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.b64 [%0];" ::"r"(s32(&bar)) : "memory");
+        uint32_t done = 0;
+        while (!done)
+            asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(done) : "r"(s32(&bar)));
+        const long long t2 = clock64();
+        cyc[0] = t1 - t0; cyc[1] = t2 - t0;
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;");
+    __syncthreads();
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem));
+}
+
 int main(int argc, char** argv) {
     const int C = 64, L = 128;
     int8_t hx[C * L], hw[16 * C];
@@ -135,6 +179,19 @@ int main(int argc, char** argv) {
         int t = (first / 16), f = i; int ref = 0;
         for (int c = 0; c < C; c++) ref += (int)hx[c * L + t] * (int)hw[f * C + c];
         printf("  t=%d f=%d got=%d ref=%d\n", t, f, ho[t * 16 + f], ref);
+    }
+    {
+        long long* dc; cudaMalloc(&dc, 16);
+        cudaFuncSetAttribute(timing, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384);
+        const int ns[] = {16, 32, 64, 128, 256};
+        for (int ni = 0; ni < 5; ni++)
+            for (int reps = 64; reps <= 1024; reps *= 4) {
+                timing<<<1, 128, 16384>>>(reps, ns[ni], dc);
+                cudaError_t e2 = cudaDeviceSynchronize();
+                long long hc[2]; cudaMemcpy(hc, dc, 16, cudaMemcpyDeviceToHost);
+                printf("N=%3d reps=%4d err=%d: issue %.1f cycles/MMA, complete %.1f cycles/MMA\n", ns[ni], reps, (int)e2,
+                       (double)hc[0] / reps, (double)hc[1] / reps);
+            }
     }
     return 0;
 }

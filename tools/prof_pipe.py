@@ -6,7 +6,9 @@ from mibminet_b200 import convert, synth, _lib
 from mibminet_b200.engine import Int8Net
 C, T = (int(sys.argv[1]), int(sys.argv[2])) if len(sys.argv) > 2 else (64, 480)
 B = 65536
+PATH = os.environ.get('MIBMI_PATH', 'auto')
 net = Int8Net(convert.params_from_state_dict(synth.make_state_dict(C=C, T=T, seed=0), C=C, T=T), device='cuda:0')
+net.set_path(PATH)
 g = torch.Generator(device='cuda'); g.manual_seed(5)
 x = torch.randint(-127, 128, (B, C, T), dtype=torch.int8, device='cuda', generator=g)
 for _ in range(3):
