@@ -31,6 +31,11 @@ __device__ __forceinline__ bool mbar_test(uint32_t bar, uint32_t parity) {
         : "=r"(done) : "r"(bar), "r"(parity) : "memory");
     return done != 0;
 }
+// suspend-time hint of try_wait: a waiting warp sleeps in hardware (no issue slots) until the phase completes
+// or the hint expires, instead of spinning through the scheduler
+#ifndef MIBMI_WAIT_HINT_NS
+#define MIBMI_WAIT_HINT_NS 20000u
+#endif
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     // test_wait first: a phase that has already completed costs one probe instead of the (suspending)
     // try_wait round trip -- measured +3 % on the whole kernel
@@ -39,10 +44,18 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     for (uint32_t spins = 0; !done; ++spins) {
         asm volatile(
             "{\n\t.reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
             "selp.u32 %0, 1, 0, p;\n\t}"
-            : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+            : "=r"(done) : "r"(bar), "r"(parity), "r"(MIBMI_WAIT_HINT_NS) : "memory");
         if (spins > (1u << 22)) __trap();   // never hang the box: a lost arrival becomes a launch failure
+    }
+}
+// same with a sleep between probes: for roles that wait most of the time (their polling would otherwise take
+// issue slots from the working warps)
+__device__ __forceinline__ void mbar_wait_sleep(uint32_t bar, uint32_t parity, uint32_t ns) {
+    for (uint32_t spins = 0; !mbar_test(bar, parity); ++spins) {
+        __nanosleep(ns);
+        if (spins > (1u << 24)) __trap();
     }
 }
 // TMA bulk copy global -> shared, completion counted in bytes on an mbarrier (SASS: UBLKCP)
@@ -85,6 +98,21 @@ __device__ __forceinline__ void umma_i8(uint32_t tmem_d, uint64_t desc_a, uint64
     asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
                  "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%5, %5, %5, %5}, p;\n\t}"
                  ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate), "r"(0u) : "memory");
+}
+// same with the descriptors given as (low word, high word): the issuing thread only adds to the low word
+// (start-address field, units of 16 bytes) between instructions
+__device__ __forceinline__ void umma_i8_lohi(uint32_t tmem_d, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi,
+                                             uint32_t idesc, uint32_t accumulate) {
+    asm volatile("{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\tsetp.ne.b32 p, %6, 0;\n\t"
+                 "mov.b64 da, {%1, %2};\n\tmov.b64 db, {%3, %4};\n\t"
+                 "tcgen05.mma.cta_group::1.kind::i8 [%0], da, db, %5, {%7, %7, %7, %7}, p;\n\t}"
+                 ::"r"(tmem_d), "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate), "r"(0u) : "memory");
+}
+// one lane of a converged warp (the warp keeps warp-uniform control flow around the tcgen05 issue)
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.b32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred != 0;
 }
 // arrive on an mbarrier when every tcgen05.mma issued so far by this thread has completed (SASS: UTCBAR)
 __device__ __forceinline__ void umma_commit(uint32_t bar) {

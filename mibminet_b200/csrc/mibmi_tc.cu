@@ -32,6 +32,21 @@
 
 namespace mibmi {
 
+#ifndef MIBMI_TC_SLEEP_NS
+#define MIBMI_TC_SLEEP_NS 64
+#endif
+#ifdef MIBMI_PROF
+__device__ long long g_prof_tc[148 * 32 * 4];
+#define TWAIT(slot, ...) do { if (!mbar_test(__VA_ARGS__)) { const long long t0_ = clock64(); mbar_wait_sleep(__VA_ARGS__, MIBMI_TC_SLEEP_NS); pw_[slot] += clock64() - t0_; } } while (0)
+#define TPROF_BEGIN long long pw_[3] = {0, 0, 0}; const long long pt0_ = clock64();
+#define TPROF_END if ((threadIdx.x & 31) == 0) { long long* o_ = g_prof_tc + (blockIdx.x * 32 + (threadIdx.x >> 5)) * 4; \
+    o_[0] = clock64() - pt0_; o_[1] = pw_[0]; o_[2] = pw_[1]; o_[3] = pw_[2]; }
+#else
+#define TWAIT(slot, ...) mbar_wait_sleep(__VA_ARGS__, MIBMI_TC_SLEEP_NS)
+#define TPROF_BEGIN
+#define TPROF_END
+#endif
+
 constexpr int kTcAW = 8, kTcBW = 8, kTcCW = 4;
 constexpr int kTcWarpP = kTcAW + kTcBW + kTcCW, kTcWarpM1 = kTcWarpP + 1, kTcWarpM2 = kTcWarpP + 2;
 constexpr int kTcThreads = (kTcWarpM2 + 1) * 32;
@@ -120,8 +135,7 @@ tc_forward_kernel(const __grid_constant__ CUtensorMap tmx, const PipeNet* __rest
             mbar_init(sbase + K::BAR_T2_FULL + 8 * i, 1);            // commit of M2 (per half of the channels)
             mbar_init(sbase + K::BAR_T2_EMPTY + 8 * i, kTcBW / 2);
             mbar_init(sbase + K::BAR_Y2_FULL + 8 * i, kTcBW);
-            mbar_init(sbase + K::BAR_Y3_FULL + 8 * i, kTcBW);
-            mbar_init(sbase + K::BAR_Y3_EMPTY + 8 * i, kTcCW);
+            mbar_init(sbase + K::BAR_Y3_EMPTY + 8 * i, kTcCW);       // "y2 buffer consumed by layer 3"
         }
         mbar_fence_init();
     }
@@ -144,6 +158,7 @@ tc_forward_kernel(const __grid_constant__ CUtensorMap tmx, const PipeNet* __rest
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *reinterpret_cast<const uint32_t*>(smem + K::OFF_TMEM);
+    TPROF_BEGIN
 
     if (warp < kTcAW) {
         // =====================================================================================
@@ -163,9 +178,9 @@ tc_forward_kernel(const __grid_constant__ CUtensorMap tmx, const PipeNet* __rest
         const int qi = warp & 3;
         for (int n = 0; n < ntr; n++) {
             const int gq = n >> 2, s = n & 3, buf = gq & 1, ab = n & 1;
-            mbar_wait(sbase + K::BAR_T1_FULL + 8 * ab, (n >> 1) & 1);
+            TWAIT(0, sbase + K::BAR_T1_FULL + 8 * ab, (n >> 1) & 1);
             tc_fence_after();
-            if (s == 0) mbar_wait(sbase + K::BAR_Y1_EMPTY + 8 * buf, ((gq >> 1) & 1) ^ 1);
+            if (s == 0) TWAIT(1, sbase + K::BAR_Y1_EMPTY + 8 * buf, ((gq >> 1) & 1) ^ 1);
             const uint32_t yb = st_off + K::SLOT * (4 * buf + s);
 #pragma unroll 1
             for (int j = ((warp >> 2) + n) & 1; j < K::TILES; j += 2) {
@@ -222,7 +237,7 @@ tc_forward_kernel(const __grid_constant__ CUtensorMap tmx, const PipeNet* __rest
             for (int s = 0; s < K::SX && s < ntr; s++) issue(s, s);
             for (int n = 0; n + K::SX < ntr; n++) {
                 const int st = n % K::SX;
-                mbar_wait(sbase + K::BAR_EMPTY_X + 8 * st, (n / K::SX) & 1);
+                TWAIT(0, sbase + K::BAR_EMPTY_X + 8 * st, (n / K::SX) & 1);
                 issue(st, n + K::SX);
             }
         }
@@ -230,49 +245,60 @@ tc_forward_kernel(const __grid_constant__ CUtensorMap tmx, const PipeNet* __rest
         // =====================================================================================
         // M1: layer-1 MMAs, TILES x KSTEPS per trial
         // =====================================================================================
-        if (lane == 0) {
+        {
             constexpr uint32_t idesc = umma_idesc_i8(128, 16);
+            // descriptors: only the start-address field (low 14 bits, units of 16 B) changes between instructions
+            const uint64_t da0 = umma_desc(sbase + K::OFF_XS, 16, 1024, 2), db0 = umma_desc(sbase + K::OFF_W1, 128, K::KSTEPS * 256, 0);
+            const uint32_t a_hi = (uint32_t)(da0 >> 32), b_hi = (uint32_t)(db0 >> 32), b_lo0 = (uint32_t)db0;
             for (int n = 0; n < ntr; n++) {
                 const int st = n % K::SX, ab = n & 1;
-                mbar_wait(sbase + K::BAR_FULL_X + 8 * st, (n / K::SX) & 1);
-                mbar_wait(sbase + K::BAR_T1_EMPTY + 8 * ab, ((n >> 1) & 1) ^ 1);
+                TWAIT(0, sbase + K::BAR_FULL_X + 8 * st, (n / K::SX) & 1);
+                TWAIT(1, sbase + K::BAR_T1_EMPTY + 8 * ab, ((n >> 1) & 1) ^ 1);
                 tc_fence_after();
-                const uint32_t xs = sbase + K::OFF_XS + st * K::XS_BYTES;
+                const uint32_t a_lo = (uint32_t)da0 + st * (K::XS_BYTES >> 4);
+                const uint32_t td = tmem_base + K::TM_L1 + ab * K::TM_L1_TRIAL;
+                if (elect_one()) {
 #pragma unroll
-                for (int j = 0; j < K::TILES; j++)
+                    for (int j = 0; j < K::TILES; j++)
 #pragma unroll
-                    for (int ks = 0; ks < K::KSTEPS; ks++)
-                        umma_i8(tmem_base + K::TM_L1 + ab * K::TM_L1_TRIAL + 16 * j,
-                                umma_desc(xs + j * K::TILE_BYTES + ks * 4096, 16, 1024, 2),
-                                umma_desc(sbase + K::OFF_W1 + ks * 256, 128, K::KSTEPS * 256, 0), idesc, ks > 0);
-                umma_commit(sbase + K::BAR_EMPTY_X + 8 * st);
-                umma_commit(sbase + K::BAR_T1_FULL + 8 * ab);
+                        for (int ks = 0; ks < K::KSTEPS; ks++)
+                            umma_i8_lohi(td + 16 * j, a_lo + ((j * K::TILE_BYTES + ks * 4096) >> 4), a_hi, b_lo0 + ((ks * 256) >> 4),
+                                         b_hi, idesc, ks > 0);
+                    umma_commit(sbase + K::BAR_EMPTY_X + 8 * st);
+                    umma_commit(sbase + K::BAR_T1_FULL + 8 * ab);
+                }
+                __syncwarp();
             }
         }
     } else if (warp == kTcWarpM2) {
         // =====================================================================================
         // M2: layer-2 MMAs of a quad: per channel 3 x (M = 128 rows, N = 16 outputs, K = 32 samples)
         // =====================================================================================
-        if (lane == 0) {
+        {
             constexpr uint32_t idesc = umma_idesc_i8_kk(128, 16);
+            const uint64_t da0 = umma_desc(sbase + K::OFF_Y1, 16, 128, 0), db0 = umma_desc(sbase + K::OFF_W2, 128, 768, 0);
+            const uint32_t a_hi = (uint32_t)(da0 >> 32), b_hi = (uint32_t)(db0 >> 32), b_lo0 = (uint32_t)db0;
             for (int gq = 0; gq < nq; gq++) {
                 const int buf = gq & 1;
-                mbar_wait(sbase + K::BAR_Y1_FULL + 8 * buf, (gq >> 1) & 1);
+                TWAIT(0, sbase + K::BAR_Y1_FULL + 8 * buf, (gq >> 1) & 1);
                 tc_fence_after();
-#pragma unroll 1
-                for (int h = 0; h < 2; h++) {
-                    mbar_wait(sbase + K::BAR_T2_EMPTY + 8 * h, (gq & 1) ^ 1);
-                    tc_fence_after();
-#pragma unroll 1
-                    for (int k = 8 * h; k < 8 * h + 8; k++)
+                const uint32_t a_lo = (uint32_t)da0 + buf * ((4 * K::SLOT) >> 4);
 #pragma unroll
-                        for (int ks = 0; ks < 3; ks++)
-                            umma_i8(tmem_base + K::TM_L2 + 16 * k,
-                                    umma_desc(sbase + K::OFF_Y1 + k * K::CHS + 4 * K::SLOT * buf + 32 * ks, 16, 128, 0),
-                                    umma_desc(sbase + K::OFF_W2 + k * K::W2_CH + 256 * ks, 128, 768, 0), idesc, ks > 0);
-                    umma_commit(sbase + K::BAR_T2_FULL + 8 * h);
+                for (int h = 0; h < 2; h++) {
+                    TWAIT(1, sbase + K::BAR_T2_EMPTY + 8 * h, (gq & 1) ^ 1);
+                    tc_fence_after();
+                    if (elect_one()) {
+#pragma unroll
+                        for (int k = 8 * h; k < 8 * h + 8; k++)
+#pragma unroll
+                            for (int ks = 0; ks < 3; ks++)
+                                umma_i8_lohi(tmem_base + K::TM_L2 + 16 * k, a_lo + ((k * K::CHS + 32 * ks) >> 4), a_hi,
+                                             b_lo0 + ((k * K::W2_CH + 256 * ks) >> 4), b_hi, idesc, ks > 0);
+                        umma_commit(sbase + K::BAR_T2_FULL + 8 * h);
+                        if (h == 1) umma_commit(sbase + K::BAR_Y1_EMPTY + 8 * buf);
+                    }
+                    __syncwarp();
                 }
-                umma_commit(sbase + K::BAR_Y1_EMPTY + 8 * buf);
             }
         }
     } else if (warp < kTcAW + kTcBW) {
@@ -280,90 +306,60 @@ tc_forward_kernel(const __grid_constant__ CUtensorMap tmx, const PipeNet* __rest
         // B: layer-2 epilogue of (trial slot = warp & 3, channels 8 h .. 8 h + 7), then layer 3 of two channels
         // =====================================================================================
         const int wb = warp - kTcAW, s = warp & 3, h = wb >> 2;
-        const int lrow = (lane & 7) + 8 * ((lane >> 3) & 1);
-        uint32_t b3[2][2][2];
-#pragma unroll
-        for (int c = 0; c < 2; c++)
-#pragma unroll
-            for (int v = 0; v < 2; v++)
-#pragma unroll
-                for (int hh = 0; hh < 2; hh++) b3[c][v][hh] = net->w3frag[2 * wb + c][v * 2 + hh][lane];
-        const int m3 = net->m3, sh3 = net->sh3;
         const int4* c2 = reinterpret_cast<const int4*>(smem + K::OFF_C2);
         for (int gq = 0; gq < nq; gq++) {
             const int buf = gq & 1, par = (gq >> 1) & 1;
             const long long b0 = 4 * (firstq + (long long)gq * strideq);
             // ---- layer 2: thread = row `lane` of slot s: conv outputs 16 lane .. 16 lane + 15 of 8 channels
-            mbar_wait(sbase + K::BAR_T2_FULL + 8 * h, gq & 1);
+            TWAIT(0, sbase + K::BAR_T2_FULL + 8 * h, gq & 1);
             tc_fence_after();
+            TWAIT(1, sbase + K::BAR_Y3_EMPTY + 8 * buf, par ^ 1);      // the C warps have consumed y2[buf] of quad gq - 2
             uint8_t* y2s = smem + K::OFF_Y2 + buf * K::Y2_BUF + s * (16 * K::Y2S) + 8 + 2 * lane;
-#pragma unroll 2
-            for (int kk = 0; kk < 8; kk++) {
-                const int k = 8 * h + kk;
-                uint32_t r[16];
-                tmem_ld_32x32b_x16(r, tmem_base + ((uint32_t)(32 * s) << 16) + K::TM_L2 + 16 * k);
-                const int4 ca = c2[2 * k];                       // thr, sig, soff, m
-                const int shk = reinterpret_cast<const int*>(smem + K::OFF_C2)[8 * k + 4];
+            // four channels per batch: 4 x 16 accumulators in flight, the TMEM half is released as soon as the
+            // last batch sits in registers
+#pragma unroll
+            for (int kb = 0; kb < 2; kb++) {
+                uint32_t r[4][16];
+#ifdef MIBMI_PROF
+                const long long tl0_ = clock64();
+#endif
+#pragma unroll
+                for (int c = 0; c < 4; c++)
+                    tmem_ld_32x32b_x16(r[c], tmem_base + ((uint32_t)(32 * s) << 16) + K::TM_L2 + 16 * (8 * h + 4 * kb + c));
                 tmem_ld_wait();
-                int s0 = 0, s1 = 0;
-#pragma unroll
-                for (int i = 0; i < 8; i++) {
-                    s0 += max((int)r[i], ca.x);
-                    s1 += max((int)r[8 + i], ca.x);
+#ifdef MIBMI_PROF
+                pw_[2] += clock64() - tl0_;       // experiment: TMEM load latency, reported in the y3_empty column
+#endif
+                if (kb == 1) {
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(sbase + K::BAR_T2_EMPTY + 8 * h);
                 }
-                const int o0 = clip8(tdiv_magic(s0 * ca.y + ca.z, ca.w, shk));
-                const int o1 = clip8(tdiv_magic(s1 * ca.y + ca.z, ca.w, shk));
-                if (lane < K::ROWS) {
-                    *reinterpret_cast<uint16_t*>(y2s + k * K::Y2S) = (uint16_t)((o0 & 0xff) | ((o1 & 0xff) << 8));
-                    if (TAPS && tap2 && b0 + s < B) {
-                        int8_t* o = tap2 + ((size_t)(b0 + s) * 16 + k) * K::T8 + 2 * lane;
-                        o[0] = (int8_t)o0;
-                        o[1] = (int8_t)o1;
+#pragma unroll
+                for (int c = 0; c < 4; c++) {
+                    const int k = 8 * h + 4 * kb + c;
+                    const int4 ca = c2[2 * k];                       // thr, sig, soff, m
+                    const int shk = reinterpret_cast<const int*>(smem + K::OFF_C2)[8 * k + 4];
+                    int s0 = 0, s1 = 0;
+#pragma unroll
+                    for (int i = 0; i < 8; i++) {
+                        s0 += max((int)r[c][i], ca.x);
+                        s1 += max((int)r[c][8 + i], ca.x);
                     }
-                }
-            }
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) {
-                mbar_arrive(sbase + K::BAR_T2_EMPTY + 8 * h);
-                mbar_arrive(sbase + K::BAR_Y2_FULL + 8 * buf);
-            }
-            // ---- layer 3 of channels 2 wb, 2 wb + 1: MMA row r = 4 slot + block of 16 samples
-            mbar_wait(sbase + K::BAR_Y2_FULL + 8 * buf, par);
-            mbar_wait(sbase + K::BAR_Y3_EMPTY + 8 * buf, par ^ 1);
-#pragma unroll
-            for (int c = 0; c < 2; c++) {
-                const int k = 2 * wb + c;
-                uint32_t a[4];
-                ldsm_x4(a, sbase + K::OFF_Y2 + buf * K::Y2_BUF + ((lrow >> 2) * 16 + k) * K::Y2S + 16 * (lrow & 3) + 16 * (lane >> 4));
-                int c3[2][4];
-#pragma unroll
-                for (int v = 0; v < 2; v++) {
-                    c3[v][0] = c3[v][1] = c3[v][2] = c3[v][3] = 0;
-                    mma_k32(c3[v], a, b3[c][v][0], b3[c][v][1]);
-                }
-#pragma unroll
-                for (int hf = 0; hf < 2; hf++) {
-                    const int row = g + 8 * hf, sl = row >> 2, i = row & 3;          // trial slot, block of 16 samples
-                    uint8_t* y3b = smem + K::OFF_Y3 + (4 * buf + sl) * K::Y3_TRIAL + k * K::Y3S + 16 * (q >> 1) + 8 * (q & 1) +
-                                   32 * (i >> 1) + 4 * (i & 1);
-#pragma unroll
-                    for (int v = 0; v < 2; v++) {
-                        const int t = 16 * i + 8 * v + 2 * q;
-                        const uint32_t w = pack2_sat(tdiv_magic(c3[v][2 * hf], m3, sh3), tdiv_magic(c3[v][2 * hf + 1], m3, sh3));
-                        if (t < K::T8) {
-                            *reinterpret_cast<uint16_t*>(y3b + 2 * v) = (uint16_t)w;
-                            if (TAPS && tap3 && b0 + sl < B) {
-                                int8_t* o = tap3 + ((size_t)(b0 + sl) * 16 + k) * K::T8 + t;
-                                o[0] = (int8_t)(w & 0xff);
-                                o[1] = (int8_t)((w >> 8) & 0xff);
-                            }
+                    const int o0 = clip8(tdiv_magic(s0 * ca.y + ca.z, ca.w, shk));
+                    const int o1 = clip8(tdiv_magic(s1 * ca.y + ca.z, ca.w, shk));
+                    if (lane < K::ROWS) {
+                        *reinterpret_cast<uint16_t*>(y2s + k * K::Y2S) = (uint16_t)((o0 & 0xff) | ((o1 & 0xff) << 8));
+                        if (TAPS && tap2 && b0 + s < B) {
+                            int8_t* o = tap2 + ((size_t)(b0 + s) * 16 + k) * K::T8 + 2 * lane;
+                            o[0] = (int8_t)o0;
+                            o[1] = (int8_t)o1;
                         }
                     }
                 }
             }
             __syncwarp();
-            if (lane == 0) mbar_arrive(sbase + K::BAR_Y3_FULL + 8 * buf);
+            if (lane == 0) mbar_arrive(sbase + K::BAR_Y2_FULL + 8 * buf);
         }
     } else if (warp < kTcAW + kTcBW + kTcCW) {
         // =====================================================================================
@@ -382,10 +378,55 @@ tc_forward_kernel(const __grid_constant__ CUtensorMap tmx, const PipeNet* __rest
 #pragma unroll
         for (int ks = 0; ks < K::KST5; ks++) { w5a[ks][0] = net->w5frag[ks][0][lane]; w5a[ks][1] = net->w5frag[ks][1][lane]; }
         const uint32_t* y4w = reinterpret_cast<const uint32_t*>(y4);
+        // layer 3: channels 4 cj .. 4 cj + 3 of the whole quad; MMA row r = 4 slot + block of 16 samples
+        const int lrow = (lane & 7) + 8 * ((lane >> 3) & 1);
+        uint32_t b3[4][2][2];
+#pragma unroll
+        for (int c = 0; c < 4; c++)
+#pragma unroll
+            for (int v = 0; v < 2; v++)
+#pragma unroll
+                for (int hh = 0; hh < 2; hh++) b3[c][v][hh] = net->w3frag[4 * cj + c][v * 2 + hh][lane];
+        const int m3 = net->m3, sh3 = net->sh3;
         for (int gq = 0; gq < nq; gq++) {
             const int buf = gq & 1, par = (gq >> 1) & 1;
-            const long long b = 4 * (firstq + (long long)gq * strideq) + sl;
-            mbar_wait(sbase + K::BAR_Y3_FULL + 8 * buf, par);
+            const long long b0 = 4 * (firstq + (long long)gq * strideq);
+            const long long b = b0 + sl;
+            TWAIT(0, sbase + K::BAR_Y2_FULL + 8 * buf, par);
+#pragma unroll
+            for (int c = 0; c < 4; c++) {
+                const int k = 4 * cj + c;
+                uint32_t a[4];
+                ldsm_x4(a, sbase + K::OFF_Y2 + buf * K::Y2_BUF + ((lrow >> 2) * 16 + k) * K::Y2S + 16 * (lrow & 3) + 16 * (lane >> 4));
+                int c3[2][4];
+#pragma unroll
+                for (int v = 0; v < 2; v++) {
+                    c3[v][0] = c3[v][1] = c3[v][2] = c3[v][3] = 0;
+                    mma_k32(c3[v], a, b3[c][v][0], b3[c][v][1]);
+                }
+#pragma unroll
+                for (int hf = 0; hf < 2; hf++) {
+                    const int row = g + 8 * hf, rs = row >> 2, i = row & 3;          // trial slot, block of 16 samples
+                    uint8_t* y3b = smem + K::OFF_Y3 + (4 * buf + rs) * K::Y3_TRIAL + k * K::Y3S + 16 * (q >> 1) + 8 * (q & 1) +
+                                   32 * (i >> 1) + 4 * (i & 1);
+#pragma unroll
+                    for (int v = 0; v < 2; v++) {
+                        const int t = 16 * i + 8 * v + 2 * q;
+                        const uint32_t w = pack2_sat(tdiv_magic(c3[v][2 * hf], m3, sh3), tdiv_magic(c3[v][2 * hf + 1], m3, sh3));
+                        if (t < K::T8) {
+                            *reinterpret_cast<uint16_t*>(y3b + 2 * v) = (uint16_t)w;
+                            if (TAPS && tap3 && b0 + rs < B) {
+                                int8_t* o = tap3 + ((size_t)(b0 + rs) * 16 + k) * K::T8 + t;
+                                o[0] = (int8_t)(w & 0xff);
+                                o[1] = (int8_t)((w >> 8) & 0xff);
+                            }
+                        }
+                    }
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(sbase + K::BAR_Y3_EMPTY + 8 * buf);      // y2[buf] is free again
+            asm volatile("bar.sync 1, %0;" ::"n"(kTcCW * 32) : "memory");        // y3[buf] of all 16 channels is complete
             const uint32_t y3a = sbase + K::OFF_Y3 + (4 * buf + sl) * K::Y3_TRIAL + l4_off;
 #pragma unroll
             for (int s4 = 0; s4 < K::NST; s4++) {
@@ -416,7 +457,6 @@ tc_forward_kernel(const __grid_constant__ CUtensorMap tmx, const PipeNet* __rest
                 }
             }
             __syncwarp();
-            if (lane == 0) mbar_arrive(sbase + K::BAR_Y3_EMPTY + 8 * buf);
             int z[4] = {0, 0, 0, 0};
 #pragma unroll
             for (int ks = 0; ks < K::KST5; ks++) {
@@ -432,6 +472,7 @@ tc_forward_kernel(const __grid_constant__ CUtensorMap tmx, const PipeNet* __rest
             __syncwarp();
         }
     }
+    TPROF_END
     tc_fence_before();
     __syncthreads();
     if (warp == kTcWarpM1) tmem_dealloc(tmem_base, 512);
@@ -483,3 +524,9 @@ cudaError_t launch_tc(const PipeNet* net_dev, bool fast1, int C, int T, const in
 }
 
 }  // namespace mibmi
+
+#ifdef MIBMI_PROF
+extern "C" __attribute__((visibility("default"))) int mibmi_debug_prof_tc(long long* out_host) {
+    return (int)cudaMemcpyFromSymbol(out_host, mibmi::g_prof_tc, sizeof(mibmi::g_prof_tc));
+}
+#endif

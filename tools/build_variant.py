@@ -1,5 +1,5 @@
 """Experiment builds of libmibmi.so: tools/build_variant.py NAME [-DFOO=1 ...] -> tools/variants/NAME/libmibmi.so
-(select at run time with MIBMI_LIB_PATH).  Only mibmi_pipe.cu is recompiled; the other objects come from the
+(select at run time with MIBMI_LIB_PATH).  Only mibmi_pipe.cu and mibmi_tc.cu are recompiled; the other objects come from the
 regular in-tree build."""
 import os, subprocess, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -9,9 +9,15 @@ _build.build_library()
 out = os.path.join(_build.ROOT, "tools", "variants", name)
 os.makedirs(out, exist_ok=True)
 nvcc = _build._nvcc()
-o = os.path.join(out, "mibmi_pipe.o")
-subprocess.run([nvcc, *_build.NVCC_FLAGS, *flags, "-c", os.path.join(_build.CSRC, "mibmi_pipe.cu"), "-o", o], check=True)
-objs = [os.path.join(_build.LIB_DIR, s.replace(".cu", ".o")) for s in _build.SOURCES if s != "mibmi_pipe.cu"] + [o]
+VAR = ["mibmi_pipe.cu", "mibmi_tc.cu"]
+objs = [os.path.join(_build.LIB_DIR, s.replace(".cu", ".o")) for s in _build.SOURCES if s not in VAR]
+procs = []
+for src in VAR:
+    o = os.path.join(out, src.replace(".cu", ".o"))
+    procs.append(subprocess.Popen([nvcc, *_build.NVCC_FLAGS, *flags, "-c", os.path.join(_build.CSRC, src), "-o", o]))
+    objs.append(o)
+for pr in procs:
+    assert pr.wait() == 0
 subprocess.run([nvcc, "-shared", "-o", os.path.join(out, "libmibmi.so"), *objs, "-gencode", "arch=compute_100a,code=sm_100a",
                 "-Xcompiler", "-fPIC"], check=True)
 print(os.path.join(out, "libmibmi.so"))

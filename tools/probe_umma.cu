@@ -98,12 +98,12 @@ probe(const __grid_constant__ CUtensorMap tm, const int8_t* __restrict__ w1, int
 }
 
 // throughput: `reps` back-to-back tcgen05.mma (M = 128, N = n, K = 32, i8) from one thread, then one commit
-__global__ void __launch_bounds__(128, 1) timing(int reps, int n, long long* cyc) {
+__global__ void __launch_bounds__(128, 1) timing(int reps, int n, long long* cyc, int astep, int mode, int issuers) {
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ __align__(8) unsigned long long bar;
     __shared__ uint32_t tmem_base_s;
     const int tid = threadIdx.x, warp = tid >> 5;
-    for (int i = tid; i < 16384 / 4; i += 128) reinterpret_cast<uint32_t*>(smem)[i] = 0x01010101u * (i & 3);
+    for (int i = tid; i < 65536 / 4; i += 128) reinterpret_cast<uint32_t*>(smem)[i] = 0x01010101u * (i & 3);
     if (tid == 0) {
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(s32(&bar)));
         asm volatile("fence.mbarrier_init.release.cluster;");
@@ -117,16 +117,44 @@ __global__ void __launch_bounds__(128, 1) timing(int reps, int n, long long* cyc
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;");
     const uint32_t tmem = tmem_base_s;
+    if (issuers > 1) {
+        __shared__ long long tt[8];
+        if ((tid & 31) == 0 && warp < issuers) {
+            const uint32_t idesc = (2u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | ((uint32_t)(n >> 3) << 17) | ((128u >> 4) << 24);
+            const uint64_t da = (uint64_t)(((s32(smem) + 8192 * warp) >> 4) & 0x3fff) | ((uint64_t)1 << 16) | ((uint64_t)(1024 >> 4) << 32) | ((uint64_t)1 << 46) | ((uint64_t)2 << 61);
+            const uint64_t db = (uint64_t)(((s32(smem) + 49152) >> 4) & 0x3fff) | ((uint64_t)(128 >> 4) << 16) | ((uint64_t)(256 >> 4) << 32) | ((uint64_t)1 << 46);
+            const uint32_t d = tmem + 64 * warp;
+            const long long t0 = clock64();
+            for (int i = 0; i < reps; i++)
+                asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                             "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%5, %5, %5, %5}, p;\n\t}"
+                             ::"r"(d), "l"(da), "l"(db), "r"(idesc), "r"(1u), "r"(0u) : "memory");
+            asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.b64 [%0];" ::"r"(s32(&bar)) : "memory");
+            tt[warp] = clock64() - t0;
+        }
+        __syncthreads();
+        if (tid == 0) {
+            uint32_t done = 0;   // barrier was initialised with count 1: only valid to wait for the first commit; use the slowest issue time instead
+            long long mx = 0;
+            for (int i = 0; i < issuers; i++) mx = tt[i] > mx ? tt[i] : mx;
+            cyc[0] = mx; cyc[1] = mx;
+            (void)done;
+        }
+    } else
     if (tid == 0) {
         const uint32_t idesc = (2u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | ((uint32_t)(n >> 3) << 17) | ((128u >> 4) << 24);
-        const uint64_t da = (uint64_t)((s32(smem) >> 4) & 0x3fff) | ((uint64_t)1 << 16) | ((uint64_t)(1024 >> 4) << 32) | ((uint64_t)1 << 46) | ((uint64_t)2 << 61);
-        const uint64_t db = (uint64_t)(((s32(smem) + 8192) >> 4) & 0x3fff) | ((uint64_t)(128 >> 4) << 16) | ((uint64_t)(256 >> 4) << 32) | ((uint64_t)1 << 46);
+        // mode 0: A = MN-major swizzled tile (layer 1); mode 1: A = K-major Hankel view, LBO 16 B / SBO 128 B (layer 2)
+        const uint32_t idesc2 = mode ? (idesc & ~(1u << 15)) : idesc;
+        const uint64_t da0 = mode ? ((uint64_t)((s32(smem) >> 4) & 0x3fff) | ((uint64_t)1 << 16) | ((uint64_t)(128 >> 4) << 32) | ((uint64_t)1 << 46))
+                                  : ((uint64_t)((s32(smem) >> 4) & 0x3fff) | ((uint64_t)1 << 16) | ((uint64_t)(1024 >> 4) << 32) | ((uint64_t)1 << 46) | ((uint64_t)2 << 61));
+        const uint64_t db = (uint64_t)(((s32(smem) + 49152) >> 4) & 0x3fff) | ((uint64_t)(128 >> 4) << 16) | ((uint64_t)(256 >> 4) << 32) | ((uint64_t)1 << 46);
         const long long t0 = clock64();
         for (int i = 0; i < reps; i++) {
             const uint32_t d = tmem + (uint32_t)((i & 3) * 64);          // 4 independent accumulators
+            const uint64_t da = da0 + (uint64_t)((i & 7) * astep);       // A operand walks over 8 x astep x 16 bytes
             asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
                          "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%5, %5, %5, %5}, p;\n\t}"
-                         ::"r"(d), "l"(da), "l"(db), "r"(idesc), "r"(1u), "r"(0u) : "memory");
+                         ::"r"(d), "l"(da), "l"(db), "r"(idesc2), "r"(1u), "r"(0u) : "memory");
         }
         const long long t1 = clock64();
         asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.b64 [%0];" ::"r"(s32(&bar)) : "memory");
@@ -182,16 +210,25 @@ int main(int argc, char** argv) {
     }
     {
         long long* dc; cudaMalloc(&dc, 16);
-        cudaFuncSetAttribute(timing, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384);
-        const int ns[] = {16, 32, 64, 128, 256};
-        for (int ni = 0; ni < 5; ni++)
-            for (int reps = 64; reps <= 1024; reps *= 4) {
-                timing<<<1, 128, 16384>>>(reps, ns[ni], dc);
+        cudaFuncSetAttribute(timing, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536);
+        const int ns[] = {16, 64, 256};
+        for (int mode = 0; mode < 2; mode++)
+        for (int astep = 0; astep <= 256; astep += 256)
+        for (int ni = 0; ni < 3; ni++)
+            for (int reps = 1024; reps <= 1024; reps *= 4) {
+                printf("mode=%d astep=%d  ", mode, astep);
+                timing<<<1, 128, 65536>>>(reps, ns[ni], dc, astep, mode, 1);
                 cudaError_t e2 = cudaDeviceSynchronize();
                 long long hc[2]; cudaMemcpy(hc, dc, 16, cudaMemcpyDeviceToHost);
                 printf("N=%3d reps=%4d err=%d: issue %.1f cycles/MMA, complete %.1f cycles/MMA\n", ns[ni], reps, (int)e2,
                        (double)hc[0] / reps, (double)hc[1] / reps);
             }
+        for (int iss = 1; iss <= 4; iss++) {
+            timing<<<1, 128, 65536>>>(1024, 16, dc, 0, 0, iss);
+            cudaError_t e2 = cudaDeviceSynchronize();
+            long long hc[2]; cudaMemcpy(hc, dc, 16, cudaMemcpyDeviceToHost);
+            printf("issuers=%d err=%d: %.1f cycles per MMA overall (each issues 1024)\n", iss, (int)e2, (double)hc[0] / (1024.0 * iss));
+        }
     }
     return 0;
 }
