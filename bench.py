@@ -30,10 +30,17 @@ sys.path.insert(0, ROOT)
 C, T, N_CLASSES, NET_SEED = 64, 480, 4, 0
 ALG_BYTES_PER_TRIAL = C * T + N_CLASSES          # int8 input + 4 B logits
 METRIC = "int8 edgeEEGNet trials/sec"
-# ncu (profiles/r1b_ncu_full_metrics.csv): 2.013346 GB read + 3.9255 MB written per launch of 65536 trials
-NCU_TRAFFIC_BYTES_PER_TRIAL = (2.013346e9 + 3.925504e6) / 65536
-KERNEL_NAMES = {"fused": "tc_forward_kernel<TCfg<64,480>>", "fused_pipe": "pipe_forward_kernel<PCfg<64,480,4>>", "fused_v1": "fused_forward_kernel<Cfg<64,480>>",
-                "generic": "generic_forward_kernel"}
+# ncu --set full (profiles/r1d_ncu_full_metrics.csv, tc_forward_kernel<TCfg<64,480>>): 2.013485 GB read + 18.797 MB written
+# per launch of 65536 trials
+NCU_TRAFFIC_BYTES_PER_TRIAL = (2.013485e9 + 18.797056e6) / 65536
+KERNEL_TEMPLATES = {"tc_forward_kernel": "tc_forward_kernel<TCfg<{C},{T}>>", "pipe_forward_kernel": "pipe_forward_kernel<PCfg<{C},{T},4>>",
+                    "fused_forward_kernel": "fused_forward_kernel<Cfg<{C},{T}>>"}
+KERNEL_NOTES = {
+    "tc_forward_kernel": "layers 1+2 on tcgen05.mma kind::i8 (TMEM accumulators), 23 warps requantise; ncu r1d: DRAM 67 % of "
+                         "ncu peak, issue slots 59 %, not pipe bound: per-trial hand-off latency between the roles, see DESIGN.md 4.1",
+    "pipe_forward_kernel": "mma.sync pipeline kernel (shape without a tcgen05 instance): issue / dependent-latency bound, "
+                           "see DESIGN.md 4.2",
+}
 WORKLOAD = "edgeEEGNet int8 forward, PhysionetMMMI shape 64ch x 480 samples, 4 classes (BASELINE config 2)"
 
 
@@ -394,12 +401,13 @@ def main():
                                       "one barrier at the end" if peer is not None else "one NCCL all_gather of int8 logits per step"),
                        "kernel_path": net.last_path, "bit_exact_checked": None, "gather_checked": gather_checked},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": NCU_TRAFFIC_BYTES_PER_TRIAL * B if (net.last_path == "fused" and args.shape == "64x480") else None,
+                         "traffic": NCU_TRAFFIC_BYTES_PER_TRIAL * B if (net.last_kernel == "tc_forward_kernel" and args.shape == "64x480") else None,
                          "traffic_source": "ncu --set full dram__bytes_read.sum + dram__bytes_write.sum per launch of 65536 "
-                                           "trials (profiles/r1b_ncu_full_metrics.csv), scaled to this batch",
-                         "peak_source": peak_src, "kernel": KERNEL_NAMES.get(net.last_path, net.last_path).replace("64,480", f"{C},{T}"),
+                                           "trials (profiles/r1d_ncu_full_metrics.csv), scaled to this batch",
+                         "peak_source": peak_src,
+                         "kernel": KERNEL_TEMPLATES.get(net.last_kernel, net.last_kernel).format(C=C, T=T),
                          "kernel_ms": ms_kernel, "alg_bytes_per_trial": ALG_BYTES_PER_TRIAL,
-                         "note": "latency/issue bound (27 warps per SM, 47 % issue slots, IMMA pipe 38 %), see DESIGN.md"},
+                         "note": KERNEL_NOTES.get(net.last_kernel, "")},
             "gpu_launches": int(launches), "clocks": clocks, "e2e": e2e,
         }
         if not args.no_cpu_baseline:

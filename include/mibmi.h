@@ -111,6 +111,9 @@ MIBMI_API int mibmi_destroy(mibmi_net_t* net);
 MIBMI_API int mibmi_set_option(mibmi_net_t* net, int option, int64_t value);
 /* Which path the most recent forward on this handle ran (MIBMI_PATH_GENERIC / MIBMI_PATH_FUSED). */
 MIBMI_API int mibmi_last_path(const mibmi_net_t* net);
+/* Name of the __global__ function the most recent forward launched ("tc_forward_kernel", "pipe_forward_kernel",
+ * "stream_forward_kernel", "generic_forward_kernel", "fused_forward_kernel"; "" before the first call). Static string. */
+MIBMI_API const char* mibmi_last_kernel(const mibmi_net_t* net);
 /* 1 if the fused path can run this network (shape supported, requant parameters within the proven
  * range of the magic-number division), else 0 with the reason in *why (static string, may be NULL). */
 MIBMI_API int mibmi_fused_supported(const mibmi_net_t* net, const char** why);

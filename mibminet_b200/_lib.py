@@ -23,7 +23,7 @@ OPT_FORCE_PATH, OPT_CTAS_PER_SM, OPT_HOST_CHUNK, OPT_STREAM_MODE = 1, 2, 3, 4
 # every symbol include/mibmi.h declares (tests/test_abi.py checks the header against this list)
 SYMBOLS = [
     "mibmi_version", "mibmi_strerror", "mibmi_last_cuda_error", "mibmi_create", "mibmi_destroy",
-    "mibmi_set_option", "mibmi_last_path", "mibmi_fused_supported", "mibmi_launch_count",
+    "mibmi_set_option", "mibmi_last_path", "mibmi_last_kernel", "mibmi_fused_supported", "mibmi_launch_count",
     "mibmi_forward_int8", "mibmi_forward_int8_taps", "mibmi_forward_int8_host",
     "mibmi_quantize_input_f32", "mibmi_dequantize_logits_f32", "mibmi_debug_magic", "mibmi_debug_pack_fused",
     "mibmi_debug_pack_pipe", "mibmi_stream_windows", "mibmi_stream_supported", "mibmi_forward_stream_int8",
@@ -77,6 +77,8 @@ def lib() -> ctypes.CDLL:
     L.mibmi_destroy.argtypes = [vp]
     L.mibmi_set_option.argtypes = [vp, i32, i64]
     L.mibmi_last_path.argtypes = [vp]
+    L.mibmi_last_kernel.argtypes = [vp]
+    L.mibmi_last_kernel.restype = ctypes.c_char_p
     L.mibmi_fused_supported.argtypes = [vp, ctypes.POINTER(ctypes.c_char_p)]
     L.mibmi_launch_count.argtypes = [vp]
     L.mibmi_launch_count.restype = i64

@@ -32,7 +32,7 @@ struct mibmi_net {
     int stream_mode = MIBMI_STREAM_AUTO;
     int force_path = MIBMI_PATH_AUTO, ctas_per_sm = 0;
     int64_t host_chunk = 0;
-    std::atomic<int> last_path{0};
+    std::atomic<int> last_path{0}, last_kernel{0};
     std::atomic<int> last_cuda{0};
     std::atomic<int64_t> launches{0};
     // host entry point staging (guarded by host_mu)
@@ -534,6 +534,8 @@ int forward_impl(mibmi_net* net, const int8_t* x, int64_t B, int layout, int8_t*
             if (e != cudaSuccess) return fail_cuda(net, e);
         }
     net->last_path.store(path);
+    net->last_kernel.store(path == MIBMI_PATH_FUSED ? (net->tc_ok ? 1 : 2) : path == MIBMI_PATH_FUSED_PIPE ? 2
+                           : path == MIBMI_PATH_FUSED_V1 ? 3 : 4);
     net->launches.fetch_add(1);
     return MIBMI_OK;
 }
@@ -559,6 +561,12 @@ const char* mibmi_strerror(int status) {
 
 int mibmi_last_cuda_error(const mibmi_net_t* net) { return net ? net->last_cuda.load() : 0; }
 int mibmi_last_path(const mibmi_net_t* net) { return net ? net->last_path.load() : 0; }
+const char* mibmi_last_kernel(const mibmi_net_t* net) {
+    static const char* const names[] = {"", "tc_forward_kernel", "pipe_forward_kernel", "fused_forward_kernel",
+                                        "generic_forward_kernel", "stream_forward_kernel"};
+    const int k = net ? net->last_kernel.load() : 0;
+    return names[k >= 0 && k <= 5 ? k : 0];
+}
 int64_t mibmi_launch_count(const mibmi_net_t* net) { return net ? net->launches.load() : 0; }
 
 int mibmi_fused_supported(const mibmi_net_t* net, const char** why) {
@@ -836,6 +844,7 @@ static int stream_impl(mibmi_net* net, const int8_t* x, int64_t S, int64_t L, in
                                       net->num_sms, stream);
         if (e != cudaSuccess) return fail_cuda(net, e);
         net->last_path.store(MIBMI_PATH_STREAM);
+        net->last_kernel.store(5);
         net->launches.fetch_add(1);
         return MIBMI_OK;
     }

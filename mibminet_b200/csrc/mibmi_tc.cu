@@ -182,36 +182,48 @@ tc_forward_kernel(const __grid_constant__ CUtensorMap tmx, const PipeNet* __rest
             tc_fence_after();
             if (s == 0) TWAIT(1, sbase + K::BAR_Y1_EMPTY + 8 * buf, ((gq >> 1) & 1) ^ 1);
             const uint32_t yb = st_off + K::SLOT * (4 * buf + s);
+            // the warp's (up to) two units of a pass are loaded from TMEM together and requantised interleaved: the
+            // TMEM latency and the dependent division chains of one unit hide behind the other
 #pragma unroll 1
-            for (int j = ((warp >> 2) + n) & 1; j < K::TILES; j += 2) {
-                const int u = 4 * j + qi;
-                if (32 * u >= K::T) break;
-                uint32_t r[2][8];
-                const uint32_t ta = tmem_base + ((uint32_t)(32 * qi) << 16) + K::TM_L1 + ab * K::TM_L1_TRIAL + 16 * j;
-                tmem_ld_16x256b_x2(r[0], ta);
-                tmem_ld_16x256b_x2(r[1], ta + (16u << 16));
+            for (int jb = ((warp >> 2) + n) & 1; jb < K::TILES; jb += 4) {
+                const int u0 = 4 * jb + qi, u1 = u0 + 8;
+                if (32 * u0 >= K::T) break;
+                const bool two = jb + 2 < K::TILES && 32 * u1 < K::T;
+                uint32_t r[2][2][8];
+                const uint32_t ta = tmem_base + ((uint32_t)(32 * qi) << 16) + K::TM_L1 + ab * K::TM_L1_TRIAL + 16 * jb;
+                tmem_ld_16x256b_x2(r[0][0], ta);
+                tmem_ld_16x256b_x2(r[0][1], ta + (16u << 16));
+                if (two) {
+                    tmem_ld_16x256b_x2(r[1][0], ta + 32);
+                    tmem_ld_16x256b_x2(r[1][1], ta + 32 + (16u << 16));
+                }
                 tmem_ld_wait();
-                uint32_t w[2][2];
 #pragma unroll
-                for (int mt = 0; mt < 2; mt++)
+                for (int uu = 0; uu < 2; uu++) {
+                    if (uu == 1 && !two) break;
+                    const int u = uu ? u1 : u0;
+                    uint32_t w[2][2];
 #pragma unroll
-                    for (int nt = 0; nt < 2; nt++) {
-                        int v[4];
+                    for (int mt = 0; mt < 2; mt++)
 #pragma unroll
-                        for (int c = 0; c < 4; c++)
-                            v[c] = tc_div1<FAST1>((int)r[mt][4 * nt + c] + off1[nt][c & 1], mg1[nt][c & 1], sh1[nt][c & 1]);
-                        w[mt][nt] = pack4_sat(v[0], v[1], v[2], v[3]);
-                        if (TAPS && tap1) {
-                            const long long b = 4 * (firstq + (long long)gq * strideq) + s;
-                            if (b < B)
+                        for (int nt = 0; nt < 2; nt++) {
+                            int v[4];
 #pragma unroll
-                                for (int c = 0; c < 4; c++) {
-                                    const int f = 8 * nt + 2 * q + (c & 1), t = 32 * u + 16 * mt + g + 8 * (c >> 1);
-                                    tap1[((size_t)b * 16 + f) * K::T + t] = (int8_t)clip8(v[c]);
-                                }
+                            for (int c = 0; c < 4; c++)
+                                v[c] = tc_div1<FAST1>((int)r[uu][mt][4 * nt + c] + off1[nt][c & 1], mg1[nt][c & 1], sh1[nt][c & 1]);
+                            w[mt][nt] = pack4_sat(v[0], v[1], v[2], v[3]);
+                            if (TAPS && tap1) {
+                                const long long b = 4 * (firstq + (long long)gq * strideq) + s;
+                                if (b < B)
+#pragma unroll
+                                    for (int c = 0; c < 4; c++) {
+                                        const int f = 8 * nt + 2 * q + (c & 1), t = 32 * u + 16 * mt + g + 8 * (c >> 1);
+                                        tap1[((size_t)b * 16 + f) * K::T + t] = (int8_t)clip8(v[c]);
+                                    }
+                            }
                         }
-                    }
-                stsm_t8_x4(yb + 32 * u, w[0][0], w[0][1], w[1][0], w[1][1]);
+                    stsm_t8_x4(yb + 32 * u, w[0][0], w[0][1], w[1][0], w[1][1]);
+                }
             }
             tc_fence_before();
             fence_proxy_async();          // y1 is read by the tensor core (async proxy)

@@ -98,6 +98,11 @@ class Int8Net:
         return _PATH_NAMES.get(self._L.mibmi_last_path(self._h), "none")
 
     @property
+    def last_kernel(self) -> str:
+        """Name of the __global__ function the most recent forward launched."""
+        return (self._L.mibmi_last_kernel(self._h) or b"").decode()
+
+    @property
     def launch_count(self) -> int:
         return int(self._L.mibmi_launch_count(self._h))
 
