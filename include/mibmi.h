@@ -187,6 +187,43 @@ MIBMI_API int64_t mibmi_debug_pack_fused(const mibmi_params_t* params, void* out
 /* Same for the warp-specialised pipeline kernel (MIBMI_PATH_FUSED). */
 MIBMI_API int64_t mibmi_debug_pack_pipe(const mibmi_params_t* params, void* out, int64_t cap, const char** why);
 
+/* ---------------------------------------------------------------------------------------------------------
+ * EEGNet / Q-EEGNet layer order: temporal conv (1, Nf) over every EEG channel first, then the
+ * depthwise spatial conv -- replaces QuantLab/quantlab/PhysionetMMMI/EEGNet/eegnet.py:137-168 (EEGNet.forward) for
+ * integer inference.  The reference tree has no integer model of this topology; semantics = the edgeEEGNet integer
+ * pipeline's (golden_model.py:153-379, REORDER_BN form) applied to this layer order, see oracle/eegnet_np.py.
+ * All weights in torch (cross-correlation) order, HOST pointers, copied by create. */
+typedef struct {
+    int32_t C, T;              /* EEG channels, samples per trial                                   */
+    int32_t F1, D, F2, N;      /* F1 % 4 == 0, F1 <= 16, D in {1, 2}, F2 <= 32, N <= 8             */
+    int32_t Nf;                /* temporal filter length (conv1 kernel (1, Nf)), multiple of 4, <= 128; pad Nf/2-1 | Nf/2 */
+    const int8_t*  l1_weight;  /* [F1][Nf]        conv1 (eegnet.py:101-102)                          */
+    const int32_t* l1_factor;  /* [F1]            batch_norm1 folded, quant2 (pool = 1)              */
+    const int32_t* l1_offset;  /* [F1]                                                              */
+    const int8_t*  l2_weight;  /* [F1*D][C]       conv2, depthwise spatial, groups = F1 (eegnet.py:105) */
+    const int32_t* l2_factor;  /* [F1*D]          batch_norm2 + ReLU + pool 8 folded (x8), quant3    */
+    const int32_t* l2_offset;  /* [F1*D]                                                            */
+    const int8_t*  l3_weight;  /* [F1*D][16]      sep_conv1 (eegnet.py:113)                          */
+    int32_t        l3_factor;
+    const int8_t*  l4_weight;  /* [F2][F1*D]      sep_conv2 (eegnet.py:115)                          */
+    const int32_t* l4_factor;  /* [F2]            batch_norm3 + ReLU + pool 8 folded, quant5         */
+    const int32_t* l4_offset;  /* [F2]                                                              */
+    const int8_t*  l5_weight;  /* [N][F2*T64]     fc, flatten order (k, q)                           */
+    const int8_t*  l5_bias;    /* [N]                                                               */
+    int32_t        l5_factor;
+} mibmi_eegnet_params_t;
+
+typedef struct mibmi_eegnet mibmi_eegnet_t; /* opaque */
+
+MIBMI_API int mibmi_eegnet_create(const mibmi_eegnet_params_t* params, int device, mibmi_eegnet_t** out);
+MIBMI_API int mibmi_eegnet_destroy(mibmi_eegnet_t* net);
+/* x_dev: int8 [B][C][T]; logits_dev: int8 [B][N]; asynchronous on `stream`. */
+MIBMI_API int mibmi_eegnet_forward_int8(mibmi_eegnet_t* net, const int8_t* x_dev, int64_t B, int8_t* logits_dev, void* stream);
+/* Same with per-layer taps (any may be NULL): y2 [B][F1*D][T/8], y3 [B][F1*D][T/8], y4 [B][F2][T/64]. */
+MIBMI_API int mibmi_eegnet_forward_int8_taps(mibmi_eegnet_t* net, const int8_t* x_dev, int64_t B, int8_t* logits_dev,
+                                             int8_t* y2, int8_t* y3, int8_t* y4, void* stream);
+MIBMI_API int64_t mibmi_eegnet_launch_count(const mibmi_eegnet_t* net);
+
 #ifdef __cplusplus
 }
 #endif

@@ -28,6 +28,8 @@ SYMBOLS = [
     "mibmi_quantize_input_f32", "mibmi_dequantize_logits_f32", "mibmi_debug_magic", "mibmi_debug_pack_fused",
     "mibmi_debug_pack_pipe", "mibmi_stream_windows", "mibmi_stream_supported", "mibmi_forward_stream_int8",
     "mibmi_forward_stream_int8_taps", "mibmi_forward_int8_gather",
+    "mibmi_eegnet_create", "mibmi_eegnet_destroy", "mibmi_eegnet_forward_int8", "mibmi_eegnet_forward_int8_taps",
+    "mibmi_eegnet_launch_count",
 ]
 
 
@@ -48,6 +50,19 @@ class Params(ctypes.Structure):
         ("l3_factor", ctypes.c_int32), ("l3_weight", ctypes.c_void_p),
         ("l4_factor", ctypes.c_void_p), ("l4_offset", ctypes.c_void_p), ("l4_weight", ctypes.c_void_p),
         ("l5_factor", ctypes.c_int32), ("l5_bias", ctypes.c_void_p), ("l5_weight", ctypes.c_void_p),
+    ]
+
+
+class EEGNetParamsC(ctypes.Structure):
+    """mibmi_eegnet_params_t"""
+    _fields_ = [
+        ("C", ctypes.c_int32), ("T", ctypes.c_int32), ("F1", ctypes.c_int32), ("D", ctypes.c_int32),
+        ("F2", ctypes.c_int32), ("N", ctypes.c_int32), ("Nf", ctypes.c_int32),
+        ("l1_weight", ctypes.c_void_p), ("l1_factor", ctypes.c_void_p), ("l1_offset", ctypes.c_void_p),
+        ("l2_weight", ctypes.c_void_p), ("l2_factor", ctypes.c_void_p), ("l2_offset", ctypes.c_void_p),
+        ("l3_weight", ctypes.c_void_p), ("l3_factor", ctypes.c_int32),
+        ("l4_weight", ctypes.c_void_p), ("l4_factor", ctypes.c_void_p), ("l4_offset", ctypes.c_void_p),
+        ("l5_weight", ctypes.c_void_p), ("l5_bias", ctypes.c_void_p), ("l5_factor", ctypes.c_int32),
     ]
 
 
@@ -98,6 +113,12 @@ def lib() -> ctypes.CDLL:
     L.mibmi_debug_pack_fused.restype = i64
     L.mibmi_debug_pack_pipe.argtypes = [ctypes.POINTER(Params), vp, i64, ctypes.POINTER(ctypes.c_char_p)]
     L.mibmi_debug_pack_pipe.restype = i64
+    L.mibmi_eegnet_create.argtypes = [ctypes.POINTER(EEGNetParamsC), i32, ctypes.POINTER(vp)]
+    L.mibmi_eegnet_destroy.argtypes = [vp]
+    L.mibmi_eegnet_forward_int8.argtypes = [vp, vp, i64, vp, vp]
+    L.mibmi_eegnet_forward_int8_taps.argtypes = [vp, vp, i64, vp, vp, vp, vp, vp]
+    L.mibmi_eegnet_launch_count.argtypes = [vp]
+    L.mibmi_eegnet_launch_count.restype = i64
     _lib = L
     return L
 

@@ -295,3 +295,106 @@ def to_wolf_input(x_int8: np.ndarray) -> np.ndarray:
     out = np.zeros((*xt.shape[:-1], align4(C)), np.int8)
     out[..., :C] = xt
     return out
+
+
+# =====================================================================================================
+# EEGNet / Q-EEGNet layer order: temporal conv (1, Nf) first, then the depthwise spatial
+# conv -- QuantLab/quantlab/PhysionetMMMI/EEGNet/eegnet.py:100-106 (modules), :137-168 (forward).
+# The reference tree holds NO integer model of this topology (the Q-EEGNet Wolf C code is not vendored);
+# the integer pipeline below applies the same export maths (a11 / a12: convert_torch_format.py:36-205) to the
+# module's layers, REORDER_BN form for the two pooled layers.  Parity: unpinned by the reference.
+# =====================================================================================================
+@dataclass
+class EEGNetParams:
+    """Integer EEGNet-order network, all weights in torch (cross-correlation) order.
+
+    L1  v[f][c][t] = sum_j xpad[c][t+j] w1[f][j]        (pad Nf/2-1 | Nf/2, eegnet.py:101-102)
+        y1 = clip8(tdiv(v + off1[f], fac1[f]))           (batch_norm1 folded, quant2)
+    L2  a[k][t]   = sum_c y1[k // D][c][t] w2[k][c]      (depthwise spatial, groups = F1, eegnet.py:105)
+        s = sum_8 max(a, -(off2[k] >> 3)); y2 = clip8(tdiv(s + off2[k], fac2[k]))   (batch_norm2, ReLU, pool 8, quant3)
+    L3..L5 as in the edgeEEGNet pipeline (sep_conv1 / sep_conv2 + batch_norm3 + pool / fc).
+    """
+    C: int
+    T: int
+    F1: int
+    D: int
+    F2: int
+    N: int
+    Nf: int
+    w1: np.ndarray    # [F1, Nf]
+    fac1: np.ndarray  # [F1]
+    off1: np.ndarray
+    w2: np.ndarray    # [F1*D, C]
+    fac2: np.ndarray  # [F1*D]
+    off2: np.ndarray
+    w3: np.ndarray    # [F1*D, 16]
+    fac3: int
+    w4: np.ndarray    # [F2, F1*D]
+    fac4: np.ndarray  # [F2]
+    off4: np.ndarray
+    w5: np.ndarray    # [N, F2 * T64]
+    b5: np.ndarray
+    fac5: int
+    input_scale: float = 1.0
+    output_scale: float = 1.0
+    scales: Dict[str, float] = field(default_factory=dict)
+
+    @property
+    def K2(self):
+        return self.F1 * self.D
+
+    def validate(self):
+        if self.Nf % 4 or not 4 <= self.Nf <= 128:
+            raise ValueError("temporal filter length must be a multiple of 4 in [4, 128]")
+        if self.w1.shape != (self.F1, self.Nf) or self.w2.shape != (self.K2, self.C):
+            raise ValueError("weight shapes do not match (F1, Nf) / (F1*D, C)")
+        if self.w4.shape != (self.F2, self.K2) or self.w5.shape != (self.N, self.F2 * ((self.T // 8) // 8)):
+            raise ValueError("sep_conv2 / fc shapes do not match")
+        for name in ("fac1", "fac2", "fac4"):
+            if np.any(getattr(self, name) == 0):
+                raise ValueError(f"{name} contains a zero divisor")
+        if self.fac3 == 0 or self.fac5 == 0:
+            raise ValueError("zero scalar divisor")
+        return self
+
+
+def eegnet_params_from_state_dict(net: Mapping, C: int, T: int, F1: int = 8, D: int = 2, F2: Optional[int] = None,
+                                  N: int = 4) -> EEGNetParams:
+    """QuantLab EEGNet state_dict (eegnet.py:100-128 key names) -> EEGNetParams, convert_torch_format.py maths."""
+    K2 = F1 * D
+    if F2 is None:
+        F2 = K2
+    T64 = (T // 8) // 8
+    s = {f"quant{i}": _ste_quant(net, f"quant{i}") for i in range(1, 7)}
+    w1, sw1 = _inq_conv2d(net, "conv1", store_reversed=True)
+    assert w1.ndim == 4 and w1.shape[:3] == (F1, 1, 1), w1.shape
+    Nf = w1.shape[3]
+    bn_s, bn_o = _batch_norm(net, "batch_norm1")
+    fac1, off1 = _div_factor_bn(s["quant1"], sw1, s["quant2"], bn_s, bn_o)
+    w2, sw2 = _inq_conv2d(net, "conv2", store_reversed=True)
+    assert w2.shape == (K2, 1, C, 1), w2.shape
+    bn_s, bn_o = _batch_norm(net, "batch_norm2")
+    fac2, off2 = _div_factor_bn(s["quant2"], sw2, s["quant3"], bn_s, bn_o, pool=8)
+    w3, sw3 = _inq_conv2d(net, "sep_conv1", store_reversed=True)
+    assert w3.shape == (K2, 1, 1, L3_TAPS), w3.shape
+    fac3 = _div_factor(s["quant3"], sw3, s["quant4"])
+    w4, sw4 = _inq_conv2d(net, "sep_conv2", store_reversed=True)
+    assert w4.shape == (F2, K2, 1, 1), w4.shape
+    bn_s, bn_o = _batch_norm(net, "batch_norm3")
+    fac4, off4 = _div_factor_bn(s["quant4"], sw4, s["quant5"], bn_s, bn_o, pool=8)
+    w5, b5, sw5 = _inq_linear(net, "fc")
+    assert w5.shape == (N, F2 * T64), w5.shape
+    fac5 = _div_factor(s["quant5"], sw5, s["quant6"])
+    i32 = lambda a: np.asarray(a, dtype=np.int64).astype(np.int32)
+    for arr in (fac1, off1, fac2, off2, fac4, off4):
+        if np.any(np.abs(arr) > 2**31 - 1):
+            raise OverflowError("requant parameter does not fit int32")
+    return EEGNetParams(
+        C=C, T=T, F1=F1, D=D, F2=F2, N=N, Nf=Nf,
+        w1=w1.reshape(F1, Nf).astype(np.int8), fac1=i32(fac1), off1=i32(off1),
+        w2=w2.reshape(K2, C).astype(np.int8), fac2=i32(fac2), off2=i32(off2),
+        w3=w3.reshape(K2, L3_TAPS).astype(np.int8), fac3=fac3,
+        w4=w4.reshape(F2, K2).astype(np.int8), fac4=i32(fac4), off4=i32(off4),
+        w5=w5.astype(np.int8), b5=b5.astype(np.int8), fac5=fac5,
+        input_scale=float(s["quant1"]), output_scale=float(s["quant6"]),
+        scales={k: float(v) for k, v in s.items()}).validate()

@@ -258,3 +258,94 @@ class Int8Net:
         _lib.check(self._L.mibmi_dequantize_logits_f32(q.data_ptr(), q.numel(), float(abs_max), y.data_ptr(), stream),
                    "mibmi_dequantize_logits_f32")
         return y
+
+
+class EEGNetInt8:
+    """Integer network of the EEGNet / Q-EEGNet layer order (temporal conv first) on one GPU:
+    one mibmi_eegnet handle.  Integer counterpart of QuantLab/quantlab/PhysionetMMMI/EEGNet/eegnet.py:137-168."""
+
+    def __init__(self, params, device=None):
+        from .convert import EEGNetParams
+        if not isinstance(params, EEGNetParams):
+            raise TypeError("EEGNetInt8 takes a convert.EEGNetParams")
+        self.params = params.validate()
+        self.C, self.T, self.F1, self.D, self.F2, self.N, self.Nf = (params.C, params.T, params.F1, params.D, params.F2,
+                                                                   params.N, params.Nf)
+        self.K2, self.T8, self.T64 = params.F1 * params.D, params.T // 8, (params.T // 8) // 8
+        self.device_index = _device_index(device)
+        self.device = torch.device("cuda", self.device_index)
+        self._L = _lib.lib()
+        keep = []
+
+        def ptr(a, dt):
+            a = np.ascontiguousarray(np.asarray(a).ravel(), dtype=dt)
+            keep.append(a)
+            return a.ctypes.data
+
+        p = _lib.EEGNetParamsC(self.C, self.T, self.F1, self.D, self.F2, self.N, self.Nf,
+                               ptr(params.w1, np.int8), ptr(params.fac1, np.int32), ptr(params.off1, np.int32),
+                               ptr(params.w2, np.int8), ptr(params.fac2, np.int32), ptr(params.off2, np.int32),
+                               ptr(params.w3, np.int8), int(params.fac3),
+                               ptr(params.w4, np.int8), ptr(params.fac4, np.int32), ptr(params.off4, np.int32),
+                               ptr(params.w5, np.int8), ptr(params.b5, np.int8), int(params.fac5))
+        h = ctypes.c_void_p()
+        _lib.check(self._L.mibmi_eegnet_create(ctypes.byref(p), self.device_index, ctypes.byref(h)), "mibmi_eegnet_create")
+        del keep
+        self._h = h
+
+    @classmethod
+    def from_state_dict(cls, sd: Mapping, C: int, T: int, F1: int = 8, D: int = 2, F2: Optional[int] = None, N: int = 4,
+                        device=None) -> "EEGNetInt8":
+        from .convert import eegnet_params_from_state_dict
+        return cls(eegnet_params_from_state_dict(sd, C=C, T=T, F1=F1, D=D, F2=F2, N=N), device=device)
+
+    def close(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            self._L.mibmi_eegnet_destroy(h)
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def launch_count(self) -> int:
+        return int(self._L.mibmi_eegnet_launch_count(self._h))
+
+    def _check_x(self, x: torch.Tensor) -> torch.Tensor:
+        if x.dtype != torch.int8 or not x.is_cuda or x.device.index != self.device_index:
+            raise ValueError(f"x must be an int8 tensor on {self.device}")
+        if x.dim() == 4 and x.shape[1] == 1:
+            x = x[:, 0]
+        if x.dim() != 3 or tuple(x.shape[1:]) != (self.C, self.T):
+            raise ValueError(f"x must be [B, {self.C}, {self.T}], got {tuple(x.shape)}")
+        return x.contiguous()
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        """int8 trials [B, C, T] -> int8 logits [B, N]; asynchronous on the current torch CUDA stream."""
+        x = self._check_x(x)
+        out = torch.empty((x.shape[0], self.N), dtype=torch.int8, device=self.device)
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        _lib.check(self._L.mibmi_eegnet_forward_int8(self._h, x.data_ptr(), x.shape[0], out.data_ptr(), stream),
+                   "mibmi_eegnet_forward_int8")
+        return out
+
+    __call__ = forward
+
+    def forward_taps(self, x: torch.Tensor):
+        x = self._check_x(x)
+        B = x.shape[0]
+        out = torch.empty((B, self.N), dtype=torch.int8, device=self.device)
+        taps = {"y2": torch.empty((B, self.K2, self.T8), dtype=torch.int8, device=self.device),
+                "y3": torch.empty((B, self.K2, self.T8), dtype=torch.int8, device=self.device),
+                "y4": torch.empty((B, self.F2, self.T64), dtype=torch.int8, device=self.device)}
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        _lib.check(self._L.mibmi_eegnet_forward_int8_taps(self._h, x.data_ptr(), B, out.data_ptr(), taps["y2"].data_ptr(),
+                                                          taps["y3"].data_ptr(), taps["y4"].data_ptr(), stream),
+                   "mibmi_eegnet_forward_int8_taps")
+        return out, taps
+
+    quantize_input = Int8Net.quantize_input
+    dequantize_logits = Int8Net.dequantize_logits

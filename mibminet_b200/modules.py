@@ -3,6 +3,7 @@
 * `edgeEEGNet`      <- QuantLab/quantlab/{PhysionetMMMI,BCI-CompIV-2a}/edgeEEGNet/edgeEEGnet.py:11-178
                        same constructor keywords, same state_dict keys, `forward(x[B,1,C,T]) -> [B,N]`.
 * `edgeEEGNetQuant` <- edge-eegnet_torch/edgeEEGnet_quant.py:10-107, `forward(x[B,C,T]) -> [B,N]`.
+* `EEGNet`          <- QuantLab/quantlab/PhysionetMMMI/EEGNet/eegnet.py:11-168 (temporal conv first, Nf = 128).
 
 Only inference is implemented (the training behaviour of INQ / STE / dropout is out of scope): the
 forward quantises the float input like `quant1` (STEActivation with floorToZero,
@@ -19,7 +20,7 @@ import torch
 from torch import nn
 
 from .convert import NF, params_from_state_dict
-from .engine import Int8Net
+from .engine import EEGNetInt8, Int8Net
 
 
 class _Quant(nn.Module):
@@ -119,6 +120,86 @@ class edgeEEGNet(nn.Module):
             y = net.forward(x)
         else:
             y = net.forward(net.quantize_input(x))
+        out = net.dequantize_logits(y)
+        if with_stats:
+            stats = [('conv1_w', self.conv1.weight.data), ('conv2_w', self.conv2.weight.data),
+                     ('sep_conv1_w', self.sep_conv1.weight.data), ('sep_conv2_w', self.sep_conv2.weight.data),
+                     ('fc_w', self.fc.weight.data), ('fc_b', self.fc.bias.data)]
+            return stats, out
+        return out
+
+    def forward_with_tensor_stats(self, x):
+        return self.forward(x, with_stats=True)
+
+
+class EEGNet(nn.Module):
+    """Quantized EEGNet / Q-EEGNet (inference): QuantLab/quantlab/PhysionetMMMI/EEGNet/eegnet.py:11-168 -- temporal conv
+    (1, 128) first, then the depthwise spatial conv.  Same constructor keywords and state_dict keys; the forward runs the
+    integer pipeline of mibmi_eegnet.cu (no integer model of this order exists in the reference; it tracks the reference's
+    float-simulated forward within a few LSB, tests/test_eegnet_order.py)."""
+
+    def __init__(self, F1=8, D=2, F2=None, C=22, T=1125, N=4, p_dropout=0.5,
+                 dropout_type='TimeDropout2d', quantWeight=True, quantAct=True,
+                 weightInqSchedule=None, weightInqNumLevels=255, weightInqStrategy="matnitude",
+                 weightInqInitMethod="uniform", actSTENumLevels=255, actSTEStartEpoch=2,
+                 floorToZero=False, actFirstLayerNumLevels=None, weightFirstLayerNumLevels=None,
+                 first_layer_only=False, Nf=128):
+        super().__init__()
+        if F2 is None:
+            F2 = F1 * D
+        if weightInqNumLevels != 255 or actSTENumLevels != 255:
+            raise ValueError("the integer pipeline exists for 255 levels only")
+        self.F1, self.D, self.F2, self.C, self.T, self.N, self.Nf = F1, D, F2, C, T, N, Nf
+        n_features = (T // 8) // 8
+        self.quant1 = _Quant()
+        self.conv1 = _InqParam((F1, 1, 1, Nf))
+        self.batch_norm1 = nn.BatchNorm2d(F1, momentum=0.01, eps=0.001)
+        self.quant2 = _Quant()
+        self.conv2 = _InqParam((D * F1, 1, C, 1))
+        self.batch_norm2 = nn.BatchNorm2d(D * F1, momentum=0.01, eps=0.001)
+        self.quant3 = _Quant()
+        self.sep_conv1 = _InqParam((D * F1, 1, 1, 16))
+        self.quant4 = _Quant()
+        self.sep_conv2 = _InqParam((F2, D * F1, 1, 1))
+        self.batch_norm3 = nn.BatchNorm2d(F2, momentum=0.01, eps=0.001)
+        self.quant5 = _Quant()
+        self.fc = _InqParam((N, F2 * n_features), bias=N)
+        self.quant6 = _Quant()
+        self._engine: Optional[EEGNetInt8] = None
+        self.eval()
+
+    def load_state_dict(self, state_dict, strict: bool = True, **kw):
+        sd = {k: (torch.as_tensor(v) if not torch.is_tensor(v) else v) for k, v in state_dict.items()}
+        r = super().load_state_dict(sd, strict=strict, **kw)
+        self._engine = None
+        return r
+
+    def _apply(self, fn, *a, **kw):
+        self._engine = None
+        return super()._apply(fn, *a, **kw)
+
+    def integer_network(self, device=None) -> EEGNetInt8:
+        dev = torch.device(device) if device is not None else self.quant1.absMaxValue.device
+        if dev.type != "cuda":
+            raise RuntimeError("EEGNet (mibminet_b200) runs on CUDA only: call .cuda() first")
+        idx = dev.index if dev.index is not None else torch.cuda.current_device()
+        if self._engine is None or self._engine.device_index != idx:
+            sd = {k: v.detach().cpu().numpy() for k, v in self.state_dict().items()}
+            self._engine = EEGNetInt8.from_state_dict(sd, C=self.C, T=self.T, F1=self.F1, D=self.D, F2=self.F2, N=self.N,
+                                                      device=torch.device("cuda", idx))
+        return self._engine
+
+    @torch.no_grad()
+    def forward_int8(self, x_int8: torch.Tensor) -> torch.Tensor:
+        return self.integer_network(x_int8.device).forward(x_int8)
+
+    @torch.no_grad()
+    def forward(self, x: torch.Tensor, with_stats: bool = False):
+        # input dimensions: (s, 1, C, T)
+        if x.dim() == 4:
+            x = x[:, 0]
+        net = self.integer_network(x.device)
+        y = net.forward(x if x.dtype == torch.int8 else net.quantize_input(x))
         out = net.dequantize_logits(y)
         if with_stats:
             stats = [('conv1_w', self.conv1.weight.data), ('conv2_w', self.conv2.weight.data),

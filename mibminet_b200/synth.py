@@ -127,3 +127,69 @@ def make_trials(B: int, C: int, T: int, seed: int = 0, dist: str = "uniform") ->
     if dist == "gauss":
         return np.clip(np.round(rng.normal(0.0, 40.0, size=(B, C, T))), -127, 127).astype(np.int8)
     raise ValueError(dist)
+
+
+def make_eegnet_state_dict(C=22, T=1125, F1=8, D=2, N=4, Nf=128, seed=0, negative_gamma=True, calib_trials=3,
+                           sat_quantile=0.995) -> Dict[str, np.ndarray]:
+    """Random-init float net of the EEGNet / Q-EEGNet order (QuantLab/quantlab/PhysionetMMMI/EEGNet/eegnet.py:100-128):
+    conv1 (F1,1,1,Nf), batch_norm1 (F1), conv2 (F1*D,1,C,1), batch_norm2, sep_conv1 (F1*D,1,1,16),
+    sep_conv2 (F2,F1*D,1,1), batch_norm3 (F2), fc (N, F2*T64); quant1..6 calibrated on random trials."""
+    rng = np.random.default_rng(seed)
+    K2 = F2 = F1 * D
+    T8, T64 = T // 8, (T // 8) // 8
+    sd: Dict[str, np.ndarray] = {}
+
+    def add_w(name, shape):
+        w = rng.uniform(-1.0, 1.0, size=shape).astype(np.float32)
+        s = np.float32(np.abs(w).max())
+        sd[f"{name}.weight"] = w
+        sd[f"{name}.weightFrozen"] = _snap(w, s)
+        sd[f"{name}.sParam"] = np.array([s], np.float32)
+
+    add_w("conv1", (F1, 1, 1, Nf))
+    add_w("conv2", (K2, 1, C, 1))
+    add_w("sep_conv1", (K2, 1, 1, 16))
+    add_w("sep_conv2", (F2, K2, 1, 1))
+    add_w("fc", (N, F2 * T64))
+    sd["fc.bias"] = rng.uniform(-0.1, 0.1, size=(N,)).astype(np.float32)
+    for i, n in ((1, F1), (2, K2), (3, F2)):
+        g = rng.uniform(0.5, 1.5, size=(n,))
+        if negative_gamma:
+            g *= rng.choice([-1.0, 1.0], size=(n,), p=[0.3, 0.7])
+        sd[f"batch_norm{i}.weight"] = g.astype(np.float32)
+        sd[f"batch_norm{i}.bias"] = rng.uniform(-0.5, 0.5, size=(n,)).astype(np.float32)
+        sd[f"batch_norm{i}.running_mean"] = rng.uniform(-0.5, 0.5, size=(n,)).astype(np.float32)
+        sd[f"batch_norm{i}.running_var"] = rng.uniform(0.5, 2.0, size=(n,)).astype(np.float32)
+        sd[f"batch_norm{i}.num_batches_tracked"] = np.array(1, np.int64)
+
+    def bn(x, i, axis):
+        g, b, m, v = (sd[f"batch_norm{i}.{k}"].astype(np.float64) for k in ("weight", "bias", "running_mean", "running_var"))
+        sc = g / np.sqrt(v + 1e-3)
+        sh = [1] * x.ndim
+        sh[axis] = -1
+        return x * sc.reshape(sh) + (b - m * sc).reshape(sh)
+
+    def absmax(x):
+        return np.float32(max(np.quantile(np.abs(x), sat_quantile), 1e-3))
+
+    wf = lambda n: sd[f"{n}.weightFrozen"].astype(np.float64)
+    s1 = np.float32(1.0)
+    x = rng.integers(-127, 128, size=(calib_trials, C, T)).astype(np.float64) / 127.0
+    xp = np.pad(x, ((0, 0), (0, 0), (Nf // 2 - 1, Nf // 2)))
+    win = np.lib.stride_tricks.sliding_window_view(xp, Nf, axis=-1)            # [B, C, T, Nf]
+    h = bn(win @ wf("conv1").reshape(F1, Nf).T, 1, 3)                          # [B, C, T, F1]
+    s2 = absmax(h); h = _fakeq(h, float(s2))
+    w2 = wf("conv2").reshape(K2, C)
+    h = np.stack([np.einsum("bct,c->bt", h[..., k // D], w2[k]) for k in range(K2)], 1)   # [B, K2, T]
+    h = np.maximum(bn(h, 2, 1), 0.0)[..., :T8 * 8].reshape(calib_trials, K2, T8, 8).mean(-1)
+    s3 = absmax(h); h = _fakeq(h, float(s3))
+    h = _corr_same(h, wf("sep_conv1").reshape(K2, 16), (7, 8))
+    s4 = absmax(h); h = _fakeq(h, float(s4))
+    h = np.maximum(bn(np.einsum("ki,bit->bkt", wf("sep_conv2").reshape(F2, K2), h), 3, 1), 0.0)
+    h = h[..., :T64 * 8].reshape(calib_trials, F2, T64, 8).mean(-1)
+    s5 = absmax(h); h = _fakeq(h, float(s5))
+    h = h.reshape(calib_trials, -1) @ wf("fc").T + sd["fc.bias"].astype(np.float64)[None]
+    s6 = np.float32(max(np.abs(h).max() * 0.8, 1e-3))
+    for i, s in enumerate((s1, s2, s3, s4, s5, s6), start=1):
+        sd[f"quant{i}.absMaxValue"] = np.array([s], np.float32)
+    return sd
