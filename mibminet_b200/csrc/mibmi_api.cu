@@ -24,7 +24,7 @@ struct mibmi_net {
     bool fused_ok = false;
     const char* fused_why = "";
     PipeNet* pipe_dev = nullptr;       // warp-specialised pipeline kernel (MIBMI_PATH_FUSED)
-    bool pipe_ok = false, pipe_fast1 = false, tc_ok = false;
+    bool pipe_ok = false, pipe_fast1 = false, tc_ok = false, tcr_ok = false;
     const char* pipe_why = "";
     StreamNet* stream_dev = nullptr;   // sliding-window streaming kernel (mibmi_forward_stream_int8)
     bool stream_ok = false;
@@ -520,6 +520,9 @@ int forward_impl(mibmi_net* net, const int8_t* x, int64_t B, int layout, int8_t*
     if (path == MIBMI_PATH_FUSED && net->tc_ok)
         e = launch_tc(net->pipe_dev, net->pipe_fast1, net->C, net->T, x, B, logits, peers ? *peers : none, t1, t2, t3, t4,
                       net->num_sms, stream);
+    else if (path == MIBMI_PATH_FUSED && net->tcr_ok)
+        e = launch_tcr(net->pipe_dev, net->pipe_fast1, net->C, net->T, x, B, logits, peers ? *peers : none, t1, t2, t3, t4,
+                       net->num_sms, stream);
     else if (path == MIBMI_PATH_FUSED || path == MIBMI_PATH_FUSED_PIPE)
         e = launch_pipe(net->pipe_dev, net->pipe_fast1, net->C, net->T, x, B, logits, peers ? *peers : none, t1, t2, t3, t4,
                         net->num_sms, stream);
@@ -534,7 +537,7 @@ int forward_impl(mibmi_net* net, const int8_t* x, int64_t B, int layout, int8_t*
             if (e != cudaSuccess) return fail_cuda(net, e);
         }
     net->last_path.store(path);
-    net->last_kernel.store(path == MIBMI_PATH_FUSED ? (net->tc_ok ? 1 : 2) : path == MIBMI_PATH_FUSED_PIPE ? 2
+    net->last_kernel.store(path == MIBMI_PATH_FUSED ? (net->tc_ok ? 1 : net->tcr_ok ? 6 : 2) : path == MIBMI_PATH_FUSED_PIPE ? 2
                            : path == MIBMI_PATH_FUSED_V1 ? 3 : 4);
     net->launches.fetch_add(1);
     return MIBMI_OK;
@@ -563,9 +566,9 @@ int mibmi_last_cuda_error(const mibmi_net_t* net) { return net ? net->last_cuda.
 int mibmi_last_path(const mibmi_net_t* net) { return net ? net->last_path.load() : 0; }
 const char* mibmi_last_kernel(const mibmi_net_t* net) {
     static const char* const names[] = {"", "tc_forward_kernel", "pipe_forward_kernel", "fused_forward_kernel",
-                                        "generic_forward_kernel", "stream_forward_kernel"};
+                                        "generic_forward_kernel", "stream_forward_kernel", "tcr_forward_kernel"};
     const int k = net ? net->last_kernel.load() : 0;
-    return names[k >= 0 && k <= 5 ? k : 0];
+    return names[k >= 0 && k <= 6 ? k : 0];
 }
 int64_t mibmi_launch_count(const mibmi_net_t* net) { return net ? net->launches.load() : 0; }
 
@@ -646,6 +649,7 @@ int mibmi_create(const mibmi_params_t* p, int device, mibmi_net_t** out) {
     n->pipe_ok = pack_pipe(p, pn, &n->pipe_why);
     n->pipe_fast1 = pn->fast1 != 0;
     n->tc_ok = n->pipe_ok && tc_has_instance(p->C, p->T);
+    n->tcr_ok = n->pipe_ok && tcr_has_instance(p->C, p->T);
     if (n->pipe_ok) n->stream_ok = pack_stream(p, pn, sn, &n->stream_why);
     else n->stream_why = n->pipe_why;
 

@@ -44,6 +44,12 @@ bool tc_has_instance(int C, int T);
 cudaError_t launch_tc(const PipeNet* net_dev, bool fast1, int C, int T, const int8_t* x, long long B, int8_t* logits,
                       const PeerOut& peers, int8_t* t1, int8_t* t2, int8_t* t3, int8_t* t4, int num_sms, cudaStream_t stream);
 
+// Same formulation for trials whose rows are not 16-byte aligned (mibmi_tcr.cu: realigning warps instead of TMA tiles,
+// MMA tiles that straddle trials): 22 x 1125.
+bool tcr_has_instance(int C, int T);
+cudaError_t launch_tcr(const PipeNet* net_dev, bool fast1, int C, int T, const int8_t* x, long long B, int8_t* logits,
+                       const PeerOut& peers, int8_t* t1, int8_t* t2, int8_t* t3, int8_t* t4, int num_sms, cudaStream_t stream);
+
 // Sliding-window streaming kernel (mibmi_stream.cu): x [S][C][L] -> logits [S][W][4], W = (L - T) / 16 + 1.
 // Optional taps: t2i [S][16][2 (W-1) + T/8] stream-level pooled layer-2 samples (interior positions only),
 // t2e [S][W][16][8] the 4 + 4 edge samples of every window, t3 [S][W][16][T/8], t4 [S][W][16][T/64].

@@ -1,0 +1,600 @@
+// tcgen05 / TMEM forward for trials whose rows are NOT 16-byte aligned and whose length is not a multiple of 32
+// (22 x 1125, BASELINE config 3).  Same tensor-core formulation as mibmi_tc.cu (layer 1 = MN-major swizzled tile x W1,
+// layer 2 = Hankel view of the y1 byte array x Toeplitz taps, accumulators in TMEM), with three differences:
+//   * a trial starts at an arbitrary byte, so TMA tiles are impossible: the producer bulk-copies the trial from the
+//     16-byte boundary below it into a raw stage and four REALIGN warps funnel-shift it into the 128-byte-swizzled tile
+//     layout the MMA reads (what the TMA unit does for aligned shapes);
+//   * a trial occupies 73 rows (16 bytes each) of the y1 row buffer, so the 128-row MMA tiles straddle trials: groups of
+//     G = 3 trials = 219 rows = 2 tiles; the layer-2 epilogue maps TMEM lane -> (trial, block of 16 outputs);
+//   * layers 3-5 of a trial run in ONE warp (private y3 / y4), as T/8 = 140 needs 9 blocks of 16 samples.
+// One persistent CTA per SM, 31 warps:
+//   A  0-11  layer-1 epilogue (3 warps per TMEM lane quarter)      layer1.c:96-104
+//   B 12-19  layer-2 epilogue (2 warps per lane quarter)           layer2.c:99-118
+//   C 20-23  layers 3 + 4 + 5 of one trial each                    layer3.c:70, layer4.c:99-140, layer5.c:81-89
+//   R 24-27  realign raw bytes -> swizzled tiles                   (rt_dma_memcpy L2 -> L1, layer1.c:137-154)
+//   P 28     bulk-copy producer     M1 29  layer-1 MMAs (layer1.c:87-96)     M2 30  layer-2 MMAs (layer2.c:87-118)
+// Bit-identical to the reference (tests/test_parity_gpu.py).
+#include <cuda.h>
+#include <string.h>
+
+#include "mibmi_common.cuh"
+#include "mibmi_kernels.h"
+#include "mibmi_ptx.cuh"
+
+namespace mibmi {
+
+#ifndef MIBMI_TCR_SLEEP_NS
+#define MIBMI_TCR_SLEEP_NS 64
+#endif
+#ifdef MIBMI_PROF
+__device__ long long g_prof_tcr[148 * 32 * 4];
+#define RWAIT(slot, ...) do { if (!mbar_test(__VA_ARGS__)) { const long long t0_ = clock64(); mbar_wait_sleep(__VA_ARGS__, MIBMI_TCR_SLEEP_NS); pw_[slot] += clock64() - t0_; } } while (0)
+#define RPROF_BEGIN long long pw_[3] = {0, 0, 0}; const long long pt0_ = clock64();
+#define RPROF_END if ((threadIdx.x & 31) == 0) { long long* o_ = g_prof_tcr + (blockIdx.x * 32 + (threadIdx.x >> 5)) * 4; \
+    o_[0] = clock64() - pt0_; o_[1] = pw_[0]; o_[2] = pw_[1]; o_[3] = pw_[2]; }
+#else
+#define RWAIT(slot, ...) mbar_wait_sleep(__VA_ARGS__, MIBMI_TCR_SLEEP_NS)
+#define RPROF_BEGIN
+#define RPROF_END
+#endif
+
+constexpr int kRAW = 12, kRBW = 8, kRCW = 4, kRRW = 4;
+constexpr int kRWarpB = kRAW, kRWarpC = kRAW + kRBW, kRWarpR = kRWarpC + kRCW, kRWarpP = kRWarpR + kRRW,
+              kRWarpM1 = kRWarpP + 1, kRWarpM2 = kRWarpP + 2;
+constexpr int kRThreads = (kRWarpM2 + 1) * 32;
+
+template <int C_, int T_>
+struct RCfg {
+    static constexpr int C = C_, T = T_, G = 3;
+    static constexpr int TILES = (T + 127) / 128, UNITS = (T + 31) / 32, CHUNKS = (T + 15) / 16;
+    static constexpr int TILE_PITCH = C <= 24 ? 3072 : 4096;                  // rows 24..31 of a tile may alias the next tile (zero weights)
+    static constexpr int XS_BYTES = TILES * TILE_PITCH + (4096 - TILE_PITCH);
+    static constexpr int RAW_BYTES = ((C * T + 15 + 48 + 127) / 128) * 128;      // + misalignment + the realign warps' read-ahead
+    static constexpr int T8 = T / 8, T64 = T8 / 8, VROWS = T8 / 2;            // layer-2 rows (16 conv outputs) per trial
+    static constexpr int SLOT = ((32 + T + 15) / 16) * 16, SROWS = SLOT / 16; // y1 bytes / rows per trial: 32 zeros | T | zeros
+    static constexpr int GROWS = G * SROWS, GT = (GROWS + 127) / 128;
+    static constexpr int CHS = G * SLOT + 96;                                 // y1 row of one filter; / 16 odd
+    static constexpr int NW3 = (T8 + 15) / 16, Y2S = 16 * (NW3 + 1), Y2_TRIAL = 16 * Y2S;
+    static constexpr int Y3CH = 2 * ((NW3 + 1) / 2), Y3S = 16 * (Y3CH + 1), Y3_BYTES = 16 * Y3S;
+    static constexpr int NST = (T64 + 3) / 4, T64P = (T64 + 1) / 2 * 2, KST5 = T64P / 2;
+    static constexpr int Y4_BYTES = ((16 * T64P + 15) / 16) * 16;
+    static constexpr int W2_CH = 16 * 96;
+    // TMEM columns
+    static constexpr int TM_L1_TRIAL = 16 * TILES, TM_L2 = 2 * TM_L1_TRIAL, TM_L2_HALF = 64;
+    // barriers
+    static constexpr int BAR_RAW_FULL = 0, BAR_RAW_EMPTY = 16, BAR_X_FULL = 32, BAR_X_EMPTY = 48, BAR_T1_FULL = 64,
+                         BAR_T1_EMPTY = 80, BAR_Y1_FULL = 96 /* G */, BAR_TILE_DONE = 128 /* GT */, BAR_T2_FULL = 160,
+                         BAR_T2_EMPTY = 176, BAR_Y2_FULL = 192 /* 2 x GT */, BAR_Y2_EMPTY = 232, BAR_END = 248;
+    // shared memory map
+    static constexpr int OFF_TMEM = 248, OFF_C2 = 256, OFF_W1 = 1024, OFF_W2 = 2048;
+    static constexpr int OFF_XS = ((OFF_W2 + 16 * W2_CH + 1023) / 1024) * 1024;
+    static constexpr int OFF_RAW = OFF_XS + 2 * XS_BYTES;
+    static constexpr int OFF_Y1 = OFF_RAW + 2 * RAW_BYTES;
+    static constexpr int OFF_Y2 = OFF_Y1 + 16 * CHS;
+    static constexpr int OFF_Y3 = OFF_Y2 + 2 * G * Y2_TRIAL;
+    static constexpr int OFF_Y4 = OFF_Y3 + kRCW * Y3_BYTES;
+    static constexpr int OFF_W3 = ((OFF_Y4 + kRCW * Y4_BYTES + 127) / 128) * 128;      // w3frag [16][4][32] words
+    static constexpr int OFF_W5 = OFF_W3 + 16 * 4 * 32 * 4;                             // w5frag [KST5][2][32] words
+    static constexpr int SMEM = ((OFF_W5 + KST5 * 2 * 32 * 4 + 127) / 128) * 128;
+    static_assert(C <= 32, "one k-step of 32 channels");
+    static_assert((8 * T8) % 16 == 0 && T8 % 2 == 0, "whole layer-2 rows, sample pairs in layer 3");
+    static_assert(SLOT - 32 - T + 32 >= 8 * T8 + 32 - T, "right padding of layer 2");
+    static_assert((CHS / 16) % 2 == 1, "conflict-free stmatrix");
+    static_assert(G <= 4 && GT <= 4 && 2 * GT <= 5, "barrier slots");
+    static_assert(TM_L2 + 2 * TM_L2_HALF <= 512, "TMEM map");
+    static_assert(NW3 <= 16 && KST5 <= kPipeMaxKst5, "layer 3 / 5 limits");
+    static_assert(XS_BYTES % 1024 == 0 && OFF_XS % 1024 == 0, "swizzle atoms are 1024-byte aligned");
+    static_assert(SMEM <= 227 * 1024, "shared memory");
+    // last tile that reads bytes of y1 slot j / last tile with valid rows of trial j / last trial with valid rows in tile i
+    __host__ __device__ static constexpr int slot_last_tile(int j) { return (SROWS * (j + 1) - 1) / 128 < GT ? (SROWS * (j + 1) - 1) / 128 : GT - 1; }
+    __host__ __device__ static constexpr int trial_last_tile(int j) { return (SROWS * j + VROWS - 1) / 128; }
+    __host__ __device__ static constexpr int tile_last_trial(int i) { return (128 * i + 127) / SROWS < G ? (128 * i + 127) / SROWS : G - 1; }
+};
+
+template <bool FAST>
+__device__ __forceinline__ int tcr_div1(int x, int m, int s) {
+    if (FAST) return __mulhi(x, m) + (int)((unsigned)x >> 31);
+    return (__mulhi(x, m) >> s) + (int)((unsigned)x >> 31);
+}
+__device__ __forceinline__ void tcr_tmem_ld_32x32b_x16(uint32_t (&r)[16], uint32_t taddr) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+                   "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]) : "r"(taddr));
+}
+__device__ __forceinline__ constexpr uint32_t tcr_idesc_i8_kk(int M, int N) {   // both operands K-major (layer 2)
+    return (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+// one row of T samples: lane = 16-byte chunk (+ 32 per pass); all loads of the row are issued before the shifts
+template <class K, int K4>
+__device__ __forceinline__ void tcr_realign_row(const uint8_t* rbase, uint8_t* xrow, int c, int sh, int lane) {
+    constexpr int P = (K::CHUNKS + 31) / 32;
+    uint4 q0[P], q1[P];
+#pragma unroll
+    for (int p = 0; p < P; p++)
+        if (32 * p + 31 < K::CHUNKS || lane + 32 * p < K::CHUNKS) {
+            q0[p] = *reinterpret_cast<const uint4*>(rbase + 512 * p);
+            q1[p] = *reinterpret_cast<const uint4*>(rbase + 512 * p + 16);
+        }
+#pragma unroll
+    for (int p = 0; p < P; p++) {
+        const int jj = lane + 32 * p;
+        if (32 * p + 31 < K::CHUNKS || jj < K::CHUNKS) {
+            const uint32_t w[8] = {q0[p].x, q0[p].y, q0[p].z, q0[p].w, q1[p].x, q1[p].y, q1[p].z, q1[p].w};
+            uint4 o;
+            o.x = __funnelshift_r(w[K4], w[K4 + 1], sh);
+            o.y = __funnelshift_r(w[K4 + 1], w[K4 + 2], sh);
+            o.z = __funnelshift_r(w[K4 + 2], w[K4 + 3], sh);
+            o.w = __funnelshift_r(w[K4 + 3], w[K4 + 4], sh);
+            *reinterpret_cast<uint4*>(xrow + (jj >> 3) * K::TILE_PITCH + (((jj & 7) ^ (c & 7)) << 4)) = o;
+        }
+    }
+}
+
+template <class K, bool FAST1, bool TAPS>
+__global__ void __launch_bounds__(kRThreads, 1)
+tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net, long long B, int8_t* __restrict__ logits,
+                   const PeerOut peers, int8_t* __restrict__ tap1, int8_t* __restrict__ tap2, int8_t* __restrict__ tap3,
+                   int8_t* __restrict__ tap4) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int g = lane >> 2, q = lane & 3;
+    const uint32_t sbase = smem_u32(smem);
+    const long long ngroups_total = (B + K::G - 1) / K::G;
+    const long long firstg = blockIdx.x, strideg = gridDim.x;
+    const int ng = firstg < ngroups_total ? (int)((ngroups_total - firstg + strideg - 1) / strideg) : 0;   // groups of this CTA
+    const int ntr = K::G * ng;                                                                              // trial slots
+    auto trial_of = [&](int n) -> long long { return K::G * (firstg + (long long)(n / K::G) * strideg) + (n % K::G); };
+
+    // ---- prologue ------------------------------------------------------------------------------------
+    if (tid == 0) {
+        for (int i = 0; i < 2; i++) {
+            mbar_init(sbase + K::BAR_RAW_FULL + 8 * i, 1);
+            mbar_init(sbase + K::BAR_RAW_EMPTY + 8 * i, kRRW);
+            mbar_init(sbase + K::BAR_X_FULL + 8 * i, kRRW);
+            mbar_init(sbase + K::BAR_X_EMPTY + 8 * i, 1);            // commit of M1
+            mbar_init(sbase + K::BAR_T1_FULL + 8 * i, 1);            // commit of M1
+            mbar_init(sbase + K::BAR_T1_EMPTY + 8 * i, kRAW);
+            mbar_init(sbase + K::BAR_T2_FULL + 8 * i, 1);            // commit of M2
+            mbar_init(sbase + K::BAR_T2_EMPTY + 8 * i, kRBW / 2);
+            mbar_init(sbase + K::BAR_Y2_EMPTY + 8 * i, K::G);
+            for (int t = 0; t < K::GT; t++) mbar_init(sbase + K::BAR_Y2_FULL + 8 * (K::GT * i + t), kRBW);
+        }
+        for (int j = 0; j < K::G; j++) mbar_init(sbase + K::BAR_Y1_FULL + 8 * j, kRAW);
+        for (int t = 0; t < K::GT; t++) mbar_init(sbase + K::BAR_TILE_DONE + 8 * t, 1);      // commit of M2
+        mbar_fence_init();
+    }
+    for (int i = tid; i < 16 * 32 / 4; i += kRThreads)
+        reinterpret_cast<uint32_t*>(smem + K::OFF_W1)[i] = reinterpret_cast<const uint32_t*>(net->w1umma)[i];
+    for (int i = tid; i < 16 * K::W2_CH / 16; i += kRThreads)
+        reinterpret_cast<uint4*>(smem + K::OFF_W2)[i] = reinterpret_cast<const uint4*>(net->w2umma)[i];
+    for (int i = tid; i < 16 * 8; i += kRThreads) {
+        const int k = i >> 3, f = i & 7;
+        reinterpret_cast<int*>(smem + K::OFF_C2)[i] = f == 0 ? net->thr2[k] : f == 1 ? net->sig2[k] : f == 2 ? net->soff2[k]
+                                                      : f == 3 ? net->m2[k] : f == 4 ? net->sh2[k] : 0;
+    }
+    {
+        uint4* z = reinterpret_cast<uint4*>(smem + K::OFF_XS);     // tiles (rows >= C are read with zero weights), y1 gaps, y2 / y3 padding
+        for (int i = tid; i < (K::OFF_W3 - K::OFF_XS) / 16; i += kRThreads) z[i] = make_uint4(0, 0, 0, 0);
+    }
+    for (int i = tid; i < 16 * 4 * 32; i += kRThreads)
+        reinterpret_cast<uint32_t*>(smem + K::OFF_W3)[i] = (&net->w3frag[0][0][0])[i];
+    for (int i = tid; i < K::KST5 * 2 * 32; i += kRThreads)
+        reinterpret_cast<uint32_t*>(smem + K::OFF_W5)[i] = (&net->w5frag[0][0][0])[i];
+    if (warp == kRWarpM1) tmem_alloc(sbase + K::OFF_TMEM, 512);
+    fence_proxy_async();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *reinterpret_cast<const uint32_t*>(smem + K::OFF_TMEM);
+    RPROF_BEGIN
+
+    if (warp < kRAW) {
+        // =====================================================================================
+        // A: layer-1 epilogue.  TMEM lanes 32 (warp & 3) .. + 31 of the tiles jt = (warp >> 2) + n (mod 3), + 3, ...
+        // =====================================================================================
+        int off1[2][2], mg1[2][2], sh1[2][2];
+#pragma unroll
+        for (int nt = 0; nt < 2; nt++)
+#pragma unroll
+            for (int e = 0; e < 2; e++) {
+                off1[nt][e] = net->off1[8 * nt + 2 * q + e];
+                mg1[nt][e] = net->m1[8 * nt + 2 * q + e];
+                sh1[nt][e] = net->sh1[8 * nt + 2 * q + e];
+            }
+        // stmatrix.trans: matrix j = lane >> 3 = 2 mt + nt: filters 8 nt .. + 7 (rows), samples 16 mt .. + 15
+        const uint32_t st_off = sbase + K::OFF_Y1 + ((lane & 7) + 8 * ((lane >> 3) & 1)) * K::CHS + 16 * (lane >> 4) + 32;
+        const int qi = warp & 3, a3 = warp >> 2;
+        for (int n = 0; n < ntr; n++) {
+            const int gq = n / K::G, j = n - gq * K::G, ab = n & 1;
+            RWAIT(0, sbase + K::BAR_T1_FULL + 8 * ab, (n >> 1) & 1);
+            tc_fence_after();
+            // slot j of the previous group must have been read by every tile that touches it
+            RWAIT(1, sbase + K::BAR_TILE_DONE + 8 * K::slot_last_tile(j), (gq & 1) ^ 1);
+            const uint32_t yb = st_off + K::SLOT * j;
+            const long long b = trial_of(n);
+            // the warp's tiles jt0, jt0 + 3, ...: the TMEM load of the next unit is in flight while this one is requantised
+            const int jt0 = (a3 + n) % 3;
+            const uint32_t ta0 = tmem_base + ((uint32_t)(32 * qi) << 16) + ab * K::TM_L1_TRIAL;
+            uint32_t r[2][2][8];
+            if (32 * (4 * jt0 + qi) < K::T) {
+                tmem_ld_16x256b_x2(r[0][0], ta0 + 16 * jt0);
+                tmem_ld_16x256b_x2(r[0][1], ta0 + 16 * jt0 + (16u << 16));
+            }
+#pragma unroll
+            for (int it = 0; it < (K::TILES + 2) / 3; it++) {
+                const int jt = jt0 + 3 * it, u = 4 * jt + qi;
+                if (jt >= K::TILES || 32 * u >= K::T) break;
+                tmem_ld_wait();
+                if (it + 1 < (K::TILES + 2) / 3 && jt + 3 < K::TILES && 32 * (u + 12) < K::T) {
+                    tmem_ld_16x256b_x2(r[(it + 1) & 1][0], ta0 + 16 * (jt + 3));
+                    tmem_ld_16x256b_x2(r[(it + 1) & 1][1], ta0 + 16 * (jt + 3) + (16u << 16));
+                }
+                uint32_t w[2][2];
+#pragma unroll
+                for (int mt = 0; mt < 2; mt++)
+#pragma unroll
+                    for (int nt = 0; nt < 2; nt++) {
+                        int v[4];
+#pragma unroll
+                        for (int c = 0; c < 4; c++)
+                            v[c] = tcr_div1<FAST1>((int)r[it & 1][mt][4 * nt + c] + off1[nt][c & 1], mg1[nt][c & 1], sh1[nt][c & 1]);
+                        w[mt][nt] = pack4_sat(v[0], v[1], v[2], v[3]);
+                        if (TAPS && tap1 && b < B)
+#pragma unroll
+                            for (int c = 0; c < 4; c++) {
+                                const int f = 8 * nt + 2 * q + (c & 1), t = 32 * u + 16 * mt + g + 8 * (c >> 1);
+                                if (t < K::T) tap1[((size_t)b * 16 + f) * K::T + t] = (int8_t)clip8(v[c]);
+                            }
+                    }
+                if (32 * u + 32 > K::T) {                   // samples >= T are layer 2's zero padding (warp-uniform branch)
+#pragma unroll
+                    for (int mt = 0; mt < 2; mt++) {
+                        const int lim = K::T - 32 * u - 16 * mt;       // bytes 0, 1 = sample g, bytes 2, 3 = sample g + 8
+                        const uint32_t m = (g < lim ? 0x0000ffffu : 0u) | (g + 8 < lim ? 0xffff0000u : 0u);
+                        w[mt][0] &= m;
+                        w[mt][1] &= m;
+                    }
+                }
+                stsm_t8_x4(yb + 32 * u, w[0][0], w[0][1], w[1][0], w[1][1]);
+            }
+            tc_fence_before();
+            fence_proxy_async();          // y1 is read by the tensor core (async proxy)
+            __syncwarp();
+            if (lane == 0) {
+                mbar_arrive(sbase + K::BAR_T1_EMPTY + 8 * ab);
+                mbar_arrive(sbase + K::BAR_Y1_FULL + 8 * j);
+            }
+        }
+    } else if (warp == kRWarpP) {
+        // =====================================================================================
+        // P: one bulk copy per trial, from the 16-byte boundary below its first byte
+        // =====================================================================================
+        if (lane == 0) {
+            for (int n = 0; n < ntr; n++) {
+                const int st = n & 1;
+                RWAIT(0, sbase + K::BAR_RAW_EMPTY + 8 * st, ((n >> 1) & 1) ^ 1);
+                const long long b = trial_of(n);
+                const uint32_t bar = sbase + K::BAR_RAW_FULL + 8 * st;
+                if (b < B) {
+                    const unsigned long long o = (unsigned long long)b * (K::C * K::T);
+                    const unsigned long long a0 = o & ~15ull;
+                    const uint32_t len = (uint32_t)(((o + K::C * K::T + 15) & ~15ull) - a0);
+                    mbar_expect_tx(bar, len);
+                    bulk_g2s(sbase + K::OFF_RAW + st * K::RAW_BYTES, x + a0, len, bar);
+                } else {
+                    mbar_arrive(bar);     // padding trial of the last group: nothing to read
+                }
+            }
+        }
+    } else if (warp >= kRWarpR && warp < kRWarpP) {
+        // =====================================================================================
+        // R: raw bytes -> [C][128 samples] tiles with the 128-byte swizzle (16-byte chunk j of row c at j ^ (c & 7))
+        // =====================================================================================
+        const int rw = warp - kRWarpR;
+        for (int n = 0; n < ntr; n++) {
+            const int st = n & 1;
+            RWAIT(0, sbase + K::BAR_RAW_FULL + 8 * st, (n >> 1) & 1);
+            RWAIT(1, sbase + K::BAR_X_EMPTY + 8 * st, ((n >> 1) & 1) ^ 1);
+            const long long b = trial_of(n);
+            if (b < B) {
+                const int o15 = (int)(((unsigned long long)b * (K::C * K::T)) & 15);
+                const uint8_t* raw = smem + K::OFF_RAW + st * K::RAW_BYTES;
+                uint8_t* xs = smem + K::OFF_XS + st * K::XS_BYTES;
+                for (int c = rw; c < K::C; c += kRRW) {
+                    const int src0 = o15 + c * K::T;                       // first byte of the row in the raw stage
+                    const int sh = 8 * (src0 & 3);                         // warp-uniform byte shift, word shift below
+                    const uint8_t* rbase = raw + (src0 & ~15) + 16 * lane;
+                    uint8_t* xrow = xs + c * 128;
+                    switch ((src0 >> 2) & 3) {
+                        case 0: tcr_realign_row<K, 0>(rbase, xrow, c, sh, lane); break;
+                        case 1: tcr_realign_row<K, 1>(rbase, xrow, c, sh, lane); break;
+                        case 2: tcr_realign_row<K, 2>(rbase, xrow, c, sh, lane); break;
+                        default: tcr_realign_row<K, 3>(rbase, xrow, c, sh, lane); break;
+                    }
+                }
+            }
+            fence_proxy_async();          // the tiles are read by the tensor core (async proxy)
+            __syncwarp();
+            if (lane == 0) {
+                mbar_arrive(sbase + K::BAR_X_FULL + 8 * st);
+                mbar_arrive(sbase + K::BAR_RAW_EMPTY + 8 * st);
+            }
+        }
+    }
+    else if (warp == kRWarpM1) {
+        // =====================================================================================
+        // M1: layer-1 MMAs, one per tile (K = 32 channels covers C)
+        // =====================================================================================
+        constexpr uint32_t idesc = umma_idesc_i8(128, 16);
+        const uint64_t da0 = umma_desc(sbase + K::OFF_XS, 16, 1024, 2), db0 = umma_desc(sbase + K::OFF_W1, 128, 256, 0);
+        const uint32_t a_hi = (uint32_t)(da0 >> 32), b_hi = (uint32_t)(db0 >> 32), b_lo0 = (uint32_t)db0;
+        for (int n = 0; n < ntr; n++) {
+            const int st = n & 1, ab = n & 1;
+            RWAIT(0, sbase + K::BAR_X_FULL + 8 * st, (n >> 1) & 1);
+            RWAIT(1, sbase + K::BAR_T1_EMPTY + 8 * ab, ((n >> 1) & 1) ^ 1);
+            tc_fence_after();
+            const uint32_t a_lo = (uint32_t)da0 + st * (K::XS_BYTES >> 4);
+            const uint32_t td = tmem_base + ab * K::TM_L1_TRIAL;
+            if (elect_one()) {
+#pragma unroll
+                for (int j = 0; j < K::TILES; j++)
+                    umma_i8_lohi(td + 16 * j, a_lo + ((j * K::TILE_PITCH) >> 4), a_hi, b_lo0, b_hi, idesc, 0);
+                umma_commit(sbase + K::BAR_X_EMPTY + 8 * st);
+                umma_commit(sbase + K::BAR_T1_FULL + 8 * ab);
+            }
+            __syncwarp();
+        }
+    } else if (warp == kRWarpM2) {
+        // =====================================================================================
+        // M2: layer-2 MMAs: per tile of 128 rows, 4 batches of 4 channels x 3 k-steps into alternating TMEM halves
+        // =====================================================================================
+        constexpr uint32_t idesc = tcr_idesc_i8_kk(128, 16);
+        const uint64_t da0 = umma_desc(sbase + K::OFF_Y1, 16, 128, 0), db0 = umma_desc(sbase + K::OFF_W2, 128, 768, 0);
+        const uint32_t a_hi = (uint32_t)(da0 >> 32), b_hi = (uint32_t)(db0 >> 32), b_lo0 = (uint32_t)db0, a_lo0 = (uint32_t)da0;
+        for (int gq = 0; gq < ng; gq++) {
+            int waited = -1;
+#pragma unroll
+            for (int i = 0; i < K::GT; i++) {
+                for (int j = waited + 1; j <= K::tile_last_trial(i); j++) RWAIT(0, sbase + K::BAR_Y1_FULL + 8 * j, gq & 1);
+                waited = K::tile_last_trial(i);
+                tc_fence_after();
+#pragma unroll
+                for (int bt = 0; bt < 4; bt++) {
+                    const int h = bt & 1;
+                    const int use = (gq * K::GT + i) * 2 + (bt >> 1);          // how often this half has been used before
+                    RWAIT(1, sbase + K::BAR_T2_EMPTY + 8 * h, (use & 1) ^ 1);
+                    tc_fence_after();
+                    if (elect_one()) {
+#pragma unroll
+                        for (int c = 0; c < 4; c++)
+#pragma unroll
+                            for (int ks = 0; ks < 3; ks++) {
+                                const int k = 4 * bt + c;
+                                umma_i8_lohi(tmem_base + K::TM_L2 + K::TM_L2_HALF * h + 16 * c,
+                                             a_lo0 + ((k * K::CHS + 2048 * i + 32 * ks) >> 4), a_hi,
+                                             b_lo0 + ((k * K::W2_CH + 256 * ks) >> 4), b_hi, idesc, ks > 0);
+                            }
+                        umma_commit(sbase + K::BAR_T2_FULL + 8 * h);
+                        if (bt == 3) umma_commit(sbase + K::BAR_TILE_DONE + 8 * i);
+                    }
+                    __syncwarp();
+                }
+            }
+        }
+    } else if (warp >= kRWarpB && warp < kRWarpC) {
+        // =====================================================================================
+        // B: layer-2 epilogue.  Thread = TMEM lane = row 128 i + 32 (warp & 3) + lane of the group's y1 buffer
+        //    = 16 consecutive conv outputs (two pooling groups) of trial row / SROWS; channels 4 (2 bb + h) .. + 3
+        // =====================================================================================
+        const int wb = warp - kRWarpB, qi = warp & 3, h = wb >> 2;
+        const int4* c2 = reinterpret_cast<const int4*>(smem + K::OFF_C2);
+        for (int gq = 0; gq < ng; gq++) {
+            const int gpar = gq & 1;
+            RWAIT(1, sbase + K::BAR_Y2_EMPTY + 8 * gpar, ((gq >> 1) & 1) ^ 1);     // the C warps have consumed y2[gpar] of group gq - 2
+#pragma unroll 1
+            for (int i = 0; i < K::GT; i++) {
+                const int row = 128 * i + 32 * qi + lane;
+                const int j = row / K::SROWS, blk = row - j * K::SROWS;
+                const bool valid = j < K::G && blk < K::VROWS;
+                const long long b = K::G * (firstg + (long long)gq * strideg) + j;
+                uint8_t* y2s = smem + K::OFF_Y2 + (gpar * K::G + (j < K::G ? j : 0)) * K::Y2_TRIAL + 8 + 2 * blk;
+#pragma unroll 1
+                for (int bb = 0; bb < 2; bb++) {
+                    const int bt = 2 * bb + h;
+                    const int use = (gq * K::GT + i) * 2 + bb;
+                    RWAIT(0, sbase + K::BAR_T2_FULL + 8 * h, use & 1);
+                    tc_fence_after();
+#pragma unroll
+                    for (int cp = 0; cp < 2; cp++) {
+                        uint32_t r[2][16];
+#pragma unroll
+                        for (int c = 0; c < 2; c++)
+                            tcr_tmem_ld_32x32b_x16(r[c], tmem_base + ((uint32_t)(32 * qi) << 16) + K::TM_L2 + K::TM_L2_HALF * h + 16 * (2 * cp + c));
+                        tmem_ld_wait();
+                        if (cp == 1) {
+                            tc_fence_before();
+                            __syncwarp();
+                            if (lane == 0) mbar_arrive(sbase + K::BAR_T2_EMPTY + 8 * h);
+                        }
+#pragma unroll
+                        for (int c = 0; c < 2; c++) {
+                            const int k = 4 * bt + 2 * cp + c;
+                            const int4 ca = c2[2 * k];                       // thr, sig, soff, m
+                            const int shk = reinterpret_cast<const int*>(smem + K::OFF_C2)[8 * k + 4];
+                            int s0 = 0, s1 = 0;
+#pragma unroll
+                            for (int e = 0; e < 8; e++) {
+                                s0 += max((int)r[c][e], ca.x);
+                                s1 += max((int)r[c][8 + e], ca.x);
+                            }
+                            const int o0 = clip8(tdiv_magic(s0 * ca.y + ca.z, ca.w, shk));
+                            const int o1 = clip8(tdiv_magic(s1 * ca.y + ca.z, ca.w, shk));
+                            if (valid) {
+                                *reinterpret_cast<uint16_t*>(y2s + k * K::Y2S) = (uint16_t)((o0 & 0xff) | ((o1 & 0xff) << 8));
+                                if (TAPS && tap2 && b < B) {
+                                    int8_t* o = tap2 + ((size_t)b * 16 + k) * K::T8 + 2 * blk;
+                                    o[0] = (int8_t)o0;
+                                    o[1] = (int8_t)o1;
+                                }
+                            }
+                        }
+                    }
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(sbase + K::BAR_Y2_FULL + 8 * (K::GT * gpar + i));
+            }
+        }
+    } else if (warp >= kRWarpC && warp < kRWarpR) {
+        // =====================================================================================
+        // C: layers 3 + 4 + 5 of the trials n = cj (mod 4); y3 / y4 are private to the warp
+        // =====================================================================================
+        const int cj = warp - kRWarpC;
+        const uint32_t w4a0 = net->w4frag[0][lane], w4a1 = net->w4frag[1][lane];
+        const int thr_lo = net->thr4[g], thr_hi = net->thr4[g + 8];
+        const int sig_lo = net->sig4[g], sig_hi = net->sig4[g + 8];
+        const int soff_lo = net->soff4[g], soff_hi = net->soff4[g + 8];
+        const int m4_lo = net->m4[g], m4_hi = net->m4[g + 8], sh4_lo = net->sh4[g], sh4_hi = net->sh4[g + 8];
+        const int b5 = net->b5[g & 3], m5 = net->m5, sh5 = net->sh5;
+        const int m3 = net->m3, sh3 = net->sh3;
+        // ldmatrix.x4 lane addressing: matrix j = lane >> 3, row (lane & 7) + 8 (j & 1), k-half j >> 1
+        const int lrow = (lane & 7) + 8 * ((lane >> 3) & 1);
+        const int l3_row = lrow < K::NW3 ? lrow : K::NW3 - 1;
+        const uint32_t l3_off = 16 * (l3_row + (lane >> 4));
+        uint8_t* y3 = smem + K::OFF_Y3 + cj * K::Y3_BYTES;
+        uint8_t* y4 = smem + K::OFF_Y4 + cj * K::Y4_BYTES;
+        const uint32_t* y4w = reinterpret_cast<const uint32_t*>(y4);
+        const uint32_t* w3s = reinterpret_cast<const uint32_t*>(smem + K::OFF_W3) + lane;
+        const uint32_t* w5s = reinterpret_cast<const uint32_t*>(smem + K::OFF_W5) + lane;
+        // layer-3 stores: sample t = 16 i + 8 v + 2 q (+1) goes to chunk 2 (i >> 1) + (q >> 1), position
+        // 8 (q & 1) + 4 (i & 1) + 2 v: the order layer 4 wants (pooling group = MMA column pair)
+        const uint32_t y3_thr = 16 * (q >> 1) + 8 * (q & 1);
+        const uint32_t y3a = smem_u32(y3) + (lane & 15) * K::Y3S + 16 * (lane >> 4);
+        for (int n = cj; n < ntr; n += kRCW) {
+            const int gq = n / K::G, j = n - gq * K::G, gpar = gq & 1;
+            const long long b = trial_of(n);
+            RWAIT(0, sbase + K::BAR_Y2_FULL + 8 * (K::GT * gpar + K::trial_last_tile(j)), (gq >> 1) & 1);
+            const uint32_t y2a = sbase + K::OFF_Y2 + (gpar * K::G + j) * K::Y2_TRIAL + l3_off;
+#pragma unroll 4
+            for (int k = 0; k < 16; k++) {
+                uint32_t a[4];
+                ldsm_x4(a, y2a + k * K::Y2S);
+                int c3[2][4];
+#pragma unroll
+                for (int v = 0; v < 2; v++) {
+                    c3[v][0] = c3[v][1] = c3[v][2] = c3[v][3] = 0;
+                    mma_k32(c3[v], a, w3s[(4 * k + 2 * v) * 32], w3s[(4 * k + 2 * v + 1) * 32]);
+                }
+                uint8_t* y3b = y3 + k * K::Y3S + y3_thr;
+#pragma unroll
+                for (int half = 0; half < (K::NW3 > 8 ? 2 : 1); half++) {
+                    const int i = g + 8 * half;
+#pragma unroll
+                    for (int v = 0; v < 2; v++) {
+                        const int t = 16 * i + 8 * v + 2 * q;
+                        const uint32_t w = pack2_sat(tdiv_magic(c3[v][2 * half], m3, sh3), tdiv_magic(c3[v][2 * half + 1], m3, sh3));
+                        if (t < K::T8) {
+                            *reinterpret_cast<uint16_t*>(y3b + 32 * (i >> 1) + 4 * (i & 1) + 2 * v) = (uint16_t)w;
+                            if (TAPS && tap3 && b < B) {
+                                tap3[((size_t)b * 16 + k) * K::T8 + t] = (int8_t)(w & 0xff);
+                                tap3[((size_t)b * 16 + k) * K::T8 + t + 1] = (int8_t)((w >> 8) & 0xff);
+                            }
+                        }
+                    }
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(sbase + K::BAR_Y2_EMPTY + 8 * gpar);      // this trial's y2 buffer is free again
+#pragma unroll 1
+            for (int s4 = 0; s4 < K::NST; s4++) {
+                uint32_t d[4];
+                ldsm_t_x2(d, y3a + 32 * s4);
+                int c[4][4];
+#pragma unroll
+                for (int v = 0; v < 4; v++) {
+                    c[v][0] = c[v][1] = c[v][2] = c[v][3] = 0;
+                    mma_k16(c[v], w4a0, w4a1, d[v]);
+                }
+                int s_lo = 0, s_hi = 0;
+#pragma unroll
+                for (int v = 0; v < 4; v++) {
+                    s_lo += max(c[v][0], thr_lo) + max(c[v][1], thr_lo);
+                    s_hi += max(c[v][2], thr_hi) + max(c[v][3], thr_hi);
+                }
+                const int grp = 4 * s4 + q;
+                const int o_lo = clip8(tdiv_magic(s_lo * sig_lo + soff_lo, m4_lo, sh4_lo));
+                const int o_hi = clip8(tdiv_magic(s_hi * sig_hi + soff_hi, m4_hi, sh4_hi));
+                if (grp < K::T64) {
+                    y4[g * K::T64P + grp] = (uint8_t)o_lo;
+                    y4[(g + 8) * K::T64P + grp] = (uint8_t)o_hi;
+                    if (TAPS && tap4 && b < B) {
+                        tap4[((size_t)b * 16 + g) * K::T64 + grp] = (int8_t)o_lo;
+                        tap4[((size_t)b * 16 + g + 8) * K::T64 + grp] = (int8_t)o_hi;
+                    }
+                }
+            }
+            __syncwarp();
+            // ---- layer 5: D[class][0] = W5[class][k, t] . y4[k, t]; only MMA column 0 carries data
+            int z[4] = {0, 0, 0, 0};
+#pragma unroll
+            for (int ks = 0; ks < K::KST5; ks++) {
+                const uint32_t a[4] = {w5s[(2 * ks) * 32], 0u, w5s[(2 * ks + 1) * 32], 0u};
+                const uint32_t bb0 = g == 0 ? y4w[8 * ks + q] : 0u, bb1 = g == 0 ? y4w[8 * ks + 4 + q] : 0u;
+                mma_k32(z, a, bb0, bb1);
+            }
+            if (q == 0 && g < 4 && b < B) {
+                const int8_t o = (int8_t)clip8(tdiv_magic(z[0] + b5, m5, sh5));
+                logits[(size_t)b * 4 + g] = o;
+                for (int i = 0; i < peers.n; i++) peers.p[i][(size_t)b * 4 + g] = o;    // fused all-gather (NVLink P2P)
+            }
+            __syncwarp();   // y3 / y4 are rewritten by the warp's next trial
+        }
+    }
+    RPROF_END
+    tc_fence_before();
+    __syncthreads();
+    if (warp == kRWarpM1) tmem_dealloc(tmem_base, 512);
+}
+
+// ---------------------------------------------------------------------------------------------
+template <int C, int T>
+static cudaError_t launch_tcr_instance(const PipeNet* net_dev, bool fast1, const int8_t* x, long long B, int8_t* logits,
+                                       const PeerOut& peers, int8_t* t1, int8_t* t2, int8_t* t3, int8_t* t4, int num_sms,
+                                       cudaStream_t stream) {
+    using K = RCfg<C, T>;
+    const bool taps = t1 || t2 || t3 || t4;
+    auto kern = taps ? tcr_forward_kernel<K, false, true>
+                     : (fast1 ? tcr_forward_kernel<K, true, false> : tcr_forward_kernel<K, false, false>);
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, K::SMEM);
+    if (e != cudaSuccess) return e;
+    long long grid = num_sms;
+    const long long groups = (B + K::G - 1) / K::G;
+    if (grid > groups) grid = groups;
+    kern<<<(unsigned)grid, kRThreads, K::SMEM, stream>>>(x, net_dev, B, logits, peers, t1, t2, t3, t4);
+    return cudaGetLastError();
+}
+
+#define MIBMI_TCR_SHAPES(X) X(22, 1125)
+
+bool tcr_has_instance(int C, int T) {
+#define X(c, t) if (C == c && T == t) return true;
+    MIBMI_TCR_SHAPES(X)
+#undef X
+    return false;
+}
+
+cudaError_t launch_tcr(const PipeNet* net_dev, bool fast1, int C, int T, const int8_t* x, long long B, int8_t* logits,
+                       const PeerOut& peers, int8_t* t1, int8_t* t2, int8_t* t3, int8_t* t4, int num_sms, cudaStream_t stream) {
+#define X(c, t) if (C == c && T == t) return launch_tcr_instance<c, t>(net_dev, fast1, x, B, logits, peers, t1, t2, t3, t4, num_sms, stream);
+    MIBMI_TCR_SHAPES(X)
+#undef X
+    return cudaErrorInvalidValue;
+}
+
+}  // namespace mibmi
+
+#ifdef MIBMI_PROF
+extern "C" __attribute__((visibility("default"))) int mibmi_debug_prof_tcr(long long* out_host) {
+    return (int)cudaMemcpyFromSymbol(out_host, mibmi::g_prof_tcr, sizeof(mibmi::g_prof_tcr));
+}
+#endif
