@@ -33,11 +33,13 @@ METRIC = "int8 edgeEEGNet trials/sec"
 # ncu --set full (profiles/r1d_ncu_full_metrics.csv, tc_forward_kernel<TCfg<64,480>>): 2.013485 GB read + 18.797 MB written
 # per launch of 65536 trials
 NCU_TRAFFIC_BYTES_PER_TRIAL = (2.013485e9 + 18.797056e6) / 65536
-KERNEL_TEMPLATES = {"tc_forward_kernel": "tc_forward_kernel<TCfg<{C},{T}>>", "pipe_forward_kernel": "pipe_forward_kernel<PCfg<{C},{T},4>>",
+KERNEL_TEMPLATES = {"tc_forward_kernel": "tc_forward_kernel<TCfg<{C},{T}>>", "tcr_forward_kernel": "tcr_forward_kernel<RCfg<{C},{T}>>", "pipe_forward_kernel": "pipe_forward_kernel<PCfg<{C},{T},4>>",
                     "fused_forward_kernel": "fused_forward_kernel<Cfg<{C},{T}>>"}
 KERNEL_NOTES = {
     "tc_forward_kernel": "layers 1+2 on tcgen05.mma kind::i8 (TMEM accumulators), 23 warps requantise; ncu r1d: DRAM 67 % of "
                          "ncu peak, issue slots 59 %, not pipe bound: per-trial hand-off latency between the roles, see DESIGN.md 4.1",
+    "tcr_forward_kernel": "tcgen05 kernel with realigning warps (rows not 16-byte aligned): issue bound, 9.4 k warp-instructions per "
+                          "trial (2.34 x the requant work of 64x480 on 0.8 x the bytes), ncu r1e, see DESIGN.md 4.1b",
     "pipe_forward_kernel": "mma.sync pipeline kernel (shape without a tcgen05 instance): issue / dependent-latency bound, "
                            "see DESIGN.md 4.2",
 }

@@ -26,14 +26,19 @@ namespace mibmi {
 #ifndef MIBMI_TCR_SLEEP_NS
 #define MIBMI_TCR_SLEEP_NS 64
 #endif
+#ifndef MIBMI_TCR_SLEEP_LONG_NS
+#define MIBMI_TCR_SLEEP_LONG_NS 128       // waits with a trial's worth of slack (producer, M1, free-buffer waits)
+#endif
 #ifdef MIBMI_PROF
 __device__ long long g_prof_tcr[148 * 32 * 4];
 #define RWAIT(slot, ...) do { if (!mbar_test(__VA_ARGS__)) { const long long t0_ = clock64(); mbar_wait_sleep(__VA_ARGS__, MIBMI_TCR_SLEEP_NS); pw_[slot] += clock64() - t0_; } } while (0)
+#define RWAITL(slot, ...) do { if (!mbar_test(__VA_ARGS__)) { const long long t0_ = clock64(); mbar_wait_sleep(__VA_ARGS__, MIBMI_TCR_SLEEP_LONG_NS); pw_[slot] += clock64() - t0_; } } while (0)
 #define RPROF_BEGIN long long pw_[3] = {0, 0, 0}; const long long pt0_ = clock64();
 #define RPROF_END if ((threadIdx.x & 31) == 0) { long long* o_ = g_prof_tcr + (blockIdx.x * 32 + (threadIdx.x >> 5)) * 4; \
     o_[0] = clock64() - pt0_; o_[1] = pw_[0]; o_[2] = pw_[1]; o_[3] = pw_[2]; }
 #else
 #define RWAIT(slot, ...) mbar_wait_sleep(__VA_ARGS__, MIBMI_TCR_SLEEP_NS)
+#define RWAITL(slot, ...) mbar_wait_sleep(__VA_ARGS__, MIBMI_TCR_SLEEP_LONG_NS)
 #define RPROF_BEGIN
 #define RPROF_END
 #endif
@@ -210,7 +215,7 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
             RWAIT(0, sbase + K::BAR_T1_FULL + 8 * ab, (n >> 1) & 1);
             tc_fence_after();
             // slot j of the previous group must have been read by every tile that touches it
-            RWAIT(1, sbase + K::BAR_TILE_DONE + 8 * K::slot_last_tile(j), (gq & 1) ^ 1);
+            RWAITL(1, sbase + K::BAR_TILE_DONE + 8 * K::slot_last_tile(j), (gq & 1) ^ 1);
             const uint32_t yb = st_off + K::SLOT * j;
             const long long b = trial_of(n);
             // the warp's tiles jt0, jt0 + 3, ...: the TMEM load of the next unit is in flight while this one is requantised
@@ -273,7 +278,7 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
         if (lane == 0) {
             for (int n = 0; n < ntr; n++) {
                 const int st = n & 1;
-                RWAIT(0, sbase + K::BAR_RAW_EMPTY + 8 * st, ((n >> 1) & 1) ^ 1);
+                RWAITL(0, sbase + K::BAR_RAW_EMPTY + 8 * st, ((n >> 1) & 1) ^ 1);
                 const long long b = trial_of(n);
                 const uint32_t bar = sbase + K::BAR_RAW_FULL + 8 * st;
                 if (b < B) {
@@ -295,7 +300,7 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
         for (int n = 0; n < ntr; n++) {
             const int st = n & 1;
             RWAIT(0, sbase + K::BAR_RAW_FULL + 8 * st, (n >> 1) & 1);
-            RWAIT(1, sbase + K::BAR_X_EMPTY + 8 * st, ((n >> 1) & 1) ^ 1);
+            RWAITL(1, sbase + K::BAR_X_EMPTY + 8 * st, ((n >> 1) & 1) ^ 1);
             const long long b = trial_of(n);
             if (b < B) {
                 const int o15 = (int)(((unsigned long long)b * (K::C * K::T)) & 15);
@@ -331,8 +336,8 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
         const uint32_t a_hi = (uint32_t)(da0 >> 32), b_hi = (uint32_t)(db0 >> 32), b_lo0 = (uint32_t)db0;
         for (int n = 0; n < ntr; n++) {
             const int st = n & 1, ab = n & 1;
-            RWAIT(0, sbase + K::BAR_X_FULL + 8 * st, (n >> 1) & 1);
-            RWAIT(1, sbase + K::BAR_T1_EMPTY + 8 * ab, ((n >> 1) & 1) ^ 1);
+            RWAITL(0, sbase + K::BAR_X_FULL + 8 * st, (n >> 1) & 1);
+            RWAITL(1, sbase + K::BAR_T1_EMPTY + 8 * ab, ((n >> 1) & 1) ^ 1);
             tc_fence_after();
             const uint32_t a_lo = (uint32_t)da0 + st * (K::XS_BYTES >> 4);
             const uint32_t td = tmem_base + ab * K::TM_L1_TRIAL;
@@ -391,7 +396,7 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
         const int4* c2 = reinterpret_cast<const int4*>(smem + K::OFF_C2);
         for (int gq = 0; gq < ng; gq++) {
             const int gpar = gq & 1;
-            RWAIT(1, sbase + K::BAR_Y2_EMPTY + 8 * gpar, ((gq >> 1) & 1) ^ 1);     // the C warps have consumed y2[gpar] of group gq - 2
+            RWAITL(1, sbase + K::BAR_Y2_EMPTY + 8 * gpar, ((gq >> 1) & 1) ^ 1);     // the C warps have consumed y2[gpar] of group gq - 2
 #pragma unroll 1
             for (int i = 0; i < K::GT; i++) {
                 const int row = 128 * i + 32 * qi + lane;

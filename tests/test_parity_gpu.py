@@ -143,8 +143,13 @@ def test_unaligned_rows_22x1125_every_misalignment():
     assert np.array_equal(y, ref)
     for lo in (8, 16, 1000):                      # views: lo * 24750 is a multiple of 16
         assert np.array_equal(net.forward(xd[lo:]).cpu().numpy(), ref[lo:]), lo
-    for Bs in (1, 2, 7, 149):
+    assert net.last_kernel == "tcr_forward_kernel"     # tcgen05 kernel with realigning warps (mibmi_tcr.cu)
+    for Bs in (1, 2, 3, 4, 7, 149, 443, 444, 445, 889):   # around 1x / 2x the persistent grid of 148 CTAs x groups of 3 trials
         assert np.array_equal(net.forward(xd[:Bs].clone()).cpu().numpy(), ref[:Bs]), Bs
+    net.set_path("fused_pipe")                          # the mma.sync predecessor stays selectable and exact
+    assert np.array_equal(net.forward(xd).cpu().numpy(), ref)
+    assert net.last_kernel == "pipe_forward_kernel"
+    net.set_path("auto")
     # saturating inputs
     xs = np.stack([np.full((C, T), v, np.int8) for v in (127, -127, -128, 0)])
     assert np.array_equal(net.forward(_cuda(xs)).cpu().numpy(), wolf_port.forward(arrays, C, T, xs))
