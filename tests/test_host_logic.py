@@ -131,3 +131,24 @@ def test_synthetic_nets_exercise_negative_factors_and_saturation():
     x = synth.make_trials(8, 64, 480, seed=1)
     y, taps = golden_np.forward(p.to_wolf_arrays(), 64, 480, x, return_layers=True)
     assert (np.abs(taps["y1"].astype(int)) >= 127).any() and len(np.unique(y)) > 8
+
+
+def test_torch_op_is_registered_and_cuda_only(golden):
+    """torch.ops.mibminet.forward_int8: schema, blob round trip, no CPU kernel."""
+    import torch
+    from mibminet_b200 import torch_op
+    fx = golden
+    dims = [fx["C"], fx["T"], 16, 1, 4]
+    blob = torch_op.pack_blob(fx["arrays"], dims)
+    back = torch_op.unpack_blob(blob, dims)
+    for name, _ in torch_op.BLOB_FIELDS:
+        assert np.array_equal(np.asarray(back[name]).ravel(), np.asarray(fx["arrays"][name]).ravel()), name
+    assert "forward_int8(Tensor x_int8, Tensor blob, int[] dims, bool reorder_bn) -> Tensor" in str(
+        torch.ops.mibminet.forward_int8.default._schema)
+    x = torch.from_numpy(fx["x"][:2])
+    with pytest.raises((NotImplementedError, RuntimeError)):
+        torch.ops.mibminet.forward_int8(x, blob, dims, True)          # CPU tensor: no kernel registered
+    y = torch.ops.mibminet.forward_int8(x.to("meta"), blob, dims, True)
+    assert y.shape == (2, 4) and y.dtype == torch.int8
+    with pytest.raises(ValueError):
+        torch_op.unpack_blob(blob[:-1], dims)

@@ -298,3 +298,15 @@ def test_forward_gather_writes_every_destination(C, T):
         h = b.cpu().numpy()
         assert np.array_equal(h[row0:row0 + B], ref)
         assert (h[:row0] == 77).all() and (h[row0 + B:] == 77).all()
+
+
+def test_torch_op_matches_the_reference_fixtures(golden):
+    """torch.ops.mibminet.forward_int8 on the reference fixtures, both reorder_bn modes."""
+    from mibminet_b200 import torch_op
+    fx = golden
+    dims = [fx["C"], fx["T"], 16, 1, 4]
+    blob = torch_op.pack_blob(fx["arrays"], dims)
+    y = torch.ops.mibminet.forward_int8(_cuda(fx["x"]), blob, dims, True)
+    assert y.is_cuda and np.array_equal(y.cpu().numpy(), fx["golden_reorder"])
+    y = torch.ops.mibminet.forward_int8(_cuda(fx["x"])[:, None], blob, dims, True)      # x[B, 1, C, T] as the module receives it
+    assert np.array_equal(y.cpu().numpy(), fx["golden_reorder"])
