@@ -7,7 +7,8 @@
 A "step" is one pass of the hot path (mibmi_forward_int8, fused sm_100a kernel) over one batch of
 B = 65536 synthetic 64 x 480 int8 trials per GPU (BASELINE config 2; 2.01 GB per batch, 16x the L2, so
 no flush is needed between steps).  Weak scaling: every rank owns its own B trials; no collective
-inside the network; the [B, 4] int8 logits are all-gathered (NCCL) once per step.
+inside the network; at N > 1 the kernel's layer-5 epilogue stores the [B, 4] int8 logits into every rank's symmetric-memory
+buffer over NVLink (fused gather; one NCCL all_gather per step is the fallback).
 
   value     whole-job trials/s, inputs resident in HBM, CUDA-event time, max over ranks
   e2e       same metric through mibmi_forward_int8_host with pinned HOST buffers: H2D copy of the
@@ -385,7 +386,10 @@ def main():
         assert torch.equal(yh.to(dev), logits), "host entry point and device path disagree"
         e2e = {"value": world * B * e_steps / float(dt[0]), "unit": "trials/s",
                "h2d_bytes_per_step": world * B * C * T, "d2h_bytes_per_step": world * B * N_CLASSES,
-               "steps": e_steps, "timing": "host wall clock around the synchronous C-ABI call, max over ranks"}
+               "steps": e_steps, "timing": "host wall clock around the synchronous C-ABI call, max over ranks",
+               "h2d_gbs_per_gpu": B * C * T * e_steps / float(dt[0]) / 1e9,
+               "bound": "PCIe host->device copy of the int8 trials (chunks of 8192 trials, copy / kernel / copy-back "
+                        "overlapped on two streams); the kernel itself is 100x faster than the link"}
         del xh
 
     if rank == 0:
