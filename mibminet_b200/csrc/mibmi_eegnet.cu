@@ -26,6 +26,8 @@ constexpr int kEegMaxF1 = 16, kEegMaxK2 = 32, kEegMaxNf = 128, kEegMaxNW = kEegM
 struct EegNet {
     int C, T, F1, D, K2, F2, N, Nf, T8, T64, XP, G, NW;
     int fac1[kEegMaxF1], off1[kEegMaxF1];
+    int mg1[kEegMaxF1], sh1[kEegMaxF1], sg1[kEegMaxF1];    // layer-1 magic division (valid when `magic1`): m, shift, sign of the factor
+    int magic1;
     int fac2[kEegMaxK2], off2[kEegMaxK2];
     int fac4[kMaxF2], off4[kMaxF2];
     int fac3, fac5;
@@ -39,7 +41,7 @@ struct EegNet {
 
 __device__ __forceinline__ int eclip8(int v) { return min(max(v, -128), 127); }
 
-template <int D>
+template <int D, bool MAGIC>
 __global__ void __launch_bounds__(384)
 eegnet_forward_kernel(const EegNet* __restrict__ net, const int8_t* __restrict__ x, long long B, int8_t* __restrict__ logits,
                       int8_t* __restrict__ tap2, int8_t* __restrict__ tap3, int8_t* __restrict__ tap4) {
@@ -72,10 +74,12 @@ eegnet_forward_kernel(const EegNet* __restrict__ net, const int8_t* __restrict__
         for (int item = tid; item < (F1 / 4) * G; item += nth) {
             const int fh = item / G, g = item - fh * G;
             int a[4][D][4];
-            int fac[4], off[4];
+            int fac[4], off[4], shf[4], sgn[4];      // MAGIC: fac = magic multiplier
 #pragma unroll
             for (int fi = 0; fi < 4; fi++) {
-                fac[fi] = net->fac1[4 * fh + fi];
+                fac[fi] = MAGIC ? net->mg1[4 * fh + fi] : net->fac1[4 * fh + fi];
+                shf[fi] = net->sh1[4 * fh + fi];
+                sgn[fi] = net->sg1[4 * fh + fi];
                 off[fi] = net->off1[4 * fh + fi];
 #pragma unroll
                 for (int d = 0; d < D; d++) a[fi][d][0] = a[fi][d][1] = a[fi][d][2] = a[fi][d][3] = 0;
@@ -104,7 +108,8 @@ eegnet_forward_kernel(const EegNet* __restrict__ net, const int8_t* __restrict__
                     for (int d = 0; d < D; d++) w2v[d] = (int)net->w2[((4 * fh + fi) * D + d) * C + c];
 #pragma unroll
                     for (int s = 0; s < 4; s++) {
-                        const int y = eclip8((acc[fi][s] + off[fi]) / fac[fi]);
+                        const int xv = acc[fi][s] + off[fi];
+                        const int y = eclip8(MAGIC ? sgn[fi] * tdiv_magic(xv, fac[fi], shf[fi]) : xv / fac[fi]);
 #pragma unroll
                         for (int d = 0; d < D; d++) a[fi][d][s] += y * w2v[d];
                     }
@@ -173,7 +178,7 @@ using namespace mibmi;
 
 struct mibmi_eegnet {
     int device = 0, num_sms = 0;
-    int C = 0, T = 0, K2 = 0, F2 = 0, N = 0, D = 0, threads = 256;
+    int C = 0, T = 0, K2 = 0, F2 = 0, N = 0, D = 0, threads = 256, magic1 = 0;
     size_t smem = 0;
     EegNet* net_dev = nullptr;
     int8_t* w5_dev = nullptr;
@@ -233,6 +238,22 @@ int mibmi_eegnet_create(const mibmi_eegnet_params_t* p, int device, mibmi_eegnet
                 h->w1s[(f * h->NW + i) * 4 + s] = (int)w;
             }
     }
+    h->magic1 = 1;
+    for (int f = 0; f < F1; f++) {
+        long long sum = 0;
+        for (int j = 0; j < Nf; j++) sum += p->l1_weight[f * Nf + j] < 0 ? -(long long)p->l1_weight[f * Nf + j] : p->l1_weight[f * Nf + j];
+        const long long fa = h->fac1[f] < 0 ? -(long long)h->fac1[f] : h->fac1[f];
+        const long long oa = h->off1[f] < 0 ? -(long long)h->off1[f] : h->off1[f];
+        h->sg1[f] = h->fac1[f] < 0 ? -1 : 1;
+        // tdiv(x, d) == (mulhi(x, m) >> s) + (x < 0) for d >= 4, |x| < 2^29; otherwise hardware division
+        if (fa < 4 || fa > 0x7fffffffLL || 128 * sum + oa >= (1LL << 29)) { h->magic1 = 0; continue; }
+        int lg = 0;
+        while ((1LL << (lg + 1)) <= fa) lg++;
+        const long long mm = (long long)(((__int128)1 << (30 + lg)) / fa) + 1;
+        if (mm >= (1LL << 31)) { h->magic1 = 0; continue; }
+        h->mg1[f] = (int)mm;
+        h->sh1[f] = lg - 2;
+    }
     for (int k = 0; k < K2; k++) {
         h->fac2[k] = p->l2_factor[k]; h->off2[k] = p->l2_offset[k];
         zero |= h->fac2[k] == 0;
@@ -252,6 +273,7 @@ int mibmi_eegnet_create(const mibmi_eegnet_params_t* p, int device, mibmi_eegnet
     if (!n) { delete h; return MIBMI_ERR_CUDA; }
     n->device = device; n->C = C; n->T = T; n->K2 = K2; n->F2 = F2; n->N = N; n->D = D;
     n->threads = threads < 128 ? 128 : threads;
+    n->magic1 = h->magic1;
     n->smem = (size_t)F1 * h->NW * 16 + (size_t)C * h->XP + (size_t)K2 * h->G * 4 + (size_t)K2 * (h->T8 + 15) + (size_t)K2 * h->T8 +
               (size_t)F2 * h->T64 + 16;
     Guard dg(device);
@@ -296,7 +318,8 @@ int mibmi_eegnet_forward_int8_taps(mibmi_eegnet_t* n, const int8_t* x_dev, int64
     if (!x_dev || !logits_dev) return MIBMI_ERR_NULL;
     Guard dg(n->device);
     cudaError_t e = dg.err;
-    auto kern = n->D == 1 ? eegnet_forward_kernel<1> : eegnet_forward_kernel<2>;
+    auto kern = n->D == 1 ? (n->magic1 ? eegnet_forward_kernel<1, true> : eegnet_forward_kernel<1, false>)
+                          : (n->magic1 ? eegnet_forward_kernel<2, true> : eegnet_forward_kernel<2, false>);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)n->smem);
     if (e == cudaSuccess) {
         long long grid = (long long)n->num_sms * (n->smem > 100 * 1024 ? 1 : 2);

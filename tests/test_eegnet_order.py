@@ -117,6 +117,21 @@ def test_gpu_saturating_inputs_and_empty_batch():
 
 
 @pytest.mark.gpu
+def test_gpu_small_factors_use_the_hardware_division():
+    """|l1_factor| < 4 is outside the proven range of the magic division: the kernel instantiation with the hardware
+    division must give the same exact results."""
+    import dataclasses
+    from mibminet_b200.engine import EEGNetInt8
+    sd, p, _, torch = _gpu_net(22, 1125, 8, 2, 128, seed=2)
+    fac1 = np.asarray(p.fac1).copy()
+    fac1[::2] = [3, -2, 1, -1]
+    p2 = dataclasses.replace(p, fac1=fac1.astype(np.int32))
+    x = synth.make_trials(24, 22, 1125, seed=6)
+    net = EEGNetInt8(p2, device="cuda:0")
+    assert np.array_equal(net.forward(torch.from_numpy(x).cuda()).cpu().numpy(), eegnet_np.forward(p2, x))
+
+
+@pytest.mark.gpu
 def test_gpu_module_drop_in_float_in_float_out():
     import torch
     from mibminet_b200.modules import EEGNet
