@@ -52,7 +52,8 @@ typedef enum {
 /* Input layouts of one batch of trials (int8, values in [-127, 127] as produced by
  * gen_input_header.py:73; -128 is accepted and handled exactly). */
 #define MIBMI_LAYOUT_BCT 0  /* [B][C][T]        -- module order, edgeEEGNet.forward x[B,1,C,T]         */
-#define MIBMI_LAYOUT_BTC 1  /* [B][T][C_ALIGN]  -- Wolf order of net_model_compute (gen_input_header.py:75-76) */
+#define MIBMI_LAYOUT_BTC 1  /* [B][T][C_ALIGN]  -- Wolf order of net_model_compute (gen_input_header.py:75-76);       *
+                             * fused tcgen05 kernel when C_ALIGN is 64 or 16 (T = 480), exact generic kernel otherwise */
 
 /* Network description: the exported arrays of gen_net_header.py (names without the "net_" prefix).
  * All pointers are HOST pointers; mibmi_create copies what it needs. */

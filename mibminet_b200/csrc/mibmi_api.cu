@@ -24,7 +24,7 @@ struct mibmi_net {
     bool fused_ok = false;
     const char* fused_why = "";
     PipeNet* pipe_dev = nullptr;       // warp-specialised pipeline kernel (MIBMI_PATH_FUSED)
-    bool pipe_ok = false, pipe_fast1 = false, tc_ok = false, tcr_ok = false;
+    bool pipe_ok = false, pipe_fast1 = false, tc_ok = false, tcr_ok = false, tc_wolf_ok = false;
     const char* pipe_why = "";
     StreamNet* stream_dev = nullptr;   // sliding-window streaming kernel (mibmi_forward_stream_int8)
     bool stream_ok = false;
@@ -507,7 +507,8 @@ int forward_impl(mibmi_net* net, const int8_t* x, int64_t B, int layout, int8_t*
     if (!x || !logits) return MIBMI_ERR_NULL;
     if (((uintptr_t)x & 15) != 0 || (net->N == 4 && ((uintptr_t)logits & 3) != 0)) return MIBMI_ERR_ALIGN;
     int path = net->force_path;
-    const bool pipe_possible = net->pipe_ok && layout == MIBMI_LAYOUT_BCT;
+    const bool wolf_fused = net->tc_wolf_ok && layout == MIBMI_LAYOUT_BTC;     // tcgen05 kernel, K-major operand from the Wolf order
+    const bool pipe_possible = net->pipe_ok && (layout == MIBMI_LAYOUT_BCT || (wolf_fused && net->force_path != MIBMI_PATH_FUSED_PIPE));
     const bool v1_possible = net->fused_ok && layout == MIBMI_LAYOUT_BCT && !taps;
     if (path == MIBMI_PATH_AUTO) path = (pipe_possible && !taps) ? MIBMI_PATH_FUSED : MIBMI_PATH_GENERIC;
     if ((path == MIBMI_PATH_FUSED || path == MIBMI_PATH_FUSED_PIPE) && !pipe_possible) return MIBMI_ERR_UNSUPPORTED;
@@ -517,7 +518,10 @@ int forward_impl(mibmi_net* net, const int8_t* x, int64_t B, int layout, int8_t*
     cudaError_t e;
     PeerOut none;
     none.n = 0;
-    if (path == MIBMI_PATH_FUSED && net->tc_ok)
+    if (path == MIBMI_PATH_FUSED && wolf_fused)
+        e = launch_tc_wolf(net->pipe_dev, net->pipe_fast1, net->C, net->T, x, B, logits, peers ? *peers : none, t1, t2, t3, t4,
+                           net->num_sms, stream);
+    else if (path == MIBMI_PATH_FUSED && net->tc_ok)
         e = launch_tc(net->pipe_dev, net->pipe_fast1, net->C, net->T, x, B, logits, peers ? *peers : none, t1, t2, t3, t4,
                       net->num_sms, stream);
     else if (path == MIBMI_PATH_FUSED && net->tcr_ok)
@@ -650,6 +654,7 @@ int mibmi_create(const mibmi_params_t* p, int device, mibmi_net_t** out) {
     n->pipe_fast1 = pn->fast1 != 0;
     n->tc_ok = n->pipe_ok && tc_has_instance(p->C, p->T);
     n->tcr_ok = n->pipe_ok && tcr_has_instance(p->C, p->T);
+    n->tc_wolf_ok = n->tc_ok && tc_has_wolf_instance(p->C, p->T);
     if (n->pipe_ok) n->stream_ok = pack_stream(p, pn, sn, &n->stream_why);
     else n->stream_why = n->pipe_why;
 

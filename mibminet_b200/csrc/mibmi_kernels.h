@@ -44,6 +44,11 @@ bool tc_has_instance(int C, int T);
 cudaError_t launch_tc(const PipeNet* net_dev, bool fast1, int C, int T, const int8_t* x, long long B, int8_t* logits,
                       const PeerOut& peers, int8_t* t1, int8_t* t2, int8_t* t3, int8_t* t4, int num_sms, cudaStream_t stream);
 
+// The same kernel fed from the Wolf order [B][T][C_ALIGN] of net_model_compute (K-major layer-1 operand through a 3-D tensor map).
+bool tc_has_wolf_instance(int C, int T);
+cudaError_t launch_tc_wolf(const PipeNet* net_dev, bool fast1, int C, int T, const int8_t* x, long long B, int8_t* logits,
+                           const PeerOut& peers, int8_t* t1, int8_t* t2, int8_t* t3, int8_t* t4, int num_sms, cudaStream_t stream);
+
 // Same formulation for trials whose rows are not 16-byte aligned (mibmi_tcr.cu: realigning warps instead of TMA tiles,
 // MMA tiles that straddle trials): 22 x 1125.
 bool tcr_has_instance(int C, int T);

@@ -107,7 +107,12 @@ __device__ __forceinline__ constexpr uint32_t umma_idesc_i8_kk(int M, int N) {
     return (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 
-template <class K, bool FAST1, bool TAPS>
+// WOLF: x is [B][T][C_ALIGN] (the order of net_model_compute, gen_input_header.py:75-76), already K-major for layer 1: a 3-D
+// tensor map (16 bytes, time rows, 16-byte channel chunks) lands every tile as [chunk][128 rows][16 B] = K-major 8 x 16-byte core
+// matrices (rows 16 B apart, SBO 128 B, LBO 2048 B), no swizzle -- the descriptor form of the layer-2 Hankel operand (WOLF = 1).
+// WOLF = 2 (rows of exactly 64 bytes): 2-D tiles [128 rows][64 B] with the 64-byte swizzle, K-major SWIZZLE_64B descriptor
+// (SBO 512 B = 8 rows, the second k-step starts 32 B into the row): full-row TMA requests instead of 16-byte ones.
+template <class K, bool FAST1, bool TAPS, int WOLF>
 __global__ void __launch_bounds__(kTcThreads, 1)
 tc_forward_kernel(const __grid_constant__ CUtensorMap tmx, const PipeNet* __restrict__ net, long long B,
                   int8_t* __restrict__ logits, const PeerOut peers, int8_t* __restrict__ tap1, int8_t* __restrict__ tap2,
@@ -242,9 +247,19 @@ tc_forward_kernel(const __grid_constant__ CUtensorMap tmx, const PipeNet* __rest
                 const long long b = 4 * (firstq + (long long)(n >> 2) * strideq) + (n & 3);   // b >= B: zero filled
                 const uint32_t dst = sbase + K::OFF_XS + st * K::XS_BYTES;
                 const uint32_t bar = sbase + K::BAR_FULL_X + 8 * st;
-                mbar_expect_tx(bar, K::TILES * K::C * 128);
+                if (WOLF == 1) {
+                    mbar_expect_tx(bar, K::TILES * K::TILE_BYTES);
 #pragma unroll
-                for (int j = 0; j < K::TILES; j++) tma_load_2d(dst + j * K::TILE_BYTES, &tmx, 128 * j, (int)(b * K::C), bar);
+                    for (int j = 0; j < K::TILES; j++) tma_load_3d(dst + j * K::TILE_BYTES, &tmx, 0, (int)(b * K::T) + 128 * j, 0, bar);
+                } else if (WOLF == 2) {
+                    mbar_expect_tx(bar, K::TILES * K::TILE_BYTES);
+#pragma unroll
+                    for (int j = 0; j < K::TILES; j++) tma_load_2d(dst + j * K::TILE_BYTES, &tmx, 0, (int)(b * K::T) + 128 * j, bar);
+                } else {
+                    mbar_expect_tx(bar, K::TILES * K::C * 128);
+#pragma unroll
+                    for (int j = 0; j < K::TILES; j++) tma_load_2d(dst + j * K::TILE_BYTES, &tmx, 128 * j, (int)(b * K::C), bar);
+                }
             };
             for (int s = 0; s < K::SX && s < ntr; s++) issue(s, s);
             for (int n = 0; n + K::SX < ntr; n++) {
@@ -258,9 +273,10 @@ tc_forward_kernel(const __grid_constant__ CUtensorMap tmx, const PipeNet* __rest
         // M1: layer-1 MMAs, TILES x KSTEPS per trial
         // =====================================================================================
         {
-            constexpr uint32_t idesc = umma_idesc_i8(128, 16);
+            constexpr uint32_t idesc = WOLF ? umma_idesc_i8_kk(128, 16) : umma_idesc_i8(128, 16);
             // descriptors: only the start-address field (low 14 bits, units of 16 B) changes between instructions
-            const uint64_t da0 = umma_desc(sbase + K::OFF_XS, 16, 1024, 2), db0 = umma_desc(sbase + K::OFF_W1, 128, K::KSTEPS * 256, 0);
+            const uint64_t da0 = WOLF == 1 ? umma_desc(sbase + K::OFF_XS, 2048, 128, 0)
+                                 : WOLF == 2 ? umma_desc(sbase + K::OFF_XS, 16, 512, 4) : umma_desc(sbase + K::OFF_XS, 16, 1024, 2), db0 = umma_desc(sbase + K::OFF_W1, 128, K::KSTEPS * 256, 0);
             const uint32_t a_hi = (uint32_t)(da0 >> 32), b_hi = (uint32_t)(db0 >> 32), b_lo0 = (uint32_t)db0;
             for (int n = 0; n < ntr; n++) {
                 const int st = n % K::SX, ab = n & 1;
@@ -274,7 +290,7 @@ tc_forward_kernel(const __grid_constant__ CUtensorMap tmx, const PipeNet* __rest
                     for (int j = 0; j < K::TILES; j++)
 #pragma unroll
                         for (int ks = 0; ks < K::KSTEPS; ks++)
-                            umma_i8_lohi(td + 16 * j, a_lo + ((j * K::TILE_BYTES + ks * 4096) >> 4), a_hi, b_lo0 + ((ks * 256) >> 4),
+                            umma_i8_lohi(td + 16 * j, a_lo + ((j * K::TILE_BYTES + ks * (WOLF == 2 ? 32 : 4096)) >> 4), a_hi, b_lo0 + ((ks * 256) >> 4),
                                          b_hi, idesc, ks > 0);
                     umma_commit(sbase + K::BAR_EMPTY_X + 8 * st);
                     umma_commit(sbase + K::BAR_T1_FULL + 8 * ab);
@@ -491,7 +507,7 @@ tc_forward_kernel(const __grid_constant__ CUtensorMap tmx, const PipeNet* __rest
 }
 
 // ---------------------------------------------------------------------------------------------
-template <int C, int T>
+template <int C, int T, int WOLF>
 static cudaError_t launch_tc_instance(const PipeNet* net_dev, bool fast1, const int8_t* x, long long B, int8_t* logits,
                                       const PeerOut& peers, int8_t* t1, int8_t* t2, int8_t* t3, int8_t* t4, int num_sms,
                                       cudaStream_t stream) {
@@ -499,16 +515,37 @@ static cudaError_t launch_tc_instance(const PipeNet* net_dev, bool fast1, const 
     tmap_encode_t enc = tmap_encoder();
     if (!enc) return cudaErrorNotSupported;
     CUtensorMap tm;
-    cuuint64_t dims[2] = {(cuuint64_t)T, (cuuint64_t)(B * C)};
-    cuuint64_t strides[1] = {(cuuint64_t)T};
-    cuuint32_t box[2] = {128, (cuuint32_t)C};
-    cuuint32_t estr[2] = {1, 1};
-    if (enc(&tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<int8_t*>(x), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-            CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
-        return cudaErrorInvalidValue;
+    CUresult r;
+    if (WOLF == 2) {
+        static_assert(WOLF != 2 || (C + 3) / 4 * 4 == 64, "64-byte rows");
+        cuuint64_t dims[2] = {64, (cuuint64_t)(B * T)};
+        cuuint64_t strides[1] = {64};
+        cuuint32_t box[2] = {64, 128};
+        cuuint32_t estr[2] = {1, 1};
+        r = enc(&tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<int8_t*>(x), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    } else if (WOLF == 1) {
+        // [B*T][C_ALIGN] seen as (16 bytes, time rows, 16-byte channel chunks): one box = [KPAD/16 chunks][128 rows][16 B]
+        constexpr int CA = (C + 3) / 4 * 4;
+        static_assert(WOLF != 1 || CA % 16 == 0, "Wolf-order rows must be a multiple of 16 bytes for the tensor map");
+        cuuint64_t dims[3] = {16, (cuuint64_t)(B * T), (cuuint64_t)(CA / 16)};
+        cuuint64_t strides[2] = {(cuuint64_t)CA, 16};
+        cuuint32_t box[3] = {16, 128, (cuuint32_t)(K::KPAD / 16)};
+        cuuint32_t estr[3] = {1, 1, 1};
+        r = enc(&tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<int8_t*>(x), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    } else {
+        cuuint64_t dims[2] = {(cuuint64_t)T, (cuuint64_t)(B * C)};
+        cuuint64_t strides[1] = {(cuuint64_t)T};
+        cuuint32_t box[2] = {128, (cuuint32_t)C};
+        cuuint32_t estr[2] = {1, 1};
+        r = enc(&tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<int8_t*>(x), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    }
+    if (r != CUDA_SUCCESS) return cudaErrorInvalidValue;
     const bool taps = t1 || t2 || t3 || t4;
-    auto kern = taps ? tc_forward_kernel<K, false, true>
-                     : (fast1 ? tc_forward_kernel<K, true, false> : tc_forward_kernel<K, false, false>);
+    auto kern = taps ? tc_forward_kernel<K, false, true, WOLF>
+                     : (fast1 ? tc_forward_kernel<K, true, false, WOLF> : tc_forward_kernel<K, false, false, WOLF>);
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, K::SMEM);
     if (e != cudaSuccess) return e;
     long long grid = num_sms;
@@ -529,8 +566,29 @@ bool tc_has_instance(int C, int T) {
 
 cudaError_t launch_tc(const PipeNet* net_dev, bool fast1, int C, int T, const int8_t* x, long long B, int8_t* logits,
                       const PeerOut& peers, int8_t* t1, int8_t* t2, int8_t* t3, int8_t* t4, int num_sms, cudaStream_t stream) {
-#define X(c, t) if (C == c && T == t) return launch_tc_instance<c, t>(net_dev, fast1, x, B, logits, peers, t1, t2, t3, t4, num_sms, stream);
+#define X(c, t) if (C == c && T == t) return launch_tc_instance<c, t, 0>(net_dev, fast1, x, B, logits, peers, t1, t2, t3, t4, num_sms, stream);
     MIBMI_TC_SHAPES(X)
+#undef X
+    return cudaErrorInvalidValue;
+}
+
+#ifndef MIBMI_WOLF_NO_SW64
+#define MIBMI_WOLF_NO_SW64 0
+#endif
+// Wolf order [B][T][C_ALIGN]: shapes whose rows are a multiple of 16 bytes (tensor-map stride rule)
+#define MIBMI_TC_WOLF_SHAPES(X) X(64, 480) X(16, 480)
+
+bool tc_has_wolf_instance(int C, int T) {
+#define X(c, t) if (C == c && T == t) return true;
+    MIBMI_TC_WOLF_SHAPES(X)
+#undef X
+    return false;
+}
+
+cudaError_t launch_tc_wolf(const PipeNet* net_dev, bool fast1, int C, int T, const int8_t* x, long long B, int8_t* logits,
+                           const PeerOut& peers, int8_t* t1, int8_t* t2, int8_t* t3, int8_t* t4, int num_sms, cudaStream_t stream) {
+#define X(c, t) if (C == c && T == t) return launch_tc_instance<c, t, ((c + 3) / 4 * 4 == 64 && !MIBMI_WOLF_NO_SW64) ? 2 : 1>(net_dev, fast1, x, B, logits, peers, t1, t2, t3, t4, num_sms, stream);
+    MIBMI_TC_WOLF_SHAPES(X)
 #undef X
     return cudaErrorInvalidValue;
 }

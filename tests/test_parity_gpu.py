@@ -79,6 +79,17 @@ def test_wolf_input_layout(golden):
     xw = convert.to_wolf_input(fx["x"])   # [B][T][C_ALIGN]  (gen_input_header.py:75-76)
     y = net.forward(_cuda(xw), layout="btc").cpu().numpy()
     assert np.array_equal(y, fx["golden_reorder"])
+    # rows of C_ALIGN bytes that are a multiple of 16 go through the tcgen05 kernel (K-major operand, 3-D tensor map)
+    assert net.last_kernel == ("tc_forward_kernel" if fx["C"] in (64, 16) and fx["T"] == 480 else "generic_forward_kernel")
+    if fx["C"] in (64, 16) and fx["T"] == 480:
+        xr = synth.make_trials(1237, fx["C"], fx["T"], seed=9)
+        ref = wolf_port.forward(fx["arrays"], fx["C"], fx["T"], xr)
+        assert np.array_equal(net.forward(_cuda(convert.to_wolf_input(xr)), layout="btc").cpu().numpy(), ref)
+        net.set_path("fused")                       # the diagnostic instantiation of the same kernel
+        _, taps = net.forward_taps(_cuda(xw), layout="btc")
+        assert net.last_kernel == "tc_forward_kernel"
+        for name in ("y1", "y2", "y3", "y4"):
+            assert np.array_equal(taps[name].cpu().numpy(), fx[f"golden_reorder_{name}"]), name
 
 
 # ---- against the oracle on seeded random nets / trials ------------------------------------------------
