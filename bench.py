@@ -326,6 +326,8 @@ def main():
     k_ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     launches0 = net.launch_count
+    if peer is not None:
+        peer.wait()                      # device-side barrier on the stream: every GPU enters the timed region together
     t_wall0 = time.perf_counter()
     ev0.record()
     for i in range(args.steps):

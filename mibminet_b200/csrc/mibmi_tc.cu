@@ -82,7 +82,8 @@ struct TCfg {
     static constexpr int OFF_Y2 = OFF_Y1 + 16 * CHS;
     static constexpr int OFF_Y3 = OFF_Y2 + 2 * Y2_BUF;
     static constexpr int OFF_Y4 = OFF_Y3 + 8 * Y3_TRIAL;
-    static constexpr int SMEM = ((OFF_Y4 + kTcCW * Y4_BYTES + 127) / 128) * 128;
+    static constexpr int OFF_LG = ((OFF_Y4 + kTcCW * Y4_BYTES + 15) / 16) * 16;        // 2 x 16 B: the logits of a quad, for the peer stores
+    static constexpr int SMEM = ((OFF_LG + 32 + 127) / 128) * 128;
     static_assert(T % 32 == 0 && T <= SLOT - 32, "trial fits a 512-byte slot with 32 zero bytes");
     static_assert(TM_L1 + 2 * TM_L1_TRIAL <= TM_L2, "TMEM map");
     static_assert(NW3 <= 4, "layer 3: 4 trials x 4 blocks fill the 16 MMA rows");
@@ -416,6 +417,20 @@ tc_forward_kernel(const __grid_constant__ CUtensorMap tmx, const PipeNet* __rest
 #pragma unroll
                 for (int hh = 0; hh < 2; hh++) b3[c][v][hh] = net->w3frag[4 * cj + c][v * 2 + hh][lane];
         const int m3 = net->m3, sh3 = net->sh3;
+        // fused all-gather (NVLink P2P): the 4 x 4 logit bytes of a quad go to every peer's buffer as ONE 16-byte store
+        // per peer (lane = peer), issued one quad late by the first C warp from the staging bytes of the four warps
+        auto flush_peers = [&](int gprev) {
+            const long long bq = 4 * (firstq + (long long)gprev * strideq);
+            if (lane < peers.n) {
+                int8_t* dst = peers.p[lane] + (size_t)bq * 4;
+                const uint8_t* src = smem + K::OFF_LG + 16 * (gprev & 1);
+                if (bq + 4 <= B && (reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
+                    *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(src);
+                } else {
+                    for (int i = 0; i < 16 && bq * 4 + i < B * 4; i++) dst[i] = (int8_t)src[i];
+                }
+            }
+        };
         for (int gq = 0; gq < nq; gq++) {
             const int buf = gq & 1, par = (gq >> 1) & 1;
             const long long b0 = 4 * (firstq + (long long)gq * strideq);
@@ -455,6 +470,7 @@ tc_forward_kernel(const __grid_constant__ CUtensorMap tmx, const PipeNet* __rest
             __syncwarp();
             if (lane == 0) mbar_arrive(sbase + K::BAR_Y3_EMPTY + 8 * buf);      // y2[buf] is free again
             asm volatile("bar.sync 1, %0;" ::"n"(kTcCW * 32) : "memory");        // y3[buf] of all 16 channels is complete
+            if (peers.n > 0 && cj == 0 && gq > 0) flush_peers(gq - 1);            // ... and so are the staged logits of the previous quad
             const uint32_t y3a = sbase + K::OFF_Y3 + (4 * buf + sl) * K::Y3_TRIAL + l4_off;
 #pragma unroll
             for (int s4 = 0; s4 < K::NST; s4++) {
@@ -495,9 +511,13 @@ tc_forward_kernel(const __grid_constant__ CUtensorMap tmx, const PipeNet* __rest
             if (q == 0 && g < 4 && b < B) {
                 const int8_t o = (int8_t)clip8(tdiv_magic(z[0] + b5, m5, sh5));
                 logits[(size_t)b * 4 + g] = o;
-                for (int i = 0; i < peers.n; i++) peers.p[i][(size_t)b * 4 + g] = o;    // fused all-gather (NVLink P2P)
+                if (peers.n > 0) smem[K::OFF_LG + 16 * (gq & 1) + 4 * sl + g] = (uint8_t)o;
             }
             __syncwarp();
+        }
+        if (peers.n > 0 && nq > 0) {
+            asm volatile("bar.sync 1, %0;" ::"n"(kTcCW * 32) : "memory");
+            if (cj == 0) flush_peers(nq - 1);
         }
     }
     TPROF_END
