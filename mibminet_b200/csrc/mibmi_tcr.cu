@@ -43,6 +43,13 @@ __device__ long long g_prof_tcr[148 * 32 * 4];
 #define RPROF_END
 #endif
 
+#ifndef MIBMI_TCR_L3_UNROLL
+#define MIBMI_TCR_L3_UNROLL 4
+#endif
+#ifndef MIBMI_TCR_L4_UNROLL
+#define MIBMI_TCR_L4_UNROLL 1
+#endif
+constexpr int kTcrL3Unroll = MIBMI_TCR_L3_UNROLL, kTcrL4Unroll = MIBMI_TCR_L4_UNROLL;   // layers 3 / 4 loops of the C warps
 constexpr int kRAW = 12, kRBW = 8, kRCW = 4, kRRW = 4;
 constexpr int kRWarpB = kRAW, kRWarpC = kRAW + kRBW, kRWarpR = kRWarpC + kRCW, kRWarpP = kRWarpR + kRRW,
               kRWarpM1 = kRWarpP + 1, kRWarpM2 = kRWarpP + 2;
@@ -92,6 +99,10 @@ struct RCfg {
     static_assert(SMEM <= 227 * 1024, "shared memory");
     // last tile that reads bytes of y1 slot j / last tile with valid rows of trial j / last trial with valid rows in tile i
     __host__ __device__ static constexpr int slot_last_tile(int j) { return (SROWS * (j + 1) - 1) / 128 < GT ? (SROWS * (j + 1) - 1) / 128 : GT - 1; }
+    // last tile that reads the bytes layer-1 tile jt of slot j writes (128 samples + the 16 bytes the last unit may spill; row r reads bytes 16 r .. 16 r + 95)
+    __host__ __device__ static constexpr int unit_last_tile(int j, int jt) {
+        return (SLOT * j + 32 + 128 * jt + 143) / 16 / 128 < GT ? (SLOT * j + 32 + 128 * jt + 143) / 16 / 128 : GT - 1;
+    }
     __host__ __device__ static constexpr int trial_last_tile(int j) { return (SROWS * j + VROWS - 1) / 128; }
     __host__ __device__ static constexpr int tile_last_trial(int i) { return (128 * i + 127) / SROWS < G ? (128 * i + 127) / SROWS : G - 1; }
 };
@@ -214,8 +225,8 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
             const int gq = n / K::G, j = n - gq * K::G, ab = n & 1;
             RWAIT(0, sbase + K::BAR_T1_FULL + 8 * ab, (n >> 1) & 1);
             tc_fence_after();
-            // slot j of the previous group must have been read by every tile that touches it
-            RWAITL(1, sbase + K::BAR_TILE_DONE + 8 * K::slot_last_tile(j), (gq & 1) ^ 1);
+            // the bytes a unit overwrites must have been read by every tile of the previous group that touches them: the
+            // slot that straddles two tiles is released in two steps (its head as soon as the first tile is done)
             const uint32_t yb = st_off + K::SLOT * j;
             const long long b = trial_of(n);
             // the warp's tiles jt0, jt0 + 3, ...: the TMEM load of the next unit is in flight while this one is requantised
@@ -230,6 +241,7 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
             for (int it = 0; it < (K::TILES + 2) / 3; it++) {
                 const int jt = jt0 + 3 * it, u = 4 * jt + qi;
                 if (jt >= K::TILES || 32 * u >= K::T) break;
+                RWAITL(1, sbase + K::BAR_TILE_DONE + 8 * K::unit_last_tile(j, jt), (gq & 1) ^ 1);
                 tmem_ld_wait();
                 if (it + 1 < (K::TILES + 2) / 3 && jt + 3 < K::TILES && 32 * (u + 12) < K::T) {
                     tmem_ld_16x256b_x2(r[(it + 1) & 1][0], ta0 + 16 * (jt + 3));
@@ -480,7 +492,7 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
             const long long b = trial_of(n);
             RWAIT(0, sbase + K::BAR_Y2_FULL + 8 * (K::GT * gpar + K::trial_last_tile(j)), (gq >> 1) & 1);
             const uint32_t y2a = sbase + K::OFF_Y2 + (gpar * K::G + j) * K::Y2_TRIAL + l3_off;
-#pragma unroll 4
+#pragma unroll kTcrL3Unroll
             for (int k = 0; k < 16; k++) {
                 uint32_t a[4];
                 ldsm_x4(a, y2a + k * K::Y2S);
@@ -510,7 +522,7 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(sbase + K::BAR_Y2_EMPTY + 8 * gpar);      // this trial's y2 buffer is free again
-#pragma unroll 1
+#pragma unroll kTcrL4Unroll
             for (int s4 = 0; s4 < K::NST; s4++) {
                 uint32_t d[4];
                 ldsm_t_x2(d, y3a + 32 * s4);
