@@ -96,6 +96,22 @@ def cpu_reference_run(x_sample, repeat, cores):
     return len(x_sample) * repeat / (time.perf_counter() - t0), "port", y
 
 
+def tensor_pipe(kernel, C, T, B, ms_kernel, clocks):
+    """Second roofline: share of the tcgen05 issue rate.  tcgen05.mma instructions per trial (counted from the
+    kernel's loops, confirmed by the UTCIMMA count of the ncu source page) x 46 cycles per M128 N16 K32 kind::i8 instruction
+    (tools/probe_umma2.cu) / the kernel's cycles per trial per SM at the SM clock sampled during the timed region."""
+    tiles, ksteps = (T + 127) // 128, (C + 31) // 32
+    if kernel == "tc_forward_kernel":
+        n_mma = tiles * ksteps + 12                   # layer 1 per tile and k-step + layer 2: 16 channels x 3 per quad of 4 trials
+    elif kernel == "tcr_forward_kernel":
+        n_mma = tiles * ksteps + 2 * 48 / 3           # layer 2: 2 tiles x 16 channels x 3 per group of 3 trials
+    else:
+        return None
+    mhz = (clocks or {}).get("sm_mhz") or 1965.0
+    cycles = ms_kernel * 1e-3 * mhz * 1e6 * 148 / B
+    return {"utcimma_per_trial": n_mma, "cycles_per_instr": 46, "cycles_per_trial_per_sm": cycles, "frac": n_mma * 46 / cycles}
+
+
 def host_cores():
     try:
         return len(os.sched_getaffinity(0))
@@ -415,7 +431,8 @@ def main():
                          "peak_source": peak_src,
                          "kernel": KERNEL_TEMPLATES.get(net.last_kernel, net.last_kernel).format(C=C, T=T),
                          "kernel_ms": ms_kernel, "alg_bytes_per_trial": ALG_BYTES_PER_TRIAL,
-                         "note": KERNEL_NOTES.get(net.last_kernel, "")},
+                         "note": KERNEL_NOTES.get(net.last_kernel, ""),
+                         "tensor_pipe": tensor_pipe(net.last_kernel, C, T, B, ms_kernel, clocks)},
             "gpu_launches": int(launches), "clocks": clocks, "e2e": e2e,
         }
         if not args.no_cpu_baseline:

@@ -47,6 +47,8 @@ struct SCfg {
     static constexpr int CPS = 144, S2K = 8 * CPS;                 // shifted copies: stride = 16 mod 128
     static constexpr int NB3 = (T8 + 15) / 16;                     // layer-3 blocks of 16 outputs
     static constexpr int Y3S = 80;                                 // layer-3 row of a (window, channel)
+    static constexpr int Y3W = 16 * Y3S + 32;                      // bytes per window; + 32: the 8 windows a store instruction touches
+                                                                   // fall into 4 bank groups instead of one (was 8-way conflicted)
     static constexpr int NST = (T64 + 3) / 4, T64P = (T64 + 1) / 2 * 2, KST5 = T64P / 2;
     static constexpr int Y4_BYTES = ((16 * T64P + 15) / 16) * 16;
     // shared memory map
@@ -56,7 +58,7 @@ struct SCfg {
     static constexpr int OFF_S2 = OFF_Y1 + 16 * Y1S + 16;          // 16 B slack: copy 0 is written from byte -6
     static constexpr int OFF_E = OFF_S2 + 16 * S2K;
     static constexpr int OFF_Y3 = OFF_E + 16 * G * 16;
-    static constexpr int OFF_Y4 = OFF_Y3 + 16 * 16 * Y3S;
+    static constexpr int OFF_Y4 = OFF_Y3 + 16 * Y3W;
     static constexpr int SMEM = ((OFF_Y4 + kStreamWarps * Y4_BYTES + 127) / 128) * 128;
     static_assert(T % 64 == 0 || T % 16 == 0, "window length");
     static_assert(UNITS <= 2 * HALF_UNITS, "a chunk is two half loads");
@@ -321,7 +323,7 @@ stream_forward_kernel(const __grid_constant__ CUtensorMap tmx, const StreamNet* 
                             for (int hf = 0; hf < 2; hf++) {
                                 const int wl = g + 8 * hf;
                                 const uint32_t w = pack2_sat(tdiv_magic(c3[2 * hf], m3, sh3), tdiv_magic(c3[2 * hf + 1], m3, sh3));
-                                *reinterpret_cast<uint16_t*>(y3k + wl * (16 * K::Y3S) + pos) = (uint16_t)w;
+                                *reinterpret_cast<uint16_t*>(y3k + wl * K::Y3W + pos) = (uint16_t)w;
                                 if (TAPS && tap3 && w0 + 16 * wt + wl < W) {
                                     int8_t* o = tap3 + (((size_t)subj * W + w0 + 16 * wt + wl) * 16 + k) * K::T8 + t;
                                     o[0] = (int8_t)(w & 0xff);
@@ -337,7 +339,7 @@ stream_forward_kernel(const __grid_constant__ CUtensorMap tmx, const StreamNet* 
             {
                 const int wl = warp, wg = w0 + 16 * wt + wl;
                 const uint32_t w4a0 = __ldg(&net->w4frag[0][lane]), w4a1 = __ldg(&net->w4frag[1][lane]);
-                const uint32_t y3a = sbase + K::OFF_Y3 + wl * (16 * K::Y3S) + l4_off;
+                const uint32_t y3a = sbase + K::OFF_Y3 + wl * K::Y3W + l4_off;
 #pragma unroll
                 for (int s4 = 0; s4 < K::NST; s4++) {
                     uint32_t d[4];

@@ -1,6 +1,6 @@
 // Tensor-core-resident int8 edgeEEGNet forward for sm_100a: layers 1 AND 2 run on tcgen05.mma (kind::i8) with
 // their int32 accumulators in TMEM; the warps only requantise.  (Successor of mibmi_pipe.cu for shapes whose
-// rows are 16-byte aligned; measured motivation in DESIGN.md 4.1: the mma.sync kernel is bound by the dependent
+// rows are 16-byte aligned; measured motivation in DESIGN.md 4.2: the mma.sync kernel is bound by the dependent
 // latency of its layer-2 warps, not by any pipe.)
 //
 // One persistent CTA per SM (23 warps) works on QUADS of 4 trials:
