@@ -121,6 +121,11 @@ __device__ __forceinline__ constexpr uint32_t tcr_idesc_i8_kk(int M, int N) {   
     return (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 
+__device__ __forceinline__ uint4 tcr_lds128(const uint8_t* p) {
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(smem_u32(p)));
+    return v;
+}
 // one row of T samples: lane = 16-byte chunk (+ 32 per pass); all loads of the row are issued before the shifts
 template <class K, int K4>
 __device__ __forceinline__ void tcr_realign_row(const uint8_t* rbase, uint8_t* xrow, int c, int sh, int lane) {
@@ -129,8 +134,8 @@ __device__ __forceinline__ void tcr_realign_row(const uint8_t* rbase, uint8_t* x
 #pragma unroll
     for (int p = 0; p < P; p++)
         if (32 * p + 31 < K::CHUNKS || lane + 32 * p < K::CHUNKS) {
-            q0[p] = *reinterpret_cast<const uint4*>(rbase + 512 * p);
-            q1[p] = *reinterpret_cast<const uint4*>(rbase + 512 * p + 16);
+            q0[p] = tcr_lds128(rbase + 512 * p);          // kept 128 bits wide: the narrower loads the compiler would pick for
+            q1[p] = tcr_lds128(rbase + 512 * p + 16);     // the 5 words in use are 4-way bank conflicted at this lane stride
         }
 #pragma unroll
     for (int p = 0; p < P; p++) {
