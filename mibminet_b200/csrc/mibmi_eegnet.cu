@@ -14,10 +14,12 @@
 // registers.  CUDA-core (dp4a) kernel: 4 x (Nf + 4) / 4 dp4a per output quadruple and channel.
 #include <atomic>
 #include <new>
+#include <stdlib.h>
 #include <string.h>
 
 #include "../../include/mibmi.h"
 #include "mibmi_common.cuh"
+#include "mibmi_ptx.cuh"
 
 namespace mibmi {
 
@@ -37,9 +39,53 @@ struct EegNet {
     int8_t w3[kEegMaxK2 * kL3Taps];                    // [K2][16] torch order
     int8_t w4[kMaxF2 * kEegMaxK2];                     // [F2][K2]
     const int8_t* w5;                                  // [N][F2 * T64] device pointer
+    const uint32_t* w1frag;                            // tensor-core kernel: Toeplitz B fragments [F1][4 v][KS][2 h][32 lanes], device pointer
+    int KS, MT, XPM;                                   // k-steps of 32 (= (Nf + 63) / 32), m-tiles of 16 rows x 32 outputs, row pitch
 };
 
 __device__ __forceinline__ int eclip8(int v) { return min(max(v, -128), 127); }
+
+// layers 3, 4, 5 of the trial whose pooled layer-2 output sits in y2 (zero padded rows); all threads of the CTA
+__device__ __forceinline__ void eeg_layers345(const EegNet* __restrict__ net, const int8_t* y2, int8_t* y3, int8_t* y4, long long b,
+                                              int8_t* __restrict__ logits, int8_t* __restrict__ tap3, int8_t* __restrict__ tap4) {
+    const int K2 = net->K2, F2 = net->F2, N = net->N, T8 = net->T8, T64 = net->T64, y2s = T8 + 15;
+    const int tid = threadIdx.x, nth = blockDim.x;
+    // ---- layer 3 (eegnet.py:155-156)
+    for (int i = tid; i < K2 * T8; i += nth) {
+        const int k = i / T8, t = i - k * T8;
+        const int8_t* w = net->w3 + k * kL3Taps;
+        const int8_t* r = y2 + k * y2s + t;
+        int acc = 0;
+        for (int j = 0; j < kL3Taps; j++) acc += (int)r[j] * (int)w[j];
+        const int o = eclip8(acc / net->fac3);
+        y3[k * T8 + t] = (int8_t)o;
+        if (tap3) tap3[((size_t)b * K2 + k) * T8 + t] = (int8_t)o;
+    }
+    __syncthreads();
+    // ---- layer 4 (eegnet.py:157-161)
+    for (int i = tid; i < F2 * T64; i += nth) {
+        const int k = i / T64, q = i - k * T64;
+        const int8_t* w = net->w4 + k * K2;
+        const int off = net->off4[k], fac = net->fac4[k];
+        int s = 0;
+        for (int e = 0; e < 8; e++) {
+            int v = 0;
+            for (int c = 0; c < K2; c++) v += (int)y3[c * T8 + q * 8 + e] * (int)w[c];
+            s += max(v, -(off >> 3));
+        }
+        const int o = eclip8((s + off) / fac);
+        y4[k * T64 + q] = (int8_t)o;
+        if (tap4) tap4[((size_t)b * F2 + k) * T64 + q] = (int8_t)o;
+    }
+    __syncthreads();
+    // ---- layer 5 (eegnet.py:164-166)
+    for (int n = tid; n < N; n += nth) {
+        const int8_t* w = net->w5 + (size_t)n * F2 * T64;
+        int z = net->b5[n];
+        for (int i = 0; i < F2 * T64; i++) z += (int)y4[i] * (int)w[i];
+        logits[(size_t)b * N + n] = (int8_t)eclip8(z / net->fac5);
+    }
+}
 
 template <int D, bool MAGIC>
 __global__ void __launch_bounds__(384)
@@ -133,41 +179,139 @@ eegnet_forward_kernel(const EegNet* __restrict__ net, const int8_t* __restrict__
             if (tap2) tap2[((size_t)b * K2 + k) * T8 + q] = (int8_t)o;
         }
         __syncthreads();
-        // ---- layer 3 (eegnet.py:155-156)
-        for (int i = tid; i < K2 * T8; i += nth) {
-            const int k = i / T8, t = i - k * T8;
-            const int8_t* w = net->w3 + k * kL3Taps;
-            const int8_t* r = y2 + k * y2s + t;
-            int acc = 0;
-            for (int j = 0; j < kL3Taps; j++) acc += (int)r[j] * (int)w[j];
-            const int o = eclip8(acc / net->fac3);
-            y3[k * T8 + t] = (int8_t)o;
-            if (tap3) tap3[((size_t)b * K2 + k) * T8 + t] = (int8_t)o;
-        }
+        eeg_layers345(net, y2, y3, y4, b, logits, tap3, tap4);
         __syncthreads();
-        // ---- layer 4 (eegnet.py:157-161)
-        for (int i = tid; i < F2 * T64; i += nth) {
-            const int k = i / T64, q = i - k * T64;
-            const int8_t* w = net->w4 + k * K2;
-            const int off = net->off4[k], fac = net->fac4[k];
-            int s = 0;
-            for (int e = 0; e < 8; e++) {
-                int v = 0;
-                for (int c = 0; c < K2; c++) v += (int)y3[c * T8 + q * 8 + e] * (int)w[c];
-                s += max(v, -(off >> 3));
+    }
+}
+
+
+// ---------------------------------------------------------------------------------------------------------
+#ifndef MIBMI_EEG_MINB
+#define MIBMI_EEG_MINB 2      // CTAs of 256 threads per SM the register allocation aims at
+#endif
+// Tensor-core form of layers 1 + 2 (the temporal conv is the dense contraction of this topology: F1 x C x T x Nf MACs).
+// Warp f = temporal filter f.  Per EEG channel the Nf-tap convolution is a Hankel x Toeplitz product on mma.sync.m16n8k32.s8:
+//   A[16 rows x 32]  = the padded input row itself, row r = bytes 32 r .. (ldmatrix.x4, rows 32 B apart, k-step s adds 32 s)
+//   B[32 x 8]        = Toeplitz of the filter's taps: B[kk][n] = w1[f][32 s + kk - (8 v + n)], 4 variants v = outputs 8 v .. 8 v + 7
+// so D[r][8 v + n] is conv output t = 32 r + 8 v + n; KS = (Nf + 63) / 32 k-steps, 4 KS IMMA per 512 outputs.  The filter's
+// 8 KS fragment words stay in registers for the whole launch.  The epilogue requantises (batch_norm1 / quant2), multiplies by
+// the D spatial weights of this filter and accumulates over the channels in registers; a pooling group of 8 outputs is one
+// (row, variant) = 4 lanes x 2 values, reduced with two shuffles, requantised (batch_norm2 + ReLU + pool, quant3) and stored.
+template <int D, int KS, bool MAGIC, int MAXT>
+__global__ void __launch_bounds__(MAXT, MAXT <= 256 ? MIBMI_EEG_MINB : 1)
+eegnet_mma_kernel(const EegNet* __restrict__ net, const int8_t* __restrict__ x, long long B, int8_t* __restrict__ logits,
+                  int8_t* __restrict__ tap2, int8_t* __restrict__ tap3, int8_t* __restrict__ tap4) {
+    extern __shared__ __align__(16) int8_t smem[];
+    const int C = net->C, T = net->T, K2 = net->K2, F2 = net->F2, Nf = net->Nf;
+    const int T8 = net->T8, T64 = net->T64, XP = net->XPM, MT = net->MT;
+    const int y2s = T8 + 15;
+    int8_t* xs = smem;                                                          // [C][XP], XP % 16 == 0
+    int8_t* y2 = xs + (size_t)C * XP;                                           // [K2][T8 + 15]
+    int8_t* y3 = y2 + (size_t)K2 * y2s;                                         // [K2][T8]
+    int8_t* y4 = y3 + (size_t)K2 * T8;                                          // [F2][T64]
+    const int tid = threadIdx.x, nth = blockDim.x, lane = tid & 31, f = tid >> 5;
+    const int g = lane >> 2, q = lane & 3;
+    const int PL = Nf / 2 - 1;
+
+    uint32_t bf[4][KS][2];
+#pragma unroll
+    for (int v = 0; v < 4; v++)
+#pragma unroll
+        for (int s = 0; s < KS; s++)
+#pragma unroll
+            for (int h = 0; h < 2; h++) bf[v][s][h] = net->w1frag[(((f * 4 + v) * KS + s) * 2 + h) * 32 + lane];
+    const int off1 = MAGIC ? net->sg1[f] * net->off1[f] : net->off1[f], fac1 = MAGIC ? net->mg1[f] : net->fac1[f], shf1 = net->sh1[f];
+    int off2[D], fac2[D], thr2[D];
+#pragma unroll
+    for (int d = 0; d < D; d++) {
+        off2[d] = net->off2[f * D + d];
+        fac2[d] = net->fac2[f * D + d];
+        thr2[d] = -(off2[d] >> 3);
+    }
+    for (int i = tid; i < C * XP / 4; i += nth) reinterpret_cast<int*>(xs)[i] = 0;
+    for (int i = tid; i < K2 * y2s; i += nth) y2[i] = 0;
+    __syncthreads();
+    // ldmatrix.x4 lane addressing: matrix j = lane >> 3, row (lane & 7) + 8 (j & 1), k-half j >> 1
+    const uint32_t a_off = 32 * ((lane & 7) + 8 * ((lane >> 3) & 1)) + 16 * (lane >> 4);
+
+    for (long long b = blockIdx.x; b < B; b += gridDim.x) {
+        const int8_t* xb = x + (size_t)b * C * T;
+{
+            // aligned 32-bit global loads of the (arbitrarily aligned) trial, bytes scattered to their padded rows; (c, t) advance
+            // incrementally (no division per element)
+            const uintptr_t ga = reinterpret_cast<uintptr_t>(xb);
+            const int mis = (int)(ga & 3), total = C * T, nwords = (mis + total + 3) >> 2;
+            const uint32_t* gw = reinterpret_cast<const uint32_t*>(ga - mis);
+            int i = 4 * tid - mis;
+            int c = i >= 0 ? i / T : 0, t = i - c * T;
+            for (int w = tid; w < nwords; w += nth) {
+                const uint32_t v = __ldg(gw + w);
+                int cj = c, tj = t;
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    if (tj >= T) { tj -= T; cj++; }
+                    if (i + j >= 0 && i + j < total) xs[cj * XP + PL + tj] = (int8_t)(v >> (8 * j));
+                    tj++;
+                }
+                i += 4 * nth;
+                t += 4 * nth;
+                while (t >= T) { t -= T; c++; }
             }
-            const int o = eclip8((s + off) / fac);
-            y4[k * T64 + q] = (int8_t)o;
-            if (tap4) tap4[((size_t)b * F2 + k) * T64 + q] = (int8_t)o;
         }
         __syncthreads();
-        // ---- layer 5 (eegnet.py:164-166)
-        for (int n = tid; n < N; n += nth) {
-            const int8_t* w = net->w5 + (size_t)n * F2 * T64;
-            int z = net->b5[n];
-            for (int i = 0; i < F2 * T64; i++) z += (int)y4[i] * (int)w[i];
-            logits[(size_t)b * N + n] = (int8_t)eclip8(z / net->fac5);
+        for (int mt = 0; mt < MT; mt++) {
+            int a[D][4][4];
+#pragma unroll
+            for (int d = 0; d < D; d++)
+#pragma unroll
+                for (int v = 0; v < 4; v++) a[d][v][0] = a[d][v][1] = a[d][v][2] = a[d][v][3] = 0;
+            const uint32_t abase = smem_u32(xs) + 512 * mt + a_off;
+#pragma unroll 2
+            for (int c = 0; c < C; c++) {
+                int acc[4][4];
+#pragma unroll
+                for (int v = 0; v < 4; v++) acc[v][0] = acc[v][1] = acc[v][2] = acc[v][3] = 0;
+#pragma unroll
+                for (int s = 0; s < KS; s++) {
+                    uint32_t af[4];
+                    ldsm_x4(af, abase + c * XP + 32 * s);
+#pragma unroll
+                    for (int v = 0; v < 4; v++) mma_k32(acc[v], af, bf[v][s][0], bf[v][s][1]);
+                }
+                int w2v[D];
+#pragma unroll
+                for (int d = 0; d < D; d++) w2v[d] = (int)net->w2[(f * D + d) * C + c];
+#pragma unroll
+                for (int v = 0; v < 4; v++)
+#pragma unroll
+                    for (int ci = 0; ci < 4; ci++) {
+                        const int xv = acc[v][ci] + off1;
+                        const int y = eclip8(MAGIC ? tdiv_magic(xv, fac1, shf1) : xv / fac1);     // MAGIC: factor sign folded into taps / offset
+#pragma unroll
+                        for (int d = 0; d < D; d++) a[d][v][ci] += y * w2v[d];
+                    }
+            }
+            // pooling group (row, v): outputs 32 row + 8 v .. + 7 = the 4 lanes q of a row x (ci & 1)
+#pragma unroll
+            for (int d = 0; d < D; d++)
+#pragma unroll
+                for (int v = 0; v < 4; v++)
+#pragma unroll
+                    for (int hf = 0; hf < 2; hf++) {
+                        int p = max(a[d][v][2 * hf], thr2[d]) + max(a[d][v][2 * hf + 1], thr2[d]);
+                        p += __shfl_xor_sync(0xffffffffu, p, 1);
+                        p += __shfl_xor_sync(0xffffffffu, p, 2);
+                        const int pg = 4 * (16 * mt + g + 8 * hf) + v;          // pooled sample index
+                        if (q == 0 && pg < T8) {
+                            const int k = f * D + d;
+                            const int o = eclip8((p + off2[d]) / fac2[d]);
+                            y2[k * y2s + 7 + pg] = (int8_t)o;
+                            if (tap2) tap2[((size_t)b * K2 + k) * T8 + pg] = (int8_t)o;
+                        }
+                    }
         }
+        __syncthreads();
+        eeg_layers345(net, y2, y3, y4, b, logits, tap3, tap4);
         __syncthreads();
     }
 }
@@ -179,9 +323,11 @@ using namespace mibmi;
 struct mibmi_eegnet {
     int device = 0, num_sms = 0;
     int C = 0, T = 0, K2 = 0, F2 = 0, N = 0, D = 0, threads = 256, magic1 = 0;
-    size_t smem = 0;
+    int F1 = 0, KS = 0;                 // tensor-core kernel: warps = F1, k-steps; KS == 0: no instantiation (dp4a kernel)
+    size_t smem = 0, smem_mma = 0;
     EegNet* net_dev = nullptr;
     int8_t* w5_dev = nullptr;
+    uint32_t* w1frag_dev = nullptr;
     std::atomic<long long> launches{0};
     std::atomic<int> last_cuda{0};
 };
@@ -246,7 +392,9 @@ int mibmi_eegnet_create(const mibmi_eegnet_params_t* p, int device, mibmi_eegnet
         const long long oa = h->off1[f] < 0 ? -(long long)h->off1[f] : h->off1[f];
         h->sg1[f] = h->fac1[f] < 0 ? -1 : 1;
         // tdiv(x, d) == (mulhi(x, m) >> s) + (x < 0) for d >= 4, |x| < 2^29; otherwise hardware division
-        if (fa < 4 || fa > 0x7fffffffLL || 128 * sum + oa >= (1LL << 29)) { h->magic1 = 0; continue; }
+        bool has_m128 = false;
+        for (int j = 0; j < Nf; j++) has_m128 |= p->l1_weight[f * Nf + j] == -128;       // cannot be negated in int8
+        if (fa < 4 || fa > 0x7fffffffLL || 128 * sum + oa >= (1LL << 29) || (has_m128 && h->fac1[f] < 0)) { h->magic1 = 0; continue; }
         int lg = 0;
         while ((1LL << (lg + 1)) <= fa) lg++;
         const long long mm = (long long)(((__int128)1 << (30 + lg)) / fa) + 1;
@@ -286,11 +434,48 @@ int mibmi_eegnet_create(const mibmi_eegnet_params_t* p, int device, mibmi_eegnet
     if (e == cudaSuccess) e = cudaMalloc(&n->w5_dev, w5n ? w5n : 1);
     if (e == cudaSuccess && w5n) e = cudaMemcpy(n->w5_dev, p->l5_weight, w5n, cudaMemcpyHostToDevice);
     h->w5 = n->w5_dev;
+    // tensor-core kernel: Toeplitz B fragments of every filter (see eegnet_mma_kernel)
+    n->F1 = F1;
+    h->KS = (Nf + 63) / 32;
+    h->MT = ((T + 31) / 32 + 15) / 16;
+    {
+        const int need1 = 32 * 16 * h->MT + 32 * h->KS, need2 = T + Nf + 32;
+        h->XPM = ((need1 > need2 ? need1 : need2) + 15) / 16 * 16;
+    }
+    const bool mma_shape = Nf % 32 == 0 && (h->KS == 2 || h->KS == 3 || h->KS == 5);
+    n->smem_mma = (size_t)C * h->XPM + (size_t)K2 * (h->T8 + 15) + (size_t)K2 * h->T8 + (size_t)F2 * h->T64 + 16;
+    if (e == cudaSuccess && mma_shape && n->smem_mma <= (size_t)prop.sharedMemPerBlockOptin) {
+        const size_t nw = (size_t)F1 * 4 * h->KS * 2 * 32;
+        uint32_t* fr = new (std::nothrow) uint32_t[nw];
+        if (fr) {
+            for (int f = 0; f < F1; f++)
+                for (int v = 0; v < 4; v++)
+                    for (int s = 0; s < h->KS; s++)
+                        for (int hh = 0; hh < 2; hh++)
+                            for (int lane = 0; lane < 32; lane++) {
+                                const int g = lane >> 2, q = lane & 3;
+                                uint32_t w = 0;
+                                for (int i = 0; i < 4; i++) {
+                                    const int tap = 32 * s + 16 * hh + 4 * q + i - (8 * v + g);
+                                    const int sg = h->magic1 ? h->sg1[f] : 1;       // tdiv(x, -d) == tdiv(-x, d)
+                                    const int val = (tap >= 0 && tap < Nf) ? sg * p->l1_weight[f * Nf + tap] : 0;
+                                    w |= (uint32_t)(uint8_t)(int8_t)val << (8 * i);
+                                }
+                                fr[(((f * 4 + v) * h->KS + s) * 2 + hh) * 32 + lane] = w;
+                            }
+            e = cudaMalloc(&n->w1frag_dev, nw * 4);
+            if (e == cudaSuccess) e = cudaMemcpy(n->w1frag_dev, fr, nw * 4, cudaMemcpyHostToDevice);
+            delete[] fr;
+            if (e == cudaSuccess) n->KS = h->KS;
+        }
+    }
+    h->w1frag = n->w1frag_dev;
     if (e == cudaSuccess) e = cudaMalloc(&n->net_dev, sizeof(EegNet));
     if (e == cudaSuccess) e = cudaMemcpy(n->net_dev, h, sizeof(EegNet), cudaMemcpyHostToDevice);
     delete h;
     if (e != cudaSuccess) {
         if (n->w5_dev) cudaFree(n->w5_dev);
+        if (n->w1frag_dev) cudaFree(n->w1frag_dev);
         if (n->net_dev) cudaFree(n->net_dev);
         delete n;
         return MIBMI_ERR_CUDA;
@@ -304,6 +489,7 @@ int mibmi_eegnet_destroy(mibmi_eegnet_t* n) {
     {
         Guard dg(n->device);
         if (n->w5_dev) cudaFree(n->w5_dev);
+        if (n->w1frag_dev) cudaFree(n->w1frag_dev);
         if (n->net_dev) cudaFree(n->net_dev);
     }
     delete n;
@@ -318,14 +504,33 @@ int mibmi_eegnet_forward_int8_taps(mibmi_eegnet_t* n, const int8_t* x_dev, int64
     if (!x_dev || !logits_dev) return MIBMI_ERR_NULL;
     Guard dg(n->device);
     cudaError_t e = dg.err;
-    auto kern = n->D == 1 ? (n->magic1 ? eegnet_forward_kernel<1, true> : eegnet_forward_kernel<1, false>)
-                          : (n->magic1 ? eegnet_forward_kernel<2, true> : eegnet_forward_kernel<2, false>);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)n->smem);
-    if (e == cudaSuccess) {
-        long long grid = (long long)n->num_sms * (n->smem > 100 * 1024 ? 1 : 2);
-        if (grid > B) grid = B;
-        kern<<<(unsigned)grid, n->threads, n->smem, (cudaStream_t)stream>>>(n->net_dev, x_dev, B, logits_dev, y2, y3, y4);
-        e = cudaGetLastError();
+    const char* force = getenv("MIBMI_EEGNET_DP4A");                       // experiment switch: CUDA-core kernel
+    if (n->KS && !(force && force[0] == '1')) {
+        using kern_t = void (*)(const EegNet*, const int8_t*, long long, int8_t*, int8_t*, int8_t*, int8_t*);
+        kern_t kern = nullptr;
+#define MIBMI_EEG_PICK(d, ks) \
+        if (n->D == d && n->KS == ks)                                                                                     \
+            kern = n->F1 <= 8 ? (n->magic1 ? eegnet_mma_kernel<d, ks, true, 256> : eegnet_mma_kernel<d, ks, false, 256>)  \
+                              : (n->magic1 ? eegnet_mma_kernel<d, ks, true, 512> : eegnet_mma_kernel<d, ks, false, 512>);
+        MIBMI_EEG_PICK(1, 2) MIBMI_EEG_PICK(1, 3) MIBMI_EEG_PICK(1, 5) MIBMI_EEG_PICK(2, 2) MIBMI_EEG_PICK(2, 3) MIBMI_EEG_PICK(2, 5)
+#undef MIBMI_EEG_PICK
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)n->smem_mma);
+        if (e == cudaSuccess) {
+            long long grid = (long long)n->num_sms * (n->F1 > 8 ? 1 : n->smem_mma > 72 * 1024 ? 2 : MIBMI_EEG_MINB);
+            if (grid > B) grid = B;
+            kern<<<(unsigned)grid, 32 * n->F1, n->smem_mma, (cudaStream_t)stream>>>(n->net_dev, x_dev, B, logits_dev, y2, y3, y4);
+            e = cudaGetLastError();
+        }
+    } else {
+        auto kern = n->D == 1 ? (n->magic1 ? eegnet_forward_kernel<1, true> : eegnet_forward_kernel<1, false>)
+                              : (n->magic1 ? eegnet_forward_kernel<2, true> : eegnet_forward_kernel<2, false>);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)n->smem);
+        if (e == cudaSuccess) {
+            long long grid = (long long)n->num_sms * (n->smem > 100 * 1024 ? 1 : 2);
+            if (grid > B) grid = B;
+            kern<<<(unsigned)grid, n->threads, n->smem, (cudaStream_t)stream>>>(n->net_dev, x_dev, B, logits_dev, y2, y3, y4);
+            e = cudaGetLastError();
+        }
     }
     if (e != cudaSuccess) {
         n->last_cuda.store((int)e);

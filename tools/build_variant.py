@@ -9,7 +9,7 @@ _build.build_library()
 out = os.path.join(_build.ROOT, "tools", "variants", name)
 os.makedirs(out, exist_ok=True)
 nvcc = _build._nvcc()
-VAR = ["mibmi_pipe.cu", "mibmi_tc.cu", "mibmi_tcr.cu"]
+VAR = ["mibmi_pipe.cu", "mibmi_tc.cu", "mibmi_tcr.cu", "mibmi_eegnet.cu"]
 objs = [os.path.join(_build.LIB_DIR, s.replace(".cu", ".o")) for s in _build.SOURCES if s not in VAR]
 procs = []
 for src in VAR:
