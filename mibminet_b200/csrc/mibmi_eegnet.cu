@@ -44,6 +44,11 @@ struct EegNet {
 };
 
 __device__ __forceinline__ int eclip8(int v) { return min(max(v, -128), 127); }
+__device__ __forceinline__ int esat8(int v) {          // the same clip as one saturating conversion
+    int r;
+    asm("cvt.sat.s8.s32 %0, %1;" : "=r"(r) : "r"(v));
+    return r;
+}
 
 // layers 3, 4, 5 of the trial whose pooled layer-2 output sits in y2 (zero padded rows); all threads of the CTA
 __device__ __forceinline__ void eeg_layers345(const EegNet* __restrict__ net, const int8_t* y2, int8_t* y3, int8_t* y4, long long b,
@@ -268,9 +273,9 @@ eegnet_mma_kernel(const EegNet* __restrict__ net, const int8_t* __restrict__ x, 
             const uint32_t abase = smem_u32(xs) + 512 * mt + a_off;
 #pragma unroll 2
             for (int c = 0; c < C; c++) {
-                int acc[4][4];
+                int acc[4][4];                                  // the BN offset rides in the accumulator
 #pragma unroll
-                for (int v = 0; v < 4; v++) acc[v][0] = acc[v][1] = acc[v][2] = acc[v][3] = 0;
+                for (int v = 0; v < 4; v++) acc[v][0] = acc[v][1] = acc[v][2] = acc[v][3] = off1;
 #pragma unroll
                 for (int s = 0; s < KS; s++) {
                     uint32_t af[4];
@@ -285,8 +290,8 @@ eegnet_mma_kernel(const EegNet* __restrict__ net, const int8_t* __restrict__ x, 
                 for (int v = 0; v < 4; v++)
 #pragma unroll
                     for (int ci = 0; ci < 4; ci++) {
-                        const int xv = acc[v][ci] + off1;
-                        const int y = eclip8(MAGIC ? tdiv_magic(xv, fac1, shf1) : xv / fac1);     // MAGIC: factor sign folded into taps / offset
+                        const int xv = acc[v][ci];
+                        const int y = esat8(MAGIC ? tdiv_magic(xv, fac1, shf1) : xv / fac1);      // MAGIC: factor sign folded into taps / offset
 #pragma unroll
                         for (int d = 0; d < D; d++) a[d][v][ci] += y * w2v[d];
                     }
