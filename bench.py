@@ -57,9 +57,10 @@ def parse_args():
     ap.add_argument("--path", default="auto", choices=["auto", "fused", "fused_pipe", "fused_v1", "generic"])
     ap.add_argument("--ctas-per-sm", type=int, default=0)
     ap.add_argument("--shape", default="64x480", help="CxT of the trials (default: BASELINE config 2; 22x1125 = config 3)")
-    ap.add_argument("--workload", default="trials", choices=["trials", "stream"],
+    ap.add_argument("--workload", default="trials", choices=["trials", "stream", "eegnet"],
                     help="trials: BASELINE config 2 (default, the headline line); stream: config 5, sliding windows "
-                         "(480 samples, stride 16) over continuous 64-ch recordings")
+                         "(480 samples, stride 16) over continuous 64-ch recordings; eegnet: the EEGNet / Q-EEGNet layer "
+                         "order (SURVEY 8(f)4, temporal conv first, F1 = 8, D = 2, Nf = 128), default shape 22x1125")
     ap.add_argument("--subjects", type=int, default=4096, help="stream workload: subjects per GPU")
     ap.add_argument("--stream-len", type=int, default=9600, help="stream workload: samples per subject (60 s at 160 Hz)")
     ap.add_argument("--stream-mode", default="auto", choices=["auto", "fused", "gather"])
@@ -259,6 +260,76 @@ def main_stream(args, rank, local_rank, world):
         dist.destroy_process_group()
 
 
+def main_eegnet(args, rank, local_rank, world):
+    """EEGNet / Q-EEGNet layer order, every rank its own B trials (weak scaling, no collective)."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from mibminet_b200 import convert, synth
+    from mibminet_b200.engine import EEGNetInt8
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    Ce, Te = (22, 1125) if args.shape == "64x480" else (C, T)
+    F1, D, Nf, B = 8, 2, 128, min(args.batch, 16384)
+    params = convert.eegnet_params_from_state_dict(synth.make_eegnet_state_dict(C=Ce, T=Te, F1=F1, D=D, Nf=Nf, seed=NET_SEED),
+                                                   C=Ce, T=Te, F1=F1, D=D)
+    net = EEGNetInt8(params, device=dev)
+    g = torch.Generator(device=dev)
+    g.manual_seed(3000 + rank)
+    x = torch.randint(-127, 128, (B, Ce, Te), dtype=torch.int8, device=dev, generator=g)
+    for _ in range(max(args.warmup, 3)):
+        y = net.forward(x)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    l0, t0 = net.launch_count, time.perf_counter()
+    ev0.record()
+    for _ in range(args.steps):
+        y = net.forward(x)
+    ev1.record()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    clocks = sampler.stop(t0, time.perf_counter()) if sampler else None
+    t = torch.tensor([ev0.elapsed_time(ev1)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t[0]) / args.steps
+    if rank == 0:
+        peak, peak_src = measured_peaks()
+        alg = B * (Ce * Te + N_CLASSES)
+        macs = F1 * Ce * Te * Nf + F1 * D * Ce * Te
+        res = {"metric": "int8 EEGNet-order trials/sec", "value": world * B / (ms * 1e-3), "unit": "trials/s", "n_gpus": world,
+               "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+               "vs_baseline": None, "dtype": "int8", "data": "synthetic",
+               "config": {"workload": f"EEGNet / Q-EEGNet layer order (SURVEY 8(f)4), {Ce}ch x {Te} samples, F1={F1} D={D} Nf={Nf}",
+                          "trials_per_gpu_per_step": B, "l2_policy": f"input per step {B * Ce * Te / 1e9:.2f} GB > 126 MB L2"},
+               "roofline": {"bound": "tensor", "achieved": B * macs * 2 / (ms * 1e-3) / 1e12, "peak": None, "unit": "TOP/s",
+                            "frac": None, "traffic": None, "hbm_frac": alg / (ms * 1e-3) / 1e9 / peak, "peak_source": peak_src,
+                            "note": "mma.sync int8 kernel bound by the requant epilogue (F1*C*T outputs per trial), DESIGN.md 4.7; no "
+                                    "measured int8 tensor peak on this pool, so no fraction is claimed"},
+               "gpu_launches": int(net.launch_count - l0), "clocks": clocks}
+        if not args.no_cpu_baseline:
+            sys.path.insert(0, os.path.join(ROOT, "oracle"))
+            import eegnet_np
+            n = 16
+            t0 = time.perf_counter()
+            ref = eegnet_np.forward(params, x[:n].cpu().numpy())
+            dt = time.perf_counter() - t0
+            res["config"]["bit_exact_checked"] = bool(np.array_equal(ref, y[:n].cpu().numpy()))
+            res["cpu_baseline"] = {"value": n / dt, "unit": "trials/s", "cores": 1, "kind": "port",
+                                   "sample": f"{n} trials through oracle/eegnet_np.py (NumPy; the reference has no integer model of this order)"}
+        print(json.dumps(res))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
 def main():
     global C, T, ALG_BYTES_PER_TRIAL, WORKLOAD
     args = parse_args()
@@ -273,6 +344,8 @@ def main():
         return main_reference(args, rank)
     if args.workload == "stream":
         return main_stream(args, rank, local_rank, world)
+    if args.workload == "eegnet":
+        return main_eegnet(args, rank, local_rank, world)
 
     import numpy as np
     import torch
