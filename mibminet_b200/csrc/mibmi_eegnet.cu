@@ -7,11 +7,15 @@
 //   L2  a[k][t] = sum_c y1[k / D][c][t] w2[k][c];  s = sum_8 max(a, -(off2[k] >> 3));  y2 = clip8(tdiv(s + off2[k], fac2[k]))
 //   L3..L5 as in mibmi_generic.cu.
 //
-// One CTA per trial.  Layers 1 and 2 are fused so that the F1 x C x T intermediate (198 kB at 22 x 1125) never exists: a thread
-// owns 4 consecutive samples of 4 temporal filters, walks over the EEG channels, computes the Nf-tap convolution with dp4a on
-// ALIGNED words of the padded input row against 4 byte-shifted copies of the taps (output t0 + s = sum_m xpad[t0 + m] W_s[m],
-// W_s[m] = w[m - s]), requantises with the hardware division (exact for any factor) and accumulates the spatial conv in
-// registers.  CUDA-core (dp4a) kernel: 4 x (Nf + 4) / 4 dp4a per output quadruple and channel.
+// One CTA per trial; layers 1 and 2 are fused so that the F1 x C x T intermediate (198 kB at 22 x 1125) never exists.
+//   eegnet_mma_kernel      (default, Nf a multiple of 32): warp = temporal filter, the Nf-tap convolution as a Hankel x Toeplitz
+//                          product on mma.sync.m16n8k32.s8 (the dense contraction of this topology), requant + spatial conv +
+//                          pooling in the epilogue -- see the comment above the kernel.
+//   eegnet_forward_kernel  (fallback, any Nf <= 128 that is a multiple of 4): a thread owns 4 consecutive samples of 4 filters,
+//                          walks over the EEG channels, convolves with dp4a on ALIGNED words of the padded row against 4
+//                          byte-shifted copies of the taps (output t0 + s = sum_m xpad[t0 + m] W_s[m], W_s[m] = w[m - s]).
+// Both requantise with the magic division of DESIGN.md section 5 when every layer-1 factor is inside its proven range, and
+// with the hardware division otherwise (exact for any factor).
 #include <atomic>
 #include <new>
 #include <stdlib.h>
@@ -23,6 +27,10 @@
 
 namespace mibmi {
 
+#ifndef MIBMI_EEG_CUNROLL
+#define MIBMI_EEG_CUNROLL 1
+#endif
+constexpr int kEegCUnroll = MIBMI_EEG_CUNROLL;       // channel loop of the tensor-core kernel
 constexpr int kEegMaxF1 = 16, kEegMaxK2 = 32, kEegMaxNf = 128, kEegMaxNW = kEegMaxNf / 4 + 1;
 
 struct EegNet {
@@ -84,11 +92,13 @@ __device__ __forceinline__ void eeg_layers345(const EegNet* __restrict__ net, co
     }
     __syncthreads();
     // ---- layer 5 (eegnet.py:164-166)
-    for (int n = tid; n < N; n += nth) {
+    for (int n = tid >> 5; n < N; n += nth >> 5) {            // warp = class: lanes split the features, shuffle reduction
         const int8_t* w = net->w5 + (size_t)n * F2 * T64;
-        int z = net->b5[n];
-        for (int i = 0; i < F2 * T64; i++) z += (int)y4[i] * (int)w[i];
-        logits[(size_t)b * N + n] = (int8_t)eclip8(z / net->fac5);
+        int z = 0;
+        for (int i = tid & 31; i < F2 * T64; i += 32) z += (int)y4[i] * (int)w[i];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) z += __shfl_xor_sync(0xffffffffu, z, o);
+        if ((tid & 31) == 0) logits[(size_t)b * N + n] = (int8_t)eclip8((z + net->b5[n]) / net->fac5);
     }
 }
 
@@ -249,18 +259,24 @@ eegnet_mma_kernel(const EegNet* __restrict__ net, const int8_t* __restrict__ x, 
             const uint32_t* gw = reinterpret_cast<const uint32_t*>(ga - mis);
             int i = 4 * tid - mis;
             int c = i >= 0 ? i / T : 0, t = i - c * T;
-            for (int w = tid; w < nwords; w += nth) {
-                const uint32_t v = __ldg(gw + w);
-                int cj = c, tj = t;
+            for (int w = tid; w < nwords; w += 4 * nth) {              // 4 independent loads in flight per thread
+                uint32_t v4[4];
 #pragma unroll
-                for (int j = 0; j < 4; j++) {
-                    if (tj >= T) { tj -= T; cj++; }
-                    if (i + j >= 0 && i + j < total) xs[cj * XP + PL + tj] = (int8_t)(v >> (8 * j));
-                    tj++;
+                for (int u = 0; u < 4; u++) v4[u] = w + u * nth < nwords ? __ldg(gw + w + u * nth) : 0u;
+#pragma unroll
+                for (int u = 0; u < 4; u++) {
+                    const uint32_t v = v4[u];
+                    int cj = c, tj = t;
+#pragma unroll
+                    for (int j = 0; j < 4; j++) {
+                        if (tj >= T) { tj -= T; cj++; }
+                        if (i + j >= 0 && i + j < total) xs[cj * XP + PL + tj] = (int8_t)(v >> (8 * j));
+                        tj++;
+                    }
+                    i += 4 * nth;
+                    t += 4 * nth;
+                    while (t >= T) { t -= T; c++; }
                 }
-                i += 4 * nth;
-                t += 4 * nth;
-                while (t >= T) { t -= T; c++; }
             }
         }
         __syncthreads();
@@ -271,7 +287,7 @@ eegnet_mma_kernel(const EegNet* __restrict__ net, const int8_t* __restrict__ x, 
 #pragma unroll
                 for (int v = 0; v < 4; v++) a[d][v][0] = a[d][v][1] = a[d][v][2] = a[d][v][3] = 0;
             const uint32_t abase = smem_u32(xs) + 512 * mt + a_off;
-#pragma unroll 2
+#pragma unroll kEegCUnroll
             for (int c = 0; c < C; c++) {
                 int acc[4][4];                                  // the BN offset rides in the accumulator
 #pragma unroll
