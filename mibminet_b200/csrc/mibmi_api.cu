@@ -43,6 +43,12 @@ struct mibmi_net {
     int8_t* hx_pin[2] = {nullptr, nullptr};
     int8_t* hy_pin[2] = {nullptr, nullptr};
     int64_t h_cap = 0;
+    // Wolf-order rows no tensor map describes: transposed chunk by chunk into an L2-sized scratch (mibmi_reorder.cu);
+    // slot 0 = caller's stream, slots 0 / 1 = the two streams of the host entry point
+    bool wolf_reorder_ok = false;
+    int64_t wolf_chunk = 0;
+    std::mutex wolf_mu;
+    int8_t* wolf_scratch[2] = {nullptr, nullptr};
 };
 
 namespace {
@@ -484,6 +490,13 @@ int validate(const mibmi_params_t* p) {
     return MIBMI_OK;
 }
 
+void free_wolf_scratch(mibmi_net* n) {
+    for (int i = 0; i < 2; i++) {
+        if (n->wolf_scratch[i]) cudaFree(n->wolf_scratch[i]);
+        n->wolf_scratch[i] = nullptr;
+    }
+}
+
 void free_host_staging(mibmi_net* n) {
     for (int i = 0; i < 2; i++) {
         if (n->hx_dev[i]) cudaFree(n->hx_dev[i]);
@@ -499,8 +512,45 @@ size_t trial_bytes(const mibmi_net* n, int layout) {
     return layout == MIBMI_LAYOUT_BCT ? (size_t)n->C * n->T : (size_t)n->T * align4(n->C);
 }
 
+// The fused module-order kernels, best first.
+cudaError_t launch_fused_bct(mibmi_net* net, int path, const int8_t* x, int64_t B, int8_t* logits, const PeerOut& peers,
+                             int8_t* t1, int8_t* t2, int8_t* t3, int8_t* t4, cudaStream_t stream) {
+    if (path == MIBMI_PATH_FUSED && net->tc_ok)
+        return launch_tc(net->pipe_dev, net->pipe_fast1, net->C, net->T, x, B, logits, peers, t1, t2, t3, t4, net->num_sms, stream);
+    if (path == MIBMI_PATH_FUSED && net->tcr_ok)
+        return launch_tcr(net->pipe_dev, net->pipe_fast1, net->C, net->T, x, B, logits, peers, t1, t2, t3, t4, net->num_sms, stream);
+    return launch_pipe(net->pipe_dev, net->pipe_fast1, net->C, net->T, x, B, logits, peers, t1, t2, t3, t4, net->num_sms, stream);
+}
+
+// Wolf order through the reorder scratch: transpose a chunk (it stays in L2), run the fused kernel on it, next chunk.
+cudaError_t launch_wolf_chunks(mibmi_net* net, int path, int slot, const int8_t* x, int64_t B, int8_t* logits,
+                               const PeerOut& peers, int8_t* t1, int8_t* t2, int8_t* t3, int8_t* t4, cudaStream_t stream) {
+    const size_t CT = (size_t)net->C * net->T, in_bytes = (size_t)net->T * align4(net->C);
+    {
+        std::lock_guard<std::mutex> lk(net->wolf_mu);
+        if (!net->wolf_scratch[slot]) {
+            cudaError_t e = cudaMalloc(&net->wolf_scratch[slot], CT * (size_t)net->wolf_chunk + 16);
+            if (e != cudaSuccess) return e;
+        }
+    }
+    int8_t* scratch = net->wolf_scratch[slot];
+    const int T8 = net->T / 8, T64 = T8 / 8;
+    for (int64_t off = 0; off < B; off += net->wolf_chunk) {
+        const int64_t nb = B - off < net->wolf_chunk ? B - off : net->wolf_chunk;
+        cudaError_t e = launch_wolf_reorder(x + off * in_bytes, scratch, nb, net->C, net->T, net->num_sms, stream);
+        if (e != cudaSuccess) return e;
+        PeerOut po = peers;
+        for (int i = 0; i < po.n; i++) po.p[i] += off * net->N;
+        e = launch_fused_bct(net, path, scratch, nb, logits + off * net->N, po,
+                             t1 ? t1 + off * net->F2 * net->T : nullptr, t2 ? t2 + off * net->F2 * T8 : nullptr,
+                             t3 ? t3 + off * net->F2 * T8 : nullptr, t4 ? t4 + off * net->F2 * T64 : nullptr, stream);
+        if (e != cudaSuccess) return e;
+    }
+    return cudaSuccess;
+}
+
 int forward_impl(mibmi_net* net, const int8_t* x, int64_t B, int layout, int8_t* logits, int8_t* t1, int8_t* t2,
-                 int8_t* t3, int8_t* t4, bool taps, cudaStream_t stream, const PeerOut* peers = nullptr) {
+                 int8_t* t3, int8_t* t4, bool taps, cudaStream_t stream, const PeerOut* peers = nullptr, int slot = 0) {
     if (!net) return MIBMI_ERR_NULL;
     if (B < 0 || (layout != MIBMI_LAYOUT_BCT && layout != MIBMI_LAYOUT_BTC)) return MIBMI_ERR_PARAM;
     if (B == 0) return MIBMI_OK;   // empty batch: nothing to read or write, pointers may be null
@@ -508,7 +558,9 @@ int forward_impl(mibmi_net* net, const int8_t* x, int64_t B, int layout, int8_t*
     if (((uintptr_t)x & 15) != 0 || (net->N == 4 && ((uintptr_t)logits & 3) != 0)) return MIBMI_ERR_ALIGN;
     int path = net->force_path;
     const bool wolf_fused = net->tc_wolf_ok && layout == MIBMI_LAYOUT_BTC;     // tcgen05 kernel, K-major operand from the Wolf order
-    const bool pipe_possible = net->pipe_ok && (layout == MIBMI_LAYOUT_BCT || (wolf_fused && net->force_path != MIBMI_PATH_FUSED_PIPE));
+    const bool wolf_reorder = net->wolf_reorder_ok && layout == MIBMI_LAYOUT_BTC && !wolf_fused;   // transpose into the L2 scratch first
+    const bool pipe_possible = net->pipe_ok && (layout == MIBMI_LAYOUT_BCT || wolf_reorder ||
+                                                (wolf_fused && net->force_path != MIBMI_PATH_FUSED_PIPE));
     const bool v1_possible = net->fused_ok && layout == MIBMI_LAYOUT_BCT && !taps;
     if (path == MIBMI_PATH_AUTO) path = (pipe_possible && !taps) ? MIBMI_PATH_FUSED : MIBMI_PATH_GENERIC;
     if ((path == MIBMI_PATH_FUSED || path == MIBMI_PATH_FUSED_PIPE) && !pipe_possible) return MIBMI_ERR_UNSUPPORTED;
@@ -521,15 +573,10 @@ int forward_impl(mibmi_net* net, const int8_t* x, int64_t B, int layout, int8_t*
     if (path == MIBMI_PATH_FUSED && wolf_fused)
         e = launch_tc_wolf(net->pipe_dev, net->pipe_fast1, net->C, net->T, x, B, logits, peers ? *peers : none, t1, t2, t3, t4,
                            net->num_sms, stream);
-    else if (path == MIBMI_PATH_FUSED && net->tc_ok)
-        e = launch_tc(net->pipe_dev, net->pipe_fast1, net->C, net->T, x, B, logits, peers ? *peers : none, t1, t2, t3, t4,
-                      net->num_sms, stream);
-    else if (path == MIBMI_PATH_FUSED && net->tcr_ok)
-        e = launch_tcr(net->pipe_dev, net->pipe_fast1, net->C, net->T, x, B, logits, peers ? *peers : none, t1, t2, t3, t4,
-                       net->num_sms, stream);
+    else if ((path == MIBMI_PATH_FUSED || path == MIBMI_PATH_FUSED_PIPE) && wolf_reorder)
+        e = launch_wolf_chunks(net, path, slot, x, B, logits, peers ? *peers : none, t1, t2, t3, t4, stream);
     else if (path == MIBMI_PATH_FUSED || path == MIBMI_PATH_FUSED_PIPE)
-        e = launch_pipe(net->pipe_dev, net->pipe_fast1, net->C, net->T, x, B, logits, peers ? *peers : none, t1, t2, t3, t4,
-                        net->num_sms, stream);
+        e = launch_fused_bct(net, path, x, B, logits, peers ? *peers : none, t1, t2, t3, t4, stream);
     else if (path == MIBMI_PATH_FUSED_V1)
         e = launch_fused(net->fused_dev, net->C, net->T, x, B, logits, net->num_sms, net->ctas_per_sm, stream);
     else
@@ -543,7 +590,8 @@ int forward_impl(mibmi_net* net, const int8_t* x, int64_t B, int layout, int8_t*
     net->last_path.store(path);
     net->last_kernel.store(path == MIBMI_PATH_FUSED ? (net->tc_ok ? 1 : net->tcr_ok ? 6 : 2) : path == MIBMI_PATH_FUSED_PIPE ? 2
                            : path == MIBMI_PATH_FUSED_V1 ? 3 : 4);
-    net->launches.fetch_add(1);
+    net->launches.fetch_add((path == MIBMI_PATH_FUSED || path == MIBMI_PATH_FUSED_PIPE) && wolf_reorder
+                                ? 2 * ((B + net->wolf_chunk - 1) / net->wolf_chunk) : 1);
     return MIBMI_OK;
 }
 
@@ -655,12 +703,21 @@ int mibmi_create(const mibmi_params_t* p, int device, mibmi_net_t** out) {
     n->tc_ok = n->pipe_ok && tc_has_instance(p->C, p->T);
     n->tcr_ok = n->pipe_ok && tcr_has_instance(p->C, p->T);
     n->tc_wolf_ok = n->tc_ok && tc_has_wolf_instance(p->C, p->T);
+    n->wolf_reorder_ok = n->pipe_ok && !n->tc_wolf_ok && reorder_has_instance(p->C, p->T);
     if (n->pipe_ok) n->stream_ok = pack_stream(p, pn, sn, &n->stream_why);
     else n->stream_why = n->pipe_why;
 
     cudaDeviceProp prop;
     if (e == cudaSuccess) e = cudaGetDeviceProperties(&prop, device);
     if (e == cudaSuccess) n->num_sms = prop.multiProcessorCount;
+    {
+        // chunk: 16 waves of the persistent grids (6 trials per CTA and wave).  Measured (r1g): the fixed cost per launch of the
+        // forward kernels outweighs keeping the chunk L2-resident, so the chunk is sized for launch count, not for the L2.
+        const int64_t wave = (int64_t)(n->num_sms > 0 ? n->num_sms : 148) * 6;
+        n->wolf_chunk = 16 * wave;
+        if (const char* ev = getenv("MIBMI_WOLF_CHUNK"))        // tuning / tests: exact chunk size
+            if (atoll(ev) > 0) n->wolf_chunk = atoll(ev);
+    }
     if (e == cudaSuccess) e = cudaMalloc(&n->w5_dev, w5.size() ? w5.size() : 1);
     if (e == cudaSuccess) e = cudaMemcpy(n->w5_dev, w5.data(), w5.size(), cudaMemcpyHostToDevice);
     g->w5 = n->w5_dev;
@@ -700,6 +757,7 @@ int mibmi_destroy(mibmi_net_t* net) {
         if (net->pipe_dev) cudaFree(net->pipe_dev);
         if (net->stream_dev) cudaFree(net->stream_dev);
         free_host_staging(net);
+        free_wolf_scratch(net);
         for (int i = 0; i < 2; i++)
             if (net->hs[i]) cudaStreamDestroy(net->hs[i]);
     }
@@ -804,7 +862,8 @@ int mibmi_forward_int8_host(mibmi_net_t* net, const int8_t* x_host, int64_t B, i
         if (!x_pinned) { memcpy(net->hx_pin[s], src, tb * nb); src = net->hx_pin[s]; }
         e = cudaMemcpyAsync(net->hx_dev[s], src, tb * nb, cudaMemcpyHostToDevice, net->hs[s]);
         if (e != cudaSuccess) { status = fail_cuda(net, e); break; }
-        status = forward_impl(net, net->hx_dev[s], nb, layout, net->hy_dev[s], nullptr, nullptr, nullptr, nullptr, false, net->hs[s]);
+        status = forward_impl(net, net->hx_dev[s], nb, layout, net->hy_dev[s], nullptr, nullptr, nullptr, nullptr, false, net->hs[s],
+                              nullptr, s);
         if (status != MIBMI_OK) break;
         int8_t* dst = y_pinned ? logits_host + (size_t)done * net->N : net->hy_pin[s];
         e = cudaMemcpyAsync(dst, net->hy_dev[s], (size_t)nb * net->N, cudaMemcpyDeviceToHost, net->hs[s]);

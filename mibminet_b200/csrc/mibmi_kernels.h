@@ -55,6 +55,10 @@ bool tcr_has_instance(int C, int T);
 cudaError_t launch_tcr(const PipeNet* net_dev, bool fast1, int C, int T, const int8_t* x, long long B, int8_t* logits,
                        const PeerOut& peers, int8_t* t1, int8_t* t2, int8_t* t3, int8_t* t4, int num_sms, cudaStream_t stream);
 
+// Wolf order [n][T][C_ALIGN] -> module order [n][C][T] (mibmi_reorder.cu) for rows of 8 / 20 / 24 / 40 bytes; y 4-byte aligned.
+bool reorder_has_instance(int C, int T);
+cudaError_t launch_wolf_reorder(const int8_t* x, int8_t* y, long long n, int C, int T, int num_sms, cudaStream_t stream);
+
 // Sliding-window streaming kernel (mibmi_stream.cu): x [S][C][L] -> logits [S][W][4], W = (L - T) / 16 + 1.
 // Optional taps: t2i [S][16][2 (W-1) + T/8] stream-level pooled layer-2 samples (interior positions only),
 // t2e [S][W][16][8] the 4 + 4 edge samples of every window, t3 [S][W][16][T/8], t4 [S][W][16][T/64].

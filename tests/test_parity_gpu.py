@@ -79,8 +79,12 @@ def test_wolf_input_layout(golden):
     xw = convert.to_wolf_input(fx["x"])   # [B][T][C_ALIGN]  (gen_input_header.py:75-76)
     y = net.forward(_cuda(xw), layout="btc").cpu().numpy()
     assert np.array_equal(y, fx["golden_reorder"])
-    # rows of C_ALIGN bytes that are a multiple of 16 go through the tcgen05 kernel (K-major operand, 3-D tensor map)
-    assert net.last_kernel == ("tc_forward_kernel" if fx["C"] in (64, 16) and fx["T"] == 480 else "generic_forward_kernel")
+    # rows of C_ALIGN bytes that are a multiple of 16 go through the tcgen05 kernel (K-major operand, 3-D tensor map); the
+    # others are transposed into an L2-sized scratch chunk by chunk (mibmi_reorder.cu) and run on the fused kernel of the shape
+    ok, _why = net.fused_supported()
+    assert net.last_path == ("fused" if ok else "generic")
+    if ok:
+        assert net.last_kernel == ("tcr_forward_kernel" if fx["T"] == 1125 else "tc_forward_kernel")
     if fx["C"] in (64, 16) and fx["T"] == 480:
         xr = synth.make_trials(1237, fx["C"], fx["T"], seed=9)
         ref = wolf_port.forward(fx["arrays"], fx["C"], fx["T"], xr)
@@ -90,6 +94,34 @@ def test_wolf_input_layout(golden):
         assert net.last_kernel == "tc_forward_kernel"
         for name in ("y1", "y2", "y3", "y4"):
             assert np.array_equal(taps[name].cpu().numpy(), fx[f"golden_reorder_{name}"]), name
+
+
+@pytest.mark.parametrize("C,T", [(22, 1125), (38, 480), (24, 480), (19, 480), (8, 480)])
+@pytest.mark.parametrize("chunk", [None, 101])
+def test_wolf_order_through_reorder_scratch(C, T, chunk, monkeypatch):
+    """Wolf-order rows of 24 / 40 / 20 / 8 bytes: several chunks (odd and even trial phases), taps, launch count."""
+    if chunk:
+        monkeypatch.setenv("MIBMI_WOLF_CHUNK", str(chunk))
+    net, arrays = _net(C, T, 31)
+    B = 1237
+    x = synth.make_trials(B, C, T, seed=77)
+    ref, lay = wolf_port.forward(arrays, C, T, x, return_layers=True)
+    xw = _cuda(convert.to_wolf_input(x))
+    n0 = net.launch_count
+    assert np.array_equal(net.forward(xw, layout="btc").cpu().numpy(), ref)
+    assert net.last_path == "fused" and net.last_kernel != "generic_forward_kernel"
+    if chunk:
+        assert net.launch_count - n0 == 2 * -(-B // chunk)
+    assert np.array_equal(net.forward(xw[:1], layout="btc").cpu().numpy(), ref[:1])
+    assert np.array_equal(net.forward(xw[4:7], layout="btc").cpu().numpy(), ref[4:7])
+    net.set_path("fused")
+    y, taps = net.forward_taps(xw[:300], layout="btc")
+    assert np.array_equal(y.cpu().numpy(), ref[:300])
+    for name in ("y1", "y2", "y3", "y4"):
+        assert np.array_equal(taps[name].cpu().numpy(), lay[name][:300]), name
+    # host entry point (two staging streams, two scratch slots)
+    net.set_path("auto")
+    assert np.array_equal(net.forward_host(convert.to_wolf_input(x), layout="btc"), ref)
 
 
 # ---- against the oracle on seeded random nets / trials ------------------------------------------------
