@@ -57,6 +57,8 @@ def parse_args():
     ap.add_argument("--path", default="auto", choices=["auto", "fused", "fused_pipe", "fused_v1", "generic"])
     ap.add_argument("--ctas-per-sm", type=int, default=0)
     ap.add_argument("--shape", default="64x480", help="CxT of the trials (default: BASELINE config 2; 22x1125 = config 3)")
+    ap.add_argument("--layout", default="bct", choices=["bct", "btc"],
+                    help="trials workload: bct = [B][C][T] (module order), btc = [B][T][C_ALIGN] (Wolf order, gen_input_header.py:75-76)")
     ap.add_argument("--workload", default="trials", choices=["trials", "stream", "eegnet"],
                     help="trials: BASELINE config 2 (default, the headline line); stream: config 5, sliding windows "
                          "(480 samples, stride 16) over continuous 64-ch recordings; eegnet: the EEGNet / Q-EEGNet layer "
@@ -372,12 +374,16 @@ def main():
     g = torch.Generator(device=dev)
     g.manual_seed(1000 + rank)
     x = torch.randint(-127, 128, (B, C, T), dtype=torch.int8, device=dev, generator=g)
+    x_bct = x
+    if args.layout == "btc":             # the order net_model_compute receives: time-major, channels padded to a multiple of 4
+        x = torch.zeros((B, T, (C + 3) // 4 * 4), dtype=torch.int8, device=dev)
+        x[:, :, :C] = x_bct.transpose(1, 2)
     logits = torch.empty((B, N_CLASSES), dtype=torch.int8, device=dev)
     gathered = torch.empty((world * B, N_CLASSES), dtype=torch.int8, device=dev) if world > 1 else None
     # multi-GPU: the all-gather of the logits is fused into the kernel (P2P stores into every rank's symmetric
     # buffer over NVLink, mibmi_forward_int8_gather); NCCL all_gather per step is the fallback
     peer = None
-    if world > 1 and args.gather in ("auto", "peer"):
+    if world > 1 and args.gather in ("auto", "peer") and args.layout == "bct":
         from mibminet_b200.sharding import PeerGather
         try:
             peer = PeerGather(net, world * B)
@@ -395,7 +401,7 @@ def main():
         if peer is not None:
             peer.forward(x)
         else:
-            net.forward(x, out=logits)
+            net.forward(x, layout=args.layout, out=logits)
             if world > 1:
                 dist.all_gather_into_tensor(gathered, logits)
 
@@ -424,7 +430,7 @@ def main():
         if peer is not None:
             peer.forward(x)
         else:
-            net.forward(x, out=logits)
+            net.forward(x, layout=args.layout, out=logits)
         k_ev[i][1].record()
         if world > 1 and peer is None:
             dist.all_gather_into_tensor(gathered, logits)
@@ -458,27 +464,27 @@ def main():
     # ---- end to end through the host entry point (pinned host buffers, copies inside the timed region)
     e2e = None
     if not args.no_e2e:
-        xh = torch.empty((B, C, T), dtype=torch.int8, pin_memory=True)
+        xh = torch.empty(tuple(x.shape), dtype=torch.int8, pin_memory=True)
         xh.copy_(x)
         yh = torch.empty((B, N_CLASSES), dtype=torch.int8, pin_memory=True)
         for _ in range(2):
-            net.forward_host(xh, out=yh)
+            net.forward_host(xh, layout=args.layout, out=yh)
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
         e_steps = max(3, min(args.steps, 10))
         t0 = time.perf_counter()
         for _ in range(e_steps):
-            net.forward_host(xh, out=yh)
+            net.forward_host(xh, layout=args.layout, out=yh)
         torch.cuda.synchronize()
         dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(dt, op=dist.ReduceOp.MAX)
         assert torch.equal(yh.to(dev), logits), "host entry point and device path disagree"
         e2e = {"value": world * B * e_steps / float(dt[0]), "unit": "trials/s",
-               "h2d_bytes_per_step": world * B * C * T, "d2h_bytes_per_step": world * B * N_CLASSES,
+               "h2d_bytes_per_step": world * x.numel(), "d2h_bytes_per_step": world * B * N_CLASSES,
                "steps": e_steps, "timing": "host wall clock around the synchronous C-ABI call, max over ranks",
-               "h2d_gbs_per_gpu": B * C * T * e_steps / float(dt[0]) / 1e9,
+               "h2d_gbs_per_gpu": x.numel() * e_steps / float(dt[0]) / 1e9,
                "bound": "PCIe host->device copy of the int8 trials (chunks of 8192 trials, copy / kernel / copy-back "
                         "overlapped on two streams); the kernel itself is 100x faster than the link"}
         del xh
@@ -491,7 +497,10 @@ def main():
             "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "int8", "data": "synthetic",
             "config": {"workload": WORKLOAD, "trials_per_gpu_per_step": B, "global_batch": world * B,
-                       "layout": "[B][C][T] int8 (module order)", "parallelism": f"trial-batch sharding x{world}",
+                       "layout": "[B][C][T] int8 (module order)" if args.layout == "bct" else
+                                 "[B][T][C_ALIGN] int8 (Wolf order; rows that are not 16 or 64 bytes are transposed on the GPU "
+                                 "into a scratch, chunk by chunk, before the fused kernel: 2 launches per chunk)",
+                       "parallelism": f"trial-batch sharding x{world}",
                        "l2_policy": f"input per step {B * C * T / 1e9:.2f} GB > 126 MB L2, no flush needed",
                        "collective": ("none" if world == 1 else
                                       "fused: kernel epilogue stores the logits into every rank's symmetric buffer over NVLink, "
@@ -511,7 +520,7 @@ def main():
         if not args.no_cpu_baseline:
             cores = host_cores()
             n = 128 * cores
-            xs = x[:n].cpu().numpy()
+            xs = x_bct[:n].cpu().numpy()
             tps, kind, y_cpu = cpu_reference_run(xs, repeat=4, cores=cores)
             same = bool(np.array_equal(y_cpu, logits[:n].cpu().numpy()))
             out["cpu_baseline"] = {"value": tps, "unit": "trials/s", "cores": cores, "kind": kind,
