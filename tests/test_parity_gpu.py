@@ -343,6 +343,23 @@ def test_forward_gather_writes_every_destination(C, T):
         assert (h[:row0] == 77).all() and (h[row0 + B:] == 77).all()
 
 
+@pytest.mark.parametrize("C,T", [(22, 1125), (38, 480), (64, 480)])
+def test_forward_gather_wolf_order(C, T, monkeypatch):
+    """The fused gather with Wolf-order input: the chunked reorder path moves the peer pointers along with the chunks."""
+    monkeypatch.setenv("MIBMI_WOLF_CHUNK", "150")
+    net, arrays = _net(C, T, seed=83)
+    B, row0, rows = 401, 52, 500                 # row0 * 4 is a multiple of 16: 16-byte peer stores; 3 chunks of 150 trials
+    x = synth.make_trials(B, C, T, seed=84)
+    ref = wolf_port.forward(arrays, C, T, x)
+    bufs = [torch.full((rows, 4), 77, dtype=torch.int8, device="cuda:0") for _ in range(3)]
+    net.forward_gather(_cuda(convert.to_wolf_input(x)), [b.data_ptr() for b in bufs], row0, layout="btc")
+    assert net.last_path == "fused"
+    for b in bufs:
+        h = b.cpu().numpy()
+        assert np.array_equal(h[row0:row0 + B], ref)
+        assert (h[:row0] == 77).all() and (h[row0 + B:] == 77).all()
+
+
 def test_torch_op_matches_the_reference_fixtures(golden):
     """torch.ops.mibminet.forward_int8 on the reference fixtures, both reorder_bn modes."""
     from mibminet_b200 import torch_op
