@@ -112,6 +112,16 @@ __device__ __forceinline__ int tcr_div1(int x, int m, int s) {
     if (FAST) return __mulhi(x, m) + (int)((unsigned)x >> 31);
     return (__mulhi(x, m) >> s) + (int)((unsigned)x >> 31);
 }
+// layer 1 with the BN offset folded into the multiplication (FAST form only): hi32((x + off) m) = hi32(x m + off m) -- one
+// multiply-add with a 64-bit constant instead of an add and a multiply-high; the quotient's sign bit stands in for (x + off < 0)
+// (m > 0, so hi32 is negative exactly when x + off is).  |x + off| < 2^29 and m < 2^31 keep the 64-bit sum exact.
+#ifndef MIBMI_TCR_FOLD
+#define MIBMI_TCR_FOLD 1
+#endif
+__device__ __forceinline__ int tcr_div1_fold(int x, int m, long long offm) {
+    const int hi = (int)(((long long)x * m + offm) >> 32);
+    return hi + (int)((unsigned)hi >> 31);
+}
 __device__ __forceinline__ void tcr_tmem_ld_32x32b_x16(uint32_t (&r)[16], uint32_t taddr) {
     asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
                  : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
@@ -223,6 +233,11 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
                 mg1[nt][e] = net->m1[8 * nt + 2 * q + e];
                 sh1[nt][e] = net->sh1[8 * nt + 2 * q + e];
             }
+        long long offm[2][2];
+#pragma unroll
+        for (int nt = 0; nt < 2; nt++)
+#pragma unroll
+            for (int e = 0; e < 2; e++) offm[nt][e] = (long long)off1[nt][e] * mg1[nt][e];
         // stmatrix.trans: matrix j = lane >> 3 = 2 mt + nt: filters 8 nt .. + 7 (rows), samples 16 mt .. + 15
         const uint32_t st_off = sbase + K::OFF_Y1 + ((lane & 7) + 8 * ((lane >> 3) & 1)) * K::CHS + 16 * (lane >> 4) + 32;
         const int qi = warp & 3, a3 = warp >> 2;
@@ -260,7 +275,9 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
                         int v[4];
 #pragma unroll
                         for (int c = 0; c < 4; c++)
-                            v[c] = tcr_div1<FAST1>((int)r[it & 1][mt][4 * nt + c] + off1[nt][c & 1], mg1[nt][c & 1], sh1[nt][c & 1]);
+                            v[c] = (FAST1 && MIBMI_TCR_FOLD)
+                                       ? tcr_div1_fold((int)r[it & 1][mt][4 * nt + c], mg1[nt][c & 1], offm[nt][c & 1])
+                                       : tcr_div1<FAST1>((int)r[it & 1][mt][4 * nt + c] + off1[nt][c & 1], mg1[nt][c & 1], sh1[nt][c & 1]);
                         w[mt][nt] = pack4_sat(v[0], v[1], v[2], v[3]);
                         if (TAPS && tap1 && b < B)
 #pragma unroll
