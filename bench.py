@@ -59,6 +59,9 @@ def parse_args():
     ap.add_argument("--shape", default="64x480", help="CxT of the trials (default: BASELINE config 2; 22x1125 = config 3)")
     ap.add_argument("--layout", default="bct", choices=["bct", "btc"],
                     help="trials workload: bct = [B][C][T] (module order), btc = [B][T][C_ALIGN] (Wolf order, gen_input_header.py:75-76)")
+    ap.add_argument("--float-input", action="store_true",
+                    help="trials workload: float32 trials in HBM -> quantise (a13) -> int8 forward -> float32 logits "
+                         "(SURVEY 8(f)2; 4x the input bytes, reported separately)")
     ap.add_argument("--workload", default="trials", choices=["trials", "stream", "eegnet"],
                     help="trials: BASELINE config 2 (default, the headline line); stream: config 5, sliding windows "
                          "(480 samples, stride 16) over continuous 64-ch recordings; eegnet: the EEGNet / Q-EEGNet layer "
@@ -397,7 +400,17 @@ def main():
         if int(ok[0]) == 0:
             peer = None
 
+    xf = None
+    if args.float_input:                 # the (Q) module's view: float trials, quant1 in front, quant6 behind (modules.edgeEEGNet)
+        if world > 1 or args.layout != "bct":
+            raise SystemExit("--float-input: single GPU, module order")
+        xf = x.to(torch.float32) * (params.input_scale / 127.0)
+        args.no_e2e = True
+
     def run_step():
+        if xf is not None:
+            net.forward(net.quantize_input(xf), out=logits)
+            return net.dequantize_logits(logits)
         if peer is not None:
             peer.forward(x)
         else:
@@ -427,7 +440,9 @@ def main():
     ev0.record()
     for i in range(args.steps):
         k_ev[i][0].record()
-        if peer is not None:
+        if xf is not None:
+            run_step()
+        elif peer is not None:
             peer.forward(x)
         else:
             net.forward(x, layout=args.layout, out=logits)
@@ -491,7 +506,8 @@ def main():
 
     if rank == 0:
         peak, peak_src = measured_peaks()
-        achieved = B * ALG_BYTES_PER_TRIAL / (ms_kernel * 1e-3) / 1e9
+        alg_bytes = ALG_BYTES_PER_TRIAL if xf is None else 4 * C * T + 4 * N_CLASSES     # float trials in, float logits out
+        achieved = B * alg_bytes / (ms_kernel * 1e-3) / 1e9
         out = {
             "metric": METRIC, "value": value, "unit": "trials/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
@@ -505,14 +521,18 @@ def main():
                        "collective": ("none" if world == 1 else
                                       "fused: kernel epilogue stores the logits into every rank's symmetric buffer over NVLink, "
                                       "one barrier at the end" if peer is not None else "one NCCL all_gather of int8 logits per step"),
+                       "input": "int8" if xf is None else
+                                "float32 trials: quantize_input_kernel_v16 (trunc(clip(x/s,-1,1)*127), IEEE division) -> int8 forward -> "
+                                "dequantize_kernel; kernel_ms covers the three launches, the int8 copy is written and read once more",
                        "kernel_path": net.last_path, "bit_exact_checked": None, "gather_checked": gather_checked},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": NCU_TRAFFIC_BYTES_PER_TRIAL * B if (net.last_kernel == "tc_forward_kernel" and args.shape == "64x480") else None,
+                         "traffic": NCU_TRAFFIC_BYTES_PER_TRIAL * B if (net.last_kernel == "tc_forward_kernel" and args.shape == "64x480" and xf is None
+                                                                             and args.layout == "bct") else None,
                          "traffic_source": "ncu --set full dram__bytes_read.sum + dram__bytes_write.sum per launch of 65536 "
                                            "trials (profiles/r1d_ncu_full_metrics.csv), scaled to this batch",
                          "peak_source": peak_src,
                          "kernel": KERNEL_TEMPLATES.get(net.last_kernel, net.last_kernel).format(C=C, T=T),
-                         "kernel_ms": ms_kernel, "alg_bytes_per_trial": ALG_BYTES_PER_TRIAL,
+                         "kernel_ms": ms_kernel, "alg_bytes_per_trial": alg_bytes,
                          "note": KERNEL_NOTES.get(net.last_kernel, ""),
                          "tensor_pipe": tensor_pipe(net.last_kernel, C, T, B, ms_kernel, clocks)},
             "gpu_launches": int(launches), "clocks": clocks, "e2e": e2e,

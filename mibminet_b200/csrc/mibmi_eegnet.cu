@@ -107,8 +107,8 @@ __global__ void __launch_bounds__(384)
 eegnet_forward_kernel(const EegNet* __restrict__ net, const int8_t* __restrict__ x, long long B, int8_t* __restrict__ logits,
                       int8_t* __restrict__ tap2, int8_t* __restrict__ tap3, int8_t* __restrict__ tap4) {
     extern __shared__ __align__(16) int8_t smem[];
-    const int C = net->C, T = net->T, F1 = net->F1, K2 = net->K2, F2 = net->F2, N = net->N, Nf = net->Nf;
-    const int T8 = net->T8, T64 = net->T64, XP = net->XP, G = net->G, NW = net->NW;
+    const int C = net->C, T = net->T, F1 = net->F1, K2 = net->K2, Nf = net->Nf;
+    const int T8 = net->T8, XP = net->XP, G = net->G, NW = net->NW;
     const int y2s = T8 + 15;
     int4* w1s = reinterpret_cast<int4*>(smem);                                  // [F1][NW] int4
     int8_t* xs = smem + (size_t)F1 * NW * 16;                                   // [C][XP]
@@ -217,8 +217,8 @@ __global__ void __launch_bounds__(MAXT, MAXT <= 256 ? MIBMI_EEG_MINB : 1)
 eegnet_mma_kernel(const EegNet* __restrict__ net, const int8_t* __restrict__ x, long long B, int8_t* __restrict__ logits,
                   int8_t* __restrict__ tap2, int8_t* __restrict__ tap3, int8_t* __restrict__ tap4) {
     extern __shared__ __align__(16) int8_t smem[];
-    const int C = net->C, T = net->T, K2 = net->K2, F2 = net->F2, Nf = net->Nf;
-    const int T8 = net->T8, T64 = net->T64, XP = net->XPM, MT = net->MT;
+    const int C = net->C, T = net->T, K2 = net->K2, Nf = net->Nf;
+    const int T8 = net->T8, XP = net->XPM, MT = net->MT;
     const int y2s = T8 + 15;
     int8_t* xs = smem;                                                          // [C][XP], XP % 16 == 0
     int8_t* y2 = xs + (size_t)C * XP;                                           // [K2][T8 + 15]

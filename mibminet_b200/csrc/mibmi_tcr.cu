@@ -50,7 +50,10 @@ __device__ long long g_prof_tcr[148 * 32 * 4];
 #define MIBMI_TCR_L4_UNROLL 1
 #endif
 constexpr int kTcrL3Unroll = MIBMI_TCR_L3_UNROLL, kTcrL4Unroll = MIBMI_TCR_L4_UNROLL;   // layers 3 / 4 loops of the C warps
-constexpr int kRAW = 12, kRBW = 8, kRCW = 4, kRRW = 4;
+#ifndef MIBMI_TCR_RW
+#define MIBMI_TCR_RW 4
+#endif
+constexpr int kRAW = 12, kRBW = 8, kRCW = 4, kRRW = MIBMI_TCR_RW;
 constexpr int kRWarpB = kRAW, kRWarpC = kRAW + kRBW, kRWarpR = kRWarpC + kRCW, kRWarpP = kRWarpR + kRRW,
               kRWarpM1 = kRWarpP + 1, kRWarpM2 = kRWarpP + 2;
 constexpr int kRThreads = (kRWarpM2 + 1) * 32;

@@ -252,6 +252,18 @@ def test_float_pre_and_post_ops():
     assert np.allclose(yf, ref, rtol=1e-6, atol=0)   # float32 vs the reference's float64: 1e-6 relative
 
 
+@pytest.mark.parametrize("n,skip", [(1, 0), (15, 0), (16, 0), (4099, 0), (4099, 1), (65536 + 7, 3)])
+def test_quantize_input_vector_body_and_tails(n, skip):
+    """The 16-floats-per-thread body, its scalar tail and unaligned views give NumPy's bytes (values beyond +-s clip)."""
+    net, _ = _net(64, 480, seed=5)
+    rng = np.random.default_rng(n)
+    xf = (rng.normal(0, 0.8, size=n + skip) * net.params.input_scale).astype(np.float32)
+    xf[:: 7] *= 3.0
+    xd = torch.from_numpy(xf).cuda()[skip:]                     # skip != 0: not 16-byte aligned -> scalar kernel
+    q = net.quantize_input(xd)
+    assert np.array_equal(q.cpu().numpy(), convert.quantize_input(xf[skip:], net.params.input_scale))
+
+
 def test_errors_are_reported_not_printed():
     C, T = 64, 480
     net, _ = _net(C, T, seed=1)
