@@ -1,0 +1,7 @@
+# sustained (power-capped) rate of the 64 x 480 kernel per barrier-poll interval; base = 64 ns
+for v in base s32 s128 s256 base s128; do
+  if [ $v = base ]; then unset MIBMI_LIB_PATH; else export MIBMI_LIB_PATH=tools/variants/$v/libmibmi.so; fi
+  python bench.py --steps 6000 --warmup 5 --no-cpu-baseline --no-e2e | python -c "
+import json,sys
+d=json.loads(sys.stdin.read().strip().splitlines()[-1]); c=d['clocks']; print('$v', round(d['value']/1e6,1), 'M trials/s', c['sm_mhz'], 'MHz', c['reasons'], c['power_w_max'], 'W')"
+done
