@@ -386,7 +386,7 @@ def main():
     # multi-GPU: the all-gather of the logits is fused into the kernel (P2P stores into every rank's symmetric
     # buffer over NVLink, mibmi_forward_int8_gather); NCCL all_gather per step is the fallback
     peer = None
-    if world > 1 and args.gather in ("auto", "peer") and args.layout == "bct":
+    if world > 1 and args.gather in ("auto", "peer"):
         from mibminet_b200.sharding import PeerGather
         try:
             peer = PeerGather(net, world * B)
@@ -412,7 +412,7 @@ def main():
             net.forward(net.quantize_input(xf), out=logits)
             return net.dequantize_logits(logits)
         if peer is not None:
-            peer.forward(x)
+            peer.forward(x, layout=args.layout)
         else:
             net.forward(x, layout=args.layout, out=logits)
             if world > 1:
@@ -443,7 +443,7 @@ def main():
         if xf is not None:
             run_step()
         elif peer is not None:
-            peer.forward(x)
+            peer.forward(x, layout=args.layout)
         else:
             net.forward(x, layout=args.layout, out=logits)
         k_ev[i][1].record()
