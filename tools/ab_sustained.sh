@@ -1,5 +1,5 @@
-# sustained (power-capped) rate of the 64 x 480 kernel per barrier-poll interval; base = 64 ns
-for v in base s32 s128 s256 base s128; do
+# sustained (power-capped) rate of the 64 x 480 kernel: variants named on the command line against the default build
+for v in base "$@" base "$@"; do
   if [ $v = base ]; then unset MIBMI_LIB_PATH; else export MIBMI_LIB_PATH=tools/variants/$v/libmibmi.so; fi
   python bench.py --steps 6000 --warmup 5 --no-cpu-baseline --no-e2e | python -c "
 import json,sys
