@@ -53,7 +53,10 @@ typedef enum {
  * gen_input_header.py:73; -128 is accepted and handled exactly). */
 #define MIBMI_LAYOUT_BCT 0  /* [B][C][T]        -- module order, edgeEEGNet.forward x[B,1,C,T]         */
 #define MIBMI_LAYOUT_BTC 1  /* [B][T][C_ALIGN]  -- Wolf order of net_model_compute (gen_input_header.py:75-76);       *
-                             * fused tcgen05 kernel when C_ALIGN is 64 or 16 (T = 480), exact generic kernel otherwise */
+                             * fused tcgen05 kernel directly when C_ALIGN is 64 or 16 (T = 480); rows of 40 / 24 / 20 / 8  *
+                             * bytes are first transposed on the GPU, 14 208 trials at a time, into a scratch the handle    *
+                             * owns (such calls on one handle must not overlap on different streams); exact generic kernel *
+                             * for every other shape */
 
 /* Network description: the exported arrays of gen_net_header.py (names without the "net_" prefix).
  * All pointers are HOST pointers; mibmi_create copies what it needs. */
