@@ -73,3 +73,24 @@ def test_verify_export_on_gpu(d, tmp_path):
     rep2 = verify.verify_export(net_npz, cfg, path, tolerance=0, net=net)
     assert all(r["result"] and r["max error"] == 0 for r in rep2.values()), rep2
     net.close()
+
+
+@pytest.mark.parametrize("scale", [1.0, 0.1, 3.3333333, 11.781072616577148, 71.22114562988281, 1e-3, 12345.678])
+def test_written_taps_quantise_back_exactly(scale):
+    """verify._dequantize_exact: float32 grid values that `quantize_to_int` (truncation) maps back to every int8 code."""
+    from mibminet_b200 import verify
+    a = np.arange(-127, 128, dtype=np.int64)
+    f = verify._dequantize_exact(a, scale)
+    assert f.dtype == np.float32
+    assert np.array_equal(convert.quantize_to_int(f, scale), a)
+    assert np.all(np.abs(f.astype(np.float64) - a * float(scale) / 127.0) <= 4 * np.spacing(np.abs(f)).astype(np.float64))
+
+
+def test_expected_taps_shapes():
+    from mibminet_b200 import verify
+    d = EXPORTS[0]
+    net, cfg, ver = _files(d)
+    p = convert.params_from_export(net, cfg)
+    exp = verify.expected_taps(np.load(ver), p)
+    assert exp["y1"].shape == (p.F2, p.T) and exp["y2"].shape == (p.F2, p.T // 8) and exp["y4"].shape == (p.F2, p.T // 64)
+    assert exp["out"].shape == (p.N,) and all(np.abs(v).max() <= 127 for v in exp.values())
