@@ -35,7 +35,7 @@ METRIC = "int8 edgeEEGNet trials/sec"
 # per launch of 65536 trials
 NCU_TRAFFIC_BYTES_PER_TRIAL = (2.013485e9 + 18.797056e6) / 65536
 KERNEL_TEMPLATES = {"tc_forward_kernel": "tc_forward_kernel<TCfg<{C},{T}>>", "tcr_forward_kernel": "tcr_forward_kernel<RCfg<{C},{T}>>", "pipe_forward_kernel": "pipe_forward_kernel<PCfg<{C},{T},4>>",
-                    "fused_forward_kernel": "fused_forward_kernel<Cfg<{C},{T}>>"}
+                    }
 KERNEL_NOTES = {
     "tc_forward_kernel": "layers 1+2 on tcgen05.mma kind::i8 (TMEM accumulators), 23 warps requantise; ncu r1d: DRAM 67 % of "
                          "ncu peak, issue slots 59 %, not pipe bound: per-trial hand-off latency between the roles, see DESIGN.md 4.1",
@@ -54,8 +54,7 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=65536, help="trials per GPU per step")
-    ap.add_argument("--path", default="auto", choices=["auto", "fused", "fused_pipe", "fused_v1", "generic"])
-    ap.add_argument("--ctas-per-sm", type=int, default=0)
+    ap.add_argument("--path", default="auto", choices=["auto", "fused", "fused_pipe", "generic"])
     ap.add_argument("--shape", default="64x480", help="CxT of the trials (default: BASELINE config 2; 22x1125 = config 3)")
     ap.add_argument("--layout", default="bct", choices=["bct", "btc"],
                     help="trials workload: bct = [B][C][T] (module order), btc = [B][T][C_ALIGN] (Wolf order, gen_input_header.py:75-76)")
@@ -370,8 +369,6 @@ def main():
     params = convert.params_from_state_dict(synth.make_state_dict(C=C, T=T, seed=NET_SEED), C=C, T=T)
     net = Int8Net(params, device=dev)
     net.set_path(args.path)
-    if args.ctas_per_sm:
-        net.set_ctas_per_sm(args.ctas_per_sm)
 
     # synthetic trials, generated on the device per rank (int8 uniform on [-127, 127])
     g = torch.Generator(device=dev)

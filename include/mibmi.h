@@ -18,8 +18,10 @@
  * All functions return MIBMI_OK (0) or a negative mibmi_status; nothing prints or aborts.  There is
  * no CPU fallback: without a CUDA device every compute entry point returns MIBMI_ERR_CUDA.
  * Distinct handles may be used concurrently from different threads; one handle may be used from
- * several threads as long as each call is given its own stream (the handle is read-only after
- * creation, except for mibmi_set_option and the *_host entry points, which own staging buffers).
+ * several threads as long as each call is given its own stream: the handle is read-only after
+ * creation, scratch memory a call needs is allocated and freed in stream order on that call's own
+ * stream.  Exceptions: mibmi_set_option, and the *_host entry points, which own staging buffers and
+ * serialise on an internal mutex.
  */
 #ifndef MIBMI_H
 #define MIBMI_H
@@ -53,10 +55,10 @@ typedef enum {
  * gen_input_header.py:73; -128 is accepted and handled exactly). */
 #define MIBMI_LAYOUT_BCT 0  /* [B][C][T]        -- module order, edgeEEGNet.forward x[B,1,C,T]         */
 #define MIBMI_LAYOUT_BTC 1  /* [B][T][C_ALIGN]  -- Wolf order of net_model_compute (gen_input_header.py:75-76);       *
-                             * fused tcgen05 kernel directly when C_ALIGN is 64 or 16 (T = 480); rows of 40 / 24 / 20 / 8  *
-                             * bytes are first transposed on the GPU, 14 208 trials at a time, into a scratch the handle    *
-                             * owns (such calls on one handle must not overlap on different streams); exact generic kernel *
-                             * for every other shape */
+                             * read directly by the fused tcgen05 kernels when C_ALIGN is 64 or 16 (T = 480) and for       *
+                             * 22 x 1125 (rows of 24 bytes, expanded in shared memory); rows of 40 / 24 / 20 / 8 bytes at  *
+                             * T = 480 are first transposed on the GPU, 14 208 trials at a time, into a scratch allocated   *
+                             * in stream order for the call; exact generic kernel for every other shape */
 
 /* Network description: the exported arrays of gen_net_header.py (names without the "net_" prefix).
  * All pointers are HOST pointers; mibmi_create copies what it needs. */
@@ -89,8 +91,6 @@ typedef struct mibmi_net mibmi_net_t; /* opaque */
 #define MIBMI_PATH_GENERIC 1  /* exact reference-order kernel: any shape, both reorder_bn modes, taps */
 #define MIBMI_PATH_FUSED 2    /* fused sm_100a kernel: tcgen05 / TMEM kernel where the shape has one, else  *
                                * the mma.sync pipeline kernel (magic-number requantisation in both)          */
-#define MIBMI_PATH_FUSED_V1 3 /* round-1 homogeneous fused kernel, kept for A/B measurements          */
-
 #define MIBMI_PATH_FUSED_PIPE 5 /* force the warp-specialised mma.sync pipeline kernel (A/B measurements)   */
 #define MIBMI_PATH_STREAM 4   /* sliding-window streaming kernel (mibmi_forward_stream_int8)             */
 
@@ -99,7 +99,6 @@ typedef struct mibmi_net mibmi_net_t; /* opaque */
 #define MIBMI_STREAM_GATHER 2  /* materialise the windows, then the per-trial path (any hop)               */
 
 #define MIBMI_OPT_FORCE_PATH 1
-#define MIBMI_OPT_CTAS_PER_SM 2   /* 0 = default */
 #define MIBMI_OPT_HOST_CHUNK 3    /* trials per H2D/compute/D2H chunk of the *_host entry point; 0 = default */
 #define MIBMI_OPT_STREAM_MODE 4   /* MIBMI_STREAM_* */
 
@@ -115,8 +114,9 @@ MIBMI_API int mibmi_destroy(mibmi_net_t* net);
 MIBMI_API int mibmi_set_option(mibmi_net_t* net, int option, int64_t value);
 /* Which path the most recent forward on this handle ran (MIBMI_PATH_GENERIC / MIBMI_PATH_FUSED). */
 MIBMI_API int mibmi_last_path(const mibmi_net_t* net);
-/* Name of the __global__ function the most recent forward launched ("tc_forward_kernel", "pipe_forward_kernel",
- * "stream_forward_kernel", "generic_forward_kernel", "fused_forward_kernel"; "" before the first call). Static string. */
+/* Name of the __global__ function the most recent forward launched, recorded at launch time ("tc_forward_kernel",
+ * "tcr_forward_kernel", "pipe_forward_kernel", "stream_forward_kernel", "generic_forward_kernel"; "" before the first
+ * call).  Static string. */
 MIBMI_API const char* mibmi_last_kernel(const mibmi_net_t* net);
 /* 1 if the fused path can run this network (shape supported, requant parameters within the proven
  * range of the magic-number division), else 0 with the reason in *why (static string, may be NULL). */
@@ -125,8 +125,12 @@ MIBMI_API int mibmi_fused_supported(const mibmi_net_t* net, const char** why);
 MIBMI_API int64_t mibmi_launch_count(const mibmi_net_t* net);
 
 /* Batched forward, device buffers, asynchronous on `stream` (a cudaStream_t, may be NULL).
- *   x_dev      int8, B trials in `layout`; 16-byte aligned
- *   logits_dev int8 [B][N], caller-allocated; 4-byte aligned
+ *   x_dev      int8, B trials in `layout`.  The fused kernels need it 16-byte aligned; no byte outside
+ *              [x_dev, x_dev + B * trial_bytes) is read.  With MIBMI_PATH_AUTO a pointer that is not 16-byte
+ *              aligned runs on the exact generic kernel (no alignment requirement); with a fused path forced it
+ *              is MIBMI_ERR_ALIGN.
+ *   logits_dev int8 [B][N], caller-allocated; 4-byte aligned for the fused kernels
+ * Any B >= 0; batches above 2^20 trials are split into several launches.
  * Replaces B calls of net_model_compute (model.c:42). */
 MIBMI_API int mibmi_forward_int8(mibmi_net_t* net, const int8_t* x_dev, int64_t B, int layout,
                        int8_t* logits_dev, void* stream);
@@ -184,11 +188,13 @@ MIBMI_API int mibmi_dequantize_logits_f32(const int8_t* q_dev, int64_t n, float 
 /* Diagnostics: the (magic, shift) pair the fused path uses for a positive divisor d >= 4, such that
  * trunc(x / d) == (mulhi32(x, magic) >> shift) + (x < 0) for |x| < 2^29.  MIBMI_ERR_PARAM if d < 4. */
 MIBMI_API int mibmi_debug_magic(int32_t d, int32_t* magic, int32_t* shift);
-/* Diagnostics (no GPU needed): writes the packed network the fused kernel reads into out[cap] and
- * returns its size; out == NULL only queries the size.  MIBMI_ERR_UNSUPPORTED (+ *why) if the fused
+/* Diagnostics: the magic of the shift-free layer-1 form clip8(mulhi32(x, magic) + (x < 0)) == clip8(trunc(x / d)) for every
+ * |x| <= xmax (the bound mibmi_create proves per filter: 128 * sum|w| + |offset|).  MIBMI_ERR_UNSUPPORTED when the form is
+ * not exact for this (d, xmax): the layer then uses the shifted form of mibmi_debug_magic. */
+MIBMI_API int mibmi_debug_magic32(int32_t d, int64_t xmax, int32_t* magic);
+/* Diagnostics (no GPU needed): writes the packed network the fused kernels (MIBMI_PATH_FUSED) read into out[cap]
+ * and returns its size; out == NULL only queries the size.  MIBMI_ERR_UNSUPPORTED (+ *why) if the fused
  * path cannot run this network. */
-MIBMI_API int64_t mibmi_debug_pack_fused(const mibmi_params_t* params, void* out, int64_t cap, const char** why);
-/* Same for the warp-specialised pipeline kernel (MIBMI_PATH_FUSED). */
 MIBMI_API int64_t mibmi_debug_pack_pipe(const mibmi_params_t* params, void* out, int64_t cap, const char** why);
 
 /* ---------------------------------------------------------------------------------------------------------

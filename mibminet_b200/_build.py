@@ -10,7 +10,7 @@ ROOT = os.path.dirname(PKG)
 CSRC = os.path.join(PKG, "csrc")
 LIB_DIR = os.path.join(PKG, "lib")
 LIB = os.path.join(LIB_DIR, "libmibmi.so")
-SOURCES = ["mibmi_api.cu", "mibmi_generic.cu", "mibmi_fused.cu", "mibmi_pipe.cu", "mibmi_stream.cu", "mibmi_tc.cu", "mibmi_tcr.cu", "mibmi_eegnet.cu", "mibmi_reorder.cu"]
+SOURCES = ["mibmi_api.cu", "mibmi_generic.cu", "mibmi_pipe.cu", "mibmi_stream.cu", "mibmi_tc.cu", "mibmi_tcr.cu", "mibmi_eegnet.cu", "mibmi_reorder.cu"]
 HEADERS = ["mibmi_common.cuh", "mibmi_kernels.h", "mibmi_ptx.cuh", "mibmi_tmap.h", os.path.join(ROOT, "include", "mibmi.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden"]

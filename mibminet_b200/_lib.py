@@ -16,16 +16,16 @@ from . import _build
 OK = 0
 ERR_NULL, ERR_SHAPE, ERR_PARAM, ERR_ALIGN, ERR_CUDA, ERR_UNSUPPORTED = -1, -2, -3, -4, -5, -6
 LAYOUT_BCT, LAYOUT_BTC = 0, 1
-PATH_AUTO, PATH_GENERIC, PATH_FUSED, PATH_FUSED_V1, PATH_STREAM, PATH_FUSED_PIPE = 0, 1, 2, 3, 4, 5
+PATH_AUTO, PATH_GENERIC, PATH_FUSED, PATH_STREAM, PATH_FUSED_PIPE = 0, 1, 2, 4, 5
 STREAM_AUTO, STREAM_FUSED, STREAM_GATHER = 0, 1, 2
-OPT_FORCE_PATH, OPT_CTAS_PER_SM, OPT_HOST_CHUNK, OPT_STREAM_MODE = 1, 2, 3, 4
+OPT_FORCE_PATH, OPT_HOST_CHUNK, OPT_STREAM_MODE = 1, 3, 4
 
 # every symbol include/mibmi.h declares (tests/test_abi.py checks the header against this list)
 SYMBOLS = [
     "mibmi_version", "mibmi_strerror", "mibmi_last_cuda_error", "mibmi_create", "mibmi_destroy",
     "mibmi_set_option", "mibmi_last_path", "mibmi_last_kernel", "mibmi_fused_supported", "mibmi_launch_count",
     "mibmi_forward_int8", "mibmi_forward_int8_taps", "mibmi_forward_int8_host",
-    "mibmi_quantize_input_f32", "mibmi_dequantize_logits_f32", "mibmi_debug_magic", "mibmi_debug_pack_fused",
+    "mibmi_quantize_input_f32", "mibmi_dequantize_logits_f32", "mibmi_debug_magic", "mibmi_debug_magic32",
     "mibmi_debug_pack_pipe", "mibmi_stream_windows", "mibmi_stream_supported", "mibmi_forward_stream_int8",
     "mibmi_forward_stream_int8_taps", "mibmi_forward_int8_gather",
     "mibmi_eegnet_create", "mibmi_eegnet_destroy", "mibmi_eegnet_forward_int8", "mibmi_eegnet_forward_int8_taps",
@@ -109,8 +109,7 @@ def lib() -> ctypes.CDLL:
     L.mibmi_quantize_input_f32.argtypes = [vp, i64, ctypes.c_float, vp, vp]
     L.mibmi_dequantize_logits_f32.argtypes = [vp, i64, ctypes.c_float, vp, vp]
     L.mibmi_debug_magic.argtypes = [ctypes.c_int32, ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_int32)]
-    L.mibmi_debug_pack_fused.argtypes = [ctypes.POINTER(Params), vp, i64, ctypes.POINTER(ctypes.c_char_p)]
-    L.mibmi_debug_pack_fused.restype = i64
+    L.mibmi_debug_magic32.argtypes = [ctypes.c_int32, i64, ctypes.POINTER(ctypes.c_int32)]
     L.mibmi_debug_pack_pipe.argtypes = [ctypes.POINTER(Params), vp, i64, ctypes.POINTER(ctypes.c_char_p)]
     L.mibmi_debug_pack_pipe.restype = i64
     L.mibmi_eegnet_create.argtypes = [ctypes.POINTER(EEGNetParamsC), i32, ctypes.POINTER(vp)]
@@ -153,6 +152,13 @@ def debug_magic(d: int):
     return st, m.value, s.value
 
 
+def debug_magic32(d: int, xmax: int):
+    """-> (status, magic) of the shift-free layer-1 division (mibmi_debug_magic32)."""
+    m = ctypes.c_int32()
+    st = lib().mibmi_debug_magic32(int(d), int(xmax), ctypes.byref(m))
+    return st, m.value
+
+
 def _debug_pack(fn, arrays, C, T, reorder_bn):
     p, keep = make_params(arrays, C, T, reorder_bn=reorder_bn)
     L = lib()
@@ -165,11 +171,6 @@ def _debug_pack(fn, arrays, C, T, reorder_bn):
     if r < 0:
         return None, (why.value or b"").decode()
     return bytes(buf), ""
-
-
-def debug_pack_fused(arrays, C, T, reorder_bn=True):
-    """-> (bytes of the packed FusedNet of the round-1 kernel | None, reason)."""
-    return _debug_pack(lib().mibmi_debug_pack_fused, arrays, C, T, reorder_bn)
 
 
 def debug_pack_pipe(arrays, C, T, reorder_bn=True):

@@ -20,9 +20,6 @@ struct mibmi_net {
     int C = 0, T = 0, F2 = 0, N = 0, reorder = 1;
     GenericNet* gen_dev = nullptr;
     int8_t* w5_dev = nullptr;
-    FusedNet* fused_dev = nullptr;     // legacy homogeneous kernel (MIBMI_PATH_FUSED_V1)
-    bool fused_ok = false;
-    const char* fused_why = "";
     PipeNet* pipe_dev = nullptr;       // warp-specialised pipeline kernel (MIBMI_PATH_FUSED)
     bool pipe_ok = false, pipe_fast1 = false, tc_ok = false, tcr_ok = false, tc_wolf_ok = false;
     const char* pipe_why = "";
@@ -30,7 +27,7 @@ struct mibmi_net {
     bool stream_ok = false;
     const char* stream_why = "";
     int stream_mode = MIBMI_STREAM_AUTO;
-    int force_path = MIBMI_PATH_AUTO, ctas_per_sm = 0;
+    int force_path = MIBMI_PATH_AUTO;
     int64_t host_chunk = 0;
     std::atomic<int> last_path{0}, last_kernel{0};
     std::atomic<int> last_cuda{0};
@@ -42,13 +39,13 @@ struct mibmi_net {
     int8_t* hy_dev[2] = {nullptr, nullptr};
     int8_t* hx_pin[2] = {nullptr, nullptr};
     int8_t* hy_pin[2] = {nullptr, nullptr};
-    int64_t h_cap = 0;
-    // Wolf-order rows no tensor map describes: transposed chunk by chunk into an L2-sized scratch (mibmi_reorder.cu);
-    // slot 0 = caller's stream, slots 0 / 1 = the two streams of the host entry point
-    bool wolf_reorder_ok = false;
+    int64_t h_cap_trials = 0;          // capacity of the staging buffers in trials ...
+    size_t h_cap_bytes = 0;            // ... and in bytes of input per buffer (the trial size depends on the layout)
+    // Wolf-order rows no tensor map describes: transposed chunk by chunk into a scratch that lives for the duration of
+    // the call on the caller's stream (cudaMallocAsync / cudaFreeAsync), so concurrent calls on different streams
+    // never share it
+    bool wolf_reorder_ok = false, tcr_wolf_ok = false;
     int64_t wolf_chunk = 0;
-    std::mutex wolf_mu;
-    int8_t* wolf_scratch[2] = {nullptr, nullptr};
 };
 
 namespace {
@@ -103,114 +100,17 @@ bool pack_pooled(int64_t vmax, int off, int fac, Pooled* o, const char** why) {
     return true;
 }
 
-bool pack_fused(const mibmi_params_t* p, FusedNet* f, const char** why) {
-    const int C = p->C, T = p->T, F2 = p->F2, CA = align4(C);
-    const int T64 = (T / 8) / 8, T64A = align4(T64), T64P = align4(T64);
-    memset(f, 0, sizeof(*f));
-    if (F2 != 16 || p->N != 4) { *why = "fused kernel needs F2 == 16 and N == 4"; return false; }
-    if (!p->reorder_bn) { *why = "fused kernel implements the REORDER_BN variant only"; return false; }
-    if (!fused_has_instance(C, T)) { *why = "no fused instantiation for this (C, T)"; return false; }
-    // ---- layer 1: sign of the factor folded into weights and offset
-    for (int k = 0; k < 16; k++) {
-        const int fac = p->l1_factor[k], sg = fac < 0 ? -1 : 1;
-        int64_t sum = 0;
-        for (int c = 0; c < C; c++) {
-            const int w = p->l1_weight_align[k * CA + c];
-            if (sg < 0 && w == -128) { *why = "weight -128 cannot be negated (negative layer-1 factor)"; return false; }
-            sum += iabs64(w);
-        }
-        if (128 * sum + iabs64(p->l1_offset[k]) >= kMagicRange) { *why = "layer-1 accumulator outside the magic-division range"; return false; }
-        if (!magic_for(iabs64(fac), &f->m1[k], &f->sh1[k])) { *why = "|l1_factor| < 4"; return false; }
-        f->off1[k] = sg * p->l1_offset[k];
-    }
-    const int ksteps = (C + 31) / 32;
-    for (int s = 0; s < ksteps; s++)
-        for (int h = 0; h < 2; h++)
-            for (int row = 0; row < 16; row++)
-                for (int q = 0; q < 4; q++) {
-                    uint32_t word = 0;
-                    const int sg = p->l1_factor[row] < 0 ? -1 : 1;
-                    for (int i = 0; i < 4; i++) {
-                        const int c = 32 * s + 16 * h + 4 * i + q;   // K position 16h + 4q + i <-> channel c
-                        const int w = c < C ? sg * p->l1_weight_align[row * CA + c] : 0;
-                        word |= (uint32_t)(uint8_t)(int8_t)w << (8 * i);
-                    }
-                    f->w1frag[((s * 2 + h) * 16 + row) * 4 + q] = word;
-                }
-    // ---- layer 2
-    for (int k = 0; k < 16; k++) {
-        const int8_t* w = p->l2_weight_reverse + k * 64;
-        int64_t sum = 0;
-        for (int j = 0; j < 64; j++) sum += iabs64(w[j]);
-        Pooled po;
-        if (!pack_pooled(128 * sum, p->l2_offset[k], p->l2_factor[k], &po, why)) return false;
-        f->thr2[k] = po.thr; f->sig2[k] = po.sig; f->soff2[k] = po.soff; f->m2[k] = po.m; f->sh2[k] = po.sh;
-        for (int r = 0; r < 4; r++)
-            for (int j = 0; j < 128; j++) {
-                const int tap = j + r - 32;
-                f->w2sh[k * kToepChanBytes + r * kToepCopyStride + j] = (tap >= 0 && tap < 64) ? (uint8_t)w[tap] : 0;
-            }
-    }
-    // ---- layer 3 (exported array is flipped: torch-order tap j = l3_weight[15 - j])
-    {
-        const int sg = p->l3_factor < 0 ? -1 : 1;
-        if (!magic_for(iabs64(p->l3_factor), &f->m3, &f->sh3)) { *why = "|l3_factor| < 4"; return false; }
-        for (int k = 0; k < 16; k++)
-            for (int r = 0; r < 4; r++)
-                for (int i = 0; i < 5; i++) {
-                    uint32_t word = 0;
-                    for (int b = 0; b < 4; b++) {
-                        const int tap = 4 * i + b - r;
-                        int w = (tap >= 0 && tap < 16) ? p->l3_weight[k * 16 + 15 - tap] : 0;
-                        if (sg < 0 && w == -128) { *why = "weight -128 cannot be negated (negative layer-3 factor)"; return false; }
-                        word |= (uint32_t)(uint8_t)(int8_t)(sg * w) << (8 * b);
-                    }
-                    f->w3sh[(k * 4 + r) * 5 + i] = word;
-                }
-    }
-    // ---- layer 4
-    for (int k = 0; k < 16; k++) {
-        const int8_t* w = p->l4_weight + k * 16;
-        int64_t sum = 0;
-        for (int i = 0; i < 16; i++) sum += iabs64(w[i]);
-        Pooled po;
-        if (!pack_pooled(128 * sum, p->l4_offset[k], p->l4_factor[k], &po, why)) return false;
-        f->thr4[k] = po.thr; f->sig4[k] = po.sig; f->soff4[k] = po.soff; f->m4[k] = po.m; f->sh4[k] = po.sh;
-        for (int q = 0; q < 4; q++) {
-            uint32_t word = 0;
-            for (int i = 0; i < 4; i++) word |= (uint32_t)(uint8_t)w[4 * q + i] << (8 * i);
-            f->w4frag[k * 4 + q] = word;
-        }
-    }
-    // ---- layer 5
-    {
-        const int sg = p->l5_factor < 0 ? -1 : 1;
-        if (!magic_for(iabs64(p->l5_factor), &f->m5, &f->sh5)) { *why = "|l5_factor| < 4"; return false; }
-        for (int n = 0; n < 4; n++) {
-            int64_t sum = 0;
-            for (int k = 0; k < 16; k++)
-                for (int t = 0; t < T64; t++) {
-                    const int w = p->l5_weight[(n * 16 + k) * T64A + t];
-                    if (sg < 0 && w == -128) { *why = "weight -128 cannot be negated (negative layer-5 factor)"; return false; }
-                    f->w5p[(n * 16 + k) * T64P + t] = (int8_t)(sg * w);
-                    sum += iabs64(w);
-                }
-            if (128 * sum + 128 >= kMagicRange) { *why = "layer-5 accumulator outside the magic-division range"; return false; }
-            f->b5[n] = sg * p->l5_bias[n];
-        }
-    }
-    return true;
-}
-
 // magic for the "no shift" form q = mulhi(x, m) + (x < 0), m = floor(2^32 / d) + 1.  With e = m d - 2^32
-// in (0, d] the form is exact while |x| e <= 2^32; outside [-129 d, 129 d] the true quotient saturates
-// under clip8 and the approximation errs only away from zero, so exactness is needed on that range only.
+// in (0, d]: x m / 2^32 = x / d + x e / (d 2^32), so the form is exact while |x| e < 2^32 (the error term stays below
+// 1 / d).  Beyond |x| >= 130 d the true quotient is >= 130 in magnitude and the approximation errs only away from zero
+// (x > 0: floor(x/d + err) >= floor(x/d) >= 130; x < 0: floor(x/d - err) + 1 <= x/d + 1 <= -129), so both saturate to
+// the same clip8 value: exactness is needed on [-130 d, 130 d] only.  Tests: tests/test_host_logic.py::test_fast1_*.
 bool magic32_for(int64_t d, int64_t xmax, int* m) {
     if (d < 4 || d > 0x7fffffff) return false;
     const int64_t mm = (int64_t(1) << 32) / d + 1;
     const int64_t e = mm * d - (int64_t(1) << 32);
     const int64_t lim = xmax < 130 * d ? xmax : 130 * d;
-    if ((__int128)lim * e > ((__int128)1 << 32)) return false;
+    if ((__int128)lim * e >= ((__int128)1 << 32)) return false;    // strict: x e == 2^32 with x mod d == d - 1 would round up
     *m = (int)mm;
     return true;
 }
@@ -490,13 +390,6 @@ int validate(const mibmi_params_t* p) {
     return MIBMI_OK;
 }
 
-void free_wolf_scratch(mibmi_net* n) {
-    for (int i = 0; i < 2; i++) {
-        if (n->wolf_scratch[i]) cudaFree(n->wolf_scratch[i]);
-        n->wolf_scratch[i] = nullptr;
-    }
-}
-
 void free_host_staging(mibmi_net* n) {
     for (int i = 0; i < 2; i++) {
         if (n->hx_dev[i]) cudaFree(n->hx_dev[i]);
@@ -505,93 +398,128 @@ void free_host_staging(mibmi_net* n) {
         if (n->hy_pin[i]) cudaFreeHost(n->hy_pin[i]);
         n->hx_dev[i] = n->hy_dev[i] = n->hx_pin[i] = n->hy_pin[i] = nullptr;
     }
-    n->h_cap = 0;
+    n->h_cap_trials = 0;
+    n->h_cap_bytes = 0;
 }
 
 size_t trial_bytes(const mibmi_net* n, int layout) {
     return layout == MIBMI_LAYOUT_BCT ? (size_t)n->C * n->T : (size_t)n->T * align4(n->C);
 }
 
-// The fused module-order kernels, best first.
+// Names mibmi_last_kernel reports; the index is stored by whoever launches (never inferred from the path afterwards).
+enum { K_NONE = 0, K_TC = 1, K_PIPE = 2, K_GENERIC = 3, K_STREAM = 4, K_TCR = 5 };
+
+// The fused module-order kernels, best first.  *which = the kernel that was launched.
 cudaError_t launch_fused_bct(mibmi_net* net, int path, const int8_t* x, int64_t B, int8_t* logits, const PeerOut& peers,
-                             int8_t* t1, int8_t* t2, int8_t* t3, int8_t* t4, cudaStream_t stream) {
-    if (path == MIBMI_PATH_FUSED && net->tc_ok)
+                             int8_t* t1, int8_t* t2, int8_t* t3, int8_t* t4, cudaStream_t stream, int* which) {
+    if (path == MIBMI_PATH_FUSED && net->tc_ok) {
+        *which = K_TC;
         return launch_tc(net->pipe_dev, net->pipe_fast1, net->C, net->T, x, B, logits, peers, t1, t2, t3, t4, net->num_sms, stream);
-    if (path == MIBMI_PATH_FUSED && net->tcr_ok)
-        return launch_tcr(net->pipe_dev, net->pipe_fast1, net->C, net->T, x, B, logits, peers, t1, t2, t3, t4, net->num_sms, stream);
+    }
+    if (path == MIBMI_PATH_FUSED && net->tcr_ok) {
+        *which = K_TCR;
+        return launch_tcr(net->pipe_dev, net->pipe_fast1, net->C, net->T, x, B, MIBMI_LAYOUT_BCT, logits, peers, t1, t2, t3, t4,
+                          net->num_sms, stream);
+    }
+    *which = K_PIPE;
     return launch_pipe(net->pipe_dev, net->pipe_fast1, net->C, net->T, x, B, logits, peers, t1, t2, t3, t4, net->num_sms, stream);
 }
 
-// Wolf order through the reorder scratch: transpose a chunk (it stays in L2), run the fused kernel on it, next chunk.
-cudaError_t launch_wolf_chunks(mibmi_net* net, int path, int slot, const int8_t* x, int64_t B, int8_t* logits,
-                               const PeerOut& peers, int8_t* t1, int8_t* t2, int8_t* t3, int8_t* t4, cudaStream_t stream) {
+// Wolf order through a reorder scratch: transpose a chunk, run the fused kernel on it, next chunk.  The scratch belongs to
+// this call: allocated and freed in stream order on the caller's stream (no handle-owned state, safe for concurrent calls
+// on different streams).
+cudaError_t launch_wolf_chunks(mibmi_net* net, int path, const int8_t* x, int64_t B, int8_t* logits, const PeerOut& peers,
+                               int8_t* t1, int8_t* t2, int8_t* t3, int8_t* t4, cudaStream_t stream, int* which, int64_t* launches) {
     const size_t CT = (size_t)net->C * net->T, in_bytes = (size_t)net->T * align4(net->C);
-    {
-        std::lock_guard<std::mutex> lk(net->wolf_mu);
-        if (!net->wolf_scratch[slot]) {
-            cudaError_t e = cudaMalloc(&net->wolf_scratch[slot], CT * (size_t)net->wolf_chunk + 16);
-            if (e != cudaSuccess) return e;
-        }
-    }
-    int8_t* scratch = net->wolf_scratch[slot];
+    const int64_t chunk = B < net->wolf_chunk ? B : net->wolf_chunk;
+    int8_t* scratch = nullptr;
+    cudaError_t e = cudaMallocAsync(&scratch, CT * (size_t)chunk + 16, stream);
+    if (e != cudaSuccess) return e;
     const int T8 = net->T / 8, T64 = T8 / 8;
-    for (int64_t off = 0; off < B; off += net->wolf_chunk) {
-        const int64_t nb = B - off < net->wolf_chunk ? B - off : net->wolf_chunk;
-        cudaError_t e = launch_wolf_reorder(x + off * in_bytes, scratch, nb, net->C, net->T, net->num_sms, stream);
-        if (e != cudaSuccess) return e;
+    for (int64_t off = 0; off < B && e == cudaSuccess; off += chunk) {
+        const int64_t nb = B - off < chunk ? B - off : chunk;
+        e = launch_wolf_reorder(x + off * in_bytes, scratch, nb, net->C, net->T, net->num_sms, stream);
+        if (e != cudaSuccess) break;
         PeerOut po = peers;
         for (int i = 0; i < po.n; i++) po.p[i] += off * net->N;
         e = launch_fused_bct(net, path, scratch, nb, logits + off * net->N, po,
                              t1 ? t1 + off * net->F2 * net->T : nullptr, t2 ? t2 + off * net->F2 * T8 : nullptr,
-                             t3 ? t3 + off * net->F2 * T8 : nullptr, t4 ? t4 + off * net->F2 * T64 : nullptr, stream);
-        if (e != cudaSuccess) return e;
+                             t3 ? t3 + off * net->F2 * T8 : nullptr, t4 ? t4 + off * net->F2 * T64 : nullptr, stream, which);
+        *launches += 2;
     }
-    return cudaSuccess;
+    const cudaError_t ef = cudaFreeAsync(scratch, stream);
+    return e != cudaSuccess ? e : ef;
 }
 
+// One launch may cover at most this many trials: the tensor-map coordinates of the TMA kernels (b * T + t, b * C + c) are
+// 32-bit.  A multiple of 16, so that every sub-batch of a 16-byte-aligned batch is 16-byte aligned again.
+constexpr int64_t kMaxLaunchTrials = int64_t(1) << 20;
+
 int forward_impl(mibmi_net* net, const int8_t* x, int64_t B, int layout, int8_t* logits, int8_t* t1, int8_t* t2,
-                 int8_t* t3, int8_t* t4, bool taps, cudaStream_t stream, const PeerOut* peers = nullptr, int slot = 0) {
+                 int8_t* t3, int8_t* t4, bool taps, cudaStream_t stream, const PeerOut* peers = nullptr) {
     if (!net) return MIBMI_ERR_NULL;
     if (B < 0 || (layout != MIBMI_LAYOUT_BCT && layout != MIBMI_LAYOUT_BTC)) return MIBMI_ERR_PARAM;
     if (B == 0) return MIBMI_OK;   // empty batch: nothing to read or write, pointers may be null
     if (!x || !logits) return MIBMI_ERR_NULL;
-    if (((uintptr_t)x & 15) != 0 || (net->N == 4 && ((uintptr_t)logits & 3) != 0)) return MIBMI_ERR_ALIGN;
+    const bool aligned = ((uintptr_t)x & 15) == 0 && (net->N != 4 || ((uintptr_t)logits & 3) == 0);
     int path = net->force_path;
     const bool wolf_fused = net->tc_wolf_ok && layout == MIBMI_LAYOUT_BTC;     // tcgen05 kernel, K-major operand from the Wolf order
-    const bool wolf_reorder = net->wolf_reorder_ok && layout == MIBMI_LAYOUT_BTC && !wolf_fused;   // transpose into the L2 scratch first
-    const bool pipe_possible = net->pipe_ok && (layout == MIBMI_LAYOUT_BCT || wolf_reorder ||
+    const bool wolf_tcr = net->tcr_wolf_ok && layout == MIBMI_LAYOUT_BTC && net->force_path != MIBMI_PATH_FUSED_PIPE;   // same, rows of 24 bytes expanded in the kernel
+    const bool wolf_reorder = net->wolf_reorder_ok && layout == MIBMI_LAYOUT_BTC && !wolf_fused && !wolf_tcr;   // transpose into a scratch first
+    const bool pipe_possible = net->pipe_ok && (layout == MIBMI_LAYOUT_BCT || wolf_reorder || wolf_tcr ||
                                                 (wolf_fused && net->force_path != MIBMI_PATH_FUSED_PIPE));
-    const bool v1_possible = net->fused_ok && layout == MIBMI_LAYOUT_BCT && !taps;
-    if (path == MIBMI_PATH_AUTO) path = (pipe_possible && !taps) ? MIBMI_PATH_FUSED : MIBMI_PATH_GENERIC;
+    // the generic kernel reads bytes: it has no alignment requirement and takes what the fused kernels cannot
+    if (path == MIBMI_PATH_AUTO) path = (pipe_possible && !taps && aligned) ? MIBMI_PATH_FUSED : MIBMI_PATH_GENERIC;
     if ((path == MIBMI_PATH_FUSED || path == MIBMI_PATH_FUSED_PIPE) && !pipe_possible) return MIBMI_ERR_UNSUPPORTED;
-    if (path == MIBMI_PATH_FUSED_V1 && !v1_possible) return MIBMI_ERR_UNSUPPORTED;
+    if ((path == MIBMI_PATH_FUSED || path == MIBMI_PATH_FUSED_PIPE) && !aligned) return MIBMI_ERR_ALIGN;
     DeviceGuard dg(net->device);
     if (dg.err != cudaSuccess) return fail_cuda(net, dg.err);
-    cudaError_t e;
-    PeerOut none;
-    none.n = 0;
-    if (path == MIBMI_PATH_FUSED && wolf_fused)
-        e = launch_tc_wolf(net->pipe_dev, net->pipe_fast1, net->C, net->T, x, B, logits, peers ? *peers : none, t1, t2, t3, t4,
-                           net->num_sms, stream);
-    else if ((path == MIBMI_PATH_FUSED || path == MIBMI_PATH_FUSED_PIPE) && wolf_reorder)
-        e = launch_wolf_chunks(net, path, slot, x, B, logits, peers ? *peers : none, t1, t2, t3, t4, stream);
-    else if (path == MIBMI_PATH_FUSED || path == MIBMI_PATH_FUSED_PIPE)
-        e = launch_fused_bct(net, path, x, B, logits, peers ? *peers : none, t1, t2, t3, t4, stream);
-    else if (path == MIBMI_PATH_FUSED_V1)
-        e = launch_fused(net->fused_dev, net->C, net->T, x, B, logits, net->num_sms, net->ctas_per_sm, stream);
-    else
-        e = launch_generic(net->gen_dev, net->T, net->F2, x, B, layout, logits, t1, t2, t3, t4, net->num_sms, stream);
-    if (e != cudaSuccess) return fail_cuda(net, e);
-    if (peers && path != MIBMI_PATH_FUSED && path != MIBMI_PATH_FUSED_PIPE)      // kernels without the fused gather: peer copies on the same stream
-        for (int i = 0; i < peers->n; i++) {
-            e = cudaMemcpyAsync(peers->p[i], logits, (size_t)B * net->N, cudaMemcpyDefault, stream);
-            if (e != cudaSuccess) return fail_cuda(net, e);
+    const bool fused = path == MIBMI_PATH_FUSED || path == MIBMI_PATH_FUSED_PIPE;
+    const size_t tb = trial_bytes(net, layout);
+    const int T8 = net->T / 8, T64 = T8 / 8;
+    int which = K_NONE;
+    int64_t launches = 0;
+    for (int64_t off = 0; off < B; off += kMaxLaunchTrials) {
+        const int64_t nb = B - off < kMaxLaunchTrials ? B - off : kMaxLaunchTrials;
+        const int8_t* xo = x + (size_t)off * tb;
+        int8_t* lo = logits + off * net->N;
+        int8_t* o1 = t1 ? t1 + off * net->F2 * net->T : nullptr;
+        int8_t* o2 = t2 ? t2 + off * net->F2 * T8 : nullptr;
+        int8_t* o3 = t3 ? t3 + off * net->F2 * T8 : nullptr;
+        int8_t* o4 = t4 ? t4 + off * net->F2 * T64 : nullptr;
+        PeerOut po;
+        po.n = 0;
+        if (peers) {
+            po = *peers;
+            for (int i = 0; i < po.n; i++) po.p[i] += off * net->N;
         }
+        cudaError_t e;
+        if (fused && wolf_fused && path == MIBMI_PATH_FUSED) {
+            which = K_TC;
+            launches++;
+            e = launch_tc_wolf(net->pipe_dev, net->pipe_fast1, net->C, net->T, xo, nb, lo, po, o1, o2, o3, o4, net->num_sms, stream);
+        } else if (fused && wolf_tcr) {
+            which = K_TCR;
+            launches++;
+            e = launch_tcr(net->pipe_dev, net->pipe_fast1, net->C, net->T, xo, nb, MIBMI_LAYOUT_BTC, lo, po, o1, o2, o3, o4,
+                           net->num_sms, stream);
+        } else if (fused && wolf_reorder) {
+            e = launch_wolf_chunks(net, path, xo, nb, lo, po, o1, o2, o3, o4, stream, &which, &launches);
+        } else if (fused) {
+            launches++;
+            e = launch_fused_bct(net, path, xo, nb, lo, po, o1, o2, o3, o4, stream, &which);
+        } else {
+            which = K_GENERIC;
+            launches++;
+            e = launch_generic(net->gen_dev, net->T, net->F2, xo, nb, layout, lo, o1, o2, o3, o4, net->num_sms, stream);
+            for (int i = 0; i < po.n && e == cudaSuccess; i++)    // no fused gather in this kernel: peer copies on the same stream
+                e = cudaMemcpyAsync(po.p[i], lo, (size_t)nb * net->N, cudaMemcpyDefault, stream);
+        }
+        if (e != cudaSuccess) return fail_cuda(net, e);
+    }
     net->last_path.store(path);
-    net->last_kernel.store(path == MIBMI_PATH_FUSED ? (net->tc_ok ? 1 : net->tcr_ok ? 6 : 2) : path == MIBMI_PATH_FUSED_PIPE ? 2
-                           : path == MIBMI_PATH_FUSED_V1 ? 3 : 4);
-    net->launches.fetch_add((path == MIBMI_PATH_FUSED || path == MIBMI_PATH_FUSED_PIPE) && wolf_reorder
-                                ? 2 * ((B + net->wolf_chunk - 1) / net->wolf_chunk) : 1);
+    net->last_kernel.store(which);
+    net->launches.fetch_add(launches);
     return MIBMI_OK;
 }
 
@@ -617,10 +545,10 @@ const char* mibmi_strerror(int status) {
 int mibmi_last_cuda_error(const mibmi_net_t* net) { return net ? net->last_cuda.load() : 0; }
 int mibmi_last_path(const mibmi_net_t* net) { return net ? net->last_path.load() : 0; }
 const char* mibmi_last_kernel(const mibmi_net_t* net) {
-    static const char* const names[] = {"", "tc_forward_kernel", "pipe_forward_kernel", "fused_forward_kernel",
-                                        "generic_forward_kernel", "stream_forward_kernel", "tcr_forward_kernel"};
+    static const char* const names[] = {"", "tc_forward_kernel", "pipe_forward_kernel", "generic_forward_kernel",
+                                        "stream_forward_kernel", "tcr_forward_kernel"};      // indexed by K_*
     const int k = net ? net->last_kernel.load() : 0;
-    return names[k >= 0 && k <= 6 ? k : 0];
+    return names[k >= 0 && k <= K_TCR ? k : 0];
 }
 int64_t mibmi_launch_count(const mibmi_net_t* net) { return net ? net->launches.load() : 0; }
 
@@ -635,19 +563,13 @@ int mibmi_debug_magic(int32_t d, int32_t* m, int32_t* s) {
     return magic_for(d, m, s) ? MIBMI_OK : MIBMI_ERR_PARAM;
 }
 
-// Diagnostics (no GPU needed): the packed network exactly as the fused kernel reads it.
-int64_t mibmi_debug_pack_fused(const mibmi_params_t* p, void* out, int64_t cap, const char** why) {
-    if (!p) return MIBMI_ERR_NULL;
-    int st = validate(p);
-    if (st != MIBMI_OK) return st;
-    if (!out) return (int64_t)sizeof(FusedNet);
-    if (cap < (int64_t)sizeof(FusedNet)) return MIBMI_ERR_PARAM;
-    const char* w = "";
-    const bool ok = pack_fused(p, reinterpret_cast<FusedNet*>(out), &w);
-    if (why) *why = w;
-    return ok ? (int64_t)sizeof(FusedNet) : MIBMI_ERR_UNSUPPORTED;
+int mibmi_debug_magic32(int32_t d, int64_t xmax, int32_t* m) {
+    if (!m) return MIBMI_ERR_NULL;
+    if (xmax < 0) return MIBMI_ERR_PARAM;
+    return magic32_for(d, xmax, m) ? MIBMI_OK : MIBMI_ERR_UNSUPPORTED;
 }
 
+// Diagnostics (no GPU needed): the packed network exactly as the fused kernels read it.
 int64_t mibmi_debug_pack_pipe(const mibmi_params_t* p, void* out, int64_t cap, const char** why) {
     if (!p) return MIBMI_ERR_NULL;
     int st = validate(p);
@@ -676,10 +598,9 @@ int mibmi_create(const mibmi_params_t* p, int device, mibmi_net_t** out) {
     const int C = p->C, T = p->T, F2 = p->F2, N = p->N, CA = align4(C), T64 = (T / 8) / 8, T64A = align4(T64);
     std::vector<int8_t> w5((size_t)N * F2 * T64);
     GenericNet* g = new (std::nothrow) GenericNet();
-    FusedNet* f = new (std::nothrow) FusedNet();
     PipeNet* pn = new (std::nothrow) PipeNet();
     StreamNet* sn = new (std::nothrow) StreamNet();
-    if (!g || !f || !pn || !sn) { delete g; delete f; delete pn; delete sn; delete n; return MIBMI_ERR_CUDA; }
+    if (!g || !pn || !sn) { delete g; delete pn; delete sn; delete n; return MIBMI_ERR_CUDA; }
     memset(g, 0, sizeof(*g));
     g->C = C; g->T = T; g->F2 = F2; g->N = N; g->T8 = T / 8; g->T64 = T64; g->reorder = n->reorder;
     for (int k = 0; k < F2; k++) {
@@ -697,12 +618,12 @@ int mibmi_create(const mibmi_params_t* p, int device, mibmi_net_t** out) {
         for (int k = 0; k < F2; k++)
             for (int t = 0; t < T64; t++) w5[((size_t)c * F2 + k) * T64 + t] = p->l5_weight[((size_t)c * F2 + k) * T64A + t];
     }
-    n->fused_ok = pack_fused(p, f, &n->fused_why);
     n->pipe_ok = pack_pipe(p, pn, &n->pipe_why);
     n->pipe_fast1 = pn->fast1 != 0;
     n->tc_ok = n->pipe_ok && tc_has_instance(p->C, p->T);
     n->tcr_ok = n->pipe_ok && tcr_has_instance(p->C, p->T);
     n->tc_wolf_ok = n->tc_ok && tc_has_wolf_instance(p->C, p->T);
+    n->tcr_wolf_ok = n->tcr_ok && tcr_has_wolf_instance(p->C, p->T);
     n->wolf_reorder_ok = n->pipe_ok && !n->tc_wolf_ok && reorder_has_instance(p->C, p->T);
     if (n->pipe_ok) n->stream_ok = pack_stream(p, pn, sn, &n->stream_why);
     else n->stream_why = n->pipe_why;
@@ -723,10 +644,6 @@ int mibmi_create(const mibmi_params_t* p, int device, mibmi_net_t** out) {
     g->w5 = n->w5_dev;
     if (e == cudaSuccess) e = cudaMalloc(&n->gen_dev, sizeof(GenericNet));
     if (e == cudaSuccess) e = cudaMemcpy(n->gen_dev, g, sizeof(GenericNet), cudaMemcpyHostToDevice);
-    if (e == cudaSuccess && n->fused_ok) {
-        e = cudaMalloc(&n->fused_dev, sizeof(FusedNet));
-        if (e == cudaSuccess) e = cudaMemcpy(n->fused_dev, f, sizeof(FusedNet), cudaMemcpyHostToDevice);
-    }
     if (e == cudaSuccess && n->pipe_ok) {
         e = cudaMalloc(&n->pipe_dev, sizeof(PipeNet));
         if (e == cudaSuccess) e = cudaMemcpy(n->pipe_dev, pn, sizeof(PipeNet), cudaMemcpyHostToDevice);
@@ -736,7 +653,6 @@ int mibmi_create(const mibmi_params_t* p, int device, mibmi_net_t** out) {
         if (e == cudaSuccess) e = cudaMemcpy(n->stream_dev, sn, sizeof(StreamNet), cudaMemcpyHostToDevice);
     }
     delete g;
-    delete f;
     delete pn;
     delete sn;
     if (e != cudaSuccess) {
@@ -753,11 +669,9 @@ int mibmi_destroy(mibmi_net_t* net) {
         DeviceGuard dg(net->device);
         if (net->gen_dev) cudaFree(net->gen_dev);
         if (net->w5_dev) cudaFree(net->w5_dev);
-        if (net->fused_dev) cudaFree(net->fused_dev);
         if (net->pipe_dev) cudaFree(net->pipe_dev);
         if (net->stream_dev) cudaFree(net->stream_dev);
         free_host_staging(net);
-        free_wolf_scratch(net);
         for (int i = 0; i < 2; i++)
             if (net->hs[i]) cudaStreamDestroy(net->hs[i]);
     }
@@ -769,14 +683,10 @@ int mibmi_set_option(mibmi_net_t* net, int option, int64_t value) {
     if (!net) return MIBMI_ERR_NULL;
     switch (option) {
         case MIBMI_OPT_FORCE_PATH:
-            if (value < MIBMI_PATH_AUTO || value > MIBMI_PATH_FUSED_PIPE || value == MIBMI_PATH_STREAM) return MIBMI_ERR_PARAM;
+            if (value != MIBMI_PATH_AUTO && value != MIBMI_PATH_GENERIC && value != MIBMI_PATH_FUSED && value != MIBMI_PATH_FUSED_PIPE)
+                return MIBMI_ERR_PARAM;
             if ((value == MIBMI_PATH_FUSED || value == MIBMI_PATH_FUSED_PIPE) && !net->pipe_ok) return MIBMI_ERR_UNSUPPORTED;
-            if (value == MIBMI_PATH_FUSED_V1 && !net->fused_ok) return MIBMI_ERR_UNSUPPORTED;
             net->force_path = (int)value;
-            return MIBMI_OK;
-        case MIBMI_OPT_CTAS_PER_SM:
-            if (value < 0 || value > 8) return MIBMI_ERR_PARAM;
-            net->ctas_per_sm = (int)value;
             return MIBMI_OK;
         case MIBMI_OPT_STREAM_MODE:
             if (value < MIBMI_STREAM_AUTO || value > MIBMI_STREAM_GATHER) return MIBMI_ERR_PARAM;
@@ -812,7 +722,6 @@ int mibmi_forward_int8_gather(mibmi_net_t* net, const int8_t* x_dev, int64_t B, 
 
 int mibmi_forward_int8_taps(mibmi_net_t* net, const int8_t* x_dev, int64_t B, int layout, int8_t* logits_dev,
                             int8_t* y1, int8_t* y2, int8_t* y3, int8_t* y4, void* stream) {
-    if (net && net->force_path == MIBMI_PATH_FUSED_V1) return MIBMI_ERR_UNSUPPORTED;
     return forward_impl(net, x_dev, B, layout, logits_dev, y1, y2, y3, y4, true, (cudaStream_t)stream);
 }
 
@@ -833,7 +742,9 @@ int mibmi_forward_int8_host(mibmi_net_t* net, const int8_t* x_host, int64_t B, i
     bool x_pinned = cudaPointerGetAttributes(&pa, x_host) == cudaSuccess && pa.type == cudaMemoryTypeHost;
     bool y_pinned = cudaPointerGetAttributes(&pa, logits_host) == cudaSuccess && pa.type == cudaMemoryTypeHost;
     cudaGetLastError();
-    if (net->h_cap < chunk) {
+    // the staging buffers hold `chunk` trials of THIS call's layout: the trial size differs between the layouts
+    // (C * T vs T * align4(C)), so capacity is tracked in bytes as well as in trials
+    if (net->h_cap_trials < chunk || net->h_cap_bytes < tb * (size_t)chunk) {
         free_host_staging(net);
         for (int i = 0; i < 2 && e == cudaSuccess; i++) {
             if (!net->hs[i]) e = cudaStreamCreateWithFlags(&net->hs[i], cudaStreamNonBlocking);
@@ -843,7 +754,8 @@ int mibmi_forward_int8_host(mibmi_net_t* net, const int8_t* x_host, int64_t B, i
             if (e == cudaSuccess) e = cudaMallocHost(&net->hy_pin[i], (size_t)net->N * chunk);
         }
         if (e != cudaSuccess) { free_host_staging(net); return fail_cuda(net, e); }
-        net->h_cap = chunk;
+        net->h_cap_trials = chunk;
+        net->h_cap_bytes = tb * (size_t)chunk;
     }
     int status = MIBMI_OK;
     int64_t pending_lo[2] = {-1, -1}, pending_n[2] = {0, 0};
@@ -862,8 +774,7 @@ int mibmi_forward_int8_host(mibmi_net_t* net, const int8_t* x_host, int64_t B, i
         if (!x_pinned) { memcpy(net->hx_pin[s], src, tb * nb); src = net->hx_pin[s]; }
         e = cudaMemcpyAsync(net->hx_dev[s], src, tb * nb, cudaMemcpyHostToDevice, net->hs[s]);
         if (e != cudaSuccess) { status = fail_cuda(net, e); break; }
-        status = forward_impl(net, net->hx_dev[s], nb, layout, net->hy_dev[s], nullptr, nullptr, nullptr, nullptr, false, net->hs[s],
-                              nullptr, s);
+        status = forward_impl(net, net->hx_dev[s], nb, layout, net->hy_dev[s], nullptr, nullptr, nullptr, nullptr, false, net->hs[s]);
         if (status != MIBMI_OK) break;
         int8_t* dst = y_pinned ? logits_host + (size_t)done * net->N : net->hy_pin[s];
         e = cudaMemcpyAsync(dst, net->hy_dev[s], (size_t)nb * net->N, cudaMemcpyDeviceToHost, net->hs[s]);
@@ -912,7 +823,7 @@ static int stream_impl(mibmi_net* net, const int8_t* x, int64_t S, int64_t L, in
                                       net->num_sms, stream);
         if (e != cudaSuccess) return fail_cuda(net, e);
         net->last_path.store(MIBMI_PATH_STREAM);
-        net->last_kernel.store(5);
+        net->last_kernel.store(K_STREAM);
         net->launches.fetch_add(1);
         return MIBMI_OK;
     }

@@ -32,40 +32,12 @@ struct GenericNet {
 };
 
 // ---------------------------------------------------------------------------------------------
-// Network as the fused kernel reads it (F2 == 16, N == 4, reorder_bn == 1).  Copied to shared
-// memory by every CTA.  Divisors are made positive on the host (the sign is folded into the L1 /
-// L3 / L5 weights and into `sig` for the pooled layers) and replaced by (magic, shift) pairs:
-//   tdiv(x, d) == (mulhi(x, magic) >> shift) + (x < 0)      for |x| < 2^29, d >= 4
-constexpr int kToepCopyStride = 192;                 // bytes between the 4 byte-shifted copies
-constexpr int kToepChanBytes = 4 * kToepCopyStride;  // 768 B per channel
-constexpr int kMaxT64P = 32;                         // padded T/64 (fused path: T <= 2048)
-
-struct FusedNet {
-    // layer 1: A fragments of mma.m16n8k32 [kstep][half][row 16][q 4]
-    uint32_t w1frag[2 * 2 * 16 * 4];
-    int off1[16], m1[16], sh1[16];
-    // layer 2: per channel 4 byte-shifted zero-padded copies of the 64 taps
-    alignas(16) uint8_t w2sh[16 * kToepChanBytes];
-    int thr2[16], sig2[16], soff2[16], m2[16], sh2[16];
-    // layer 3: per channel, per byte phase r, 5 words of shifted taps
-    uint32_t w3sh[16 * 4 * 5];
-    int m3, sh3;
-    // layer 4: A fragments of mma.m16n8k16 [row 16][q 4]
-    uint32_t w4frag[16 * 4];
-    int thr4[16], sig4[16], soff4[16], m4[16], sh4[16];
-    // layer 5: [n 4][k 16][T64P] zero padded, sign folded
-    alignas(16) int8_t w5p[4 * 16 * kMaxT64P];
-    int b5[4];
-    int m5, sh5;
-    int pad_[2];
-};
-static_assert(sizeof(FusedNet) % 16 == 0, "FusedNet is copied with 128-bit accesses");
-
-// ---------------------------------------------------------------------------------------------
 // Network as the warp-specialised pipeline kernel (mibmi_pipe.cu) reads it: every array is already
 // in MMA-fragment order, one 32-bit word per lane, so each warp loads its constants once with
 // coalesced global loads and keeps them in registers for the whole launch (nothing of the network
-// lives in shared memory).  Same host-side sign folding as FusedNet.
+// lives in shared memory).  Divisors are made positive on the host (the sign is folded into the L1 / L3 / L5 weights and
+// into `sig` for the pooled layers) and replaced by (magic, shift) pairs:
+//   tdiv(x, d) == (mulhi(x, magic) >> shift) + (x < 0)      for |x| < 2^29, d >= 4
 constexpr int kPipeMaxKB16 = 4;     // layer-1 blocks of 16 channels (C <= 64)
 constexpr int kPipeMaxKst5 = 16;    // layer-5 k-steps of 32 (T/64 padded to even <= 32)
 

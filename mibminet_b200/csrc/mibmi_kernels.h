@@ -6,7 +6,6 @@
 namespace mibmi {
 
 struct GenericNet;
-struct FusedNet;
 struct PipeNet;
 struct StreamNet;
 
@@ -16,13 +15,6 @@ cudaError_t launch_generic(const GenericNet* net_dev, int T, int F2, const int8_
                            cudaStream_t stream);
 cudaError_t launch_quantize(const float* x, long long n, float s, int8_t* q, cudaStream_t stream);
 cudaError_t launch_dequantize(const int8_t* q, long long n, float s, float* y, cudaStream_t stream);
-
-// Fused kernel: shapes are compile-time instantiations; returns false if (C, T) has none.
-bool fused_has_instance(int C, int T);
-// ctas_per_sm <= 0: default.  x must be [B][C][T], 16-byte aligned.
-cudaError_t launch_fused(const FusedNet* net_dev, int C, int T, const int8_t* x, long long B, int8_t* logits,
-                         int num_sms, int ctas_per_sm, cudaStream_t stream);
-
 
 // Warp-specialised pipeline kernel (mibmi_pipe.cu): the default fused path.  Optional taps
 // (y1 [B][16][T], y2/y3 [B][16][T/8], y4 [B][16][T/64]) select a diagnostic instantiation.
@@ -52,7 +44,10 @@ cudaError_t launch_tc_wolf(const PipeNet* net_dev, bool fast1, int C, int T, con
 // Same formulation for trials whose rows are not 16-byte aligned (mibmi_tcr.cu: realigning warps instead of TMA tiles,
 // MMA tiles that straddle trials): 22 x 1125.
 bool tcr_has_instance(int C, int T);
-cudaError_t launch_tcr(const PipeNet* net_dev, bool fast1, int C, int T, const int8_t* x, long long B, int8_t* logits,
+// layout 0: x [B][C][T] (rows realigned by funnel shifts); layout 1: Wolf order x [B][T][C_ALIGN] (rows of 24 bytes expanded
+// to the K-major 32-byte rows of the layer-1 operand inside the kernel -- no scratch, no second pass over HBM)
+bool tcr_has_wolf_instance(int C, int T);
+cudaError_t launch_tcr(const PipeNet* net_dev, bool fast1, int C, int T, const int8_t* x, long long B, int layout, int8_t* logits,
                        const PeerOut& peers, int8_t* t1, int8_t* t2, int8_t* t3, int8_t* t4, int num_sms, cudaStream_t stream);
 
 // Wolf order [n][T][C_ALIGN] -> module order [n][C][T] (mibmi_reorder.cu) for rows of 8 / 20 / 24 / 40 bytes; y 4-byte aligned.

@@ -502,14 +502,21 @@ pipe_forward_kernel(const __grid_constant__ CUtensorMap tmx, const PipeNet* __re
             const uint32_t dst = sbase + K::OFF_XS + st * K::XS_BYTES;
             const uint32_t bar = sbase + K::BAR_FULL_X + 8 * st;
             if (K::REAL) {
-                // lane c copies row c from the 16-byte boundary below it (x is 16-byte aligned); the last row of
-                // the last trial may read up to 15 bytes past the batch, inside its final 16-byte granule
-                const size_t off = toff + (size_t)lane * K::T;
-                const uint32_t bytes = lane < K::C ? (uint32_t)(((off & 15) + K::T + 15) & ~(size_t)15) : 0u;
+                // lane c copies row c from the 16-byte boundary below it (x is 16-byte aligned).  No byte outside the batch
+                // is read: the copy of the last row of the LAST trial stops at the 16-byte boundary below the end of the
+                // batch and its lane fetches the remaining <= 15 bytes with byte loads
+                const size_t off = toff + (size_t)lane * K::T, a0 = off & ~(size_t)15, end = (size_t)B * K::TRIAL_BYTES;
+                size_t a1 = (off + K::T + 15) & ~(size_t)15;
+                if (lane < K::C && a1 > end) {
+                    a1 = end & ~(size_t)15;
+                    for (size_t i = a1; i < end; i++) smem[K::OFF_XS + st * K::XS_BYTES + lane * K::XP + (i - a0)] = (uint8_t)x[i];
+                }
+                const uint32_t bytes = lane < K::C ? (uint32_t)(a1 - a0) : 0u;
                 const uint32_t total = __reduce_add_sync(0xffffffffu, bytes);
+                __syncwarp();                                      // the byte stores are ordered before lane 0's arrive (release)
                 if (lane == 0) mbar_expect_tx(bar, total);
                 __syncwarp();
-                if (lane < K::C) bulk_g2s(dst + lane * K::XP, x + (off & ~(size_t)15), bytes, bar);
+                if (lane < K::C) bulk_g2s(dst + lane * K::XP, x + a0, bytes, bar);
             } else if (K::UMMA) {
                 if (lane == 0) {
                     // 128-sample tiles [C][128] of the [B * C][T] tensor; columns past T are zero-filled

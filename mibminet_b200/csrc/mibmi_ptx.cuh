@@ -58,6 +58,26 @@ __device__ __forceinline__ void mbar_wait_sleep(uint32_t bar, uint32_t parity, u
         if (spins > (1u << 24)) __trap();
     }
 }
+// pure hardware wait: mbarrier.try_wait suspends the thread until the phase completes or the (implementation-defined) time
+// limit expires -- no instruction is issued while it sleeps, the loop only re-arms after a time-out
+__device__ __forceinline__ void mbar_wait_hw(uint32_t bar, uint32_t parity) {
+    uint32_t done = 0;
+    for (uint32_t spins = 0; !done; ++spins) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done) : "r"(bar), "r"(parity), "r"(MIBMI_WAIT_HINT_NS) : "memory");
+        if (spins > (1u << 22)) __trap();
+    }
+}
+// MODE 0: test_wait + nanosleep polling (round 1), 1: test_wait, then the suspending try_wait, 2: try_wait only
+template <int MODE>
+__device__ __forceinline__ void mbar_wait_mode(uint32_t bar, uint32_t parity, uint32_t ns) {
+    if (MODE == 0) mbar_wait_sleep(bar, parity, ns);
+    else if (MODE == 1) mbar_wait(bar, parity);
+    else mbar_wait_hw(bar, parity);
+}
 // TMA bulk copy global -> shared, completion counted in bytes on an mbarrier (SASS: UBLKCP)
 __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"

@@ -35,14 +35,17 @@ namespace mibmi {
 #ifndef MIBMI_TC_SLEEP_NS
 #define MIBMI_TC_SLEEP_NS 64
 #endif
+#ifndef MIBMI_TC_WAIT
+#define MIBMI_TC_WAIT 0                   // mbar_wait_mode: 0 = test_wait + nanosleep, 1 = test_wait then try_wait, 2 = try_wait
+#endif
 #ifdef MIBMI_PROF
 __device__ long long g_prof_tc[148 * 32 * 4];
-#define TWAIT(slot, ...) do { if (!mbar_test(__VA_ARGS__)) { const long long t0_ = clock64(); mbar_wait_sleep(__VA_ARGS__, MIBMI_TC_SLEEP_NS); pw_[slot] += clock64() - t0_; } } while (0)
+#define TWAIT(slot, ...) do { if (!mbar_test(__VA_ARGS__)) { const long long t0_ = clock64(); mbar_wait_mode<MIBMI_TC_WAIT>(__VA_ARGS__, MIBMI_TC_SLEEP_NS); pw_[slot] += clock64() - t0_; } } while (0)
 #define TPROF_BEGIN long long pw_[3] = {0, 0, 0}; const long long pt0_ = clock64();
 #define TPROF_END if ((threadIdx.x & 31) == 0) { long long* o_ = g_prof_tc + (blockIdx.x * 32 + (threadIdx.x >> 5)) * 4; \
     o_[0] = clock64() - pt0_; o_[1] = pw_[0]; o_[2] = pw_[1]; o_[3] = pw_[2]; }
 #else
-#define TWAIT(slot, ...) mbar_wait_sleep(__VA_ARGS__, MIBMI_TC_SLEEP_NS)
+#define TWAIT(slot, ...) mbar_wait_mode<MIBMI_TC_WAIT>(__VA_ARGS__, MIBMI_TC_SLEEP_NS)
 #define TPROF_BEGIN
 #define TPROF_END
 #endif
@@ -393,14 +396,13 @@ tc_forward_kernel(const __grid_constant__ CUtensorMap tmx, const PipeNet* __rest
                         s0 += max((int)r[c][i], ca.x);
                         s1 += max((int)r[c][8 + i], ca.x);
                     }
-                    const int o0 = clip8(tdiv_magic(s0 * ca.y + ca.z, ca.w, shk));
-                    const int o1 = clip8(tdiv_magic(s1 * ca.y + ca.z, ca.w, shk));
+                    const uint32_t o01 = pack2_sat(tdiv_magic(s0 * ca.y + ca.z, ca.w, shk), tdiv_magic(s1 * ca.y + ca.z, ca.w, shk));
                     if (lane < K::ROWS) {
-                        *reinterpret_cast<uint16_t*>(y2s + k * K::Y2S) = (uint16_t)((o0 & 0xff) | ((o1 & 0xff) << 8));
+                        *reinterpret_cast<uint16_t*>(y2s + k * K::Y2S) = (uint16_t)o01;
                         if (TAPS && tap2 && b0 + s < B) {
                             int8_t* o = tap2 + ((size_t)(b0 + s) * 16 + k) * K::T8 + 2 * lane;
-                            o[0] = (int8_t)o0;
-                            o[1] = (int8_t)o1;
+                            o[0] = (int8_t)(o01 & 0xff);
+                            o[1] = (int8_t)((o01 >> 8) & 0xff);
                         }
                     }
                 }

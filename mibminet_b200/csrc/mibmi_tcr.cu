@@ -29,16 +29,19 @@ namespace mibmi {
 #ifndef MIBMI_TCR_SLEEP_LONG_NS
 #define MIBMI_TCR_SLEEP_LONG_NS 128       // waits with a trial's worth of slack (producer, M1, free-buffer waits)
 #endif
+#ifndef MIBMI_TCR_WAIT
+#define MIBMI_TCR_WAIT 0                  // mbar_wait_mode: 0 = test_wait + nanosleep, 1 = test_wait then try_wait, 2 = try_wait
+#endif
 #ifdef MIBMI_PROF
 __device__ long long g_prof_tcr[148 * 32 * 4];
-#define RWAIT(slot, ...) do { if (!mbar_test(__VA_ARGS__)) { const long long t0_ = clock64(); mbar_wait_sleep(__VA_ARGS__, MIBMI_TCR_SLEEP_NS); pw_[slot] += clock64() - t0_; } } while (0)
-#define RWAITL(slot, ...) do { if (!mbar_test(__VA_ARGS__)) { const long long t0_ = clock64(); mbar_wait_sleep(__VA_ARGS__, MIBMI_TCR_SLEEP_LONG_NS); pw_[slot] += clock64() - t0_; } } while (0)
+#define RWAIT(slot, ...) do { if (!mbar_test(__VA_ARGS__)) { const long long t0_ = clock64(); mbar_wait_mode<MIBMI_TCR_WAIT>(__VA_ARGS__, MIBMI_TCR_SLEEP_NS); pw_[slot] += clock64() - t0_; } } while (0)
+#define RWAITL(slot, ...) do { if (!mbar_test(__VA_ARGS__)) { const long long t0_ = clock64(); mbar_wait_mode<MIBMI_TCR_WAIT>(__VA_ARGS__, MIBMI_TCR_SLEEP_LONG_NS); pw_[slot] += clock64() - t0_; } } while (0)
 #define RPROF_BEGIN long long pw_[3] = {0, 0, 0}; const long long pt0_ = clock64();
 #define RPROF_END if ((threadIdx.x & 31) == 0) { long long* o_ = g_prof_tcr + (blockIdx.x * 32 + (threadIdx.x >> 5)) * 4; \
     o_[0] = clock64() - pt0_; o_[1] = pw_[0]; o_[2] = pw_[1]; o_[3] = pw_[2]; }
 #else
-#define RWAIT(slot, ...) mbar_wait_sleep(__VA_ARGS__, MIBMI_TCR_SLEEP_NS)
-#define RWAITL(slot, ...) mbar_wait_sleep(__VA_ARGS__, MIBMI_TCR_SLEEP_LONG_NS)
+#define RWAIT(slot, ...) mbar_wait_mode<MIBMI_TCR_WAIT>(__VA_ARGS__, MIBMI_TCR_SLEEP_NS)
+#define RWAITL(slot, ...) mbar_wait_mode<MIBMI_TCR_WAIT>(__VA_ARGS__, MIBMI_TCR_SLEEP_LONG_NS)
 #define RPROF_BEGIN
 #define RPROF_END
 #endif
@@ -310,24 +313,34 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
         }
     } else if (warp == kRWarpP) {
         // =====================================================================================
-        // P: one bulk copy per trial, from the 16-byte boundary below its first byte
+        // P: one bulk copy per trial, from the 16-byte boundary below its first byte.  No byte outside the batch is
+        //    read: the copy of the LAST trial of the batch stops at the 16-byte boundary below its end and the lanes
+        //    fetch the remaining <= 15 bytes with byte loads
         // =====================================================================================
-        if (lane == 0) {
-            for (int n = 0; n < ntr; n++) {
-                const int st = n & 1;
-                RWAITL(0, sbase + K::BAR_RAW_EMPTY + 8 * st, ((n >> 1) & 1) ^ 1);
-                const long long b = trial_of(n);
-                const uint32_t bar = sbase + K::BAR_RAW_FULL + 8 * st;
-                if (b < B) {
-                    const unsigned long long o = (unsigned long long)b * (K::C * K::T);
-                    const unsigned long long a0 = o & ~15ull;
-                    const uint32_t len = (uint32_t)(((o + K::C * K::T + 15) & ~15ull) - a0);
+        const unsigned long long total = (unsigned long long)B * (K::C * K::T);
+        for (int n = 0; n < ntr; n++) {
+            const int st = n & 1;
+            RWAITL(0, sbase + K::BAR_RAW_EMPTY + 8 * st, ((n >> 1) & 1) ^ 1);
+            const long long b = trial_of(n);
+            const uint32_t bar = sbase + K::BAR_RAW_FULL + 8 * st;
+            if (b < B) {
+                const unsigned long long o = (unsigned long long)b * (K::C * K::T);
+                const unsigned long long a0 = o & ~15ull;
+                unsigned long long a1 = (o + K::C * K::T + 15) & ~15ull;
+                if (a1 > total) {                                  // warp-uniform: only the last trial of the batch
+                    a1 = total & ~15ull;
+                    if (a1 + lane < total) smem[K::OFF_RAW + st * K::RAW_BYTES + (a1 - a0) + lane] = (uint8_t)x[a1 + lane];
+                    __syncwarp();                                  // the byte stores are ordered before lane 0's arrive (release)
+                }
+                if (lane == 0) {
+                    const uint32_t len = (uint32_t)(a1 - a0);
                     mbar_expect_tx(bar, len);
                     bulk_g2s(sbase + K::OFF_RAW + st * K::RAW_BYTES, x + a0, len, bar);
-                } else {
-                    mbar_arrive(bar);     // padding trial of the last group: nothing to read
                 }
+            } else if (lane == 0) {
+                mbar_arrive(bar);     // padding trial of the last group: nothing to read
             }
+            __syncwarp();
         }
     } else if (warp >= kRWarpR && warp < kRWarpP) {
         // =====================================================================================
@@ -470,14 +483,13 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
                                 s0 += max((int)r[c][e], ca.x);
                                 s1 += max((int)r[c][8 + e], ca.x);
                             }
-                            const int o0 = clip8(tdiv_magic(s0 * ca.y + ca.z, ca.w, shk));
-                            const int o1 = clip8(tdiv_magic(s1 * ca.y + ca.z, ca.w, shk));
+                            const uint32_t o01 = pack2_sat(tdiv_magic(s0 * ca.y + ca.z, ca.w, shk), tdiv_magic(s1 * ca.y + ca.z, ca.w, shk));
                             if (valid) {
-                                *reinterpret_cast<uint16_t*>(y2s + k * K::Y2S) = (uint16_t)((o0 & 0xff) | ((o1 & 0xff) << 8));
+                                *reinterpret_cast<uint16_t*>(y2s + k * K::Y2S) = (uint16_t)o01;
                                 if (TAPS && tap2 && b < B) {
                                     int8_t* o = tap2 + ((size_t)b * 16 + k) * K::T8 + 2 * blk;
-                                    o[0] = (int8_t)o0;
-                                    o[1] = (int8_t)o1;
+                                    o[0] = (int8_t)(o01 & 0xff);
+                                    o[1] = (int8_t)((o01 >> 8) & 0xff);
                                 }
                             }
                         }
@@ -625,8 +637,11 @@ bool tcr_has_instance(int C, int T) {
     return false;
 }
 
-cudaError_t launch_tcr(const PipeNet* net_dev, bool fast1, int C, int T, const int8_t* x, long long B, int8_t* logits,
+bool tcr_has_wolf_instance(int C, int T) { (void)C; (void)T; return false; }
+
+cudaError_t launch_tcr(const PipeNet* net_dev, bool fast1, int C, int T, const int8_t* x, long long B, int layout, int8_t* logits,
                        const PeerOut& peers, int8_t* t1, int8_t* t2, int8_t* t3, int8_t* t4, int num_sms, cudaStream_t stream) {
+    if (layout != 0) return cudaErrorInvalidValue;
 #define X(c, t) if (C == c && T == t) return launch_tcr_instance<c, t>(net_dev, fast1, x, B, logits, peers, t1, t2, t3, t4, num_sms, stream);
     MIBMI_TCR_SHAPES(X)
 #undef X

@@ -20,7 +20,7 @@ from .convert import WolfParams, align4, params_from_export, params_from_state_d
 
 _LAYOUTS = {"bct": _lib.LAYOUT_BCT, "btc": _lib.LAYOUT_BTC}
 _PATHS = {"auto": _lib.PATH_AUTO, "generic": _lib.PATH_GENERIC, "fused": _lib.PATH_FUSED,
-          "fused_v1": _lib.PATH_FUSED_V1, "fused_pipe": _lib.PATH_FUSED_PIPE}
+          "fused_pipe": _lib.PATH_FUSED_PIPE}
 _PATH_NAMES = {v: k for k, v in _PATHS.items()}
 _PATH_NAMES[_lib.PATH_STREAM] = "stream"
 _STREAM_MODES = {"auto": _lib.STREAM_AUTO, "fused": _lib.STREAM_FUSED, "gather": _lib.STREAM_GATHER}
@@ -86,9 +86,6 @@ class Int8Net:
     # ---- options / introspection ---------------------------------------------------------------
     def set_path(self, path: str):
         _lib.check(self._L.mibmi_set_option(self._h, _lib.OPT_FORCE_PATH, _PATHS[path]), "set_path")
-
-    def set_ctas_per_sm(self, n: int):
-        _lib.check(self._L.mibmi_set_option(self._h, _lib.OPT_CTAS_PER_SM, int(n)), "set_ctas_per_sm")
 
     def set_host_chunk(self, n: int):
         _lib.check(self._L.mibmi_set_option(self._h, _lib.OPT_HOST_CHUNK, int(n)), "set_host_chunk")

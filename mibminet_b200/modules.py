@@ -55,11 +55,16 @@ class edgeEEGNet(nn.Module):
         super().__init__()
         if F2 is None:
             F2 = F1 * D
-        # constraints of the integer tool-chain (golden_model.py:61-83)
+        # constraints of the integer tool-chain (golden_model.py:61-83): the reference's own defaults (floorToZero=False,
+        # Nf=128) describe nets its integer deployment cannot run either, so they are refused here, at construction
         if weightInqNumLevels != 255 or actSTENumLevels != 255:
             raise ValueError("the integer pipeline exists for 255 levels only (golden_model.py:61-62)")
-        if F2 != F1 * D:
-            raise ValueError("F2 must equal F1 * D (golden_model.py:83)")
+        if not floorToZero:
+            raise ValueError("the integer pipeline needs floorToZero=True (golden_model.py:65): truncating activations")
+        if F2 != F1 * D or D != 1:
+            raise ValueError("F2 must equal F1 * D with D == 1 (golden_model.py:83,169)")
+        if Nf != NF:
+            raise ValueError("the integer tool-chain only supports Nf == 64 (golden_model.py:216-219); pass Nf=64")
         self.F1, self.D, self.F2, self.C, self.T, self.N, self.Nf = F1, D, F2, C, T, N, Nf
         self.reorder_bn = reorder_bn
         n_features = (T // 8) // 8
@@ -78,9 +83,11 @@ class edgeEEGNet(nn.Module):
         self.fc = _InqParam((N, F2 * n_features), bias=N)
         self.quant6 = _Quant()
         self._engine: Optional[Int8Net] = None
+        self._engine_key = None
         self.eval()
 
-    # any parameter change invalidates the packed integer network
+    # any parameter change invalidates the packed integer network: load_state_dict / .to() / .cuda() directly, in-place
+    # edits of parameters or buffers (quant1.absMaxValue.fill_(...)) through the tensors' version counters
     def load_state_dict(self, state_dict, strict: bool = True, **kw):
         sd = {k: (torch.as_tensor(v) if not torch.is_tensor(v) else v) for k, v in state_dict.items()}
         r = super().load_state_dict(sd, strict=strict, **kw)
@@ -91,18 +98,21 @@ class edgeEEGNet(nn.Module):
         self._engine = None
         return super()._apply(fn, *a, **kw)
 
+    def _state_key(self):
+        return tuple((t.data_ptr(), t._version) for t in self.state_dict(keep_vars=True).values())
+
     def integer_network(self, device=None) -> Int8Net:
         """The packed integer network (built lazily from the current state_dict)."""
         dev = torch.device(device) if device is not None else self.quant1.absMaxValue.device
         if dev.type != "cuda":
             raise RuntimeError("edgeEEGNet (mibminet_b200) runs on CUDA only: call .cuda() first")
         idx = dev.index if dev.index is not None else torch.cuda.current_device()
-        if self._engine is None or self._engine.device_index != idx:
-            if self.Nf != NF:
-                raise ValueError("the integer tool-chain only supports Nf == 64 (golden_model.py:216-219)")
+        key = self._state_key()
+        if self._engine is None or self._engine.device_index != idx or self._engine_key != key:
             sd = {k: v.detach().cpu().numpy() for k, v in self.state_dict().items()}
             params = params_from_state_dict(sd, C=self.C, T=self.T, F1=self.F1, D=self.D, F2=self.F2, N=self.N)
             self._engine = Int8Net(params, device=torch.device("cuda", idx), reorder_bn=self.reorder_bn)
+            self._engine_key = key
         return self._engine
 
     @torch.no_grad()
@@ -166,6 +176,9 @@ class EEGNet(nn.Module):
         self.fc = _InqParam((N, F2 * n_features), bias=N)
         self.quant6 = _Quant()
         self._engine: Optional[EEGNetInt8] = None
+        self._engine_key = None
+        if not floorToZero:
+            raise ValueError("the integer pipeline needs floorToZero=True: truncating activations")
         self.eval()
 
     def load_state_dict(self, state_dict, strict: bool = True, **kw):
@@ -183,10 +196,12 @@ class EEGNet(nn.Module):
         if dev.type != "cuda":
             raise RuntimeError("EEGNet (mibminet_b200) runs on CUDA only: call .cuda() first")
         idx = dev.index if dev.index is not None else torch.cuda.current_device()
-        if self._engine is None or self._engine.device_index != idx:
+        key = tuple((t.data_ptr(), t._version) for t in self.state_dict(keep_vars=True).values())
+        if self._engine is None or self._engine.device_index != idx or self._engine_key != key:
             sd = {k: v.detach().cpu().numpy() for k, v in self.state_dict().items()}
             self._engine = EEGNetInt8.from_state_dict(sd, C=self.C, T=self.T, F1=self.F1, D=self.D, F2=self.F2, N=self.N,
                                                       device=torch.device("cuda", idx))
+            self._engine_key = key
         return self._engine
 
     @torch.no_grad()

@@ -95,7 +95,9 @@ def integer_verification(net: Int8Net, x_float: np.ndarray) -> Dict[str, np.ndar
     x_int = quantize_to_int(x_float, p.input_scale).astype(np.int8)
     got = gpu_taps(net, x_int)
     deq = lambda a, q: _dequantize_exact(a, p.scales[q])
-    out = {"input": x_float, "input_quant": deq(x_int, "quant1").reshape(1, 1, p.C, p.T)}
+    # 'input' keeps the leading dimension of the dataset sample export_net_data.py:109,116 stores (the reference's tests
+    # index ["input"][0, :, :], test/cl/net/model/testcase.py:55)
+    out = {"input": x_float.reshape(1, p.C, p.T), "input_quant": deq(x_int, "quant1").reshape(1, 1, p.C, p.T)}
     for name, key, q in ACTIV_TAPS:
         a = deq(got[key], q)
         out[name] = a.reshape(1, p.N) if key == "out" else a.reshape(1, p.F2, 1, -1)

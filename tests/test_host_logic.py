@@ -1,5 +1,5 @@
 """CPU tests of the host-side logic of libmibmi.so: ABI surface, validation, magic-number division,
-the fused-kernel parameter packing (through a lane-level emulation of the kernel), converters."""
+the fused-kernel parameter packing (layout of the tcgen05 operands), converters."""
 import ctypes
 import os
 import re
@@ -9,8 +9,13 @@ import pytest
 
 import golden_np
 from conftest import ROOT, golden_files, load_golden
-from fused_emulator import forward_trial, parse, tdiv_magic
 from mibminet_b200 import _lib, convert, synth
+
+
+def tdiv_magic(x, m, s):
+    """(mulhi32(x, m) >> s) + (x < 0) on int64 arrays: the device-side division of the fused kernels."""
+    x = np.asarray(x, dtype=np.int64)
+    return ((x * int(m)) >> 32 >> int(s)) + (x < 0)
 
 
 def test_library_exports_every_declared_symbol():
@@ -71,34 +76,116 @@ def test_magic_rejects_small_divisors():
         assert _lib.debug_magic(d)[0] == _lib.ERR_PARAM
 
 
-def test_fused_packing_emulation_matches_reference(golden):
+def _clip8(v):
+    return np.clip(v, -128, 127)
+
+
+FAST1_DIVISORS = [4, 5, 6, 7, 8, 9, 15, 16, 17, 31, 32, 33, 63, 64, 65, 127, 128, 129, 255, 256, 257, 1023, 1025, 4095, 4097,
+                  65535, 65536, 65537, (1 << 20) - 1, (1 << 20) + 1, (1 << 24) + 1]
+
+
+@pytest.mark.parametrize("d", FAST1_DIVISORS)
+def test_fast1_division_adversarial(d):
+    """The shift-free layer-1 form (FAST1): clip8(mulhi32(x, m) + (x < 0)) == clip8(trunc(x / d)) on the WHOLE proven range
+    |x| <= xmax, for every xmax the host accepts: every value of the +-131 d window where exactness is needed (sampled with
+    all residues near the multiples of d for large d), and the saturated region up to xmax."""
+    rng = np.random.default_rng(d)
+    m0 = (1 << 32) // d + 1
+    e = m0 * d - (1 << 32)
+    assert 0 < e <= d
+    edge = ((1 << 32) - 1) // e                 # the largest |x| with x e < 2^32
+    bounds = [129 * d + 1, 130 * d, 130 * d + d // 2 + 1, 1000 * d + 7, 128 * 127 * 64 + 4000, (1 << 29) - 1, edge, edge + 1]
+    accepted = 0
+    for xmax in bounds:
+        if xmax >= (1 << 29):
+            continue
+        st, m = _lib.debug_magic32(d, xmax)
+        if st != 0:
+            assert st == _lib.ERR_UNSUPPORTED
+            continue
+        accepted += 1
+        assert m == (1 << 32) // d + 1
+        win = min(xmax, 131 * d + 5)
+        if 2 * win + 1 <= 3_000_000:
+            xs = np.arange(-win, win + 1)
+        else:       # large d: every multiple of d in the window with its neighbours, plus random values
+            k = np.arange(-131, 132)[:, None] * d + np.array([-2, -1, 0, 1, 2, d - 2, d - 1, d // 2])[None]
+            xs = np.concatenate([k.ravel(), rng.integers(-win, win + 1, 200000)])
+            xs = xs[np.abs(xs) <= win]
+        far = np.concatenate([rng.integers(-xmax, xmax + 1, 200000), np.array([xmax, -xmax, xmax - 1, -xmax + 1])])
+        xs = np.concatenate([xs, far])
+        got = _clip8(((xs * int(m)) >> 32) + (xs < 0))
+        assert np.array_equal(got, _clip8(golden_np.tdiv(xs, d))), (d, xmax)
+        assert xmax <= edge or 130 * d <= edge, "accepted although exactness is not proven on the window"
+    assert accepted >= 1 or edge >= (1 << 29)
+    if edge + 1 < min(130 * d, 1 << 29):         # just beyond the proof: must be refused
+        assert _lib.debug_magic32(d, edge + 1)[0] == _lib.ERR_UNSUPPORTED
+
+
+def test_fast1_rejects_what_it_cannot_prove():
+    """e = m d - 2^32 close to d and a wide accumulator range: the host must fall back to the shifted form."""
+    assert _lib.debug_magic32(3, 100)[0] == _lib.ERR_UNSUPPORTED                # d < 4
+    # d = 2^16 + 1: m = 65536, e = m d - 2^32 = 65536; exact only while |x| e < 2^32, i.e. |x| < 65536 << 130 d
+    st, m = _lib.debug_magic32(65537, 10_000_000)
+    assert st == _lib.ERR_UNSUPPORTED
+    st, m = _lib.debug_magic32(65537, 65535)
+    assert st == 0 and m == 65536
+    # boundary of the strict inequality: x e == 2^32 must be refused.  d = 2^26: m = 65, e = 2^26; x = 64 gives x e == 2^32
+    assert _lib.debug_magic32(1 << 26, 63)[0] == 0
+    assert _lib.debug_magic32(1 << 26, 64)[0] == _lib.ERR_UNSUPPORTED
+
+
+def _pipe_blob(arrays, C, T, **kw):
+    blob, why = _lib.debug_pack_pipe(arrays, C, T, **kw)
+    return (None if blob is None else np.frombuffer(blob, np.uint8)), why
+
+
+# byte offsets inside PipeNet (mibmi_common.cuh): w1blk 4*2*32 words, off1 / m1 / sh1 16 ints each, fast1 + 3 pad, w1umma
+_OFF_OFF1 = 4 * 2 * 32 * 4
+_OFF_W1UMMA = _OFF_OFF1 + 3 * 64 + 16
+_OFF_W2UMMA = _OFF_W1UMMA + 16 * 64
+
+
+def test_fused_packing_tcgen05_operands(golden):
+    """The operands the tcgen05 kernels read (PipeNet::w1umma / w2umma) against the exported arrays: layer 1 = W1 with the
+    factor sign folded in, as K-major 8 x 16-byte core matrices; layer 2 = the Toeplitz matrix B[n][kk] = tap (kk - n - 1)."""
     fx = golden
-    blob, why = _lib.debug_pack_fused(fx["arrays"], fx["C"], fx["T"])
-    if fx["T"] % 16:
-        assert blob is None and "instantiation" in why
+    C, T = fx["C"], fx["T"]
+    blob, why = _pipe_blob(fx["arrays"], C, T)
+    if blob is None:
+        assert "instantiation" in why, why
         return
-    assert blob is not None, why
-    net = parse(blob)
-    n = 2 if fx["C"] > 32 else 1
-    for i in range(n):
-        out, taps = forward_trial(net, fx["C"], fx["T"], fx["x"][i])
-        for name in ("y1", "y2", "y3", "y4"):
-            assert np.array_equal(taps[name], fx[f"golden_reorder_{name}"][i]), name
-        assert np.array_equal(out, fx["golden_reorder"][i])
+    CA, kpad = convert.align4(C), (C + 31) // 32 * 32
+    w1 = np.asarray(fx["arrays"]["l1_weight_align"]).reshape(16, CA).astype(np.int64)
+    sg = np.where(np.asarray(fx["arrays"]["l1_factor"]) < 0, -1, 1)
+    u1 = blob[_OFF_W1UMMA:_OFF_W1UMMA + 16 * 64].view(np.int8)
+    for n in range(16):
+        for c in range(min(C, 64)):
+            assert u1[(n >> 3) * (kpad // 16) * 128 + (c >> 4) * 128 + (n & 7) * 16 + (c & 15)] == sg[n] * w1[n, c], (n, c)
+    w2 = np.asarray(fx["arrays"]["l2_weight_reverse"]).reshape(16, 64)
+    u2 = blob[_OFF_W2UMMA:_OFF_W2UMMA + 16 * 1536].view(np.int8).reshape(16, 1536)
+    n, kk = np.meshgrid(np.arange(16), np.arange(96), indexing="ij")
+    tap = kk - n - 1
+    for k in range(16):
+        exp = np.where((tap >= 0) & (tap < 64), w2[k][np.clip(tap, 0, 63)], 0)
+        got = u2[k][(n >> 3) * 768 + (kk >> 4) * 128 + (n & 7) * 16 + (kk & 15)]
+        assert np.array_equal(got, exp), k
+    off1 = blob[_OFF_OFF1:_OFF_OFF1 + 64].view(np.int32)
+    assert np.array_equal(off1, sg * np.asarray(fx["arrays"]["l1_offset"]))
 
 
 def test_fused_packing_refuses_what_it_cannot_run():
     fx = load_golden(golden_files()[0])
-    assert _lib.debug_pack_fused(fx["arrays"], fx["C"], fx["T"], reorder_bn=False)[0] is None
+    assert _pipe_blob(fx["arrays"], fx["C"], fx["T"], reorder_bn=False)[0] is None
     a = dict(fx["arrays"])
     a["l1_factor"] = a["l1_factor"].copy()
     a["l1_factor"][0] = 3
-    blob, why = _lib.debug_pack_fused(a, fx["C"], fx["T"])
+    blob, why = _pipe_blob(a, fx["C"], fx["T"])
     assert blob is None and "l1_factor" in why
     a = dict(fx["arrays"])
     a["l1_offset"] = a["l1_offset"].copy()
     a["l1_offset"][5] = 2 ** 30
-    blob, why = _lib.debug_pack_fused(a, fx["C"], fx["T"])
+    blob, why = _pipe_blob(a, fx["C"], fx["T"])
     assert blob is None and "range" in why
 
 

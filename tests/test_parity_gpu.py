@@ -266,16 +266,127 @@ def test_quantize_input_vector_body_and_tails(n, skip):
 
 def test_errors_are_reported_not_printed():
     C, T = 64, 480
-    net, _ = _net(C, T, seed=1)
+    net, arrays = _net(C, T, seed=1)
     with pytest.raises(ValueError):
         net.forward(torch.zeros((2, C, T + 1), dtype=torch.int8, device="cuda:0"))
     with pytest.raises(TypeError):
         net.forward(torch.zeros((2, C, T), dtype=torch.float32, device="cuda:0"))
-    x = torch.zeros((2 * C * T + 1,), dtype=torch.int8, device="cuda:0")[1:].view(2, C, T)   # misaligned
+    # a pointer that is not 16-byte aligned: the exact generic kernel (no alignment requirement) under AUTO, MIBMI_ERR_ALIGN
+    # when a fused path is forced
+    xs = synth.make_trials(2, C, T, seed=3)
+    buf = torch.zeros((2 * C * T + 1,), dtype=torch.int8, device="cuda:0")
+    buf[1:] = torch.from_numpy(xs).cuda().flatten()
+    x = buf[1:].view(2, C, T)
+    assert x.data_ptr() % 16 != 0
+    assert np.array_equal(net.forward(x).cpu().numpy(), wolf_port.forward(arrays, C, T, xs))
+    assert net.last_path == "generic" and net.last_kernel == "generic_forward_kernel"
     from mibminet_b200._lib import MibmiError, ERR_ALIGN
+    net.set_path("fused")
     with pytest.raises(MibmiError) as ei:
         net.forward(x)
     assert ei.value.status == ERR_ALIGN
+
+
+def test_sub_batch_views_of_unaligned_trials_run_exactly():
+    """22 x 1125 / 19 x 480: a trial is not a multiple of 16 bytes, so x[1:] is a contiguous view at an odd address:
+    it must work (generic kernel under AUTO), and 16-byte-aligned views stay on the fused kernel."""
+    for C, T in ((22, 1125), (19, 480)):
+        net, arrays = _net(C, T, seed=9)
+        x = synth.make_trials(40, C, T, seed=10)
+        ref = wolf_port.forward(arrays, C, T, x)
+        xd = _cuda(x)
+        for lo in (1, 3, 8, 16):
+            v = xd[lo:]
+            y = net.forward(v).cpu().numpy()
+            assert np.array_equal(y, ref[lo:]), (C, T, lo)
+            assert net.last_path == ("fused" if v.data_ptr() % 16 == 0 else "generic"), (C, T, lo)
+
+
+@pytest.mark.parametrize("C,T", [(22, 1125), (38, 480), (64, 480)])
+def test_host_entry_point_both_layouts_on_one_handle(C, T):
+    """The staging buffers of mibmi_forward_int8_host are sized per call: module order (C * T bytes per trial) first, then Wolf
+    order (T * align4(C) bytes per trial, larger for C % 4 != 0) on the same handle, and back."""
+    net, arrays = _net(C, T, seed=12)
+    net.set_host_chunk(256)
+    B = 700
+    x = synth.make_trials(B, C, T, seed=13)
+    ref = wolf_port.forward(arrays, C, T, x)
+    xw = convert.to_wolf_input(x)
+    assert np.array_equal(net.forward_host(x, layout="bct").numpy(), ref)
+    assert np.array_equal(net.forward_host(xw, layout="btc").numpy(), ref)
+    assert np.array_equal(net.forward_host(x, layout="bct").numpy(), ref)
+    net.set_host_chunk(512)                                   # larger chunk: reallocation by trial count
+    assert np.array_equal(net.forward_host(torch.from_numpy(xw).pin_memory(), layout="btc").numpy(), ref)
+
+
+@pytest.mark.parametrize("C,T", [(38, 480), (22, 1125)])
+def test_wolf_order_calls_on_concurrent_streams(C, T, monkeypatch):
+    """Wolf-order calls of ONE handle on different streams at the same time: scratch memory belongs to the call (allocated in
+    stream order), so the results cannot mix."""
+    monkeypatch.setenv("MIBMI_WOLF_CHUNK", "64")
+    net, arrays = _net(C, T, seed=14)
+    xs = [synth.make_trials(500, C, T, seed=20 + i) for i in range(3)]
+    refs = [wolf_port.forward(arrays, C, T, x) for x in xs]
+    xd = [_cuda(convert.to_wolf_input(x)) for x in xs]
+    outs = [torch.empty((500, 4), dtype=torch.int8, device="cuda:0") for _ in xs]
+    streams = [torch.cuda.Stream() for _ in xs]
+    torch.cuda.synchronize()
+    for rep in range(3):
+        for st, x, o in zip(streams, xd, outs):
+            with torch.cuda.stream(st):
+                net.forward(x, layout="btc", out=o)
+    torch.cuda.synchronize()
+    for o, r in zip(outs, refs):
+        assert np.array_equal(o.cpu().numpy(), r)
+
+
+def _adversarial_arrays(C, T, seed):
+    """Exported arrays (gen_net_header.py layout) built to stress the requantisation: layer-1 factors just above the smallest
+    divisor the fused path takes and at 2^k +- 1, both signs; offsets that push |acc + off| to the bound the host proves
+    (128 * sum|w| + |off|); weights with small integer steps so that the accumulator visits every residue modulo the factor."""
+    rng = np.random.default_rng(seed)
+    base = convert.params_from_state_dict(synth.make_state_dict(C=C, T=T, seed=seed), C=C, T=T).to_wolf_arrays()
+    a = {k: np.array(v, copy=True) for k, v in base.items()}
+    CA = convert.align4(C)
+    facs = np.array([4, -5, 7, -8, 9, 15, -16, 17, 31, -33, 63, 65, -127, 129, 255, -257], np.int32)
+    w1 = np.zeros((16, CA), np.int8)
+    for k in range(16):
+        w1[k, :C] = rng.integers(-2, 3, C)                   # small steps: every residue is reached
+        w1[k, rng.integers(0, C)] = 1
+        if k % 3 == 0:
+            w1[k, :C] = rng.integers(-127, 128, C)           # and full-range rows that saturate
+    a["l1_weight_align"] = w1.ravel()
+    a["l1_factor"] = facs
+    off = np.array([0, 3, -2, 1000, -1000, 7, 129 * 16, -130 * 17, 12345, -54321, 1, -1, 20000, -20000, 99, -77], np.int32)
+    a["l1_offset"] = off
+    a["l2_factor"] = np.where(np.arange(16) % 2 == 0, 1, -1).astype(np.int32) * np.array(
+        [8, 9, 15, 17, 31, 33, 63, 65, 127, 129, 255, 257, 511, 513, 4097, 65537], np.int32) * 8
+    a["l3_factor"] = np.int32(-5)
+    a["l4_factor"] = (np.array([4, 5, 7, 9, 15, 17, 31, 33, 63, 65, 127, 129, 255, 257, 1023, 1025], np.int32) *
+                      np.where(np.arange(16) % 3 == 0, -1, 1)).astype(np.int32)
+    a["l5_factor"] = np.int32(-337)
+    return a
+
+
+@pytest.mark.parametrize("C,T", [(64, 480), (22, 1125), (8, 480)])
+def test_adversarial_requantisation_parameters(C, T):
+    """Factors at 4, 5, 2^k +- 1 with both signs, large offsets, saturating and small-step weights: fused kernels == oracle."""
+    for seed in (1, 2):
+        arrays = _adversarial_arrays(C, T, seed)
+        net = Int8Net(arrays, C=C, T=T, device="cuda:0")
+        ok, why = net.fused_supported()
+        assert ok, why
+        x = np.concatenate([synth.make_trials(300, C, T, seed=seed), synth.make_trials(100, C, T, seed=seed + 1, dist="gauss"),
+                            np.stack([np.full((C, T), v, np.int8) for v in (127, -127, -128, 0, 1, -1)])])
+        ref, lay = wolf_port.forward(arrays, C, T, x, return_layers=True)
+        y = net.forward(_cuda(x)).cpu().numpy()
+        assert net.last_path == "fused"
+        assert np.array_equal(y, ref)
+        net.set_path("fused")
+        _, taps = net.forward_taps(_cuda(x[:64]))
+        for name in ("y1", "y2", "y3", "y4"):
+            assert np.array_equal(taps[name].cpu().numpy(), lay[name][:64]), name
+        assert (np.abs(lay["y1"].astype(int)) >= 127).any() and (np.abs(lay["y1"].astype(int)) < 100).any()
 
 
 # ---- sliding-window streaming (BASELINE config 5) -------------------------------------------------------
