@@ -16,6 +16,8 @@ buffer over NVLink (fused gather; one NCCL all_gather per step is the fallback).
   roofline  fused kernel: algorithmic bytes (30 724 B/trial) / kernel time vs MEASURED_PEAKS.json
   cpu_baseline  the reference's C model (oracle/_ref, built from /root/reference sources) on the
             host cores, bounded sample, outputs cross-checked against the GPU logits
+  sustained the same step held for >= 2 s back to back (the board's power cap, not the burst clock, decides there)
+  --workload config1   BASELINE config 1: batch-1 latency of the reference's CPU implementations beside the GPU's
 """
 import argparse
 import json
@@ -61,15 +63,18 @@ def parse_args():
     ap.add_argument("--float-input", action="store_true",
                     help="trials workload: float32 trials in HBM -> quantise (a13) -> int8 forward -> float32 logits "
                          "(SURVEY 8(f)2; 4x the input bytes, reported separately)")
-    ap.add_argument("--workload", default="trials", choices=["trials", "stream", "eegnet"],
+    ap.add_argument("--workload", default="trials", choices=["trials", "stream", "eegnet", "config1"],
                     help="trials: BASELINE config 2 (default, the headline line); stream: config 5, sliding windows "
                          "(480 samples, stride 16) over continuous 64-ch recordings; eegnet: the EEGNet / Q-EEGNet layer "
                          "order (SURVEY 8(f)4, temporal conv first, F1 = 8, D = 2, Nf = 128), default shape 22x1125")
     ap.add_argument("--subjects", type=int, default=4096, help="stream workload: subjects per GPU")
     ap.add_argument("--stream-len", type=int, default=9600, help="stream workload: samples per subject (60 s at 160 Hz)")
     ap.add_argument("--stream-mode", default="auto", choices=["auto", "fused", "gather"])
-    ap.add_argument("--gather", default="auto", choices=["auto", "peer", "nccl"],
-                    help="multi-GPU logits gather: fused peer stores (symmetric memory) or NCCL all_gather per step")
+    ap.add_argument("--gather", default="auto", choices=["auto", "peer", "root", "nccl", "none"],
+                    help="multi-GPU logits gather: auto / peer = fused peer stores into EVERY rank's symmetric buffer (all-gather); "
+                         "root = fused peer stores into rank 0's buffer only (a gather, what north_star asks for); nccl = one NCCL "
+                         "all_gather per step; none = no gather at all (isolates the cost of the remote stores)")
+    ap.add_argument("--sustained-seconds", type=float, default=2.0, help="length of the sustained block (0 = skip)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
@@ -167,12 +172,27 @@ def measured_peaks():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def make_config(args, world, B):
+    """The workload description shared by BOTH arms (ours / --impl reference): static facts only, so that the driver's
+    same_config check compares like with like; what a particular run did (kernel path, checks) lives outside `config`."""
+    return {"workload": WORKLOAD, "trials_per_gpu_per_step": B, "global_batch": world * B,
+            "layout": "[B][C][T] int8 (module order)" if args.layout == "bct" else
+                      "[B][T][C_ALIGN] int8 (Wolf order of net_model_compute, gen_input_header.py:75-76)",
+            "parallelism": f"trial-batch sharding x{world}",
+            "l2_policy": f"input per step {B * C * T / 1e9:.2f} GB > 126 MB L2, no flush needed",
+            "collective": "none" if world == 1 else f"logits gather mode '{args.gather}' (bench.py --gather)",
+            "input": "float32 trials (quantise -> int8 forward -> dequantise)" if args.float_input else "int8"}
+
+
 def main_reference(args, rank):
+    """The reference's own CPU implementation of the path (edge-eegnet_wolf/src/cl compiled for the host, oracle/_ref; the
+    oracle C port when the binary is absent) on all host cores.  A step = a bounded sample of the batch the repo arm runs."""
     if rank != 0:
         return
     import numpy as np
     from mibminet_b200 import synth
     cores = host_cores()
+    world = int(os.environ.get("WORLD_SIZE", "1"))
     per_core = 192
     x = synth.make_trials(per_core * cores, C, T, seed=1234)
     vals = []
@@ -181,16 +201,98 @@ def main_reference(args, rank):
         if i >= args.warmup:
             vals.append(tps)
     v = float(np.mean(vals))
-    sample = f"{len(x)} trials x 2 repeats per step over {cores} worker processes"
-    print(json.dumps({
+    one, _, _ = cpu_reference_run(x[:per_core], repeat=2, cores=1)                   # one core
+    sample = (f"{len(x)} of the {args.batch} trials of a step x 2 repeats, {cores} worker processes; "
+              f"{'reference C (edge-eegnet_wolf/src/cl, gcc -O2, Makefile-default flags) compiled for the host' if kind == 'reference' else 'oracle C port'}")
+    out = {
         "impl": "reference", "metric": METRIC, "value": v, "unit": "trials/s", "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * len(x) * 2 / v, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "int8", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "impl": "reference C model (edge-eegnet_wolf/src/cl) compiled for the host"
-                   if kind == "reference" else "oracle C port", "sample": sample},
-        "cpu_baseline": {"value": v, "unit": "trials/s", "cores": cores, "kind": kind, "sample": sample},
+        "config": make_config(args, world, args.batch),
+        "cpu_baseline": {"value": v, "unit": "trials/s", "cores": cores, "kind": kind, "sample": sample,
+                         "one_core_trials_per_s": one},
         "e2e": {"value": v, "unit": "trials/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "gpu_launches": 0}))
+        "gpu_launches": 0}
+    exe3 = ref_exe_o3()
+    if exe3 is not None and kind == "reference":
+        _, build_ref = _ref_exe()
+        _, tim = build_ref.run(exe3, x, procs=cores, repeat=2)
+        out["cpu_baseline"]["O3_march_native_trials_per_s"] = tim["trials_per_s"]
+    print(json.dumps(out))
+
+
+def ref_exe_o3():
+    """The same reference sources built with -O3 (and -march=native where the binary was built on this CPU type): reported
+    beside the -O2 figure of the reference's own recipe so that the CPU side cannot be said to be sandbagged."""
+    _, build_ref = _ref_exe()
+    exe = os.path.join(build_ref.OUT, build_ref.tag_for(C, T, NET_SEED), "ref_model_default_o3")
+    return exe if os.path.exists(exe) else None
+
+
+def main_config1(args):
+    """BASELINE config 1: batch 1 on the CPU -- the reference C at ONE core, edgeEEGNetQuant after
+    tq.convert on qnnpack (1 thread and default threads), the Python golden model -- beside the GPU's batch-1 latency."""
+    import numpy as np
+    import torch
+    from mibminet_b200 import convert, synth
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    res = {"metric": "int8 edgeEEGNet batch-1 latency", "unit": "ms/trial", "higher_is_better": False, "n_gpus": 1,
+           "dtype": "int8", "data": "synthetic", "vs_baseline": None,
+           "config": {"workload": "BASELINE config 1: edgeEEGNet 64ch x 480 samples, 4 classes, batch 1"}}
+    x = synth.make_trials(256, C, T, seed=1234)
+    tps, kind, y_ref = cpu_reference_run(x, repeat=2, cores=1)
+    res["reference_c_one_core"] = {"ms_per_trial": 1e3 / tps, "kind": kind,
+                                   "what": "net_model_compute (model.c:42), gcc -O2, Makefile-default flags, 1 process"}
+    exe3 = ref_exe_o3()
+    if exe3 is not None:
+        _, build_ref = _ref_exe()
+        _, tim = build_ref.run(exe3, x, procs=1, repeat=2)
+        res["reference_c_one_core"]["ms_per_trial_O3"] = 1e3 / tim["trials_per_s"]
+    import golden_np
+    params = convert.params_from_state_dict(synth.make_state_dict(C=C, T=T, seed=NET_SEED), C=C, T=T)
+    arrays = params.to_wolf_arrays()
+    t0 = time.perf_counter()
+    for i in range(20):
+        golden_np.forward(arrays, C, T, x[i:i + 1])
+    res["python_golden_port"] = {"ms_per_trial": 1e3 * (time.perf_counter() - t0) / 20,
+                                 "what": "oracle/golden_np.py (NumPy restatement of golden_model.py:104-107), one trial per call"}
+    try:
+        import qnnpack_quant
+        for th, name in ((1, "threads_1"), (0, "threads_default")):
+            ms, n = qnnpack_quant.time_batch1(C, T, threads=th, seconds=2.0)
+            res.setdefault("edgeeegnetquant_qnnpack", {"what": "edge-eegnet_torch/edgeEEGnet_quant.py:14-107 restated (oracle/"
+                                                               "qnnpack_quant.py), prepare_qat -> convert, engine qnnpack, batch 1"})[name] = ms
+    except Exception as e:      # noqa: BLE001 -- the quantized backend may be missing on a box
+        res["edgeeegnetquant_qnnpack"] = {"unavailable": str(e)[:200]}
+    if torch.cuda.is_available():
+        from mibminet_b200.engine import Int8Net
+        net = Int8Net(params, device="cuda:0")
+        xd = torch.from_numpy(x).cuda()
+        out = torch.empty((1, N_CLASSES), dtype=torch.int8, device="cuda:0")
+        for _ in range(20):
+            net.forward(xd[:1], out=out)
+        torch.cuda.synchronize()
+        n = 2000
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(n):
+            net.forward(xd[:1], out=out)
+        e1.record()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(200):
+            net.forward(xd[:1], out=out)
+            torch.cuda.synchronize()
+        res["gpu_batch1"] = {"device_ms_per_call": e0.elapsed_time(e1) / n, "kernel": net.last_kernel,
+                             "host_round_trip_ms": 1e3 * (time.perf_counter() - t0) / 200,
+                             "matches_reference_c": bool(np.array_equal(net.forward(xd).cpu().numpy(), y_ref))}
+        res["value"] = res["gpu_batch1"]["device_ms_per_call"]
+        res["gpu_launches"] = 2000
+    else:
+        res["value"] = None
+    res["cpu_baseline"] = {"value": res["reference_c_one_core"]["ms_per_trial"], "unit": "ms/trial", "cores": 1, "kind": kind,
+                           "sample": "256 trials x 2 repeats, one process"}
+    print(json.dumps(res))
 
 
 def main_stream(args, rank, local_rank, world):
@@ -346,6 +448,8 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     if args.impl == "reference":
         return main_reference(args, rank)
+    if args.workload == "config1":
+        return main_config1(args) if rank == 0 else None
     if args.workload == "stream":
         return main_stream(args, rank, local_rank, world)
     if args.workload == "eegnet":

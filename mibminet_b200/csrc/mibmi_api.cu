@@ -192,6 +192,12 @@ bool pack_pipe(const mibmi_params_t* p, PipeNet* f, const char** why) {
                 f->w2umma[k * 1536 + (n >> 3) * 768 + (kk >> 4) * 128 + (n & 7) * 16 + (kk & 15)] =
                     (tap >= 0 && tap < 64) ? (uint8_t)w[tap] : 0;
             }
+        for (int n = 0; n < 32; n++)        // N = 32, reversed outputs, overlapping core matrices (equal values where they overlap)
+            for (int kk = 0; kk < 96; kk++) {
+                const int tap = kk + n - 32;
+                f->w2umma32[k * kW2U32 + (n >> 3) * 128 + (kk >> 4) * 256 + (n & 7) * 16 + (kk & 15)] =
+                    (tap >= 0 && tap < 64) ? (uint8_t)w[tap] : 0;
+            }
         for (int v = 0; v < 4; v++)
             for (int s = 0; s < 3; s++)
                 for (int h = 0; h < 2; h++)

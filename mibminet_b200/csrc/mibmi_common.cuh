@@ -40,6 +40,7 @@ struct GenericNet {
 //   tdiv(x, d) == (mulhi(x, magic) >> shift) + (x < 0)      for |x| < 2^29, d >= 4
 constexpr int kPipeMaxKB16 = 4;     // layer-1 blocks of 16 channels (C <= 64)
 constexpr int kPipeMaxKst5 = 16;    // layer-5 k-steps of 32 (T/64 padded to even <= 32)
+constexpr int kW2U32 = 1792;        // bytes per channel of PipeNet::w2umma32
 
 struct PipeNet {
     // layer 1: W1 as MMA B fragments per 16-channel block: [block][filter n-tile (0-7, 8-15)][lane]
@@ -66,6 +67,11 @@ struct PipeNet {
     uint32_t w5frag[kPipeMaxKst5][2][32];
     int b5[4];
     int m5, sh5, pad2_[2];
+    // layer 2 for tcgen05.mma with N = 32 outputs per row (mibmi_tcr.cu): Toeplitz operand with REVERSED output order,
+    // B'[n'][kk] = tap (kk + n' - 32) of the 64 taps (column n' = output 31 - n' of the row), n' < 32, kk < 96.  Reversal makes
+    // B'[n' + 16][kk - 16] == B'[n'][kk], so the 8 x 16-byte core matrices may overlap: byte (n' >> 3) * 128 + (kk >> 4) * 256 +
+    // (n' & 7) * 16 + (kk & 15) (descriptor LBO = 256 B, SBO = 128 B), 1792 bytes per channel instead of 3072
+    alignas(16) uint8_t w2umma32[16 * kW2U32];
 };
 static_assert(sizeof(PipeNet) % 16 == 0, "PipeNet alignment");
 

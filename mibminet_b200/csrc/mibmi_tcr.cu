@@ -1,17 +1,24 @@
 // tcgen05 / TMEM forward for trials whose rows are NOT 16-byte aligned and whose length is not a multiple of 32
-// (22 x 1125, BASELINE config 3).  Same tensor-core formulation as mibmi_tc.cu (layer 1 = MN-major swizzled tile x W1,
-// layer 2 = Hankel view of the y1 byte array x Toeplitz taps, accumulators in TMEM), with three differences:
+// (22 x 1125, BASELINE config 3).  Same tensor-core formulation as mibmi_tc.cu (layer 1 = tile x W1, layer 2 = Hankel view of
+// the y1 byte array x Toeplitz taps, accumulators in TMEM), with these differences:
 //   * a trial starts at an arbitrary byte, so TMA tiles are impossible: the producer bulk-copies the trial from the
-//     16-byte boundary below it into a raw stage and four REALIGN warps funnel-shift it into the 128-byte-swizzled tile
-//     layout the MMA reads (what the TMA unit does for aligned shapes);
-//   * a trial occupies 73 rows (16 bytes each) of the y1 row buffer, so the 128-row MMA tiles straddle trials: groups of
-//     G = 3 trials = 219 rows = 2 tiles; the layer-2 epilogue maps TMEM lane -> (trial, block of 16 outputs);
+//     16-byte boundary below it into a raw stage and four REALIGN warps build the layer-1 operand tiles:
+//       WOLF = 0  x [B][C][T] (module order): every row is funnel-shifted into the 128-byte-swizzled MN-major tile layout the TMA
+//                 unit would have produced;
+//       WOLF = 1  x [B][T][C_ALIGN] (the order net_model_compute receives, gen_input_header.py:75-76): a sample is 24 contiguous
+//                 bytes (8-byte aligned) = already K-major for layer 1; the warps only expand it to two 16-byte chunks (channels
+//                 0-15, 16-31) of a no-swizzle K-major tile -- no shifts, no scratch, no second pass over HBM;
+//   * layer 2 computes N = 32 outputs per MMA row: the y1 buffer is read with a row pitch of 32 bytes through a K-major
+//     SWIZZLE_32B descriptor (the bytes are stored where the absolute-address XOR of that mode puts them; k-step ks = start + 32 ks,
+//     i.e. "the next row": the Hankel view) against a Toeplitz operand with reversed output order whose core matrices overlap
+//     (PipeNet::w2umma32; both verified on the box with tools/probe_umma3.cu).  A trial takes 37 rows, a group of G = 3 trials
+//     = 111 rows = ONE tile of 128 rows: 16 channels x 3 k-steps = 48 instructions per group (96 with N = 16);
 //   * layers 3-5 of a trial run in ONE warp (private y3 / y4), as T/8 = 140 needs 9 blocks of 16 samples.
 // One persistent CTA per SM, 31 warps:
 //   A  0-11  layer-1 epilogue (3 warps per TMEM lane quarter)      layer1.c:96-104
 //   B 12-19  layer-2 epilogue (2 warps per lane quarter)           layer2.c:99-118
 //   C 20-23  layers 3 + 4 + 5 of one trial each                    layer3.c:70, layer4.c:99-140, layer5.c:81-89
-//   R 24-27  realign raw bytes -> swizzled tiles                   (rt_dma_memcpy L2 -> L1, layer1.c:137-154)
+//   R 24-27  raw bytes -> layer-1 operand tiles                    (rt_dma_memcpy L2 -> L1, layer1.c:137-154)
 //   P 28     bulk-copy producer     M1 29  layer-1 MMAs (layer1.c:87-96)     M2 30  layer-2 MMAs (layer2.c:87-118)
 // Bit-identical to the reference (tests/test_parity_gpu.py).
 #include <cuda.h>
@@ -30,7 +37,7 @@ namespace mibmi {
 #define MIBMI_TCR_SLEEP_LONG_NS 128       // waits with a trial's worth of slack (producer, M1, free-buffer waits)
 #endif
 #ifndef MIBMI_TCR_WAIT
-#define MIBMI_TCR_WAIT 0                  // mbar_wait_mode: 0 = test_wait + nanosleep, 1 = test_wait then try_wait, 2 = try_wait
+#define MIBMI_TCR_WAIT 1                  // mbar_wait_mode: 0 = test_wait + nanosleep, 1 = test_wait then try_wait (r2a: +3 %), 2 = try_wait
 #endif
 #ifdef MIBMI_PROF
 __device__ long long g_prof_tcr[148 * 32 * 4];
@@ -61,31 +68,38 @@ constexpr int kRWarpB = kRAW, kRWarpC = kRAW + kRBW, kRWarpR = kRWarpC + kRCW, k
               kRWarpM1 = kRWarpP + 1, kRWarpM2 = kRWarpP + 2;
 constexpr int kRThreads = (kRWarpM2 + 1) * 32;
 
-template <int C_, int T_>
+template <int C_, int T_, int WOLF_>
 struct RCfg {
-    static constexpr int C = C_, T = T_, G = 3;
+    static constexpr int C = C_, T = T_, WOLF = WOLF_, G = 3;
+    static constexpr int CA = (C + 3) / 4 * 4;                                  // bytes per sample in Wolf order
+    static constexpr int TRIAL_BYTES = WOLF ? T * CA : C * T;
     static constexpr int TILES = (T + 127) / 128, UNITS = (T + 31) / 32, CHUNKS = (T + 15) / 16;
-    static constexpr int TILE_PITCH = C <= 24 ? 3072 : 4096;                  // rows 24..31 of a tile may alias the next tile (zero weights)
-    static constexpr int XS_BYTES = TILES * TILE_PITCH + (4096 - TILE_PITCH);
-    static constexpr int RAW_BYTES = ((C * T + 15 + 48 + 127) / 128) * 128;      // + misalignment + the realign warps' read-ahead
-    static constexpr int T8 = T / 8, T64 = T8 / 8, VROWS = T8 / 2;            // layer-2 rows (16 conv outputs) per trial
-    static constexpr int SLOT = ((32 + T + 15) / 16) * 16, SROWS = SLOT / 16; // y1 bytes / rows per trial: 32 zeros | T | zeros
-    static constexpr int GROWS = G * SROWS, GT = (GROWS + 127) / 128;
-    static constexpr int CHS = G * SLOT + 96;                                 // y1 row of one filter; / 16 odd
+    // layer-1 operand tiles.  WOLF = 0: MN-major [C][128 samples], 128-byte swizzle, rows 24..31 of a tile may alias the next
+    // tile (zero weights); the whole trial per stage.  WOLF = 1: K-major [2 chunks][128 samples][16 B]; half a trial per stage.
+    static constexpr int TILE_PITCH = WOLF ? 4096 : (C <= 24 ? 3072 : 4096);
+    static constexpr int PARTS = WOLF ? 2 : 1;                                  // hand-offs R -> M1 per trial
+    static constexpr int PART0_TILES = WOLF ? 4 : TILES;                        // tiles of part 0 (part 1: the rest)
+    static constexpr int PART_TILES_MAX = WOLF ? (TILES - 4 > 4 ? TILES - 4 : 4) : TILES;
+    static constexpr int XS_BYTES = ((PART_TILES_MAX * TILE_PITCH + 1023) / 1024) * 1024;
+    static constexpr int RAW_BYTES = ((TRIAL_BYTES + 15 + 48 + 127) / 128) * 128;   // + misalignment + the realign warps' read-ahead
+    static constexpr int T8 = T / 8, T64 = T8 / 8;
+    static constexpr int VROWS = (8 * T8) / 32;                               // layer-2 rows (32 conv outputs) per trial
+    static constexpr int SLOT = ((32 + T + 31) / 32) * 32, SROWS = SLOT / 32;   // y1 bytes / rows per trial: 32 zeros | T | zeros
+    static constexpr int GROWS = G * SROWS;
+    static constexpr int CHS = ((G * SLOT + 15) / 16 | 1) * 16;                 // y1 row of one filter; / 16 odd (stmatrix banks)
     static constexpr int NW3 = (T8 + 15) / 16, Y2S = 16 * (NW3 + 1), Y2_TRIAL = 16 * Y2S;
     static constexpr int Y3CH = 2 * ((NW3 + 1) / 2), Y3S = 16 * (Y3CH + 1), Y3_BYTES = 16 * Y3S;
     static constexpr int NST = (T64 + 3) / 4, T64P = (T64 + 1) / 2 * 2, KST5 = T64P / 2;
     static constexpr int Y4_BYTES = ((16 * T64P + 15) / 16) * 16;
-    static constexpr int W2_CH = 16 * 96;
-    // TMEM columns
+    // TMEM columns: layer-1 accumulators of two trials, then two layer-2 halves of 2 channels x 32 outputs
     static constexpr int TM_L1_TRIAL = 16 * TILES, TM_L2 = 2 * TM_L1_TRIAL, TM_L2_HALF = 64;
     // barriers
     static constexpr int BAR_RAW_FULL = 0, BAR_RAW_EMPTY = 16, BAR_X_FULL = 32, BAR_X_EMPTY = 48, BAR_T1_FULL = 64,
-                         BAR_T1_EMPTY = 80, BAR_Y1_FULL = 96 /* G */, BAR_TILE_DONE = 128 /* GT */, BAR_T2_FULL = 160,
-                         BAR_T2_EMPTY = 176, BAR_Y2_FULL = 192 /* 2 x GT */, BAR_Y2_EMPTY = 232, BAR_END = 248;
+                         BAR_T1_EMPTY = 80, BAR_Y1_FULL = 96 /* G */, BAR_TILE_DONE = 128, BAR_T2_FULL = 160,
+                         BAR_T2_EMPTY = 176, BAR_Y2_FULL = 192 /* 2 */, BAR_Y2_EMPTY = 232, BAR_END = 248;
     // shared memory map
     static constexpr int OFF_TMEM = 248, OFF_C2 = 256, OFF_W1 = 1024, OFF_W2 = 2048;
-    static constexpr int OFF_XS = ((OFF_W2 + 16 * W2_CH + 1023) / 1024) * 1024;
+    static constexpr int OFF_XS = ((OFF_W2 + 16 * kW2U32 + 1023) / 1024) * 1024;
     static constexpr int OFF_RAW = OFF_XS + 2 * XS_BYTES;
     static constexpr int OFF_Y1 = OFF_RAW + 2 * RAW_BYTES;
     static constexpr int OFF_Y2 = OFF_Y1 + 16 * CHS;
@@ -94,23 +108,19 @@ struct RCfg {
     static constexpr int OFF_W3 = ((OFF_Y4 + kRCW * Y4_BYTES + 127) / 128) * 128;      // w3frag [16][4][32] words
     static constexpr int OFF_W5 = OFF_W3 + 16 * 4 * 32 * 4;                             // w5frag [KST5][2][32] words
     static constexpr int SMEM = ((OFF_W5 + KST5 * 2 * 32 * 4 + 127) / 128) * 128;
-    static_assert(C <= 32, "one k-step of 32 channels");
-    static_assert((8 * T8) % 16 == 0 && T8 % 2 == 0, "whole layer-2 rows, sample pairs in layer 3");
-    static_assert(SLOT - 32 - T + 32 >= 8 * T8 + 32 - T, "right padding of layer 2");
+    static_assert(C <= 32 && CA <= 32, "one k-step of 32 channels");
+    static_assert(!WOLF || CA == 24, "Wolf-order expansion is written for rows of 24 bytes");
+    static_assert((8 * T8) % 32 == 0 && T8 % 4 == 0, "whole layer-2 rows of 32 outputs");
+    static_assert(SLOT - 32 - T >= 8 * T8 + 32 - T, "right padding of layer 2 inside the slot");
+    static_assert(GROWS <= 128, "a group is one MMA tile");
     static_assert((CHS / 16) % 2 == 1, "conflict-free stmatrix");
-    static_assert(G <= 4 && GT <= 4 && 2 * GT <= 5, "barrier slots");
+    static_assert(G <= 4, "barrier slots");
     static_assert(TM_L2 + 2 * TM_L2_HALF <= 512, "TMEM map");
     static_assert(NW3 <= 16 && KST5 <= kPipeMaxKst5, "layer 3 / 5 limits");
     static_assert(XS_BYTES % 1024 == 0 && OFF_XS % 1024 == 0, "swizzle atoms are 1024-byte aligned");
     static_assert(SMEM <= 227 * 1024, "shared memory");
-    // last tile that reads bytes of y1 slot j / last tile with valid rows of trial j / last trial with valid rows in tile i
-    __host__ __device__ static constexpr int slot_last_tile(int j) { return (SROWS * (j + 1) - 1) / 128 < GT ? (SROWS * (j + 1) - 1) / 128 : GT - 1; }
-    // last tile that reads the bytes layer-1 tile jt of slot j writes (128 samples + the 16 bytes the last unit may spill; row r reads bytes 16 r .. 16 r + 95)
-    __host__ __device__ static constexpr int unit_last_tile(int j, int jt) {
-        return (SLOT * j + 32 + 128 * jt + 143) / 16 / 128 < GT ? (SLOT * j + 32 + 128 * jt + 143) / 16 / 128 : GT - 1;
-    }
-    __host__ __device__ static constexpr int trial_last_tile(int j) { return (SROWS * j + VROWS - 1) / 128; }
-    __host__ __device__ static constexpr int tile_last_trial(int i) { return (128 * i + 127) / SROWS < G ? (128 * i + 127) / SROWS : G - 1; }
+    __host__ __device__ static constexpr int part_first(int h) { return h == 0 ? 0 : PART0_TILES; }
+    __host__ __device__ static constexpr int part_tiles(int h) { return PARTS == 1 ? TILES : (h == 0 ? PART0_TILES : TILES - PART0_TILES); }
 };
 
 template <bool FAST>
@@ -133,7 +143,7 @@ __device__ __forceinline__ void tcr_tmem_ld_32x32b_x16(uint32_t (&r)[16], uint32
                  : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
                    "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]) : "r"(taddr));
 }
-__device__ __forceinline__ constexpr uint32_t tcr_idesc_i8_kk(int M, int N) {   // both operands K-major (layer 2)
+__device__ __forceinline__ constexpr uint32_t tcr_idesc_i8_kk(int M, int N) {   // both operands K-major
     return (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 
@@ -142,7 +152,12 @@ __device__ __forceinline__ uint4 tcr_lds128(const uint8_t* p) {
     asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(smem_u32(p)));
     return v;
 }
-// one row of T samples: lane = 16-byte chunk (+ 32 per pass); all loads of the row are issued before the shifts
+__device__ __forceinline__ uint2 tcr_lds64(const uint8_t* p) {
+    uint2 v;
+    asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(smem_u32(p)));
+    return v;
+}
+// WOLF = 0: one row of T samples: lane = 16-byte chunk (+ 32 per pass); all loads of the row are issued before the shifts
 template <class K, int K4>
 __device__ __forceinline__ void tcr_realign_row(const uint8_t* rbase, uint8_t* xrow, int c, int sh, int lane) {
     constexpr int P = (K::CHUNKS + 31) / 32;
@@ -195,16 +210,16 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
             mbar_init(sbase + K::BAR_T2_FULL + 8 * i, 1);            // commit of M2
             mbar_init(sbase + K::BAR_T2_EMPTY + 8 * i, kRBW / 2);
             mbar_init(sbase + K::BAR_Y2_EMPTY + 8 * i, K::G);
-            for (int t = 0; t < K::GT; t++) mbar_init(sbase + K::BAR_Y2_FULL + 8 * (K::GT * i + t), kRBW);
+            mbar_init(sbase + K::BAR_Y2_FULL + 8 * i, kRBW);
         }
         for (int j = 0; j < K::G; j++) mbar_init(sbase + K::BAR_Y1_FULL + 8 * j, kRAW);
-        for (int t = 0; t < K::GT; t++) mbar_init(sbase + K::BAR_TILE_DONE + 8 * t, 1);      // commit of M2
+        mbar_init(sbase + K::BAR_TILE_DONE, 1);                      // commit of M2: the y1 buffer of the group has been read
         mbar_fence_init();
     }
     for (int i = tid; i < 16 * 32 / 4; i += kRThreads)
         reinterpret_cast<uint32_t*>(smem + K::OFF_W1)[i] = reinterpret_cast<const uint32_t*>(net->w1umma)[i];
-    for (int i = tid; i < 16 * K::W2_CH / 16; i += kRThreads)
-        reinterpret_cast<uint4*>(smem + K::OFF_W2)[i] = reinterpret_cast<const uint4*>(net->w2umma)[i];
+    for (int i = tid; i < 16 * kW2U32 / 16; i += kRThreads)
+        reinterpret_cast<uint4*>(smem + K::OFF_W2)[i] = reinterpret_cast<const uint4*>(net->w2umma32)[i];
     for (int i = tid; i < 16 * 8; i += kRThreads) {
         const int k = i >> 3, f = i & 7;
         reinterpret_cast<int*>(smem + K::OFF_C2)[i] = f == 0 ? net->thr2[k] : f == 1 ? net->sig2[k] : f == 2 ? net->soff2[k]
@@ -251,8 +266,6 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
             const int gq = n / K::G, j = n - gq * K::G, ab = n & 1;
             RWAIT(0, sbase + K::BAR_T1_FULL + 8 * ab, (n >> 1) & 1);
             tc_fence_after();
-            // the bytes a unit overwrites must have been read by every tile of the previous group that touches them: the
-            // slot that straddles two tiles is released in two steps (its head as soon as the first tile is done)
             const uint32_t yb = st_off + K::SLOT * j;
             const long long b = trial_of(n);
             // the warp's tiles jt0, jt0 + 3, ...: the TMEM load of the next unit is in flight while this one is requantised
@@ -263,11 +276,12 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
                 tmem_ld_16x256b_x2(r[0][0], ta0 + 16 * jt0);
                 tmem_ld_16x256b_x2(r[0][1], ta0 + 16 * jt0 + (16u << 16));
             }
+            // the y1 buffer is single: the layer-2 MMAs of the previous group must have read it (one commit per group)
+            RWAITL(1, sbase + K::BAR_TILE_DONE, (gq & 1) ^ 1);
 #pragma unroll
             for (int it = 0; it < (K::TILES + 2) / 3; it++) {
                 const int jt = jt0 + 3 * it, u = 4 * jt + qi;
                 if (jt >= K::TILES || 32 * u >= K::T) break;
-                RWAITL(1, sbase + K::BAR_TILE_DONE + 8 * K::unit_last_tile(j, jt), (gq & 1) ^ 1);
                 tmem_ld_wait();
                 if (it + 1 < (K::TILES + 2) / 3 && jt + 3 < K::TILES && 32 * (u + 12) < K::T) {
                     tmem_ld_16x256b_x2(r[(it + 1) & 1][0], ta0 + 16 * (jt + 3));
@@ -301,7 +315,9 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
                         w[mt][1] &= m;
                     }
                 }
-                stsm_t8_x4(yb + 32 * u, w[0][0], w[0][1], w[1][0], w[1][1]);
+                // 32-byte swizzle of the layer-2 operand: 16-byte chunk bit ^= address bit 7 (absolute shared address)
+                const uint32_t ya = yb + 32 * u;
+                stsm_t8_x4(ya ^ ((ya >> 3) & 16u), w[0][0], w[0][1], w[1][0], w[1][1]);
             }
             tc_fence_before();
             fence_proxy_async();          // y1 is read by the tensor core (async proxy)
@@ -317,16 +333,16 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
         //    read: the copy of the LAST trial of the batch stops at the 16-byte boundary below its end and the lanes
         //    fetch the remaining <= 15 bytes with byte loads
         // =====================================================================================
-        const unsigned long long total = (unsigned long long)B * (K::C * K::T);
+        const unsigned long long total = (unsigned long long)B * K::TRIAL_BYTES;
         for (int n = 0; n < ntr; n++) {
             const int st = n & 1;
             RWAITL(0, sbase + K::BAR_RAW_EMPTY + 8 * st, ((n >> 1) & 1) ^ 1);
             const long long b = trial_of(n);
             const uint32_t bar = sbase + K::BAR_RAW_FULL + 8 * st;
             if (b < B) {
-                const unsigned long long o = (unsigned long long)b * (K::C * K::T);
+                const unsigned long long o = (unsigned long long)b * K::TRIAL_BYTES;
                 const unsigned long long a0 = o & ~15ull;
-                unsigned long long a1 = (o + K::C * K::T + 15) & ~15ull;
+                unsigned long long a1 = (o + K::TRIAL_BYTES + 15) & ~15ull;
                 if (a1 > total) {                                  // warp-uniform: only the last trial of the batch
                     a1 = total & ~15ull;
                     if (a1 + lane < total) smem[K::OFF_RAW + st * K::RAW_BYTES + (a1 - a0) + lane] = (uint8_t)x[a1 + lane];
@@ -344,160 +360,185 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
         }
     } else if (warp >= kRWarpR && warp < kRWarpP) {
         // =====================================================================================
-        // R: raw bytes -> [C][128 samples] tiles with the 128-byte swizzle (16-byte chunk j of row c at j ^ (c & 7))
+        // R: raw bytes -> layer-1 operand tiles
         // =====================================================================================
         const int rw = warp - kRWarpR;
         for (int n = 0; n < ntr; n++) {
             const int st = n & 1;
             RWAIT(0, sbase + K::BAR_RAW_FULL + 8 * st, (n >> 1) & 1);
-            RWAITL(1, sbase + K::BAR_X_EMPTY + 8 * st, ((n >> 1) & 1) ^ 1);
             const long long b = trial_of(n);
-            if (b < B) {
-                const int o15 = (int)(((unsigned long long)b * (K::C * K::T)) & 15);
-                const uint8_t* raw = smem + K::OFF_RAW + st * K::RAW_BYTES;
-                uint8_t* xs = smem + K::OFF_XS + st * K::XS_BYTES;
-                for (int c = rw; c < K::C; c += kRRW) {
-                    const int src0 = o15 + c * K::T;                       // first byte of the row in the raw stage
-                    const int sh = 8 * (src0 & 3);                         // warp-uniform byte shift, word shift below
-                    const uint8_t* rbase = raw + (src0 & ~15) + 16 * lane;
-                    uint8_t* xrow = xs + c * 128;
-                    switch ((src0 >> 2) & 3) {
-                        case 0: tcr_realign_row<K, 0>(rbase, xrow, c, sh, lane); break;
-                        case 1: tcr_realign_row<K, 1>(rbase, xrow, c, sh, lane); break;
-                        case 2: tcr_realign_row<K, 2>(rbase, xrow, c, sh, lane); break;
-                        default: tcr_realign_row<K, 3>(rbase, xrow, c, sh, lane); break;
+            const int o15 = (int)(((unsigned long long)b * K::TRIAL_BYTES) & 15);
+            const uint8_t* raw = smem + K::OFF_RAW + st * K::RAW_BYTES;
+            if (K::WOLF) {
+                // sample t = 24 bytes at raw + o15 + 24 t (8-byte aligned): chunk 0 = bytes 0..15, chunk 1 = bytes 16..31 (the
+                // last 8 belong to the next sample and meet zero weights).  lane = sample: conflict-free 8-byte loads
+                // (lane stride 24 B) and 16-byte stores (lane stride 16 B)
+#pragma unroll
+                for (int h = 0; h < K::PARTS; h++) {
+                    RWAITL(1, sbase + K::BAR_X_EMPTY + 8 * h, (n & 1) ^ 1);
+                    if (b < B) {
+                        uint8_t* xs = smem + K::OFF_XS + h * K::XS_BYTES;
+                        const int t0 = 128 * K::part_first(h), nit = 4 * K::part_tiles(h);      // warp iterations of 32 samples
+                        for (int it = rw; it < nit; it += kRRW) {
+                            const int tl = 32 * it + lane, t = t0 + tl;
+                            if (t < K::T) {
+                                const uint8_t* s = raw + o15 + 24 * t;
+                                const uint2 w0 = tcr_lds64(s), w1 = tcr_lds64(s + 8), w2 = tcr_lds64(s + 16), w3 = tcr_lds64(s + 24);
+                                uint8_t* d = xs + (tl >> 7) * K::TILE_PITCH + 16 * (tl & 127);
+                                *reinterpret_cast<uint4*>(d) = make_uint4(w0.x, w0.y, w1.x, w1.y);
+                                *reinterpret_cast<uint4*>(d + 2048) = make_uint4(w2.x, w2.y, w3.x, w3.y);
+                            }
+                        }
+                    }
+                    fence_proxy_async();          // the tiles are read by the tensor core (async proxy)
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(sbase + K::BAR_X_FULL + 8 * h);
+                }
+            } else {
+                RWAITL(1, sbase + K::BAR_X_EMPTY + 8 * st, ((n >> 1) & 1) ^ 1);
+                if (b < B) {
+                    // [C][128 samples] tiles with the 128-byte swizzle (16-byte chunk j of row c at j ^ (c & 7))
+                    uint8_t* xs = smem + K::OFF_XS + st * K::XS_BYTES;
+                    for (int c = rw; c < K::C; c += kRRW) {
+                        const int src0 = o15 + c * K::T;                       // first byte of the row in the raw stage
+                        const int sh = 8 * (src0 & 3);                         // warp-uniform byte shift, word shift below
+                        const uint8_t* rbase = raw + (src0 & ~15) + 16 * lane;
+                        uint8_t* xrow = xs + c * 128;
+                        switch ((src0 >> 2) & 3) {
+                            case 0: tcr_realign_row<K, 0>(rbase, xrow, c, sh, lane); break;
+                            case 1: tcr_realign_row<K, 1>(rbase, xrow, c, sh, lane); break;
+                            case 2: tcr_realign_row<K, 2>(rbase, xrow, c, sh, lane); break;
+                            default: tcr_realign_row<K, 3>(rbase, xrow, c, sh, lane); break;
+                        }
                     }
                 }
+                fence_proxy_async();          // the tiles are read by the tensor core (async proxy)
+                __syncwarp();
+                if (lane == 0) mbar_arrive(sbase + K::BAR_X_FULL + 8 * st);
             }
-            fence_proxy_async();          // the tiles are read by the tensor core (async proxy)
             __syncwarp();
-            if (lane == 0) {
-                mbar_arrive(sbase + K::BAR_X_FULL + 8 * st);
-                mbar_arrive(sbase + K::BAR_RAW_EMPTY + 8 * st);
-            }
+            if (lane == 0) mbar_arrive(sbase + K::BAR_RAW_EMPTY + 8 * st);
         }
     }
     else if (warp == kRWarpM1) {
         // =====================================================================================
         // M1: layer-1 MMAs, one per tile (K = 32 channels covers C)
         // =====================================================================================
-        constexpr uint32_t idesc = umma_idesc_i8(128, 16);
-        const uint64_t da0 = umma_desc(sbase + K::OFF_XS, 16, 1024, 2), db0 = umma_desc(sbase + K::OFF_W1, 128, 256, 0);
+        constexpr uint32_t idesc = K::WOLF ? tcr_idesc_i8_kk(128, 16) : umma_idesc_i8(128, 16);
+        const uint64_t da0 = K::WOLF ? umma_desc(sbase + K::OFF_XS, 2048, 128, 0) : umma_desc(sbase + K::OFF_XS, 16, 1024, 2);
+        const uint64_t db0 = umma_desc(sbase + K::OFF_W1, 128, 256, 0);
         const uint32_t a_hi = (uint32_t)(da0 >> 32), b_hi = (uint32_t)(db0 >> 32), b_lo0 = (uint32_t)db0;
         for (int n = 0; n < ntr; n++) {
-            const int st = n & 1, ab = n & 1;
-            RWAITL(0, sbase + K::BAR_X_FULL + 8 * st, (n >> 1) & 1);
-            RWAITL(1, sbase + K::BAR_T1_EMPTY + 8 * ab, ((n >> 1) & 1) ^ 1);
-            tc_fence_after();
-            const uint32_t a_lo = (uint32_t)da0 + st * (K::XS_BYTES >> 4);
+            const int ab = n & 1;
             const uint32_t td = tmem_base + ab * K::TM_L1_TRIAL;
-            if (elect_one()) {
 #pragma unroll
-                for (int j = 0; j < K::TILES; j++)
-                    umma_i8_lohi(td + 16 * j, a_lo + ((j * K::TILE_PITCH) >> 4), a_hi, b_lo0, b_hi, idesc, 0);
-                umma_commit(sbase + K::BAR_X_EMPTY + 8 * st);
-                umma_commit(sbase + K::BAR_T1_FULL + 8 * ab);
+            for (int h = 0; h < K::PARTS; h++) {
+                const int st = K::PARTS == 1 ? (n & 1) : h;
+                const int par = K::PARTS == 1 ? ((n >> 1) & 1) : (n & 1);
+                RWAITL(0, sbase + K::BAR_X_FULL + 8 * st, par);
+                if (h == 0) RWAITL(1, sbase + K::BAR_T1_EMPTY + 8 * ab, ((n >> 1) & 1) ^ 1);
+                tc_fence_after();
+                const uint32_t a_lo = (uint32_t)da0 + st * (K::XS_BYTES >> 4);
+                if (elect_one()) {
+#pragma unroll
+                    for (int j = 0; j < K::part_tiles(h); j++)
+                        umma_i8_lohi(td + 16 * (K::part_first(h) + j), a_lo + ((j * K::TILE_PITCH) >> 4), a_hi, b_lo0, b_hi, idesc, 0);
+                    umma_commit(sbase + K::BAR_X_EMPTY + 8 * st);
+                    if (h == K::PARTS - 1) umma_commit(sbase + K::BAR_T1_FULL + 8 * ab);
+                }
+                __syncwarp();
             }
-            __syncwarp();
         }
     } else if (warp == kRWarpM2) {
         // =====================================================================================
-        // M2: layer-2 MMAs: per tile of 128 rows, 4 batches of 4 channels x 3 k-steps into alternating TMEM halves
+        // M2: layer-2 MMAs: one tile of 128 rows x 32 outputs per group; 8 batches of 2 channels x 3 k-steps into
+        //     alternating TMEM halves.  A = y1 row of the channel, K-major SWIZZLE_32B (rows 32 B apart, SBO = 256 B), k-step ks
+        //     starts 32 ks bytes further; B = w2umma32 of the channel (LBO = 256 B, SBO = 128 B), k-step ks = + 512 ks bytes
         // =====================================================================================
-        constexpr uint32_t idesc = tcr_idesc_i8_kk(128, 16);
-        const uint64_t da0 = umma_desc(sbase + K::OFF_Y1, 16, 128, 0), db0 = umma_desc(sbase + K::OFF_W2, 128, 768, 0);
+        constexpr uint32_t idesc = tcr_idesc_i8_kk(128, 32);
+        const uint64_t da0 = umma_desc(sbase + K::OFF_Y1, 16, 256, 6), db0 = umma_desc(sbase + K::OFF_W2, 256, 128, 0);
         const uint32_t a_hi = (uint32_t)(da0 >> 32), b_hi = (uint32_t)(db0 >> 32), b_lo0 = (uint32_t)db0, a_lo0 = (uint32_t)da0;
         for (int gq = 0; gq < ng; gq++) {
-            int waited = -1;
 #pragma unroll
-            for (int i = 0; i < K::GT; i++) {
-                for (int j = waited + 1; j <= K::tile_last_trial(i); j++) RWAIT(0, sbase + K::BAR_Y1_FULL + 8 * j, gq & 1);
-                waited = K::tile_last_trial(i);
+            for (int j = 0; j < K::G; j++) RWAIT(0, sbase + K::BAR_Y1_FULL + 8 * j, gq & 1);
+            tc_fence_after();
+#pragma unroll
+            for (int bt = 0; bt < 8; bt++) {
+                const int h = bt & 1;
+                const int use = gq * 4 + (bt >> 1);                         // how often this half has been used before
+                RWAIT(1, sbase + K::BAR_T2_EMPTY + 8 * h, (use & 1) ^ 1);
                 tc_fence_after();
+                if (elect_one()) {
 #pragma unroll
-                for (int bt = 0; bt < 4; bt++) {
-                    const int h = bt & 1;
-                    const int use = (gq * K::GT + i) * 2 + (bt >> 1);          // how often this half has been used before
-                    RWAIT(1, sbase + K::BAR_T2_EMPTY + 8 * h, (use & 1) ^ 1);
-                    tc_fence_after();
-                    if (elect_one()) {
+                    for (int c = 0; c < 2; c++)
 #pragma unroll
-                        for (int c = 0; c < 4; c++)
-#pragma unroll
-                            for (int ks = 0; ks < 3; ks++) {
-                                const int k = 4 * bt + c;
-                                umma_i8_lohi(tmem_base + K::TM_L2 + K::TM_L2_HALF * h + 16 * c,
-                                             a_lo0 + ((k * K::CHS + 2048 * i + 32 * ks) >> 4), a_hi,
-                                             b_lo0 + ((k * K::W2_CH + 256 * ks) >> 4), b_hi, idesc, ks > 0);
-                            }
-                        umma_commit(sbase + K::BAR_T2_FULL + 8 * h);
-                        if (bt == 3) umma_commit(sbase + K::BAR_TILE_DONE + 8 * i);
-                    }
-                    __syncwarp();
+                        for (int ks = 0; ks < 3; ks++) {
+                            const int k = 2 * bt + c;
+                            umma_i8_lohi(tmem_base + K::TM_L2 + K::TM_L2_HALF * h + 32 * c,
+                                         a_lo0 + ((k * K::CHS + 32 * ks) >> 4), a_hi,
+                                         b_lo0 + ((k * kW2U32 + 512 * ks) >> 4), b_hi, idesc, ks > 0);
+                        }
+                    umma_commit(sbase + K::BAR_T2_FULL + 8 * h);
+                    if (bt == 7) umma_commit(sbase + K::BAR_TILE_DONE);
                 }
+                __syncwarp();
             }
         }
     } else if (warp >= kRWarpB && warp < kRWarpC) {
         // =====================================================================================
-        // B: layer-2 epilogue.  Thread = TMEM lane = row 128 i + 32 (warp & 3) + lane of the group's y1 buffer
-        //    = 16 consecutive conv outputs (two pooling groups) of trial row / SROWS; channels 4 (2 bb + h) .. + 3
+        // B: layer-2 epilogue.  Thread = TMEM lane = row 32 (warp & 3) + lane of the group's y1 buffer
+        //    = 32 consecutive conv outputs (four pooling groups) of trial row / SROWS; channels 2 (2 bb + h), + 1.
+        //    Column n' of the accumulator = output 31 - n' of the row (reversed Toeplitz, PipeNet::w2umma32)
         // =====================================================================================
         const int wb = warp - kRWarpB, qi = warp & 3, h = wb >> 2;
         const int4* c2 = reinterpret_cast<const int4*>(smem + K::OFF_C2);
+        const int row = 32 * qi + lane;
+        const int j = row / K::SROWS, blk = row - j * K::SROWS;
+        const bool valid = j < K::G && blk < K::VROWS;
         for (int gq = 0; gq < ng; gq++) {
             const int gpar = gq & 1;
             RWAITL(1, sbase + K::BAR_Y2_EMPTY + 8 * gpar, ((gq >> 1) & 1) ^ 1);     // the C warps have consumed y2[gpar] of group gq - 2
+            const long long b = K::G * (firstg + (long long)gq * strideg) + j;
+            uint8_t* y2s = smem + K::OFF_Y2 + (gpar * K::G + (j < K::G ? j : 0)) * K::Y2_TRIAL + 8 + 4 * blk;
 #pragma unroll 1
-            for (int i = 0; i < K::GT; i++) {
-                const int row = 128 * i + 32 * qi + lane;
-                const int j = row / K::SROWS, blk = row - j * K::SROWS;
-                const bool valid = j < K::G && blk < K::VROWS;
-                const long long b = K::G * (firstg + (long long)gq * strideg) + j;
-                uint8_t* y2s = smem + K::OFF_Y2 + (gpar * K::G + (j < K::G ? j : 0)) * K::Y2_TRIAL + 8 + 2 * blk;
-#pragma unroll 1
-                for (int bb = 0; bb < 2; bb++) {
-                    const int bt = 2 * bb + h;
-                    const int use = (gq * K::GT + i) * 2 + bb;
-                    RWAIT(0, sbase + K::BAR_T2_FULL + 8 * h, use & 1);
-                    tc_fence_after();
+            for (int bb = 0; bb < 4; bb++) {
+                const int bt = 2 * bb + h;
+                const int use = gq * 4 + bb;
+                RWAIT(0, sbase + K::BAR_T2_FULL + 8 * h, use & 1);
+                tc_fence_after();
 #pragma unroll
-                    for (int cp = 0; cp < 2; cp++) {
-                        uint32_t r[2][16];
+                for (int c = 0; c < 2; c++) {
+                    uint32_t r[2][16];
+                    const uint32_t ta = tmem_base + ((uint32_t)(32 * qi) << 16) + K::TM_L2 + K::TM_L2_HALF * h + 32 * c;
+                    tcr_tmem_ld_32x32b_x16(r[0], ta);
+                    tcr_tmem_ld_32x32b_x16(r[1], ta + 16);
+                    tmem_ld_wait();
+                    if (c == 1) {
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(sbase + K::BAR_T2_EMPTY + 8 * h);
+                    }
+                    const int k = 2 * bt + c;
+                    const int4 ca = c2[2 * k];                       // thr, sig, soff, m
+                    const int shk = reinterpret_cast<const int*>(smem + K::OFF_C2)[8 * k + 4];
+                    int s[4];                                        // s[p] = pooling group p = outputs 8 p .. 8 p + 7 = columns 24 - 8 p .. 31 - 8 p
 #pragma unroll
-                        for (int c = 0; c < 2; c++)
-                            tcr_tmem_ld_32x32b_x16(r[c], tmem_base + ((uint32_t)(32 * qi) << 16) + K::TM_L2 + K::TM_L2_HALF * h + 16 * (2 * cp + c));
-                        tmem_ld_wait();
-                        if (cp == 1) {
-                            tc_fence_before();
-                            __syncwarp();
-                            if (lane == 0) mbar_arrive(sbase + K::BAR_T2_EMPTY + 8 * h);
-                        }
+                    for (int p = 0; p < 4; p++) {
+                        const int col = 24 - 8 * p;
+                        int acc = 0;
 #pragma unroll
-                        for (int c = 0; c < 2; c++) {
-                            const int k = 4 * bt + 2 * cp + c;
-                            const int4 ca = c2[2 * k];                       // thr, sig, soff, m
-                            const int shk = reinterpret_cast<const int*>(smem + K::OFF_C2)[8 * k + 4];
-                            int s0 = 0, s1 = 0;
-#pragma unroll
-                            for (int e = 0; e < 8; e++) {
-                                s0 += max((int)r[c][e], ca.x);
-                                s1 += max((int)r[c][8 + e], ca.x);
-                            }
-                            const uint32_t o01 = pack2_sat(tdiv_magic(s0 * ca.y + ca.z, ca.w, shk), tdiv_magic(s1 * ca.y + ca.z, ca.w, shk));
-                            if (valid) {
-                                *reinterpret_cast<uint16_t*>(y2s + k * K::Y2S) = (uint16_t)o01;
-                                if (TAPS && tap2 && b < B) {
-                                    int8_t* o = tap2 + ((size_t)b * 16 + k) * K::T8 + 2 * blk;
-                                    o[0] = (int8_t)(o01 & 0xff);
-                                    o[1] = (int8_t)((o01 >> 8) & 0xff);
-                                }
-                            }
-                        }
+                        for (int e = 0; e < 8; e++) acc += max((int)r[col >> 4][(col & 15) + e], ca.x);
+                        s[p] = tdiv_magic(acc * ca.y + ca.z, ca.w, shk);
+                    }
+                    const uint32_t o = pack4_sat(s[0], s[1], s[2], s[3]);
+                    if (valid) {
+                        *reinterpret_cast<uint32_t*>(y2s + k * K::Y2S) = o;
+                        if (TAPS && tap2 && b < B) *reinterpret_cast<uint32_t*>(tap2 + ((size_t)b * 16 + k) * K::T8 + 4 * blk) = o;
                     }
                 }
-                __syncwarp();
-                if (lane == 0) mbar_arrive(sbase + K::BAR_Y2_FULL + 8 * (K::GT * gpar + i));
             }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(sbase + K::BAR_Y2_FULL + 8 * gpar);
         }
     } else if (warp >= kRWarpC && warp < kRWarpR) {
         // =====================================================================================
@@ -527,7 +568,7 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
         for (int n = cj; n < ntr; n += kRCW) {
             const int gq = n / K::G, j = n - gq * K::G, gpar = gq & 1;
             const long long b = trial_of(n);
-            RWAIT(0, sbase + K::BAR_Y2_FULL + 8 * (K::GT * gpar + K::trial_last_tile(j)), (gq >> 1) & 1);
+            RWAIT(0, sbase + K::BAR_Y2_FULL + 8 * gpar, (gq >> 1) & 1);
             const uint32_t y2a = sbase + K::OFF_Y2 + (gpar * K::G + j) * K::Y2_TRIAL + l3_off;
 #pragma unroll kTcrL3Unroll
             for (int k = 0; k < 16; k++) {
@@ -596,10 +637,13 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
                 const uint32_t bb0 = g == 0 ? y4w[8 * ks + q] : 0u, bb1 = g == 0 ? y4w[8 * ks + 4 + q] : 0u;
                 mma_k32(z, a, bb0, bb1);
             }
-            if (q == 0 && g < 4 && b < B) {
-                const int8_t o = (int8_t)clip8(tdiv_magic(z[0] + b5, m5, sh5));
-                logits[(size_t)b * 4 + g] = o;
-                for (int i = 0; i < peers.n; i++) peers.p[i][(size_t)b * 4 + g] = o;    // fused all-gather (NVLink P2P)
+            // the four logit bytes of the trial (lanes g = 0..3, q = 0) become one word: one 4-byte store to the local buffer and
+            // one per peer (fused gather over NVLink P2P; lane 0 = local, lane i = peer i - 1)
+            const uint32_t ob = (q == 0 && g < 4) ? ((uint32_t)(uint8_t)(int8_t)clip8(tdiv_magic(z[0] + b5, m5, sh5)) << (8 * g)) : 0u;
+            const uint32_t word = __reduce_or_sync(0xffffffffu, ob);
+            if (b < B && lane <= peers.n) {
+                int8_t* dst = lane == 0 ? logits : peers.p[lane - 1];
+                *reinterpret_cast<uint32_t*>(dst + (size_t)b * 4) = word;
             }
             __syncwarp();   // y3 / y4 are rewritten by the warp's next trial
         }
@@ -611,11 +655,11 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
 }
 
 // ---------------------------------------------------------------------------------------------
-template <int C, int T>
+template <int C, int T, int WOLF>
 static cudaError_t launch_tcr_instance(const PipeNet* net_dev, bool fast1, const int8_t* x, long long B, int8_t* logits,
                                        const PeerOut& peers, int8_t* t1, int8_t* t2, int8_t* t3, int8_t* t4, int num_sms,
                                        cudaStream_t stream) {
-    using K = RCfg<C, T>;
+    using K = RCfg<C, T, WOLF>;
     const bool taps = t1 || t2 || t3 || t4;
     auto kern = taps ? tcr_forward_kernel<K, false, true>
                      : (fast1 ? tcr_forward_kernel<K, true, false> : tcr_forward_kernel<K, false, false>);
@@ -636,13 +680,14 @@ bool tcr_has_instance(int C, int T) {
 #undef X
     return false;
 }
-
-bool tcr_has_wolf_instance(int C, int T) { (void)C; (void)T; return false; }
+bool tcr_has_wolf_instance(int C, int T) { return tcr_has_instance(C, T); }
 
 cudaError_t launch_tcr(const PipeNet* net_dev, bool fast1, int C, int T, const int8_t* x, long long B, int layout, int8_t* logits,
                        const PeerOut& peers, int8_t* t1, int8_t* t2, int8_t* t3, int8_t* t4, int num_sms, cudaStream_t stream) {
-    if (layout != 0) return cudaErrorInvalidValue;
-#define X(c, t) if (C == c && T == t) return launch_tcr_instance<c, t>(net_dev, fast1, x, B, logits, peers, t1, t2, t3, t4, num_sms, stream);
+#define X(c, t)                                                                                                                     \
+    if (C == c && T == t)                                                                                                           \
+        return layout == 0 ? launch_tcr_instance<c, t, 0>(net_dev, fast1, x, B, logits, peers, t1, t2, t3, t4, num_sms, stream)     \
+                           : launch_tcr_instance<c, t, 1>(net_dev, fast1, x, B, logits, peers, t1, t2, t3, t4, num_sms, stream);
     MIBMI_TCR_SHAPES(X)
 #undef X
     return cudaErrorInvalidValue;

@@ -79,8 +79,9 @@ def test_wolf_input_layout(golden):
     xw = convert.to_wolf_input(fx["x"])   # [B][T][C_ALIGN]  (gen_input_header.py:75-76)
     y = net.forward(_cuda(xw), layout="btc").cpu().numpy()
     assert np.array_equal(y, fx["golden_reorder"])
-    # rows of C_ALIGN bytes that are a multiple of 16 go through the tcgen05 kernel (K-major operand, 3-D tensor map); the
-    # others are transposed into an L2-sized scratch chunk by chunk (mibmi_reorder.cu) and run on the fused kernel of the shape
+    # rows of C_ALIGN bytes that are a multiple of 16 go through the tcgen05 kernel (K-major operand, 3-D tensor map), 22 x 1125
+    # through the realign warps of tcr_forward_kernel; the others are transposed into a scratch chunk by chunk
+    # (mibmi_reorder.cu) and run on the fused kernel of the shape
     ok, _why = net.fused_supported()
     assert net.last_path == ("fused" if ok else "generic")
     if ok:
@@ -96,10 +97,10 @@ def test_wolf_input_layout(golden):
             assert np.array_equal(taps[name].cpu().numpy(), fx[f"golden_reorder_{name}"]), name
 
 
-@pytest.mark.parametrize("C,T", [(22, 1125), (38, 480), (24, 480), (19, 480), (8, 480)])
+@pytest.mark.parametrize("C,T", [(38, 480), (24, 480), (19, 480), (8, 480)])
 @pytest.mark.parametrize("chunk", [None, 101])
 def test_wolf_order_through_reorder_scratch(C, T, chunk, monkeypatch):
-    """Wolf-order rows of 24 / 40 / 20 / 8 bytes: several chunks (odd and even trial phases), taps, launch count."""
+    """Wolf-order rows of 40 / 24 / 20 / 8 bytes at T = 480: several chunks (odd and even trial phases), taps, launch count."""
     if chunk:
         monkeypatch.setenv("MIBMI_WOLF_CHUNK", str(chunk))
     net, arrays = _net(C, T, 31)
@@ -109,7 +110,7 @@ def test_wolf_order_through_reorder_scratch(C, T, chunk, monkeypatch):
     xw = _cuda(convert.to_wolf_input(x))
     n0 = net.launch_count
     assert np.array_equal(net.forward(xw, layout="btc").cpu().numpy(), ref)
-    assert net.last_path == "fused" and net.last_kernel != "generic_forward_kernel"
+    assert net.last_path == "fused" and net.last_kernel == "tc_forward_kernel"
     if chunk:
         assert net.launch_count - n0 == 2 * -(-B // chunk)
     assert np.array_equal(net.forward(xw[:1], layout="btc").cpu().numpy(), ref[:1])
@@ -119,9 +120,47 @@ def test_wolf_order_through_reorder_scratch(C, T, chunk, monkeypatch):
     assert np.array_equal(y.cpu().numpy(), ref[:300])
     for name in ("y1", "y2", "y3", "y4"):
         assert np.array_equal(taps[name].cpu().numpy(), lay[name][:300]), name
-    # host entry point (two staging streams, two scratch slots)
+    # host entry point (two staging streams)
     net.set_path("auto")
     assert np.array_equal(net.forward_host(convert.to_wolf_input(x), layout="btc"), ref)
+
+
+def test_wolf_order_22x1125_inside_the_kernel():
+    """BASELINE config 3 in the order net_model_compute receives it ([T][24] rows, gen_input_header.py:75-76): ONE launch of
+    tcr_forward_kernel, the 24-byte rows are expanded to the K-major layer-1 operand in shared memory (no scratch, no second pass
+    over HBM).  A Wolf-order trial is 27 000 bytes: trials alternate between 0 and 8 modulo 16, any sub-batch start is legal when
+    16-byte aligned (even trial index)."""
+    C, T = 22, 1125
+    net, arrays = _net(C, T, 31)
+    B = 1237
+    x = synth.make_trials(B, C, T, seed=77)
+    ref, lay = wolf_port.forward(arrays, C, T, x, return_layers=True)
+    xw = _cuda(convert.to_wolf_input(x))
+    n0 = net.launch_count
+    y = net.forward(xw, layout="btc").cpu().numpy()
+    bad = np.nonzero((y != ref).any(axis=1))[0]
+    assert bad.size == 0, f"{bad.size} trials differ, first {bad[:5]}"
+    assert net.last_path == "fused" and net.last_kernel == "tcr_forward_kernel" and net.launch_count - n0 == 1
+    for lo, hi in ((0, 1), (4, 7), (2, 445), (1000, 1237)):
+        assert np.array_equal(net.forward(xw[lo:hi], layout="btc").cpu().numpy(), ref[lo:hi]), (lo, hi)
+    # odd start: 8 modulo 16 -> the exact generic kernel under AUTO
+    assert np.array_equal(net.forward(xw[1:40], layout="btc").cpu().numpy(), ref[1:40])
+    assert net.last_path == "generic"
+    net.set_path("fused")
+    yt, taps = net.forward_taps(xw[:300], layout="btc")
+    assert net.last_kernel == "tcr_forward_kernel"
+    assert np.array_equal(yt.cpu().numpy(), ref[:300])
+    for name in ("y1", "y2", "y3", "y4"):
+        assert np.array_equal(taps[name].cpu().numpy(), lay[name][:300]), name
+    net.set_path("auto")
+    assert np.array_equal(net.forward_host(convert.to_wolf_input(x), layout="btc"), ref)
+    # padding bytes of the Wolf rows (channels 22, 23) are never trusted: garbage there must not change anything
+    xg = convert.to_wolf_input(x[:64]).copy()
+    xg[:, :, 22:] = np.random.default_rng(0).integers(-128, 128, xg[:, :, 22:].shape)
+    assert np.array_equal(net.forward(_cuda(xg), layout="btc").cpu().numpy(), ref[:64])
+    # saturating inputs
+    xs = np.stack([np.full((C, T), v, np.int8) for v in (127, -127, -128, 0)])
+    assert np.array_equal(net.forward(_cuda(convert.to_wolf_input(xs)), layout="btc").cpu().numpy(), wolf_port.forward(arrays, C, T, xs))
 
 
 # ---- against the oracle on seeded random nets / trials ------------------------------------------------

@@ -4,21 +4,24 @@ sys.path.insert(0, '/root/repo')
 from mibminet_b200 import convert, synth, _lib
 from mibminet_b200.engine import Int8Net
 C, T = (int(sys.argv[1]), int(sys.argv[2])) if len(sys.argv) > 2 else (22, 1125)
+layout = sys.argv[3] if len(sys.argv) > 3 else 'bct'
 B = 65536
 net = Int8Net(convert.params_from_state_dict(synth.make_state_dict(C=C, T=T, seed=0), C=C, T=T), device='cuda:0')
 g = torch.Generator(device='cuda'); g.manual_seed(5)
 x = torch.randint(-127, 128, (B, C, T), dtype=torch.int8, device='cuda', generator=g)
+if layout == 'btc':
+    xw = torch.zeros((B, T, (C + 3) // 4 * 4), dtype=torch.int8, device='cuda'); xw[:, :, :C] = x.transpose(1, 2); x = xw
 for _ in range(3):
-    y = net.forward(x)
+    y = net.forward(x, layout=layout)
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 e0.record()
 for _ in range(10):
-    net.forward(x)
+    net.forward(x, layout=layout)
 e1.record()
 torch.cuda.synchronize()
 ms = e0.elapsed_time(e1) / 10
 w = torch.arange(1, 4 * B + 1, device='cuda', dtype=torch.int64)
-print(f'{os.environ.get("MIBMI_LIB_PATH", "default")}: {ms:.4f} ms  {B / ms / 1e3:.1f} M trials/s  checksum {int((y.flatten().long() * w).sum())}')
+print(f'{os.environ.get("MIBMI_LIB_PATH", "default")} {layout}: {ms:.4f} ms  {B / ms / 1e3:.1f} M trials/s  checksum {int((y.flatten().long() * w).sum())}')
 L = _lib.lib()
 if not hasattr(L, 'mibmi_debug_prof_tcr'):
     sys.exit(0)
