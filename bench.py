@@ -21,6 +21,7 @@ buffer over NVLink (fused gather; one NCCL all_gather per step is the fallback).
 """
 import argparse
 import json
+import math
 import os
 import subprocess
 import sys
@@ -114,7 +115,7 @@ def tensor_pipe(kernel, C, T, B, ms_kernel, clocks):
     if kernel == "tc_forward_kernel":
         n_mma = tiles * ksteps + 12                   # layer 1 per tile and k-step + layer 2: 16 channels x 3 per quad of 4 trials
     elif kernel == "tcr_forward_kernel":
-        n_mma = tiles * ksteps + 2 * 48 / 3           # layer 2: 2 tiles x 16 channels x 3 per group of 3 trials
+        n_mma = tiles * ksteps + 48 / 3               # layer 2: one tile of N = 32 x 16 channels x 3 k-steps per group of 3 trials
     else:
         return None
     mhz = (clocks or {}).get("sm_mhz") or 1965.0
@@ -162,6 +163,31 @@ class ClockSampler:
         reasons = [n for i, n in enumerate(names) if any(r[3 + i].lower().startswith("active") for r in rows)]
         return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(rows[0][1]), "reasons": reasons, "samples": len(rows),
                 "power_w_max": max(float(r[2]) for r in rows)}
+
+
+def bind_to_gpu_cpus(gpu_index):
+    """Pin this rank (and the pinned host buffers it allocates afterwards: first touch) to the CPU cores NVML reports as
+    local to its GPU -- under torchrun every rank otherwise inherits the whole machine and the pinned staging buffers land
+    on whichever NUMA node the allocating thread happens to run on.  Returns a small record for the e2e block."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(gpu_index)
+        allowed = os.sched_getaffinity(0)
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (max(allowed) // 64) + 1)
+        local = {64 * i + b for i, w in enumerate(words) for b in range(64) if (w >> b) & 1}
+        try:
+            node = pynvml.nvmlDeviceGetNumaNodeId(h)
+        except Exception:       # noqa: BLE001 -- older NVML
+            node = None
+        use = sorted(local & allowed)
+        if use and len(use) < len(allowed):
+            os.sched_setaffinity(0, use)
+            return {"bound": True, "cpus": len(use), "of": len(allowed), "numa_node": node}
+        return {"bound": False, "cpus": len(allowed), "of": len(allowed), "numa_node": node,
+                "why": "NVML reports every allowed CPU as local to the GPU (one NUMA node visible)" if use else "no overlap"}
+    except Exception as e:      # noqa: BLE001 -- binding is an optimisation, never a requirement
+        return {"bound": False, "why": str(e)[:120]}
 
 
 def measured_peaks():
@@ -487,12 +513,13 @@ def main():
     # multi-GPU: the all-gather of the logits is fused into the kernel (P2P stores into every rank's symmetric
     # buffer over NVLink, mibmi_forward_int8_gather); NCCL all_gather per step is the fallback
     peer = None
-    if world > 1 and args.gather in ("auto", "peer"):
+    affinity = bind_to_gpu_cpus(local_rank) if world > 1 else None
+    if world > 1 and args.gather in ("auto", "peer", "root"):
         from mibminet_b200.sharding import PeerGather
         try:
-            peer = PeerGather(net, world * B)
+            peer = PeerGather(net, world * B, mode="root" if args.gather == "root" else "all")
         except RuntimeError as e:
-            if args.gather == "peer":
+            if args.gather in ("peer", "root"):
                 raise
             if rank == 0:
                 print(f"[bench] peer gather unavailable ({e}); using NCCL all_gather", file=sys.stderr)
@@ -500,6 +527,7 @@ def main():
         dist.all_reduce(ok, op=dist.ReduceOp.MIN)
         if int(ok[0]) == 0:
             peer = None
+    use_nccl_gather = world > 1 and peer is None and args.gather != "none"
 
     xf = None
     if args.float_input:                 # the (Q) module's view: float trials, quant1 in front, quant6 behind (modules.edgeEEGNet)
@@ -516,7 +544,7 @@ def main():
             peer.forward(x, layout=args.layout)
         else:
             net.forward(x, layout=args.layout, out=logits)
-            if world > 1:
+            if use_nccl_gather:
                 dist.all_gather_into_tensor(gathered, logits)
 
     def step():
@@ -548,7 +576,7 @@ def main():
         else:
             net.forward(x, layout=args.layout, out=logits)
         k_ev[i][1].record()
-        if world > 1 and peer is None:
+        if use_nccl_gather:
             dist.all_gather_into_tensor(gathered, logits)
     if peer is not None:
         gathered = peer.wait()           # one barrier: every rank's rows of the last step are in place
@@ -563,19 +591,70 @@ def main():
     clocks = sampler.stop(t_wall0, t_wall1) if sampler else None
 
     gather_checked = None
-    if world > 1:
+    if world > 1 and args.gather != "none":
         # outside the timed region: the gathered logits against an independent NCCL all_gather of the local ones
+        # (gather-to-root: only the root's buffer is complete, the verdict is the root's)
         chk = torch.empty((world * B, N_CLASSES), dtype=torch.int8, device=dev)
         dist.all_gather_into_tensor(chk, logits.contiguous())
-        gather_checked = bool(torch.equal(chk, gathered))
+        good = torch.equal(chk, gathered) if (args.gather != "root" or rank == 0) else torch.equal(chk[rank * B:(rank + 1) * B], logits)
+        flag = torch.tensor([1 if good else 0], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        gather_checked = bool(int(flag[0]))
     ms_total = ev0.elapsed_time(ev1)
-    ms_kernel = float(np.mean([a.elapsed_time(b) for a, b in k_ev]))
+    k_ms = sorted(a.elapsed_time(b) for a, b in k_ev)
+    ms_kernel = float(np.mean(k_ms))
     t = torch.tensor([ms_total, ms_kernel], dtype=torch.float64, device=dev)
+    per_rank = None
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        # per-rank record: the slowest GPU and the cost of the remote stores are separate numbers (compare --gather none)
+        mine = torch.tensor([k_ms[0], k_ms[len(k_ms) // 2], k_ms[-1], ms_kernel, ev0.elapsed_time(ev1)], dtype=torch.float64, device=dev)
+        allr = torch.empty((world, 5), dtype=torch.float64, device=dev)
+        dist.all_gather_into_tensor(allr, mine)
+        per_rank = [{"rank": r, "kernel_ms_min": float(v[0]), "kernel_ms_median": float(v[1]), "kernel_ms_max": float(v[2]),
+                     "kernel_ms_mean": float(v[3]), "region_ms": float(v[4])} for r, v in enumerate(allr.cpu())]
     ms_total, ms_kernel_max = float(t[0]), float(t[1])
     ms_per_step = ms_total / args.steps
     value = world * B / (ms_per_step * 1e-3)
+
+    # ---- the same step held back to back for >= --sustained-seconds: the board's power cap decides here, not the burst clock
+    sustained = None
+    if args.sustained_seconds > 0 and xf is None:
+        n_sus = max(args.steps, int(math.ceil(args.sustained_seconds * 1e3 / ms_per_step)))
+        if world > 1:
+            nt = torch.tensor([n_sus], device=dev)
+            dist.all_reduce(nt, op=dist.ReduceOp.MAX)
+            n_sus = int(nt[0])
+            dist.barrier()
+        torch.cuda.synchronize()
+        s_sampler = ClockSampler(local_rank) if rank == 0 else None
+        s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        if peer is not None:
+            peer.wait()
+        tw0 = time.perf_counter()
+        s0.record()
+        for i in range(n_sus):
+            if peer is not None:
+                peer.forward(x, layout=args.layout)
+            else:
+                net.forward(x, layout=args.layout, out=logits)
+                if use_nccl_gather:
+                    dist.all_gather_into_tensor(gathered, logits)
+        if peer is not None:
+            peer.wait()
+        s1.record()
+        torch.cuda.synchronize()
+        tw1 = time.perf_counter()
+        st = torch.tensor([s0.elapsed_time(s1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(st, op=dist.ReduceOp.MAX)
+        s_ms = float(st[0])
+        s_clocks = s_sampler.stop(tw0, tw1) if s_sampler else None
+        sustained = {"value": world * B * n_sus / (s_ms * 1e-3), "unit": "trials/s", "steps": n_sus, "seconds": s_ms * 1e-3,
+                     "ms_per_step": s_ms / n_sus, "clocks": s_clocks,
+                     "note": "same launches as the headline region, back to back; sw_power_cap is expected on a 1 kW part and is kept"}
+        if world > 1:
+            dist.barrier()
 
     # ---- end to end through the host entry point (pinned host buffers, copies inside the timed region)
     e2e = None
@@ -594,13 +673,18 @@ def main():
             net.forward_host(xh, layout=args.layout, out=yh)
         torch.cuda.synchronize()
         dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+        per_rank_gbs = None
         if world > 1:
+            alld = torch.empty((world,), dtype=torch.float64, device=dev)
+            dist.all_gather_into_tensor(alld, dt)
+            per_rank_gbs = [x.numel() * e_steps / float(v) / 1e9 for v in alld.cpu()]      # each rank's own wall clock
             dist.all_reduce(dt, op=dist.ReduceOp.MAX)
         assert torch.equal(yh.to(dev), logits), "host entry point and device path disagree"
         e2e = {"value": world * B * e_steps / float(dt[0]), "unit": "trials/s",
                "h2d_bytes_per_step": world * x.numel(), "d2h_bytes_per_step": world * B * N_CLASSES,
                "steps": e_steps, "timing": "host wall clock around the synchronous C-ABI call, max over ranks",
                "h2d_gbs_per_gpu": x.numel() * e_steps / float(dt[0]) / 1e9,
+               "h2d_gbs_per_rank": per_rank_gbs, "cpu_affinity": affinity,
                "bound": "PCIe host->device copy of the int8 trials (chunks of 8192 trials, copy / kernel / copy-back "
                         "overlapped on two streams); the kernel itself is 100x faster than the link"}
         del xh
@@ -613,19 +697,18 @@ def main():
             "metric": METRIC, "value": value, "unit": "trials/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "int8", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "trials_per_gpu_per_step": B, "global_batch": world * B,
-                       "layout": "[B][C][T] int8 (module order)" if args.layout == "bct" else
-                                 "[B][T][C_ALIGN] int8 (Wolf order; rows that are not 16 or 64 bytes are transposed on the GPU "
-                                 "into a scratch, chunk by chunk, before the fused kernel: 2 launches per chunk)",
-                       "parallelism": f"trial-batch sharding x{world}",
-                       "l2_policy": f"input per step {B * C * T / 1e9:.2f} GB > 126 MB L2, no flush needed",
-                       "collective": ("none" if world == 1 else
-                                      "fused: kernel epilogue stores the logits into every rank's symmetric buffer over NVLink, "
-                                      "one barrier at the end" if peer is not None else "one NCCL all_gather of int8 logits per step"),
-                       "input": "int8" if xf is None else
-                                "float32 trials: quantize_input_kernel_v16 (trunc(clip(x/s,-1,1)*127), IEEE division) -> int8 forward -> "
-                                "dequantize_kernel; kernel_ms covers the three launches, the int8 copy is written and read once more",
-                       "kernel_path": net.last_path, "bit_exact_checked": None, "gather_checked": gather_checked},
+            "config": make_config(args, world, B),
+            "run": {"kernel_path": net.last_path, "bit_exact_checked": None, "gather_checked": gather_checked,
+                    "collective": ("none" if world == 1 else
+                                   ("fused: the kernel epilogue stores the logits into every rank's symmetric buffer over NVLink (all-gather), "
+                                    "one barrier at the end" if args.gather != "root" else
+                                    "fused: the kernel epilogue stores the logits into rank 0's symmetric buffer over NVLink (gather to root), "
+                                    "one barrier at the end") if peer is not None else
+                                   "none (--gather none: local logits only)" if args.gather == "none" else
+                                   "one NCCL all_gather of int8 logits per step"),
+                    "input": "int8" if xf is None else
+                             "float32 trials: quantize_input_kernel_v16 (trunc(clip(x/s,-1,1)*127), IEEE division) -> int8 forward -> "
+                             "dequantize_kernel; kernel_ms covers the three launches, the int8 copy is written and read once more"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": NCU_TRAFFIC_BYTES_PER_TRIAL * B if (net.last_kernel == "tc_forward_kernel" and args.shape == "64x480" and xf is None
                                                                              and args.layout == "bct") else None,
@@ -636,8 +719,12 @@ def main():
                          "kernel_ms": ms_kernel, "alg_bytes_per_trial": alg_bytes,
                          "note": KERNEL_NOTES.get(net.last_kernel, ""),
                          "tensor_pipe": tensor_pipe(net.last_kernel, C, T, B, ms_kernel, clocks)},
-            "gpu_launches": int(launches), "clocks": clocks, "e2e": e2e,
+            "gpu_launches": int(launches), "clocks": clocks, "e2e": e2e, "sustained": sustained,
         }
+        if sustained is not None:
+            sustained["roofline_frac"] = (B * alg_bytes * world / (sustained["ms_per_step"] * 1e-3) / 1e9) / (peak * world)
+        if per_rank is not None:
+            out["per_rank"] = per_rank
         if not args.no_cpu_baseline:
             cores = host_cores()
             n = 128 * cores
@@ -647,7 +734,7 @@ def main():
             out["cpu_baseline"] = {"value": tps, "unit": "trials/s", "cores": cores, "kind": kind,
                                    "sample": f"first {n} trials of the batch x 4 repeats, {cores} worker processes",
                                    "matches_gpu_logits": same}
-            out["config"]["bit_exact_checked"] = same
+            out["run"]["bit_exact_checked"] = same
         print(json.dumps(out))
     if world > 1:
         dist.barrier()

@@ -66,6 +66,17 @@ class ShardedInt8Net:
         return gather_logits(self.forward_local(x_local, **kw), n_total, self.group)
 
 
+def destination_ptrs(ptrs: List[int], rank: int, mode: str = "all", root: int = 0) -> List[int]:
+    """Destination buffers of one rank's kernel, own buffer first (the kernel's primary destination)."""
+    if mode == "all":
+        return [ptrs[rank]] + [p for r, p in enumerate(ptrs) if r != rank]
+    if mode == "root":
+        return [ptrs[rank]] if rank == root else [ptrs[rank], ptrs[root]]
+    if mode == "none":
+        return [ptrs[rank]]
+    raise ValueError("mode")
+
+
 class PeerGather:
     """All-gather fused into the kernel (mibmi_forward_int8_gather): every rank owns a `[n_total, N]` int8 buffer
     in CUDA symmetric memory; a rank's kernel stores the logits of its own trials into the same rows of ALL
@@ -78,8 +89,16 @@ class PeerGather:
 
     Raises RuntimeError when symmetric memory cannot be set up (the caller then uses `gather_logits`)."""
 
-    def __init__(self, net, n_total: int, group: Optional[dist.ProcessGroup] = None):
+    MODES = ("all", "root", "none")
+
+    def __init__(self, net, n_total: int, group: Optional[dist.ProcessGroup] = None, mode: str = "all", root: int = 0):
+        """mode 'all': every rank ends up with every rank's logits (all-gather, N - 1 remote 16-byte stores per quad);
+        'root': only rank `root`'s buffer is complete (a gather: one remote store per quad from the other ranks, none from the
+        root); 'none': local rows only (no remote store at all; isolates the cost of the peer stores in measurements)."""
         import torch.distributed._symmetric_memory as symm_mem
+        if mode not in self.MODES:
+            raise ValueError(f"mode must be one of {self.MODES}")
+        self.mode, self.root = mode, int(root)
         self.net = net
         self.group = group if group is not None else dist.group.WORLD
         self.world, self.rank = dist.get_world_size(self.group), dist.get_rank(self.group)
@@ -94,7 +113,7 @@ class PeerGather:
         if len(ptrs) != self.world:
             raise RuntimeError("symmetric memory rendezvous returned an unexpected number of peers")
         # own buffer first: the kernel's primary destination
-        self.ptrs = [ptrs[self.rank]] + [p for r, p in enumerate(ptrs) if r != self.rank]
+        self.ptrs = destination_ptrs(ptrs, self.rank, mode, self.root)
 
     def forward(self, x_local: torch.Tensor, **kw) -> None:
         if x_local.shape[0] != self.hi - self.lo:

@@ -58,3 +58,17 @@ def test_gather_logits_world2_gloo(n_total):
         assert p.exitcode == 0
     assert sorted(r[0] for r in res) == [0, 1]
     assert all(ok and shape == (n_total, 4) for _, ok, shape in res)
+
+
+def test_destination_ptrs_modes():
+    """Peer-store destinations of the fused gather: own buffer first; 'root' = a gather (one remote destination, none on the
+    root), 'all' = an all-gather (every peer), 'none' = local rows only."""
+    from mibminet_b200.sharding import destination_ptrs
+    ptrs = [100, 200, 300, 400]
+    assert destination_ptrs(ptrs, 2, "all") == [300, 100, 200, 400]
+    assert destination_ptrs(ptrs, 2, "root") == [300, 100]
+    assert destination_ptrs(ptrs, 0, "root") == [100]
+    assert destination_ptrs(ptrs, 3, "root", root=3) == [400]
+    assert destination_ptrs(ptrs, 1, "none") == [200]
+    with pytest.raises(ValueError):
+        destination_ptrs(ptrs, 1, "ring")
