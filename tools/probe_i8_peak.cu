@@ -16,12 +16,13 @@ __device__ __forceinline__ uint64_t desc(uint32_t a, uint32_t lbo, uint32_t sbo)
 
 __global__ void __launch_bounds__(128, 1) peak(long long iters, int N, long long* cycles_out) {
     extern __shared__ __align__(1024) uint8_t smem[];      // A: 128 x 32 B, B: N x 32 B (K-major core matrices, contents irrelevant)
-    __shared__ __align__(8) unsigned long long bar;
+    __shared__ __align__(8) unsigned long long bar[2];     // alternate: a barrier never runs more than one phase ahead of its waiter
     __shared__ uint32_t tmem_base_s;
     const int tid = threadIdx.x, warp = tid >> 5;
     for (int i = tid; i < (128 + 256) * 32; i += 128) smem[i] = (uint8_t)(i * 7 + 1);
     if (tid == 0) {
-        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(s32(&bar)));
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(s32(&bar[0])));
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(s32(&bar[1])));
         asm volatile("fence.mbarrier_init.release.cluster;");
     }
     if (warp == 0) {
@@ -37,26 +38,22 @@ __global__ void __launch_bounds__(128, 1) peak(long long iters, int N, long long
         const uint32_t idesc = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((128u >> 4) << 24);
         const uint64_t da = desc(s32(smem), 128, 256), db = desc(s32(smem) + 128 * 32, 128, 256);
         const long long t0 = clock64();
-        uint32_t phase = 0;
+        auto wait = [&](long long k) {       // completion of the commit of batch k (barrier k & 1, its (k >> 1)-th phase)
+            uint32_t done = 0;
+            while (!done)
+                asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                             : "=r"(done) : "r"(s32(&bar[k & 1])), "r"((uint32_t)((k >> 1) & 1)) : "memory");
+        };
         for (long long it = 0; it < iters; it++) {
 #pragma unroll 8
             for (int j = 0; j < 64; j++)
                 asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
                              "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%5, %5, %5, %5}, p;\n\t}"
                              ::"r"(tmem + (uint32_t)((j & 1) * 256)), "l"(da), "l"(db), "r"(idesc), "r"(1u), "r"(0u) : "memory");
-            asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.b64 [%0];" ::"r"(s32(&bar)) : "memory");
-            if (it >= 1) {          // wait for the commit of the previous batch: at most 128 instructions in flight
-                uint32_t done = 0;
-                while (!done)
-                    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
-                                 : "=r"(done) : "r"(s32(&bar)), "r"(phase));
-                phase ^= 1;
-            }
+            asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.b64 [%0];" ::"r"(s32(&bar[it & 1])) : "memory");
+            if (it >= 1) wait(it - 1);       // at most 128 instructions in flight
         }
-        uint32_t done = 0;
-        while (!done)
-            asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
-                         : "=r"(done) : "r"(s32(&bar)), "r"(phase));
+        if (iters > 0) wait(iters - 1);
         cycles_out[blockIdx.x] = clock64() - t0;
     }
     asm volatile("tcgen05.fence::before_thread_sync;");
