@@ -69,7 +69,7 @@ constexpr int kTcrL3Unroll = MIBMI_TCR_L3_UNROLL, kTcrL4Unroll = MIBMI_TCR_L4_UN
 #define MIBMI_TCR_RW 4
 #endif
 #ifndef MIBMI_TCR_RB
-#define MIBMI_TCR_RB 4                    // module order: rows of a realign warp in flight (two 16-byte loads each)
+#define MIBMI_TCR_RB 3                    // module order: rows of a realign warp in flight (two 16-byte loads each)
 #endif
 constexpr int kRAW = 12, kRBW = 8, kRCW = 4, kRRW = MIBMI_TCR_RW;
 constexpr int kRWarpB = kRAW, kRWarpC = kRAW + kRBW, kRWarpR = kRWarpC + kRCW, kRWarpP = kRWarpR + kRRW,
@@ -213,9 +213,13 @@ __device__ __forceinline__ void tcr_realign_store(const uint4& q0, const uint4& 
 // (row & 7) == k; `wait` (for the ring slot) is called after the first loads are in flight.  No lane is predicated off: in the last
 // part (7 chunks) the other lanes read bytes behind the row and write tiles of the ring slot that no MMA reads -- with a per-lane
 // predicate on the sixteen unrolled bodies ptxas kept the loaded words in local memory (2.8 KB of spills).
-template <class K, int O15, int MEM, int TW, int RB, class F>
-__device__ __forceinline__ void tcr_realign_part(uint32_t rl, const uint32_t (&xsw)[8], F&& wait) {
+template <class K, int O15, int MEM, int TW, int RB>
+__device__ __noinline__ void tcr_realign_part(uint32_t rl, uint32_t xl, uint32_t xbar, uint32_t xpar) {
     constexpr int NR = (K::C - MEM + TW - 1) / TW;
+    const uint32_t lane7 = threadIdx.x & 7;
+    uint32_t xsw[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) xsw[k] = xl + ((lane7 ^ k) << 4);
 #pragma unroll
     for (int j0 = 0; j0 < NR; j0 += RB) {
         uint4 q0[RB], q1[RB];
@@ -227,7 +231,7 @@ __device__ __forceinline__ void tcr_realign_part(uint32_t rl, const uint32_t (&x
                 q1[i] = tcr_lds128a(rl + (src0 & ~15) + 16);
             }
         }
-        if (j0 == 0) wait();
+        if (j0 == 0) mbar_wait_mode<MIBMI_TCR_WAIT>(xbar, xpar, MIBMI_TCR_SLEEP_LONG_NS);
 #pragma unroll
         for (int i = 0; i < RB; i++) {
             const int c = MEM + TW * (j0 + i), src0 = O15 + c * K::T;
@@ -490,19 +494,15 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
                 // 32 h .. 32 h + 31 of every row, lane = chunk; rows mem, mem + TW, ... of the team member, RB rows in flight.
                 // The code is specialised on (first-byte offset of the trial, member): see tcr_realign_part
                 constexpr int RB = MIBMI_TCR_RB;
-                const uint32_t xl = smem_u32(xs) + (lane >> 3) * K::TILE_PITCH, lane7 = lane & 7;
-                uint32_t xsw[8];
-#pragma unroll
-                for (int k = 0; k < 8; k++) xsw[k] = xl + ((lane7 ^ k) << 4);
+                const uint32_t xl = smem_u32(xs) + (lane >> 3) * K::TILE_PITCH;
                 const uint32_t rl = smem_u32(raw) + 512 * h + 16 * lane;
-                auto wait = [&]() { RWAITL(1, xbar, xpar); };
                 static_assert(K::TRIAL_BYTES % 2 == 0 && TW == 2, "first-byte offsets are even; two members per team");
                 if (32 * h + lane < K::CHUNKS + 1)              // last part: 8 of 32 lanes (a branch around the body, no predicates inside)
                 switch ((o15 >> 1) * 2 + mem) {
-#define MIBMI_RCASE(v) case v: tcr_realign_part<K, 2 * (v / 2), v % 2, TW, RB>(rl, xsw, wait); break;
+#define MIBMI_RCASE(v) case v: tcr_realign_part<K, 2 * (v / 2), v % 2, TW, RB>(rl, xl, xbar, xpar); break;
                     MIBMI_RCASE(0) MIBMI_RCASE(1) MIBMI_RCASE(2) MIBMI_RCASE(3) MIBMI_RCASE(4) MIBMI_RCASE(5) MIBMI_RCASE(6) MIBMI_RCASE(7)
                     MIBMI_RCASE(8) MIBMI_RCASE(9) MIBMI_RCASE(10) MIBMI_RCASE(11) MIBMI_RCASE(12) MIBMI_RCASE(13) MIBMI_RCASE(14)
-                    default: tcr_realign_part<K, 14, 1, TW, RB>(rl, xsw, wait); break;
+                    default: tcr_realign_part<K, 14, 1, TW, RB>(rl, xl, xbar, xpar); break;
 #undef MIBMI_RCASE
                 }
             }
@@ -559,8 +559,9 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
             for (int j = 0; j < K::G; j++) RWAIT(0, sbase + K::BAR_Y1_FULL + 8 * (4 * buf + j), (gq >> 1) & 1);
             tc_fence_after();
             const uint32_t a_lob = a_lo0 + ((buf * K::YBUF) >> 4);
-#pragma unroll
-            for (int bt = 0; bt < 8; bt++) {
+#pragma unroll 2
+            for (int bt = 0; bt < 8; bt++) {          // two batches per iteration (the TMEM half is a compile-time constant); unrolled 8 x
+                                                      // this loop alone was 800 instructions of an instruction cache that holds ~3000
                 const int h = bt & 1;
                 const int use = gq * 4 + (bt >> 1);                         // how often this half has been used before
                 RWAIT(2, sbase + K::BAR_W2_FULL + 8 * wst, wuse & 1);
