@@ -13,11 +13,6 @@
 //     i.e. "the next row": the Hankel view) against a Toeplitz operand with reversed output order whose core matrices overlap
 //     (PipeNet::w2umma32; both verified on the box with tools/probe_umma3.cu).  A trial takes 37 rows, a group of G = 3 trials
 //     = 111 rows = ONE tile of 128 rows: 16 channels x 3 k-steps = 48 instructions per group (96 with N = 16);
-//   * the y1 buffer is DOUBLE (two groups): the layer-1 epilogue of group g + 1 overlaps the layer-2 MMAs / epilogue of group g
-//     (round 2e: with a single buffer the two phases alternated, 5.3 k + 4.9 k cycles per group).  The shared memory for it comes
-//     from (i) operand tiles handed from R to M1 in PARTS of a trial through a two-slot ring instead of two whole trials,
-//     (ii) the layer-2 Toeplitz operands (28 KB) streamed from global memory (L2) by the producer warp, one batch of two
-//     channels per bulk copy, three stages, (iii) the layer-3 / 5 fragments read through L1 instead of from shared memory;
 //   * layers 3-5 of a trial run in ONE warp (private y3 / y4), as T/8 = 140 needs 9 blocks of 16 samples.
 // One persistent CTA per SM, 31 warps:
 //   A  0-11  layer-1 epilogue (3 warps per TMEM lane quarter)      layer1.c:96-104
@@ -68,9 +63,6 @@ constexpr int kTcrL3Unroll = MIBMI_TCR_L3_UNROLL, kTcrL4Unroll = MIBMI_TCR_L4_UN
 #ifndef MIBMI_TCR_RW
 #define MIBMI_TCR_RW 4
 #endif
-#ifndef MIBMI_TCR_RB
-#define MIBMI_TCR_RB 3                    // module order: rows of a realign warp in flight (two 16-byte loads each)
-#endif
 constexpr int kRAW = 12, kRBW = 8, kRCW = 4, kRRW = MIBMI_TCR_RW;
 constexpr int kRWarpB = kRAW, kRWarpC = kRAW + kRBW, kRWarpR = kRWarpC + kRCW, kRWarpP = kRWarpR + kRRW,
               kRWarpM1 = kRWarpP + 1, kRWarpM2 = kRWarpP + 2;
@@ -84,62 +76,56 @@ struct RCfg {
     static constexpr int CA = (C + 3) / 4 * 4;                                  // bytes per sample in Wolf order
     static constexpr int TRIAL_BYTES = WOLF ? T * CA : C * T;
     static constexpr int TILES = (T + 127) / 128, UNITS = (T + 31) / 32, CHUNKS = (T + 15) / 16;
-    // layer-1 operand tiles.  WOLF = 0: MN-major [C][128 samples], 128-byte swizzle, rows 24..31 of a tile alias the bytes behind
-    // it (zero weights).  WOLF = 1: K-major [2 chunks][128 samples][16 B].  R hands them to M1 in parts of PART_TILES tiles
-    // through a ring of two slots (WOLF = 0: a part = one realign pass of 32 chunks = 4 tiles)
+    // layer-1 operand tiles.  WOLF = 0: MN-major [C][128 samples], 128-byte swizzle, rows 24..31 of a tile may alias the next
+    // tile (zero weights); the whole trial per stage.  WOLF = 1: K-major [2 chunks][128 samples][16 B]; half a trial per stage.
     static constexpr int TILE_PITCH = WOLF ? 4096 : (C <= 24 ? 3072 : 4096);
-    static constexpr int PART_TILES = WOLF ? 2 : 4;
-    static constexpr int PARTS = (TILES + PART_TILES - 1) / PART_TILES;         // hand-offs R -> M1 per trial
-    static constexpr int XS_BYTES = ((PART_TILES * TILE_PITCH + 1023) / 1024) * 1024;
-    static constexpr int RAW_BYTES = ((TRIAL_BYTES + 15 + 48 + 15) / 16) * 16;  // + misalignment + the realign warps' read-ahead
+    static constexpr int PARTS = WOLF ? 2 : 1;                                  // hand-offs R -> M1 per trial
+    static constexpr int PART0_TILES = WOLF ? 4 : TILES;                        // tiles of part 0 (part 1: the rest)
+    static constexpr int PART_TILES_MAX = WOLF ? (TILES - 4 > 4 ? TILES - 4 : 4) : TILES;
+    static constexpr int XS_BYTES = ((PART_TILES_MAX * TILE_PITCH + 1023) / 1024) * 1024;
+    static constexpr int RAW_BYTES = ((TRIAL_BYTES + 15 + 48 + 127) / 128) * 128;   // + misalignment + the realign warps' read-ahead
     static constexpr int T8 = T / 8, T64 = T8 / 8;
     static constexpr int VROWS = (8 * T8) / 32;                               // layer-2 rows (32 conv outputs) per trial
     static constexpr int SLOT = ((32 + T + 31) / 32) * 32, SROWS = SLOT / 32;   // y1 bytes / rows per trial: 32 zeros | T | zeros
     static constexpr int GROWS = G * SROWS;
-    static constexpr int YBUF = G * SLOT;                                       // one group in a y1 row; the row holds two groups
-    // y1 row of one filter (two groups).  stmatrix writes 8 rows x 16 B per phase at chunk (a >> 4) ^ ((a >> 7) & 1) (the 32-byte
-    // swizzle): the eight rows hit eight different 16-byte bank groups iff pitch / 16 = 2 (mod 4) (an odd pitch / 16, right for
-    // the unswizzled layout, costs 1.5 - 2 wavefronts per phase here: ncu r2e / r2i)
-    static constexpr int CHS = 16 * tcr_pitch16((2 * YBUF + 15) / 16);
+    // y1 row of one filter.  stmatrix writes 8 rows x 16 B per phase at chunk (a >> 4) ^ ((a >> 7) & 1) (the 32-byte swizzle of the
+    // layer-2 operand): the eight rows fall into eight different 16-byte bank groups iff pitch / 16 = 2 (mod 4).  (An odd pitch / 16,
+    // the rule for an unswizzled layout, cost 6 wavefronts per stmatrix.x4 instead of 4: ncu r2e, 72 excess wavefronts per trial.)
+    static constexpr int CHS = 16 * tcr_pitch16((G * SLOT + 15) / 16);
     static constexpr int NW3 = (T8 + 15) / 16, Y2S = 16 * (NW3 + 1), Y2_TRIAL = 16 * Y2S;
     static constexpr int Y3CH = 2 * ((NW3 + 1) / 2), Y3S = 16 * (Y3CH + 1), Y3_BYTES = 16 * Y3S;
     static constexpr int NST = (T64 + 3) / 4, T64P = (T64 + 1) / 2 * 2, KST5 = T64P / 2;
     static constexpr int Y4_BYTES = ((16 * T64P + 15) / 16) * 16;
     // TMEM columns: layer-1 accumulators of two trials, then two layer-2 halves of 2 channels x 32 outputs
     static constexpr int TM_L1_TRIAL = 16 * TILES, TM_L2 = 2 * TM_L1_TRIAL, TM_L2_HALF = 64;
-    // layer-2 Toeplitz operands: ring of W2_STAGES batches of two channels, filled by bulk copies from PipeNet::w2umma32
-    static constexpr int W2_STAGES = 3, W2_BATCH = 2 * kW2U32;
     // barriers
     static constexpr int BAR_RAW_FULL = 0, BAR_RAW_EMPTY = 16, BAR_X_FULL = 32, BAR_X_EMPTY = 48, BAR_T1_FULL = 64,
-                         BAR_T1_EMPTY = 80, BAR_T2_FULL = 96, BAR_T2_EMPTY = 112, BAR_Y2_FULL = 128, BAR_Y2_EMPTY = 144,
-                         BAR_TILE_DONE = 160 /* 2 */, BAR_W2_FULL = 176 /* 3 */, BAR_W2_EMPTY = 200 /* 3 */,
-                         BAR_Y1_FULL = 768 /* [2 buffers][4] */;
+                         BAR_T1_EMPTY = 80, BAR_Y1_FULL = 96 /* G */, BAR_TILE_DONE = 128, BAR_T2_FULL = 160,
+                         BAR_T2_EMPTY = 176, BAR_Y2_FULL = 192 /* 2 */, BAR_Y2_EMPTY = 232, BAR_END = 248;
     // shared memory map
     static constexpr int OFF_TMEM = 248, OFF_C2 = 256, OFF_W1 = 1024, OFF_W2 = 2048;
-    static constexpr int OFF_XS = ((OFF_W2 + W2_STAGES * W2_BATCH + 1023) / 1024) * 1024;
+    static constexpr int OFF_XS = ((OFF_W2 + 16 * kW2U32 + 1023) / 1024) * 1024;
     static constexpr int OFF_RAW = OFF_XS + 2 * XS_BYTES;
-    static constexpr int OFF_Y1 = ((OFF_RAW + 2 * RAW_BYTES + 127) / 128) * 128;
+    static constexpr int OFF_Y1 = OFF_RAW + 2 * RAW_BYTES;
     static constexpr int OFF_Y2 = OFF_Y1 + 16 * CHS;
     static constexpr int OFF_Y3 = OFF_Y2 + 2 * G * Y2_TRIAL;
     static constexpr int OFF_Y4 = OFF_Y3 + kRCW * Y3_BYTES;
-    static constexpr int SMEM = ((OFF_Y4 + kRCW * Y4_BYTES + 127) / 128) * 128;
+    static constexpr int OFF_W3 = ((OFF_Y4 + kRCW * Y4_BYTES + 127) / 128) * 128;      // w3frag [16][4][32] words
+    static constexpr int OFF_W5 = OFF_W3 + 16 * 4 * 32 * 4;                             // w5frag [KST5][2][32] words
+    static constexpr int SMEM = ((OFF_W5 + KST5 * 2 * 32 * 4 + 127) / 128) * 128;
     static_assert(C <= 32 && CA <= 32, "one k-step of 32 channels");
     static_assert(!WOLF || CA == 24, "Wolf-order expansion is written for rows of 24 bytes");
     static_assert((8 * T8) % 32 == 0 && T8 % 4 == 0, "whole layer-2 rows of 32 outputs");
     static_assert(SLOT - 32 - T >= 8 * T8 + 32 - T, "right padding of layer 2 inside the slot");
     static_assert(GROWS <= 128, "a group is one MMA tile");
-    static_assert((CHS / 16) % 4 == 2 && CHS >= 2 * YBUF, "conflict-free stmatrix under the 32-byte swizzle");
+    static_assert((CHS / 16) % 4 == 2 && CHS >= G * SLOT, "conflict-free stmatrix under the 32-byte swizzle");
     static_assert(G <= 4, "barrier slots");
-    static_assert(PARTS >= 2 && kRRW % 2 == 0, "two teams of realign warps, each with a part in every trial");
     static_assert(TM_L2 + 2 * TM_L2_HALF <= 512, "TMEM map");
     static_assert(NW3 <= 16 && KST5 <= kPipeMaxKst5, "layer 3 / 5 limits");
     static_assert(XS_BYTES % 1024 == 0 && OFF_XS % 1024 == 0, "swizzle atoms are 1024-byte aligned");
-    static_assert(WOLF || PART_TILES == 4, "module order: a part is one realign pass of 32 chunks");
-    static_assert(YBUF % 32 == 0 && W2_BATCH % 16 == 0 && RAW_BYTES % 16 == 0, "alignment of the layer-2 rows / bulk copies");
-    static_assert(BAR_W2_EMPTY + 8 * W2_STAGES <= OFF_TMEM && BAR_Y1_FULL + 64 <= OFF_W1, "barrier area");
     static_assert(SMEM <= 227 * 1024, "shared memory");
-    __host__ __device__ static constexpr int part_first(int h) { return h * PART_TILES; }
-    __host__ __device__ static constexpr int part_tiles(int h) { return TILES - h * PART_TILES < PART_TILES ? TILES - h * PART_TILES : PART_TILES; }
+    __host__ __device__ static constexpr int part_first(int h) { return h == 0 ? 0 : PART0_TILES; }
+    __host__ __device__ static constexpr int part_tiles(int h) { return PARTS == 1 ? TILES : (h == 0 ? PART0_TILES : TILES - PART0_TILES); }
 };
 
 template <bool FAST>
@@ -171,71 +157,33 @@ __device__ __forceinline__ uint4 tcr_lds128(const uint8_t* p) {
     asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(smem_u32(p)));
     return v;
 }
-__device__ __forceinline__ uint4 tcr_lds128a(uint32_t a) {
-    uint4 v;
-    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a));
-    return v;
-}
-__device__ __forceinline__ void tcr_sts128a(uint32_t a, const uint4& v) {
-    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
-}
 __device__ __forceinline__ uint2 tcr_lds64(const uint8_t* p) {
     uint2 v;
     asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(smem_u32(p)));
     return v;
 }
-// WOLF = 0: 32 chunks of 16 bytes (= 4 tiles) of one row: lane = chunk 32 pass + lane.  q0 / q1 are the two aligned 16-byte
-// words that hold the chunk (loaded by the caller, several rows in flight); K4 = word offset, sh = bit shift inside a word
-template <int K4>
-__device__ __forceinline__ uint4 tcr_shift_chunk(const uint4& q0, const uint4& q1, int sh) {
-    const uint32_t w[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
-    uint4 o;
-    o.x = __funnelshift_r(w[K4], w[K4 + 1], sh);
-    o.y = __funnelshift_r(w[K4 + 1], w[K4 + 2], sh);
-    o.z = __funnelshift_r(w[K4 + 2], w[K4 + 3], sh);
-    o.w = __funnelshift_r(w[K4 + 3], w[K4 + 4], sh);
-    return o;
-}
-__device__ __forceinline__ void tcr_realign_store(const uint4& q0, const uint4& q1, int src0, uint32_t dst) {
-    const int sh = 8 * (src0 & 3);                         // src0 (first byte of the row) is a compile-time constant at the call site
-    switch ((src0 >> 2) & 3) {
-        case 0: tcr_sts128a(dst, tcr_shift_chunk<0>(q0, q1, sh)); break;
-        case 1: tcr_sts128a(dst, tcr_shift_chunk<1>(q0, q1, sh)); break;
-        case 2: tcr_sts128a(dst, tcr_shift_chunk<2>(q0, q1, sh)); break;
-        default: tcr_sts128a(dst, tcr_shift_chunk<3>(q0, q1, sh)); break;
-    }
-}
-
-// WOLF = 0, one part (32 chunks of every row) for team member MEM (rows MEM, MEM + TW, ...) of a trial whose first byte sits
-// O15 bytes above a 16-byte boundary.  O15 and the row are compile-time constants, so every load offset, word offset and shift is
-// an immediate: 2 LDS.128 + 4 SHF + 1 STS.128 (+ 1 address add) per row and lane -- the run-time version spent 34 instructions per
-// row, and the realign warps are bound by their own instruction latency.  xsw[k] = destination of the lane's chunk in a row with
-// (row & 7) == k; `wait` (for the ring slot) is called after the first loads are in flight.  No lane is predicated off: in the last
-// part (7 chunks) the other lanes read bytes behind the row and write tiles of the ring slot that no MMA reads -- with a per-lane
-// predicate on the sixteen unrolled bodies ptxas kept the loaded words in local memory (2.8 KB of spills).
-template <class K, int O15, int MEM, int TW, int RB>
-__device__ __noinline__ void tcr_realign_part(uint32_t rl, uint32_t xl, uint32_t xbar, uint32_t xpar) {
-    constexpr int NR = (K::C - MEM + TW - 1) / TW;
-    const uint32_t lane7 = threadIdx.x & 7;
-    uint32_t xsw[8];
+// WOLF = 0: one row of T samples: lane = 16-byte chunk (+ 32 per pass); all loads of the row are issued before the shifts
+template <class K, int K4>
+__device__ __forceinline__ void tcr_realign_row(const uint8_t* rbase, uint8_t* xrow, int c, int sh, int lane) {
+    constexpr int P = (K::CHUNKS + 31) / 32;
+    uint4 q0[P], q1[P];
 #pragma unroll
-    for (int k = 0; k < 8; k++) xsw[k] = xl + ((lane7 ^ k) << 4);
-#pragma unroll
-    for (int j0 = 0; j0 < NR; j0 += RB) {
-        uint4 q0[RB], q1[RB];
-#pragma unroll
-        for (int i = 0; i < RB; i++) {
-            const int c = MEM + TW * (j0 + i), src0 = O15 + c * K::T;
-            if (j0 + i < NR) {
-                q0[i] = tcr_lds128a(rl + (src0 & ~15));
-                q1[i] = tcr_lds128a(rl + (src0 & ~15) + 16);
-            }
+    for (int p = 0; p < P; p++)
+        if (32 * p + 31 < K::CHUNKS || lane + 32 * p < K::CHUNKS) {
+            q0[p] = tcr_lds128(rbase + 512 * p);          // kept 128 bits wide: the narrower loads the compiler would pick for
+            q1[p] = tcr_lds128(rbase + 512 * p + 16);     // the 5 words in use are 4-way bank conflicted at this lane stride
         }
-        if (j0 == 0) mbar_wait_mode<MIBMI_TCR_WAIT>(xbar, xpar, MIBMI_TCR_SLEEP_LONG_NS);
 #pragma unroll
-        for (int i = 0; i < RB; i++) {
-            const int c = MEM + TW * (j0 + i), src0 = O15 + c * K::T;
-            if (j0 + i < NR) tcr_realign_store(q0[i], q1[i], src0, xsw[c & 7] + c * 128);
+    for (int p = 0; p < P; p++) {
+        const int jj = lane + 32 * p;
+        if (32 * p + 31 < K::CHUNKS || jj < K::CHUNKS) {
+            const uint32_t w[8] = {q0[p].x, q0[p].y, q0[p].z, q0[p].w, q1[p].x, q1[p].y, q1[p].z, q1[p].w};
+            uint4 o;
+            o.x = __funnelshift_r(w[K4], w[K4 + 1], sh);
+            o.y = __funnelshift_r(w[K4 + 1], w[K4 + 2], sh);
+            o.z = __funnelshift_r(w[K4 + 2], w[K4 + 3], sh);
+            o.w = __funnelshift_r(w[K4 + 3], w[K4 + 4], sh);
+            *reinterpret_cast<uint4*>(xrow + (jj >> 3) * K::TILE_PITCH + (((jj & 7) ^ (c & 7)) << 4)) = o;
         }
     }
 }
@@ -249,26 +197,18 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int g = lane >> 2, q = lane & 3;
     const uint32_t sbase = smem_u32(smem);
-    // Trials are dealt out in CLASSES b = cls (mod 8): the byte offset of a trial inside its 16-byte granule, (b TRIAL_BYTES) & 15,
-    // depends on b & 7 only, so a CTA that keeps to one class sees ONE offset for the whole launch and runs one of the sixteen
-    // specialised realign bodies (tcr_realign_part) -- with all of them in rotation the kernel does not fit the instruction cache
-    // (ncu r2k: icc hit rate 74 %, 4 no-instruction stalls per issue).  CTA i: class i & 7, the ci = i >> 3 -th CTA of its class;
-    // a group = G consecutive trials of the class.  Fewer than 8 CTAs (tiny batches): one class, any offset (still correct)
-    const int ncls = gridDim.x >= 8 ? 8 : 1;
-    const int cls = blockIdx.x % ncls, ci = blockIdx.x / ncls;
-    const int ncta = ((int)gridDim.x - cls + ncls - 1) / ncls;                                             // CTAs of this class
-    const long long mcls = B > cls ? (B - cls + ncls - 1) / ncls : 0;                                      // trials of this class
-    const long long ngroups_cls = (mcls + K::G - 1) / K::G;
-    const int ng = ci < ngroups_cls ? (int)((ngroups_cls - ci + ncta - 1) / ncta) : 0;                     // groups of this CTA
+    const long long ngroups_total = (B + K::G - 1) / K::G;
+    const long long firstg = blockIdx.x, strideg = gridDim.x;
+    const int ng = firstg < ngroups_total ? (int)((ngroups_total - firstg + strideg - 1) / strideg) : 0;   // groups of this CTA
     const int ntr = K::G * ng;                                                                              // trial slots
-    auto trial_of = [&](int n) -> long long { return cls + (long long)ncls * (K::G * (ci + (long long)(n / K::G) * ncta) + (n % K::G)); };
+    auto trial_of = [&](int n) -> long long { return K::G * (firstg + (long long)(n / K::G) * strideg) + (n % K::G); };
 
     // ---- prologue ------------------------------------------------------------------------------------
     if (tid == 0) {
         for (int i = 0; i < 2; i++) {
             mbar_init(sbase + K::BAR_RAW_FULL + 8 * i, 1);
             mbar_init(sbase + K::BAR_RAW_EMPTY + 8 * i, kRRW);
-            mbar_init(sbase + K::BAR_X_FULL + 8 * i, kRRW / 2);      // the team of realign warps that owns ring slot i
+            mbar_init(sbase + K::BAR_X_FULL + 8 * i, kRRW);
             mbar_init(sbase + K::BAR_X_EMPTY + 8 * i, 1);            // commit of M1
             mbar_init(sbase + K::BAR_T1_FULL + 8 * i, 1);            // commit of M1
             mbar_init(sbase + K::BAR_T1_EMPTY + 8 * i, kRAW);
@@ -276,17 +216,15 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
             mbar_init(sbase + K::BAR_T2_EMPTY + 8 * i, kRBW / 2);
             mbar_init(sbase + K::BAR_Y2_EMPTY + 8 * i, K::G);
             mbar_init(sbase + K::BAR_Y2_FULL + 8 * i, kRBW);
-            mbar_init(sbase + K::BAR_TILE_DONE + 8 * i, 1);          // commit of M2: y1 buffer i has been read by the tensor core
-            for (int j = 0; j < K::G; j++) mbar_init(sbase + K::BAR_Y1_FULL + 8 * (4 * i + j), kRAW);
         }
-        for (int i = 0; i < K::W2_STAGES; i++) {
-            mbar_init(sbase + K::BAR_W2_FULL + 8 * i, 1);
-            mbar_init(sbase + K::BAR_W2_EMPTY + 8 * i, 1);           // commit of M2
-        }
+        for (int j = 0; j < K::G; j++) mbar_init(sbase + K::BAR_Y1_FULL + 8 * j, kRAW);
+        mbar_init(sbase + K::BAR_TILE_DONE, 1);                      // commit of M2: the y1 buffer of the group has been read
         mbar_fence_init();
     }
     for (int i = tid; i < 16 * 32 / 4; i += kRThreads)
         reinterpret_cast<uint32_t*>(smem + K::OFF_W1)[i] = reinterpret_cast<const uint32_t*>(net->w1umma)[i];
+    for (int i = tid; i < 16 * kW2U32 / 16; i += kRThreads)
+        reinterpret_cast<uint4*>(smem + K::OFF_W2)[i] = reinterpret_cast<const uint4*>(net->w2umma32)[i];
     for (int i = tid; i < 16 * 8; i += kRThreads) {
         const int k = i >> 3, f = i & 7;
         reinterpret_cast<int*>(smem + K::OFF_C2)[i] = f == 0 ? net->thr2[k] : f == 1 ? net->sig2[k] : f == 2 ? net->soff2[k]
@@ -294,8 +232,12 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
     }
     {
         uint4* z = reinterpret_cast<uint4*>(smem + K::OFF_XS);     // tiles (rows >= C are read with zero weights), y1 gaps, y2 / y3 padding
-        for (int i = tid; i < (K::SMEM - K::OFF_XS) / 16; i += kRThreads) z[i] = make_uint4(0, 0, 0, 0);
+        for (int i = tid; i < (K::OFF_W3 - K::OFF_XS) / 16; i += kRThreads) z[i] = make_uint4(0, 0, 0, 0);
     }
+    for (int i = tid; i < 16 * 4 * 32; i += kRThreads)
+        reinterpret_cast<uint32_t*>(smem + K::OFF_W3)[i] = (&net->w3frag[0][0][0])[i];
+    for (int i = tid; i < K::KST5 * 2 * 32; i += kRThreads)
+        reinterpret_cast<uint32_t*>(smem + K::OFF_W5)[i] = (&net->w5frag[0][0][0])[i];
     if (warp == kRWarpM1) tmem_alloc(sbase + K::OFF_TMEM, 512);
     fence_proxy_async();
     tc_fence_before();
@@ -326,10 +268,10 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
         const uint32_t st_off = sbase + K::OFF_Y1 + ((lane & 7) + 8 * ((lane >> 3) & 1)) * K::CHS + 16 * (lane >> 4) + 32;
         const int qi = warp & 3, a3 = warp >> 2;
         for (int n = 0; n < ntr; n++) {
-            const int gq = n / K::G, j = n - gq * K::G, ab = n & 1, buf = gq & 1;
+            const int gq = n / K::G, j = n - gq * K::G, ab = n & 1;
             RWAIT(0, sbase + K::BAR_T1_FULL + 8 * ab, (n >> 1) & 1);
             tc_fence_after();
-            const uint32_t yb = st_off + K::YBUF * buf + K::SLOT * j;
+            const uint32_t yb = st_off + K::SLOT * j;
             const long long b = trial_of(n);
             // the warp's tiles jt0, jt0 + 3, ...: the TMEM load of the next unit is in flight while this one is requantised
             const int jt0 = (a3 + n) % 3;
@@ -339,8 +281,8 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
                 tmem_ld_16x256b_x2(r[0][0], ta0 + 16 * jt0);
                 tmem_ld_16x256b_x2(r[0][1], ta0 + 16 * jt0 + (16u << 16));
             }
-            // y1 buffer `buf` was last used by group gq - 2: its layer-2 MMAs must have read it (one commit per group)
-            RWAITL(1, sbase + K::BAR_TILE_DONE + 8 * buf, ((gq >> 1) & 1) ^ 1);
+            // the y1 buffer is single: the layer-2 MMAs of the previous group must have read it (one commit per group)
+            RWAITL(1, sbase + K::BAR_TILE_DONE, (gq & 1) ^ 1);
 #pragma unroll
             for (int it = 0; it < (K::TILES + 2) / 3; it++) {
                 const int jt = jt0 + 3 * it, u = 4 * jt + qi;
@@ -387,7 +329,7 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
             __syncwarp();
             if (lane == 0) {
                 mbar_arrive(sbase + K::BAR_T1_EMPTY + 8 * ab);
-                mbar_arrive(sbase + K::BAR_Y1_FULL + 8 * (4 * buf + j));
+                mbar_arrive(sbase + K::BAR_Y1_FULL + 8 * j);
             }
         }
     } else if (warp == kRWarpP) {
@@ -396,122 +338,91 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
         //    read: the copy of the LAST trial of the batch stops at the 16-byte boundary below its end and the lanes
         //    fetch the remaining <= 15 bytes with byte loads
         // =====================================================================================
-        //    The same warp streams the layer-2 Toeplitz operands: batch w (two channels, 3.5 KB of PipeNet::w2umma32, an L2 hit)
-        //    goes into ring stage w % 3 as soon as the MMAs of batch w - 3 have been committed.  Both queues are polled
-        //    without blocking so that neither holds the other up
         const unsigned long long total = (unsigned long long)B * K::TRIAL_BYTES;
-        const int wtotal = 8 * ng;
-        int n = 0, w = 0, wst = 0, wuse = 0;            // next trial; next W2 batch, its ring stage and how often the stage was used
-        while (n < ntr || w < wtotal) {
-            bool progress = false;
-            if (w < wtotal && __shfl_sync(0xffffffffu, (int)mbar_test(sbase + K::BAR_W2_EMPTY + 8 * wst, (wuse & 1) ^ 1), 0)) {
-                if (lane == 0) {
-                    const uint32_t bar = sbase + K::BAR_W2_FULL + 8 * wst;
-                    mbar_expect_tx(bar, K::W2_BATCH);
-                    bulk_g2s(sbase + K::OFF_W2 + wst * K::W2_BATCH, net->w2umma32 + (w & 7) * K::W2_BATCH, K::W2_BATCH, bar);
-                }
-                w++;
-                if (++wst == K::W2_STAGES) { wst = 0; wuse++; }
-                progress = true;
-            }
+        for (int n = 0; n < ntr; n++) {
             const int st = n & 1;
-            if (n < ntr && __shfl_sync(0xffffffffu, (int)mbar_test(sbase + K::BAR_RAW_EMPTY + 8 * st, ((n >> 1) & 1) ^ 1), 0)) {
-                const long long b = trial_of(n);
-                const uint32_t bar = sbase + K::BAR_RAW_FULL + 8 * st;
-                if (b < B) {
-                    const unsigned long long o = (unsigned long long)b * K::TRIAL_BYTES;
-                    const unsigned long long a0 = o & ~15ull;
-                    unsigned long long a1 = (o + K::TRIAL_BYTES + 15) & ~15ull;
-                    if (a1 > total) {                                  // warp-uniform: only the last trial of the batch
-                        a1 = total & ~15ull;
-                        if (a1 + lane < total) smem[K::OFF_RAW + st * K::RAW_BYTES + (a1 - a0) + lane] = (uint8_t)x[a1 + lane];
-                        __syncwarp();                                  // the byte stores are ordered before lane 0's arrive (release)
-                    }
-                    if (lane == 0) {
-                        const uint32_t len = (uint32_t)(a1 - a0);
-                        mbar_expect_tx(bar, len);
-                        bulk_g2s(sbase + K::OFF_RAW + st * K::RAW_BYTES, x + a0, len, bar);
-                    }
-                } else if (lane == 0) {
-                    mbar_arrive(bar);     // padding trial of the last group: nothing to read
+            RWAITL(0, sbase + K::BAR_RAW_EMPTY + 8 * st, ((n >> 1) & 1) ^ 1);
+            const long long b = trial_of(n);
+            const uint32_t bar = sbase + K::BAR_RAW_FULL + 8 * st;
+            if (b < B) {
+                const unsigned long long o = (unsigned long long)b * K::TRIAL_BYTES;
+                const unsigned long long a0 = o & ~15ull;
+                unsigned long long a1 = (o + K::TRIAL_BYTES + 15) & ~15ull;
+                if (a1 > total) {                                  // warp-uniform: only the last trial of the batch
+                    a1 = total & ~15ull;
+                    if (a1 + lane < total) smem[K::OFF_RAW + st * K::RAW_BYTES + (a1 - a0) + lane] = (uint8_t)x[a1 + lane];
+                    __syncwarp();                                  // the byte stores are ordered before lane 0's arrive (release)
                 }
-                __syncwarp();
-                n++;
-                progress = true;
+                if (lane == 0) {
+                    const uint32_t len = (uint32_t)(a1 - a0);
+                    mbar_expect_tx(bar, len);
+                    bulk_g2s(sbase + K::OFF_RAW + st * K::RAW_BYTES, x + a0, len, bar);
+                }
+            } else if (lane == 0) {
+                mbar_arrive(bar);     // padding trial of the last group: nothing to read
             }
-            if (!progress) __nanosleep(MIBMI_TCR_SLEEP_NS);
+            __syncwarp();
         }
     } else if (warp >= kRWarpR && warp < kRWarpP) {
         // =====================================================================================
         // R: raw bytes -> layer-1 operand tiles
         // =====================================================================================
-        //    Two teams of kRRW / 2 warps; team t builds the parts that go into ring slot t (every other part), so the fixed latency
-        //    of a hand-off (barrier probe, load latency, membar + proxy fence, arrive: about 500 cycles) of one team overlaps the
-        //    other team's.  The loads of a part are issued BEFORE the slot is waited for (they do not depend on it)
-        constexpr int TW = kRRW / 2;
-        const int rw = warp - kRWarpR, team = rw / TW, mem = rw - team * TW;
-        int cur_n = -1;
-        for (int pc = team; pc < ntr * K::PARTS; pc += 2) {
-            const int n = pc / K::PARTS, h = pc - n * K::PARTS, st = n & 1;
-            if (n != cur_n) {
-                RWAIT(0, sbase + K::BAR_RAW_FULL + 8 * st, (n >> 1) & 1);
-                cur_n = n;
-            }
+        const int rw = warp - kRWarpR;
+        for (int n = 0; n < ntr; n++) {
+            const int st = n & 1;
+            RWAIT(0, sbase + K::BAR_RAW_FULL + 8 * st, (n >> 1) & 1);
             const long long b = trial_of(n);
             const int o15 = (int)(((unsigned long long)b * K::TRIAL_BYTES) & 15);
             const uint8_t* raw = smem + K::OFF_RAW + st * K::RAW_BYTES;
-            uint8_t* xs = smem + K::OFF_XS + team * K::XS_BYTES;
-            const uint32_t xbar = sbase + K::BAR_X_EMPTY + 8 * team, xpar = ((pc >> 1) & 1) ^ 1;
-            if (b >= B) {
-                RWAITL(1, xbar, xpar);                     // padding trial of the last group: protocol only
-            } else if (K::WOLF) {
+            if (K::WOLF) {
                 // sample t = 24 bytes at raw + o15 + 24 t (8-byte aligned): chunk 0 = bytes 0..15, chunk 1 = bytes 16..31 (the
                 // last 8 belong to the next sample and meet zero weights).  lane = sample: conflict-free 8-byte loads
                 // (lane stride 24 B) and 16-byte stores (lane stride 16 B)
-                constexpr int NIT = (4 * K::PART_TILES + TW - 1) / TW;                   // warp iterations of 32 samples
-                const int t0 = 128 * K::PART_TILES * h;
-                uint2 w[NIT][4];
 #pragma unroll
-                for (int i = 0; i < NIT; i++) {
-                    const int tl = 32 * (mem + TW * i) + lane;
-                    if (mem + TW * i < 4 * K::PART_TILES && t0 + tl < K::T) {
-                        const uint8_t* s = raw + o15 + 24 * (t0 + tl);
-                        w[i][0] = tcr_lds64(s); w[i][1] = tcr_lds64(s + 8); w[i][2] = tcr_lds64(s + 16); w[i][3] = tcr_lds64(s + 24);
+                for (int h = 0; h < K::PARTS; h++) {
+                    RWAITL(1, sbase + K::BAR_X_EMPTY + 8 * h, (n & 1) ^ 1);
+                    if (b < B) {
+                        uint8_t* xs = smem + K::OFF_XS + h * K::XS_BYTES;
+                        const int t0 = 128 * K::part_first(h), nit = 4 * K::part_tiles(h);      // warp iterations of 32 samples
+                        for (int it = rw; it < nit; it += kRRW) {
+                            const int tl = 32 * it + lane, t = t0 + tl;
+                            if (t < K::T) {
+                                const uint8_t* s = raw + o15 + 24 * t;
+                                const uint2 w0 = tcr_lds64(s), w1 = tcr_lds64(s + 8), w2 = tcr_lds64(s + 16), w3 = tcr_lds64(s + 24);
+                                uint8_t* d = xs + (tl >> 7) * K::TILE_PITCH + 16 * (tl & 127);
+                                *reinterpret_cast<uint4*>(d) = make_uint4(w0.x, w0.y, w1.x, w1.y);
+                                *reinterpret_cast<uint4*>(d + 2048) = make_uint4(w2.x, w2.y, w3.x, w3.y);
+                            }
+                        }
                     }
-                }
-                RWAITL(1, xbar, xpar);
-#pragma unroll
-                for (int i = 0; i < NIT; i++) {
-                    const int tl = 32 * (mem + TW * i) + lane;
-                    if (mem + TW * i < 4 * K::PART_TILES && t0 + tl < K::T) {
-                        uint8_t* d = xs + (tl >> 7) * K::TILE_PITCH + 16 * (tl & 127);
-                        *reinterpret_cast<uint4*>(d) = make_uint4(w[i][0].x, w[i][0].y, w[i][1].x, w[i][1].y);
-                        *reinterpret_cast<uint4*>(d + 2048) = make_uint4(w[i][2].x, w[i][2].y, w[i][3].x, w[i][3].y);
-                    }
+                    fence_proxy_async();          // the tiles are read by the tensor core (async proxy)
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(sbase + K::BAR_X_FULL + 8 * h);
                 }
             } else {
-                // [C][128 samples] tiles with the 128-byte swizzle (16-byte chunk j of row c at j ^ (c & 7)); this part = chunks
-                // 32 h .. 32 h + 31 of every row, lane = chunk; rows mem, mem + TW, ... of the team member, RB rows in flight.
-                // The code is specialised on (first-byte offset of the trial, member): see tcr_realign_part
-                constexpr int RB = MIBMI_TCR_RB;
-                const uint32_t xl = smem_u32(xs) + (lane >> 3) * K::TILE_PITCH;
-                const uint32_t rl = smem_u32(raw) + 512 * h + 16 * lane;
-                static_assert(K::TRIAL_BYTES % 2 == 0 && TW == 2, "first-byte offsets are even; two members per team");
-                if (32 * h + lane < K::CHUNKS + 1)              // last part: 8 of 32 lanes (a branch around the body, no predicates inside)
-                switch ((o15 >> 1) * 2 + mem) {
-#define MIBMI_RCASE(v) case v: tcr_realign_part<K, 2 * (v / 2), v % 2, TW, RB>(rl, xl, xbar, xpar); break;
-                    MIBMI_RCASE(0) MIBMI_RCASE(1) MIBMI_RCASE(2) MIBMI_RCASE(3) MIBMI_RCASE(4) MIBMI_RCASE(5) MIBMI_RCASE(6) MIBMI_RCASE(7)
-                    MIBMI_RCASE(8) MIBMI_RCASE(9) MIBMI_RCASE(10) MIBMI_RCASE(11) MIBMI_RCASE(12) MIBMI_RCASE(13) MIBMI_RCASE(14)
-                    default: tcr_realign_part<K, 14, 1, TW, RB>(rl, xl, xbar, xpar); break;
-#undef MIBMI_RCASE
+                RWAITL(1, sbase + K::BAR_X_EMPTY + 8 * st, ((n >> 1) & 1) ^ 1);
+                if (b < B) {
+                    // [C][128 samples] tiles with the 128-byte swizzle (16-byte chunk j of row c at j ^ (c & 7))
+                    uint8_t* xs = smem + K::OFF_XS + st * K::XS_BYTES;
+                    for (int c = rw; c < K::C; c += kRRW) {
+                        const int src0 = o15 + c * K::T;                       // first byte of the row in the raw stage
+                        const int sh = 8 * (src0 & 3);                         // warp-uniform byte shift, word shift below
+                        const uint8_t* rbase = raw + (src0 & ~15) + 16 * lane;
+                        uint8_t* xrow = xs + c * 128;
+                        switch ((src0 >> 2) & 3) {
+                            case 0: tcr_realign_row<K, 0>(rbase, xrow, c, sh, lane); break;
+                            case 1: tcr_realign_row<K, 1>(rbase, xrow, c, sh, lane); break;
+                            case 2: tcr_realign_row<K, 2>(rbase, xrow, c, sh, lane); break;
+                            default: tcr_realign_row<K, 3>(rbase, xrow, c, sh, lane); break;
+                        }
+                    }
                 }
+                fence_proxy_async();          // the tiles are read by the tensor core (async proxy)
+                __syncwarp();
+                if (lane == 0) mbar_arrive(sbase + K::BAR_X_FULL + 8 * st);
             }
-            fence_proxy_async();          // the tiles are read by the tensor core (async proxy)
             __syncwarp();
-            if (lane == 0) {
-                mbar_arrive(sbase + K::BAR_X_FULL + 8 * team);
-                if (h + 2 >= K::PARTS) mbar_arrive(sbase + K::BAR_RAW_EMPTY + 8 * st);     // the team's last part of this trial
-            }
+            if (lane == 0) mbar_arrive(sbase + K::BAR_RAW_EMPTY + 8 * st);
         }
     }
     else if (warp == kRWarpM1) {
@@ -527,16 +438,17 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
             const uint32_t td = tmem_base + ab * K::TM_L1_TRIAL;
 #pragma unroll
             for (int h = 0; h < K::PARTS; h++) {
-                const int pc = n * K::PARTS + h, xsl = pc & 1;
-                RWAITL(0, sbase + K::BAR_X_FULL + 8 * xsl, (pc >> 1) & 1);
+                const int st = K::PARTS == 1 ? (n & 1) : h;
+                const int par = K::PARTS == 1 ? ((n >> 1) & 1) : (n & 1);
+                RWAITL(0, sbase + K::BAR_X_FULL + 8 * st, par);
                 if (h == 0) RWAITL(1, sbase + K::BAR_T1_EMPTY + 8 * ab, ((n >> 1) & 1) ^ 1);
                 tc_fence_after();
-                const uint32_t a_lo = (uint32_t)da0 + xsl * (K::XS_BYTES >> 4);
+                const uint32_t a_lo = (uint32_t)da0 + st * (K::XS_BYTES >> 4);
                 if (elect_one()) {
 #pragma unroll
                     for (int j = 0; j < K::part_tiles(h); j++)
                         umma_i8_lohi(td + 16 * (K::part_first(h) + j), a_lo + ((j * K::TILE_PITCH) >> 4), a_hi, b_lo0, b_hi, idesc, 0);
-                    umma_commit(sbase + K::BAR_X_EMPTY + 8 * xsl);
+                    umma_commit(sbase + K::BAR_X_EMPTY + 8 * st);
                     if (h == K::PARTS - 1) umma_commit(sbase + K::BAR_T1_FULL + 8 * ab);
                 }
                 __syncwarp();
@@ -546,44 +458,35 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
         // =====================================================================================
         // M2: layer-2 MMAs: one tile of 128 rows x 32 outputs per group; 8 batches of 2 channels x 3 k-steps into
         //     alternating TMEM halves.  A = y1 row of the channel, K-major SWIZZLE_32B (rows 32 B apart, SBO = 256 B), k-step ks
-        //     starts 32 ks bytes further; B = w2umma32 of the channel (LBO = 256 B, SBO = 128 B), k-step ks = + 512 ks bytes,
-        //     from the ring stage the producer warp filled for this batch
+        //     starts 32 ks bytes further; B = w2umma32 of the channel (LBO = 256 B, SBO = 128 B), k-step ks = + 512 ks bytes
         // =====================================================================================
         constexpr uint32_t idesc = tcr_idesc_i8_kk(128, 32);
         const uint64_t da0 = umma_desc(sbase + K::OFF_Y1, 16, 256, 6), db0 = umma_desc(sbase + K::OFF_W2, 256, 128, 0);
         const uint32_t a_hi = (uint32_t)(da0 >> 32), b_hi = (uint32_t)(db0 >> 32), b_lo0 = (uint32_t)db0, a_lo0 = (uint32_t)da0;
-        int wst = 0, wuse = 0;                                              // ring stage of the next batch, uses of that stage so far
         for (int gq = 0; gq < ng; gq++) {
-            const int buf = gq & 1;
 #pragma unroll
-            for (int j = 0; j < K::G; j++) RWAIT(0, sbase + K::BAR_Y1_FULL + 8 * (4 * buf + j), (gq >> 1) & 1);
+            for (int j = 0; j < K::G; j++) RWAIT(0, sbase + K::BAR_Y1_FULL + 8 * j, gq & 1);
             tc_fence_after();
-            const uint32_t a_lob = a_lo0 + ((buf * K::YBUF) >> 4);
-#pragma unroll 2
-            for (int bt = 0; bt < 8; bt++) {          // two batches per iteration (the TMEM half is a compile-time constant); unrolled 8 x
-                                                      // this loop alone was 800 instructions of an instruction cache that holds ~3000
+#pragma unroll
+            for (int bt = 0; bt < 8; bt++) {
                 const int h = bt & 1;
                 const int use = gq * 4 + (bt >> 1);                         // how often this half has been used before
-                RWAIT(2, sbase + K::BAR_W2_FULL + 8 * wst, wuse & 1);
                 RWAIT(1, sbase + K::BAR_T2_EMPTY + 8 * h, (use & 1) ^ 1);
                 tc_fence_after();
                 if (elect_one()) {
-                    const uint32_t b_los = b_lo0 + ((wst * K::W2_BATCH) >> 4);
 #pragma unroll
                     for (int c = 0; c < 2; c++)
 #pragma unroll
                         for (int ks = 0; ks < 3; ks++) {
                             const int k = 2 * bt + c;
                             umma_i8_lohi(tmem_base + K::TM_L2 + K::TM_L2_HALF * h + 32 * c,
-                                         a_lob + ((k * K::CHS + 32 * ks) >> 4), a_hi,
-                                         b_los + ((c * kW2U32 + 512 * ks) >> 4), b_hi, idesc, ks > 0);
+                                         a_lo0 + ((k * K::CHS + 32 * ks) >> 4), a_hi,
+                                         b_lo0 + ((k * kW2U32 + 512 * ks) >> 4), b_hi, idesc, ks > 0);
                         }
                     umma_commit(sbase + K::BAR_T2_FULL + 8 * h);
-                    umma_commit(sbase + K::BAR_W2_EMPTY + 8 * wst);
-                    if (bt == 7) umma_commit(sbase + K::BAR_TILE_DONE + 8 * buf);
+                    if (bt == 7) umma_commit(sbase + K::BAR_TILE_DONE);
                 }
                 __syncwarp();
-                if (++wst == K::W2_STAGES) { wst = 0; wuse++; }
             }
         }
     } else if (warp >= kRWarpB && warp < kRWarpC) {
@@ -600,7 +503,7 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
         for (int gq = 0; gq < ng; gq++) {
             const int gpar = gq & 1;
             RWAITL(1, sbase + K::BAR_Y2_EMPTY + 8 * gpar, ((gq >> 1) & 1) ^ 1);     // the C warps have consumed y2[gpar] of group gq - 2
-            const long long b = trial_of(K::G * gq + (j < K::G ? j : 0));
+            const long long b = K::G * (firstg + (long long)gq * strideg) + j;
             uint8_t* y2s = smem + K::OFF_Y2 + (gpar * K::G + (j < K::G ? j : 0)) * K::Y2_TRIAL + 8 + 4 * blk;
 #pragma unroll 1
             for (int bb = 0; bb < 4; bb++) {
@@ -661,8 +564,8 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
         uint8_t* y3 = smem + K::OFF_Y3 + cj * K::Y3_BYTES;
         uint8_t* y4 = smem + K::OFF_Y4 + cj * K::Y4_BYTES;
         const uint32_t* y4w = reinterpret_cast<const uint32_t*>(y4);
-        const uint32_t* w3s = &net->w3frag[0][0][0] + lane;          // fragments through L1 (8 KB + 2 KB, shared by the four warps)
-        const uint32_t* w5s = &net->w5frag[0][0][0] + lane;
+        const uint32_t* w3s = reinterpret_cast<const uint32_t*>(smem + K::OFF_W3) + lane;
+        const uint32_t* w5s = reinterpret_cast<const uint32_t*>(smem + K::OFF_W5) + lane;
         // layer-3 stores: sample t = 16 i + 8 v + 2 q (+1) goes to chunk 2 (i >> 1) + (q >> 1), position
         // 8 (q & 1) + 4 (i & 1) + 2 v: the order layer 4 wants (pooling group = MMA column pair)
         const uint32_t y3_thr = 16 * (q >> 1) + 8 * (q & 1);
@@ -680,7 +583,7 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
 #pragma unroll
                 for (int v = 0; v < 2; v++) {
                     c3[v][0] = c3[v][1] = c3[v][2] = c3[v][3] = 0;
-                    mma_k32(c3[v], a, __ldg(w3s + (4 * k + 2 * v) * 32), __ldg(w3s + (4 * k + 2 * v + 1) * 32));
+                    mma_k32(c3[v], a, w3s[(4 * k + 2 * v) * 32], w3s[(4 * k + 2 * v + 1) * 32]);
                 }
                 uint8_t* y3b = y3 + k * K::Y3S + y3_thr;
 #pragma unroll
@@ -735,7 +638,7 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
             int z[4] = {0, 0, 0, 0};
 #pragma unroll
             for (int ks = 0; ks < K::KST5; ks++) {
-                const uint32_t a[4] = {__ldg(w5s + (2 * ks) * 32), 0u, __ldg(w5s + (2 * ks + 1) * 32), 0u};
+                const uint32_t a[4] = {w5s[(2 * ks) * 32], 0u, w5s[(2 * ks + 1) * 32], 0u};
                 const uint32_t bb0 = g == 0 ? y4w[8 * ks + q] : 0u, bb1 = g == 0 ? y4w[8 * ks + 4 + q] : 0u;
                 mma_k32(z, a, bb0, bb1);
             }

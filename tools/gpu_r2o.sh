@@ -1,6 +1,6 @@
-# round 2, call n: layer-2 MMA loop unrolled 2 x instead of 8 x (instruction cache)
+# round 2, call o: single-buffer kernel (cb75378) with the conflict-free y1 pitch
 set -x
-O=gpurun_out/r2n; mkdir -p $O
+O=gpurun_out/r2o; mkdir -p $O
 timeout 600 python -m pytest tests -m gpu -x -q -k "22 or tcr or wolf or unaligned or gather or taps" > $O/pytest_tcr.log 2>&1; tail -3 $O/pytest_tcr.log
 bench1() { timeout 200 python bench.py --steps 20 --warmup 5 --no-cpu-baseline --no-e2e --sustained-seconds 0 "$@" | python -c "import json,sys; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print(round(d['value']/1e6,2), round(d['roofline']['frac'],4), d['roofline']['kernel'], d['gpu_launches'], d['clocks']['sm_mhz'], d['clocks']['reasons'])"; }
 for i in 1 2; do

@@ -32,8 +32,8 @@ p = buf.reshape(148, 32, 4).astype(np.float64)
 ntr = B / 148
 roles = {'A  L1 epilogue': (range(0, 12), ['t1_full', 'tile_done']), 'B  L2 epilogue': (range(12, 20), ['t2_full', 'y2_empty']),
          'C  L3/4/5': (range(20, 24), ['y2_full']), 'R  realign': (range(24, 28), ['raw_full', 'x_empty']),
-         'P  bulk copy': (range(28, 29), []),
-         'M1 L1 mma': (range(29, 30), ['x_full', 't1_empty']), 'M2 L2 mma': (range(30, 31), ['y1_full', 't2_empty', 'w2_full'])}
+         'P  bulk copy': (range(28, 29), ['raw_empty']),
+         'M1 L1 mma': (range(29, 30), ['x_full', 't1_empty']), 'M2 L2 mma': (range(30, 31), ['y1_full', 't2_empty'])}
 print(f'{C}x{T}: cycles per trial per CTA = {p[:, 0, 0].mean() / ntr:.0f}')
 for r, (ws, names) in roles.items():
     q = p[:, list(ws), :]
