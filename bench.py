@@ -72,9 +72,10 @@ def parse_args():
     ap.add_argument("--stream-len", type=int, default=9600, help="stream workload: samples per subject (60 s at 160 Hz)")
     ap.add_argument("--stream-mode", default="auto", choices=["auto", "fused", "gather"])
     ap.add_argument("--gather", default="auto", choices=["auto", "peer", "root", "nccl", "none"],
-                    help="multi-GPU logits gather: auto / peer = fused peer stores into EVERY rank's symmetric buffer (all-gather); "
-                         "root = fused peer stores into rank 0's buffer only (a gather, what north_star asks for); nccl = one NCCL "
-                         "all_gather per step; none = no gather at all (isolates the cost of the remote stores)")
+                    help="multi-GPU logits gather: auto / root = fused peer stores into rank 0's symmetric buffer (a gather, what "
+                         "north_star asks for: 8 GPUs 1396 M trials/s, r2q); peer = into EVERY rank's buffer (all-gather, 7 x the remote "
+                         "stores: 1341 M); nccl = one NCCL all_gather per step; none = no gather at all (isolates the cost of the remote "
+                         "stores: 1408 M)")
     ap.add_argument("--sustained-seconds", type=float, default=2.0, help="length of the sustained block (0 = skip)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -517,7 +518,7 @@ def main():
     if world > 1 and args.gather in ("auto", "peer", "root"):
         from mibminet_b200.sharding import PeerGather
         try:
-            peer = PeerGather(net, world * B, mode="root" if args.gather == "root" else "all")
+            peer = PeerGather(net, world * B, mode="all" if args.gather == "peer" else "root")
         except RuntimeError as e:
             if args.gather in ("peer", "root"):
                 raise
@@ -596,7 +597,8 @@ def main():
         # (gather-to-root: only the root's buffer is complete, the verdict is the root's)
         chk = torch.empty((world * B, N_CLASSES), dtype=torch.int8, device=dev)
         dist.all_gather_into_tensor(chk, logits.contiguous())
-        good = torch.equal(chk, gathered) if (args.gather != "root" or rank == 0) else torch.equal(chk[rank * B:(rank + 1) * B], logits)
+        to_root = peer is not None and args.gather != "peer"
+        good = torch.equal(chk, gathered) if (not to_root or rank == 0) else torch.equal(chk[rank * B:(rank + 1) * B], logits)
         flag = torch.tensor([1 if good else 0], device=dev)
         dist.all_reduce(flag, op=dist.ReduceOp.MIN)
         gather_checked = bool(int(flag[0]))
@@ -701,7 +703,7 @@ def main():
             "run": {"kernel_path": net.last_path, "bit_exact_checked": None, "gather_checked": gather_checked,
                     "collective": ("none" if world == 1 else
                                    ("fused: the kernel epilogue stores the logits into every rank's symmetric buffer over NVLink (all-gather), "
-                                    "one barrier at the end" if args.gather != "root" else
+                                    "one barrier at the end" if args.gather == "peer" else
                                     "fused: the kernel epilogue stores the logits into rank 0's symmetric buffer over NVLink (gather to root), "
                                     "one barrier at the end") if peer is not None else
                                    "none (--gather none: local logits only)" if args.gather == "none" else
