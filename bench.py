@@ -37,13 +37,22 @@ METRIC = "int8 edgeEEGNet trials/sec"
 # ncu --set full (profiles/r1d_ncu_full_metrics.csv, tc_forward_kernel<TCfg<64,480>>): 2.013485 GB read + 18.797 MB written
 # per launch of 65536 trials
 NCU_TRAFFIC_BYTES_PER_TRIAL = (2.013485e9 + 18.797056e6) / 65536
+# per kernel and shape: (DRAM bytes per trial, source) from `ncu --set full` dram__bytes_read.sum + dram__bytes_write.sum per launch of 65536 trials
+NCU_TRAFFIC = {("tc_forward_kernel", "64x480", "bct"): (NCU_TRAFFIC_BYTES_PER_TRIAL, "profiles/r1d_ncu_full_metrics.csv"),
+               ("tcr_forward_kernel", "22x1125", "bct"): ((1.622439e9 + 23.239168e6) / 65536, "profiles/r2o_tcr_ncu_full_metrics.csv")}
+# shared-memory data pipe of the 22x1125 kernel (ncu r2o): LSU + tensor-core wavefronts per trial; one wavefront = one cycle of the pipe
+NCU_SMEM_WAVEFRONTS = {("tcr_forward_kernel", "22x1125", "bct"): (1585.9, 964.0, "profiles/r2o_tcr_ncu_full_metrics.csv")}
+# measured on this pool (tools/probe_i8_peak.cu, profiles/r2d_int8_tcgen05_peak.jsonl): tcgen05.mma kind::i8 M128 K32, one issuing thread
+# per SM: N = 256 runs at 128 cycles per instruction = 4464 TOP/s dense int8 on 148 SMs; N <= 64 at 54.6 cycles per instruction
+INT8_PEAK_TOPS, UMMA_CYCLES_N_LE_64 = 4464.4, 54.6
 KERNEL_TEMPLATES = {"tc_forward_kernel": "tc_forward_kernel<TCfg<{C},{T}>>", "tcr_forward_kernel": "tcr_forward_kernel<RCfg<{C},{T}>>", "pipe_forward_kernel": "pipe_forward_kernel<PCfg<{C},{T},4>>",
                     }
 KERNEL_NOTES = {
     "tc_forward_kernel": "layers 1+2 on tcgen05.mma kind::i8 (TMEM accumulators), 23 warps requantise; ncu r1d: DRAM 67 % of "
                          "ncu peak, issue slots 59 %, not pipe bound: per-trial hand-off latency between the roles, see DESIGN.md 4.1",
-    "tcr_forward_kernel": "tcgen05 kernel with realigning warps (rows not 16-byte aligned): issue bound, 9.4 k warp-instructions per "
-                          "trial (2.34 x the requant work of 64x480 on 0.8 x the bytes), ncu r1e, see DESIGN.md 4.1b",
+    "tcr_forward_kernel": "tcgen05 kernel with realigning warps (rows not 16-byte aligned), layer 2 as N = 32 MMAs: 7.5 k warp-instructions "
+                          "per trial at 57 % issue, shared-memory data pipe 76 % busy (LSU 1586 + tensor-core 964 wavefronts per trial), the "
+                          "layer-1 epilogue and the layer-2 MMAs alternate on a single y1 buffer; ncu r2o, DESIGN.md 4.1b",
     "pipe_forward_kernel": "mma.sync pipeline kernel (shape without a tcgen05 instance): issue / dependent-latency bound, "
                            "see DESIGN.md 4.2",
 }
@@ -109,19 +118,38 @@ def cpu_reference_run(x_sample, repeat, cores):
 
 
 def tensor_pipe(kernel, C, T, B, ms_kernel, clocks):
-    """Second roofline: share of the tcgen05 issue rate.  tcgen05.mma instructions per trial (counted from the
-    kernel's loops, confirmed by the UTCIMMA count of the ncu source page) x 46 cycles per M128 N16 K32 kind::i8 instruction
-    (tools/probe_umma2.cu) / the kernel's cycles per trial per SM at the SM clock sampled during the timed region."""
+    """Second roofline: share of the tcgen05 issue rate and of the MEASURED int8 tensor peak.  tcgen05.mma instructions
+    per trial (counted from the kernel's loops, confirmed by the UTCIMMA count of the ncu source page) x the measured 54.6 cycles
+    per M128 N<=64 K32 kind::i8 instruction (tools/probe_i8_peak.cu; the first estimate, 46 cycles, came from a shorter probe) /
+    the kernel's cycles per trial per SM at the SM clock sampled during the timed region.  `tops` counts the multiply-adds the
+    instructions execute (2 M N K each, padding included) against the measured 4464 TOP/s of back-to-back N = 256 instructions."""
     tiles, ksteps = (T + 127) // 128, (C + 31) // 32
     if kernel == "tc_forward_kernel":
-        n_mma = tiles * ksteps + 12                   # layer 1 per tile and k-step + layer 2: 16 channels x 3 per quad of 4 trials
+        n_mma, ops = tiles * ksteps + 12, (tiles * ksteps + 12) * 2 * 128 * 16 * 32      # layer 1 per tile and k-step + layer 2: 16 channels x 3 (N = 16) per quad
     elif kernel == "tcr_forward_kernel":
         n_mma = tiles * ksteps + 48 / 3               # layer 2: one tile of N = 32 x 16 channels x 3 k-steps per group of 3 trials
+        ops = tiles * ksteps * 2 * 128 * 16 * 32 + 16 * 2 * 128 * 32 * 32
     else:
         return None
     mhz = (clocks or {}).get("sm_mhz") or 1965.0
     cycles = ms_kernel * 1e-3 * mhz * 1e6 * 148 / B
-    return {"utcimma_per_trial": n_mma, "cycles_per_instr": 46, "cycles_per_trial_per_sm": cycles, "frac": n_mma * 46 / cycles}
+    tops = ops * B / (ms_kernel * 1e-3) / 1e12
+    return {"utcimma_per_trial": n_mma, "cycles_per_instr": UMMA_CYCLES_N_LE_64, "cycles_per_trial_per_sm": cycles,
+            "frac": n_mma * UMMA_CYCLES_N_LE_64 / cycles, "tops": tops, "int8_peak_tops_measured": INT8_PEAK_TOPS,
+            "frac_of_int8_peak": tops / INT8_PEAK_TOPS,
+            "note": "issue-rate fraction is the binding one: an N <= 64 instruction costs 54.6 cycles whatever N is"}
+
+
+def smem_pipe(kernel, shape, layout, B, ms_kernel, clocks):
+    """Third roofline, for the kernel that is bound by neither HBM nor the tensor pipe (22 x 1125): utilisation of the shared-memory
+    data pipe = (LSU + tensor-core wavefronts per trial, ncu) / cycles per trial per SM, live."""
+    w = NCU_SMEM_WAVEFRONTS.get((kernel, shape, layout))
+    if w is None:
+        return None
+    mhz = (clocks or {}).get("sm_mhz") or 1965.0
+    cycles = ms_kernel * 1e-3 * mhz * 1e6 * 148 / B
+    return {"lsu_wavefronts_per_trial": w[0], "tc_wavefronts_per_trial": w[1], "cycles_per_trial_per_sm": cycles,
+            "frac": (w[0] + w[1]) / cycles, "source": w[2]}
 
 
 def host_cores():
@@ -442,10 +470,14 @@ def main_eegnet(args, rank, local_rank, world):
                "vs_baseline": None, "dtype": "int8", "data": "synthetic",
                "config": {"workload": f"EEGNet / Q-EEGNet layer order (SURVEY 8(f)4), {Ce}ch x {Te} samples, F1={F1} D={D} Nf={Nf}",
                           "trials_per_gpu_per_step": B, "l2_policy": f"input per step {B * Ce * Te / 1e9:.2f} GB > 126 MB L2"},
-               "roofline": {"bound": "tensor", "achieved": B * macs * 2 / (ms * 1e-3) / 1e12, "peak": None, "unit": "TOP/s",
-                            "frac": None, "traffic": None, "hbm_frac": alg / (ms * 1e-3) / 1e9 / peak, "peak_source": peak_src,
-                            "note": "mma.sync int8 kernel bound by the requant epilogue (F1*C*T outputs per trial), DESIGN.md 4.7; no "
-                                    "measured int8 tensor peak on this pool, so no fraction is claimed"},
+               "roofline": {"bound": "tensor", "achieved": B * macs * 2 / (ms * 1e-3) / 1e12, "peak": INT8_PEAK_TOPS, "unit": "TOP/s",
+                            "frac": B * macs * 2 / (ms * 1e-3) / 1e12 / INT8_PEAK_TOPS, "traffic": None,
+                            "hbm_frac": alg / (ms * 1e-3) / 1e9 / peak,
+                            "peak_source": "measured: tcgen05.mma kind::i8 M128 N256 K32 back to back on 148 SMs (tools/probe_i8_peak.cu, "
+                                           "profiles/r2d_int8_tcgen05_peak.jsonl); this kernel uses the legacy mma.sync path, whose own "
+                                           "ceiling is lower",
+                            "note": "mma.sync int8 kernel bound by the requant epilogue (F1*C*T outputs per trial), DESIGN.md 4.7; parity "
+                                    "of this layer order is unpinned by the reference (tolerance pin only)"},
                "gpu_launches": int(net.launch_count - l0), "clocks": clocks}
         if not args.no_cpu_baseline:
             sys.path.insert(0, os.path.join(ROOT, "oracle"))
@@ -695,6 +727,7 @@ def main():
         peak, peak_src = measured_peaks()
         alg_bytes = ALG_BYTES_PER_TRIAL if xf is None else 4 * C * T + 4 * N_CLASSES     # float trials in, float logits out
         achieved = B * alg_bytes / (ms_kernel * 1e-3) / 1e9
+        traffic_per_trial, traffic_src = NCU_TRAFFIC.get((net.last_kernel, args.shape, args.layout), (None, None)) if xf is None else (None, None)
         out = {
             "metric": METRIC, "value": value, "unit": "trials/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
@@ -712,15 +745,15 @@ def main():
                              "float32 trials: quantize_input_kernel_v16 (trunc(clip(x/s,-1,1)*127), IEEE division) -> int8 forward -> "
                              "dequantize_kernel; kernel_ms covers the three launches, the int8 copy is written and read once more"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": NCU_TRAFFIC_BYTES_PER_TRIAL * B if (net.last_kernel == "tc_forward_kernel" and args.shape == "64x480" and xf is None
-                                                                             and args.layout == "bct") else None,
-                         "traffic_source": "ncu --set full dram__bytes_read.sum + dram__bytes_write.sum per launch of 65536 "
-                                           "trials (profiles/r1d_ncu_full_metrics.csv), scaled to this batch",
+                         "traffic": traffic_per_trial * B if traffic_per_trial else None,
+                         "traffic_source": (f"ncu --set full dram__bytes_read.sum + dram__bytes_write.sum per launch of 65536 trials ({traffic_src}), "
+                                            "scaled to this batch") if traffic_per_trial else None,
                          "peak_source": peak_src,
                          "kernel": KERNEL_TEMPLATES.get(net.last_kernel, net.last_kernel).format(C=C, T=T),
                          "kernel_ms": ms_kernel, "alg_bytes_per_trial": alg_bytes,
                          "note": KERNEL_NOTES.get(net.last_kernel, ""),
-                         "tensor_pipe": tensor_pipe(net.last_kernel, C, T, B, ms_kernel, clocks)},
+                         "tensor_pipe": tensor_pipe(net.last_kernel, C, T, B, ms_kernel, clocks),
+                         "smem_pipe": smem_pipe(net.last_kernel, args.shape, args.layout, B, ms_kernel, clocks)},
             "gpu_launches": int(launches), "clocks": clocks, "e2e": e2e, "sustained": sustained,
         }
         if sustained is not None:
