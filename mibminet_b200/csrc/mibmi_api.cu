@@ -177,6 +177,21 @@ bool pack_pipe(const mibmi_params_t* p, PipeNet* f, const char** why) {
                     (uint8_t)(int8_t)(sg * p->l1_weight_align[n * CA4 + c]);
         }
     }
+    {   // Wolf-order super-rows (PipeNet::w1x): only when the rows are not a multiple of 16 bytes and the block structure fits
+        int gcd = CA4, b16 = 16;
+        while (b16) { const int t = gcd % b16; gcd = b16; b16 = t; }
+        const int S = CA4 % 16 ? 16 / gcd : 1, kp = (S * CA4 + 31) / 32 * 32;
+        if (S > 1 && 16 * S * kp <= kW1X)
+            for (int pp = 0; pp < S; pp++)
+                for (int n = 0; n < 16; n++) {
+                    const int sg = p->l1_factor[n] < 0 ? -1 : 1, nn = 16 * pp + n;
+                    for (int c = 0; c < C; c++) {
+                        const int k = CA4 * pp + c;
+                        f->w1x[(nn >> 3) * (kp / 16) * 128 + (k >> 4) * 128 + (nn & 7) * 16 + (k & 15)] =
+                            (uint8_t)(int8_t)(sg * p->l1_weight_align[n * CA4 + c]);
+                    }
+                }
+    }
     // ---- layer 2: Toeplitz B fragments.  Window-relative sample j = o + 1 + tap (o = output offset in
     // the 32-sample window), K position kk of k-step s <-> j = 32 s + kk
     for (int k = 0; k < 16; k++) {
@@ -469,11 +484,11 @@ int forward_impl(mibmi_net* net, const int8_t* x, int64_t B, int layout, int8_t*
     if (!x || !logits) return MIBMI_ERR_NULL;
     const bool aligned = ((uintptr_t)x & 15) == 0 && (net->N != 4 || ((uintptr_t)logits & 3) == 0);
     int path = net->force_path;
-    const bool wolf_fused = net->tc_wolf_ok && layout == MIBMI_LAYOUT_BTC;     // tcgen05 kernel, K-major operand from the Wolf order
+    // tcgen05 kernel, K-major operand straight from the Wolf order (rows of 64 / 16 bytes as tiles, rows of 40 / 24 / 20 / 8 bytes as super-rows)
+    const bool wolf_fused = net->tc_wolf_ok && layout == MIBMI_LAYOUT_BTC && net->force_path != MIBMI_PATH_FUSED_PIPE;
     const bool wolf_tcr = net->tcr_wolf_ok && layout == MIBMI_LAYOUT_BTC && net->force_path != MIBMI_PATH_FUSED_PIPE;   // same, rows of 24 bytes expanded in the kernel
-    const bool wolf_reorder = net->wolf_reorder_ok && layout == MIBMI_LAYOUT_BTC && !wolf_fused && !wolf_tcr;   // transpose into a scratch first
-    const bool pipe_possible = net->pipe_ok && (layout == MIBMI_LAYOUT_BCT || wolf_reorder || wolf_tcr ||
-                                                (wolf_fused && net->force_path != MIBMI_PATH_FUSED_PIPE));
+    const bool wolf_reorder = net->wolf_reorder_ok && layout == MIBMI_LAYOUT_BTC && !wolf_fused && !wolf_tcr;   // transpose into a scratch first (pipe kernel only)
+    const bool pipe_possible = net->pipe_ok && (layout == MIBMI_LAYOUT_BCT || wolf_reorder || wolf_tcr || wolf_fused);
     // the generic kernel reads bytes: it has no alignment requirement and takes what the fused kernels cannot
     if (path == MIBMI_PATH_AUTO) path = (pipe_possible && !taps && aligned) ? MIBMI_PATH_FUSED : MIBMI_PATH_GENERIC;
     if ((path == MIBMI_PATH_FUSED || path == MIBMI_PATH_FUSED_PIPE) && !pipe_possible) return MIBMI_ERR_UNSUPPORTED;
@@ -630,7 +645,7 @@ int mibmi_create(const mibmi_params_t* p, int device, mibmi_net_t** out) {
     n->tcr_ok = n->pipe_ok && tcr_has_instance(p->C, p->T);
     n->tc_wolf_ok = n->tc_ok && tc_has_wolf_instance(p->C, p->T);
     n->tcr_wolf_ok = n->tcr_ok && tcr_has_wolf_instance(p->C, p->T);
-    n->wolf_reorder_ok = n->pipe_ok && !n->tc_wolf_ok && reorder_has_instance(p->C, p->T);
+    n->wolf_reorder_ok = n->pipe_ok && reorder_has_instance(p->C, p->T);     // used when the mma.sync pipeline kernel is forced
     if (n->pipe_ok) n->stream_ok = pack_stream(p, pn, sn, &n->stream_why);
     else n->stream_why = n->pipe_why;
 

@@ -41,6 +41,7 @@ struct GenericNet {
 constexpr int kPipeMaxKB16 = 4;     // layer-1 blocks of 16 channels (C <= 64)
 constexpr int kPipeMaxKst5 = 16;    // layer-5 k-steps of 32 (T/64 padded to even <= 32)
 constexpr int kW2U32 = 1792;        // bytes per channel of PipeNet::w2umma32
+constexpr int kW1X = 64 * 96;       // PipeNet::w1x: N <= 64 (4 samples x 16 filters) x K <= 96 bytes
 
 struct PipeNet {
     // layer 1: W1 as MMA B fragments per 16-channel block: [block][filter n-tile (0-7, 8-15)][lane]
@@ -72,6 +73,12 @@ struct PipeNet {
     // B'[n' + 16][kk - 16] == B'[n'][kk], so the 8 x 16-byte core matrices may overlap: byte (n' >> 3) * 128 + (kk >> 4) * 256 +
     // (n' & 7) * 16 + (kk & 15) (descriptor LBO = 256 B, SBO = 128 B), 1792 bytes per channel instead of 3072
     alignas(16) uint8_t w2umma32[16 * kW2U32];
+    // layer 1 for tcgen05.mma when the Wolf-order input [B][T][C_ALIGN] has rows that are not a multiple of 16 bytes (C_ALIGN = 40, 24,
+    // 20, 8): S = 16 / gcd(C_ALIGN, 16) samples form one "super-row" of S * C_ALIGN bytes (a multiple of 16, so a tensor map can
+    // describe it) and the weights become block structured: W1x[16 p + f][C_ALIGN p + c] = W1[f][c], p < S, zero elsewhere -- one MMA row
+    // yields S samples x 16 filters (N = 16 S).  K-major core matrices over KP = ceil(S C_ALIGN / 32) * 32 bytes:
+    // byte (n >> 3) * (KP / 16) * 128 + (k >> 4) * 128 + (n & 7) * 16 + (k & 15)
+    alignas(16) uint8_t w1x[kW1X];
 };
 static_assert(sizeof(PipeNet) % 16 == 0, "PipeNet alignment");
 

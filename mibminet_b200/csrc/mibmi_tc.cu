@@ -68,6 +68,12 @@ struct TCfg {
     static constexpr int NST = (T64 + 3) / 4, T64P = (T64 + 1) / 2 * 2, KST5 = T64P / 2;
     static constexpr int Y4_BYTES = ((16 * T64P + 15) / 16) * 16;
     static constexpr int W2_CH = 16 * 96;                                   // Toeplitz B operand of one channel
+    // Wolf order with rows that are not a multiple of 16 bytes (WOLF = 3): super-rows of WS samples (PipeNet::w1x)
+    static constexpr int CA = (C + 3) / 4 * 4;
+    static constexpr int WS = CA % 16 == 0 ? 1 : (CA % 8 == 0 ? 2 : 4);    // 16 / gcd(CA, 16)
+    static constexpr int RB3 = WS * CA, NCH3 = RB3 / 16, KS3 = (RB3 + 31) / 32, KP3 = 32 * KS3;
+    static constexpr int TILE3 = 2 * KS3 * 2048;                            // [chunk][128 super-rows][16 B], padded to whole k-steps
+    static constexpr int TILES3 = (T / WS + 127) / 128;
     // TMEM columns
     static constexpr int TM_L1 = 0, TM_L1_TRIAL = 16 * TILES, TM_L2 = 128;
     // barriers
@@ -80,7 +86,8 @@ struct TCfg {
     static constexpr int OFF_C2 = 256;                                      // int [16][8]: thr, sig, soff, m, sh
     static constexpr int OFF_W1 = 1024;
     static constexpr int OFF_W2 = 2048;
-    static constexpr int OFF_XS = ((OFF_W2 + 16 * W2_CH + 1023) / 1024) * 1024;
+    static constexpr int OFF_W1X = OFF_W2 + 16 * W2_CH;                     // block-structured W1 of the super-row form (6 KB)
+    static constexpr int OFF_XS = ((OFF_W1X + kW1X + 1023) / 1024) * 1024;
     static constexpr int OFF_Y1 = OFF_XS + SX * XS_BYTES;
     static constexpr int OFF_Y2 = OFF_Y1 + 16 * CHS;
     static constexpr int OFF_Y3 = OFF_Y2 + 2 * Y2_BUF;
@@ -93,6 +100,8 @@ struct TCfg {
     static_assert(KST5 <= 4, "classifier fragments live in registers");
     static_assert(BAR_END <= OFF_TMEM && 16 * KPAD <= 1024, "barrier / W1 area");
     static_assert(SMEM <= 227 * 1024, "shared memory");
+    static_assert(WS == 1 || (RB3 % 16 == 0 && T % WS == 0 && 16 * WS * KP3 <= kW1X && TILES3 * TILE3 <= XS_BYTES &&
+                              TILES3 * 16 * WS <= TM_L1_TRIAL && OFF_W1X % 128 == 0), "super-row form");
 };
 
 template <bool FAST>
@@ -163,6 +172,9 @@ tc_forward_kernel(const __grid_constant__ CUtensorMap tmx, const PipeNet* __rest
         reinterpret_cast<uint32_t*>(smem + K::OFF_W1)[i] = reinterpret_cast<const uint32_t*>(net->w1umma)[i];
     for (int i = tid; i < 16 * K::W2_CH / 16; i += kTcThreads)
         reinterpret_cast<uint4*>(smem + K::OFF_W2)[i] = reinterpret_cast<const uint4*>(net->w2umma)[i];
+    if (WOLF == 3)
+        for (int i = tid; i < 16 * K::WS * K::KP3 / 16; i += kTcThreads)
+            reinterpret_cast<uint4*>(smem + K::OFF_W1X)[i] = reinterpret_cast<const uint4*>(net->w1x)[i];
     for (int i = tid; i < 16 * 8; i += kTcThreads) {
         const int k = i >> 3, f = i & 7;
         reinterpret_cast<int*>(smem + K::OFF_C2)[i] = f == 0 ? net->thr2[k] : f == 1 ? net->sig2[k] : f == 2 ? net->soff2[k]
@@ -207,49 +219,94 @@ tc_forward_kernel(const __grid_constant__ CUtensorMap tmx, const PipeNet* __rest
             tc_fence_after();
             if (s == 0) TWAIT(1, sbase + K::BAR_Y1_EMPTY + 8 * buf, ((gq >> 1) & 1) ^ 1);
             const uint32_t yb = st_off + K::SLOT * (4 * buf + s);
-            // the warp's (up to) two units of a pass are loaded from TMEM together and requantised interleaved: the
-            // TMEM latency and the dependent division chains of one unit hide behind the other
-#pragma unroll 1
-            for (int jb = ((warp >> 2) + n) & 1; jb < K::TILES; jb += 4) {
-                const int u0 = 4 * jb + qi, u1 = u0 + 8;
-                if (32 * u0 >= K::T) break;
-                const bool two = jb + 2 < K::TILES && 32 * u1 < K::T;
-                uint32_t r[2][2][8];
-                const uint32_t ta = tmem_base + ((uint32_t)(32 * qi) << 16) + K::TM_L1 + ab * K::TM_L1_TRIAL + 16 * jb;
-                tmem_ld_16x256b_x2(r[0][0], ta);
-                tmem_ld_16x256b_x2(r[0][1], ta + (16u << 16));
-                if (two) {
-                    tmem_ld_16x256b_x2(r[1][0], ta + 32);
-                    tmem_ld_16x256b_x2(r[1][1], ta + 32 + (16u << 16));
-                }
-                tmem_ld_wait();
+            if (WOLF == 3) {
+                // super-row form: TMEM lane = super-row of WS samples, column 16 p + f = (sample p of the row, filter f).  The warp takes
+                // the quarter qi of tile jb3 = 32 super-rows = 32 WS samples; per half of 16 lanes the thread holds, for its four
+                // filters and two rows, the WS adjacent samples of a row: ONE store of WS bytes each into y1[f][WS row ..]
+                const int jb3 = ((warp >> 2) + n) & 1;
+                const int sr0 = 128 * jb3 + 32 * qi;
+                if (jb3 < K::TILES3 && K::WS * sr0 < K::T) {
+                    const uint32_t ta = tmem_base + ((uint32_t)(32 * qi) << 16) + K::TM_L1 + ab * K::TM_L1_TRIAL + 16 * K::WS * jb3;
+                    const uint32_t y1s = sbase + K::OFF_Y1 + 32 + K::SLOT * (4 * buf + s);
 #pragma unroll
-                for (int uu = 0; uu < 2; uu++) {
-                    if (uu == 1 && !two) break;
-                    const int u = uu ? u1 : u0;
-                    uint32_t w[2][2];
+                    for (int mt = 0; mt < 2; mt++) {
+                        if (K::WS * (sr0 + 16 * mt) >= K::T) break;                    // warp-uniform
+                        uint32_t r[K::WS][8];
 #pragma unroll
-                    for (int mt = 0; mt < 2; mt++)
+                        for (int pp = 0; pp < K::WS; pp++) tmem_ld_16x256b_x2(r[pp], ta + 16 * pp + ((uint32_t)(16 * mt) << 16));
+                        tmem_ld_wait();
 #pragma unroll
-                        for (int nt = 0; nt < 2; nt++) {
-                            int v[4];
+                        for (int nt = 0; nt < 2; nt++)
 #pragma unroll
-                            for (int c = 0; c < 4; c++)
-                                v[c] = (FAST1 && MIBMI_TC_FOLD)
-                                           ? tc_div1_fold((int)r[uu][mt][4 * nt + c], mg1[nt][c & 1], offm[nt][c & 1])
-                                           : tc_div1<FAST1>((int)r[uu][mt][4 * nt + c] + off1[nt][c & 1], mg1[nt][c & 1], sh1[nt][c & 1]);
-                            w[mt][nt] = pack4_sat(v[0], v[1], v[2], v[3]);
-                            if (TAPS && tap1) {
-                                const long long b = 4 * (firstq + (long long)gq * strideq) + s;
-                                if (b < B)
+                            for (int c = 0; c < 4; c++) {
+                                const int f = 8 * nt + 2 * q + (c & 1), sr = sr0 + 16 * mt + g + 8 * (c >> 1);
+                                int v[K::WS];
 #pragma unroll
-                                    for (int c = 0; c < 4; c++) {
-                                        const int f = 8 * nt + 2 * q + (c & 1), t = 32 * u + 16 * mt + g + 8 * (c >> 1);
-                                        tap1[((size_t)b * 16 + f) * K::T + t] = (int8_t)clip8(v[c]);
+                                for (int pp = 0; pp < K::WS; pp++)
+                                    v[pp] = (FAST1 && MIBMI_TC_FOLD) ? tc_div1_fold((int)r[pp][4 * nt + c], mg1[nt][c & 1], offm[nt][c & 1])
+                                                                    : tc_div1<FAST1>((int)r[pp][4 * nt + c] + off1[nt][c & 1], mg1[nt][c & 1], sh1[nt][c & 1]);
+                                if (K::WS * sr < K::T) {
+                                    const uint32_t ya = y1s + f * K::CHS + K::WS * sr;
+                                    if (K::WS == 2)
+                                        asm volatile("st.shared.u16 [%0], %1;" ::"r"(ya), "h"((uint16_t)pack2_sat(v[0], v[K::WS > 1 ? 1 : 0])) : "memory");
+                                    else
+                                        asm volatile("st.shared.u32 [%0], %1;" ::"r"(ya), "r"(pack4_sat(v[0], v[K::WS > 1 ? 1 : 0], v[K::WS > 2 ? 2 : 0], v[K::WS > 3 ? 3 : 0])) : "memory");
+                                    if (TAPS && tap1) {
+                                        const long long b = 4 * (firstq + (long long)gq * strideq) + s;
+                                        if (b < B)
+#pragma unroll
+                                            for (int pp = 0; pp < K::WS; pp++)
+                                                tap1[((size_t)b * 16 + f) * K::T + K::WS * sr + pp] = (int8_t)clip8(v[pp]);
                                     }
+                                }
                             }
-                        }
-                    stsm_t8_x4(yb + 32 * u, w[0][0], w[0][1], w[1][0], w[1][1]);
+                    }
+                }
+            } else {
+            // the warp's (up to) two units of a pass are loaded from TMEM together and requantised interleaved: the
+                // TMEM latency and the dependent division chains of one unit hide behind the other
+    #pragma unroll 1
+                for (int jb = ((warp >> 2) + n) & 1; jb < K::TILES; jb += 4) {
+                    const int u0 = 4 * jb + qi, u1 = u0 + 8;
+                    if (32 * u0 >= K::T) break;
+                    const bool two = jb + 2 < K::TILES && 32 * u1 < K::T;
+                    uint32_t r[2][2][8];
+                    const uint32_t ta = tmem_base + ((uint32_t)(32 * qi) << 16) + K::TM_L1 + ab * K::TM_L1_TRIAL + 16 * jb;
+                    tmem_ld_16x256b_x2(r[0][0], ta);
+                    tmem_ld_16x256b_x2(r[0][1], ta + (16u << 16));
+                    if (two) {
+                        tmem_ld_16x256b_x2(r[1][0], ta + 32);
+                        tmem_ld_16x256b_x2(r[1][1], ta + 32 + (16u << 16));
+                    }
+                    tmem_ld_wait();
+    #pragma unroll
+                    for (int uu = 0; uu < 2; uu++) {
+                        if (uu == 1 && !two) break;
+                        const int u = uu ? u1 : u0;
+                        uint32_t w[2][2];
+    #pragma unroll
+                        for (int mt = 0; mt < 2; mt++)
+    #pragma unroll
+                            for (int nt = 0; nt < 2; nt++) {
+                                int v[4];
+    #pragma unroll
+                                for (int c = 0; c < 4; c++)
+                                    v[c] = (FAST1 && MIBMI_TC_FOLD)
+                                               ? tc_div1_fold((int)r[uu][mt][4 * nt + c], mg1[nt][c & 1], offm[nt][c & 1])
+                                               : tc_div1<FAST1>((int)r[uu][mt][4 * nt + c] + off1[nt][c & 1], mg1[nt][c & 1], sh1[nt][c & 1]);
+                                w[mt][nt] = pack4_sat(v[0], v[1], v[2], v[3]);
+                                if (TAPS && tap1) {
+                                    const long long b = 4 * (firstq + (long long)gq * strideq) + s;
+                                    if (b < B)
+    #pragma unroll
+                                        for (int c = 0; c < 4; c++) {
+                                            const int f = 8 * nt + 2 * q + (c & 1), t = 32 * u + 16 * mt + g + 8 * (c >> 1);
+                                            tap1[((size_t)b * 16 + f) * K::T + t] = (int8_t)clip8(v[c]);
+                                        }
+                                }
+                            }
+                        stsm_t8_x4(yb + 32 * u, w[0][0], w[0][1], w[1][0], w[1][1]);
+                    }
                 }
             }
             tc_fence_before();
@@ -269,7 +326,12 @@ tc_forward_kernel(const __grid_constant__ CUtensorMap tmx, const PipeNet* __rest
                 const long long b = 4 * (firstq + (long long)(n >> 2) * strideq) + (n & 3);   // b >= B: zero filled
                 const uint32_t dst = sbase + K::OFF_XS + st * K::XS_BYTES;
                 const uint32_t bar = sbase + K::BAR_FULL_X + 8 * st;
-                if (WOLF == 1) {
+                if (WOLF == 3) {
+                    mbar_expect_tx(bar, K::TILES3 * K::NCH3 * 2048);
+#pragma unroll
+                    for (int j = 0; j < K::TILES3; j++)
+                        tma_load_3d(dst + j * K::TILE3, &tmx, 0, (int)(b * (K::T / K::WS)) + 128 * j, 0, bar);
+                } else if (WOLF == 1) {
                     mbar_expect_tx(bar, K::TILES * K::TILE_BYTES);
 #pragma unroll
                     for (int j = 0; j < K::TILES; j++) tma_load_3d(dst + j * K::TILE_BYTES, &tmx, 0, (int)(b * K::T) + 128 * j, 0, bar);
@@ -295,10 +357,12 @@ tc_forward_kernel(const __grid_constant__ CUtensorMap tmx, const PipeNet* __rest
         // M1: layer-1 MMAs, TILES x KSTEPS per trial
         // =====================================================================================
         {
-            constexpr uint32_t idesc = WOLF ? umma_idesc_i8_kk(128, 16) : umma_idesc_i8(128, 16);
+            constexpr uint32_t idesc = WOLF == 3 ? umma_idesc_i8_kk(128, 16 * K::WS) : WOLF ? umma_idesc_i8_kk(128, 16) : umma_idesc_i8(128, 16);
             // descriptors: only the start-address field (low 14 bits, units of 16 B) changes between instructions
-            const uint64_t da0 = WOLF == 1 ? umma_desc(sbase + K::OFF_XS, 2048, 128, 0)
-                                 : WOLF == 2 ? umma_desc(sbase + K::OFF_XS, 16, 512, 4) : umma_desc(sbase + K::OFF_XS, 16, 1024, 2), db0 = umma_desc(sbase + K::OFF_W1, 128, K::KSTEPS * 256, 0);
+            const uint64_t da0 = (WOLF == 1 || WOLF == 3) ? umma_desc(sbase + K::OFF_XS, 2048, 128, 0)
+                                 : WOLF == 2 ? umma_desc(sbase + K::OFF_XS, 16, 512, 4) : umma_desc(sbase + K::OFF_XS, 16, 1024, 2),
+                           db0 = WOLF == 3 ? umma_desc(sbase + K::OFF_W1X, 128, (K::KP3 / 16) * 128, 0)
+                                           : umma_desc(sbase + K::OFF_W1, 128, K::KSTEPS * 256, 0);
             const uint32_t a_hi = (uint32_t)(da0 >> 32), b_hi = (uint32_t)(db0 >> 32), b_lo0 = (uint32_t)db0;
             for (int n = 0; n < ntr; n++) {
                 const int st = n % K::SX, ab = n & 1;
@@ -308,12 +372,22 @@ tc_forward_kernel(const __grid_constant__ CUtensorMap tmx, const PipeNet* __rest
                 const uint32_t a_lo = (uint32_t)da0 + st * (K::XS_BYTES >> 4);
                 const uint32_t td = tmem_base + K::TM_L1 + ab * K::TM_L1_TRIAL;
                 if (elect_one()) {
+                    if (WOLF == 3) {
+                        // super-rows: per tile of 128 super-rows KS3 k-steps of 32 bytes (two 16-byte chunks, 2048 B apart); N = 16 WS
 #pragma unroll
-                    for (int j = 0; j < K::TILES; j++)
+                        for (int j = 0; j < K::TILES3; j++)
 #pragma unroll
-                        for (int ks = 0; ks < K::KSTEPS; ks++)
-                            umma_i8_lohi(td + 16 * j, a_lo + ((j * K::TILE_BYTES + ks * (WOLF == 2 ? 32 : 4096)) >> 4), a_hi, b_lo0 + ((ks * 256) >> 4),
-                                         b_hi, idesc, ks > 0);
+                            for (int ks = 0; ks < K::KS3; ks++)
+                                umma_i8_lohi(td + 16 * K::WS * j, a_lo + ((j * K::TILE3 + ks * 4096) >> 4), a_hi, b_lo0 + ((ks * 256) >> 4),
+                                             b_hi, idesc, ks > 0);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < K::TILES; j++)
+#pragma unroll
+                            for (int ks = 0; ks < K::KSTEPS; ks++)
+                                umma_i8_lohi(td + 16 * j, a_lo + ((j * K::TILE_BYTES + ks * (WOLF == 2 ? 32 : 4096)) >> 4), a_hi, b_lo0 + ((ks * 256) >> 4),
+                                             b_hi, idesc, ks > 0);
+                    }
                     umma_commit(sbase + K::BAR_EMPTY_X + 8 * st);
                     umma_commit(sbase + K::BAR_T1_FULL + 8 * ab);
                 }
@@ -556,7 +630,17 @@ static cudaError_t launch_tc_instance(const PipeNet* net_dev, bool fast1, const 
     if (!enc) return cudaErrorNotSupported;
     CUtensorMap tm;
     CUresult r;
-    if (WOLF == 2) {
+    if (WOLF == 3) {
+        // [B*T][C_ALIGN] seen as super-rows of WS samples = RB3 bytes (a multiple of 16): (16 bytes, super-rows, 16-byte chunks);
+        // one box = [NCH3 chunks][128 super-rows][16 B]
+        static_assert(WOLF != 3 || K::WS > 1, "super-row form is for rows that are not a multiple of 16 bytes");
+        cuuint64_t dims[3] = {16, (cuuint64_t)(B * T / K::WS), (cuuint64_t)K::NCH3};
+        cuuint64_t strides[2] = {(cuuint64_t)K::RB3, 16};
+        cuuint32_t box[3] = {16, 128, (cuuint32_t)K::NCH3};
+        cuuint32_t estr[3] = {1, 1, 1};
+        r = enc(&tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<int8_t*>(x), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    } else if (WOLF == 2) {
         static_assert(WOLF != 2 || (C + 3) / 4 * 4 == 64, "64-byte rows");
         cuuint64_t dims[2] = {64, (cuuint64_t)(B * T)};
         cuuint64_t strides[1] = {64};
@@ -567,7 +651,7 @@ static cudaError_t launch_tc_instance(const PipeNet* net_dev, bool fast1, const 
     } else if (WOLF == 1) {
         // [B*T][C_ALIGN] seen as (16 bytes, time rows, 16-byte channel chunks): one box = [KPAD/16 chunks][128 rows][16 B]
         constexpr int CA = (C + 3) / 4 * 4;
-        static_assert(WOLF != 1 || CA % 16 == 0, "Wolf-order rows must be a multiple of 16 bytes for the tensor map");
+        static_assert(WOLF != 1 || CA % 16 == 0, "Wolf-order rows must be a multiple of 16 bytes for this tensor map (else WOLF = 3)");
         cuuint64_t dims[3] = {16, (cuuint64_t)(B * T), (cuuint64_t)(CA / 16)};
         cuuint64_t strides[2] = {(cuuint64_t)CA, 16};
         cuuint32_t box[3] = {16, 128, (cuuint32_t)(K::KPAD / 16)};
@@ -615,8 +699,9 @@ cudaError_t launch_tc(const PipeNet* net_dev, bool fast1, int C, int T, const in
 #ifndef MIBMI_WOLF_NO_SW64
 #define MIBMI_WOLF_NO_SW64 0
 #endif
-// Wolf order [B][T][C_ALIGN]: shapes whose rows are a multiple of 16 bytes (tensor-map stride rule)
-#define MIBMI_TC_WOLF_SHAPES(X) X(64, 480) X(16, 480)
+// Wolf order [B][T][C_ALIGN]: rows of 64 bytes (WOLF = 2), of 16 bytes (WOLF = 1), and -- WOLF = 3 -- rows that are not a multiple of
+// 16 bytes, as super-rows of 2 or 4 samples (C_ALIGN = 40, 24, 20, 8)
+#define MIBMI_TC_WOLF_SHAPES(X) X(64, 480) X(16, 480) X(38, 480) X(24, 480) X(19, 480) X(8, 480)
 
 bool tc_has_wolf_instance(int C, int T) {
 #define X(c, t) if (C == c && T == t) return true;
@@ -627,7 +712,7 @@ bool tc_has_wolf_instance(int C, int T) {
 
 cudaError_t launch_tc_wolf(const PipeNet* net_dev, bool fast1, int C, int T, const int8_t* x, long long B, int8_t* logits,
                            const PeerOut& peers, int8_t* t1, int8_t* t2, int8_t* t3, int8_t* t4, int num_sms, cudaStream_t stream) {
-#define X(c, t) if (C == c && T == t) return launch_tc_instance<c, t, ((c + 3) / 4 * 4 == 64 && !MIBMI_WOLF_NO_SW64) ? 2 : 1>(net_dev, fast1, x, B, logits, peers, t1, t2, t3, t4, num_sms, stream);
+#define X(c, t) if (C == c && T == t) return launch_tc_instance<c, t, ((c + 3) / 4 * 4 == 64 && !MIBMI_WOLF_NO_SW64) ? 2 : (((c + 3) / 4 * 4) % 16 == 0 ? 1 : 3)>(net_dev, fast1, x, B, logits, peers, t1, t2, t3, t4, num_sms, stream);
     MIBMI_TC_WOLF_SHAPES(X)
 #undef X
     return cudaErrorInvalidValue;
