@@ -55,10 +55,10 @@ typedef enum {
  * gen_input_header.py:73; -128 is accepted and handled exactly). */
 #define MIBMI_LAYOUT_BCT 0  /* [B][C][T]        -- module order, edgeEEGNet.forward x[B,1,C,T]         */
 #define MIBMI_LAYOUT_BTC 1  /* [B][T][C_ALIGN]  -- Wolf order of net_model_compute (gen_input_header.py:75-76);       *
-                             * read directly by the fused tcgen05 kernels when C_ALIGN is 64 or 16 (T = 480) and for       *
-                             * 22 x 1125 (rows of 24 bytes, expanded in shared memory); rows of 40 / 24 / 20 / 8 bytes at  *
-                             * T = 480 are first transposed on the GPU, 14 208 trials at a time, into a scratch allocated   *
-                             * in stream order for the call; exact generic kernel for every other shape */
+                             * read directly by the fused tcgen05 kernels of every shipped shape: rows of 64 / 16 bytes as   *
+                             * TMA tiles, rows of 40 / 24 / 20 / 8 bytes (T = 480) as super-rows of 2 or 4 samples, the      *
+                             * 24-byte rows of 22 x 1125 expanded in shared memory -- one launch, no scratch; exact generic  *
+                             * kernel for every other shape */
 
 /* Network description: the exported arrays of gen_net_header.py (names without the "net_" prefix).
  * All pointers are HOST pointers; mibmi_create copies what it needs. */
