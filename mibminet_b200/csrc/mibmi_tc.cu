@@ -50,7 +50,11 @@ __device__ long long g_prof_tc[148 * 32 * 4];
 #define TPROF_END
 #endif
 
-constexpr int kTcAW = 8, kTcBW = 8, kTcCW = 4;
+#ifndef MIBMI_TC_AW
+#define MIBMI_TC_AW 8                     // layer-1 epilogue warps: a multiple of 4 (one per TMEM lane quarter)
+#endif
+constexpr int kTcAW = MIBMI_TC_AW, kTcBW = 8, kTcCW = 4, kTcNA = kTcAW / 4;
+static_assert(kTcAW % 4 == 0 && kTcAW >= 4, "layer-1 epilogue warps come in sets of four TMEM lane quarters");
 constexpr int kTcWarpP = kTcAW + kTcBW + kTcCW, kTcWarpM1 = kTcWarpP + 1, kTcWarpM2 = kTcWarpP + 2;
 constexpr int kTcThreads = (kTcWarpM2 + 1) * 32;
 
@@ -223,8 +227,10 @@ tc_forward_kernel(const __grid_constant__ CUtensorMap tmx, const PipeNet* __rest
                 // super-row form: TMEM lane = super-row of WS samples, column 16 p + f = (sample p of the row, filter f).  The warp takes
                 // the quarter qi of tile jb3 = 32 super-rows = 32 WS samples; per half of 16 lanes the thread holds, for its four
                 // filters and two rows, the WS adjacent samples of a row: ONE store of WS bytes each into y1[f][WS row ..]
-                const int jb3 = ((warp >> 2) + n) & 1;
+                // tiles jb3 with (jb3 + n) % kTcNA == warp >> 2 (at most one per warp and trial: TILES3 <= 2 <= kTcNA)
+                const int jb3 = (((warp >> 2) - n) % kTcNA + kTcNA) % kTcNA;
                 const int sr0 = 128 * jb3 + 32 * qi;
+                static_assert(K::WS == 1 || K::TILES3 <= kTcNA, "one super-row tile per warp and trial");
                 if (jb3 < K::TILES3 && K::WS * sr0 < K::T) {
                     const uint32_t ta = tmem_base + ((uint32_t)(32 * qi) << 16) + K::TM_L1 + ab * K::TM_L1_TRIAL + 16 * K::WS * jb3;
                     const uint32_t y1s = sbase + K::OFF_Y1 + 32 + K::SLOT * (4 * buf + s);
@@ -266,17 +272,17 @@ tc_forward_kernel(const __grid_constant__ CUtensorMap tmx, const PipeNet* __rest
             // the warp's (up to) two units of a pass are loaded from TMEM together and requantised interleaved: the
                 // TMEM latency and the dependent division chains of one unit hide behind the other
     #pragma unroll 1
-                for (int jb = ((warp >> 2) + n) & 1; jb < K::TILES; jb += 4) {
-                    const int u0 = 4 * jb + qi, u1 = u0 + 8;
+                for (int jb = (((warp >> 2) - n) % kTcNA + kTcNA) % kTcNA; jb < K::TILES; jb += 2 * kTcNA) {   // tiles jb, jb + kTcNA of a pass
+                    const int u0 = 4 * jb + qi, u1 = u0 + 4 * kTcNA;
                     if (32 * u0 >= K::T) break;
-                    const bool two = jb + 2 < K::TILES && 32 * u1 < K::T;
+                    const bool two = jb + kTcNA < K::TILES && 32 * u1 < K::T;
                     uint32_t r[2][2][8];
                     const uint32_t ta = tmem_base + ((uint32_t)(32 * qi) << 16) + K::TM_L1 + ab * K::TM_L1_TRIAL + 16 * jb;
                     tmem_ld_16x256b_x2(r[0][0], ta);
                     tmem_ld_16x256b_x2(r[0][1], ta + (16u << 16));
                     if (two) {
-                        tmem_ld_16x256b_x2(r[1][0], ta + 32);
-                        tmem_ld_16x256b_x2(r[1][1], ta + 32 + (16u << 16));
+                        tmem_ld_16x256b_x2(r[1][0], ta + 16 * kTcNA);
+                        tmem_ld_16x256b_x2(r[1][1], ta + 16 * kTcNA + (16u << 16));
                     }
                     tmem_ld_wait();
     #pragma unroll

@@ -262,6 +262,25 @@ def test_full_size_batch_22x1125_every_logit():
     assert np.array_equal(net.forward(_cuda(x[perm])).cpu().numpy(), y[perm])
 
 
+@pytest.mark.parametrize("C,T", [(38, 480), (19, 480), (22, 1125)])
+def test_full_size_batch_wolf_order_every_logit(C, T):
+    """The order net_model_compute receives ([B][T][C_ALIGN]) at 65536 trials, every logit against the CPU integer path and against
+    the module-order result of the same kernel family: super-rows of 2 samples (40-byte rows), of 4 samples (20-byte rows), and the
+    24-byte rows of 22 x 1125 expanded in shared memory."""
+    B = 65536
+    net, arrays = _net(C, T, seed=4)
+    x = synth.make_trials(B, C, T, seed=55)
+    xw = _cuda(convert.to_wolf_input(x))
+    n0 = net.launch_count
+    y = net.forward(xw, layout="btc").cpu().numpy()
+    assert net.last_path == "fused" and net.launch_count - n0 == 1
+    ref = wolf_port.forward(arrays, C, T, x)
+    bad = np.nonzero((y != ref).any(axis=1))[0]
+    assert bad.size == 0, f"{bad.size} trials differ, first {bad[:5]}"
+    del xw
+    assert np.array_equal(net.forward(_cuda(x)).cpu().numpy(), y)
+
+
 def test_full_size_batch_65536_every_logit():
     """BASELINE config 2: 64 x 480, B = 65536, every logit compared with the CPU integer path."""
     C, T, B = 64, 480, 65536
