@@ -38,18 +38,21 @@ METRIC = "int8 edgeEEGNet trials/sec"
 # per launch of 65536 trials
 NCU_TRAFFIC_BYTES_PER_TRIAL = (2.013485e9 + 18.797056e6) / 65536
 # per kernel and shape: (DRAM bytes per trial, source) from `ncu --set full` dram__bytes_read.sum + dram__bytes_write.sum per launch of 65536 trials
-NCU_TRAFFIC = {("tc_forward_kernel", "64x480", "bct"): (NCU_TRAFFIC_BYTES_PER_TRIAL, "profiles/r1d_ncu_full_metrics.csv"),
-               ("tcr_forward_kernel", "22x1125", "bct"): ((1.622439e9 + 23.239168e6) / 65536, "profiles/r2o_tcr_ncu_full_metrics.csv")}
+NCU_TRAFFIC = {("tc_forward_kernel", "64x480", "bct"): ((2.013607e9 + 19.332608e6) / 65536, "profiles/r2u_tc64_ncu_full_metrics.csv"),
+               ("tcr_forward_kernel", "22x1125", "bct"): ((1.622110e9 + 23.006464e6) / 65536, "profiles/r2o_tcr_ncu_full_metrics.csv")}
 # shared-memory data pipe of the 22x1125 kernel (ncu r2o): LSU + tensor-core wavefronts per trial; one wavefront = one cycle of the pipe
-NCU_SMEM_WAVEFRONTS = {("tcr_forward_kernel", "22x1125", "bct"): (1585.9, 964.0, "profiles/r2o_tcr_ncu_full_metrics.csv")}
+NCU_SMEM_WAVEFRONTS = {("tcr_forward_kernel", "22x1125", "bct"): (1585.9, 964.0, "profiles/r2o_tcr_ncu_full_metrics.csv"),
+                       ("tc_forward_kernel", "64x480", "bct"): (434.1, 720.0, "profiles/r2u_tc64_ncu_full_metrics.csv"),
+                       ("tc_forward_kernel", "16x480", "bct"): (372.5, 576.0, "profiles/r2u_tc16_ncu_full_metrics.csv")}
 # measured on this pool (tools/probe_i8_peak.cu, profiles/r2d_int8_tcgen05_peak.jsonl): tcgen05.mma kind::i8 M128 K32, one issuing thread
 # per SM: N = 256 runs at 128 cycles per instruction = 4464 TOP/s dense int8 on 148 SMs; N <= 64 at 54.6 cycles per instruction
 INT8_PEAK_TOPS, UMMA_CYCLES_N_LE_64 = 4464.4, 54.6
 KERNEL_TEMPLATES = {"tc_forward_kernel": "tc_forward_kernel<TCfg<{C},{T}>>", "tcr_forward_kernel": "tcr_forward_kernel<RCfg<{C},{T}>>", "pipe_forward_kernel": "pipe_forward_kernel<PCfg<{C},{T},4>>",
                     }
 KERNEL_NOTES = {
-    "tc_forward_kernel": "layers 1+2 on tcgen05.mma kind::i8 (TMEM accumulators), 23 warps requantise; ncu r1d: DRAM 67 % of "
-                         "ncu peak, issue slots 59 %, not pipe bound: per-trial hand-off latency between the roles, see DESIGN.md 4.1",
+    "tc_forward_kernel": "layers 1+2 on tcgen05.mma kind::i8 (TMEM accumulators), 23 warps requantise; ncu r2u: DRAM 70 % of ncu peak, "
+                         "issue slots 55 %, shared-memory pipe 76 %, layer-1 epilogue warps 84-90 % busy (the compute-side limit, 197 M "
+                         "trials/s away from HBM), see DESIGN.md 4.1 / 10",
     "tcr_forward_kernel": "tcgen05 kernel with realigning warps (rows not 16-byte aligned), layer 2 as N = 32 MMAs: 7.5 k warp-instructions "
                           "per trial at 57 % issue, shared-memory data pipe 76 % busy (LSU 1586 + tensor-core 964 wavefronts per trial), the "
                           "layer-1 epilogue and the layer-2 MMAs alternate on a single y1 buffer; ncu r2o, DESIGN.md 4.1b",
