@@ -148,6 +148,11 @@ __device__ __forceinline__ void tmem_ld_16x256b_x2(uint32_t (&r)[8], uint32_t ta
     asm volatile("tcgen05.ld.sync.aligned.16x256b.x2.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                  : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]) : "r"(taddr));
 }
+// 16 TMEM lanes x 8 columns -> 4 registers: r[c] = (lane g + 8 (c >> 1), column 2 q + (c & 1))   (SASS: LDTM.16dp256bit)
+__device__ __forceinline__ void tmem_ld_16x256b_x1(uint32_t (&r)[4], uint32_t taddr) {
+    asm volatile("tcgen05.ld.sync.aligned.16x256b.x1.b32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(taddr));
+}
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // ---- warp-level int8 MMA (SASS: IMMA.16832.S8.S8 / IMMA.16816.S8.S8) --------------------------
@@ -186,6 +191,9 @@ __device__ __forceinline__ void stsm_x4(uint32_t addr, uint32_t r0, uint32_t r1,
 __device__ __forceinline__ void stsm_t8_x4(uint32_t addr, uint32_t r0, uint32_t r1, uint32_t r2, uint32_t r3) {
     asm volatile("stmatrix.sync.aligned.m16n8.x4.trans.shared.b8 [%0], {%1,%2,%3,%4};"
                  ::"r"(addr), "r"(r0), "r"(r1), "r"(r2), "r"(r3) : "memory");
+}
+__device__ __forceinline__ void stsm_t8_x2(uint32_t addr, uint32_t r0, uint32_t r1) {       // two matrices: addresses from lanes 0..15
+    asm volatile("stmatrix.sync.aligned.m16n8.x2.trans.shared.b8 [%0], {%1,%2};" ::"r"(addr), "r"(r0), "r"(r1) : "memory");
 }
 // transposing byte load: 16 rows x 16 bytes per matrix, lane l (l < 16 per matrix; lanes 16..31 address the
 // second matrix of .x2) supplies row l & 15.  Thread (g, q) receives per matrix M
