@@ -275,13 +275,13 @@ def main_reference(args, rank):
     if exe3 is not None and kind == "reference":
         _, build_ref = _ref_exe()
         _, tim = build_ref.run(exe3, x, procs=cores, repeat=2)
-        out["cpu_baseline"]["O3_march_native_trials_per_s"] = tim["trials_per_s"]
+        out["cpu_baseline"]["O3_x86_64_v3_trials_per_s"] = tim["trials_per_s"]
     print(json.dumps(out))
 
 
 def ref_exe_o3():
-    """The same reference sources built with -O3 (and -march=native where the binary was built on this CPU type): reported
-    beside the -O2 figure of the reference's own recipe so that the CPU side cannot be said to be sandbagged."""
+    """The same reference sources built with -O3 -march=x86-64-v3 (oracle/build_ref.py; the binary travels, so no -march=native):
+    reported beside the -O2 figure of the reference's own recipe so that the CPU side cannot be said to be held back."""
     _, build_ref = _ref_exe()
     exe = os.path.join(build_ref.OUT, build_ref.tag_for(C, T, NET_SEED), "ref_model_default_o3")
     return exe if os.path.exists(exe) else None
