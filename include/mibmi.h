@@ -66,7 +66,7 @@ typedef struct {
     int32_t C, T;          /* EEG channels, samples per trial                     (NET_C, NET_T)          */
     int32_t F1, D, F2, N;  /* F2 must equal F1*D and D == 1 (golden_model.py:169); N classes               */
     int32_t Nf;            /* temporal filter length, must be 64 (golden_model.py:216-219)                */
-    int32_t reorder_bn;    /* 1: REORDER_BN build (Makefile:34, canonical); 0: plain variant (follows the C) */
+    int32_t reorder_bn;    /* 1: REORDER_BN build (Makefile:34, canonical); 0: plain variant (follows the C); both fused */
 
     const int32_t* l1_factor;          /* [F2]            gen_net_header.py:109 */
     const int32_t* l1_offset;          /* [F2]            :110                  */

@@ -21,7 +21,7 @@ struct mibmi_net {
     GenericNet* gen_dev = nullptr;
     int8_t* w5_dev = nullptr;
     PipeNet* pipe_dev = nullptr;       // warp-specialised pipeline kernel (MIBMI_PATH_FUSED)
-    bool pipe_ok = false, pipe_fast1 = false, tc_ok = false, tcr_ok = false, tc_wolf_ok = false;
+    bool pipe_ok = false, pipe_fast1 = false, tc_ok = false, tcr_ok = false, tc_wolf_ok = false, plain = false;
     const char* pipe_why = "";
     StreamNet* stream_dev = nullptr;   // sliding-window streaming kernel (mibmi_forward_stream_int8)
     bool stream_ok = false;
@@ -100,6 +100,18 @@ bool pack_pooled(int64_t vmax, int off, int fac, Pooled* o, const char** why) {
     return true;
 }
 
+// requant of a pooled layer in the plain variant (REORDER_BN off; layer2.c:139-210, layer4.c:99-140): every accumulator is divided,
+// u = tdiv(v + (off >> 3), fac >> 3) -- the kernels compute tdiv(sig v + soff, |fac >> 3|) -- then ReLU, sum of 8, >> 3
+bool pack_pooled_plain(int64_t vmax, int off, int fac, Pooled* o, const char** why) {
+    const int d = fac >> 3, oo = off >> 3;                      // C arithmetic shifts, as in the reference
+    if (vmax + iabs64(oo) >= kMagicRange) { *why = "pooled accumulator outside the magic-division range"; return false; }
+    if (!magic_for(iabs64(d), &o->m, &o->sh)) { *why = "|factor >> 3| < 4 in a pooled layer (plain variant)"; return false; }
+    o->thr = 0;
+    o->sig = d < 0 ? -1 : 1;
+    o->soff = d < 0 ? -oo : oo;
+    return true;
+}
+
 // magic for the "no shift" form q = mulhi(x, m) + (x < 0), m = floor(2^32 / d) + 1.  With e = m d - 2^32
 // in (0, d]: x m / 2^32 = x / d + x e / (d 2^32), so the form is exact while |x| e < 2^32 (the error term stays below
 // 1 / d).  Beyond |x| >= 130 d the true quotient is >= 130 in magnitude and the approximation errs only away from zero
@@ -121,7 +133,8 @@ bool pack_pipe(const mibmi_params_t* p, PipeNet* f, const char** why) {
     const int T64 = (T / 8) / 8, T64A = align4(T64), T64P = (T64 + 1) / 2 * 2;
     memset(f, 0, sizeof(*f));
     if (F2 != 16 || p->N != 4) { *why = "fused kernel needs F2 == 16 and N == 4"; return false; }
-    if (!p->reorder_bn) { *why = "fused kernel implements the REORDER_BN variant only"; return false; }
+    const bool plain = !p->reorder_bn;       // tcgen05 kernels only (module order); the pipeline / streaming kernels refuse it
+    f->plain = plain ? 1 : 0;
     if (!pipe_has_instance(C, T)) { *why = "no fused instantiation for this (C, T)"; return false; }
     // ---- layer 1: sign of the factor folded into weights and offset
     const int half0 = (C + 1) / 2, half1 = C - half0;      // PCfg::CA / CB
@@ -199,7 +212,8 @@ bool pack_pipe(const mibmi_params_t* p, PipeNet* f, const char** why) {
         int64_t sum = 0;
         for (int j = 0; j < 64; j++) sum += iabs64(w[j]);
         Pooled po;
-        if (!pack_pooled(128 * sum, p->l2_offset[k], p->l2_factor[k], &po, why)) return false;
+        if (!(plain ? pack_pooled_plain(128 * sum, p->l2_offset[k], p->l2_factor[k], &po, why)
+                    : pack_pooled(128 * sum, p->l2_offset[k], p->l2_factor[k], &po, why))) return false;
         f->thr2[k] = po.thr; f->sig2[k] = po.sig; f->soff2[k] = po.soff; f->m2[k] = po.m; f->sh2[k] = po.sh;
         for (int n = 0; n < 16; n++)
             for (int kk = 0; kk < 96; kk++) {
@@ -255,7 +269,8 @@ bool pack_pipe(const mibmi_params_t* p, PipeNet* f, const char** why) {
         int64_t sum = 0;
         for (int i = 0; i < 16; i++) sum += iabs64(w[i]);
         Pooled po;
-        if (!pack_pooled(128 * sum, p->l4_offset[k], p->l4_factor[k], &po, why)) return false;
+        if (!(plain ? pack_pooled_plain(128 * sum, p->l4_offset[k], p->l4_factor[k], &po, why)
+                    : pack_pooled(128 * sum, p->l4_offset[k], p->l4_factor[k], &po, why))) return false;
         f->thr4[k] = po.thr; f->sig4[k] = po.sig; f->soff4[k] = po.soff; f->m4[k] = po.m; f->sh4[k] = po.sh;
     }
     for (int hf = 0; hf < 2; hf++)
@@ -435,13 +450,15 @@ cudaError_t launch_fused_bct(mibmi_net* net, int path, const int8_t* x, int64_t 
                              int8_t* t1, int8_t* t2, int8_t* t3, int8_t* t4, cudaStream_t stream, int* which) {
     if (path == MIBMI_PATH_FUSED && net->tc_ok) {
         *which = K_TC;
-        return launch_tc(net->pipe_dev, net->pipe_fast1, net->C, net->T, x, B, logits, peers, t1, t2, t3, t4, net->num_sms, stream);
+        return launch_tc(net->pipe_dev, net->pipe_fast1, net->C, net->T, x, B, logits, peers, t1, t2, t3, t4, net->num_sms, stream,
+                         net->plain);
     }
     if (path == MIBMI_PATH_FUSED && net->tcr_ok) {
         *which = K_TCR;
         return launch_tcr(net->pipe_dev, net->pipe_fast1, net->C, net->T, x, B, MIBMI_LAYOUT_BCT, logits, peers, t1, t2, t3, t4,
-                          net->num_sms, stream);
+                          net->num_sms, stream, net->plain);
     }
+    if (net->plain) return cudaErrorNotSupported;       // the mma.sync pipeline kernel implements REORDER_BN only
     *which = K_PIPE;
     return launch_pipe(net->pipe_dev, net->pipe_fast1, net->C, net->T, x, B, logits, peers, t1, t2, t3, t4, net->num_sms, stream);
 }
@@ -641,13 +658,18 @@ int mibmi_create(const mibmi_params_t* p, int device, mibmi_net_t** out) {
     }
     n->pipe_ok = pack_pipe(p, pn, &n->pipe_why);
     n->pipe_fast1 = pn->fast1 != 0;
+    n->plain = pn->plain != 0;
     n->tc_ok = n->pipe_ok && tc_has_instance(p->C, p->T);
     n->tcr_ok = n->pipe_ok && tcr_has_instance(p->C, p->T);
-    n->tc_wolf_ok = n->tc_ok && tc_has_wolf_instance(p->C, p->T);
-    n->tcr_wolf_ok = n->tcr_ok && tcr_has_wolf_instance(p->C, p->T);
-    n->wolf_reorder_ok = n->pipe_ok && reorder_has_instance(p->C, p->T);     // used when the mma.sync pipeline kernel is forced
-    if (n->pipe_ok) n->stream_ok = pack_stream(p, pn, sn, &n->stream_why);
-    else n->stream_why = n->pipe_why;
+    if (n->plain && !n->tc_ok && !n->tcr_ok && n->pipe_ok) {        // the plain variant exists in the tcgen05 kernels only
+        n->pipe_ok = false;
+        n->pipe_why = "the plain (REORDER_BN off) variant needs a tcgen05 instantiation of this (C, T)";
+    }
+    n->tc_wolf_ok = n->tc_ok && !n->plain && tc_has_wolf_instance(p->C, p->T);       // plain: module order only
+    n->tcr_wolf_ok = n->tcr_ok && !n->plain && tcr_has_wolf_instance(p->C, p->T);
+    n->wolf_reorder_ok = n->pipe_ok && !n->plain && reorder_has_instance(p->C, p->T);     // used when the mma.sync pipeline kernel is forced
+    if (n->pipe_ok && !n->plain) n->stream_ok = pack_stream(p, pn, sn, &n->stream_why);
+    else n->stream_why = n->pipe_ok ? "the streaming kernel implements the REORDER_BN variant only" : n->pipe_why;
 
     cudaDeviceProp prop;
     if (e == cudaSuccess) e = cudaGetDeviceProperties(&prop, device);
@@ -707,6 +729,7 @@ int mibmi_set_option(mibmi_net_t* net, int option, int64_t value) {
             if (value != MIBMI_PATH_AUTO && value != MIBMI_PATH_GENERIC && value != MIBMI_PATH_FUSED && value != MIBMI_PATH_FUSED_PIPE)
                 return MIBMI_ERR_PARAM;
             if ((value == MIBMI_PATH_FUSED || value == MIBMI_PATH_FUSED_PIPE) && !net->pipe_ok) return MIBMI_ERR_UNSUPPORTED;
+            if (value == MIBMI_PATH_FUSED_PIPE && net->plain) return MIBMI_ERR_UNSUPPORTED;      // REORDER_BN only
             net->force_path = (int)value;
             return MIBMI_OK;
         case MIBMI_OPT_STREAM_MODE:

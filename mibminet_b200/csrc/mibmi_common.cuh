@@ -48,7 +48,10 @@ struct PipeNet {
     uint32_t w1blk[kPipeMaxKB16][2][32];
     int off1[16], m1[16], sh1[16];
     int fast1;                      // 1: sh1 == 0 everywhere (magic = floor(2^32/d)+1, exact after clip8)
-    int pad0_[3];
+    int plain;                      // 1: the plain (REORDER_BN off) variant, layer2.c:139-210 / layer4.c:99-140: the pooled layers
+                                    // requantise EVERY accumulator, u = tdiv(v + (off >> 3), fac >> 3), then ReLU, sum of 8, >> 3;
+                                    // sig / soff / m / sh of layers 2 and 4 then describe fac >> 3 and off >> 3 (thr unused)
+    int pad0_[2];
     // layer 1 for tcgen05.mma: W1 [16 filters][KPAD channels] as K-major 8 x 16-byte core matrices,
     // byte (n >> 3) * (KPAD / 16) * 128 + (c >> 4) * 128 + (n & 7) * 16 + (c & 15), natural channel order
     alignas(16) uint8_t w1umma[16 * 64];

@@ -34,7 +34,8 @@ cudaError_t launch_pipe(const PipeNet* net_dev, bool fast1, int C, int T, const 
 // fused path for shapes with 16-byte-aligned rows.  Same PipeNet, same optional taps.
 bool tc_has_instance(int C, int T);
 cudaError_t launch_tc(const PipeNet* net_dev, bool fast1, int C, int T, const int8_t* x, long long B, int8_t* logits,
-                      const PeerOut& peers, int8_t* t1, int8_t* t2, int8_t* t3, int8_t* t4, int num_sms, cudaStream_t stream);
+                      const PeerOut& peers, int8_t* t1, int8_t* t2, int8_t* t3, int8_t* t4, int num_sms, cudaStream_t stream,
+                      bool plain = false);      // plain: the REORDER_BN-off variant (PipeNet::plain), module order only
 
 // The same kernel fed from the Wolf order [B][T][C_ALIGN] of net_model_compute (K-major layer-1 operand through a 3-D tensor map).
 bool tc_has_wolf_instance(int C, int T);
@@ -48,7 +49,8 @@ bool tcr_has_instance(int C, int T);
 // to the K-major 32-byte rows of the layer-1 operand inside the kernel -- no scratch, no second pass over HBM)
 bool tcr_has_wolf_instance(int C, int T);
 cudaError_t launch_tcr(const PipeNet* net_dev, bool fast1, int C, int T, const int8_t* x, long long B, int layout, int8_t* logits,
-                       const PeerOut& peers, int8_t* t1, int8_t* t2, int8_t* t3, int8_t* t4, int num_sms, cudaStream_t stream);
+                       const PeerOut& peers, int8_t* t1, int8_t* t2, int8_t* t3, int8_t* t4, int num_sms, cudaStream_t stream,
+                       bool plain = false);
 
 // Wolf order [n][T][C_ALIGN] -> module order [n][C][T] (mibmi_reorder.cu) for rows of 8 / 20 / 24 / 40 bytes; y 4-byte aligned.
 bool reorder_has_instance(int C, int T);

@@ -140,7 +140,9 @@ __device__ __forceinline__ constexpr uint32_t umma_idesc_i8_kk(int M, int N) {
 // matrices (rows 16 B apart, SBO 128 B, LBO 2048 B), no swizzle -- the descriptor form of the layer-2 Hankel operand (WOLF = 1).
 // WOLF = 2 (rows of exactly 64 bytes): 2-D tiles [128 rows][64 B] with the 64-byte swizzle, K-major SWIZZLE_64B descriptor
 // (SBO 512 B = 8 rows, the second k-step starts 32 B into the row): full-row TMA requests instead of 16-byte ones.
-template <class K, bool FAST1, bool TAPS, int WOLF>
+// PLAIN: the REORDER_BN-off variant of the pooled layers (layer2.c:139-210, layer4.c:99-140 -- the C, which does not clip the layer-4
+// quotients): every accumulator is divided, u = tdiv(sig v + soff, |fac >> 3|), then ReLU (layer 2: clip to 127 first), sum of 8, >> 3.
+template <class K, bool FAST1, bool TAPS, int WOLF, bool PLAIN = false>
 __global__ void __launch_bounds__(kTcThreads, 1)
 tc_forward_kernel(const __grid_constant__ CUtensorMap tmx, const PipeNet* __restrict__ net, long long B,
                   int8_t* __restrict__ logits, const PeerOut peers, int8_t* __restrict__ tap1, int8_t* __restrict__ tap2,
@@ -473,10 +475,16 @@ tc_forward_kernel(const __grid_constant__ CUtensorMap tmx, const PipeNet* __rest
                     int s0 = 0, s1 = 0;
 #pragma unroll
                     for (int i = 0; i < 8; i++) {
-                        s0 += max((int)r[c][i], ca.x);
-                        s1 += max((int)r[c][8 + i], ca.x);
+                        if (PLAIN) {
+                            s0 += min(max(tdiv_magic((int)r[c][i] * ca.y + ca.z, ca.w, shk), 0), 127);
+                            s1 += min(max(tdiv_magic((int)r[c][8 + i] * ca.y + ca.z, ca.w, shk), 0), 127);
+                        } else {
+                            s0 += max((int)r[c][i], ca.x);
+                            s1 += max((int)r[c][8 + i], ca.x);
+                        }
                     }
-                    const uint32_t o01 = pack2_sat(tdiv_magic(s0 * ca.y + ca.z, ca.w, shk), tdiv_magic(s1 * ca.y + ca.z, ca.w, shk));
+                    const uint32_t o01 = PLAIN ? (uint32_t)((s0 >> 3) | ((s1 >> 3) << 8))          // 0 .. 127 each
+                                               : pack2_sat(tdiv_magic(s0 * ca.y + ca.z, ca.w, shk), tdiv_magic(s1 * ca.y + ca.z, ca.w, shk));
                     if (lane < K::ROWS) {
                         *reinterpret_cast<uint16_t*>(y2s + k * K::Y2S) = (uint16_t)o01;
                         if (TAPS && tap2 && b0 + s < B) {
@@ -585,12 +593,17 @@ tc_forward_kernel(const __grid_constant__ CUtensorMap tmx, const PipeNet* __rest
                 int s_lo = 0, s_hi = 0;
 #pragma unroll
                 for (int v = 0; v < 4; v++) {
-                    s_lo += max(c[v][0], thr_lo) + max(c[v][1], thr_lo);
-                    s_hi += max(c[v][2], thr_hi) + max(c[v][3], thr_hi);
+                    if (PLAIN) {
+                        s_lo += max(tdiv_magic(c[v][0] * sig_lo + soff_lo, m4_lo, sh4_lo), 0) + max(tdiv_magic(c[v][1] * sig_lo + soff_lo, m4_lo, sh4_lo), 0);
+                        s_hi += max(tdiv_magic(c[v][2] * sig_hi + soff_hi, m4_hi, sh4_hi), 0) + max(tdiv_magic(c[v][3] * sig_hi + soff_hi, m4_hi, sh4_hi), 0);
+                    } else {
+                        s_lo += max(c[v][0], thr_lo) + max(c[v][1], thr_lo);
+                        s_hi += max(c[v][2], thr_hi) + max(c[v][3], thr_hi);
+                    }
                 }
                 const int grp = 4 * s4 + q;
-                const int o_lo = clip8(tdiv_magic(s_lo * sig_lo + soff_lo, m4_lo, sh4_lo));
-                const int o_hi = clip8(tdiv_magic(s_hi * sig_hi + soff_hi, m4_hi, sh4_hi));
+                const int o_lo = PLAIN ? clip8(s_lo >> 3) : clip8(tdiv_magic(s_lo * sig_lo + soff_lo, m4_lo, sh4_lo));
+                const int o_hi = PLAIN ? clip8(s_hi >> 3) : clip8(tdiv_magic(s_hi * sig_hi + soff_hi, m4_hi, sh4_hi));
                 if (grp < K::T64) {
                     y4[g * K::T64P + grp] = (uint8_t)o_lo;
                     y4[(g + 8) * K::T64P + grp] = (uint8_t)o_hi;
@@ -630,7 +643,7 @@ tc_forward_kernel(const __grid_constant__ CUtensorMap tmx, const PipeNet* __rest
 template <int C, int T, int WOLF>
 static cudaError_t launch_tc_instance(const PipeNet* net_dev, bool fast1, const int8_t* x, long long B, int8_t* logits,
                                       const PeerOut& peers, int8_t* t1, int8_t* t2, int8_t* t3, int8_t* t4, int num_sms,
-                                      cudaStream_t stream) {
+                                      cudaStream_t stream, bool plain = false) {
     using K = TCfg<C, T>;
     tmap_encode_t enc = tmap_encoder();
     if (!enc) return cudaErrorNotSupported;
@@ -674,8 +687,11 @@ static cudaError_t launch_tc_instance(const PipeNet* net_dev, bool fast1, const 
     }
     if (r != CUDA_SUCCESS) return cudaErrorInvalidValue;
     const bool taps = t1 || t2 || t3 || t4;
-    auto kern = taps ? tc_forward_kernel<K, false, true, WOLF>
-                     : (fast1 ? tc_forward_kernel<K, true, false, WOLF> : tc_forward_kernel<K, false, false, WOLF>);
+    if (plain && WOLF != 0) return cudaErrorNotSupported;      // the plain variant is instantiated for the module order only
+    constexpr bool P0 = WOLF == 0;                             // (keeps the Wolf-order instantiations from doubling)
+    auto kern = plain ? (taps ? tc_forward_kernel<K, false, true, WOLF, P0> : tc_forward_kernel<K, false, false, WOLF, P0>)
+                : taps ? tc_forward_kernel<K, false, true, WOLF>
+                       : (fast1 ? tc_forward_kernel<K, true, false, WOLF> : tc_forward_kernel<K, false, false, WOLF>);
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, K::SMEM);
     if (e != cudaSuccess) return e;
     long long grid = num_sms;
@@ -695,8 +711,8 @@ bool tc_has_instance(int C, int T) {
 }
 
 cudaError_t launch_tc(const PipeNet* net_dev, bool fast1, int C, int T, const int8_t* x, long long B, int8_t* logits,
-                      const PeerOut& peers, int8_t* t1, int8_t* t2, int8_t* t3, int8_t* t4, int num_sms, cudaStream_t stream) {
-#define X(c, t) if (C == c && T == t) return launch_tc_instance<c, t, 0>(net_dev, fast1, x, B, logits, peers, t1, t2, t3, t4, num_sms, stream);
+                      const PeerOut& peers, int8_t* t1, int8_t* t2, int8_t* t3, int8_t* t4, int num_sms, cudaStream_t stream, bool plain) {
+#define X(c, t) if (C == c && T == t) return launch_tc_instance<c, t, 0>(net_dev, fast1, x, B, logits, peers, t1, t2, t3, t4, num_sms, stream, plain);
     MIBMI_TC_SHAPES(X)
 #undef X
     return cudaErrorInvalidValue;

@@ -188,7 +188,8 @@ __device__ __forceinline__ void tcr_realign_row(const uint8_t* rbase, uint8_t* x
     }
 }
 
-template <class K, bool FAST1, bool TAPS>
+// PLAIN: the REORDER_BN-off variant of the pooled layers (see mibmi_tc.cu)
+template <class K, bool FAST1, bool TAPS, bool PLAIN = false>
 __global__ void __launch_bounds__(kRThreads, 1)
 tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net, long long B, int8_t* __restrict__ logits,
                    const PeerOut peers, int8_t* __restrict__ tap1, int8_t* __restrict__ tap2, int8_t* __restrict__ tap3,
@@ -532,8 +533,10 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
                         const int col = 24 - 8 * p;
                         int acc = 0;
 #pragma unroll
-                        for (int e = 0; e < 8; e++) acc += max((int)r[col >> 4][(col & 15) + e], ca.x);
-                        s[p] = tdiv_magic(acc * ca.y + ca.z, ca.w, shk);
+                        for (int e = 0; e < 8; e++)
+                            acc += PLAIN ? min(max(tdiv_magic((int)r[col >> 4][(col & 15) + e] * ca.y + ca.z, ca.w, shk), 0), 127)
+                                         : max((int)r[col >> 4][(col & 15) + e], ca.x);
+                        s[p] = PLAIN ? (acc >> 3) : tdiv_magic(acc * ca.y + ca.z, ca.w, shk);
                     }
                     const uint32_t o = pack4_sat(s[0], s[1], s[2], s[3]);
                     if (valid) {
@@ -618,12 +621,17 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
                 int s_lo = 0, s_hi = 0;
 #pragma unroll
                 for (int v = 0; v < 4; v++) {
-                    s_lo += max(c[v][0], thr_lo) + max(c[v][1], thr_lo);
-                    s_hi += max(c[v][2], thr_hi) + max(c[v][3], thr_hi);
+                    if (PLAIN) {
+                        s_lo += max(tdiv_magic(c[v][0] * sig_lo + soff_lo, m4_lo, sh4_lo), 0) + max(tdiv_magic(c[v][1] * sig_lo + soff_lo, m4_lo, sh4_lo), 0);
+                        s_hi += max(tdiv_magic(c[v][2] * sig_hi + soff_hi, m4_hi, sh4_hi), 0) + max(tdiv_magic(c[v][3] * sig_hi + soff_hi, m4_hi, sh4_hi), 0);
+                    } else {
+                        s_lo += max(c[v][0], thr_lo) + max(c[v][1], thr_lo);
+                        s_hi += max(c[v][2], thr_hi) + max(c[v][3], thr_hi);
+                    }
                 }
                 const int grp = 4 * s4 + q;
-                const int o_lo = clip8(tdiv_magic(s_lo * sig_lo + soff_lo, m4_lo, sh4_lo));
-                const int o_hi = clip8(tdiv_magic(s_hi * sig_hi + soff_hi, m4_hi, sh4_hi));
+                const int o_lo = PLAIN ? clip8(s_lo >> 3) : clip8(tdiv_magic(s_lo * sig_lo + soff_lo, m4_lo, sh4_lo));
+                const int o_hi = PLAIN ? clip8(s_hi >> 3) : clip8(tdiv_magic(s_hi * sig_hi + soff_hi, m4_hi, sh4_hi));
                 if (grp < K::T64) {
                     y4[g * K::T64P + grp] = (uint8_t)o_lo;
                     y4[(g + 8) * K::T64P + grp] = (uint8_t)o_hi;
@@ -663,11 +671,14 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
 template <int C, int T, int WOLF>
 static cudaError_t launch_tcr_instance(const PipeNet* net_dev, bool fast1, const int8_t* x, long long B, int8_t* logits,
                                        const PeerOut& peers, int8_t* t1, int8_t* t2, int8_t* t3, int8_t* t4, int num_sms,
-                                       cudaStream_t stream) {
+                                       cudaStream_t stream, bool plain) {
     using K = RCfg<C, T, WOLF>;
     const bool taps = t1 || t2 || t3 || t4;
-    auto kern = taps ? tcr_forward_kernel<K, false, true>
-                     : (fast1 ? tcr_forward_kernel<K, true, false> : tcr_forward_kernel<K, false, false>);
+    if (plain && WOLF != 0) return cudaErrorNotSupported;      // the plain variant is instantiated for the module order only
+    constexpr bool P0 = WOLF == 0;
+    auto kern = plain ? (taps ? tcr_forward_kernel<K, false, true, P0> : tcr_forward_kernel<K, false, false, P0>)
+                : taps ? tcr_forward_kernel<K, false, true>
+                       : (fast1 ? tcr_forward_kernel<K, true, false> : tcr_forward_kernel<K, false, false>);
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, K::SMEM);
     if (e != cudaSuccess) return e;
     long long grid = num_sms;
@@ -688,11 +699,11 @@ bool tcr_has_instance(int C, int T) {
 bool tcr_has_wolf_instance(int C, int T) { return tcr_has_instance(C, T); }
 
 cudaError_t launch_tcr(const PipeNet* net_dev, bool fast1, int C, int T, const int8_t* x, long long B, int layout, int8_t* logits,
-                       const PeerOut& peers, int8_t* t1, int8_t* t2, int8_t* t3, int8_t* t4, int num_sms, cudaStream_t stream) {
+                       const PeerOut& peers, int8_t* t1, int8_t* t2, int8_t* t3, int8_t* t4, int num_sms, cudaStream_t stream, bool plain) {
 #define X(c, t)                                                                                                                     \
     if (C == c && T == t)                                                                                                           \
-        return layout == 0 ? launch_tcr_instance<c, t, 0>(net_dev, fast1, x, B, logits, peers, t1, t2, t3, t4, num_sms, stream)     \
-                           : launch_tcr_instance<c, t, 1>(net_dev, fast1, x, B, logits, peers, t1, t2, t3, t4, num_sms, stream);
+        return layout == 0 ? launch_tcr_instance<c, t, 0>(net_dev, fast1, x, B, logits, peers, t1, t2, t3, t4, num_sms, stream, plain)     \
+                           : launch_tcr_instance<c, t, 1>(net_dev, fast1, x, B, logits, peers, t1, t2, t3, t4, num_sms, stream, plain);
     MIBMI_TCR_SHAPES(X)
 #undef X
     return cudaErrorInvalidValue;

@@ -144,6 +144,7 @@ def _pipe_blob(arrays, C, T, **kw):
 _OFF_OFF1 = 4 * 2 * 32 * 4
 _OFF_W1UMMA = _OFF_OFF1 + 3 * 64 + 16
 _OFF_W2UMMA = _OFF_W1UMMA + 16 * 64
+_OFF_C2 = _OFF_W2UMMA + 16 * 1536 + 16 * 24 * 32 * 4          # thr2, sig2, soff2, m2, sh2: 16 ints each
 
 
 def test_fused_packing_tcgen05_operands(golden):
@@ -174,9 +175,31 @@ def test_fused_packing_tcgen05_operands(golden):
     assert np.array_equal(off1, sg * np.asarray(fx["arrays"]["l1_offset"]))
 
 
+def test_fused_packing_plain_variant_constants():
+    """REORDER_BN off: the pooled layers' constants describe fac >> 3 and off >> 3 (layer2.c:139-210): sign folded into sig / soff,
+    magic pair exact for |fac >> 3| on the accumulator range; |fac >> 3| < 4 is refused (generic kernel)."""
+    fx = load_golden(golden_files()[0])
+    blob, why = _pipe_blob(fx["arrays"], fx["C"], fx["T"], reorder_bn=False)
+    assert blob is not None, why
+    assert blob[_OFF_OFF1 + 3 * 64:_OFF_OFF1 + 3 * 64 + 8].view(np.int32).tolist()[1] == 1          # PipeNet::plain
+    c2 = blob[_OFF_C2:_OFF_C2 + 5 * 64].view(np.int32).reshape(5, 16).astype(np.int64)             # thr2, sig2, soff2, m2, sh2
+    fac, off = np.asarray(fx["arrays"]["l2_factor"], np.int64) >> 3, np.asarray(fx["arrays"]["l2_offset"], np.int64) >> 3
+    assert np.array_equal(c2[1], np.where(fac < 0, -1, 1)) and np.array_equal(c2[2], np.where(fac < 0, -off, off))
+    rng = np.random.default_rng(0)
+    for k in range(16):
+        x = np.concatenate([rng.integers(-2 ** 28, 2 ** 28, 2000), np.arange(-300, 300) * abs(fac[k]), [0, 1, -1]]).astype(np.int64)
+        q = ((x * c2[3][k]) >> 32 >> c2[4][k]) + (x < 0)
+        assert np.array_equal(q, np.sign(x) * (np.abs(x) // abs(fac[k]))), k
+    a = dict(fx["arrays"])
+    a["l2_factor"] = a["l2_factor"].copy()
+    a["l2_factor"][3] = 31                                             # 31 >> 3 == 3
+    blob, why = _pipe_blob(a, fx["C"], fx["T"], reorder_bn=False)
+    assert blob is None and ">> 3" in why
+    assert _pipe_blob(a, fx["C"], fx["T"])[0] is not None              # fine with REORDER_BN
+
+
 def test_fused_packing_refuses_what_it_cannot_run():
     fx = load_golden(golden_files()[0])
-    assert _pipe_blob(fx["arrays"], fx["C"], fx["T"], reorder_bn=False)[0] is None
     a = dict(fx["arrays"])
     a["l1_factor"] = a["l1_factor"].copy()
     a["l1_factor"][0] = 3

@@ -51,11 +51,51 @@ def test_reference_fixtures_taps_and_plain_variant(golden):
     for name in ("y1", "y2", "y3", "y4"):
         assert np.array_equal(taps[name].cpu().numpy(), fx[f"golden_reorder_{name}"]), name
     plain = Int8Net(fx["arrays"], C=fx["C"], T=fx["T"], device="cuda:0", reorder_bn=False)
-    assert not plain.fused_supported()[0]
-    yp, tp = plain.forward_taps(x)
+    yp, tp = plain.forward_taps(x)                            # AUTO with taps: the exact generic kernel
+    assert plain.last_path == "generic"
     assert np.array_equal(yp.cpu().numpy(), fx["c_plain"])   # follows the C (layer4.c:115-117)
     for name in ("y1", "y2", "y3"):
         assert np.array_equal(tp[name].cpu().numpy(), fx[f"golden_plain_{name}"]), name
+
+
+def test_plain_variant_on_the_fused_kernels(golden):
+    """REORDER_BN off (layer2.c:139-210, layer4.c:99-140: every accumulator divided, ReLU, sum of 8, >> 3) on the tcgen05 kernels:
+    logits equal to the reference C built without -DREORDER_BN, per-layer taps of the fused kernel equal to the oracle's;
+    Wolf order and the forced pipeline kernel fall back / refuse."""
+    fx = golden
+    C, T = fx["C"], fx["T"]
+    x = _cuda(fx["x"])
+    plain = Int8Net(fx["arrays"], C=C, T=T, device="cuda:0", reorder_bn=False)
+    ok, why = plain.fused_supported()
+    assert ok, why
+    y = plain.forward(x).cpu().numpy()
+    assert plain.last_path == "fused" and plain.last_kernel in ("tc_forward_kernel", "tcr_forward_kernel")
+    assert np.array_equal(y, fx["c_plain"])
+    ref, lay = wolf_port.forward(fx["arrays"], C, T, fx["x"], reorder_bn=False, return_layers=True)
+    assert np.array_equal(ref, fx["c_plain"])
+    plain.set_path("fused")
+    yt, taps = plain.forward_taps(x)
+    assert np.array_equal(yt.cpu().numpy(), ref)
+    for name in ("y1", "y2", "y3", "y4"):
+        assert np.array_equal(taps[name].cpu().numpy(), lay[name]), name
+    plain.set_path("auto")
+    xw = _cuda(convert.to_wolf_input(fx["x"]))
+    assert np.array_equal(plain.forward(xw, layout="btc").cpu().numpy(), ref) and plain.last_path == "generic"
+    with pytest.raises(Exception):
+        plain.set_path("fused_pipe")
+
+
+@pytest.mark.parametrize("C,T,B", [(64, 480, 65536), (22, 1125, 20000), (38, 480, 4099), (8, 480, 777)])
+def test_plain_variant_fused_vs_oracle_random(C, T, B):
+    arrays = _net(C, T, seed=41)[1]
+    net = Int8Net(arrays, C=C, T=T, device="cuda:0", reorder_bn=False)
+    x = synth.make_trials(B, C, T, seed=6)
+    y = net.forward(_cuda(x)).cpu().numpy()
+    assert net.last_path == "fused", net.fused_supported()
+    ref = wolf_port.forward(arrays, C, T, x, reorder_bn=False)
+    bad = np.nonzero((y != ref).any(axis=1))[0]
+    assert bad.size == 0, f"{bad.size} trials differ, first {bad[:5]}"
+    assert np.array_equal(ref[:300], golden_np.forward(arrays, C, T, x[:300], reorder_bn=False))
 
 
 def test_reference_fixtures_taps_from_the_fused_kernel(golden):
