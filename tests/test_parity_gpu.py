@@ -321,6 +321,37 @@ def test_full_size_batch_wolf_order_every_logit(C, T):
     assert np.array_equal(net.forward(_cuda(x)).cpu().numpy(), y)
 
 
+@pytest.mark.parametrize("C,T,layout", [(22, 1125, "bct"), (8, 480, "btc")])
+def test_batch_beyond_one_launch(C, T, layout):
+    """The upper end of BASELINE config 3's batch sweep and past it: 2^20 + 37 trials in ONE call, which the library splits into two
+    launches (32-bit tensor-map coordinates / kMaxLaunchTrials).  The head, the trials on both sides of the split and the tail are
+    compared with the CPU integer path; the whole result with the same trials run in smaller calls (determinism and per-trial
+    independence at full size)."""
+    free, _ = torch.cuda.mem_get_info()
+    B = (1 << 20) + 37
+    CA = C if layout == "bct" else (C + 3) // 4 * 4
+    if free < 2.5 * B * CA * T:
+        pytest.skip("not enough device memory for a 2^20-trial batch")
+    net, arrays = _net(C, T, seed=9)
+    g = torch.Generator(device="cuda")
+    g.manual_seed(3)
+    x = torch.randint(-127, 128, (B, C, T), dtype=torch.int8, device="cuda", generator=g)
+    if layout == "btc":
+        xw = torch.zeros((B, T, CA), dtype=torch.int8, device="cuda")
+        xw[:, :, :C] = x.transpose(1, 2)
+    else:
+        xw = x
+    n0 = net.launch_count
+    y = net.forward(xw, layout=layout)
+    assert net.last_path == "fused" and net.launch_count - n0 == 2
+    for lo, hi in ((0, 2048), ((1 << 20) - 1024, (1 << 20) + 37)):
+        ref = wolf_port.forward(arrays, C, T, x[lo:hi].cpu().numpy())
+        assert np.array_equal(y[lo:hi].cpu().numpy(), ref), (lo, hi)
+    step = 1 << 18                          # a multiple of 16 trials: every piece is 16-byte aligned again
+    y2 = torch.cat([net.forward(xw[i:i + step], layout=layout) for i in range(0, B, step)])
+    assert torch.equal(y, y2)
+
+
 def test_full_size_batch_65536_every_logit():
     """BASELINE config 2: 64 x 480, B = 65536, every logit compared with the CPU integer path."""
     C, T, B = 64, 480, 65536
