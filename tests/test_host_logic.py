@@ -175,6 +175,30 @@ def test_fused_packing_tcgen05_operands(golden):
     assert np.array_equal(off1, sg * np.asarray(fx["arrays"]["l1_offset"]))
 
 
+@pytest.mark.parametrize("C", [38, 24, 19, 8])
+def test_fused_packing_superrow_weights(C):
+    """PipeNet::w1x, the block-structured layer-1 weights of the Wolf-order super-row form (rows of 40 / 24 / 20 / 8 bytes):
+    W1x[16 p + f][C_ALIGN p + c] = sign(factor f) W1[f][c] for the S = 16 / gcd(C_ALIGN, 16) samples p of a super-row, zero
+    elsewhere, as K-major 8 x 16-byte core matrices over KP = ceil(S C_ALIGN / 32) * 32 bytes."""
+    import math
+    T = 480
+    arrays = convert.params_from_state_dict(synth.make_state_dict(C=C, T=T, seed=5), C=C, T=T).to_wolf_arrays()
+    blob, why = _pipe_blob(arrays, C, T)
+    assert blob is not None, why
+    CA = convert.align4(C)
+    S = 16 // math.gcd(CA, 16)
+    KP = (S * CA + 31) // 32 * 32
+    w1x = blob[len(blob) - 64 * 96:].view(np.int8)                     # last member of PipeNet
+    w1 = np.asarray(arrays["l1_weight_align"]).reshape(16, CA).astype(np.int64)
+    sg = np.where(np.asarray(arrays["l1_factor"]) < 0, -1, 1)
+    exp = np.zeros((16 * S, KP), np.int64)
+    for p_ in range(S):
+        exp[16 * p_:16 * p_ + 16, CA * p_:CA * p_ + C] = sg[:, None] * w1[:, :C]
+    n, k = np.meshgrid(np.arange(16 * S), np.arange(KP), indexing="ij")
+    got = w1x[(n >> 3) * (KP // 16) * 128 + (k >> 4) * 128 + (n & 7) * 16 + (k & 15)]
+    assert np.array_equal(got, exp)
+
+
 def test_fused_packing_plain_variant_constants():
     """REORDER_BN off: the pooled layers' constants describe fac >> 3 and off >> 3 (layer2.c:139-210): sign folded into sig / soff,
     magic pair exact for |fac >> 3| on the accumulator range; |fac >> 3| < 4 is refused (generic kernel)."""
