@@ -63,7 +63,11 @@ constexpr int kTcrL3Unroll = MIBMI_TCR_L3_UNROLL, kTcrL4Unroll = MIBMI_TCR_L4_UN
 #ifndef MIBMI_TCR_RW
 #define MIBMI_TCR_RW 4
 #endif
-constexpr int kRAW = 12, kRBW = 8, kRCW = 4, kRRW = MIBMI_TCR_RW;
+#ifndef MIBMI_TCR_AW
+#define MIBMI_TCR_AW 12                   // layer-1 epilogue warps (a multiple of 4: one per TMEM lane quarter)
+#endif
+constexpr int kRAW = MIBMI_TCR_AW, kRNA = kRAW / 4, kRBW = 8, kRCW = 4, kRRW = MIBMI_TCR_RW;
+static_assert(kRAW % 4 == 0 && kRAW >= 4, "layer-1 epilogue warps come in sets of four");
 constexpr int kRWarpB = kRAW, kRWarpC = kRAW + kRBW, kRWarpR = kRWarpC + kRCW, kRWarpP = kRWarpR + kRRW,
               kRWarpM1 = kRWarpP + 1, kRWarpM2 = kRWarpP + 2;
 constexpr int kRThreads = (kRWarpM2 + 1) * 32;
@@ -249,7 +253,7 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
 
     if (warp < kRAW) {
         // =====================================================================================
-        // A: layer-1 epilogue.  TMEM lanes 32 (warp & 3) .. + 31 of the tiles jt = (warp >> 2) + n (mod 3), + 3, ...
+        // A: layer-1 epilogue.  TMEM lanes 32 (warp & 3) .. + 31 of the tiles jt = (warp >> 2) + n (mod kRNA), + kRNA, ...
         // =====================================================================================
         int off1[2][2], mg1[2][2], sh1[2][2];
 #pragma unroll
@@ -275,7 +279,7 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
             const uint32_t yb = st_off + K::SLOT * j;
             const long long b = trial_of(n);
             // the warp's tiles jt0, jt0 + 3, ...: the TMEM load of the next unit is in flight while this one is requantised
-            const int jt0 = (a3 + n) % 3;
+            const int jt0 = (a3 + n) % kRNA;
             const uint32_t ta0 = tmem_base + ((uint32_t)(32 * qi) << 16) + ab * K::TM_L1_TRIAL;
             uint32_t r[2][2][8];
             if (32 * (4 * jt0 + qi) < K::T) {
@@ -285,13 +289,13 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
             // the y1 buffer is single: the layer-2 MMAs of the previous group must have read it (one commit per group)
             RWAITL(1, sbase + K::BAR_TILE_DONE, (gq & 1) ^ 1);
 #pragma unroll
-            for (int it = 0; it < (K::TILES + 2) / 3; it++) {
-                const int jt = jt0 + 3 * it, u = 4 * jt + qi;
+            for (int it = 0; it < (K::TILES + kRNA - 1) / kRNA; it++) {
+                const int jt = jt0 + kRNA * it, u = 4 * jt + qi;
                 if (jt >= K::TILES || 32 * u >= K::T) break;
                 tmem_ld_wait();
-                if (it + 1 < (K::TILES + 2) / 3 && jt + 3 < K::TILES && 32 * (u + 12) < K::T) {
-                    tmem_ld_16x256b_x2(r[(it + 1) & 1][0], ta0 + 16 * (jt + 3));
-                    tmem_ld_16x256b_x2(r[(it + 1) & 1][1], ta0 + 16 * (jt + 3) + (16u << 16));
+                if (it + 1 < (K::TILES + kRNA - 1) / kRNA && jt + kRNA < K::TILES && 32 * (u + 4 * kRNA) < K::T) {
+                    tmem_ld_16x256b_x2(r[(it + 1) & 1][0], ta0 + 16 * (jt + kRNA));
+                    tmem_ld_16x256b_x2(r[(it + 1) & 1][1], ta0 + 16 * (jt + kRNA) + (16u << 16));
                 }
                 uint32_t w[2][2];
 #pragma unroll
