@@ -48,7 +48,8 @@ typedef enum {
     MIBMI_ERR_PARAM = -3,       /* invalid parameter value (zero divisor, bad layout / option ...) */
     MIBMI_ERR_ALIGN = -4,       /* device pointer not sufficiently aligned for the selected layout */
     MIBMI_ERR_CUDA = -5,        /* CUDA runtime error (see mibmi_last_cuda_error) or no device */
-    MIBMI_ERR_UNSUPPORTED = -6  /* request valid but not available on the forced kernel path */
+    MIBMI_ERR_UNSUPPORTED = -6, /* request valid but not available on the forced kernel path */
+    MIBMI_ERR_TOO_LARGE = -7    /* request exceeds the fixed scratch of an allocation-free entry point */
 } mibmi_status;
 
 /* Input layouts of one batch of trials (int8, values in [-127, 127] as produced by
@@ -177,6 +178,20 @@ MIBMI_API int mibmi_forward_stream_int8(mibmi_net_t* net, const int8_t* x_dev, i
 MIBMI_API int mibmi_forward_stream_int8_taps(mibmi_net_t* net, const int8_t* x_dev, int64_t S, int64_t L, int32_t hop,
                                              int8_t* logits_dev, int8_t* y2_stream, int8_t* y2_edges, int8_t* y3,
                                              int8_t* y4, void* stream);
+
+/* Allocation-free variant of the any-hop (window-materialising) form of mibmi_forward_stream_int8.  NO COUNTERPART IN THE
+ * REFERENCE: added for callers that cannot call cudaMalloc (code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid it).  The windows are materialised in a file-scope `static __device__` array of
+ * MIBMI_NOALLOC_SCRATCH_BYTES (32 MiB) that every GPU which loads the library holds until exit; the call itself performs no
+ * cudaMalloc / cudaFree / stream-ordered allocation.  Same arguments, results and alignment rules as mibmi_forward_stream_int8
+ * (any hop >= 1; always the gather path: one gather_windows launch + one per-trial forward launch).
+ *   S * W * C * T > MIBMI_NOALLOC_SCRATCH_BYTES  ->  MIBMI_ERR_TOO_LARGE (nothing is launched; split the request)
+ * All calls on a device share the one array, which keeps the previous call's contents (every byte the forward reads is
+ * rewritten by the gather of the same call, nothing has to start at zero): calls that overlap on the GPU (different streams /
+ * threads / handles on the same device) RACE -- serialise them.  Asynchronous on `stream`. */
+#define MIBMI_NOALLOC_SCRATCH_BYTES (32 * 1024 * 1024)
+MIBMI_API int mibmi_forward_stream_int8_noalloc(mibmi_net_t* net, const int8_t* x_dev, int64_t S, int64_t L, int32_t hop,
+                                                int8_t* logits_dev, void* stream);
 
 /* Input quantisation pre-op (gen_input_header.py:73, STEActivation with floorToZero,
  * QuantLab/quantlab/indiv/ste_ops.py:88-102):  q = trunc(clip(x / abs_max, -1, 1) * 127).

@@ -26,7 +26,7 @@ SYMBOLS = [
     "mibmi_set_option", "mibmi_last_path", "mibmi_last_kernel", "mibmi_fused_supported", "mibmi_launch_count",
     "mibmi_forward_int8", "mibmi_forward_int8_taps", "mibmi_forward_int8_host",
     "mibmi_quantize_input_f32", "mibmi_dequantize_logits_f32", "mibmi_debug_magic", "mibmi_debug_magic32",
-    "mibmi_debug_pack_pipe", "mibmi_stream_windows", "mibmi_stream_supported", "mibmi_forward_stream_int8",
+    "mibmi_debug_pack_pipe", "mibmi_stream_windows", "mibmi_stream_supported", "mibmi_forward_stream_int8", "mibmi_forward_stream_int8_noalloc",
     "mibmi_forward_stream_int8_taps", "mibmi_forward_int8_gather",
     "mibmi_eegnet_create", "mibmi_eegnet_destroy", "mibmi_eegnet_forward_int8", "mibmi_eegnet_forward_int8_taps",
     "mibmi_eegnet_launch_count",
@@ -105,6 +105,7 @@ def lib() -> ctypes.CDLL:
     L.mibmi_stream_windows.restype = i64
     L.mibmi_stream_supported.argtypes = [vp, ctypes.POINTER(ctypes.c_char_p)]
     L.mibmi_forward_stream_int8.argtypes = [vp, vp, i64, i64, ctypes.c_int32, vp, vp]
+    L.mibmi_forward_stream_int8_noalloc.argtypes = [vp, vp, i64, i64, ctypes.c_int32, vp, vp]
     L.mibmi_forward_stream_int8_taps.argtypes = [vp, vp, i64, i64, ctypes.c_int32, vp, vp, vp, vp, vp, vp]
     L.mibmi_quantize_input_f32.argtypes = [vp, i64, ctypes.c_float, vp, vp]
     L.mibmi_dequantize_logits_f32.argtypes = [vp, i64, ctypes.c_float, vp, vp]

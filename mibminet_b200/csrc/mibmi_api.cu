@@ -576,6 +576,7 @@ const char* mibmi_strerror(int status) {
         case MIBMI_ERR_ALIGN: return "device pointer not sufficiently aligned";
         case MIBMI_ERR_CUDA: return "CUDA error or no CUDA device";
         case MIBMI_ERR_UNSUPPORTED: return "not available on the forced kernel path";
+        case MIBMI_ERR_TOO_LARGE: return "request exceeds the fixed scratch of the allocation-free entry point (MIBMI_NOALLOC_SCRATCH_BYTES)";
         default: return "unknown status";
     }
 }
@@ -900,6 +901,50 @@ int mibmi_forward_stream_int8_taps(mibmi_net_t* net, const int8_t* x_dev, int64_
                                    int8_t* logits_dev, int8_t* y2_stream, int8_t* y2_edges, int8_t* y3, int8_t* y4,
                                    void* stream) {
     return stream_impl(net, x_dev, S, L, hop, logits_dev, y2_stream, y2_edges, y3, y4, true, (cudaStream_t)stream);
+}
+
+// ---- allocation-free windowed scoring (no counterpart in the reference; see mibmi.h) ------------------------------------
+// The window scratch of the gather path as a file-scope device array.  In HOST code `g_noalloc_scratch` is only a stand-in for
+// the symbol, not a device address: its address on each device comes from cudaGetSymbolAddress, asked once per device with that
+// device current, and that pointer is what the kernels receive.
+static __device__ __align__(256) int8_t g_noalloc_scratch[MIBMI_NOALLOC_SCRATCH_BYTES];
+constexpr int kNoallocMaxDevices = 64;
+static std::mutex g_noalloc_mu;
+static int8_t* g_noalloc_ptr[kNoallocMaxDevices] = {};
+
+static cudaError_t noalloc_scratch_ptr(int device, int8_t** out) {      // the caller has made `device` current
+    if (device < 0 || device >= kNoallocMaxDevices) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (!g_noalloc_ptr[device]) {
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (e != cudaSuccess) return e;
+        g_noalloc_ptr[device] = static_cast<int8_t*>(p);
+    }
+    *out = g_noalloc_ptr[device];
+    return cudaSuccess;
+}
+
+int mibmi_forward_stream_int8_noalloc(mibmi_net_t* net, const int8_t* x_dev, int64_t S, int64_t L, int32_t hop,
+                                      int8_t* logits_dev, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (!net) return MIBMI_ERR_NULL;
+    if (S < 0 || hop < 1 || L < net->T) return MIBMI_ERR_PARAM;
+    if (S == 0) return MIBMI_OK;
+    if (!x_dev || !logits_dev) return MIBMI_ERR_NULL;
+    if (((uintptr_t)x_dev & 15) != 0 || (net->N == 4 && ((uintptr_t)logits_dev & 3) != 0)) return MIBMI_ERR_ALIGN;
+    const int64_t W = (L - net->T) / hop + 1, tb = (int64_t)net->C * net->T;
+    if (S > (int64_t(1) << 40) / W || S * W > MIBMI_NOALLOC_SCRATCH_BYTES / tb) return MIBMI_ERR_TOO_LARGE;
+    const int64_t total = S * W;
+    DeviceGuard dg(net->device);
+    if (dg.err != cudaSuccess) return fail_cuda(net, dg.err);
+    int8_t* scratch = nullptr;
+    cudaError_t e = noalloc_scratch_ptr(net->device, &scratch);
+    if (e != cudaSuccess) return fail_cuda(net, e);
+    e = launch_gather_windows(x_dev, L, net->C, net->T, hop, W, 0, total, scratch, stream);
+    if (e != cudaSuccess) return fail_cuda(net, e);
+    net->launches.fetch_add(1);
+    return forward_impl(net, scratch, total, MIBMI_LAYOUT_BCT, logits_dev, nullptr, nullptr, nullptr, nullptr, false, stream);
 }
 
 int mibmi_quantize_input_f32(const float* x_dev, int64_t n, float abs_max, int8_t* q_dev, void* stream) {
