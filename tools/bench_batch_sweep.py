@@ -24,4 +24,4 @@ for C, T in ((22, 1125), (64, 480)):
         out[f'{C}x{T}:{B}'] = {'us_per_call': us, 'trials_per_s': B / us * 1e6, 'kernel': net.last_kernel}
         print(f'{C}x{T} B={B:8d}: {us:10.1f} us/call  {B / us:9.3f} M trials/s  {net.last_kernel}', flush=True)
     del xall
-json.dump(out, open('gpurun_out/r1g/batch_sweep.json', 'w'), indent=1)
+import os; os.makedirs('gpurun_out/r2bs', exist_ok=True); json.dump(out, open('gpurun_out/r2bs/batch_sweep.json', 'w'), indent=1)
