@@ -59,7 +59,15 @@ struct SCfg {
     static constexpr int OFF_E = OFF_S2 + 16 * S2K;
     static constexpr int OFF_Y3 = OFF_E + 16 * G * 16;
     static constexpr int OFF_Y4 = OFF_Y3 + 16 * Y3W;
-    static constexpr int SMEM = ((OFF_Y4 + kStreamWarps * Y4_BYTES + 127) / 128) * 128;
+    // the small constants every warp needs in every chunk, staged once per CTA (words).  With two CTAs of ~100 KB of shared memory per
+    // SM the L1 is ~28 KB and the per-channel fragments streaming through it (147 KB per chunk) evict everything: these loads were L2
+    // round trips (79 LDG per window, 13 % of the stall samples, ncu r1f)
+    static constexpr int CW_W1 = 0, CW_OFF1 = 256, CW_M1 = 272, CW_SH1 = 288, CW_C2 = 304 /* thr, sig, soff, m, sh [16] */,
+                         CW_W4 = 384, CW_W5 = 448, CW_C4 = 704 /* thr, sig, soff, m, sh [16] */, CW_MISC = 784 /* b5[4], m5, sh5, m3, sh3 */,
+                         CW_WORDS = 792;
+    static constexpr int OFF_CONS = ((OFF_Y4 + kStreamWarps * Y4_BYTES + 127) / 128) * 128;
+    static constexpr int SMEM = ((OFF_CONS + 4 * CW_WORDS + 127) / 128) * 128;
+    static_assert(KB16 <= 4, "w1nat block of the constant area");
     static_assert(T % 64 == 0 || T % 16 == 0, "window length");
     static_assert(UNITS <= 2 * HALF_UNITS, "a chunk is two half loads");
     static_assert(2 * (UNITS + 1) + 1 < 2 * NCH && 2 * (16 * MT2 - 1) + 5 < 2 * NCH, "y1 planes");
@@ -96,7 +104,29 @@ stream_forward_kernel(const __grid_constant__ CUtensorMap tmx, const StreamNet* 
     }
     {
         uint4* z = reinterpret_cast<uint4*>(smem + K::OFF_Y1);
-        for (int i = tid; i < (K::SMEM - K::OFF_Y1) / 16; i += kStreamThreads) z[i] = make_uint4(0, 0, 0, 0);
+        for (int i = tid; i < (K::OFF_CONS - K::OFF_Y1) / 16; i += kStreamThreads) z[i] = make_uint4(0, 0, 0, 0);
+    }
+    uint32_t* const cw = reinterpret_cast<uint32_t*>(smem + K::OFF_CONS);
+    const int* const ci = reinterpret_cast<const int*>(cw);
+    for (int i = tid; i < K::CW_WORDS; i += kStreamThreads) {
+        uint32_t v = 0;
+        if (i < K::CW_OFF1) v = (&net->w1nat[0][0][0])[i];
+        else if (i < K::CW_M1) v = (uint32_t)net->off1[i - K::CW_OFF1];
+        else if (i < K::CW_SH1) v = (uint32_t)net->m1[i - K::CW_M1];
+        else if (i < K::CW_C2) v = (uint32_t)net->sh1[i - K::CW_SH1];
+        else if (i < K::CW_W4) {
+            const int f = (i - K::CW_C2) >> 4, kk = (i - K::CW_C2) & 15;
+            v = (uint32_t)(f == 0 ? net->thr2[kk] : f == 1 ? net->sig2[kk] : f == 2 ? net->soff2[kk] : f == 3 ? net->m2[kk] : net->sh2[kk]);
+        } else if (i < K::CW_W5) v = (&net->w4frag[0][0])[i - K::CW_W4];
+        else if (i < K::CW_C4) v = (i - K::CW_W5) < K::KST5 * 64 ? (&net->w5frag[0][0][0])[i - K::CW_W5] : 0u;
+        else if (i < K::CW_MISC) {
+            const int f = (i - K::CW_C4) >> 4, kk = (i - K::CW_C4) & 15;
+            v = (uint32_t)(f == 0 ? net->thr4[kk] : f == 1 ? net->sig4[kk] : f == 2 ? net->soff4[kk] : f == 3 ? net->m4[kk] : net->sh4[kk]);
+        } else {
+            const int j = i - K::CW_MISC;
+            v = (uint32_t)(j < 4 ? net->b5[j] : j == 4 ? net->m5 : j == 5 ? net->sh5 : j == 6 ? net->m3 : net->sh3);
+        }
+        cw[i] = v;
     }
     __syncthreads();
 
@@ -151,15 +181,15 @@ stream_forward_kernel(const __grid_constant__ CUtensorMap tmx, const StreamNet* 
                 uint32_t wfr[K::KB16][2];
 #pragma unroll
                 for (int kb = 0; kb < K::KB16; kb++) {
-                    wfr[kb][0] = __ldg(&net->w1nat[kb][0][lane]);
-                    wfr[kb][1] = __ldg(&net->w1nat[kb][1][lane]);
+                    wfr[kb][0] = cw[K::CW_W1 + (2 * kb) * 32 + lane];
+                    wfr[kb][1] = cw[K::CW_W1 + (2 * kb + 1) * 32 + lane];
                 }
                 const uint32_t xt = sbase + K::OFF_X + (warp >> 2) * K::TILE_BYTES;
                 const uint32_t j0 = 2 * (warp & 3);
                 int acc[2][2][4];
 #pragma unroll
                 for (int nt = 0; nt < 2; nt++) {
-                    const int o0 = __ldg(&net->off1[8 * nt + 2 * q]), o1 = __ldg(&net->off1[8 * nt + 2 * q + 1]);
+                    const int o0 = ci[K::CW_OFF1 + 8 * nt + 2 * q], o1 = ci[K::CW_OFF1 + 8 * nt + 2 * q + 1];
 #pragma unroll
                     for (int mt = 0; mt < 2; mt++) {
                         acc[mt][nt][0] = acc[mt][nt][2] = o0;
@@ -186,8 +216,8 @@ stream_forward_kernel(const __grid_constant__ CUtensorMap tmx, const StreamNet* 
                 uint32_t w[2][2];
 #pragma unroll
                 for (int nt = 0; nt < 2; nt++) {
-                    const int mg0 = __ldg(&net->m1[8 * nt + 2 * q]), mg1 = __ldg(&net->m1[8 * nt + 2 * q + 1]);
-                    const int s0 = __ldg(&net->sh1[8 * nt + 2 * q]), s1 = __ldg(&net->sh1[8 * nt + 2 * q + 1]);
+                    const int mg0 = ci[K::CW_M1 + 8 * nt + 2 * q], mg1 = ci[K::CW_M1 + 8 * nt + 2 * q + 1];
+                    const int s0 = ci[K::CW_SH1 + 8 * nt + 2 * q], s1 = ci[K::CW_SH1 + 8 * nt + 2 * q + 1];
 #pragma unroll
                     for (int mt = 0; mt < 2; mt++) {
                         const int v0 = sdiv1<FAST1>(acc[mt][nt][0], mg0, s0), v1 = sdiv1<FAST1>(acc[mt][nt][1], mg1, s1);
@@ -209,8 +239,8 @@ stream_forward_kernel(const __grid_constant__ CUtensorMap tmx, const StreamNet* 
         // P2: warp k = channel k.  (a) stream-level layer 2 + pooling, stored as 8 shifted copies
         // ================================================================================================
         {
-            const int thr = __ldg(&net->thr2[k]), sig = __ldg(&net->sig2[k]), soff = __ldg(&net->soff2[k]);
-            const int m2 = __ldg(&net->m2[k]), sh2 = __ldg(&net->sh2[k]);
+            const int thr = ci[K::CW_C2 + k], sig = ci[K::CW_C2 + 16 + k], soff = ci[K::CW_C2 + 32 + k];
+            const int m2 = ci[K::CW_C2 + 48 + k], sh2 = ci[K::CW_C2 + 64 + k];
             {
                 uint32_t bt[4][3][2];
 #pragma unroll
@@ -298,7 +328,7 @@ stream_forward_kernel(const __grid_constant__ CUtensorMap tmx, const StreamNet* 
         for (int wt = 0; wt < K::G / 16; wt++) {
             // ---- P3: warp k, layer 3 of windows 16 wt .. + 15; D[window][16 outputs] per block b
             {
-                const int m3 = __ldg(&net->m3), sh3 = __ldg(&net->sh3);
+                const int m3 = ci[K::CW_MISC + 6], sh3 = ci[K::CW_MISC + 7];
                 const int gw = 16 * wt + lrow;                                  // this lane's ldmatrix row
                 const uint32_t arow = smem_u32(s2k) + (gw & 7) * K::CPS + 16 * (gw >> 3) + 16 * (lane >> 4);
                 uint32_t ae[2];
@@ -338,7 +368,7 @@ stream_forward_kernel(const __grid_constant__ CUtensorMap tmx, const StreamNet* 
             // ---- P4: warp = window 16 wt + warp, layers 4 + 5
             {
                 const int wl = warp, wg = w0 + 16 * wt + wl;
-                const uint32_t w4a0 = __ldg(&net->w4frag[0][lane]), w4a1 = __ldg(&net->w4frag[1][lane]);
+                const uint32_t w4a0 = cw[K::CW_W4 + lane], w4a1 = cw[K::CW_W4 + 32 + lane];
                 const uint32_t y3a = sbase + K::OFF_Y3 + wl * K::Y3W + l4_off;
 #pragma unroll
                 for (int s4 = 0; s4 < K::NST; s4++) {
@@ -350,7 +380,7 @@ stream_forward_kernel(const __grid_constant__ CUtensorMap tmx, const StreamNet* 
                         c[v][0] = c[v][1] = c[v][2] = c[v][3] = 0;
                         mma_k16(c[v], w4a0, w4a1, d[v]);
                     }
-                    const int thr_lo = __ldg(&net->thr4[g]), thr_hi = __ldg(&net->thr4[g + 8]);
+                    const int thr_lo = ci[K::CW_C4 + g], thr_hi = ci[K::CW_C4 + g + 8];
                     int s_lo = 0, s_hi = 0;
 #pragma unroll
                     for (int v = 0; v < 4; v++) {
@@ -358,8 +388,8 @@ stream_forward_kernel(const __grid_constant__ CUtensorMap tmx, const StreamNet* 
                         s_hi += max(c[v][2], thr_hi) + max(c[v][3], thr_hi);
                     }
                     const int grp = 4 * s4 + q;
-                    const int o_lo = clip8(tdiv_magic(s_lo * __ldg(&net->sig4[g]) + __ldg(&net->soff4[g]), __ldg(&net->m4[g]), __ldg(&net->sh4[g])));
-                    const int o_hi = clip8(tdiv_magic(s_hi * __ldg(&net->sig4[g + 8]) + __ldg(&net->soff4[g + 8]), __ldg(&net->m4[g + 8]), __ldg(&net->sh4[g + 8])));
+                    const int o_lo = clip8(tdiv_magic(s_lo * ci[K::CW_C4 + 16 + g] + ci[K::CW_C4 + 32 + g], ci[K::CW_C4 + 48 + g], ci[K::CW_C4 + 64 + g]));
+                    const int o_hi = clip8(tdiv_magic(s_hi * ci[K::CW_C4 + 24 + g] + ci[K::CW_C4 + 40 + g], ci[K::CW_C4 + 56 + g], ci[K::CW_C4 + 72 + g]));
                     if (grp < K::T64) {
                         y4[g * K::T64P + grp] = (uint8_t)o_lo;
                         y4[(g + 8) * K::T64P + grp] = (uint8_t)o_hi;
@@ -373,13 +403,13 @@ stream_forward_kernel(const __grid_constant__ CUtensorMap tmx, const StreamNet* 
                 int z[4] = {0, 0, 0, 0};
 #pragma unroll
                 for (int ks = 0; ks < K::KST5; ks++) {
-                    const uint32_t a[4] = {__ldg(&net->w5frag[ks][0][lane]), 0u, __ldg(&net->w5frag[ks][1][lane]), 0u};
+                    const uint32_t a[4] = {cw[K::CW_W5 + (2 * ks) * 32 + lane], 0u, cw[K::CW_W5 + (2 * ks + 1) * 32 + lane], 0u};
                     const uint32_t b0 = g == 0 ? y4w[8 * ks + q] : 0u, b1 = g == 0 ? y4w[8 * ks + 4 + q] : 0u;
                     mma_k32(z, a, b0, b1);
                 }
                 if (q == 0 && g < 4 && wg < W)
                     logits[((size_t)subj * W + wg) * 4 + g] =
-                        (int8_t)clip8(tdiv_magic(z[0] + __ldg(&net->b5[g]), __ldg(&net->m5), __ldg(&net->sh5)));
+                        (int8_t)clip8(tdiv_magic(z[0] + ci[K::CW_MISC + (g & 3)], ci[K::CW_MISC + 4], ci[K::CW_MISC + 5]));
                 __syncwarp();
             }
             __syncthreads();      // y3 (and, after the last tile, y1 / the copies / the edges) may be rewritten
