@@ -1,4 +1,4 @@
-# round 2: streaming kernel with its small constants staged in shared memory (A/B against the previous build)
+# round 2: streaming kernel A/B (stbase = previous build)
 set -x
 O=gpurun_out/r2st; mkdir -p $O
 timeout 600 python -m pytest tests -m gpu -x -q -k "stream" > $O/pytest_stream.log 2>&1; tail -3 $O/pytest_stream.log
