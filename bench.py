@@ -344,6 +344,32 @@ def main_config1(args):
         res["gpu_batch1"] = {"device_ms_per_call": e0.elapsed_time(e1) / n, "kernel": net.last_kernel,
                              "host_round_trip_ms": 1e3 * (time.perf_counter() - t0) / 200,
                              "matches_reference_c": bool(np.array_equal(net.forward(xd).cpu().numpy(), y_ref))}
+        # the same call captured once in a CUDA graph (64 launches per graph) and replayed: the device time of a batch-1 call without
+        # the Python / ctypes / tensor-map encode cost of issuing it -- what a serving loop that replays a graph per trial sees
+        per_graph, replays = 64, 40
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            for _ in range(per_graph):
+                net.forward(xd[:1], out=out)
+        graph.replay()
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(replays):
+            graph.replay()
+        e1.record()
+        torch.cuda.synchronize()
+        res["gpu_batch1"]["graph_replay_ms_per_call"] = e0.elapsed_time(e1) / (per_graph * replays)
+        one = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(one):
+            net.forward(xd[:1], out=out)
+        one.replay()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(200):
+            one.replay()
+            torch.cuda.synchronize()
+        res["gpu_batch1"]["graph_host_round_trip_ms"] = 1e3 * (time.perf_counter() - t0) / 200
+        res["gpu_batch1"]["graph_matches_reference_c"] = bool(np.array_equal(out.cpu().numpy(), y_ref[:1]))
         res["value"] = res["gpu_batch1"]["device_ms_per_call"]
         res["gpu_launches"] = 2000
     else:

@@ -446,7 +446,7 @@ static cudaError_t launch_stream_instance(const StreamNet* net_dev, bool fast1, 
     return cudaGetLastError();
 }
 
-#define MIBMI_STREAM_SHAPES(X) X(64, 480) X(38, 480) X(24, 480) X(16, 480) X(8, 480)
+#define MIBMI_STREAM_SHAPES(X) X(64, 480) X(38, 480) X(24, 480) X(19, 480) X(16, 480) X(8, 480)
 
 bool stream_has_instance(int C, int T) {
 #define X(c, t) if (C == c && T == t) return true;

@@ -262,6 +262,50 @@ def test_edge_batches_and_extreme_inputs():
     assert y.shape == (0, 4)
 
 
+@pytest.mark.parametrize("C,T,layout", [(64, 480, "bct"), (22, 1125, "bct"), (22, 1125, "btc"), (38, 480, "btc"), (5, 64, "bct")])
+def test_forward_captured_in_a_cuda_graph(C, T, layout):
+    """mibmi_forward_int8 under stream capture: the call only encodes a tensor map on the host and launches, so it can be
+    captured once and replayed (a serving loop's small batches); every replay reads the buffers' current contents."""
+    net, arrays = _net(C, T, seed=45)
+    B = 37
+    xs = [synth.make_trials(B, C, T, seed=450 + i, dist="gauss" if i else "uniform") for i in range(3)]
+    wolf = lambda x: convert.to_wolf_input(x) if layout == "btc" else x
+    xd = _cuda(wolf(xs[0])).clone()
+    out = torch.zeros((B, 4), dtype=torch.int8, device="cuda:0")
+    net.forward(xd, layout=layout, out=out)          # first call outside the capture (function attributes, module load)
+    torch.cuda.synchronize()
+    kernel = net.last_kernel
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        net.forward(xd, layout=layout, out=out)
+    assert net.last_kernel == kernel
+    for x in xs:
+        xd.copy_(_cuda(wolf(x)))
+        out.zero_()
+        graph.replay()
+        torch.cuda.synchronize()
+        assert np.array_equal(out.cpu().numpy(), wolf_port.forward(arrays, C, T, x))
+
+
+def test_stream_forward_captured_in_a_cuda_graph():
+    C, T, S, L = 64, 480, 3, 480 + 16 * 50
+    net, arrays, x0 = _stream_case(C, T, S, L, 46)
+    xd = _cuda(x0).clone()
+    out = net.forward_stream(xd)
+    torch.cuda.synchronize()
+    assert net.last_path == "stream"
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        net.forward_stream(xd, out=out)
+    for seed in (47, 48):
+        x = synth.make_trials(S, C, L, seed=seed)
+        xd.copy_(_cuda(x))
+        out.zero_()
+        graph.replay()
+        torch.cuda.synchronize()
+        assert np.array_equal(out.cpu().numpy(), wolf_port.forward_stream(arrays, C, T, x))
+
+
 def test_unaligned_rows_22x1125_every_misalignment():
     """BASELINE config 3 (BCI-IV-2a): rows of 1125 bytes are never 16-byte aligned; the byte shift of a
     row depends on (trial, channel).  A 16-byte-aligned sub-batch view may start at any multiple of 8 trials."""
@@ -539,7 +583,7 @@ def _stream_case(C, T, S, L, seed):
 
 @pytest.mark.parametrize("C,S,L,seed", [(64, 3, 480 + 16 * 70, 61), (64, 2, 480, 62), (64, 5, 480 + 16 * 31, 63),
                                          (64, 1, 480 + 16 * 32, 64), (38, 2, 480 + 16 * 40, 65), (8, 3, 480 + 16 * 45, 66),
-                                         (16, 2, 480 + 16 * 33, 67), (24, 2, 480 + 16 * 64, 68)])
+                                         (16, 2, 480 + 16 * 33, 67), (24, 2, 480 + 16 * 64, 68), (19, 2, 480 + 16 * 37, 69)])
 def test_stream_fused_vs_materialised_windows(C, S, L, seed):
     """Every window of the fused streaming kernel == the oracle on the materialised window, per layer."""
     T = 480
