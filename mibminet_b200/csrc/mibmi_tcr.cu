@@ -66,7 +66,12 @@ constexpr int kTcrL3Unroll = MIBMI_TCR_L3_UNROLL, kTcrL4Unroll = MIBMI_TCR_L4_UN
 #ifndef MIBMI_TCR_AW
 #define MIBMI_TCR_AW 12                   // layer-1 epilogue warps (a multiple of 4: one per TMEM lane quarter)
 #endif
+#ifndef MIBMI_TCR_HELP
+#define MIBMI_TCR_HELP 1                  // the first set of layer-1 epilogue warps is a third consumer of layer-2 batches (third TMEM half)
+#endif                                    // while it would otherwise wait for tile_done: the phases A / M2+B alternate on the single y1 buffer
 constexpr int kRAW = MIBMI_TCR_AW, kRNA = kRAW / 4, kRBW = 8, kRCW = 4, kRRW = MIBMI_TCR_RW;
+constexpr int kRL2Sets = 2 + (MIBMI_TCR_HELP ? 1 : 0);                        // consumer sets (4 warps each) = TMEM halves of layer 2
+__host__ __device__ constexpr int tcr_l2_batches(int set) { return (8 - set + kRL2Sets - 1) / kRL2Sets; }   // batches bt = set, set + kRL2Sets, ... < 8
 static_assert(kRAW % 4 == 0 && kRAW >= 4, "layer-1 epilogue warps come in sets of four");
 constexpr int kRWarpB = kRAW, kRWarpC = kRAW + kRBW, kRWarpR = kRWarpC + kRCW, kRWarpP = kRWarpR + kRRW,
               kRWarpM1 = kRWarpP + 1, kRWarpM2 = kRWarpP + 2;
@@ -100,12 +105,12 @@ struct RCfg {
     static constexpr int Y3CH = 2 * ((NW3 + 1) / 2), Y3S = 16 * (Y3CH + 1), Y3_BYTES = 16 * Y3S;
     static constexpr int NST = (T64 + 3) / 4, T64P = (T64 + 1) / 2 * 2, KST5 = T64P / 2;
     static constexpr int Y4_BYTES = ((16 * T64P + 15) / 16) * 16;
-    // TMEM columns: layer-1 accumulators of two trials, then two layer-2 halves of 2 channels x 32 outputs
+    // TMEM columns: layer-1 accumulators of two trials, then kRL2Sets layer-2 "halves" of 2 channels x 32 outputs
     static constexpr int TM_L1_TRIAL = 16 * TILES, TM_L2 = 2 * TM_L1_TRIAL, TM_L2_HALF = 64;
     // barriers
     static constexpr int BAR_RAW_FULL = 0, BAR_RAW_EMPTY = 16, BAR_X_FULL = 32, BAR_X_EMPTY = 48, BAR_T1_FULL = 64,
-                         BAR_T1_EMPTY = 80, BAR_Y1_FULL = 96 /* G */, BAR_TILE_DONE = 128, BAR_T2_FULL = 160,
-                         BAR_T2_EMPTY = 176, BAR_Y2_FULL = 192 /* 2 */, BAR_Y2_EMPTY = 232, BAR_END = 248;
+                         BAR_T1_EMPTY = 80, BAR_Y1_FULL = 96 /* G */, BAR_TILE_DONE = 128, BAR_T2_FULL = 136 /* kRL2Sets */,
+                         BAR_T2_EMPTY = 160 /* kRL2Sets */, BAR_Y2_FULL = 192 /* 2 */, BAR_Y2_EMPTY = 232, BAR_END = 248;
     // shared memory map
     static constexpr int OFF_TMEM = 248, OFF_C2 = 256, OFF_W1 = 1024, OFF_W2 = 2048;
     static constexpr int OFF_XS = ((OFF_W2 + 16 * kW2U32 + 1023) / 1024) * 1024;
@@ -124,7 +129,7 @@ struct RCfg {
     static_assert(GROWS <= 128, "a group is one MMA tile");
     static_assert((CHS / 16) % 4 == 2 && CHS >= G * SLOT, "conflict-free stmatrix under the 32-byte swizzle");
     static_assert(G <= 4, "barrier slots");
-    static_assert(TM_L2 + 2 * TM_L2_HALF <= 512, "TMEM map");
+    static_assert(TM_L2 + kRL2Sets * TM_L2_HALF <= 512 && kRL2Sets <= 3, "TMEM map / barrier slots");
     static_assert(NW3 <= 16 && KST5 <= kPipeMaxKst5, "layer 3 / 5 limits");
     static_assert(XS_BYTES % 1024 == 0 && OFF_XS % 1024 == 0, "swizzle atoms are 1024-byte aligned");
     static_assert(SMEM <= 227 * 1024, "shared memory");
@@ -217,10 +222,12 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
             mbar_init(sbase + K::BAR_X_EMPTY + 8 * i, 1);            // commit of M1
             mbar_init(sbase + K::BAR_T1_FULL + 8 * i, 1);            // commit of M1
             mbar_init(sbase + K::BAR_T1_EMPTY + 8 * i, kRAW);
-            mbar_init(sbase + K::BAR_T2_FULL + 8 * i, 1);            // commit of M2
-            mbar_init(sbase + K::BAR_T2_EMPTY + 8 * i, kRBW / 2);
             mbar_init(sbase + K::BAR_Y2_EMPTY + 8 * i, K::G);
-            mbar_init(sbase + K::BAR_Y2_FULL + 8 * i, kRBW);
+            mbar_init(sbase + K::BAR_Y2_FULL + 8 * i, 4 * kRL2Sets);
+        }
+        for (int i = 0; i < kRL2Sets; i++) {
+            mbar_init(sbase + K::BAR_T2_FULL + 8 * i, 1);            // commit of M2
+            mbar_init(sbase + K::BAR_T2_EMPTY + 8 * i, 4);           // the four warps (TMEM lane quarters) of the consumer set
         }
         for (int j = 0; j < K::G; j++) mbar_init(sbase + K::BAR_Y1_FULL + 8 * j, kRAW);
         mbar_init(sbase + K::BAR_TILE_DONE, 1);                      // commit of M2: the y1 buffer of the group has been read
@@ -250,6 +257,65 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
     tc_fence_after();
     const uint32_t tmem_base = *reinterpret_cast<const uint32_t*>(smem + K::OFF_TMEM);
     RPROF_BEGIN
+
+    // Layer-2 epilogue of one consumer set (four warps, one per TMEM lane quarter): the batches bt = set, set + kRL2Sets, ... of
+    // group gq from TMEM half `set`.  Thread = TMEM lane = row 32 (warp & 3) + lane of the group's y1 buffer = 32 consecutive conv
+    // outputs (four pooling groups) of trial row / SROWS; channels 2 bt, 2 bt + 1.  Column n' of the accumulator = output 31 - n' of
+    // the row (reversed Toeplitz, PipeNet::w2umma32).  ws0 / ws1: wait-profile slots of the calling role
+    auto l2_consume = [&](const int set, const int gq, const int ws0, const int ws1) {
+        (void)ws0; (void)ws1;
+        const int qi = warp & 3;
+        const int4* c2 = reinterpret_cast<const int4*>(smem + K::OFF_C2);
+        const int row = 32 * qi + lane;
+        const int j = row / K::SROWS, blk = row - j * K::SROWS;
+        const bool valid = j < K::G && blk < K::VROWS;
+        const int gpar = gq & 1;
+        const int cnt = tcr_l2_batches(set);
+        RWAITL(ws1, sbase + K::BAR_Y2_EMPTY + 8 * gpar, ((gq >> 1) & 1) ^ 1);     // the C warps have consumed y2[gpar] of group gq - 2
+        const long long b = K::G * (firstg + (long long)gq * strideg) + j;
+        uint8_t* y2s = smem + K::OFF_Y2 + (gpar * K::G + (j < K::G ? j : 0)) * K::Y2_TRIAL + 8 + 4 * blk;
+#pragma unroll 1
+        for (int i = 0; i < cnt; i++) {
+            const int bt = set + kRL2Sets * i;
+            const int use = gq * cnt + i;                                   // how often this half has been used before
+            RWAIT(ws0, sbase + K::BAR_T2_FULL + 8 * set, use & 1);
+            tc_fence_after();
+#pragma unroll
+            for (int c = 0; c < 2; c++) {
+                uint32_t r[2][16];
+                const uint32_t ta = tmem_base + ((uint32_t)(32 * qi) << 16) + K::TM_L2 + K::TM_L2_HALF * set + 32 * c;
+                tcr_tmem_ld_32x32b_x16(r[0], ta);
+                tcr_tmem_ld_32x32b_x16(r[1], ta + 16);
+                tmem_ld_wait();
+                if (c == 1) {
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(sbase + K::BAR_T2_EMPTY + 8 * set);
+                }
+                const int k = 2 * bt + c;
+                const int4 ca = c2[2 * k];                       // thr, sig, soff, m
+                const int shk = reinterpret_cast<const int*>(smem + K::OFF_C2)[8 * k + 4];
+                int s[4];                                        // s[p] = pooling group p = outputs 8 p .. 8 p + 7 = columns 24 - 8 p .. 31 - 8 p
+#pragma unroll
+                for (int p = 0; p < 4; p++) {
+                    const int col = 24 - 8 * p;
+                    int acc = 0;
+#pragma unroll
+                    for (int e = 0; e < 8; e++)
+                        acc += PLAIN ? min(max(tdiv_magic((int)r[col >> 4][(col & 15) + e] * ca.y + ca.z, ca.w, shk), 0), 127)
+                                     : max((int)r[col >> 4][(col & 15) + e], ca.x);
+                    s[p] = PLAIN ? (acc >> 3) : tdiv_magic(acc * ca.y + ca.z, ca.w, shk);
+                }
+                const uint32_t o = pack4_sat(s[0], s[1], s[2], s[3]);
+                if (valid) {
+                    *reinterpret_cast<uint32_t*>(y2s + k * K::Y2S) = o;
+                    if (TAPS && tap2 && b < B) *reinterpret_cast<uint32_t*>(tap2 + ((size_t)b * 16 + k) * K::T8 + 4 * blk) = o;
+                }
+            }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(sbase + K::BAR_Y2_FULL + 8 * gpar);
+    };
 
     if (warp < kRAW) {
         // =====================================================================================
@@ -336,6 +402,9 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
                 mbar_arrive(sbase + K::BAR_T1_EMPTY + 8 * ab);
                 mbar_arrive(sbase + K::BAR_Y1_FULL + 8 * j);
             }
+            // the group's y1 is complete: until tile_done the layer-1 epilogue has nothing to do -- the first set takes the layer-2
+            // batches of the third TMEM half meanwhile
+            if (MIBMI_TCR_HELP && a3 == 0 && j == K::G - 1) l2_consume(kRL2Sets - 1, gq, 2, 2);
         }
     } else if (warp == kRWarpP) {
         // =====================================================================================
@@ -474,8 +543,8 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
             tc_fence_after();
 #pragma unroll
             for (int bt = 0; bt < 8; bt++) {
-                const int h = bt & 1;
-                const int use = gq * 4 + (bt >> 1);                         // how often this half has been used before
+                const int h = bt % kRL2Sets;                                // TMEM half = consumer set
+                const int use = gq * tcr_l2_batches(h) + bt / kRL2Sets;     // how often this half has been used before
                 RWAIT(1, sbase + K::BAR_T2_EMPTY + 8 * h, (use & 1) ^ 1);
                 tc_fence_after();
                 if (elect_one()) {
@@ -496,62 +565,10 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
         }
     } else if (warp >= kRWarpB && warp < kRWarpC) {
         // =====================================================================================
-        // B: layer-2 epilogue.  Thread = TMEM lane = row 32 (warp & 3) + lane of the group's y1 buffer
-        //    = 32 consecutive conv outputs (four pooling groups) of trial row / SROWS; channels 2 (2 bb + h), + 1.
-        //    Column n' of the accumulator = output 31 - n' of the row (reversed Toeplitz, PipeNet::w2umma32)
+        // B: layer-2 epilogue, consumer sets 0 and 1 (l2_consume above)
         // =====================================================================================
-        const int wb = warp - kRWarpB, qi = warp & 3, h = wb >> 2;
-        const int4* c2 = reinterpret_cast<const int4*>(smem + K::OFF_C2);
-        const int row = 32 * qi + lane;
-        const int j = row / K::SROWS, blk = row - j * K::SROWS;
-        const bool valid = j < K::G && blk < K::VROWS;
-        for (int gq = 0; gq < ng; gq++) {
-            const int gpar = gq & 1;
-            RWAITL(1, sbase + K::BAR_Y2_EMPTY + 8 * gpar, ((gq >> 1) & 1) ^ 1);     // the C warps have consumed y2[gpar] of group gq - 2
-            const long long b = K::G * (firstg + (long long)gq * strideg) + j;
-            uint8_t* y2s = smem + K::OFF_Y2 + (gpar * K::G + (j < K::G ? j : 0)) * K::Y2_TRIAL + 8 + 4 * blk;
-#pragma unroll 1
-            for (int bb = 0; bb < 4; bb++) {
-                const int bt = 2 * bb + h;
-                const int use = gq * 4 + bb;
-                RWAIT(0, sbase + K::BAR_T2_FULL + 8 * h, use & 1);
-                tc_fence_after();
-#pragma unroll
-                for (int c = 0; c < 2; c++) {
-                    uint32_t r[2][16];
-                    const uint32_t ta = tmem_base + ((uint32_t)(32 * qi) << 16) + K::TM_L2 + K::TM_L2_HALF * h + 32 * c;
-                    tcr_tmem_ld_32x32b_x16(r[0], ta);
-                    tcr_tmem_ld_32x32b_x16(r[1], ta + 16);
-                    tmem_ld_wait();
-                    if (c == 1) {
-                        tc_fence_before();
-                        __syncwarp();
-                        if (lane == 0) mbar_arrive(sbase + K::BAR_T2_EMPTY + 8 * h);
-                    }
-                    const int k = 2 * bt + c;
-                    const int4 ca = c2[2 * k];                       // thr, sig, soff, m
-                    const int shk = reinterpret_cast<const int*>(smem + K::OFF_C2)[8 * k + 4];
-                    int s[4];                                        // s[p] = pooling group p = outputs 8 p .. 8 p + 7 = columns 24 - 8 p .. 31 - 8 p
-#pragma unroll
-                    for (int p = 0; p < 4; p++) {
-                        const int col = 24 - 8 * p;
-                        int acc = 0;
-#pragma unroll
-                        for (int e = 0; e < 8; e++)
-                            acc += PLAIN ? min(max(tdiv_magic((int)r[col >> 4][(col & 15) + e] * ca.y + ca.z, ca.w, shk), 0), 127)
-                                         : max((int)r[col >> 4][(col & 15) + e], ca.x);
-                        s[p] = PLAIN ? (acc >> 3) : tdiv_magic(acc * ca.y + ca.z, ca.w, shk);
-                    }
-                    const uint32_t o = pack4_sat(s[0], s[1], s[2], s[3]);
-                    if (valid) {
-                        *reinterpret_cast<uint32_t*>(y2s + k * K::Y2S) = o;
-                        if (TAPS && tap2 && b < B) *reinterpret_cast<uint32_t*>(tap2 + ((size_t)b * 16 + k) * K::T8 + 4 * blk) = o;
-                    }
-                }
-            }
-            __syncwarp();
-            if (lane == 0) mbar_arrive(sbase + K::BAR_Y2_FULL + 8 * gpar);
-        }
+        const int set = (warp - kRWarpB) >> 2;
+        for (int gq = 0; gq < ng; gq++) l2_consume(set, gq, 0, 1);
     } else if (warp >= kRWarpC && warp < kRWarpR) {
         // =====================================================================================
         // C: layers 3 + 4 + 5 of the trials n = cj (mod 4); y3 / y4 are private to the warp
