@@ -503,9 +503,11 @@ def main_eegnet(args, rank, local_rank, world):
                             "frac": B * macs * 2 / (ms * 1e-3) / 1e12 / INT8_PEAK_TOPS, "traffic": None,
                             "hbm_frac": alg / (ms * 1e-3) / 1e9 / peak,
                             "peak_source": "measured: tcgen05.mma kind::i8 M128 N256 K32 back to back on 148 SMs (tools/probe_i8_peak.cu, "
-                                           "profiles/r2d_int8_tcgen05_peak.jsonl); this kernel uses the legacy mma.sync path, whose own "
-                                           "ceiling is lower",
-                            "note": "mma.sync int8 kernel bound by the requant epilogue (F1*C*T outputs per trial), DESIGN.md 4.7; parity "
+                                           "profiles/r2d_int8_tcgen05_peak.jsonl)",
+                            "kernel": net.last_kernel,
+                            "note": ("both contractions on tcgen05.mma (TMEM accumulators), " if net.last_kernel == "eegnet_tc_kernel"
+                                     else "mma.sync int8 kernel, ") +
+                                    "bound by the requant epilogue (F1*C*T outputs per trial), DESIGN.md 4.7; parity "
                                     "of this layer order is unpinned by the reference (tolerance pin only)"},
                "gpu_launches": int(net.launch_count - l0), "clocks": clocks}
         if not args.no_cpu_baseline:

@@ -248,6 +248,9 @@ MIBMI_API int mibmi_eegnet_forward_int8(mibmi_eegnet_t* net, const int8_t* x_dev
 MIBMI_API int mibmi_eegnet_forward_int8_taps(mibmi_eegnet_t* net, const int8_t* x_dev, int64_t B, int8_t* logits_dev,
                                              int8_t* y2, int8_t* y3, int8_t* y4, void* stream);
 MIBMI_API int64_t mibmi_eegnet_launch_count(const mibmi_eegnet_t* net);
+/* Name of the __global__ function the most recent forward of this handle launched ("eegnet_tc_kernel": both contractions on
+ * tcgen05.mma with TMEM accumulators, F1 = 8 and Nf = 128; "eegnet_mma_kernel": mma.sync; "eegnet_forward_kernel": dp4a). */
+MIBMI_API const char* mibmi_eegnet_last_kernel(const mibmi_eegnet_t* net);
 
 #ifdef __cplusplus
 }

@@ -29,7 +29,7 @@ SYMBOLS = [
     "mibmi_debug_pack_pipe", "mibmi_stream_windows", "mibmi_stream_supported", "mibmi_forward_stream_int8", "mibmi_forward_stream_int8_noalloc",
     "mibmi_forward_stream_int8_taps", "mibmi_forward_int8_gather",
     "mibmi_eegnet_create", "mibmi_eegnet_destroy", "mibmi_eegnet_forward_int8", "mibmi_eegnet_forward_int8_taps",
-    "mibmi_eegnet_launch_count",
+    "mibmi_eegnet_launch_count", "mibmi_eegnet_last_kernel",
 ]
 
 
@@ -119,6 +119,8 @@ def lib() -> ctypes.CDLL:
     L.mibmi_eegnet_forward_int8_taps.argtypes = [vp, vp, i64, vp, vp, vp, vp, vp]
     L.mibmi_eegnet_launch_count.argtypes = [vp]
     L.mibmi_eegnet_launch_count.restype = i64
+    L.mibmi_eegnet_last_kernel.argtypes = [vp]
+    L.mibmi_eegnet_last_kernel.restype = ctypes.c_char_p
     _lib = L
     return L
 

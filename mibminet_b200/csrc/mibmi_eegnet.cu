@@ -49,6 +49,12 @@ struct EegNet {
     const int8_t* w5;                                  // [N][F2 * T64] device pointer
     const uint32_t* w1frag;                            // tensor-core kernel: Toeplitz B fragments [F1][4 v][KS][2 h][32 lanes], device pointer
     int KS, MT, XPM;                                   // k-steps of 32 (= (Nf + 63) / 32), m-tiles of 16 rows x 32 outputs, row pitch
+    // tcgen05 kernel (eegnet_tc_kernel): chunks of 128 samples, row pitch of a padded channel, tiles of 16 channels, input stages
+    int NCH, P, CT, NXS;
+    int m32[kEegMaxF1];                                // layer 1, "no shift" magic (floor(2^32 / |fac|) + 1), factor sign folded into taps / offset
+    long long offm32[kEegMaxF1];                       // sg * off1 * m32: hi32(x m + off m) = hi32((x + off) m)
+    const uint8_t* b1umma;                             // Toeplitz operand of the temporal conv [128 = (f, n)][160] as K-major core matrices
+    const uint8_t* b2umma;                             // block-diagonal spatial weights [16 = k][8 * 16 CT = (f, c)] as K-major core matrices
 };
 
 __device__ __forceinline__ int eclip8(int v) { return min(max(v, -128), 127); }
@@ -337,6 +343,384 @@ eegnet_mma_kernel(const EegNet* __restrict__ net, const int8_t* __restrict__ x, 
     }
 }
 
+
+// ---------------------------------------------------------------------------------------------------------
+// tcgen05 form of layers 1 + 2 for F1 = 8 temporal filters of Nf = 128 taps (the QuantLab EEGNet configuration, eegnet.py:100-106):
+// BOTH contractions run on the 5th-generation tensor core with their accumulators in TMEM, the warps only requantise.
+//   MMA 1 (temporal conv, eegnet.py:143-145): per chunk of 128 samples and tile of 16 EEG channels ONE accumulator tile
+//         D1[128 rows = (channel, block of 16 samples)][128 columns = (filter f, sample n of the block)] = Hankel(x) * Toeplitz(w1):
+//         the A operand is the padded input row itself, described with overlapping strides (row = bytes 16 r .., LBO = 16 B: the next
+//         16 K positions are the next 16 bytes; SBO = row pitch: the next 8 rows are the next channel) -- no im2col; K = 160 in 5 k-steps.
+//   E1    thread = TMEM lane = (channel, block): per filter 16 accumulators -> batch_norm1 / quant2 (hi32(x m + off m), sign, saturating
+//         pack) -> ONE 16-byte store into the A operand of MMA 2: [row (f, c)][128 samples], 128-byte swizzle, MN-major (the layout a
+//         TMA tile [C][128] has in mibmi_tc.cu)
+//   MMA 2 (depthwise spatial conv, eegnet.py:147): D2[128 samples][16 = f D + d] = A2[128][(f, c)] * blockdiag(w2), K = 8 x 16 CT
+//   E2    batch_norm2 + ReLU + sum-pool 8 (8 consecutive TMEM lanes = 8 lanes of the m16n8 fragment: three shuffles) + quant3 -> y2
+//   L     layers 3 - 5 (eeg_layers345_sub) on the double-buffered y2, one trial behind
+// Warps: L 0-3, E2 4-7, E1 8-19 (three sets of four TMEM lane quarters, one accumulator buffer each), S 20-23 (trial -> padded rows),
+// M 24 (issues both MMAs).  One persistent CTA per SM; hand-off is mbarrier-only.
+constexpr int kEtL = 4, kEtE2 = 4, kEtE1 = 12, kEtS = 4, kEtSets = kEtE1 / 4;
+constexpr int kEtWarpE2 = kEtL, kEtWarpE1 = kEtWarpE2 + kEtE2, kEtWarpS = kEtWarpE1 + kEtE1, kEtWarpM = kEtWarpS + kEtS;
+constexpr int kEtThreads = (kEtWarpM + 1) * 32;
+constexpr int kEtB1Bytes = 128 * 160, kEtTmT2 = 128 * kEtSets;
+// barriers (8 bytes each)
+constexpr int kEtXsFull = 0, kEtXsEmpty = 16, kEtT1Full = 32, kEtT1Empty = 56, kEtA2Full = 80, kEtA2Empty = 96, kEtT2Full = 112,
+              kEtT2Empty = 128, kEtY2Full = 144, kEtY2Empty = 160, kEtTmemSlot = 176, kEtOffCons = 256, kEtOffB1 = 1024;
+static_assert(kEtTmT2 + 32 <= 512, "TMEM map");
+
+struct EtSmem { int off_b2, off_xs, off_a2, off_y2, off_y3, off_y4, total; };
+__host__ __device__ inline EtSmem et_smem(int C, int T, int K2, int F2, int NCH, int P, int CT, int NXS) {
+    EtSmem m;
+    (void)C;
+    const int T8 = T / 8, T64 = T8 / 8;
+    m.off_b2 = kEtOffB1 + kEtB1Bytes;
+    m.off_a2 = (m.off_b2 + 16 * 8 * 16 * CT + 1023) / 1024 * 1024;          // swizzle atoms are 1024-byte aligned
+    m.off_xs = m.off_a2 + 2 * 8 * 16 * CT * 128;
+    m.off_y2 = m.off_xs + NXS * 16 * CT * P;
+    m.off_y3 = (m.off_y2 + 2 * K2 * (T8 + 15) + 15) / 16 * 16;
+    m.off_y4 = m.off_y3 + K2 * T8;
+    m.total = (m.off_y4 + F2 * T64 + 127) / 128 * 128;
+    (void)NCH;
+    return m;
+}
+
+__device__ __forceinline__ constexpr uint32_t et_idesc_i8_kk(int M, int N) {   // both operands K-major
+    return (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+__device__ __forceinline__ void et_tmem_ld_32x32b_x16(uint32_t (&r)[16], uint32_t taddr) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+                   "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]) : "r"(taddr));
+}
+__device__ __forceinline__ int et_div_fold(int x, int m, long long offm) {     // tdiv(x + off, d) up to saturation
+    const int hi = (int)(((long long)x * m + offm) >> 32);
+    return hi + (int)((unsigned)hi >> 31);
+}
+__device__ __forceinline__ void et_bar_sync_l() { asm volatile("bar.sync 1, %0;" ::"n"(kEtL * 32) : "memory"); }
+
+// layers 3, 4, 5 (eeg_layers345) on a subset of the CTA: threads tid of nth, named barrier 1
+__device__ __forceinline__ void eeg_layers345_sub(const EegNet* __restrict__ net, const int8_t* y2, int8_t* y3, int8_t* y4, long long b,
+                                                  int8_t* __restrict__ logits, int8_t* __restrict__ tap3, int8_t* __restrict__ tap4,
+                                                  int tid, int nth) {
+    const int K2 = net->K2, F2 = net->F2, N = net->N, T8 = net->T8, T64 = net->T64, y2s = T8 + 15;
+    const int fac3 = net->fac3;
+    for (int i = tid; i < K2 * T8; i += nth) {
+        const int k = i / T8, t = i - k * T8;
+        const int8_t* w = net->w3 + k * kL3Taps;
+        const int8_t* r = y2 + k * y2s + t;
+        int acc = 0;
+#pragma unroll
+        for (int j = 0; j < kL3Taps; j++) acc += (int)r[j] * (int)w[j];
+        const int o = eclip8(acc / fac3);
+        y3[k * T8 + t] = (int8_t)o;
+        if (tap3) tap3[((size_t)b * K2 + k) * T8 + t] = (int8_t)o;
+    }
+    et_bar_sync_l();
+    for (int i = tid; i < F2 * T64; i += nth) {
+        const int k = i / T64, q = i - k * T64;
+        const int8_t* w = net->w4 + k * K2;
+        const int off = net->off4[k], fac = net->fac4[k];
+        int s = 0;
+        for (int e = 0; e < 8; e++) {
+            int v = 0;
+            for (int c = 0; c < K2; c++) v += (int)y3[c * T8 + q * 8 + e] * (int)w[c];
+            s += max(v, -(off >> 3));
+        }
+        const int o = eclip8((s + off) / fac);
+        y4[k * T64 + q] = (int8_t)o;
+        if (tap4) tap4[((size_t)b * F2 + k) * T64 + q] = (int8_t)o;
+    }
+    et_bar_sync_l();
+    for (int n = tid >> 5; n < N; n += nth >> 5) {
+        const int8_t* w = net->w5 + (size_t)n * F2 * T64;
+        int z = 0;
+        for (int i = tid & 31; i < F2 * T64; i += 32) z += (int)y4[i] * (int)w[i];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) z += __shfl_xor_sync(0xffffffffu, z, o);
+        if ((tid & 31) == 0) logits[(size_t)b * N + n] = (int8_t)eclip8((z + net->b5[n]) / net->fac5);
+    }
+    et_bar_sync_l();
+}
+
+template <int D>
+__global__ void __launch_bounds__(kEtThreads, 1)
+eegnet_tc_kernel(const EegNet* __restrict__ net, const int8_t* __restrict__ x, long long B, int8_t* __restrict__ logits,
+                 int8_t* __restrict__ tap2, int8_t* __restrict__ tap3, int8_t* __restrict__ tap4) {
+    extern __shared__ __align__(1024) uint8_t esm[];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int g = lane >> 2, q = lane & 3;
+    const uint32_t sbase = smem_u32(esm);
+    const int C = net->C, T = net->T, K2 = net->K2, T8 = net->T8;
+    const int NCH = net->NCH, P = net->P, CT = net->CT, NXS = net->NXS, KC = 16 * CT;
+    const int y2s = T8 + 15, PL = 63;
+    const EtSmem sm = et_smem(C, T, K2, net->F2, NCH, P, CT, NXS);
+    const int xs_bytes = 16 * CT * P, a2_bytes = 8 * KC * 128;
+    const long long first = blockIdx.x, stride = gridDim.x;
+    const int ntr = first < B ? (int)((B - first + stride - 1) / stride) : 0;
+
+    // ---- prologue
+    if (tid == 0) {
+        for (int i = 0; i < 2; i++) {
+            mbar_init(sbase + kEtXsFull + 8 * i, kEtS);
+            mbar_init(sbase + kEtXsEmpty + 8 * i, 1);            // commit of M
+            mbar_init(sbase + kEtA2Full + 8 * i, 4 * CT);        // the four warps of every tile of the chunk
+            mbar_init(sbase + kEtA2Empty + 8 * i, 1);            // commit of M
+            mbar_init(sbase + kEtT2Full + 8 * i, 1);             // commit of M
+            mbar_init(sbase + kEtT2Empty + 8 * i, kEtE2);
+            mbar_init(sbase + kEtY2Full + 8 * i, kEtE2);
+            mbar_init(sbase + kEtY2Empty + 8 * i, 1);
+        }
+        for (int i = 0; i < kEtSets; i++) {
+            mbar_init(sbase + kEtT1Full + 8 * i, 1);             // commit of M
+            mbar_init(sbase + kEtT1Empty + 8 * i, 4);
+        }
+        mbar_fence_init();
+    }
+    for (int i = tid; i < kEtB1Bytes / 16; i += kEtThreads)
+        reinterpret_cast<uint4*>(esm + kEtOffB1)[i] = reinterpret_cast<const uint4*>(net->b1umma)[i];
+    for (int i = tid; i < 16 * 8 * KC / 16; i += kEtThreads)
+        reinterpret_cast<uint4*>(esm + sm.off_b2)[i] = reinterpret_cast<const uint4*>(net->b2umma)[i];
+    {   // constants: [0..7] m32, [8..23] offm32 (lo, hi), [24..39] thr2, [40..55] off2, [56..71] fac2
+        int* cw = reinterpret_cast<int*>(esm + kEtOffCons);
+        for (int i = tid; i < 72; i += kEtThreads) {
+            int v = 0;
+            if (i < 8) v = net->m32[i];
+            else if (i < 24) v = (int)((unsigned long long)net->offm32[(i - 8) >> 1] >> (32 * ((i - 8) & 1)));
+            else if (i < 40) v = (i - 24) < K2 ? -(net->off2[i - 24] >> 3) : 0;
+            else if (i < 56) v = (i - 40) < K2 ? net->off2[i - 40] : 0;
+            else v = (i - 56) < K2 ? net->fac2[i - 56] : 1;
+            cw[i] = v;
+        }
+    }
+    {
+        uint4* z = reinterpret_cast<uint4*>(esm + sm.off_a2);     // A2 rows of channels >= C, the zero padding of the input rows and of y2
+        for (int i = tid; i < (sm.total - sm.off_a2) / 16; i += kEtThreads) z[i] = make_uint4(0, 0, 0, 0);
+    }
+    if (warp == kEtWarpM) tmem_alloc(sbase + kEtTmemSlot, 512);
+    fence_proxy_async();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *reinterpret_cast<const uint32_t*>(esm + kEtTmemSlot);
+    const int* cw = reinterpret_cast<const int*>(esm + kEtOffCons);
+
+    if (warp < kEtL) {
+        // ===================================================================================== L: layers 3 - 5
+        for (int i = 0; i < ntr; i++) {
+            const long long b = first + (long long)i * stride;
+            const int yb = i & 1;
+            mbar_wait(sbase + kEtY2Full + 8 * yb, (i >> 1) & 1);
+            eeg_layers345_sub(net, reinterpret_cast<const int8_t*>(esm + sm.off_y2 + yb * K2 * y2s), reinterpret_cast<int8_t*>(esm + sm.off_y3),
+                              reinterpret_cast<int8_t*>(esm + sm.off_y4), b, logits, tap3, tap4, tid, kEtL * 32);
+            if (tid == 0) mbar_arrive(sbase + kEtY2Empty + 8 * yb);
+        }
+    } else if (warp < kEtWarpE1) {
+        // ===================================================================================== E2: batch_norm2 + ReLU + pool + quant3
+        const int qi = warp & 3;
+        int thr[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) thr[j] = cw[24 + 8 * (j >> 1) + 2 * q + (j & 1)];      // column 8 nt + 2 q + e, j = 2 nt + e
+        // after the reduction lane g requantises the group rg = g >> 1 of the columns 8 nt + 2 q + e, nt = g & 1
+        const int nt_l = g & 1, rg_l = g >> 1;
+        const int k0 = 8 * nt_l + 2 * q;
+        const int off_a = cw[40 + k0], off_b = cw[41 + k0], fac_a = cw[56 + k0], fac_b = cw[57 + k0];
+        for (int i = 0; i < ntr; i++) {
+            const long long b = first + (long long)i * stride;
+            const int yb = i & 1;
+            mbar_wait(sbase + kEtY2Empty + 8 * yb, ((i >> 1) & 1) ^ 1);       // the L warps are done with this y2 buffer (trial i - 2)
+            int8_t* y2 = reinterpret_cast<int8_t*>(esm + sm.off_y2 + yb * K2 * y2s);
+            for (int ch = 0; ch < NCH; ch++) {
+                const int gch = i * NCH + ch, buf = gch & 1;
+                mbar_wait(sbase + kEtT2Full + 8 * buf, (gch >> 1) & 1);
+                tc_fence_after();
+                uint32_t r0[8], r1[8];
+                const uint32_t ta = tmem_base + ((uint32_t)(32 * qi) << 16) + kEtTmT2 + 16 * buf;
+                tmem_ld_16x256b_x2(r0, ta);
+                tmem_ld_16x256b_x2(r1, ta + (16u << 16));
+                tmem_ld_wait();
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(sbase + kEtT2Empty + 8 * buf);
+                // r[4 nt + c] = (row g + 8 (c >> 1), column 8 nt + 2 q + (c & 1)): threshold, then sum over the 8 rows g of a group
+                int p[4][4];                                                    // [rg][2 nt + e]
+#pragma unroll
+                for (int nt = 0; nt < 2; nt++)
+#pragma unroll
+                    for (int c = 0; c < 4; c++) {
+                        p[c >> 1][2 * nt + (c & 1)] = max((int)r0[4 * nt + c], thr[2 * nt + (c & 1)]);
+                        p[2 + (c >> 1)][2 * nt + (c & 1)] = max((int)r1[4 * nt + c], thr[2 * nt + (c & 1)]);
+                    }
+#pragma unroll
+                for (int rg = 0; rg < 4; rg++)
+#pragma unroll
+                    for (int j = 0; j < 4; j++) {
+                        int v = p[rg][j];
+                        v += __shfl_xor_sync(0xffffffffu, v, 4);
+                        v += __shfl_xor_sync(0xffffffffu, v, 8);
+                        v += __shfl_xor_sync(0xffffffffu, v, 16);
+                        p[rg][j] = v;
+                    }
+                int sa = 0, sb = 0;
+#pragma unroll
+                for (int rg = 0; rg < 4; rg++)
+#pragma unroll
+                    for (int nt = 0; nt < 2; nt++)
+                        if (rg == rg_l && nt == nt_l) { sa = p[rg][2 * nt]; sb = p[rg][2 * nt + 1]; }
+                const int pg = 16 * ch + 4 * qi + rg_l;                          // pooled sample of the trial
+                if (pg < T8) {
+                    if (k0 < K2) {
+                        const int o = eclip8((sa + off_a) / fac_a);
+                        y2[k0 * y2s + 7 + pg] = (int8_t)o;
+                        if (tap2) tap2[((size_t)b * K2 + k0) * T8 + pg] = (int8_t)o;
+                    }
+                    if (k0 + 1 < K2) {
+                        const int o = eclip8((sb + off_b) / fac_b);
+                        y2[(k0 + 1) * y2s + 7 + pg] = (int8_t)o;
+                        if (tap2) tap2[((size_t)b * K2 + k0 + 1) * T8 + pg] = (int8_t)o;
+                    }
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(sbase + kEtY2Full + 8 * yb);
+        }
+    } else if (warp < kEtWarpS) {
+        // ===================================================================================== E1: batch_norm1 / quant2 -> A operand of MMA 2
+        const int es = (warp - kEtWarpE1) >> 2, qi = warp & 3;
+        const int r = lane & 7, cl = 4 * qi + (lane >> 3);
+        long long gq = 0;
+        for (int i = 0; i < ntr; i++)
+            for (int ch = 0; ch < NCH; ch++)
+                for (int ct = 0; ct < CT; ct++, gq++) {
+                    if ((int)(gq % kEtSets) != es) continue;
+                    const int use = (int)(gq / kEtSets);
+                    const int gch = i * NCH + ch, buf = gch & 1;
+                    mbar_wait(sbase + kEtT1Full + 8 * es, use & 1);
+                    mbar_wait(sbase + kEtA2Empty + 8 * buf, ((gch >> 1) & 1) ^ 1);     // MMA 2 of chunk gch - 2 has read this buffer
+                    tc_fence_after();
+                    const int c = 16 * ct + cl;
+                    if (16 * ct + 4 * qi < C) {                                          // warp-uniform: some channel of the quarter exists
+                        const uint32_t ta = tmem_base + ((uint32_t)(32 * qi) << 16) + 128 * es;
+                        uint8_t* a2 = esm + sm.off_a2 + buf * a2_bytes + c * 128 + ((r ^ (c & 7)) << 4);
+#pragma unroll 1
+                        for (int fp = 0; fp < 4; fp++) {
+                            uint32_t ra[16], rb[16];
+                            et_tmem_ld_32x32b_x16(ra, ta + 32 * fp);
+                            et_tmem_ld_32x32b_x16(rb, ta + 32 * fp + 16);
+                            tmem_ld_wait();
+#pragma unroll
+                            for (int h = 0; h < 2; h++) {
+                                const int f = 2 * fp + h;
+                                const int m = cw[f];
+                                const long long offm = *reinterpret_cast<const long long*>(cw + 8 + 2 * f);
+                                uint32_t w[4];
+#pragma unroll
+                                for (int j = 0; j < 4; j++) {
+                                    int v[4];
+#pragma unroll
+                                    for (int e = 0; e < 4; e++) v[e] = et_div_fold((int)(h ? rb[4 * j + e] : ra[4 * j + e]), m, offm);
+                                    w[j] = pack4_sat(v[0], v[1], v[2], v[3]);
+                                }
+                                if (c < C) *reinterpret_cast<uint4*>(a2 + f * KC * 128) = make_uint4(w[0], w[1], w[2], w[3]);
+                            }
+                        }
+                    }
+                    tc_fence_before();
+                    fence_proxy_async();          // A2 is read by the tensor core (async proxy)
+                    __syncwarp();
+                    if (lane == 0) {
+                        mbar_arrive(sbase + kEtT1Empty + 8 * es);
+                        mbar_arrive(sbase + kEtA2Full + 8 * buf);
+                    }
+                }
+    } else if (warp < kEtWarpM) {
+        // ===================================================================================== S: trial -> padded rows (x[c][t] at byte PL + t)
+        const int st_tid = tid - 32 * kEtWarpS, nth = 32 * kEtS;
+        for (int i = 0; i < ntr; i++) {
+            const long long b = first + (long long)i * stride;
+            const int st = i % NXS;
+            mbar_wait(sbase + kEtXsEmpty + 8 * st, ((i / NXS) & 1) ^ 1);
+            uint8_t* xs = esm + sm.off_xs + st * xs_bytes;
+            const int8_t* xb = x + (size_t)b * C * T;
+            // aligned 32-bit global loads of the (arbitrarily aligned) trial, bytes scattered to their padded rows
+            const uintptr_t ga = reinterpret_cast<uintptr_t>(xb);
+            const int mis = (int)(ga & 3), total = C * T, nwords = (mis + total + 3) >> 2;
+            const uint32_t* gw = reinterpret_cast<const uint32_t*>(ga - mis);
+            int ii = 4 * st_tid - mis;
+            int c = ii >= 0 ? ii / T : 0, t = ii - c * T;
+            for (int w = st_tid; w < nwords; w += 4 * nth) {
+                uint32_t v4[4];
+#pragma unroll
+                for (int u = 0; u < 4; u++) v4[u] = w + u * nth < nwords ? __ldg(gw + w + u * nth) : 0u;
+#pragma unroll
+                for (int u = 0; u < 4; u++) {
+                    const uint32_t v = v4[u];
+                    int cj = c, tj = t;
+#pragma unroll
+                    for (int j = 0; j < 4; j++) {
+                        if (tj >= T) { tj -= T; cj++; }
+                        if (ii + j >= 0 && ii + j < total) xs[cj * P + PL + tj] = (uint8_t)(v >> (8 * j));
+                        tj++;
+                    }
+                    ii += 4 * nth;
+                    t += 4 * nth;
+                    while (t >= T) { t -= T; c++; }
+                }
+            }
+            fence_proxy_async();                  // the rows are read by the tensor core (async proxy)
+            __syncwarp();
+            if (lane == 0) mbar_arrive(sbase + kEtXsFull + 8 * st);
+        }
+    } else {
+        // ===================================================================================== M: both MMAs
+        constexpr uint32_t idesc1 = et_idesc_i8_kk(128, 128), idesc2 = umma_idesc_i8(128, 16);
+        const uint64_t da1 = umma_desc(sbase + sm.off_xs, 16, (uint32_t)P, 0), db1 = umma_desc(sbase + kEtOffB1, 128, 1280, 0);
+        const uint64_t da2 = umma_desc(sbase + sm.off_a2, 16, 1024, 2), db2 = umma_desc(sbase + sm.off_b2, 128, (uint32_t)(8 * KC / 16) * 128, 0);
+        const uint32_t a1_hi = (uint32_t)(da1 >> 32), b1_hi = (uint32_t)(db1 >> 32), a2_hi = (uint32_t)(da2 >> 32), b2_hi = (uint32_t)(db2 >> 32);
+        const int ks2 = 8 * KC / 32;
+        auto mma2 = [&](int gch) {                // spatial conv of chunk gch (issued one chunk late: E1 needs the time)
+            const int buf = gch & 1;
+            mbar_wait(sbase + kEtA2Full + 8 * buf, (gch >> 1) & 1);
+            mbar_wait(sbase + kEtT2Empty + 8 * buf, ((gch >> 1) & 1) ^ 1);
+            tc_fence_after();
+            if (elect_one()) {
+                for (int ks = 0; ks < ks2; ks++)
+                    umma_i8_lohi(tmem_base + kEtTmT2 + 16 * buf, (uint32_t)da2 + ((buf * a2_bytes + ks * 4096) >> 4), a2_hi,
+                                 (uint32_t)db2 + ((ks * 256) >> 4), b2_hi, idesc2, ks > 0);
+                umma_commit(sbase + kEtT2Full + 8 * buf);
+                umma_commit(sbase + kEtA2Empty + 8 * buf);
+            }
+            __syncwarp();
+        };
+        long long gq = 0;
+        for (int i = 0; i < ntr; i++) {
+            const int st = i % NXS;
+            mbar_wait(sbase + kEtXsFull + 8 * st, (i / NXS) & 1);
+            for (int ch = 0; ch < NCH; ch++) {
+                const int gch = i * NCH + ch;
+                for (int ct = 0; ct < CT; ct++, gq++) {
+                    const int tb = (int)(gq % kEtSets), use = (int)(gq / kEtSets);
+                    mbar_wait(sbase + kEtT1Empty + 8 * tb, (use & 1) ^ 1);
+                    tc_fence_after();
+                    if (elect_one()) {
+                        const uint32_t a_lo = (uint32_t)da1 + ((st * xs_bytes + 16 * ct * P + 128 * ch) >> 4);
+#pragma unroll
+                        for (int s = 0; s < 5; s++)
+                            umma_i8_lohi(tmem_base + 128 * tb, a_lo + ((32 * s) >> 4), a1_hi, (uint32_t)db1 + ((256 * s) >> 4), b1_hi, idesc1, s > 0);
+                        umma_commit(sbase + kEtT1Full + 8 * tb);
+                        if (ch == NCH - 1 && ct == CT - 1) umma_commit(sbase + kEtXsEmpty + 8 * st);
+                    }
+                    __syncwarp();
+                }
+                if (gch > 0) mma2(gch - 1);
+            }
+        }
+        if (ntr > 0) mma2(ntr * NCH - 1);
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == kEtWarpM) tmem_dealloc(tmem_base, 512);
+}
+
 }  // namespace mibmi
 
 using namespace mibmi;
@@ -345,10 +729,14 @@ struct mibmi_eegnet {
     int device = 0, num_sms = 0;
     int C = 0, T = 0, K2 = 0, F2 = 0, N = 0, D = 0, threads = 256, magic1 = 0;
     int F1 = 0, KS = 0;                 // tensor-core kernel: warps = F1, k-steps; KS == 0: no instantiation (dp4a kernel)
-    size_t smem = 0, smem_mma = 0;
+    size_t smem = 0, smem_mma = 0, smem_tc = 0;
+    int tc = 0;                         // tcgen05 kernel (eegnet_tc_kernel) available for this network
     EegNet* net_dev = nullptr;
     int8_t* w5_dev = nullptr;
     uint32_t* w1frag_dev = nullptr;
+    uint8_t* b1_dev = nullptr;          // operands of the tcgen05 kernel
+    uint8_t* b2_dev = nullptr;
+    std::atomic<int> last_kernel{0};    // 0 none, 1 eegnet_tc_kernel, 2 eegnet_mma_kernel, 3 eegnet_forward_kernel
     std::atomic<long long> launches{0};
     std::atomic<int> last_cuda{0};
 };
@@ -491,12 +879,68 @@ int mibmi_eegnet_create(const mibmi_eegnet_params_t* p, int device, mibmi_eegnet
         }
     }
     h->w1frag = n->w1frag_dev;
+    // tcgen05 kernel: F1 = 8 filters of 128 taps, every layer-1 factor inside the range of the "no shift" magic
+    if (e == cudaSuccess && F1 == 8 && Nf == 128 && C <= 64 && K2 <= 16 && h->magic1) {
+        bool ok = true;
+        for (int f = 0; f < F1 && ok; f++) {
+            long long sum = 0;
+            for (int j = 0; j < Nf; j++) sum += p->l1_weight[f * Nf + j] < 0 ? -(long long)p->l1_weight[f * Nf + j] : p->l1_weight[f * Nf + j];
+            const long long d = h->fac1[f] < 0 ? -(long long)h->fac1[f] : h->fac1[f];
+            const long long oa = h->off1[f] < 0 ? -(long long)h->off1[f] : h->off1[f];
+            const long long xmax = 128 * sum + oa;
+            const long long mm = (1LL << 32) / d + 1, er = mm * d - (1LL << 32), lim = xmax < 130 * d ? xmax : 130 * d;
+            if (d < 4 || mm >= (1LL << 31) || (__int128)lim * er >= ((__int128)1 << 32)) { ok = false; break; }
+            h->m32[f] = (int)mm;
+            h->offm32[f] = (long long)h->sg1[f] * h->off1[f] * mm;
+        }
+        h->NCH = (T + 127) / 128;
+        h->P = 128 * h->NCH + 144;
+        h->CT = (C + 15) / 16;
+        h->NXS = 2;
+        if (ok && (size_t)et_smem(C, T, K2, F2, h->NCH, h->P, h->CT, 2).total > (size_t)prop.sharedMemPerBlockOptin) h->NXS = 1;
+        if (ok && (size_t)et_smem(C, T, K2, F2, h->NCH, h->P, h->CT, h->NXS).total > (size_t)prop.sharedMemPerBlockOptin) ok = false;
+        if (ok) {
+            const int KC = 16 * h->CT, K2T = 8 * KC;
+            const size_t nb1 = kEtB1Bytes, nb2 = (size_t)16 * K2T;
+            uint8_t* b1 = new (std::nothrow) uint8_t[nb1];
+            uint8_t* b2 = new (std::nothrow) uint8_t[nb2];
+            if (b1 && b2) {
+                memset(b1, 0, nb1);
+                memset(b2, 0, nb2);
+                for (int nn = 0; nn < 128; nn++)            // B1[(f, n)][kk] = sg w1[f][kk - n]: output n of a row reads bytes n .. n + 127 of its window
+                    for (int kk = 0; kk < 160; kk++) {
+                        const int f = nn >> 4, tap = kk - (nn & 15);
+                        if (tap >= 0 && tap < Nf)
+                            b1[(nn >> 3) * 1280 + (kk >> 4) * 128 + (nn & 7) * 16 + (kk & 15)] = (uint8_t)(int8_t)(h->sg1[f] * p->l1_weight[f * Nf + tap]);
+                    }
+                for (int k = 0; k < K2; k++)                // B2[k][(f, c)] = w2[k][c] for f = k / D (depthwise: groups = F1)
+                    for (int c = 0; c < C; c++) {
+                        const int kk = (k / D) * KC + c;
+                        b2[(k >> 3) * (K2T / 16) * 128 + (kk >> 4) * 128 + (k & 7) * 16 + (kk & 15)] = (uint8_t)p->l2_weight[k * C + c];
+                    }
+                e = cudaMalloc(&n->b1_dev, nb1);
+                if (e == cudaSuccess) e = cudaMalloc(&n->b2_dev, nb2);
+                if (e == cudaSuccess) e = cudaMemcpy(n->b1_dev, b1, nb1, cudaMemcpyHostToDevice);
+                if (e == cudaSuccess) e = cudaMemcpy(n->b2_dev, b2, nb2, cudaMemcpyHostToDevice);
+                if (e == cudaSuccess) {
+                    n->tc = 1;
+                    n->smem_tc = (size_t)et_smem(C, T, K2, F2, h->NCH, h->P, h->CT, h->NXS).total;
+                }
+            }
+            delete[] b1;
+            delete[] b2;
+        }
+    }
+    h->b1umma = n->b1_dev;
+    h->b2umma = n->b2_dev;
     if (e == cudaSuccess) e = cudaMalloc(&n->net_dev, sizeof(EegNet));
     if (e == cudaSuccess) e = cudaMemcpy(n->net_dev, h, sizeof(EegNet), cudaMemcpyHostToDevice);
     delete h;
     if (e != cudaSuccess) {
         if (n->w5_dev) cudaFree(n->w5_dev);
         if (n->w1frag_dev) cudaFree(n->w1frag_dev);
+        if (n->b1_dev) cudaFree(n->b1_dev);
+        if (n->b2_dev) cudaFree(n->b2_dev);
         if (n->net_dev) cudaFree(n->net_dev);
         delete n;
         return MIBMI_ERR_CUDA;
@@ -511,6 +955,8 @@ int mibmi_eegnet_destroy(mibmi_eegnet_t* n) {
         Guard dg(n->device);
         if (n->w5_dev) cudaFree(n->w5_dev);
         if (n->w1frag_dev) cudaFree(n->w1frag_dev);
+        if (n->b1_dev) cudaFree(n->b1_dev);
+        if (n->b2_dev) cudaFree(n->b2_dev);
         if (n->net_dev) cudaFree(n->net_dev);
     }
     delete n;
@@ -526,7 +972,20 @@ int mibmi_eegnet_forward_int8_taps(mibmi_eegnet_t* n, const int8_t* x_dev, int64
     Guard dg(n->device);
     cudaError_t e = dg.err;
     const char* force = getenv("MIBMI_EEGNET_DP4A");                       // experiment switch: CUDA-core kernel
-    if (n->KS && !(force && force[0] == '1')) {
+    const char* notc = getenv("MIBMI_EEGNET_TC");                          // experiment switch: "0" = the mma.sync kernel
+    int which = 0;
+    if (n->tc && !(notc && notc[0] == '0') && !(force && force[0] == '1')) {
+        auto kern = n->D == 1 ? eegnet_tc_kernel<1> : eegnet_tc_kernel<2>;
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)n->smem_tc);
+        if (e == cudaSuccess) {
+            long long grid = n->num_sms;
+            if (grid > B) grid = B;
+            kern<<<(unsigned)grid, kEtThreads, n->smem_tc, (cudaStream_t)stream>>>(n->net_dev, x_dev, B, logits_dev, y2, y3, y4);
+            e = cudaGetLastError();
+            which = 1;
+        }
+    } else if (n->KS && !(force && force[0] == '1')) {
+        which = 2;
         using kern_t = void (*)(const EegNet*, const int8_t*, long long, int8_t*, int8_t*, int8_t*, int8_t*);
         kern_t kern = nullptr;
 #define MIBMI_EEG_PICK(d, ks) \
@@ -543,6 +1002,7 @@ int mibmi_eegnet_forward_int8_taps(mibmi_eegnet_t* n, const int8_t* x_dev, int64
             e = cudaGetLastError();
         }
     } else {
+        which = 3;
         auto kern = n->D == 1 ? (n->magic1 ? eegnet_forward_kernel<1, true> : eegnet_forward_kernel<1, false>)
                               : (n->magic1 ? eegnet_forward_kernel<2, true> : eegnet_forward_kernel<2, false>);
         if (e == cudaSuccess) e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)n->smem);
@@ -558,7 +1018,13 @@ int mibmi_eegnet_forward_int8_taps(mibmi_eegnet_t* n, const int8_t* x_dev, int64
         return MIBMI_ERR_CUDA;
     }
     n->launches.fetch_add(1);
+    n->last_kernel.store(which);
     return MIBMI_OK;
+}
+
+const char* mibmi_eegnet_last_kernel(const mibmi_eegnet_t* n) {
+    static const char* const names[] = {"", "eegnet_tc_kernel", "eegnet_mma_kernel", "eegnet_forward_kernel"};
+    return n ? names[n->last_kernel.load() & 3] : "";
 }
 
 int mibmi_eegnet_forward_int8(mibmi_eegnet_t* n, const int8_t* x_dev, int64_t B, int8_t* logits_dev, void* stream) {

@@ -311,6 +311,11 @@ class EEGNetInt8:
     def launch_count(self) -> int:
         return int(self._L.mibmi_eegnet_launch_count(self._h))
 
+    @property
+    def last_kernel(self) -> str:
+        """Name of the __global__ function the most recent forward launched."""
+        return (self._L.mibmi_eegnet_last_kernel(self._h) or b"").decode()
+
     def _check_x(self, x: torch.Tensor) -> torch.Tensor:
         if x.dtype != torch.int8 or not x.is_cuda or x.device.index != self.device_index:
             raise ValueError(f"x must be an int8 tensor on {self.device}")

@@ -105,6 +105,28 @@ def test_gpu_bit_exact_with_taps(C, T, F1, D, Nf, B):
     for k in ("y2", "y3", "y4"):
         assert np.array_equal(taps[k].cpu().numpy(), layers[k]), k
     assert net.launch_count == 2
+    # F1 = 8 filters of 128 taps (the QuantLab EEGNet configuration): both contractions on tcgen05.mma
+    assert net.last_kernel == ("eegnet_tc_kernel" if (F1 == 8 and Nf == 128) else "eegnet_mma_kernel" if Nf % 32 == 0 else "eegnet_forward_kernel")
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("C,T,D,B", [(22, 1125, 2, 1500), (64, 480, 2, 1000), (19, 484, 1, 777), (5, 128, 2, 300)])
+def test_gpu_tcgen05_kernel_over_many_trials(C, T, D, B, monkeypatch):
+    """eegnet_tc_kernel with several trials per persistent CTA (input stages, accumulator buffers and y2 buffers wrap around):
+    equal to the oracle on a sample and to the mma.sync kernel on every trial, logits and taps."""
+    sd, p, net, torch = _gpu_net(C, T, 8, D, 128, seed=7)
+    x = synth.make_trials(B, C, T, seed=8, dist="gauss")
+    xd = torch.from_numpy(x).cuda()
+    y, taps = net.forward_taps(xd)
+    assert net.last_kernel == "eegnet_tc_kernel"
+    y1 = net.forward(xd[1:])                       # another alignment of the trials (C * T odd shifts the rows)
+    monkeypatch.setenv("MIBMI_EEGNET_TC", "0")
+    yr, tr = net.forward_taps(xd)
+    assert net.last_kernel == "eegnet_mma_kernel"
+    for k in ("y2", "y3", "y4"):
+        assert torch.equal(taps[k], tr[k]), k
+    assert torch.equal(y, yr) and torch.equal(y1, yr[1:])
+    assert np.array_equal(y[:48].cpu().numpy(), eegnet_np.forward(p, x[:48]))
 
 
 @pytest.mark.gpu
