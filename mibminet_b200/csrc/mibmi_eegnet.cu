@@ -359,6 +359,17 @@ eegnet_mma_kernel(const EegNet* __restrict__ net, const int8_t* __restrict__ x, 
 //   L     layers 3 - 5 (eeg_layers345_sub) on the double-buffered y2, one trial behind
 // Warps: L 0-3, E2 4-7, E1 8-19 (three sets of four TMEM lane quarters, one accumulator buffer each), S 20-23 (trial -> padded rows),
 // M 24 (issues both MMAs).  One persistent CTA per SM; hand-off is mbarrier-only.
+#ifdef MIBMI_PROF
+__device__ long long g_prof_et[148 * 32 * 4];
+#define EWAIT(slot, ...) do { if (!mbar_test(__VA_ARGS__)) { const long long t0_ = clock64(); mbar_wait(__VA_ARGS__); pw_[slot] += clock64() - t0_; } } while (0)
+#define EPROF_BEGIN long long pw_[3] = {0, 0, 0}; const long long pt0_ = clock64();
+#define EPROF_END if ((threadIdx.x & 31) == 0) { long long* o_ = g_prof_et + (blockIdx.x * 32 + (threadIdx.x >> 5)) * 4; \
+    o_[0] = clock64() - pt0_; o_[1] = pw_[0]; o_[2] = pw_[1]; o_[3] = pw_[2]; }
+#else
+#define EWAIT(slot, ...) mbar_wait(__VA_ARGS__)
+#define EPROF_BEGIN
+#define EPROF_END
+#endif
 constexpr int kEtL = 4, kEtE2 = 4, kEtE1 = 12, kEtS = 4, kEtSets = kEtE1 / 4;
 constexpr int kEtWarpE2 = kEtL, kEtWarpE1 = kEtWarpE2 + kEtE2, kEtWarpS = kEtWarpE1 + kEtE1, kEtWarpM = kEtWarpS + kEtS;
 constexpr int kEtThreads = (kEtWarpM + 1) * 32;
@@ -369,6 +380,7 @@ constexpr int kEtXsFull = 0, kEtXsEmpty = 16, kEtT1Full = 32, kEtT1Empty = 56, k
 static_assert(kEtTmT2 + 32 <= 512, "TMEM map");
 
 struct EtSmem { int off_b2, off_xs, off_a2, off_y2, off_y3, off_y4, total; };
+__host__ __device__ inline int et_y2s(int T8) { return (T8 + 3) / 4 * 4 + 20; }     // y2 row: 7 zeros | T8 samples | zeros, whole words
 __host__ __device__ inline EtSmem et_smem(int C, int T, int K2, int F2, int NCH, int P, int CT, int NXS) {
     EtSmem m;
     (void)C;
@@ -377,8 +389,8 @@ __host__ __device__ inline EtSmem et_smem(int C, int T, int K2, int F2, int NCH,
     m.off_a2 = (m.off_b2 + 16 * 8 * 16 * CT + 1023) / 1024 * 1024;          // swizzle atoms are 1024-byte aligned
     m.off_xs = m.off_a2 + 2 * 8 * 16 * CT * 128;
     m.off_y2 = m.off_xs + NXS * 16 * CT * P;
-    m.off_y3 = (m.off_y2 + 2 * K2 * (T8 + 15) + 15) / 16 * 16;
-    m.off_y4 = m.off_y3 + K2 * T8;
+    m.off_y3 = (m.off_y2 + 2 * K2 * et_y2s(T8) + 15) / 16 * 16;   // y3t [T8][16 channels], time-major
+    m.off_y4 = m.off_y3 + 16 * T8;
     m.total = (m.off_y4 + F2 * T64 + 127) / 128 * 128;
     (void)NCH;
     return m;
@@ -398,40 +410,86 @@ __device__ __forceinline__ int et_div_fold(int x, int m, long long offm) {     /
 }
 __device__ __forceinline__ void et_bar_sync_l() { asm volatile("bar.sync 1, %0;" ::"n"(kEtL * 32) : "memory"); }
 
-// layers 3, 4, 5 (eeg_layers345) on a subset of the CTA: threads tid of nth, named barrier 1
-__device__ __forceinline__ void eeg_layers345_sub(const EegNet* __restrict__ net, const int8_t* y2, int8_t* y3, int8_t* y4, long long b,
-                                                  int8_t* __restrict__ logits, int8_t* __restrict__ tap3, int8_t* __restrict__ tap4,
-                                                  int tid, int nth) {
-    const int K2 = net->K2, F2 = net->F2, N = net->N, T8 = net->T8, T64 = net->T64, y2s = T8 + 15;
-    const int fac3 = net->fac3;
-    for (int i = tid; i < K2 * T8; i += nth) {
-        const int k = i / T8, t = i - k * T8;
-        const int8_t* w = net->w3 + k * kL3Taps;
-        const int8_t* r = y2 + k * y2s + t;
-        int acc = 0;
+// Layers 3, 4, 5 on the four L warps (128 threads, named barrier 1).  Eight threads per channel:
+//   layer 3 (eegnet.py:155-156): thread (k, u) owns the outputs 4 u .. 4 u + 3 of channel k: 5 aligned words of the padded y2 row against
+//            4 byte-shifted copies of the 16 taps (W_s[m] = w3[k][m - s]) = 20 dp4a; results stored time-major, y3t[t][16 channels]
+//   layer 4 (eegnet.py:157-161): thread (k, e) owns sample e of every pooling group: one 16-byte load of y3t[t] against the 16 input
+//            weights of output channel k = 4 dp4a, threshold, sum over the 8 threads of the group with three shuffles
+//   layer 5 (eegnet.py:164-166): warp = class
+struct EtLRegs { uint32_t w3[5][4]; uint32_t w4[4]; int thr4, off4, fac4; };
+__device__ __forceinline__ void et_l_setup(const EegNet* __restrict__ net, int tid, EtLRegs& R) {
+    const int k = tid >> 3, K2 = net->K2, F2 = net->F2;
 #pragma unroll
-        for (int j = 0; j < kL3Taps; j++) acc += (int)r[j] * (int)w[j];
-        const int o = eclip8(acc / fac3);
-        y3[k * T8 + t] = (int8_t)o;
-        if (tap3) tap3[((size_t)b * K2 + k) * T8 + t] = (int8_t)o;
-    }
-    et_bar_sync_l();
-    for (int i = tid; i < F2 * T64; i += nth) {
-        const int k = i / T64, q = i - k * T64;
-        const int8_t* w = net->w4 + k * K2;
-        const int off = net->off4[k], fac = net->fac4[k];
-        int s = 0;
-        for (int e = 0; e < 8; e++) {
-            int v = 0;
-            for (int c = 0; c < K2; c++) v += (int)y3[c * T8 + q * 8 + e] * (int)w[c];
-            s += max(v, -(off >> 3));
+    for (int i = 0; i < 5; i++)
+#pragma unroll
+        for (int sft = 0; sft < 4; sft++) {
+            uint32_t w = 0;
+            for (int e = 0; e < 4; e++) {
+                const int j = 4 * i + e - sft;
+                const int v = (k < K2 && j >= 0 && j < kL3Taps) ? net->w3[k * kL3Taps + j] : 0;
+                w |= (uint32_t)(uint8_t)(int8_t)v << (8 * e);
+            }
+            R.w3[i][sft] = w;
         }
-        const int o = eclip8((s + off) / fac);
-        y4[k * T64 + q] = (int8_t)o;
-        if (tap4) tap4[((size_t)b * F2 + k) * T64 + q] = (int8_t)o;
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        uint32_t w = 0;
+        for (int e = 0; e < 4; e++) {
+            const int c = 4 * i + e;
+            const int v = (k < F2 && c < K2) ? net->w4[k * K2 + c] : 0;
+            w |= (uint32_t)(uint8_t)(int8_t)v << (8 * e);
+        }
+        R.w4[i] = w;
+    }
+    R.off4 = k < F2 ? net->off4[k] : 0;
+    R.fac4 = k < F2 ? net->fac4[k] : 1;
+    R.thr4 = -(R.off4 >> 3);
+}
+__device__ __forceinline__ void et_layers345(const EegNet* __restrict__ net, const EtLRegs& R, const int8_t* y2, int y2s, int8_t* y3t,
+                                             int8_t* y4, long long b, int8_t* __restrict__ logits, int8_t* __restrict__ tap3,
+                                             int8_t* __restrict__ tap4, int tid) {
+    const int K2 = net->K2, F2 = net->F2, N = net->N, T8 = net->T8, T64 = net->T64;
+    const int k = tid >> 3, e8 = tid & 7, fac3 = net->fac3;
+    if (k < K2) {
+        const uint32_t* row = reinterpret_cast<const uint32_t*>(y2 + k * y2s);
+        for (int u = e8; 4 * u < T8; u += 8) {
+            int acc[4] = {0, 0, 0, 0};
+#pragma unroll
+            for (int i = 0; i < 5; i++) {
+                const int xw = (int)row[u + i];
+#pragma unroll
+                for (int sft = 0; sft < 4; sft++) acc[sft] = __dp4a(xw, (int)R.w3[i][sft], acc[sft]);
+            }
+#pragma unroll
+            for (int sft = 0; sft < 4; sft++) {
+                const int t = 4 * u + sft;
+                if (t < T8) {
+                    const int o = eclip8(acc[sft] / fac3);
+                    y3t[t * 16 + k] = (int8_t)o;
+                    if (tap3) tap3[((size_t)b * K2 + k) * T8 + t] = (int8_t)o;
+                }
+            }
+        }
     }
     et_bar_sync_l();
-    for (int n = tid >> 5; n < N; n += nth >> 5) {
+    for (int q = 0; q < T64; q++) {
+        const uint4 yv = *reinterpret_cast<const uint4*>(y3t + (8 * q + e8) * 16);
+        int v = __dp4a((int)yv.x, (int)R.w4[0], 0);
+        v = __dp4a((int)yv.y, (int)R.w4[1], v);
+        v = __dp4a((int)yv.z, (int)R.w4[2], v);
+        v = __dp4a((int)yv.w, (int)R.w4[3], v);
+        int m = max(v, R.thr4);
+        m += __shfl_xor_sync(0xffffffffu, m, 1);
+        m += __shfl_xor_sync(0xffffffffu, m, 2);
+        m += __shfl_xor_sync(0xffffffffu, m, 4);
+        if (e8 == (q & 7) && k < F2) {
+            const int o = eclip8((m + R.off4) / R.fac4);
+            y4[k * T64 + q] = (int8_t)o;
+            if (tap4) tap4[((size_t)b * F2 + k) * T64 + q] = (int8_t)o;
+        }
+    }
+    et_bar_sync_l();
+    for (int n = tid >> 5; n < N; n += kEtL) {
         const int8_t* w = net->w5 + (size_t)n * F2 * T64;
         int z = 0;
         for (int i = tid & 31; i < F2 * T64; i += 32) z += (int)y4[i] * (int)w[i];
@@ -452,7 +510,7 @@ eegnet_tc_kernel(const EegNet* __restrict__ net, const int8_t* __restrict__ x, l
     const uint32_t sbase = smem_u32(esm);
     const int C = net->C, T = net->T, K2 = net->K2, T8 = net->T8;
     const int NCH = net->NCH, P = net->P, CT = net->CT, NXS = net->NXS, KC = 16 * CT;
-    const int y2s = T8 + 15, PL = 63;
+    const int y2s = et_y2s(T8), PL = 64;
     const EtSmem sm = et_smem(C, T, K2, net->F2, NCH, P, CT, NXS);
     const int xs_bytes = 16 * CT * P, a2_bytes = 8 * KC * 128;
     const long long first = blockIdx.x, stride = gridDim.x;
@@ -503,15 +561,18 @@ eegnet_tc_kernel(const EegNet* __restrict__ net, const int8_t* __restrict__ x, l
     tc_fence_after();
     const uint32_t tmem_base = *reinterpret_cast<const uint32_t*>(esm + kEtTmemSlot);
     const int* cw = reinterpret_cast<const int*>(esm + kEtOffCons);
+    EPROF_BEGIN
 
     if (warp < kEtL) {
         // ===================================================================================== L: layers 3 - 5
+        EtLRegs R;
+        et_l_setup(net, tid, R);
         for (int i = 0; i < ntr; i++) {
             const long long b = first + (long long)i * stride;
             const int yb = i & 1;
-            mbar_wait(sbase + kEtY2Full + 8 * yb, (i >> 1) & 1);
-            eeg_layers345_sub(net, reinterpret_cast<const int8_t*>(esm + sm.off_y2 + yb * K2 * y2s), reinterpret_cast<int8_t*>(esm + sm.off_y3),
-                              reinterpret_cast<int8_t*>(esm + sm.off_y4), b, logits, tap3, tap4, tid, kEtL * 32);
+            EWAIT(0, sbase + kEtY2Full + 8 * yb, (i >> 1) & 1);
+            et_layers345(net, R, reinterpret_cast<const int8_t*>(esm + sm.off_y2 + yb * K2 * y2s), y2s, reinterpret_cast<int8_t*>(esm + sm.off_y3),
+                         reinterpret_cast<int8_t*>(esm + sm.off_y4), b, logits, tap3, tap4, tid);
             if (tid == 0) mbar_arrive(sbase + kEtY2Empty + 8 * yb);
         }
     } else if (warp < kEtWarpE1) {
@@ -527,11 +588,11 @@ eegnet_tc_kernel(const EegNet* __restrict__ net, const int8_t* __restrict__ x, l
         for (int i = 0; i < ntr; i++) {
             const long long b = first + (long long)i * stride;
             const int yb = i & 1;
-            mbar_wait(sbase + kEtY2Empty + 8 * yb, ((i >> 1) & 1) ^ 1);       // the L warps are done with this y2 buffer (trial i - 2)
+            EWAIT(1, sbase + kEtY2Empty + 8 * yb, ((i >> 1) & 1) ^ 1);       // the L warps are done with this y2 buffer (trial i - 2)
             int8_t* y2 = reinterpret_cast<int8_t*>(esm + sm.off_y2 + yb * K2 * y2s);
             for (int ch = 0; ch < NCH; ch++) {
                 const int gch = i * NCH + ch, buf = gch & 1;
-                mbar_wait(sbase + kEtT2Full + 8 * buf, (gch >> 1) & 1);
+                EWAIT(0, sbase + kEtT2Full + 8 * buf, (gch >> 1) & 1);
                 tc_fence_after();
                 uint32_t r0[8], r1[8];
                 const uint32_t ta = tmem_base + ((uint32_t)(32 * qi) << 16) + kEtTmT2 + 16 * buf;
@@ -594,8 +655,8 @@ eegnet_tc_kernel(const EegNet* __restrict__ net, const int8_t* __restrict__ x, l
                     if ((int)(gq % kEtSets) != es) continue;
                     const int use = (int)(gq / kEtSets);
                     const int gch = i * NCH + ch, buf = gch & 1;
-                    mbar_wait(sbase + kEtT1Full + 8 * es, use & 1);
-                    mbar_wait(sbase + kEtA2Empty + 8 * buf, ((gch >> 1) & 1) ^ 1);     // MMA 2 of chunk gch - 2 has read this buffer
+                    EWAIT(0, sbase + kEtT1Full + 8 * es, use & 1);
+                    EWAIT(1, sbase + kEtA2Empty + 8 * buf, ((gch >> 1) & 1) ^ 1);     // MMA 2 of chunk gch - 2 has read this buffer
                     tc_fence_after();
                     const int c = 16 * ct + cl;
                     if (16 * ct + 4 * qi < C) {                                          // warp-uniform: some channel of the quarter exists
@@ -634,41 +695,62 @@ eegnet_tc_kernel(const EegNet* __restrict__ net, const int8_t* __restrict__ x, l
                 }
     } else if (warp < kEtWarpM) {
         // ===================================================================================== S: trial -> padded rows (x[c][t] at byte PL + t)
-        const int st_tid = tid - 32 * kEtWarpS, nth = 32 * kEtS;
+        // PL = 64: every row starts on a 16-byte boundary of the stage.  Rows that are 16-byte aligned in global memory too (64 x 480)
+        // arrive as one bulk copy each (TMA, no instructions per byte); otherwise a lane builds a 16-byte chunk from five aligned words
+        // (funnel shift) and stores it once; bytes >= T of the last chunk are written as zeros (they are the convolution's padding)
+        const int sw = warp - kEtWarpS;
+        const int chunks = (T + 15) >> 4;
+        const uintptr_t gend = (reinterpret_cast<uintptr_t>(x) + (size_t)B * C * T + 3) & ~(uintptr_t)3;
         for (int i = 0; i < ntr; i++) {
             const long long b = first + (long long)i * stride;
             const int st = i % NXS;
-            mbar_wait(sbase + kEtXsEmpty + 8 * st, ((i / NXS) & 1) ^ 1);
-            uint8_t* xs = esm + sm.off_xs + st * xs_bytes;
+            EWAIT(0, sbase + kEtXsEmpty + 8 * st, ((i / NXS) & 1) ^ 1);
+            uint8_t* xs = esm + sm.off_xs + st * xs_bytes + PL;
             const int8_t* xb = x + (size_t)b * C * T;
-            // aligned 32-bit global loads of the (arbitrarily aligned) trial, bytes scattered to their padded rows
-            const uintptr_t ga = reinterpret_cast<uintptr_t>(xb);
-            const int mis = (int)(ga & 3), total = C * T, nwords = (mis + total + 3) >> 2;
-            const uint32_t* gw = reinterpret_cast<const uint32_t*>(ga - mis);
-            int ii = 4 * st_tid - mis;
-            int c = ii >= 0 ? ii / T : 0, t = ii - c * T;
-            for (int w = st_tid; w < nwords; w += 4 * nth) {
-                uint32_t v4[4];
-#pragma unroll
-                for (int u = 0; u < 4; u++) v4[u] = w + u * nth < nwords ? __ldg(gw + w + u * nth) : 0u;
-#pragma unroll
-                for (int u = 0; u < 4; u++) {
-                    const uint32_t v = v4[u];
-                    int cj = c, tj = t;
-#pragma unroll
-                    for (int j = 0; j < 4; j++) {
-                        if (tj >= T) { tj -= T; cj++; }
-                        if (ii + j >= 0 && ii + j < total) xs[cj * P + PL + tj] = (uint8_t)(v >> (8 * j));
-                        tj++;
-                    }
-                    ii += 4 * nth;
-                    t += 4 * nth;
-                    while (t >= T) { t -= T; c++; }
+            const uint32_t bar = sbase + kEtXsFull + 8 * st;
+            if (((reinterpret_cast<uintptr_t>(xb) | (uintptr_t)T) & 15) == 0) {
+                if (sw == 0) {
+                    if (lane == 0) mbar_expect_tx(bar, (uint32_t)(C * T));
+                    __syncwarp();
+                    for (int c = lane; c < C; c += 32) bulk_g2s(smem_u32(xs + c * P), xb + (size_t)c * T, (uint32_t)T, bar);
+                } else if (lane == 0) {
+                    mbar_arrive(bar);
                 }
+            } else {
+                for (int c = sw; c < C; c += kEtS) {
+                    const uintptr_t ra = reinterpret_cast<uintptr_t>(xb) + (size_t)c * T;
+                    const int sh = 8 * (int)(ra & 3);
+                    uint8_t* drow = xs + c * P;
+                    for (int j0 = 0; j0 < chunks; j0 += 96) {
+                        uint32_t w[3][5];
+#pragma unroll
+                        for (int pp = 0; pp < 3; pp++) {
+                            const int j = j0 + 32 * pp + lane;
+                            const uintptr_t wa = (ra & ~(uintptr_t)3) + 16 * (size_t)j;
+#pragma unroll
+                            for (int u = 0; u < 5; u++)
+                                w[pp][u] = (j < chunks && wa + 4 * u < gend) ? __ldg(reinterpret_cast<const uint32_t*>(wa + 4 * u)) : 0u;
+                        }
+#pragma unroll
+                        for (int pp = 0; pp < 3; pp++) {
+                            const int j = j0 + 32 * pp + lane;
+                            if (j < chunks) {
+                                uint32_t o[4];
+#pragma unroll
+                                for (int u = 0; u < 4; u++) {
+                                    o[u] = __funnelshift_r(w[pp][u], w[pp][u + 1], sh);
+                                    const int nv = T - 16 * j - 4 * u;                 // valid bytes of this word
+                                    if (nv < 4) o[u] = nv <= 0 ? 0u : (o[u] & (0xffffffffu >> (8 * (4 - nv))));
+                                }
+                                *reinterpret_cast<uint4*>(drow + 16 * j) = make_uint4(o[0], o[1], o[2], o[3]);
+                            }
+                        }
+                    }
+                }
+                fence_proxy_async();              // the rows are read by the tensor core (async proxy)
+                __syncwarp();
+                if (lane == 0) mbar_arrive(bar);
             }
-            fence_proxy_async();                  // the rows are read by the tensor core (async proxy)
-            __syncwarp();
-            if (lane == 0) mbar_arrive(sbase + kEtXsFull + 8 * st);
         }
     } else {
         // ===================================================================================== M: both MMAs
@@ -679,8 +761,8 @@ eegnet_tc_kernel(const EegNet* __restrict__ net, const int8_t* __restrict__ x, l
         const int ks2 = 8 * KC / 32;
         auto mma2 = [&](int gch) {                // spatial conv of chunk gch (issued one chunk late: E1 needs the time)
             const int buf = gch & 1;
-            mbar_wait(sbase + kEtA2Full + 8 * buf, (gch >> 1) & 1);
-            mbar_wait(sbase + kEtT2Empty + 8 * buf, ((gch >> 1) & 1) ^ 1);
+            EWAIT(1, sbase + kEtA2Full + 8 * buf, (gch >> 1) & 1);
+            EWAIT(2, sbase + kEtT2Empty + 8 * buf, ((gch >> 1) & 1) ^ 1);
             tc_fence_after();
             if (elect_one()) {
                 for (int ks = 0; ks < ks2; ks++)
@@ -694,12 +776,12 @@ eegnet_tc_kernel(const EegNet* __restrict__ net, const int8_t* __restrict__ x, l
         long long gq = 0;
         for (int i = 0; i < ntr; i++) {
             const int st = i % NXS;
-            mbar_wait(sbase + kEtXsFull + 8 * st, (i / NXS) & 1);
+            EWAIT(0, sbase + kEtXsFull + 8 * st, (i / NXS) & 1);
             for (int ch = 0; ch < NCH; ch++) {
                 const int gch = i * NCH + ch;
                 for (int ct = 0; ct < CT; ct++, gq++) {
                     const int tb = (int)(gq % kEtSets), use = (int)(gq / kEtSets);
-                    mbar_wait(sbase + kEtT1Empty + 8 * tb, (use & 1) ^ 1);
+                    EWAIT(2, sbase + kEtT1Empty + 8 * tb, (use & 1) ^ 1);
                     tc_fence_after();
                     if (elect_one()) {
                         const uint32_t a_lo = (uint32_t)da1 + ((st * xs_bytes + 16 * ct * P + 128 * ch) >> 4);
@@ -716,6 +798,7 @@ eegnet_tc_kernel(const EegNet* __restrict__ net, const int8_t* __restrict__ x, l
         }
         if (ntr > 0) mma2(ntr * NCH - 1);
     }
+    EPROF_END
     tc_fence_before();
     __syncthreads();
     if (warp == kEtWarpM) tmem_dealloc(tmem_base, 512);
@@ -880,7 +963,7 @@ int mibmi_eegnet_create(const mibmi_eegnet_params_t* p, int device, mibmi_eegnet
     }
     h->w1frag = n->w1frag_dev;
     // tcgen05 kernel: F1 = 8 filters of 128 taps, every layer-1 factor inside the range of the "no shift" magic
-    if (e == cudaSuccess && F1 == 8 && Nf == 128 && C <= 64 && K2 <= 16 && h->magic1) {
+    if (e == cudaSuccess && F1 == 8 && Nf == 128 && C <= 64 && K2 <= 16 && F2 <= 16 && h->magic1) {
         bool ok = true;
         for (int f = 0; f < F1 && ok; f++) {
             long long sum = 0;
@@ -907,9 +990,9 @@ int mibmi_eegnet_create(const mibmi_eegnet_params_t* p, int device, mibmi_eegnet
             if (b1 && b2) {
                 memset(b1, 0, nb1);
                 memset(b2, 0, nb2);
-                for (int nn = 0; nn < 128; nn++)            // B1[(f, n)][kk] = sg w1[f][kk - n]: output n of a row reads bytes n .. n + 127 of its window
+                for (int nn = 0; nn < 128; nn++)            // B1[(f, n)][kk] = sg w1[f][kk - n - 1]: output n of a row reads bytes n + 1 .. n + 128 of its window
                     for (int kk = 0; kk < 160; kk++) {
-                        const int f = nn >> 4, tap = kk - (nn & 15);
+                        const int f = nn >> 4, tap = kk - (nn & 15) - 1;     // x[t] sits at byte 64 + t of its padded row, the window of output t starts at byte t
                         if (tap >= 0 && tap < Nf)
                             b1[(nn >> 3) * 1280 + (kk >> 4) * 128 + (nn & 7) * 16 + (kk & 15)] = (uint8_t)(int8_t)(h->sg1[f] * p->l1_weight[f * Nf + tap]);
                     }
@@ -1034,3 +1117,9 @@ int mibmi_eegnet_forward_int8(mibmi_eegnet_t* n, const int8_t* x_dev, int64_t B,
 int64_t mibmi_eegnet_launch_count(const mibmi_eegnet_t* n) { return n ? n->launches.load() : 0; }
 
 }  // extern "C"
+
+#ifdef MIBMI_PROF
+extern "C" __attribute__((visibility("default"))) int mibmi_debug_prof_et(long long* out_host) {
+    return (int)cudaMemcpyFromSymbol(out_host, mibmi::g_prof_et, sizeof(mibmi::g_prof_et));
+}
+#endif
