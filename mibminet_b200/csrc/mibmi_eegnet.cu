@@ -53,6 +53,8 @@ struct EegNet {
     int NCH, P, CT, NXS;
     int m32[kEegMaxF1];                                // layer 1, "no shift" magic (floor(2^32 / |fac|) + 1), factor sign folded into taps / offset
     long long offm32[kEegMaxF1];                       // sg * off1 * m32: hi32(x m + off m) = hi32((x + off) m)
+    int magic_rest;                                    // 1: layers 2 - 5 requantise with the magic division below (else hardware division)
+    int mg2[kEegMaxK2], sh2[kEegMaxK2], sg2[kEegMaxK2], mg4[kMaxF2], sh4[kMaxF2], sg4[kMaxF2], mg3, sh3, sg3, mg5, sh5, sg5;
     const uint8_t* b1umma;                             // Toeplitz operand of the temporal conv [128 = (f, n)][160] as K-major core matrices
     const uint8_t* b2umma;                             // block-diagonal spatial weights [16 = k][8 * 16 CT = (f, c)] as K-major core matrices
 };
@@ -408,6 +410,10 @@ __device__ __forceinline__ int et_div_fold(int x, int m, long long offm) {     /
     const int hi = (int)(((long long)x * m + offm) >> 32);
     return hi + (int)((unsigned)hi >> 31);
 }
+// tdiv(x, fac): magic form sg * tdiv_magic(x, m, sh) (|fac| >= 4, |x| < 2^29, proven per network at create) or the hardware division
+__device__ __forceinline__ int et_div(int x, int fac, int m, int sh, int sg, int magic) {
+    return magic ? sg * tdiv_magic(x, m, sh) : x / fac;
+}
 __device__ __forceinline__ void et_bar_sync_l() { asm volatile("bar.sync 1, %0;" ::"n"(kEtL * 32) : "memory"); }
 
 // Layers 3, 4, 5 on the four L warps (128 threads, named barrier 1).  Eight threads per channel:
@@ -416,7 +422,7 @@ __device__ __forceinline__ void et_bar_sync_l() { asm volatile("bar.sync 1, %0;"
 //   layer 4 (eegnet.py:157-161): thread (k, e) owns sample e of every pooling group: one 16-byte load of y3t[t] against the 16 input
 //            weights of output channel k = 4 dp4a, threshold, sum over the 8 threads of the group with three shuffles
 //   layer 5 (eegnet.py:164-166): warp = class
-struct EtLRegs { uint32_t w3[5][4]; uint32_t w4[4]; int thr4, off4, fac4; };
+struct EtLRegs { uint32_t w3[5][4]; uint32_t w4[4]; int thr4, off4, fac4, m4, sh4, sg4; };
 __device__ __forceinline__ void et_l_setup(const EegNet* __restrict__ net, int tid, EtLRegs& R) {
     const int k = tid >> 3, K2 = net->K2, F2 = net->F2;
 #pragma unroll
@@ -444,12 +450,14 @@ __device__ __forceinline__ void et_l_setup(const EegNet* __restrict__ net, int t
     R.off4 = k < F2 ? net->off4[k] : 0;
     R.fac4 = k < F2 ? net->fac4[k] : 1;
     R.thr4 = -(R.off4 >> 3);
+    R.m4 = k < F2 ? net->mg4[k] : 0; R.sh4 = k < F2 ? net->sh4[k] : 0; R.sg4 = k < F2 ? net->sg4[k] : 1;
 }
 __device__ __forceinline__ void et_layers345(const EegNet* __restrict__ net, const EtLRegs& R, const int8_t* y2, int y2s, int8_t* y3t,
                                              int8_t* y4, long long b, int8_t* __restrict__ logits, int8_t* __restrict__ tap3,
                                              int8_t* __restrict__ tap4, int tid) {
     const int K2 = net->K2, F2 = net->F2, N = net->N, T8 = net->T8, T64 = net->T64;
-    const int k = tid >> 3, e8 = tid & 7, fac3 = net->fac3;
+    const int k = tid >> 3, e8 = tid & 7, fac3 = net->fac3, mg = net->magic_rest;
+    const int m3 = net->mg3, sh3 = net->sh3, sg3 = net->sg3;
     if (k < K2) {
         const uint32_t* row = reinterpret_cast<const uint32_t*>(y2 + k * y2s);
         for (int u = e8; 4 * u < T8; u += 8) {
@@ -464,7 +472,7 @@ __device__ __forceinline__ void et_layers345(const EegNet* __restrict__ net, con
             for (int sft = 0; sft < 4; sft++) {
                 const int t = 4 * u + sft;
                 if (t < T8) {
-                    const int o = eclip8(acc[sft] / fac3);
+                    const int o = eclip8(et_div(acc[sft], fac3, m3, sh3, sg3, mg));
                     y3t[t * 16 + k] = (int8_t)o;
                     if (tap3) tap3[((size_t)b * K2 + k) * T8 + t] = (int8_t)o;
                 }
@@ -483,7 +491,7 @@ __device__ __forceinline__ void et_layers345(const EegNet* __restrict__ net, con
         m += __shfl_xor_sync(0xffffffffu, m, 2);
         m += __shfl_xor_sync(0xffffffffu, m, 4);
         if (e8 == (q & 7) && k < F2) {
-            const int o = eclip8((m + R.off4) / R.fac4);
+            const int o = eclip8(et_div(m + R.off4, R.fac4, R.m4, R.sh4, R.sg4, mg));
             y4[k * T64 + q] = (int8_t)o;
             if (tap4) tap4[((size_t)b * F2 + k) * T64 + q] = (int8_t)o;
         }
@@ -495,7 +503,7 @@ __device__ __forceinline__ void et_layers345(const EegNet* __restrict__ net, con
         for (int i = tid & 31; i < F2 * T64; i += 32) z += (int)y4[i] * (int)w[i];
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) z += __shfl_xor_sync(0xffffffffu, z, o);
-        if ((tid & 31) == 0) logits[(size_t)b * N + n] = (int8_t)eclip8((z + net->b5[n]) / net->fac5);
+        if ((tid & 31) == 0) logits[(size_t)b * N + n] = (int8_t)eclip8(et_div(z + net->b5[n], net->fac5, net->mg5, net->sh5, net->sg5, mg));
     }
     et_bar_sync_l();
 }
@@ -540,13 +548,16 @@ eegnet_tc_kernel(const EegNet* __restrict__ net, const int8_t* __restrict__ x, l
         reinterpret_cast<uint4*>(esm + sm.off_b2)[i] = reinterpret_cast<const uint4*>(net->b2umma)[i];
     {   // constants: [0..7] m32, [8..23] offm32 (lo, hi), [24..39] thr2, [40..55] off2, [56..71] fac2
         int* cw = reinterpret_cast<int*>(esm + kEtOffCons);
-        for (int i = tid; i < 72; i += kEtThreads) {
+        for (int i = tid; i < 120; i += kEtThreads) {     // ... [72..87] mg2, [88..103] sh2, [104..119] sg2
             int v = 0;
             if (i < 8) v = net->m32[i];
             else if (i < 24) v = (int)((unsigned long long)net->offm32[(i - 8) >> 1] >> (32 * ((i - 8) & 1)));
             else if (i < 40) v = (i - 24) < K2 ? -(net->off2[i - 24] >> 3) : 0;
             else if (i < 56) v = (i - 40) < K2 ? net->off2[i - 40] : 0;
-            else v = (i - 56) < K2 ? net->fac2[i - 56] : 1;
+            else if (i < 72) v = (i - 56) < K2 ? net->fac2[i - 56] : 1;
+            else if (i < 88) v = (i - 72) < K2 ? net->mg2[i - 72] : 0;
+            else if (i < 104) v = (i - 88) < K2 ? net->sh2[i - 88] : 0;
+            else v = (i - 104) < K2 ? net->sg2[i - 104] : 1;
             cw[i] = v;
         }
     }
@@ -581,10 +592,13 @@ eegnet_tc_kernel(const EegNet* __restrict__ net, const int8_t* __restrict__ x, l
         int thr[4];
 #pragma unroll
         for (int j = 0; j < 4; j++) thr[j] = cw[24 + 8 * (j >> 1) + 2 * q + (j & 1)];      // column 8 nt + 2 q + e, j = 2 nt + e
-        // after the reduction lane g requantises the group rg = g >> 1 of the columns 8 nt + 2 q + e, nt = g & 1
-        const int nt_l = g & 1, rg_l = g >> 1;
+        // the reduction over the 8 rows g of a pooling group halves the values a lane carries in every round (xor 4, 8, 16 on the lane
+        // = bits 0, 1, 2 of g): lane g ends with the two columns e = 0, 1 of nt = g & 1 in the group rg = 2 ((g >> 1) & 1) + ((g >> 2) & 1)
+        const int nt_l = g & 1, rg_l = 2 * ((g >> 1) & 1) + ((g >> 2) & 1);
         const int k0 = 8 * nt_l + 2 * q;
         const int off_a = cw[40 + k0], off_b = cw[41 + k0], fac_a = cw[56 + k0], fac_b = cw[57 + k0];
+        const int mg_a = cw[72 + k0], mg_b = cw[73 + k0], sh_a = cw[88 + k0], sh_b = cw[89 + k0], sg_a = cw[104 + k0], sg_b = cw[105 + k0];
+        const int mgc = net->magic_rest;
         for (int i = 0; i < ntr; i++) {
             const long long b = first + (long long)i * stride;
             const int yb = i & 1;
@@ -603,39 +617,50 @@ eegnet_tc_kernel(const EegNet* __restrict__ net, const int8_t* __restrict__ x, l
                 __syncwarp();
                 if (lane == 0) mbar_arrive(sbase + kEtT2Empty + 8 * buf);
                 // r[4 nt + c] = (row g + 8 (c >> 1), column 8 nt + 2 q + (c & 1)): threshold, then sum over the 8 rows g of a group
-                int p[4][4];                                                    // [rg][2 nt + e]
+                // v[8 nt + 4 b2 + 2 c2 + e]: row group rg = 2 b2 + c2, column 8 nt + 2 q + e
+                int v[16];
 #pragma unroll
                 for (int nt = 0; nt < 2; nt++)
 #pragma unroll
                     for (int c = 0; c < 4; c++) {
-                        p[c >> 1][2 * nt + (c & 1)] = max((int)r0[4 * nt + c], thr[2 * nt + (c & 1)]);
-                        p[2 + (c >> 1)][2 * nt + (c & 1)] = max((int)r1[4 * nt + c], thr[2 * nt + (c & 1)]);
+                        const int e = c & 1, th = thr[2 * nt + e];
+                        v[8 * nt + 2 * (c >> 1) + e] = max((int)r0[4 * nt + c], th);           // rg = c >> 1      (b2 = 0)
+                        v[8 * nt + 4 + 2 * (c >> 1) + e] = max((int)r1[4 * nt + c], th);       // rg = 2 + (c >> 1) (b2 = 1)
                     }
+                {
+                    const bool up = g & 1;                  // round 1 (lane xor 4): keep nt = g & 1
 #pragma unroll
-                for (int rg = 0; rg < 4; rg++)
+                    for (int j = 0; j < 8; j++) {
+                        const int send = up ? v[j] : v[j + 8], keep = up ? v[j + 8] : v[j];
+                        v[j] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+                    }
+                }
+                {
+                    const bool up = (g >> 1) & 1;           // round 2 (lane xor 8): keep b2
 #pragma unroll
                     for (int j = 0; j < 4; j++) {
-                        int v = p[rg][j];
-                        v += __shfl_xor_sync(0xffffffffu, v, 4);
-                        v += __shfl_xor_sync(0xffffffffu, v, 8);
-                        v += __shfl_xor_sync(0xffffffffu, v, 16);
-                        p[rg][j] = v;
+                        const int send = up ? v[j] : v[j + 4], keep = up ? v[j + 4] : v[j];
+                        v[j] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
                     }
-                int sa = 0, sb = 0;
+                }
+                {
+                    const bool up = (g >> 2) & 1;           // round 3 (lane xor 16): keep c2
 #pragma unroll
-                for (int rg = 0; rg < 4; rg++)
-#pragma unroll
-                    for (int nt = 0; nt < 2; nt++)
-                        if (rg == rg_l && nt == nt_l) { sa = p[rg][2 * nt]; sb = p[rg][2 * nt + 1]; }
+                    for (int j = 0; j < 2; j++) {
+                        const int send = up ? v[j] : v[j + 2], keep = up ? v[j + 2] : v[j];
+                        v[j] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+                    }
+                }
+                const int sa = v[0], sb = v[1];
                 const int pg = 16 * ch + 4 * qi + rg_l;                          // pooled sample of the trial
                 if (pg < T8) {
                     if (k0 < K2) {
-                        const int o = eclip8((sa + off_a) / fac_a);
+                        const int o = eclip8(et_div(sa + off_a, fac_a, mg_a, sh_a, sg_a, mgc));
                         y2[k0 * y2s + 7 + pg] = (int8_t)o;
                         if (tap2) tap2[((size_t)b * K2 + k0) * T8 + pg] = (int8_t)o;
                     }
                     if (k0 + 1 < K2) {
-                        const int o = eclip8((sb + off_b) / fac_b);
+                        const int o = eclip8(et_div(sb + off_b, fac_b, mg_b, sh_b, sg_b, mgc));
                         y2[(k0 + 1) * y2s + 7 + pg] = (int8_t)o;
                         if (tap2) tap2[((size_t)b * K2 + k0 + 1) * T8 + pg] = (int8_t)o;
                     }
@@ -975,6 +1000,41 @@ int mibmi_eegnet_create(const mibmi_eegnet_params_t* p, int device, mibmi_eegnet
             if (d < 4 || mm >= (1LL << 31) || (__int128)lim * er >= ((__int128)1 << 32)) { ok = false; break; }
             h->m32[f] = (int)mm;
             h->offm32[f] = (long long)h->sg1[f] * h->off1[f] * mm;
+        }
+        {   // layers 2 - 5: tdiv(x, d) == (mulhi(x, m) >> s) + (x < 0) for |d| >= 4, |x| < 2^29, sign of d applied after
+            auto magic = [](long long fac, long long xmax, int* m, int* sh, int* sg) -> bool {
+                const long long fa = fac < 0 ? -fac : fac;
+                *sg = fac < 0 ? -1 : 1;
+                if (fa < 4 || fa > 0x7fffffffLL || xmax >= (1LL << 29)) return false;
+                int lg = 0;
+                while ((1LL << (lg + 1)) <= fa) lg++;
+                const long long mm = (long long)(((__int128)1 << (30 + lg)) / fa) + 1;
+                if (mm >= (1LL << 31)) return false;
+                *m = (int)mm;
+                *sh = lg - 2;
+                return true;
+            };
+            auto l1 = [](const int8_t* w, int n) { long long t = 0; for (int i = 0; i < n; i++) t += w[i] < 0 ? -(long long)w[i] : w[i]; return t; };
+            auto ab = [](long long v) { return v < 0 ? -v : v; };
+            bool mr = true;
+            for (int k = 0; k < K2 && mr; k++) {
+                const long long am = 128 * l1(p->l2_weight + k * C, C), th = ab(-((long long)h->off2[k] >> 3));
+                mr = magic(h->fac2[k], 8 * (am > th ? am : th) + ab(h->off2[k]), &h->mg2[k], &h->sh2[k], &h->sg2[k]);
+            }
+            long long m3x = 0;
+            for (int k = 0; k < K2; k++) { const long long v = 128 * l1(p->l3_weight + k * kL3Taps, kL3Taps); m3x = v > m3x ? v : m3x; }
+            mr = mr && magic(h->fac3, m3x, &h->mg3, &h->sh3, &h->sg3);
+            for (int k = 0; k < F2 && mr; k++) {
+                const long long am = 128 * l1(p->l4_weight + k * K2, K2), th = ab(-((long long)h->off4[k] >> 3));
+                mr = magic(h->fac4[k], 8 * (am > th ? am : th) + ab(h->off4[k]), &h->mg4[k], &h->sh4[k], &h->sg4[k]);
+            }
+            long long m5x = 0;
+            for (int nn = 0; nn < N; nn++) {
+                const long long v = 128 * l1(p->l5_weight + (size_t)nn * F2 * h->T64, F2 * h->T64) + ab(h->b5[nn]);
+                m5x = v > m5x ? v : m5x;
+            }
+            mr = mr && magic(h->fac5, m5x, &h->mg5, &h->sh5, &h->sg5);
+            h->magic_rest = mr ? 1 : 0;
         }
         h->NCH = (T + 127) / 128;
         h->P = 128 * h->NCH + 144;

@@ -130,6 +130,25 @@ def test_gpu_tcgen05_kernel_over_many_trials(C, T, D, B, monkeypatch):
 
 
 @pytest.mark.gpu
+def test_gpu_tcgen05_kernel_with_factors_outside_the_magic_range():
+    """|factor| < 4 in layers 2 - 5 is outside the proven range of the magic division: eegnet_tc_kernel then divides in hardware there
+    (layer 1 keeps its own magic) and must stay exact; negative factors go through the sign path."""
+    import dataclasses
+    from mibminet_b200.engine import EEGNetInt8
+    sd, p, _, torch = _gpu_net(22, 1125, 8, 2, 128, seed=12)
+    x = synth.make_trials(200, 22, 1125, seed=13)
+    fac2 = np.asarray(p.fac2).copy(); fac2[::3] *= -1
+    fac4 = np.asarray(p.fac4).copy(); fac4[1::2] *= -1
+    for kw in ({"fac3": -int(p.fac3), "fac2": fac2.astype(np.int32), "fac4": fac4.astype(np.int32), "fac5": -int(p.fac5)},
+               {"fac3": 3}, {"fac5": -2}):
+        p2 = dataclasses.replace(p, **kw)
+        net = EEGNetInt8(p2, device="cuda:0")
+        y = net.forward(torch.from_numpy(x).cuda()).cpu().numpy()
+        assert net.last_kernel == "eegnet_tc_kernel"
+        assert np.array_equal(y, eegnet_np.forward(p2, x)), kw.keys()
+
+
+@pytest.mark.gpu
 def test_gpu_saturating_inputs_and_empty_batch():
     sd, p, net, torch = _gpu_net(22, 1125, 8, 2, 128, seed=1)
     x = np.stack([np.full((22, 1125), 127, np.int8), np.full((22, 1125), -128, np.int8),
