@@ -679,12 +679,12 @@ eegnet_tc_kernel(const EegNet* __restrict__ net, const int8_t* __restrict__ x, l
         // ===================================================================================== E1: batch_norm1 / quant2 -> A operand of MMA 2
         const int es = (warp - kEtWarpE1) >> 2, qi = warp & 3;
         const int r = lane & 7, cl = 4 * qi + (lane >> 3);
-        long long gq = 0;
-        for (int i = 0; i < ntr; i++)
-            for (int ch = 0; ch < NCH; ch++)
-                for (int ct = 0; ct < CT; ct++, gq++) {
-                    if ((int)(gq % kEtSets) != es) continue;
-                    const int use = (int)(gq / kEtSets);
+        // this set owns the tiles es, es + kEtSets, ... of the CTA's tile sequence (trial, chunk, channel tile); no division per tile
+        int i = 0, ch = 0, ct = es;
+        while (ct >= CT) { ct -= CT; ch++; }
+        while (ch >= NCH) { ch -= NCH; i++; }
+        for (int use = 0; i < ntr; use++) {
+                {
                     const int gch = i * NCH + ch, buf = gch & 1;
                     EWAIT(0, sbase + kEtT1Full + 8 * es, use & 1);
                     EWAIT(1, sbase + kEtA2Empty + 8 * buf, ((gch >> 1) & 1) ^ 1);     // MMA 2 of chunk gch - 2 has read this buffer
@@ -724,6 +724,10 @@ eegnet_tc_kernel(const EegNet* __restrict__ net, const int8_t* __restrict__ x, l
                         mbar_arrive(sbase + kEtA2Full + 8 * buf);
                     }
                 }
+                ct += kEtSets;
+                while (ct >= CT) { ct -= CT; ch++; }
+                while (ch >= NCH) { ch -= NCH; i++; }
+        }
     } else if (warp < kEtWarpM) {
         // ===================================================================================== S: trial -> padded rows (x[c][t] at byte PL + t)
         // PL = 64: every row starts on a 16-byte boundary of the stage.  Rows that are 16-byte aligned in global memory too (64 x 480)
@@ -734,8 +738,8 @@ eegnet_tc_kernel(const EegNet* __restrict__ net, const int8_t* __restrict__ x, l
         const uintptr_t gend = (reinterpret_cast<uintptr_t>(x) + (size_t)B * C * T + 3) & ~(uintptr_t)3;
         for (int i = 0; i < ntr; i++) {
             const long long b = first + (long long)i * stride;
-            const int st = i % NXS;
-            EWAIT(0, sbase + kEtXsEmpty + 8 * st, ((i / NXS) & 1) ^ 1);
+            const int st = NXS == 1 ? 0 : (i & 1), xuse = NXS == 1 ? i : (i >> 1);       // NXS is 1 or 2
+            EWAIT(0, sbase + kEtXsEmpty + 8 * st, (xuse & 1) ^ 1);
             uint8_t* xs = esm + sm.off_xs + st * xs_bytes + PL;
             const int8_t* xb = x + (size_t)b * C * T;
             const uint32_t bar = sbase + kEtXsFull + 8 * st;
@@ -804,14 +808,12 @@ eegnet_tc_kernel(const EegNet* __restrict__ net, const int8_t* __restrict__ x, l
             }
             __syncwarp();
         };
-        long long gq = 0;
+        int tb = 0, use = 0, st = 0, xuse = 0;             // accumulator buffer of the next tile / its use count; input stage / its use count
         for (int i = 0; i < ntr; i++) {
-            const int st = i % NXS;
-            EWAIT(0, sbase + kEtXsFull + 8 * st, (i / NXS) & 1);
+            EWAIT(0, sbase + kEtXsFull + 8 * st, xuse & 1);
             for (int ch = 0; ch < NCH; ch++) {
                 const int gch = i * NCH + ch;
-                for (int ct = 0; ct < CT; ct++, gq++) {
-                    const int tb = (int)(gq % kEtSets), use = (int)(gq / kEtSets);
+                for (int ct = 0; ct < CT; ct++) {
                     EWAIT(2, sbase + kEtT1Empty + 8 * tb, (use & 1) ^ 1);
                     tc_fence_after();
                     if (elect_one()) {
@@ -823,9 +825,11 @@ eegnet_tc_kernel(const EegNet* __restrict__ net, const int8_t* __restrict__ x, l
                         if (ch == NCH - 1 && ct == CT - 1) umma_commit(sbase + kEtXsEmpty + 8 * st);
                     }
                     __syncwarp();
+                    if (++tb == kEtSets) { tb = 0; use++; }
                 }
                 if (gch > 0) mma2(gch - 1);
             }
+            if (++st == NXS) { st = 0; xuse++; }
         }
         if (ntr > 0) mma2(ntr * NCH - 1);
     }

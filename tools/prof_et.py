@@ -28,8 +28,8 @@ assert L.mibmi_debug_prof_et(buf.ctypes.data) == 0
 q = buf.reshape(148, 32, 4).astype(np.float64)
 ntr = B / 148
 roles = {'L  layers 3-5': (range(0, 4), ['y2_full', '-', '-']), 'E2 pool': (range(4, 8), ['t2_full', 'y2_empty', '-']),
-         'E1 requant': (range(8, 20), ['t1_full', 'a2_empty', '-']), 'S  staging': (range(20, 24), ['xs_empty', '-', '-']),
-         'M  mma': (range(24, 25), ['xs_full', 'a2_full', 't1/t2_empty'])}
+         'E1 requant': (range(8, 20), ['t1_full', 'a2_empty', '-']), 'S  staging': (range(20, 23), ['xs_empty', '-', '-']),
+         'M  mma': (range(23, 24), ['xs_full', 'a2_full', 't1/t2_empty'])}
 print(f'{C}x{T}: cycles per trial per CTA = {q[:, 0, 0].mean() / ntr:.0f}')
 for r, (ws, names) in roles.items():
     w = q[:, list(ws), :]
