@@ -679,6 +679,13 @@ eegnet_tc_kernel(const EegNet* __restrict__ net, const int8_t* __restrict__ x, l
         // ===================================================================================== E1: batch_norm1 / quant2 -> A operand of MMA 2
         const int es = (warp - kEtWarpE1) >> 2, qi = warp & 3;
         const int r = lane & 7, cl = 4 * qi + (lane >> 3);
+        int m1c[8];
+        long long offm1c[8];
+#pragma unroll
+        for (int f = 0; f < 8; f++) {
+            m1c[f] = cw[f];
+            offm1c[f] = *reinterpret_cast<const long long*>(cw + 8 + 2 * f);
+        }
         // this set owns the tiles es, es + kEtSets, ... of the CTA's tile sequence (trial, chunk, channel tile); no division per tile
         int i = 0, ch = 0, ct = es;
         while (ct >= CT) { ct -= CT; ch++; }
@@ -693,7 +700,7 @@ eegnet_tc_kernel(const EegNet* __restrict__ net, const int8_t* __restrict__ x, l
                     if (16 * ct + 4 * qi < C) {                                          // warp-uniform: some channel of the quarter exists
                         const uint32_t ta = tmem_base + ((uint32_t)(32 * qi) << 16) + 128 * es;
                         uint8_t* a2 = esm + sm.off_a2 + buf * a2_bytes + c * 128 + ((r ^ (c & 7)) << 4);
-#pragma unroll 1
+#pragma unroll
                         for (int fp = 0; fp < 4; fp++) {
                             uint32_t ra[16], rb[16];
                             et_tmem_ld_32x32b_x16(ra, ta + 32 * fp);
@@ -702,8 +709,8 @@ eegnet_tc_kernel(const EegNet* __restrict__ net, const int8_t* __restrict__ x, l
 #pragma unroll
                             for (int h = 0; h < 2; h++) {
                                 const int f = 2 * fp + h;
-                                const int m = cw[f];
-                                const long long offm = *reinterpret_cast<const long long*>(cw + 8 + 2 * f);
+                                const int m = m1c[f];
+                                const long long offm = offm1c[f];
                                 uint32_t w[4];
 #pragma unroll
                                 for (int j = 0; j < 4; j++) {
