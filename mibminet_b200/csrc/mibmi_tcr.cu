@@ -172,9 +172,20 @@ __device__ __forceinline__ uint2 tcr_lds64(const uint8_t* p) {
     return v;
 }
 // WOLF = 0: one row of T samples: lane = 16-byte chunk (+ 32 per pass); all loads of the row are issued before the shifts
+#ifndef MIBMI_TCR_TAIL
+#define MIBMI_TCR_TAIL 0                  // 1: the <= 8 chunks beyond the second pass of every row are realigned four rows at a time
+                                          // (13 instead of 16.5 passes per warp and trial; r2j: bit-exact but slower, 82.8 vs 83.7 M trials/s -- the
+                                          // per-lane word selects and the bank conflicts of four rows in one pass cost what the passes save)
+#endif
+template <class K>
+struct TcrTail {
+    static constexpr int TAILC = K::CHUNKS - 64;                                 // chunks of a row beyond two full passes (7 at T = 1125)
+    static constexpr bool SPLIT = MIBMI_TCR_TAIL && TAILC > 0 && TAILC <= 8;
+    static constexpr int RPT = SPLIT ? 32 / TAILC : 1;                           // rows per tail pass
+};
 template <class K, int K4>
 __device__ __forceinline__ void tcr_realign_row(const uint8_t* rbase, uint8_t* xrow, int c, int sh, int lane) {
-    constexpr int P = (K::CHUNKS + 31) / 32;
+    constexpr int P = TcrTail<K>::SPLIT ? 2 : (K::CHUNKS + 31) / 32;
     uint4 q0[P], q1[P];
 #pragma unroll
     for (int p = 0; p < P; p++)
@@ -488,6 +499,36 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
                             case 1: tcr_realign_row<K, 1>(rbase, xrow, c, sh, lane); break;
                             case 2: tcr_realign_row<K, 2>(rbase, xrow, c, sh, lane); break;
                             default: tcr_realign_row<K, 3>(rbase, xrow, c, sh, lane); break;
+                        }
+                    }
+                    if (TcrTail<K>::SPLIT) {
+                        // the chunks 64 .. of the warp's rows, RPT rows per pass: lane = (row, chunk), so shift and word offset are per
+                        // lane: the five words are picked with two rounds of selects (word offset bits 1 and 0) before the funnel shifts
+                        constexpr int TAILC = TcrTail<K>::TAILC, RPT = TcrTail<K>::RPT;
+                        constexpr int NROWS = (K::C + kRRW - 1) / kRRW, NTP = (NROWS + RPT - 1) / RPT;
+                        const int ri = lane / TAILC, jt = lane - ri * TAILC;
+#pragma unroll
+                        for (int tp = 0; tp < NTP; tp++) {
+                            const int c = rw + kRRW * (RPT * tp + ri);
+                            if (ri < RPT && c < K::C) {
+                                const int src0 = o15 + c * K::T;
+                                const uint8_t* a = raw + (src0 & ~15) + 16 * (64 + jt);
+                                const uint4 q0 = tcr_lds128(a), q1 = tcr_lds128(a + 16);
+                                const int k4 = (src0 >> 2) & 3, sh = 8 * (src0 & 3);
+                                const uint32_t w[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
+                                uint32_t v[6], u[5];
+#pragma unroll
+                                for (int i = 0; i < 6; i++) v[i] = (k4 & 2) ? w[i + 2] : w[i];
+#pragma unroll
+                                for (int i = 0; i < 5; i++) u[i] = (k4 & 1) ? v[i + 1] : v[i];
+                                uint4 o;
+                                o.x = __funnelshift_r(u[0], u[1], sh);
+                                o.y = __funnelshift_r(u[1], u[2], sh);
+                                o.z = __funnelshift_r(u[2], u[3], sh);
+                                o.w = __funnelshift_r(u[3], u[4], sh);
+                                const int jj = 64 + jt;
+                                *reinterpret_cast<uint4*>(xs + c * 128 + (jj >> 3) * K::TILE_PITCH + (((jj & 7) ^ (c & 7)) << 4)) = o;
+                            }
                         }
                     }
                 }

@@ -1,13 +1,12 @@
-# round 2, call j: realign warps specialised on the trial offset (immediates for every load, shift and word select)
+# round 2: tcr realign warps: tail chunks of four rows per pass (notail = previous form)
 set -x
 O=gpurun_out/r2j; mkdir -p $O
-timeout 600 python -m pytest tests -m gpu -x -q -k "22 or tcr or wolf or unaligned or gather or taps" > $O/pytest_tcr.log 2>&1; tail -5 $O/pytest_tcr.log
-bench1() { timeout 200 python bench.py --steps 20 --warmup 5 --no-cpu-baseline --no-e2e --sustained-seconds 0 "$@" | python -c "import json,sys; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print(round(d['value']/1e6,2), round(d['roofline']['frac'],4), d['roofline']['kernel'], d['gpu_launches'], d['clocks']['sm_mhz'], d['clocks']['reasons'])"; }
-for v in base rb3 rb6; do
-  if [ $v = base ]; then unset MIBMI_LIB_PATH; else export MIBMI_LIB_PATH=tools/variants/$v/libmibmi.so; fi
-  echo "== $v 22x1125 bct"; bench1 --shape 22x1125
-  echo "== $v 22x1125 btc"; bench1 --shape 22x1125 --layout btc
-done > $O/bench.txt 2>&1
-cat $O/bench.txt
-MIBMI_LIB_PATH=tools/variants/prof/libmibmi.so timeout 180 python tools/prof_tcr.py 22 1125 bct > $O/prof_bct.txt 2>&1; cat $O/prof_bct.txt
-MIBMI_LIB_PATH=tools/variants/prof/libmibmi.so timeout 180 python tools/prof_tcr.py 22 1125 btc > $O/prof_btc.txt 2>&1; cat $O/prof_btc.txt
+timeout 600 python -m pytest tests -m gpu -x -q -k "1125 or 22 or gather or graph" > $O/pytest_22.log 2>&1; tail -3 $O/pytest_22.log
+b() { timeout 200 python bench.py --shape 22x1125 --steps 20 --warmup 5 --no-cpu-baseline --no-e2e --sustained-seconds 0 "$@" | python -c "import json,sys; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print(round(d['value']/1e6,2), round(d['roofline']['frac'],4), d['clocks']['sm_mhz'], d['clocks']['reasons'])"; }
+for v in notail tail notail tail; do
+  if [ $v = tail ]; then unset MIBMI_LIB_PATH; else export MIBMI_LIB_PATH=tools/variants/$v/libmibmi.so; fi
+  echo "== $v bct"; b
+done > $O/ab.txt 2>&1
+grep -E "^== |^[0-9]" $O/ab.txt | paste - -
+export MIBMI_LIB_PATH=tools/variants/prof/libmibmi.so
+timeout 200 python tools/prof_tcr.py 22 1125 bct > $O/role_profile_bct.txt 2>&1; cat $O/role_profile_bct.txt
