@@ -375,6 +375,11 @@ __device__ long long g_prof_et[148 * 32 * 4];
 #ifndef MIBMI_ET_SW
 #define MIBMI_ET_SW 3                     // staging warps (r2h4: 3 instead of 4 = 24 warps, 80 registers: 9.96 -> 11.09 M trials/s at 22 x 1125)
 #endif
+#ifndef MIBMI_ET_M64
+#define MIBMI_ET_M64 0                    // 1: a last channel tile of <= 8 channels (22 channels: 16 + 6) as an M = 64 instruction: bit-exact (the
+                                          // TMEM lane of row i is 32 (i / 16) + i % 16), no faster (r2h8: 12.35 vs 12.72 M trials/s, the same 3 % that the
+                                          // extra selects cost at 64 x 480, where no tile is short)
+#endif
 #ifndef MIBMI_ET_E1W
 #define MIBMI_ET_E1W 12                   // layer-1 epilogue warps: sets of four (one TMEM accumulator buffer per set)
 #endif
@@ -696,8 +701,11 @@ eegnet_tc_kernel(const EegNet* __restrict__ net, const int8_t* __restrict__ x, l
                     EWAIT(0, sbase + kEtT1Full + 8 * es, use & 1);
                     EWAIT(1, sbase + kEtA2Empty + 8 * buf, ((gch >> 1) & 1) ^ 1);     // MMA 2 of chunk gch - 2 has read this buffer
                     tc_fence_after();
-                    const int c = 16 * ct + cl;
-                    if (16 * ct + 4 * qi < C) {                                          // warp-uniform: some channel of the quarter exists
+                    // a last tile of at most 8 channels is an M = 64 instruction (MIBMI_ET_M64): its row i sits in TMEM lane
+                    // 32 (i / 16) + i % 16, i.e. a lane quarter holds two channels in its lanes 0 .. 15
+                    const bool half = MIBMI_ET_M64 && C - 16 * ct <= 8;
+                    const int c = half ? 16 * ct + 2 * qi + ((lane >> 3) & 1) + (lane >= 16 ? 64 : 0) : 16 * ct + cl;
+                    if (half ? (16 * ct + 2 * qi < C) : (16 * ct + 4 * qi < C)) {       // warp-uniform: some channel of the quarter exists
                         const uint32_t ta = tmem_base + ((uint32_t)(32 * qi) << 16) + 128 * es;
                         uint8_t* a2 = esm + sm.off_a2 + buf * a2_bytes + c * 128 + ((r ^ (c & 7)) << 4);
 #pragma unroll
@@ -796,7 +804,7 @@ eegnet_tc_kernel(const EegNet* __restrict__ net, const int8_t* __restrict__ x, l
         }
     } else {
         // ===================================================================================== M: both MMAs
-        constexpr uint32_t idesc1 = et_idesc_i8_kk(128, 128), idesc2 = umma_idesc_i8(128, 16);
+        constexpr uint32_t idesc1 = et_idesc_i8_kk(128, 128), idesc1h = et_idesc_i8_kk(64, 128), idesc2 = umma_idesc_i8(128, 16);
         const uint64_t da1 = umma_desc(sbase + sm.off_xs, 16, (uint32_t)P, 0), db1 = umma_desc(sbase + kEtOffB1, 128, 1280, 0);
         const uint64_t da2 = umma_desc(sbase + sm.off_a2, 16, 1024, 2), db2 = umma_desc(sbase + sm.off_b2, 128, (uint32_t)(8 * KC / 16) * 128, 0);
         const uint32_t a1_hi = (uint32_t)(da1 >> 32), b1_hi = (uint32_t)(db1 >> 32), a2_hi = (uint32_t)(da2 >> 32), b2_hi = (uint32_t)(db2 >> 32);
@@ -827,7 +835,8 @@ eegnet_tc_kernel(const EegNet* __restrict__ net, const int8_t* __restrict__ x, l
                         const uint32_t a_lo = (uint32_t)da1 + ((st * xs_bytes + 16 * ct * P + 128 * ch) >> 4);
 #pragma unroll
                         for (int s = 0; s < 5; s++)
-                            umma_i8_lohi(tmem_base + 128 * tb, a_lo + ((32 * s) >> 4), a1_hi, (uint32_t)db1 + ((256 * s) >> 4), b1_hi, idesc1, s > 0);
+                            umma_i8_lohi(tmem_base + 128 * tb, a_lo + ((32 * s) >> 4), a1_hi, (uint32_t)db1 + ((256 * s) >> 4), b1_hi,
+                                         (MIBMI_ET_M64 && C - 16 * ct <= 8) ? idesc1h : idesc1, s > 0);
                         umma_commit(sbase + kEtT1Full + 8 * tb);
                         if (ch == NCH - 1 && ct == CT - 1) umma_commit(sbase + kEtXsEmpty + 8 * st);
                     }
