@@ -21,7 +21,7 @@ struct mibmi_net {
     GenericNet* gen_dev = nullptr;
     int8_t* w5_dev = nullptr;
     PipeNet* pipe_dev = nullptr;       // warp-specialised pipeline kernel (MIBMI_PATH_FUSED)
-    bool pipe_ok = false, pipe_fast1 = false, tc_ok = false, tcr_ok = false, tc_wolf_ok = false, plain = false;
+    bool pipe_ok = false, pipe_fast1 = false, stream_fast3 = false, tc_ok = false, tcr_ok = false, tc_wolf_ok = false, plain = false;
     const char* pipe_why = "";
     StreamNet* stream_dev = nullptr;   // sliding-window streaming kernel (mibmi_forward_stream_int8)
     bool stream_ok = false;
@@ -247,6 +247,16 @@ bool pack_pipe(const mibmi_params_t* p, PipeNet* f, const char** why) {
     {
         const int sg = p->l3_factor < 0 ? -1 : 1;
         if (!magic_for(iabs64(p->l3_factor), &f->m3, &f->sh3)) { *why = "|l3_factor| < 4"; return false; }
+        {   // "no shift" form (magic32_for above) when it is exact up to saturation: every kernel clips the layer-3 quotient to int8
+            int64_t xmax3 = 0;
+            for (int k = 0; k < 16; k++) {
+                int64_t sum = 0;
+                for (int j = 0; j < 16; j++) sum += iabs64(p->l3_weight[k * 16 + j]);
+                if (128 * sum > xmax3) xmax3 = 128 * sum;
+            }
+            int m32;
+            if (magic32_for(iabs64(p->l3_factor), xmax3, &m32)) { f->m3 = m32; f->sh3 = 0; }
+        }
         for (int k = 0; k < 16; k++)
             for (int v = 0; v < 2; v++)
                 for (int h = 0; h < 2; h++)
@@ -659,6 +669,7 @@ int mibmi_create(const mibmi_params_t* p, int device, mibmi_net_t** out) {
     }
     n->pipe_ok = pack_pipe(p, pn, &n->pipe_why);
     n->pipe_fast1 = pn->fast1 != 0;
+    n->stream_fast3 = pn->sh3 == 0;
     n->plain = pn->plain != 0;
     n->tc_ok = n->pipe_ok && tc_has_instance(p->C, p->T);
     n->tcr_ok = n->pipe_ok && tcr_has_instance(p->C, p->T);
@@ -864,7 +875,7 @@ static int stream_impl(mibmi_net* net, const int8_t* x, int64_t S, int64_t L, in
     DeviceGuard dg(net->device);
     if (dg.err != cudaSuccess) return fail_cuda(net, dg.err);
     if (mode == MIBMI_STREAM_FUSED) {
-        cudaError_t e = launch_stream(net->stream_dev, net->pipe_fast1, net->C, net->T, x, S, L, logits, t2i, t2e, t3, t4,
+        cudaError_t e = launch_stream(net->stream_dev, (net->pipe_fast1 ? 1 : 0) | (net->stream_fast3 ? 2 : 0), net->C, net->T, x, S, L, logits, t2i, t2e, t3, t4,
                                       net->num_sms, stream);
         if (e != cudaSuccess) return fail_cuda(net, e);
         net->last_path.store(MIBMI_PATH_STREAM);

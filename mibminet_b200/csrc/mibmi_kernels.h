@@ -60,7 +60,7 @@ cudaError_t launch_wolf_reorder(const int8_t* x, int8_t* y, long long n, int C, 
 // Optional taps: t2i [S][16][2 (W-1) + T/8] stream-level pooled layer-2 samples (interior positions only),
 // t2e [S][W][16][8] the 4 + 4 edge samples of every window, t3 [S][W][16][T/8], t4 [S][W][16][T/64].
 bool stream_has_instance(int C, int T);
-cudaError_t launch_stream(const StreamNet* net_dev, bool fast1, int C, int T, const int8_t* x, long long S, long long L,
+cudaError_t launch_stream(const StreamNet* net_dev, int fast /* bit 0: layer 1, bit 1: layer 3 in the no-shift form */, int C, int T, const int8_t* x, long long S, long long L,
                           int8_t* logits, int8_t* t2i, int8_t* t2e, int8_t* t3, int8_t* t4, int num_sms, cudaStream_t stream);
 // Fallback: windows first .. first + nw - 1 (global index subject * W + w) of the streams -> out [nw][C][T]
 cudaError_t launch_gather_windows(const int8_t* x, long long L, int C, int T, int hop, long long W, long long first,

@@ -86,7 +86,7 @@ __device__ __forceinline__ int sdiv1(int x, int m, int s) {
 // work item -> (subject, first window)
 struct StreamItem { long long subj; int w0; };
 
-template <class K, bool FAST1, bool TAPS>
+template <class K, bool FAST1, bool TAPS, bool FAST3 = false>
 __global__ void __launch_bounds__(kStreamThreads, 2)
 stream_forward_kernel(const __grid_constant__ CUtensorMap tmx, const StreamNet* __restrict__ net, long long S, int W,
                       int chunks_per_subject, int8_t* __restrict__ logits, int8_t* __restrict__ tap2i,
@@ -352,7 +352,8 @@ stream_forward_kernel(const __grid_constant__ CUtensorMap tmx, const StreamNet* 
 #pragma unroll
                             for (int hf = 0; hf < 2; hf++) {
                                 const int wl = g + 8 * hf;
-                                const uint32_t w = pack2_sat(tdiv_magic(c3[2 * hf], m3, sh3), tdiv_magic(c3[2 * hf + 1], m3, sh3));
+                                const uint32_t w = FAST3 ? pack2_sat(sdiv1<true>(c3[2 * hf], m3, 0), sdiv1<true>(c3[2 * hf + 1], m3, 0))
+                                                         : pack2_sat(tdiv_magic(c3[2 * hf], m3, sh3), tdiv_magic(c3[2 * hf + 1], m3, sh3));
                                 *reinterpret_cast<uint16_t*>(y3k + wl * K::Y3W + pos) = (uint16_t)w;
                                 if (TAPS && tap3 && w0 + 16 * wt + wl < W) {
                                     int8_t* o = tap3 + (((size_t)subj * W + w0 + 16 * wt + wl) * 16 + k) * K::T8 + t;
@@ -419,7 +420,7 @@ stream_forward_kernel(const __grid_constant__ CUtensorMap tmx, const StreamNet* 
 
 // ---------------------------------------------------------------------------------------------
 template <int C, int T>
-static cudaError_t launch_stream_instance(const StreamNet* net_dev, bool fast1, const int8_t* x, long long S, long long L,
+static cudaError_t launch_stream_instance(const StreamNet* net_dev, int fast, const int8_t* x, long long S, long long L,
                                           int8_t* logits, int8_t* t2i, int8_t* t2e, int8_t* t3, int8_t* t4, int num_sms,
                                           cudaStream_t stream) {
     using K = SCfg<C, T>;
@@ -437,7 +438,8 @@ static cudaError_t launch_stream_instance(const StreamNet* net_dev, bool fast1, 
         return cudaErrorInvalidValue;
     const bool taps = t2i || t2e || t3 || t4;
     auto kern = taps ? stream_forward_kernel<K, false, true>
-                     : (fast1 ? stream_forward_kernel<K, true, false> : stream_forward_kernel<K, false, false>);
+                     : ((fast & 1) ? ((fast & 2) ? stream_forward_kernel<K, true, false, true> : stream_forward_kernel<K, true, false>)
+                                   : stream_forward_kernel<K, false, false>);
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, K::SMEM);
     if (e != cudaSuccess) return e;
     long long grid = 2LL * num_sms;
@@ -455,9 +457,9 @@ bool stream_has_instance(int C, int T) {
     return false;
 }
 
-cudaError_t launch_stream(const StreamNet* net_dev, bool fast1, int C, int T, const int8_t* x, long long S, long long L,
+cudaError_t launch_stream(const StreamNet* net_dev, int fast, int C, int T, const int8_t* x, long long S, long long L,
                           int8_t* logits, int8_t* t2i, int8_t* t2e, int8_t* t3, int8_t* t4, int num_sms, cudaStream_t stream) {
-#define X(c, t) if (C == c && T == t) return launch_stream_instance<c, t>(net_dev, fast1, x, S, L, logits, t2i, t2e, t3, t4, num_sms, stream);
+#define X(c, t) if (C == c && T == t) return launch_stream_instance<c, t>(net_dev, fast, x, S, L, logits, t2i, t2e, t3, t4, num_sms, stream);
     MIBMI_STREAM_SHAPES(X)
 #undef X
     return cudaErrorInvalidValue;
