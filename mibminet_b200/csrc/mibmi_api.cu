@@ -460,12 +460,12 @@ cudaError_t launch_fused_bct(mibmi_net* net, int path, const int8_t* x, int64_t 
                              int8_t* t1, int8_t* t2, int8_t* t3, int8_t* t4, cudaStream_t stream, int* which) {
     if (path == MIBMI_PATH_FUSED && net->tc_ok) {
         *which = K_TC;
-        return launch_tc(net->pipe_dev, net->pipe_fast1, net->C, net->T, x, B, logits, peers, t1, t2, t3, t4, net->num_sms, stream,
+        return launch_tc(net->pipe_dev, net->pipe_fast1 && net->stream_fast3, net->C, net->T, x, B, logits, peers, t1, t2, t3, t4, net->num_sms, stream,
                          net->plain);
     }
     if (path == MIBMI_PATH_FUSED && net->tcr_ok) {
         *which = K_TCR;
-        return launch_tcr(net->pipe_dev, net->pipe_fast1, net->C, net->T, x, B, MIBMI_LAYOUT_BCT, logits, peers, t1, t2, t3, t4,
+        return launch_tcr(net->pipe_dev, net->pipe_fast1 && net->stream_fast3, net->C, net->T, x, B, MIBMI_LAYOUT_BCT, logits, peers, t1, t2, t3, t4,
                           net->num_sms, stream, net->plain);
     }
     if (net->plain) return cudaErrorNotSupported;       // the mma.sync pipeline kernel implements REORDER_BN only
@@ -545,11 +545,11 @@ int forward_impl(mibmi_net* net, const int8_t* x, int64_t B, int layout, int8_t*
         if (fused && wolf_fused && path == MIBMI_PATH_FUSED) {
             which = K_TC;
             launches++;
-            e = launch_tc_wolf(net->pipe_dev, net->pipe_fast1, net->C, net->T, xo, nb, lo, po, o1, o2, o3, o4, net->num_sms, stream);
+            e = launch_tc_wolf(net->pipe_dev, net->pipe_fast1 && net->stream_fast3, net->C, net->T, xo, nb, lo, po, o1, o2, o3, o4, net->num_sms, stream);
         } else if (fused && wolf_tcr) {
             which = K_TCR;
             launches++;
-            e = launch_tcr(net->pipe_dev, net->pipe_fast1, net->C, net->T, xo, nb, MIBMI_LAYOUT_BTC, lo, po, o1, o2, o3, o4,
+            e = launch_tcr(net->pipe_dev, net->pipe_fast1 && net->stream_fast3, net->C, net->T, xo, nb, MIBMI_LAYOUT_BTC, lo, po, o1, o2, o3, o4,
                            net->num_sms, stream);
         } else if (fused && wolf_reorder) {
             e = launch_wolf_chunks(net, path, xo, nb, lo, po, o1, o2, o3, o4, stream, &which, &launches);

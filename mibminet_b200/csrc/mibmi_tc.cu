@@ -563,7 +563,8 @@ tc_forward_kernel(const __grid_constant__ CUtensorMap tmx, const PipeNet* __rest
 #pragma unroll
                     for (int v = 0; v < 2; v++) {
                         const int t = 16 * i + 8 * v + 2 * q;
-                        const uint32_t w = pack2_sat(tdiv_magic(c3[v][2 * hf], m3, sh3), tdiv_magic(c3[v][2 * hf + 1], m3, sh3));
+                        const uint32_t w = FAST1 ? pack2_sat(tc_div1<true>(c3[v][2 * hf], m3, 0), tc_div1<true>(c3[v][2 * hf + 1], m3, 0))      // FAST1: layers 1 and 3 without the shift
+                                                  : pack2_sat(tdiv_magic(c3[v][2 * hf], m3, sh3), tdiv_magic(c3[v][2 * hf + 1], m3, sh3));
                         if (t < K::T8) {
                             *reinterpret_cast<uint16_t*>(y3b + 2 * v) = (uint16_t)w;
                             if (TAPS && tap3 && b0 + rs < B) {

@@ -657,7 +657,8 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
 #pragma unroll
                     for (int v = 0; v < 2; v++) {
                         const int t = 16 * i + 8 * v + 2 * q;
-                        const uint32_t w = pack2_sat(tdiv_magic(c3[v][2 * half], m3, sh3), tdiv_magic(c3[v][2 * half + 1], m3, sh3));
+                        const uint32_t w = FAST1 ? pack2_sat(tcr_div1<true>(c3[v][2 * half], m3, 0), tcr_div1<true>(c3[v][2 * half + 1], m3, 0))  // FAST1: layers 1 and 3 without the shift
+                                                  : pack2_sat(tdiv_magic(c3[v][2 * half], m3, sh3), tdiv_magic(c3[v][2 * half + 1], m3, sh3));
                         if (t < K::T8) {
                             *reinterpret_cast<uint16_t*>(y3b + 32 * (i >> 1) + 4 * (i & 1) + 2 * v) = (uint16_t)w;
                             if (TAPS && tap3 && b < B) {
