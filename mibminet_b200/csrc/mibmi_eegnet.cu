@@ -361,6 +361,10 @@ eegnet_mma_kernel(const EegNet* __restrict__ net, const int8_t* __restrict__ x, 
 //   L     layers 3 - 5 (eeg_layers345_sub) on the double-buffered y2, one trial behind
 // Warps: L 0-3, E2 4-7, E1 8-19 (three sets of four TMEM lane quarters, one accumulator buffer each), S 20-23 (trial -> padded rows),
 // M 24 (issues both MMAs).  One persistent CTA per SM; hand-off is mbarrier-only.
+#ifndef MIBMI_ET_SLEEP_NS
+#define MIBMI_ET_SLEEP_NS 0               // > 0: the roles with long waits (L, E2, S) poll with nanosleep instead of the suspending try_wait
+                                          // (r2h9: 100 / 400 ns are slower, 12.06 / 12.20 vs 12.69 M trials/s)
+#endif
 #ifdef MIBMI_PROF
 __device__ long long g_prof_et[148 * 32 * 4];
 #define EWAIT(slot, ...) do { if (!mbar_test(__VA_ARGS__)) { const long long t0_ = clock64(); mbar_wait(__VA_ARGS__); pw_[slot] += clock64() - t0_; } } while (0)
@@ -372,6 +376,7 @@ __device__ long long g_prof_et[148 * 32 * 4];
 #define EPROF_BEGIN
 #define EPROF_END
 #endif
+#define EWAITS(slot, ...) do { if (MIBMI_ET_SLEEP_NS > 0) mbar_wait_sleep(__VA_ARGS__, MIBMI_ET_SLEEP_NS); else EWAIT(slot, __VA_ARGS__); } while (0)
 #ifndef MIBMI_ET_SW
 #define MIBMI_ET_SW 3                     // staging warps (r2h4: 3 instead of 4 = 24 warps, 80 registers: 9.96 -> 11.09 M trials/s at 22 x 1125)
 #endif
@@ -592,7 +597,7 @@ eegnet_tc_kernel(const EegNet* __restrict__ net, const int8_t* __restrict__ x, l
         for (int i = 0; i < ntr; i++) {
             const long long b = first + (long long)i * stride;
             const int yb = i & 1;
-            EWAIT(0, sbase + kEtY2Full + 8 * yb, (i >> 1) & 1);
+            EWAITS(0, sbase + kEtY2Full + 8 * yb, (i >> 1) & 1);
             et_layers345(net, R, reinterpret_cast<const int8_t*>(esm + sm.off_y2 + yb * K2 * y2s), y2s, reinterpret_cast<int8_t*>(esm + sm.off_y3),
                          reinterpret_cast<int8_t*>(esm + sm.off_y4), b, logits, tap3, tap4, tid);
             if (tid == 0) mbar_arrive(sbase + kEtY2Empty + 8 * yb);
@@ -613,11 +618,11 @@ eegnet_tc_kernel(const EegNet* __restrict__ net, const int8_t* __restrict__ x, l
         for (int i = 0; i < ntr; i++) {
             const long long b = first + (long long)i * stride;
             const int yb = i & 1;
-            EWAIT(1, sbase + kEtY2Empty + 8 * yb, ((i >> 1) & 1) ^ 1);       // the L warps are done with this y2 buffer (trial i - 2)
+            EWAITS(1, sbase + kEtY2Empty + 8 * yb, ((i >> 1) & 1) ^ 1);       // the L warps are done with this y2 buffer (trial i - 2)
             int8_t* y2 = reinterpret_cast<int8_t*>(esm + sm.off_y2 + yb * K2 * y2s);
             for (int ch = 0; ch < NCH; ch++) {
                 const int gch = i * NCH + ch, buf = gch & 1;
-                EWAIT(0, sbase + kEtT2Full + 8 * buf, (gch >> 1) & 1);
+                EWAITS(0, sbase + kEtT2Full + 8 * buf, (gch >> 1) & 1);
                 tc_fence_after();
                 uint32_t r0[8], r1[8];
                 const uint32_t ta = tmem_base + ((uint32_t)(32 * qi) << 16) + kEtTmT2 + 16 * buf;
@@ -754,7 +759,7 @@ eegnet_tc_kernel(const EegNet* __restrict__ net, const int8_t* __restrict__ x, l
         for (int i = 0; i < ntr; i++) {
             const long long b = first + (long long)i * stride;
             const int st = NXS == 1 ? 0 : (i & 1), xuse = NXS == 1 ? i : (i >> 1);       // NXS is 1 or 2
-            EWAIT(0, sbase + kEtXsEmpty + 8 * st, (xuse & 1) ^ 1);
+            EWAITS(0, sbase + kEtXsEmpty + 8 * st, (xuse & 1) ^ 1);
             uint8_t* xs = esm + sm.off_xs + st * xs_bytes + PL;
             const int8_t* xb = x + (size_t)b * C * T;
             const uint32_t bar = sbase + kEtXsFull + 8 * st;
