@@ -75,7 +75,16 @@ __host__ __device__ constexpr int tcr_l2_batches(int set) { return (8 - set + kR
 static_assert(kRAW % 4 == 0 && kRAW >= 4, "layer-1 epilogue warps come in sets of four");
 constexpr int kRWarpB = kRAW, kRWarpC = kRAW + kRBW, kRWarpR = kRWarpC + kRCW, kRWarpP = kRWarpR + kRRW,
               kRWarpM1 = kRWarpP + 1, kRWarpM2 = kRWarpP + 2;
-constexpr int kRThreads = (kRWarpM2 + 1) * 32;
+#ifndef MIBMI_TCR_ROW2
+#define MIBMI_TCR_ROW2 0                  // 1: realign warps keep the loads of two rows in flight (needs SETREG; r2o2: slower, 75.7 vs 84 M trials/s)
+#endif
+#ifndef MIBMI_TCR_SETREG
+#define MIBMI_TCR_SETREG 0                // 1 (r2o3: 89.8 vs 88.6 M trials/s in Wolf order, 83.1 vs 84.5 M in module order: off) = 32 warps: the producer / MMA warpgroup (+ one idle warp) shrinks to kRRegsPM registers, the realign warpgroup grows to
+#endif                                    // kRRegsR (setmaxnreg) and keeps the loads of two rows in flight
+constexpr bool kRSetReg = MIBMI_TCR_SETREG && (kRWarpM2 + 2 == 32) && kRWarpR % 4 == 0 && kRRW == 4;
+constexpr int kRRegsPM = 40, kRRegsR = 88;            // 64 - 24 and 64 + 24: four warps each
+constexpr int kRThreads = (kRWarpM2 + 1 + (MIBMI_TCR_SETREG ? 1 : 0)) * 32;
+static_assert(!MIBMI_TCR_SETREG || kRSetReg, "setmaxnreg needs whole warpgroups: 12 A + 8 B + 4 C warps, then R = warps 24-27, then P, M1, M2, idle");
 
 __host__ __device__ constexpr int tcr_pitch16(int n) { return n % 4 == 2 ? n : tcr_pitch16(n + 1); }   // smallest p >= n, p = 2 (mod 4)
 
@@ -183,21 +192,27 @@ struct TcrTail {
     static constexpr bool SPLIT = MIBMI_TCR_TAIL && TAILC > 0 && TAILC <= 8;
     static constexpr int RPT = SPLIT ? 32 / TAILC : 1;                           // rows per tail pass
 };
-template <class K, int K4>
-__device__ __forceinline__ void tcr_realign_row(const uint8_t* rbase, uint8_t* xrow, int c, int sh, int lane) {
-    constexpr int P = TcrTail<K>::SPLIT ? 2 : (K::CHUNKS + 31) / 32;
+template <class K>
+struct TcrRow {                                                                   // the aligned 32 bytes around every chunk of a row (lane = chunk)
+    static constexpr int P = TcrTail<K>::SPLIT ? 2 : (K::CHUNKS + 31) / 32;
     uint4 q0[P], q1[P];
+};
+template <class K>
+__device__ __forceinline__ void tcr_row_load(TcrRow<K>& r, const uint8_t* rbase, int lane) {
 #pragma unroll
-    for (int p = 0; p < P; p++)
+    for (int p = 0; p < TcrRow<K>::P; p++)
         if (32 * p + 31 < K::CHUNKS || lane + 32 * p < K::CHUNKS) {
-            q0[p] = tcr_lds128(rbase + 512 * p);          // kept 128 bits wide: the narrower loads the compiler would pick for
-            q1[p] = tcr_lds128(rbase + 512 * p + 16);     // the 5 words in use are 4-way bank conflicted at this lane stride
+            r.q0[p] = tcr_lds128(rbase + 512 * p);          // kept 128 bits wide: the narrower loads the compiler would pick for
+            r.q1[p] = tcr_lds128(rbase + 512 * p + 16);     // the 5 words in use are 4-way bank conflicted at this lane stride
         }
+}
+template <class K, int K4>
+__device__ __forceinline__ void tcr_row_store(const TcrRow<K>& r, uint8_t* xrow, int c, int sh, int lane) {
 #pragma unroll
-    for (int p = 0; p < P; p++) {
+    for (int p = 0; p < TcrRow<K>::P; p++) {
         const int jj = lane + 32 * p;
         if (32 * p + 31 < K::CHUNKS || jj < K::CHUNKS) {
-            const uint32_t w[8] = {q0[p].x, q0[p].y, q0[p].z, q0[p].w, q1[p].x, q1[p].y, q1[p].z, q1[p].w};
+            const uint32_t w[8] = {r.q0[p].x, r.q0[p].y, r.q0[p].z, r.q0[p].w, r.q1[p].x, r.q1[p].y, r.q1[p].z, r.q1[p].w};
             uint4 o;
             o.x = __funnelshift_r(w[K4], w[K4 + 1], sh);
             o.y = __funnelshift_r(w[K4 + 1], w[K4 + 2], sh);
@@ -205,6 +220,18 @@ __device__ __forceinline__ void tcr_realign_row(const uint8_t* rbase, uint8_t* x
             o.w = __funnelshift_r(w[K4 + 3], w[K4 + 4], sh);
             *reinterpret_cast<uint4*>(xrow + (jj >> 3) * K::TILE_PITCH + (((jj & 7) ^ (c & 7)) << 4)) = o;
         }
+    }
+}
+// WOLF = 0: one row of T samples: lane = 16-byte chunk (+ 32 per pass); all loads of the row are issued before the shifts
+template <class K>
+__device__ __forceinline__ void tcr_row_shift(const TcrRow<K>& r, uint8_t* xs, int c, int src0, int lane) {
+    const int sh = 8 * (src0 & 3);                         // warp-uniform byte shift, word shift below
+    uint8_t* xrow = xs + c * 128;
+    switch ((src0 >> 2) & 3) {
+        case 0: tcr_row_store<K, 0>(r, xrow, c, sh, lane); break;
+        case 1: tcr_row_store<K, 1>(r, xrow, c, sh, lane); break;
+        case 2: tcr_row_store<K, 2>(r, xrow, c, sh, lane); break;
+        default: tcr_row_store<K, 3>(r, xrow, c, sh, lane); break;
     }
 }
 
@@ -417,38 +444,9 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
             // batches of the third TMEM half meanwhile
             if (MIBMI_TCR_HELP && a3 == 0 && j == K::G - 1) l2_consume(kRL2Sets - 1, gq, 2, 2);
         }
-    } else if (warp == kRWarpP) {
-        // =====================================================================================
-        // P: one bulk copy per trial, from the 16-byte boundary below its first byte.  No byte outside the batch is
-        //    read: the copy of the LAST trial of the batch stops at the 16-byte boundary below its end and the lanes
-        //    fetch the remaining <= 15 bytes with byte loads
-        // =====================================================================================
-        const unsigned long long total = (unsigned long long)B * K::TRIAL_BYTES;
-        for (int n = 0; n < ntr; n++) {
-            const int st = n & 1;
-            RWAITL(0, sbase + K::BAR_RAW_EMPTY + 8 * st, ((n >> 1) & 1) ^ 1);
-            const long long b = trial_of(n);
-            const uint32_t bar = sbase + K::BAR_RAW_FULL + 8 * st;
-            if (b < B) {
-                const unsigned long long o = (unsigned long long)b * K::TRIAL_BYTES;
-                const unsigned long long a0 = o & ~15ull;
-                unsigned long long a1 = (o + K::TRIAL_BYTES + 15) & ~15ull;
-                if (a1 > total) {                                  // warp-uniform: only the last trial of the batch
-                    a1 = total & ~15ull;
-                    if (a1 + lane < total) smem[K::OFF_RAW + st * K::RAW_BYTES + (a1 - a0) + lane] = (uint8_t)x[a1 + lane];
-                    __syncwarp();                                  // the byte stores are ordered before lane 0's arrive (release)
-                }
-                if (lane == 0) {
-                    const uint32_t len = (uint32_t)(a1 - a0);
-                    mbar_expect_tx(bar, len);
-                    bulk_g2s(sbase + K::OFF_RAW + st * K::RAW_BYTES, x + a0, len, bar);
-                }
-            } else if (lane == 0) {
-                mbar_arrive(bar);     // padding trial of the last group: nothing to read
-            }
-            __syncwarp();
-        }
     } else if (warp >= kRWarpR && warp < kRWarpP) {
+        // the realign warps are one warpgroup: they take the registers the producer / MMA warpgroup gives up (two rows in flight)
+        if (MIBMI_TCR_SETREG) asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(kRRegsR));
         // =====================================================================================
         // R: raw bytes -> layer-1 operand tiles
         // =====================================================================================
@@ -489,16 +487,28 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
                 if (b < B) {
                     // [C][128 samples] tiles with the 128-byte swizzle (16-byte chunk j of row c at j ^ (c & 7))
                     uint8_t* xs = smem + K::OFF_XS + st * K::XS_BYTES;
-                    for (int c = rw; c < K::C; c += kRRW) {
-                        const int src0 = o15 + c * K::T;                       // first byte of the row in the raw stage
-                        const int sh = 8 * (src0 & 3);                         // warp-uniform byte shift, word shift below
-                        const uint8_t* rbase = raw + (src0 & ~15) + 16 * lane;
-                        uint8_t* xrow = xs + c * 128;
-                        switch ((src0 >> 2) & 3) {
-                            case 0: tcr_realign_row<K, 0>(rbase, xrow, c, sh, lane); break;
-                            case 1: tcr_realign_row<K, 1>(rbase, xrow, c, sh, lane); break;
-                            case 2: tcr_realign_row<K, 2>(rbase, xrow, c, sh, lane); break;
-                            default: tcr_realign_row<K, 3>(rbase, xrow, c, sh, lane); break;
+                    if (kRSetReg && MIBMI_TCR_ROW2) {
+                        // two rows in flight (88 registers): the loads of the next row are issued before the shifts of this one
+                        TcrRow<K> ra, rb;
+                        auto src_of = [&](int c) { return o15 + c * K::T; };
+                        auto base_of = [&](int c) { return raw + (src_of(c) & ~15) + 16 * lane; };
+                        tcr_row_load<K>(ra, base_of(rw), lane);
+#pragma unroll 1
+                        for (int c = rw; c < K::C; c += 2 * kRRW) {
+                            const bool two = c + kRRW < K::C;
+                            if (two) tcr_row_load<K>(rb, base_of(c + kRRW), lane);
+                            tcr_row_shift<K>(ra, xs, c, src_of(c), lane);
+                            if (two) {
+                                if (c + 2 * kRRW < K::C) tcr_row_load<K>(ra, base_of(c + 2 * kRRW), lane);
+                                tcr_row_shift<K>(rb, xs, c + kRRW, src_of(c + kRRW), lane);
+                            }
+                        }
+                    } else {
+                        for (int c = rw; c < K::C; c += kRRW) {
+                            const int src0 = o15 + c * K::T;                       // first byte of the row in the raw stage
+                            TcrRow<K> r;
+                            tcr_row_load<K>(r, raw + (src0 & ~15) + 16 * lane, lane);
+                            tcr_row_shift<K>(r, xs, c, src0, lane);
                         }
                     }
                     if (TcrTail<K>::SPLIT) {
@@ -540,7 +550,41 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
             if (lane == 0) mbar_arrive(sbase + K::BAR_RAW_EMPTY + 8 * st);
         }
     }
-    else if (warp == kRWarpM1) {
+    else if (warp >= kRWarpP) {
+        // P, M1, M2 (and the idle warp that completes the warpgroup) need few registers
+        if (MIBMI_TCR_SETREG) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRRegsPM));
+    if (warp == kRWarpP) {
+        // =====================================================================================
+        // P: one bulk copy per trial, from the 16-byte boundary below its first byte.  No byte outside the batch is
+        //    read: the copy of the LAST trial of the batch stops at the 16-byte boundary below its end and the lanes
+        //    fetch the remaining <= 15 bytes with byte loads
+        // =====================================================================================
+        const unsigned long long total = (unsigned long long)B * K::TRIAL_BYTES;
+        for (int n = 0; n < ntr; n++) {
+            const int st = n & 1;
+            RWAITL(0, sbase + K::BAR_RAW_EMPTY + 8 * st, ((n >> 1) & 1) ^ 1);
+            const long long b = trial_of(n);
+            const uint32_t bar = sbase + K::BAR_RAW_FULL + 8 * st;
+            if (b < B) {
+                const unsigned long long o = (unsigned long long)b * K::TRIAL_BYTES;
+                const unsigned long long a0 = o & ~15ull;
+                unsigned long long a1 = (o + K::TRIAL_BYTES + 15) & ~15ull;
+                if (a1 > total) {                                  // warp-uniform: only the last trial of the batch
+                    a1 = total & ~15ull;
+                    if (a1 + lane < total) smem[K::OFF_RAW + st * K::RAW_BYTES + (a1 - a0) + lane] = (uint8_t)x[a1 + lane];
+                    __syncwarp();                                  // the byte stores are ordered before lane 0's arrive (release)
+                }
+                if (lane == 0) {
+                    const uint32_t len = (uint32_t)(a1 - a0);
+                    mbar_expect_tx(bar, len);
+                    bulk_g2s(sbase + K::OFF_RAW + st * K::RAW_BYTES, x + a0, len, bar);
+                }
+            } else if (lane == 0) {
+                mbar_arrive(bar);     // padding trial of the last group: nothing to read
+            }
+            __syncwarp();
+        }
+    } else if (warp == kRWarpM1) {
         // =====================================================================================
         // M1: layer-1 MMAs, one per tile (K = 32 channels covers C)
         // =====================================================================================
@@ -577,11 +621,15 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
         // =====================================================================================
         constexpr uint32_t idesc = tcr_idesc_i8_kk(128, 32);
         const uint64_t da0 = umma_desc(sbase + K::OFF_Y1, 16, 256, 6), db0 = umma_desc(sbase + K::OFF_W2, 256, 128, 0);
-        const uint32_t a_hi = (uint32_t)(da0 >> 32), b_hi = (uint32_t)(db0 >> 32), b_lo0 = (uint32_t)db0, a_lo0 = (uint32_t)da0;
+        const uint32_t a_hi = (uint32_t)(da0 >> 32), b_hi = (uint32_t)(db0 >> 32), b_lo0_ = (uint32_t)db0, a_lo0_ = (uint32_t)da0;
         for (int gq = 0; gq < ng; gq++) {
 #pragma unroll
             for (int j = 0; j < K::G; j++) RWAIT(0, sbase + K::BAR_Y1_FULL + 8 * j, gq & 1);
             tc_fence_after();
+            // the descriptor words of the 48 instructions are immediates away from these two: keeping them opaque per group stops the
+            // compiler from hoisting 96 precomputed words out of the group loop (they would not fit the 40 registers of this warpgroup)
+            uint32_t a_lo0 = a_lo0_, b_lo0 = b_lo0_;
+            asm volatile("" : "+r"(a_lo0), "+r"(b_lo0));
 #pragma unroll
             for (int bt = 0; bt < 8; bt++) {
                 const int h = bt % kRL2Sets;                                // TMEM half = consumer set
@@ -604,6 +652,7 @@ tcr_forward_kernel(const int8_t* __restrict__ x, const PipeNet* __restrict__ net
                 __syncwarp();
             }
         }
+    }
     } else if (warp >= kRWarpB && warp < kRWarpC) {
         // =====================================================================================
         // B: layer-2 epilogue, consumer sets 0 and 1 (l2_consume above)

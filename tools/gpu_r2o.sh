@@ -1,15 +1,7 @@
-# round 2, call o: single-buffer kernel (cb75378) with the conflict-free y1 pitch
+# round 2: 22x1125 kernel with setmaxnreg (32 warps; realign warpgroup 88 registers, producer / MMA warpgroup 40)
 set -x
-O=gpurun_out/r2o; mkdir -p $O
-timeout 600 python -m pytest tests -m gpu -x -q -k "22 or tcr or wolf or unaligned or gather or taps" > $O/pytest_tcr.log 2>&1; tail -3 $O/pytest_tcr.log
-bench1() { timeout 200 python bench.py --steps 20 --warmup 5 --no-cpu-baseline --no-e2e --sustained-seconds 0 "$@" | python -c "import json,sys; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print(round(d['value']/1e6,2), round(d['roofline']['frac'],4), d['roofline']['kernel'], d['gpu_launches'], d['clocks']['sm_mhz'], d['clocks']['reasons'])"; }
-for i in 1 2; do
-  echo "== 22x1125 bct"; bench1 --shape 22x1125
-  echo "== 22x1125 btc"; bench1 --shape 22x1125 --layout btc
-done > $O/bench.txt 2>&1
-cat $O/bench.txt
-MIBMI_LIB_PATH=tools/variants/prof/libmibmi.so timeout 180 python tools/prof_tcr.py 22 1125 bct > $O/prof_bct.txt 2>&1; cat $O/prof_bct.txt
-MIBMI_LIB_PATH=tools/variants/prof/libmibmi.so timeout 180 python tools/prof_tcr.py 22 1125 btc > $O/prof_btc.txt 2>&1; cat $O/prof_btc.txt
-timeout 300 python bench.py --shape 22x1125 --steps 3 --warmup 3 --no-e2e --no-cpu-baseline --sustained-seconds 0 > $O/plain.log 2>&1 &&
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:tcr_forward -c 1 -s 4 -o $O/tcr_full -f python bench.py --shape 22x1125 --steps 3 --warmup 3 --no-e2e --no-cpu-baseline --sustained-seconds 0 > $O/ncu_tcr.log 2>&1
-tail -2 $O/ncu_tcr.log
+O=gpurun_out/r2o2; mkdir -p $O
+timeout 400 python -m pytest tests -m gpu -x -q -k "1125 or 22 or gather or graph" > $O/pytest_22.log 2>&1; tail -3 $O/pytest_22.log
+b() { timeout 200 python bench.py --shape 22x1125 --steps 20 --warmup 5 --no-cpu-baseline --no-e2e --sustained-seconds 0 "$@" | python -c "import json,sys; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print(round(d['value']/1e6,2), round(d['roofline']['frac'],4), d['clocks']['sm_mhz'], d['clocks']['reasons'])"; }
+b; b --layout btc; b; b --layout btc
+MIBMI_LIB_PATH=tools/variants/prof/libmibmi.so timeout 200 python tools/prof_tcr.py 22 1125 bct 2>&1 | tail -9
