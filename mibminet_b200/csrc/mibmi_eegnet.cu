@@ -524,7 +524,6 @@ __device__ __forceinline__ void et_layers345(const EegNet* __restrict__ net, con
     et_bar_sync_l();
 }
 
-template <int D>
 __global__ void __launch_bounds__(kEtThreads, 1)
 eegnet_tc_kernel(const EegNet* __restrict__ net, const int8_t* __restrict__ x, long long B, int8_t* __restrict__ logits,
                  int8_t* __restrict__ tap2, int8_t* __restrict__ tap3, int8_t* __restrict__ tap4) {
@@ -1149,7 +1148,7 @@ int mibmi_eegnet_forward_int8_taps(mibmi_eegnet_t* n, const int8_t* x_dev, int64
     const char* notc = getenv("MIBMI_EEGNET_TC");                          // experiment switch: "0" = the mma.sync kernel
     int which = 0;
     if (n->tc && !(notc && notc[0] == '0') && !(force && force[0] == '1')) {
-        auto kern = n->D == 1 ? eegnet_tc_kernel<1> : eegnet_tc_kernel<2>;
+        auto kern = eegnet_tc_kernel;        // D only shapes the block-diagonal operand of the second MMA (b2umma)
         if (e == cudaSuccess) e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)n->smem_tc);
         if (e == cudaSuccess) {
             long long grid = n->num_sms;
