@@ -149,6 +149,31 @@ def test_gpu_tcgen05_kernel_with_factors_outside_the_magic_range():
 
 
 @pytest.mark.gpu
+def test_gpu_forward_captured_in_a_cuda_graph():
+    """The EEGNet-order forward only launches (no allocation, no synchronisation): captured once, replayed on new buffer contents."""
+    sd, p, net, torch = _gpu_net(22, 1125, 8, 2, 128, seed=14)
+    B = 150                                          # more trials than SMs: the persistent CTAs of eegnet_tc_kernel loop
+    xs = [synth.make_trials(B, 22, 1125, seed=140 + i) for i in range(2)]
+    xd = torch.from_numpy(xs[0]).cuda()
+    stream = torch.cuda.Stream()
+    with torch.cuda.stream(stream):
+        net.forward(xd)                              # first call outside the capture (function attributes)
+    torch.cuda.synchronize()
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        y = net.forward(xd)
+    assert net.last_kernel == "eegnet_tc_kernel"
+    for x in xs:
+        ref = net.forward(torch.from_numpy(x).cuda()).cpu().numpy()       # a plain call on other buffers
+        xd.copy_(torch.from_numpy(x).cuda())
+        y.fill_(-77)
+        graph.replay()
+        torch.cuda.synchronize()
+        assert np.array_equal(y.cpu().numpy(), ref)
+        assert np.array_equal(ref[:24], eegnet_np.forward(p, x[:24]))
+
+
+@pytest.mark.gpu
 def test_gpu_saturating_inputs_and_empty_batch():
     sd, p, net, torch = _gpu_net(22, 1125, 8, 2, 128, seed=1)
     x = np.stack([np.full((22, 1125), 127, np.int8), np.full((22, 1125), -128, np.int8),
