@@ -217,7 +217,10 @@ MIBMI_API int64_t mibmi_debug_pack_pipe(const mibmi_params_t* params, void* out,
  * depthwise spatial conv -- replaces QuantLab/quantlab/PhysionetMMMI/EEGNet/eegnet.py:137-168 (EEGNet.forward) for
  * integer inference.  The reference tree has no integer model of this topology; semantics = the edgeEEGNet integer
  * pipeline's (golden_model.py:153-379, REORDER_BN form) applied to this layer order, see oracle/eegnet_np.py.
- * All weights in torch (cross-correlation) order, HOST pointers, copied by create. */
+ * All weights in torch (cross-correlation) order, HOST pointers, copied by create.
+ * Kernels (same bytes from all of them; mibmi_eegnet_last_kernel names the one that ran): F1 = 8 filters of Nf = 128 taps with
+ * C <= 64 (the QuantLab EEGNet configuration) run both contractions on tcgen05.mma with TMEM accumulators; Nf a multiple of 32
+ * otherwise on mma.sync; anything else on dp4a. */
 typedef struct {
     int32_t C, T;              /* EEG channels, samples per trial                                   */
     int32_t F1, D, F2, N;      /* F1 % 4 == 0, F1 <= 16, D in {1, 2}, F2 <= 32, N <= 8             */
