@@ -175,6 +175,34 @@ def test_fused_packing_tcgen05_operands(golden):
     assert np.array_equal(off1, sg * np.asarray(fx["arrays"]["l1_offset"]))
 
 
+_OFF_M3 = _OFF_C2 + 5 * 64 + 16 * 4 * 32 * 4                       # after thr2 .. sh2 and w3frag: m3, sh3
+
+
+def test_layer3_magic_is_exact_after_the_clip():
+    """PipeNet::m3 / sh3: the no-shift form (sh3 == 0, m3 = floor(2^32 / d) + 1) where it is proven, the shifted one otherwise; either
+    way clip8(tdiv_magic(x)) == clip8(trunc(x / d)) for every layer-3 accumulator the weights allow (brute force over the range)."""
+    import dataclasses
+    C, T = 64, 480
+    p0 = convert.params_from_state_dict(synth.make_state_dict(C=C, T=T, seed=3), C=C, T=T)
+    seen = set()
+    for fac3 in (4, 5, 7, 64, 255, 257, 1000, 4099, 65535, 65537, 1 << 20, -9, -300):
+        arrays = dict(p0.to_wolf_arrays())
+        arrays["l3_factor"] = np.int32(fac3)
+        blob, why = _pipe_blob(arrays, C, T)
+        assert blob is not None, why
+        m3, sh3 = (int(v) for v in blob[_OFF_M3:_OFF_M3 + 8].view(np.int32))
+        d = abs(fac3)
+        xmax = int(128 * np.abs(np.asarray(arrays["l3_weight"]).reshape(16, 16).astype(np.int64)).sum(axis=1).max())
+        x = np.arange(-xmax, xmax + 1, dtype=np.int64)
+        q = ((x * m3) >> 32 >> sh3) + (x < 0)
+        ref = np.sign(x) * (np.abs(x) // d)
+        assert np.array_equal(np.clip(q, -128, 127), np.clip(ref, -128, 127)), fac3
+        if sh3 == 0:
+            assert m3 == (1 << 32) // d + 1
+        seen.add(sh3 == 0)
+    assert seen == {True, False}          # both forms occur over these factors
+
+
 @pytest.mark.parametrize("C", [38, 24, 19, 8])
 def test_fused_packing_superrow_weights(C):
     """PipeNet::w1x, the block-structured layer-1 weights of the Wolf-order super-row form (rows of 40 / 24 / 20 / 8 bytes):
